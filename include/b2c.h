@@ -1,0 +1,159 @@
+/* b2c.h — C ABI of libb2c.so, the B200-native kernels behind the training hot path of
+ * aqualovers/pytorch-cifar (conv + BatchNorm + ReLU forward/backward, input augmentation, SGD).
+ *
+ * The reference has no FFI of its own: every arithmetic step on this path is a call from
+ * models/*.py / main.py into torch / torchvision. Each entry point below therefore
+ * cites the reference call site (file:line under the reference tree) whose library kernel it replaces.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is DEVICE memory unless it says "host";
+ *   - the caller owns every buffer, including scratch ("part_*", "partial"); nothing here allocates;
+ *   - `stream` is a cudaStream_t passed as void*; all work is asynchronous on it;
+ *   - activations are NHWC bf16; statistics, master weights, gradients of weights are fp32;
+ *   - return 0 on success; a negative value otherwise: -(cudaError_t) for CUDA runtime errors,
+ *     B2C_ERR_* below for argument / capability errors. Nothing throws, nothing falls back to a CPU or
+ *     library path: an unsupported shape is an error.
+ */
+#ifndef B2C_H_
+#define B2C_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B2C_API __attribute__((visibility("default")))
+#else
+#define B2C_API
+#endif
+
+#define B2C_ERR_UNSUPPORTED (-10001) /* shape / option outside what the kernels implement */
+#define B2C_ERR_DRIVER (-10002)      /* cuTensorMapEncodeTiled unavailable or failed */
+#define B2C_ERR_ARG (-10003)         /* null / misaligned / inconsistent argument */
+
+B2C_API int b2c_version(void);
+/* Human-readable text for a return code of this library (static storage). */
+B2C_API const char* b2c_error_string(int code);
+
+/* One convolution as the reference constructs it: nn.Conv2d(cin, cout, ksize, stride, padding=ksize/2,
+ * bias=False), models/resnet.py:23-27 (3x3) and :33-34 (1x1 shortcut). */
+typedef struct B2cConvDesc {
+    int n, h, w;     /* input batch / height / width; tensor is [n, h, w, cin] bf16 */
+    int cin, cout;   /* channel counts as laid out in memory, multiples of 64 */
+    int ksize;       /* 1 or 3 */
+    int stride;      /* 1 or 2 */
+    int cin_valid;   /* wgrad only: real input channels (<= cin); 0 means cin */
+    int kflat_cin;   /* wgrad only: >0 for the im2col'ed stem, whose `cin` axis is k = tap*kflat_cin + c */
+    int block_n;     /* GEMM N tile (64/128/256); 0 = choose */
+    int max_ctas;    /* persistent grid cap; 0 = 148 (one CTA per SM) */
+} B2cConvDesc;
+
+/* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)
+ * at models/resnet.py:47-48,102-103,132. `w_fprop` is bf16 [tap][cout][cin] (see b2c_repack_weights).
+ * If part_sum/part_sq are non-null the epilogue also writes per-CTA per-channel sums of y and y^2
+ * (fp32, rows*cout each, rows <= 148 returned in *stat_rows (host int)) for b2c_bn_finalize. */
+B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, void* y, float* part_sum,
+                   float* part_sq, int* stat_rows, void* stream);
+
+/* dx[n,h,w,cin] = conv_transpose(dy, w) (+ add_src). Replaces cudnn_convolution_backward_input reached
+ * from loss.backward(), main.py:104. `w_dgrad` is bf16 [tap][cin][cout]. add_src (optional, bf16, dx's
+ * shape) is added in the epilogue; for ksize==1 && stride==2 it must be NULL (dx is zero-filled first)
+ * or equal to dx (accumulate in place). */
+B2C_API int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
+                   void* stream);
+
+/* dw[cout,cin_valid,k,k] (fp32, OIHW = the reference's .grad layout) += sum over pixels of x * dy.
+ * Replaces cudnn_convolution_backward_weight, main.py:104. Accumulates with fp32 atomics: the caller
+ * zero-fills dw (optimizer.zero_grad(), main.py:101). */
+B2C_API int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, void* stream);
+
+/* Training-mode BatchNorm statistics -> per-channel scale/shift, saved mean/rstd, running-stat update.
+ * Replaces the statistics half of F.batch_norm for nn.BatchNorm2d, models/resnet.py:25,28,35,104.
+ * running_mean/var may be NULL (no update). count = n*h*w. */
+B2C_API int b2c_bn_finalize(const float* part_sum, const float* part_sq, int rows, int channels, float count,
+                    const float* gamma, const float* beta, float eps, float momentum, float* running_mean,
+                    float* running_var, float* scale, float* shift, float* save_mean, float* save_rstd,
+                    void* stream);
+
+/* Eval-mode BatchNorm: scale/shift from running statistics (net.eval(), main.py:118). */
+B2C_API int b2c_bn_eval_scale_shift(int channels, const float* gamma, const float* beta, const float* running_mean,
+                            const float* running_var, float eps, float* scale, float* shift, void* stream);
+
+/* out = act(y*scale + shift + residual'), residual' = res (identity shortcut) or res*res_scale+res_shift
+ * (conv shortcut's own BatchNorm). Replaces F.relu(bn(..)), `out += self.shortcut(x)`, F.relu(out),
+ * models/resnet.py:47-50. rows = n*h*w; tensors are [rows, channels] bf16. */
+B2C_API int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
+                     const float* res_scale, const float* res_shift, void* out, long long rows, int channels,
+                     int relu, void* stream);
+
+/* Number of partial rows b2c_bn_bwd_reduce writes for (rows, channels): size `partial` as
+ * rows_returned * 2 * channels floats. Host-only arithmetic. */
+B2C_API int b2c_bn_bwd_partial_rows(long long rows, int channels);
+
+/* BatchNorm(+ReLU) backward, reduction pass: per-channel sums of dz and dz*y with dz = dout*[act>0]
+ * (act NULL: dz = dout). If dz_out is non-NULL the masked gradient is stored there (may alias dout).
+ * Replaces the reductions of cudnn_batch_norm_backward + relu backward, main.py:104. */
+B2C_API int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
+                      int channels, float* partial, void* stream);
+
+/* Combine partial rows: dgamma, dbeta (fp32, written) and the coefficients of dy = A*dz + B*y + C. */
+B2C_API int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, float count, const float* gamma,
+                        const float* save_mean, const float* save_rstd, float* dgamma, float* dbeta, float* coef_a,
+                        float* coef_b, float* coef_c, void* stream);
+
+/* dy = A*dz + B*y + C per channel (bf16). */
+B2C_API int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,
+                     void* dy, long long rows, int channels, void* stream);
+
+/* Head: F.avg_pool2d(out, 4) -> view -> nn.Linear, models/resnet.py:137-139. act is [n, hw, channels]
+ * bf16; pooled [n, channels] and logits [n, classes] are fp32 outputs. */
+B2C_API int b2c_head_fwd(const void* act, int n, int hw, int channels, const float* weight, const float* bias,
+                 int classes, float* pooled, float* logits, void* stream);
+
+/* nn.CrossEntropyLoss() (mean), main.py:86,103: loss[0], dlogits = (softmax - onehot)/n, and the number of
+ * top-1 hits (main.py:108-110; may be NULL). target is int64. n <= 65536. */
+B2C_API int b2c_ce_loss(const float* logits, const long long* target, int n, int classes, float* dlogits, float* loss,
+                int* correct, void* stream);
+
+/* Backward of the head given dlogits: dact (bf16 [n,hw,channels]), dweight [classes,channels], dbias. */
+B2C_API int b2c_head_bwd(const float* dlogits, const float* pooled, const float* weight, int n, int hw, int channels,
+                 int classes, void* dact, float* dweight, float* dbias, void* stream);
+
+/* Input pipeline of main.py:30-35 on the GPU: RandomCrop(32, padding=4) + RandomHorizontalFlip + ToTensor
+ * + Normalize over a uint8 dataset [*,32,32,3] resident in HBM. idx[n] (int64) selects the sample,
+ * ijf[n*3..] (int8) = crop row i, crop col j (0..8), flip (0/1) drawn on the host exactly as torchvision
+ * draws them. mean/std are HOST pointers to 3 floats. */
+B2C_API int b2c_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out_nchw_f32, int n,
+                     const float* mean_host, const float* std_host, void* stream);
+/* Same pixels, written as the stem conv's GEMM operand: [n,32,32,64] bf16, k = (r*3+s)*3+c for k<27. */
+B2C_API int b2c_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out_im2col_bf16,
+                       int n, const float* mean_host, const float* std_host, void* stream);
+/* fp32 NCHW network input (what the reference DataLoader yields, main.py:99) -> stem GEMM operand. */
+B2C_API int b2c_stem_im2col(const float* x_nchw_f32, void* out_im2col_bf16, int n, void* stream);
+
+/* optim.SGD(...).step(), main.py:87-88,105, over one flat fp32 arena (n % 4 == 0, 16-byte aligned).
+ * hyper is a DEVICE array {lr, momentum, weight_decay, grad_scale, first_step(0/1)}. */
+B2C_API int b2c_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, const float* hyper,
+                 void* stream);
+
+/* One conv weight tensor in the fp32 master arena and where its bf16 operand copies go. */
+typedef struct B2cRepackEntry {
+    long long src_off; /* element offset of the OIHW fp32 tensor */
+    long long wf_off;  /* element offset of the fprop operand [tap][cout][cin_pad] */
+    long long wd_off;  /* element offset of the dgrad operand [tap][cin][cout]; <0: none */
+    int cout, cin, taps, cin_pad;
+    int kflat;         /* stem: fprop operand is [cout][cin_pad], k = tap*cin + c */
+    int pad_;
+} B2cRepackEntry;
+
+/* fp32 OIHW master weights (the reference's state_dict layout) -> bf16 GEMM operands, all convs in
+ * one launch. `table` is a DEVICE array of `entries` records. */
+B2C_API int b2c_repack_weights(const float* master, void* w_fprop_arena, void* w_dgrad_arena, const B2cRepackEntry* table,
+                       int entries, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2C_H_ */

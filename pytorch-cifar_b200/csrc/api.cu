@@ -1,0 +1,459 @@
+// api.cu — the extern "C" boundary of libb2c.so (declared in include/b2c.h).
+// Host-side only: validates arguments, derives the GEMM view of each convolution, encodes the TMA
+// tensor maps and launches the kernels on the caller's stream. No allocation, no synchronisation.
+#include "../../include/b2c.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <mutex>
+
+#include "b2c_elementwise.h"
+#include "b2c_kernels.h"
+
+namespace {
+
+using b2c::TapGemmParams;
+using b2c::WgradParams;
+
+inline int cuda_rc(cudaError_t e) { return e == cudaSuccess ? 0 : -static_cast<int>(e); }
+inline cudaStream_t as_stream(void* s) { return static_cast<cudaStream_t>(s); }
+
+// cuTensorMapEncodeTiled is a driver entry point; resolve it through the runtime so that the
+// library links (and loads on a machine without a GPU driver) with cudart alone.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess) {
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+        }
+    });
+    return fn;
+}
+
+// NHWC bf16 tensor [n, h, w, c] -> 4-D map, box {64 ch, bw, bh, bn} pixels, traversal stride `es` on w/h.
+int encode_nhwc(CUtensorMap* m, const void* base, int n, int h, int w, int c, int bw, int bh, int bn, int es) {
+    EncodeTiledFn enc = get_encode();
+    if (enc == nullptr) return B2C_ERR_DRIVER;
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(c), static_cast<cuuint64_t>(w), static_cast<cuuint64_t>(h),
+                          static_cast<cuuint64_t>(n)};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(c) * 2, static_cast<cuuint64_t>(w) * c * 2,
+                             static_cast<cuuint64_t>(h) * w * c * 2};
+    cuuint32_t box[4] = {64u, static_cast<cuuint32_t>(bw * es), static_cast<cuuint32_t>(bh * es),
+                         static_cast<cuuint32_t>(bn)};
+    cuuint32_t estr[4] = {1u, static_cast<cuuint32_t>(es), static_cast<cuuint32_t>(es), 1u};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : B2C_ERR_DRIVER;
+}
+
+// Row-major bf16 matrix [rows, cols] -> 2-D map, box {64 cols, brows}.
+int encode_2d(CUtensorMap* m, const void* base, long long rows, int cols, int brows) {
+    EncodeTiledFn enc = get_encode();
+    if (enc == nullptr) return B2C_ERR_DRIVER;
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(cols) * 2};
+    cuuint32_t box[2] = {64u, static_cast<cuuint32_t>(brows)};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : B2C_ERR_DRIVER;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// pixel grid (gH x gW per image) must tile into boxes of `px` pixels: full rows, whole images.
+bool grid_tiles(int gH, int gW, int px) {
+    if (gW < 1 || gH < 1 || gW > px || (px % gW) != 0) return false;
+    const int img = gH * gW;
+    return (img % px) == 0 || (px % img) == 0;
+}
+
+int pick_bn(int requested, int n_dim) {
+    if (requested != 0) return requested;
+    if (n_dim % 128 == 0) return 128;
+    return 64;
+}
+
+int check_conv(const B2cConvDesc* d) {
+    if (d == nullptr) return B2C_ERR_ARG;
+    if (d->n < 1 || d->h < 1 || d->w < 1) return B2C_ERR_ARG;
+    if (d->cin < 64 || d->cout < 64 || (d->cin % 64) != 0 || (d->cout % 64) != 0) return B2C_ERR_UNSUPPORTED;
+    if (d->ksize != 1 && d->ksize != 3) return B2C_ERR_UNSUPPORTED;
+    if (d->stride != 1 && d->stride != 2) return B2C_ERR_UNSUPPORTED;
+    if (d->stride == 2 && ((d->h & 1) || (d->w & 1))) return B2C_ERR_UNSUPPORTED;
+    if (d->block_n != 0 && d->block_n != 64 && d->block_n != 128 && d->block_n != 256) return B2C_ERR_ARG;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b2c_version(void) { return 100; }
+
+const char* b2c_error_string(int code) {
+    if (code == 0) return "success";
+    if (code == B2C_ERR_UNSUPPORTED) return "b2c: shape or option not supported by the sm_100a kernels";
+    if (code == B2C_ERR_DRIVER) return "b2c: cuTensorMapEncodeTiled unavailable or failed (no CUDA driver?)";
+    if (code == B2C_ERR_ARG) return "b2c: invalid argument (null, misaligned or inconsistent)";
+    if (code < 0) return cudaGetErrorString(static_cast<cudaError_t>(-code));
+    return "b2c: unknown code";
+}
+
+int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, void* y, float* part_sum,
+                   float* part_sq, int* stat_rows, void* stream) {
+    int rc = check_conv(d);
+    if (rc) return rc;
+    if (!x || !w_fprop || !y || !aligned16(x) || !aligned16(w_fprop) || !aligned16(y)) return B2C_ERR_ARG;
+    if ((part_sum == nullptr) != (part_sq == nullptr)) return B2C_ERR_ARG;
+    const int ho = d->h / d->stride, wo = d->w / d->stride;
+    if (!grid_tiles(ho, wo, 128)) return B2C_ERR_UNSUPPORTED;
+    const int bn = pick_bn(d->block_n, d->cout);
+    if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
+    const int taps = d->ksize * d->ksize;
+
+    TapGemmParams p = {};
+    p.m_total = d->n * ho * wo;
+    p.num_m_tiles = (p.m_total + 127) / 128;
+    p.num_n_tiles = d->cout / bn;
+    p.k_chunks = d->cin / 64;
+    p.num_taps = taps;
+    p.gH = ho;
+    p.gW = wo;
+    p.in_stride = d->stride;
+    for (int t = 0; t < taps; ++t) {
+        const int r = t / d->ksize, s = t % d->ksize;
+        p.tap_dh[t] = static_cast<int8_t>(r - d->ksize / 2);
+        p.tap_dw[t] = static_cast<int8_t>(s - d->ksize / 2);
+        p.tap_a[t] = 0;
+        p.tap_brow[t] = t * d->cout;
+    }
+    p.out = static_cast<__nv_bfloat16*>(y);
+    p.add_src = nullptr;
+    p.out_H = ho;
+    p.out_W = wo;
+    p.out_ld = d->cout;
+    p.sy = p.sx = 1;
+    p.py = p.px = 0;
+    p.part_sum = part_sum;
+    p.part_sq = part_sq;
+    p.cout = d->cout;
+
+    const int bh = (128 / wo) < ho ? (128 / wo) : ho;
+    const int bnb = 128 / (wo * bh);
+    CUtensorMap ma, mb;
+    rc = encode_nhwc(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
+    if (rc) return rc;
+    rc = encode_2d(&mb, w_fprop, static_cast<long long>(taps) * d->cout, d->cin, bn);
+    if (rc) return rc;
+    const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+    return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
+}
+
+int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
+                   void* stream) {
+    int rc = check_conv(d);
+    if (rc) return rc;
+    if (!dy || !w_dgrad || !dx || !aligned16(dy) || !aligned16(w_dgrad) || !aligned16(dx) || !aligned16(add_src))
+        return B2C_ERR_ARG;
+    const int ho = d->h / d->stride, wo = d->w / d->stride;
+    // GEMM: rows = dx pixels (per output phase for stride 2), N = cin, K = cout
+    const int bn = pick_bn(d->block_n, d->cin);
+    if (d->cin % bn) return B2C_ERR_UNSUPPORTED;
+    const int taps = d->ksize * d->ksize;
+    const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+    cudaStream_t st = as_stream(stream);
+
+    TapGemmParams p = {};
+    p.num_n_tiles = d->cin / bn;
+    p.k_chunks = d->cout / 64;
+    p.in_stride = 1;
+    p.out = static_cast<__nv_bfloat16*>(dx);
+    p.add_src = static_cast<const __nv_bfloat16*>(add_src);
+    p.out_H = d->h;
+    p.out_W = d->w;
+    p.out_ld = d->cin;
+    p.part_sum = nullptr;
+    p.part_sq = nullptr;
+    p.cout = d->cin;
+
+    CUtensorMap ma, mb;
+    rc = encode_2d(&mb, w_dgrad, static_cast<long long>(taps) * d->cin, d->cout, bn);
+    if (rc) return rc;
+
+    if (d->stride == 1) {
+        if (!grid_tiles(d->h, d->w, 128)) return B2C_ERR_UNSUPPORTED;
+        const int bh = (128 / d->w) < d->h ? (128 / d->w) : d->h;
+        const int bnb = 128 / (d->w * bh);
+        rc = encode_nhwc(&ma, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+        if (rc) return rc;
+        p.m_total = d->n * d->h * d->w;
+        p.num_m_tiles = (p.m_total + 127) / 128;
+        p.gH = d->h;
+        p.gW = d->w;
+        p.num_taps = taps;
+        for (int t = 0; t < taps; ++t) {
+            const int r = t / d->ksize, s = t % d->ksize;
+            p.tap_dh[t] = static_cast<int8_t>(d->ksize / 2 - r);
+            p.tap_dw[t] = static_cast<int8_t>(d->ksize / 2 - s);
+            p.tap_a[t] = 0;
+            p.tap_brow[t] = t * d->cin;
+        }
+        p.sy = p.sx = 1;
+        p.py = p.px = 0;
+        return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st));
+    }
+
+    // stride 2: one GEMM per output parity phase (ph, pw); dx[2i+ph, 2j+pw] only sees taps with
+    // r = ph+1 (mod 2), s = pw+1 (mod 2), reading dy[i + (ph+1-r)/2, j + (pw+1-s)/2].
+    if (!grid_tiles(ho, wo, 128)) return B2C_ERR_UNSUPPORTED;
+    const int bh = (128 / wo) < ho ? (128 / wo) : ho;
+    const int bnb = 128 / (wo * bh);
+    rc = encode_nhwc(&ma, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+    if (rc) return rc;
+    p.m_total = d->n * ho * wo;
+    p.num_m_tiles = (p.m_total + 127) / 128;
+    p.gH = ho;
+    p.gW = wo;
+    p.sy = p.sx = 2;
+    if (d->ksize == 1) {
+        if (add_src != nullptr && add_src != dx) return B2C_ERR_UNSUPPORTED;
+        if (add_src == nullptr) {
+            cudaError_t e = cudaMemsetAsync(dx, 0, static_cast<size_t>(d->n) * d->h * d->w * d->cin * 2, st);
+            if (e != cudaSuccess) return cuda_rc(e);
+        }
+        p.num_taps = 1;
+        p.tap_dh[0] = 0;
+        p.tap_dw[0] = 0;
+        p.tap_a[0] = 0;
+        p.tap_brow[0] = 0;
+        p.py = p.px = 0;
+        return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st));
+    }
+    for (int ph = 0; ph < 2; ++ph) {
+        for (int pw = 0; pw < 2; ++pw) {
+            int nt = 0;
+            for (int r = 0; r < 3; ++r) {
+                if (((ph + 1 - r) & 1) != 0) continue;
+                for (int s = 0; s < 3; ++s) {
+                    if (((pw + 1 - s) & 1) != 0) continue;
+                    p.tap_dh[nt] = static_cast<int8_t>((ph + 1 - r) / 2);
+                    p.tap_dw[nt] = static_cast<int8_t>((pw + 1 - s) / 2);
+                    p.tap_a[nt] = 0;
+                    p.tap_brow[nt] = (r * 3 + s) * d->cin;
+                    ++nt;
+                }
+            }
+            p.num_taps = nt;
+            p.py = ph;
+            p.px = pw;
+            cudaError_t e = b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st);
+            if (e != cudaSuccess) return cuda_rc(e);
+        }
+    }
+    return 0;
+}
+
+int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, void* stream) {
+    int rc = check_conv(d);
+    if (rc) return rc;
+    if (!x || !dy || !dw || !aligned16(x) || !aligned16(dy)) return B2C_ERR_ARG;
+    const int ho = d->h / d->stride, wo = d->w / d->stride;
+    if (!grid_tiles(ho, wo, 64)) return B2C_ERR_UNSUPPORTED;
+    const int bn = pick_bn(d->block_n, d->cout);
+    if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
+    const int taps = d->ksize * d->ksize;
+    const int cin_valid = d->cin_valid > 0 ? d->cin_valid : d->cin;
+    if (cin_valid > d->cin) return B2C_ERR_ARG;
+    if (d->kflat_cin > 0 && (taps != 1 || (cin_valid % d->kflat_cin) != 0)) return B2C_ERR_ARG;
+
+    WgradParams p = {};
+    const long long pixels = static_cast<long long>(d->n) * ho * wo;
+    p.k_chunks_total = static_cast<int>((pixels + 63) / 64);
+    p.cin_blocks = d->cin / 64;
+    p.num_slabs = taps * p.cin_blocks;
+    p.num_m_blocks = (p.num_slabs + 1) / 2;
+    p.num_n_tiles = d->cout / bn;
+    const int tiles = p.num_m_blocks * p.num_n_tiles;
+    const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+    int splits = max_ctas / tiles;
+    if (splits < 1) splits = 1;
+    if (splits > p.k_chunks_total) splits = p.k_chunks_total;
+    p.chunks_per_split = (p.k_chunks_total + splits - 1) / splits;
+    p.splits = (p.k_chunks_total + p.chunks_per_split - 1) / p.chunks_per_split;
+    p.gH = ho;
+    p.gW = wo;
+    p.in_stride = d->stride;
+    p.num_taps = taps;
+    for (int t = 0; t < taps; ++t) {
+        const int r = t / d->ksize, s = t % d->ksize;
+        p.tap_dh[t] = static_cast<int8_t>(r - d->ksize / 2);
+        p.tap_dw[t] = static_cast<int8_t>(s - d->ksize / 2);
+    }
+    p.cin = d->cin;
+    p.cout = d->cout;
+    p.cin_valid = cin_valid;
+    p.kflat_cin = d->kflat_cin;
+    p.dw = dw;
+    if (d->kflat_cin > 0) {
+        // dw is [cout, kflat_cin, kk, kk] with kk*kk = cin_valid / kflat_cin flattened taps
+        const int ftaps = cin_valid / d->kflat_cin;
+        p.o_stride = static_cast<long long>(cin_valid);
+        p.c_stride = ftaps;
+        p.t_stride = 1;
+    } else {
+        p.o_stride = static_cast<long long>(cin_valid) * taps;
+        p.c_stride = taps;
+        p.t_stride = 1;
+    }
+
+    const int bh = (64 / wo) < ho ? (64 / wo) : ho;
+    const int bnb = 64 / (wo * bh);
+    CUtensorMap mx, mdy;
+    rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
+    if (rc) return rc;
+    rc = encode_nhwc(&mdy, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+    if (rc) return rc;
+    return cuda_rc(b2c::launch_wgrad(bn, mx, mdy, p, as_stream(stream)));
+}
+
+int b2c_bn_finalize(const float* part_sum, const float* part_sq, int rows, int channels, float count,
+                    const float* gamma, const float* beta, float eps, float momentum, float* running_mean,
+                    float* running_var, float* scale, float* shift, float* save_mean, float* save_rstd,
+                    void* stream) {
+    if (!part_sum || !part_sq || !gamma || !beta || !scale || !shift || !save_mean || !save_rstd || rows < 1 ||
+        channels < 1 || count <= 0.f)
+        return B2C_ERR_ARG;
+    if ((running_mean == nullptr) != (running_var == nullptr)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_bn_finalize(part_sum, part_sq, rows, channels, count, gamma, beta, eps, momentum,
+                                           running_mean, running_var, scale, shift, save_mean, save_rstd,
+                                           as_stream(stream)));
+}
+
+int b2c_bn_eval_scale_shift(int channels, const float* gamma, const float* beta, const float* running_mean,
+                            const float* running_var, float eps, float* scale, float* shift, void* stream) {
+    if (!gamma || !beta || !running_mean || !running_var || !scale || !shift || channels < 1) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_bn_eval_scale_shift(channels, gamma, beta, running_mean, running_var, eps, scale,
+                                                   shift, as_stream(stream)));
+}
+
+int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
+                     const float* res_scale, const float* res_shift, void* out, long long rows, int channels,
+                     int relu, void* stream) {
+    if (!y || !scale || !shift || !out || rows < 0 || channels < 8 || (channels & 7)) return B2C_ERR_ARG;
+    if (!aligned16(y) || !aligned16(out) || !aligned16(res) || !aligned16(scale) || !aligned16(shift))
+        return B2C_ERR_ARG;
+    if ((res_scale == nullptr) != (res_shift == nullptr)) return B2C_ERR_ARG;
+    if (res_scale != nullptr && res == nullptr) return B2C_ERR_ARG;
+    if (rows == 0) return 0;
+    return cuda_rc(b2c::launch_bn_act_apply(y, scale, shift, res, res_scale, res_shift, out, rows, channels, relu,
+                                            as_stream(stream)));
+}
+
+int b2c_bn_bwd_partial_rows(long long rows, int channels) {
+    if (channels < 8 || (channels & 7) || (256 % (channels >> 3)) != 0) return B2C_ERR_UNSUPPORTED;
+    return b2c::bn_bwd_partial_rows(rows, channels);
+}
+
+int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
+                      int channels, float* partial, void* stream) {
+    if (!dout || !y || !partial || rows < 1) return B2C_ERR_ARG;
+    if (channels < 8 || (channels & 7) || (channels >> 3) > 256 || (256 % (channels >> 3)) != 0)
+        return B2C_ERR_UNSUPPORTED;
+    if (!aligned16(dout) || !aligned16(act) || !aligned16(y) || !aligned16(dz_out)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, as_stream(stream)));
+}
+
+int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, float count, const float* gamma,
+                        const float* save_mean, const float* save_rstd, float* dgamma, float* dbeta, float* coef_a,
+                        float* coef_b, float* coef_c, void* stream) {
+    if (!partial || !gamma || !save_mean || !save_rstd || !dgamma || !dbeta || !coef_a || !coef_b || !coef_c ||
+        partial_rows < 1 || channels < 1 || count <= 0.f)
+        return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_bn_bwd_finalize(partial, partial_rows, channels, count, gamma, save_mean, save_rstd,
+                                               dgamma, dbeta, coef_a, coef_b, coef_c, as_stream(stream)));
+}
+
+int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,
+                     void* dy, long long rows, int channels, void* stream) {
+    if (!dz || !y || !coef_a || !coef_b || !coef_c || !dy || rows < 0 || channels < 8 || (channels & 7))
+        return B2C_ERR_ARG;
+    if (!aligned16(dz) || !aligned16(y) || !aligned16(dy)) return B2C_ERR_ARG;
+    if (rows == 0) return 0;
+    return cuda_rc(b2c::launch_bn_bwd_apply(dz, y, coef_a, coef_b, coef_c, dy, rows, channels, as_stream(stream)));
+}
+
+int b2c_head_fwd(const void* act, int n, int hw, int channels, const float* weight, const float* bias,
+                 int classes, float* pooled, float* logits, void* stream) {
+    if (!act || !weight || !bias || !pooled || !logits || n < 1 || hw < 1 || classes < 1) return B2C_ERR_ARG;
+    if (channels > 1024 || (channels & 31)) return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_head_fwd(act, n, hw, channels, weight, bias, classes, pooled, logits,
+                                        as_stream(stream)));
+}
+
+int b2c_ce_loss(const float* logits, const long long* target, int n, int classes, float* dlogits, float* loss,
+                int* correct, void* stream) {
+    if (!logits || !target || !dlogits || !loss || n < 1 || n > 65536 || classes < 1) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_ce_loss(logits, target, n, classes, dlogits, loss, correct, as_stream(stream)));
+}
+
+int b2c_head_bwd(const float* dlogits, const float* pooled, const float* weight, int n, int hw, int channels,
+                 int classes, void* dact, float* dweight, float* dbias, void* stream) {
+    if (!dlogits || !pooled || !weight || !dact || !dweight || !dbias || n < 1 || hw < 1 || classes < 1)
+        return B2C_ERR_ARG;
+    if (channels > 1024 || (channels & 31)) return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, dbias,
+                                        as_stream(stream)));
+}
+
+int b2c_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out_nchw_f32, int n,
+                     const float* mean_host, const float* std_host, void* stream) {
+    if (!data || !idx || !ijf || !out_nchw_f32 || !mean_host || !std_host || n < 0 || !aligned16(data))
+        return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_augment_nchw(data, idx, ijf, out_nchw_f32, n, mean_host, std_host, as_stream(stream)));
+}
+
+int b2c_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out_im2col_bf16,
+                       int n, const float* mean_host, const float* std_host, void* stream) {
+    if (!data || !idx || !ijf || !out_im2col_bf16 || !mean_host || !std_host || n < 0 || !aligned16(data) ||
+        !aligned16(out_im2col_bf16))
+        return B2C_ERR_ARG;
+    return cuda_rc(
+        b2c::launch_augment_im2col(data, idx, ijf, out_im2col_bf16, n, mean_host, std_host, as_stream(stream)));
+}
+
+int b2c_stem_im2col(const float* x_nchw_f32, void* out_im2col_bf16, int n, void* stream) {
+    if (!x_nchw_f32 || !out_im2col_bf16 || n < 0 || !aligned16(out_im2col_bf16)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_stem_im2col(x_nchw_f32, out_im2col_bf16, n, as_stream(stream)));
+}
+
+int b2c_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, const float* hyper,
+                 void* stream) {
+    if (!param || !grad || !momentum_buf || !hyper || n < 0 || (n & 3) || !aligned16(param) || !aligned16(grad) ||
+        !aligned16(momentum_buf))
+        return B2C_ERR_ARG;
+    if (n == 0) return 0;
+    return cuda_rc(b2c::launch_sgd(param, grad, momentum_buf, n, hyper, as_stream(stream)));
+}
+
+int b2c_repack_weights(const float* master, void* w_fprop_arena, void* w_dgrad_arena, const B2cRepackEntry* table,
+                       int entries, void* stream) {
+    static_assert(sizeof(B2cRepackEntry) == sizeof(b2c::RepackEntry), "ABI struct mismatch");
+    if (!master || !w_fprop_arena || !table || entries < 0) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_repack(master, w_fprop_arena, w_dgrad_arena,
+                                      reinterpret_cast<const b2c::RepackEntry*>(table), entries,
+                                      as_stream(stream)));
+}
+
+}  // extern "C"

@@ -1,0 +1,51 @@
+// b2c_elementwise.h — internal launch interface for the HBM-bound kernels (elementwise.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2c {
+
+// One conv weight tensor in the flat fp32 master arena and where its bf16 operand copies go.
+// Mirrors B2cRepackEntry in include/b2c.h (same field order and types).
+struct RepackEntry {
+    long long src_off;  // element offset of the OIHW fp32 tensor in the master arena
+    long long wf_off;   // element offset of the fprop operand [tap][cout][cin_pad] in the bf16 arena
+    long long wd_off;   // element offset of the dgrad operand [tap][cin][cout]; < 0: none
+    int cout, cin, taps, cin_pad;
+    int kflat;          // stem: fprop operand is [cout][cin_pad] with k = tap*cin + c
+    int pad_;
+};
+
+cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int rows, int C, float count,
+                               const float* gamma, const float* beta, float eps, float momentum,
+                               float* running_mean, float* running_var, float* scale, float* shift, float* mean,
+                               float* rstd, cudaStream_t s);
+cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* beta, const float* rm,
+                                       const float* rv, float eps, float* scale, float* shift, cudaStream_t s);
+cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
+                                const float* res_scale, const float* res_shift, void* out, long long rows, int C,
+                                int relu, cudaStream_t s);
+int bn_bwd_partial_rows(long long rows, int C);
+cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
+                                 int C, float* partial, cudaStream_t s);
+cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float count, const float* gamma,
+                                   const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
+                                   float* coefB, float* coefC, cudaStream_t s);
+cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coefA, const float* coefB,
+                                const float* coefC, void* dy, long long rows, int C, cudaStream_t s);
+cudaError_t launch_head_fwd(const void* act, int N, int hw, int C, const float* W, const float* bias, int K,
+                            float* pooled, float* logits, cudaStream_t s);
+cudaError_t launch_ce_loss(const float* logits, const long long* target, int N, int K, float* dlogits, float* loss,
+                           int* correct, cudaStream_t s);
+cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const float* W, int N, int hw, int C, int K,
+                            void* dact, float* dW, float* db, cudaStream_t s);
+cudaError_t launch_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out, int N,
+                                const float* mean, const float* stdv, cudaStream_t s);
+cudaError_t launch_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out, int N,
+                                  const float* mean, const float* stdv, cudaStream_t s);
+cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s);
+cudaError_t launch_sgd(float* p, const float* g, float* buf, long long n, const float* hyper, cudaStream_t s);
+cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackEntry* table_dev, int entries,
+                          cudaStream_t s);
+
+}  // namespace b2c

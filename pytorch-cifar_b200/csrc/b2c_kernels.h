@@ -1,0 +1,64 @@
+// b2c_kernels.h — internal (C++) launch interface between the C-ABI layer (api.cu) and the
+// kernel translation units. Not part of the public boundary; see include/b2c.h for that.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+namespace b2c {
+
+constexpr int kMaxTaps = 12;
+
+// One "tap GEMM": D[pixel, cout] = sum_t A_t[pixel + shift_t, :] . B_t[cout, :]^T
+// covers conv fprop (3x3 / 1x1, stride 1 / 2) and dgrad (stride 1, and stride 2 by output phase).
+struct TapGemmParams {
+    int m_total;      // valid GEMM rows (pixels of the GEMM grid = n * gH * gW)
+    int num_m_tiles;  // ceil(m_total / 128)
+    int num_n_tiles;  // cout / BN
+    int k_chunks;     // 64-channel chunks of the reduction per tap
+    int num_taps;
+    int gH, gW;       // pixel grid of the GEMM rows (j fastest, then i, then image)
+    int in_stride;    // A coordinate = grid coordinate * in_stride + tap offset
+    int8_t tap_dh[kMaxTaps];
+    int8_t tap_dw[kMaxTaps];
+    uint8_t tap_a[kMaxTaps];   // which A tensor map (0 or 1) the tap reads
+    int tap_brow[kMaxTaps];    // first row of the tap's weight slab in the B matrix
+    // epilogue
+    __nv_bfloat16* out;
+    const __nv_bfloat16* add_src;  // optional, same addressing as out
+    int out_H, out_W, out_ld;      // output tensor pixel dims and channel pitch
+    int sy, sx, py, px;            // output pixel = (i * sy + py, j * sx + px)
+    float* part_sum;               // optional [stat_rows][cout] per-CTA column sums (stat_rows <= 148)
+    float* part_sq;                // optional [stat_rows][cout] per-CTA column sums of squares
+    int cout;
+};
+
+// wgrad: dW[cout, cin, tap] += sum_pixels dY[pixel, cout] * X[pixel + shift_tap, cin]
+// D rows = two 64-channel (tap, cin-block) slabs, D cols = cout tile, reduction = pixels.
+struct WgradParams {
+    int k_chunks_total;   // ceil(pixels / 64)
+    int splits;           // split-K factor; CTA handles chunks [s*per, min((s+1)*per, total))
+    int chunks_per_split;
+    int num_m_blocks;     // ceil(num_slabs / 2)
+    int num_n_tiles;      // cout / BN
+    int num_slabs;        // taps * cin/64
+    int cin_blocks;       // cin / 64
+    int gH, gW;           // dY pixel grid
+    int in_stride;
+    int8_t tap_dh[kMaxTaps];
+    int8_t tap_dw[kMaxTaps];
+    int num_taps;
+    int cin, cout;
+    int cin_valid;        // real input channels (stem: 27 of 64)
+    int kflat_cin;        // >0: the cin axis is k = tap*kflat_cin + c (im2col'ed stem); address from (c, tap)
+    float* dw;            // fp32 gradient, element (o, c, t) at o*o_stride + c*c_stride + t*t_stride
+    long long o_stride, c_stride, t_stride;
+};
+
+cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                            const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream);
+cudaError_t launch_wgrad(int bn, const CUtensorMap& x, const CUtensorMap& dy, const WgradParams& p,
+                         cudaStream_t stream);
+
+}  // namespace b2c

@@ -1,0 +1,299 @@
+// conv_gemm.cu — implicit-GEMM convolution forward / data-gradient on tcgen05 tensor cores.
+//
+// Replaces what `nn.Conv2d.forward` and its autograd dgrad resolve to in the reference
+// (models/resnet.py:23-27,33-34,102-103; models/vgg.py:33; models/preact_resnet.py:19,21,70 and
+// `loss.backward()` main.py:104), i.e. cuDNN / oneDNN library kernels. Here: one persistent,
+// warp-specialised sm_100a kernel.
+//
+//   GEMM view      D[pixel, cout] = sum_{tap, cin} A[pixel shifted by tap, cin] * W[tap][cout, cin]
+//   A operand      NHWC bf16 activations; one TMA 4-D box {64 ch, gW, Hb, Nb} = 128 pixels per k-step,
+//                  shifted by the tap offset; out-of-image taps are zero-filled by the TMA unit
+//                  (this is the conv's zero padding), stride-2 convs use the TMA traversal stride.
+//   B operand      weights as [tap][cout][cin] bf16 (fprop) or [tap][cin][cout] (dgrad): 2-D TMA box.
+//   accumulators   fp32 in TMEM, double buffered (2 x BN columns) so the epilogue of tile i overlaps
+//                  the mainloop of tile i+1.
+//   epilogue       tcgen05.ld -> optional residual add -> bf16 NHWC store, plus per-tile per-channel
+//                  sum / sum-of-squares (fp32, taken before rounding) for the following BatchNorm.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..5 = epilogue (one TMEM lane quarter each).
+#include "b2c_kernels.h"
+#include "b2c_ptx.cuh"
+
+namespace b2c {
+
+namespace {
+
+constexpr int kBM = 128;            // GEMM rows (pixels) per tile
+constexpr int kABytes = kBM * 128;  // 128 rows x 64 bf16
+
+template <int BN>
+struct TapCfg {
+    static constexpr int kBBytes = BN * 128;
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = BN == 64 ? 8 : (BN == 128 ? 6 : 4);
+    static constexpr int kTmemCols = 2 * BN;
+    static constexpr int kBarBytes = 256;                       // (2*stages + 4) mbarriers + tmem ptr
+    static constexpr int kStatBytes = 2 * 4 * BN * 4;           // [sum|sq][quarter][BN] fp32 running sums
+    static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes + kStatBytes;
+};
+
+template <int BN, bool kStats>
+__global__ void __launch_bounds__(192, 1)
+tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+                const __grid_constant__ CUtensorMap mapB, const __grid_constant__ TapGemmParams p) {
+    using Cfg = TapCfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* aux = smem + Cfg::kStages * Cfg::kStageBytes;
+    uint64_t* full = reinterpret_cast<uint64_t*>(aux);
+    uint64_t* empty = full + Cfg::kStages;
+    uint64_t* tfull = empty + Cfg::kStages;
+    uint64_t* tempty = tfull + 2;
+    uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
+    float* stat = reinterpret_cast<float*>(aux + Cfg::kBarBytes);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&mapA0);
+        tma_prefetch_desc(&mapA1);
+        tma_prefetch_desc(&mapB);
+    }
+    if (warp == 1) {
+        if (lane == 0) {
+            for (int s = 0; s < Cfg::kStages; ++s) {
+                mbar_init(&full[s], 1);
+                mbar_init(&empty[s], 1);
+            }
+            mbar_init(&tfull[0], 1);
+            mbar_init(&tfull[1], 1);
+            mbar_init(&tempty[0], 4);
+            mbar_init(&tempty[1], 4);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc<Cfg::kTmemCols>(tmem_ptr);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_ptr;
+
+    const int total_tiles = p.num_m_tiles * p.num_n_tiles;
+    const int k_iters = p.num_taps * p.k_chunks;
+    const int img = p.gH * p.gW;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            // ------------------------------ TMA producer ------------------------------
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int m_tile = tile / p.num_n_tiles;
+                const int n_tile = tile - m_tile * p.num_n_tiles;
+                const int p0 = m_tile * kBM;
+                const int n0 = p0 / img;
+                const int h0 = (p0 - n0 * img) / p.gW;
+                for (int t = 0; t < p.num_taps; ++t) {
+                    const CUtensorMap* ma = p.tap_a[t] ? &mapA1 : &mapA0;
+                    const int cw = p.tap_dw[t];
+                    const int ch = h0 * p.in_stride + p.tap_dh[t];
+                    const int brow = p.tap_brow[t] + n_tile * BN;
+                    for (int kc = 0; kc < p.k_chunks; ++kc) {
+                        mbar_wait(&empty[stage], phase ^ 1u, 1);
+                        mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+                        uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                        tma_load_4d(sa, ma, &full[stage], kc * 64, cw, ch, n0);
+                        tma_load_2d(sa + kABytes, &mapB, &full[stage], kc * 64, brow);
+                        if (++stage == Cfg::kStages) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // ------------------------------ MMA issuer --------------------------------
+            constexpr uint32_t idesc = make_idesc_bf16(kBM, BN, 0, 0);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                mbar_wait(&tempty[acc], acc_phase ^ 1u, 2);
+                tc_fence_after();
+                const uint32_t d = tmem_base + static_cast<uint32_t>(acc * BN);
+                for (int it = 0; it < k_iters; ++it) {
+                    mbar_wait(&full[stage], phase, 3);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+                    const uint64_t ad = make_smem_desc_sw128(sa, 16, 1024);
+                    const uint64_t bd = make_smem_desc_sw128(sa + kABytes, 16, 1024);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        // advance 16 bf16 = 32 B along K inside the 128 B swizzle span
+                        umma_bf16(d, ad + 2u * k, bd + 2u * k, idesc, (it | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty[stage]);
+                    if (++stage == Cfg::kStages) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+                umma_commit(&tfull[acc]);
+                if (++acc == 2) {
+                    acc = 0;
+                    acc_phase ^= 1u;
+                }
+            }
+        }
+    } else {
+        // ---------------------------------- epilogue --------------------------------------
+        const int q = warp & 3;  // TMEM lane quarter this warp may read
+        const int row = q * 32 + lane;
+        const int et = threadIdx.x - 64;  // 0..127
+        if (kStats) {
+            // each (quarter, column) slot is owned by exactly one thread: no sync needed to clear it
+            for (int c = lane; c < BN; c += 32) {
+                stat[(0 * 4 + q) * BN + c] = 0.f;
+                stat[(1 * 4 + q) * BN + c] = 0.f;
+            }
+        }
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int m_tile = tile / p.num_n_tiles;
+            const int n_tile = tile - m_tile * p.num_n_tiles;
+            mbar_wait(&tfull[acc], acc_phase, 4);
+            tc_fence_after();
+            const int pix = m_tile * kBM + row;
+            const bool valid = pix < p.m_total;
+            const int n = pix / img;
+            const int rem = pix - n * img;
+            const int i = rem / p.gW;
+            const int j = rem - i * p.gW;
+            const size_t off =
+                (static_cast<size_t>(n * p.out_H + i * p.sy + p.py) * p.out_W + (j * p.sx + p.px)) * p.out_ld +
+                static_cast<size_t>(n_tile) * BN;
+            float* st = stat;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                float v[32];
+                tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                  static_cast<uint32_t>(acc * BN + c * 32),
+                              v);
+                if (valid) {
+                    if (p.add_src != nullptr) {
+                        const uint4* src = reinterpret_cast<const uint4*>(p.add_src + off + c * 32);
+#pragma unroll
+                        for (int g = 0; g < 4; ++g) {
+                            const uint4 u = __ldg(src + g);
+                            v[g * 8 + 0] += bf16lo(u.x);
+                            v[g * 8 + 1] += bf16hi(u.x);
+                            v[g * 8 + 2] += bf16lo(u.y);
+                            v[g * 8 + 3] += bf16hi(u.y);
+                            v[g * 8 + 4] += bf16lo(u.z);
+                            v[g * 8 + 5] += bf16hi(u.z);
+                            v[g * 8 + 6] += bf16lo(u.w);
+                            v[g * 8 + 7] += bf16hi(u.w);
+                        }
+                    }
+                    uint4* dst = reinterpret_cast<uint4*>(p.out + off + c * 32);
+#pragma unroll
+                    for (int g = 0; g < 4; ++g) {
+                        uint4 u;
+                        u.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
+                        u.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
+                        u.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
+                        u.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
+                        dst[g] = u;
+                    }
+                }
+                if (kStats) {
+                    // rows past m_total were zero-filled by TMA, so they add nothing
+                    float sq[32];
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) sq[e] = v[e] * v[e];
+                    const float s1 = warp_colsum32(v, lane);
+                    const float s2 = warp_colsum32(sq, lane);
+                    st[(0 * 4 + q) * BN + c * 32 + lane] += s1;
+                    st[(1 * 4 + q) * BN + c * 32 + lane] += s2;
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[acc]);
+            if (++acc == 2) {
+                acc = 0;
+                acc_phase ^= 1u;
+            }
+        }
+        if (kStats) {
+            // gridDim.x is a multiple of num_n_tiles (see launch_one), so every tile of this CTA had
+            // the same n_tile: one partial row per CTA, P = gridDim.x / num_n_tiles rows in all.
+            named_bar_sync(1, 128);
+            const int n_tile = blockIdx.x % p.num_n_tiles;
+            const int prow = blockIdx.x / p.num_n_tiles;
+            for (int col = et; col < BN; col += 128) {
+                const float s1 = stat[(0 * 4 + 0) * BN + col] + stat[(0 * 4 + 1) * BN + col] +
+                                 stat[(0 * 4 + 2) * BN + col] + stat[(0 * 4 + 3) * BN + col];
+                const float s2 = stat[(1 * 4 + 0) * BN + col] + stat[(1 * 4 + 1) * BN + col] +
+                                 stat[(1 * 4 + 2) * BN + col] + stat[(1 * 4 + 3) * BN + col];
+                const size_t o = static_cast<size_t>(prow) * p.cout + n_tile * BN + col;
+                p.part_sum[o] = s1;
+                p.part_sq[o] = s2;
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+template <int BN, bool kStats>
+cudaError_t launch_one(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                       const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream) {
+    using Cfg = TapCfg<BN>;
+    auto kern = tap_gemm_kernel<BN, kStats>;
+    static bool attr_done = false;  // per instantiation
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    const int total = p.num_m_tiles * p.num_n_tiles;
+    int grid = total < max_ctas ? total : max_ctas;
+    grid -= grid % p.num_n_tiles;  // keeps n_tile constant per CTA (per-CTA BatchNorm partial rows)
+    if (grid < p.num_n_tiles) grid = p.num_n_tiles;
+    if (stat_rows != nullptr) *stat_rows = grid / p.num_n_tiles;
+    kern<<<grid, 192, Cfg::kSmemBytes, stream>>>(a0, a1, b, p);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                            const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream) {
+    const bool stats = p.part_sum != nullptr;
+    switch (bn) {
+        case 64:
+            return stats ? launch_one<64, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
+                         : launch_one<64, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
+        case 128:
+            return stats ? launch_one<128, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
+                         : launch_one<128, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
+        case 256:
+            return stats ? launch_one<256, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
+                         : launch_one<256, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
+        default:
+            return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace b2c

@@ -1,0 +1,670 @@
+// elementwise.cu — the HBM-bound kernels of the training step (NHWC bf16 activations, fp32 statistics):
+// BatchNorm finalize / apply / backward, the pooling+linear+cross-entropy head, the input
+// augmentation, fused SGD and the weight re-layout. Each kernel states the reference call site it
+// replaces; all of them are judged against HBM bandwidth, not the tensor pipe.
+#include "b2c_elementwise.h"
+#include "b2c_ptx.cuh"
+
+namespace b2c {
+
+namespace {
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+    f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
+    f[4] = bf16lo(u.z); f[5] = bf16hi(u.z); f[6] = bf16lo(u.w); f[7] = bf16hi(u.w);
+}
+__device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
+    uint4 u;
+    u.x = pack_bf16x2(f[0], f[1]); u.y = pack_bf16x2(f[2], f[3]);
+    u.z = pack_bf16x2(f[4], f[5]); u.w = pack_bf16x2(f[6], f[7]);
+    return u;
+}
+__device__ __forceinline__ uint4 ld_stream(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// BatchNorm finalize (training statistics). Reference: nn.BatchNorm2d in train mode,
+// models/resnet.py:25,28,35,104 -> F.batch_norm: biased variance for normalisation, unbiased for the
+// running estimate, momentum 0.1, eps 1e-5. One warp per channel; lanes stride over the per-CTA
+// partial rows the conv epilogue wrote and combine with a shuffle tree in fp64.
+// ------------------------------------------------------------------------------------------------
+__global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const float* __restrict__ part_sq, int rows,
+                                   int C, float count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float eps, float momentum,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var,
+                                   float* __restrict__ scale, float* __restrict__ shift,
+                                   float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= C) return;
+    double s1 = 0.0, s2 = 0.0;
+    for (int r = lane; r < rows; r += 32) {
+        s1 += static_cast<double>(part_sum[static_cast<size_t>(r) * C + warp]);
+        s2 += static_cast<double>(part_sq[static_cast<size_t>(r) * C + warp]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    if (lane == 0) {
+        const double n = static_cast<double>(count);
+        const double mean = s1 / n;
+        double var = s2 / n - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(eps)));
+        const float g = gamma[warp];
+        const float sc = g * rstd;
+        scale[warp] = sc;
+        shift[warp] = beta[warp] - static_cast<float>(mean) * sc;
+        mean_out[warp] = static_cast<float>(mean);
+        rstd_out[warp] = rstd;
+        if (running_mean != nullptr) {
+            const double unbiased = n > 1.0 ? var * n / (n - 1.0) : var;
+            running_mean[warp] = (1.f - momentum) * running_mean[warp] + momentum * static_cast<float>(mean);
+            running_var[warp] = (1.f - momentum) * running_var[warp] + momentum * static_cast<float>(unbiased);
+        }
+    }
+}
+
+// Eval-mode BatchNorm: fold the running statistics into scale / shift (main.py:116-134 `net.eval()`).
+__global__ void bn_eval_scale_shift_kernel(int C, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                           const float* __restrict__ running_mean,
+                                           const float* __restrict__ running_var, float eps,
+                                           float* __restrict__ scale, float* __restrict__ shift) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const float sc = gamma[c] / sqrtf(running_var[c] + eps);
+    scale[c] = sc;
+    shift[c] = beta[c] - running_mean[c] * sc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// BN apply + residual + ReLU. Reference: `F.relu(self.bn1(...))`, `out += self.shortcut(x)`,
+// `F.relu(out)` models/resnet.py:47-50. 16-byte vectors of 8 channels; C % 8 == 0.
+//   out = act( y*scale + shift  [+ res]  or  [+ res*res_scale + res_shift] )
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
+                    const uint4* __restrict__ res, const float* __restrict__ res_scale,
+                    const float* __restrict__ res_shift, uint4* __restrict__ out, long long nvec, int C, int relu) {
+    const int cvec = C >> 3;
+    for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec;
+         v += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int c0 = static_cast<int>(v % cvec) << 3;
+        float f[8];
+        unpack8(ld_stream(y + v), f);
+        const float4 sa = __ldg(reinterpret_cast<const float4*>(scale + c0));
+        const float4 sb = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
+        const float4 ha = __ldg(reinterpret_cast<const float4*>(shift + c0));
+        const float4 hb = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
+        f[0] = fmaf(f[0], sa.x, ha.x); f[1] = fmaf(f[1], sa.y, ha.y);
+        f[2] = fmaf(f[2], sa.z, ha.z); f[3] = fmaf(f[3], sa.w, ha.w);
+        f[4] = fmaf(f[4], sb.x, hb.x); f[5] = fmaf(f[5], sb.y, hb.y);
+        f[6] = fmaf(f[6], sb.z, hb.z); f[7] = fmaf(f[7], sb.w, hb.w);
+        if (res != nullptr) {
+            float r[8];
+            unpack8(ld_stream(res + v), r);
+            if (res_scale != nullptr) {
+                const float4 ra = __ldg(reinterpret_cast<const float4*>(res_scale + c0));
+                const float4 rb = __ldg(reinterpret_cast<const float4*>(res_scale + c0 + 4));
+                const float4 ta = __ldg(reinterpret_cast<const float4*>(res_shift + c0));
+                const float4 tb = __ldg(reinterpret_cast<const float4*>(res_shift + c0 + 4));
+                r[0] = fmaf(r[0], ra.x, ta.x); r[1] = fmaf(r[1], ra.y, ta.y);
+                r[2] = fmaf(r[2], ra.z, ta.z); r[3] = fmaf(r[3], ra.w, ta.w);
+                r[4] = fmaf(r[4], rb.x, tb.x); r[5] = fmaf(r[5], rb.y, tb.y);
+                r[6] = fmaf(r[6], rb.z, tb.z); r[7] = fmaf(r[7], rb.w, tb.w);
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] += r[e];
+        }
+        if (relu) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+        }
+        out[v] = pack8(f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// BN(+ReLU) backward, pass 1: per-channel sums of dz and dz*y, where dz = dout * [act > 0].
+// Reference: autograd of F.relu + nn.BatchNorm2d (cudnn_batch_norm_backward), main.py:104.
+// If `dz_out` is given, the masked gradient is written back (so later passes and the shortcut
+// branch read dz directly). Each block writes one partial row [2][C]; bn_bwd_finalize combines them.
+// Thread layout: blockDim = 256; thread t owns channel vector (t % cvec) and walks rows.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ act, const uint4* __restrict__ y,
+                     uint4* __restrict__ dz_out, long long rows, int C, float* __restrict__ partial) {
+    extern __shared__ float red[];  // [rows_per_iter][2][C]
+    const int cvec = C >> 3;
+    const int rpi = 256 / cvec;     // rows handled per block iteration (cvec <= 256, divides 256)
+    const int cv = threadIdx.x % cvec;
+    const int rl = threadIdx.x / cvec;
+    float s1[8], s2[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { s1[e] = 0.f; s2[e] = 0.f; }
+    for (long long r = static_cast<long long>(blockIdx.x) * rpi + rl; r < rows;
+         r += static_cast<long long>(gridDim.x) * rpi) {
+        const long long v = r * cvec + cv;
+        float d[8], yy[8];
+        unpack8(ld_stream(dout + v), d);
+        unpack8(ld_stream(y + v), yy);
+        if (act != nullptr) {
+            float a[8];
+            unpack8(ld_stream(act + v), a);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) d[e] = a[e] > 0.f ? d[e] : 0.f;
+            if (dz_out != nullptr) dz_out[v] = pack8(d);
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            s1[e] += d[e];
+            s2[e] = fmaf(d[e], yy[e], s2[e]);
+        }
+    }
+    // block reduce over the rl dimension
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        red[(rl * 2 + 0) * C + cv * 8 + e] = s1[e];
+        red[(rl * 2 + 1) * C + cv * 8 + e] = s2[e];
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * C; i += 256) {
+        float s = 0.f;
+        for (int k = 0; k < rpi; ++k) s += red[k * 2 * C + i];
+        partial[static_cast<size_t>(blockIdx.x) * 2 * C + i] = s;
+    }
+}
+
+// Pass 2 (tiny): combine partial rows, emit dgamma / dbeta and the per-channel coefficients of
+//   dy = A*dz + B*y + Cc   (= gamma*rstd*(dz - dbeta/n - xhat*dgamma/n), xhat = (y-mean)*rstd).
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int prow, int C, float count,
+                                       const float* __restrict__ gamma, const float* __restrict__ mean,
+                                       const float* __restrict__ rstd, float* __restrict__ dgamma,
+                                       float* __restrict__ dbeta, float* __restrict__ coefA,
+                                       float* __restrict__ coefB, float* __restrict__ coefC) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= C) return;
+    double s1 = 0.0, s2 = 0.0;
+    for (int r = lane; r < prow; r += 32) {
+        s1 += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + warp]);
+        s2 += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + warp]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    if (lane == 0) {
+        const double mu = mean[warp], rs = rstd[warp], g = gamma[warp], n = count;
+        const double db = s1;
+        const double dg = rs * (s2 - mu * s1);
+        dgamma[warp] = static_cast<float>(dg);
+        dbeta[warp] = static_cast<float>(db);
+        const double A = g * rs;
+        const double B = -g * rs * rs * dg / n;
+        const double Cc = -g * rs * db / n + g * rs * rs * mu * dg / n;
+        coefA[warp] = static_cast<float>(A);
+        coefB[warp] = static_cast<float>(B);
+        coefC[warp] = static_cast<float>(Cc);
+    }
+}
+
+// Pass 3: dy = A*dz + B*y + Cc (bf16 out).
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, const float* __restrict__ coefA,
+                    const float* __restrict__ coefB, const float* __restrict__ coefC, uint4* __restrict__ dy,
+                    long long nvec, int C) {
+    const int cvec = C >> 3;
+    for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec;
+         v += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int c0 = static_cast<int>(v % cvec) << 3;
+        float d[8], yy[8], o[8];
+        unpack8(ld_stream(dz + v), d);
+        unpack8(ld_stream(y + v), yy);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            o[e] = fmaf(__ldg(coefA + c0 + e), d[e], fmaf(__ldg(coefB + c0 + e), yy[e], __ldg(coefC + c0 + e)));
+        }
+        dy[v] = pack8(o);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Head forward. Reference: F.avg_pool2d(out, 4) -> view -> nn.Linear(512, 10), models/resnet.py:137-139.
+// One block per image; thread c owns channel c (blockDim.x == C).
+// ------------------------------------------------------------------------------------------------
+__global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ act, int hw, int C, const float* __restrict__ W,
+                                const float* __restrict__ bias, int K, float* __restrict__ pooled,
+                                float* __restrict__ logits) {
+    extern __shared__ float sp[];  // [C]
+    const int n = blockIdx.x;
+    const int c = threadIdx.x;
+    float s = 0.f;
+    const __nv_bfloat16* a = act + static_cast<size_t>(n) * hw * C + c;
+    for (int i = 0; i < hw; ++i) s += __bfloat162float(a[static_cast<size_t>(i) * C]);
+    s *= 1.f / static_cast<float>(hw);
+    sp[c] = s;
+    pooled[static_cast<size_t>(n) * C + c] = s;
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int k = warp; k < K; k += nwarps) {
+        float acc = 0.f;
+        for (int j = lane; j < C; j += 32) acc = fmaf(sp[j], __ldg(W + static_cast<size_t>(k) * C + j), acc);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        if (lane == 0) logits[static_cast<size_t>(n) * K + k] = acc + bias[k];
+    }
+}
+
+// Cross-entropy (mean reduction) and its gradient. Reference: nn.CrossEntropyLoss(), main.py:86,103.
+// One thread per image; a single block reduces the loss (N <= a few thousand).
+__global__ void ce_loss_kernel(const float* __restrict__ logits, const long long* __restrict__ target, int N, int K,
+                               float* __restrict__ dlogits, float* __restrict__ loss_out,
+                               int* __restrict__ correct_out) {
+    __shared__ float sl[32];
+    __shared__ int sc[32];
+    float local = 0.f;
+    int corr = 0;
+    for (int n = threadIdx.x; n < N; n += blockDim.x) {
+        const float* l = logits + static_cast<size_t>(n) * K;
+        float m = l[0];
+        int arg = 0;
+        for (int k = 1; k < K; ++k) {
+            if (l[k] > m) { m = l[k]; arg = k; }
+        }
+        float se = 0.f;
+        for (int k = 0; k < K; ++k) se += expf(l[k] - m);
+        const float lse = m + logf(se);
+        const int t = static_cast<int>(target[n]);
+        local += lse - l[t];
+        corr += (arg == t);
+        const float invn = 1.f / static_cast<float>(N);
+        for (int k = 0; k < K; ++k) {
+            const float pk = expf(l[k] - lse);
+            dlogits[static_cast<size_t>(n) * K + k] = (pk - (k == t ? 1.f : 0.f)) * invn;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        local += __shfl_xor_sync(0xffffffffu, local, o);
+        corr += __shfl_xor_sync(0xffffffffu, corr, o);
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) { sl[warp] = local; sc[warp] = corr; }
+    __syncthreads();
+    if (warp == 0) {
+        const int nw = blockDim.x >> 5;
+        local = lane < nw ? sl[lane] : 0.f;
+        corr = lane < nw ? sc[lane] : 0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            local += __shfl_xor_sync(0xffffffffu, local, o);
+            corr += __shfl_xor_sync(0xffffffffu, corr, o);
+        }
+        if (lane == 0) {
+            loss_out[0] = local / static_cast<float>(N);
+            if (correct_out != nullptr) correct_out[0] = corr;
+        }
+    }
+}
+
+// Head backward, part 1: gradient w.r.t. the last activation (avg-pool + linear backward), bf16 NHWC.
+__global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const float* __restrict__ W, int K, int hw,
+                                    int C, __nv_bfloat16* __restrict__ dact) {
+    const int n = blockIdx.x;
+    const int c = threadIdx.x;
+    float g = 0.f;
+    for (int k = 0; k < K; ++k) g = fmaf(dlogits[static_cast<size_t>(n) * K + k], __ldg(W + static_cast<size_t>(k) * C + c), g);
+    g *= 1.f / static_cast<float>(hw);
+    const __nv_bfloat16 b = __float2bfloat16(g);
+    __nv_bfloat16* d = dact + static_cast<size_t>(n) * hw * C + c;
+    for (int i = 0; i < hw; ++i) d[static_cast<size_t>(i) * C] = b;
+}
+// Head backward, part 2: dW[k, c] = sum_n dlogits[n,k] * pooled[n,c]; db[k] = sum_n dlogits[n,k].
+__global__ void head_bwd_param_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, int N,
+                                      int K, int C, float* __restrict__ dW, float* __restrict__ db) {
+    const int k = blockIdx.y;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < C) {
+        float s = 0.f;
+        for (int n = 0; n < N; ++n) s = fmaf(dlogits[static_cast<size_t>(n) * K + k], pooled[static_cast<size_t>(n) * C + c], s);
+        dW[static_cast<size_t>(k) * C + c] = s;
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        float s = 0.f;
+        for (int n = 0; n < N; ++n) s += dlogits[static_cast<size_t>(n) * K + k];
+        db[k] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Input pipeline. Reference: transforms.Compose([RandomCrop(32, padding=4), RandomHorizontalFlip(),
+// ToTensor(), Normalize(mean, std)]) main.py:30-35, per sample in DataLoader workers.
+// The uint8 dataset [Nd,32,32,3] lives in HBM; (i, j, flip) per sample come from the host-side
+// MT19937 restatement (bit-exact with torchvision's draws). Pixel math is the reference's:
+// pad(0) on uint8 -> crop -> flip -> x/255 -> (x-mean)/std in fp32.
+//
+// augment_sample(): value of augmented pixel (y, x, c), y/x in [0,32).
+// ------------------------------------------------------------------------------------------------
+struct AugConst {
+    float mean[3];
+    float std[3];
+};
+
+__device__ __forceinline__ float aug_value(const uint8_t* simg, int y, int x, int c, int ci, int cj, int flip,
+                                           const AugConst& k) {
+    const int xs = flip ? 31 - x : x;
+    const int oy = y + ci - 4;
+    const int ox = xs + cj - 4;
+    unsigned int u = 0;
+    if (oy >= 0 && oy < 32 && ox >= 0 && ox < 32) u = simg[(oy * 32 + ox) * 3 + c];
+    const float f = __fdiv_rn(static_cast<float>(u), 255.f);   // ToTensor: .div(255)
+    return __fdiv_rn(__fsub_rn(f, k.mean[c]), k.std[c]);       // Normalize: sub_(mean).div_(std)
+}
+
+// fp32 NCHW output — the reference's tensor, for parity checks and the drop-in path.
+__global__ void __launch_bounds__(256)
+augment_nchw_kernel(const uint8_t* __restrict__ data, const long long* __restrict__ idx,
+                    const int8_t* __restrict__ ijf, float* __restrict__ out, AugConst k) {
+    __shared__ __align__(16) uint8_t simg[3072];
+    const int n = blockIdx.x;
+    const uint4* src = reinterpret_cast<const uint4*>(data + static_cast<size_t>(idx[n]) * 3072);
+    if (threadIdx.x < 192) reinterpret_cast<uint4*>(simg)[threadIdx.x] = __ldg(src + threadIdx.x);
+    __syncthreads();
+    const int ci = ijf[n * 3 + 0], cj = ijf[n * 3 + 1], flip = ijf[n * 3 + 2];
+    float* o = out + static_cast<size_t>(n) * 3072;
+    for (int e = threadIdx.x; e < 3072; e += 256) {
+        const int c = e >> 10, y = (e >> 5) & 31, x = e & 31;
+        o[e] = aug_value(simg, y, x, c, ci, cj, flip, k);
+    }
+}
+
+// Fused fast path: augmented image written directly as the stem conv's im2col operand,
+// [N,32,32,64] bf16 with k = (r*3+s)*3 + c for k < 27 and zeros above (conv zero padding applied).
+__global__ void __launch_bounds__(256)
+augment_im2col_kernel(const uint8_t* __restrict__ data, const long long* __restrict__ idx,
+                      const int8_t* __restrict__ ijf, uint4* __restrict__ out, AugConst k) {
+    __shared__ __align__(16) uint8_t simg[3072];
+    __shared__ __nv_bfloat16 saug[34 * 34 * 3];  // augmented image with the conv's 1-px zero border
+    const int n = blockIdx.x;
+    const uint4* src = reinterpret_cast<const uint4*>(data + static_cast<size_t>(idx[n]) * 3072);
+    if (threadIdx.x < 192) reinterpret_cast<uint4*>(simg)[threadIdx.x] = __ldg(src + threadIdx.x);
+    __syncthreads();
+    const int ci = ijf[n * 3 + 0], cj = ijf[n * 3 + 1], flip = ijf[n * 3 + 2];
+    for (int e = threadIdx.x; e < 34 * 34 * 3; e += 256) {
+        const int c = e % 3, x = (e / 3) % 34 - 1, y = e / (3 * 34) - 1;
+        float v = 0.f;
+        if (y >= 0 && y < 32 && x >= 0 && x < 32) v = aug_value(simg, y, x, c, ci, cj, flip, k);
+        saug[e] = __float2bfloat16(v);
+    }
+    __syncthreads();
+    // 1024 pixels x 8 vectors of 8 bf16
+    uint4* o = out + static_cast<size_t>(n) * 1024 * 8;
+    for (int e = threadIdx.x; e < 1024 * 8; e += 256) {
+        const int pix = e >> 3, vec = e & 7;
+        const int y = pix >> 5, x = pix & 31;
+        __nv_bfloat16 h[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int kk = vec * 8 + q;
+            __nv_bfloat16 v = __float2bfloat16(0.f);
+            if (kk < 27) {
+                const int tap = kk / 3, c = kk - tap * 3;
+                const int r = tap / 3, s = tap - r * 3;
+                v = saug[((y + r) * 34 + (x + s)) * 3 + c];
+            }
+            h[q] = v;
+        }
+        o[e] = *reinterpret_cast<uint4*>(h);
+    }
+}
+
+// Drop-in path: fp32 NCHW network input (what the reference's DataLoader yields) -> stem im2col operand.
+__global__ void __launch_bounds__(256)
+stem_im2col_kernel(const float* __restrict__ x, uint4* __restrict__ out) {
+    __shared__ __nv_bfloat16 saug[34 * 34 * 3];
+    const int n = blockIdx.x;
+    const float* xi = x + static_cast<size_t>(n) * 3072;
+    for (int e = threadIdx.x; e < 34 * 34 * 3; e += 256) {
+        const int c = e % 3, xx = (e / 3) % 34 - 1, y = e / (3 * 34) - 1;
+        float v = 0.f;
+        if (y >= 0 && y < 32 && xx >= 0 && xx < 32) v = xi[c * 1024 + y * 32 + xx];
+        saug[e] = __float2bfloat16(v);
+    }
+    __syncthreads();
+    uint4* o = out + static_cast<size_t>(n) * 1024 * 8;
+    for (int e = threadIdx.x; e < 1024 * 8; e += 256) {
+        const int pix = e >> 3, vec = e & 7;
+        const int y = pix >> 5, xx = pix & 31;
+        __nv_bfloat16 h[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int kk = vec * 8 + q;
+            __nv_bfloat16 v = __float2bfloat16(0.f);
+            if (kk < 27) {
+                const int tap = kk / 3, c = kk - tap * 3;
+                const int r = tap / 3, s = tap - r * 3;
+                v = saug[((y + r) * 34 + (xx + s)) * 3 + c];
+            }
+            h[q] = v;
+        }
+        o[e] = *reinterpret_cast<uint4*>(h);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused SGD. Reference: optim.SGD(lr, momentum=0.9, weight_decay=5e-4).step(), main.py:87-88,105:
+//   d = g + wd*p;  buf = d (first step) | momentum*buf + d;  p -= lr*buf      (dampening 0, no Nesterov)
+// over one flat fp32 arena holding every parameter (BN gamma/beta and biases included).
+// hyper = {lr, momentum, weight_decay, grad_scale (1/world for DDP mean), first_step} on the device,
+// so a captured CUDA graph replays with new values.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+sgd_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ buf, long long nvec,
+           const float* __restrict__ hyper) {
+    const float lr = hyper[0], mom = hyper[1], wd = hyper[2], gs = hyper[3];
+    const bool first = hyper[4] != 0.f;
+    for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec;
+         v += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float4 pp = p[v];
+        const float4 gg = g[v];
+        float4 bb = first ? make_float4(0.f, 0.f, 0.f, 0.f) : buf[v];
+        const float dx = fmaf(wd, pp.x, gg.x * gs), dy = fmaf(wd, pp.y, gg.y * gs);
+        const float dz = fmaf(wd, pp.z, gg.z * gs), dw = fmaf(wd, pp.w, gg.w * gs);
+        if (first) { bb.x = dx; bb.y = dy; bb.z = dz; bb.w = dw; }
+        else {
+            bb.x = fmaf(mom, bb.x, dx); bb.y = fmaf(mom, bb.y, dy);
+            bb.z = fmaf(mom, bb.z, dz); bb.w = fmaf(mom, bb.w, dw);
+        }
+        pp.x = fmaf(-lr, bb.x, pp.x); pp.y = fmaf(-lr, bb.y, pp.y);
+        pp.z = fmaf(-lr, bb.z, pp.z); pp.w = fmaf(-lr, bb.w, pp.w);
+        buf[v] = bb;
+        p[v] = pp;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Weight re-layout: fp32 OIHW master weights (the reference's state_dict layout, models/resnet.py:23-27)
+// -> the two bf16 operand layouts the conv kernels read:
+//    fprop B  [tap][cout][cin_pad]      dgrad B  [tap][cin][cout]
+// One launch for every conv of the network: blockIdx.y = tensor index into a device table.
+// kflat != 0 (stem): fprop B is [cout][64] with k = tap*cin + c (matches the im2col operand), no dgrad copy.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, __nv_bfloat16* __restrict__ wd,
+              const RepackEntry* __restrict__ table) {
+    const RepackEntry e = table[blockIdx.y];
+    const int taps = e.taps;
+    const long long total = static_cast<long long>(e.cout) * e.cin * taps;
+    const float* src = master + e.src_off;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        // i enumerates OIHW: o, c, t
+        const int t = static_cast<int>(i % taps);
+        const int c = static_cast<int>((i / taps) % e.cin);
+        const int o = static_cast<int>(i / (static_cast<long long>(taps) * e.cin));
+        const __nv_bfloat16 b = __float2bfloat16(src[i]);
+        if (e.kflat) {
+            wf[e.wf_off + static_cast<long long>(o) * e.cin_pad + t * e.cin + c] = b;
+        } else {
+            wf[e.wf_off + (static_cast<long long>(t) * e.cout + o) * e.cin_pad + c] = b;
+            if (e.wd_off >= 0) wd[e.wd_off + (static_cast<long long>(t) * e.cin + c) * e.cout + o] = b;
+        }
+    }
+}
+
+inline int grid_for(long long work_items, int block, int max_blocks) {
+    long long g = (work_items + block - 1) / block;
+    if (g > max_blocks) g = max_blocks;
+    if (g < 1) g = 1;
+    return static_cast<int>(g);
+}
+
+}  // namespace
+
+// ---------------------------------------- launchers ---------------------------------------------
+cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int rows, int C, float count,
+                               const float* gamma, const float* beta, float eps, float momentum,
+                               float* running_mean, float* running_var, float* scale, float* shift, float* mean,
+                               float* rstd, cudaStream_t s) {
+    const int threads = 128;
+    const int blocks = (C * 32 + threads - 1) / threads;
+    bn_finalize_kernel<<<blocks, threads, 0, s>>>(part_sum, part_sq, rows, C, count, gamma, beta, eps, momentum,
+                                                  running_mean, running_var, scale, shift, mean, rstd);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* beta, const float* rm,
+                                       const float* rv, float eps, float* scale, float* shift, cudaStream_t s) {
+    bn_eval_scale_shift_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, gamma, beta, rm, rv, eps, scale, shift);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
+                                const float* res_scale, const float* res_shift, void* out, long long rows, int C,
+                                int relu, cudaStream_t s) {
+    const long long nvec = rows * (C >> 3);
+    bn_act_apply_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(
+        static_cast<const uint4*>(y), scale, shift, static_cast<const uint4*>(res), res_scale, res_shift,
+        static_cast<uint4*>(out), nvec, C, relu);
+    return cudaGetLastError();
+}
+
+int bn_bwd_partial_rows(long long rows, int C) {
+    const int rpi = 256 / (C >> 3);
+    long long blocks = (rows + rpi - 1) / rpi;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
+                                 int C, float* partial, cudaStream_t s) {
+    const int cvec = C >> 3;
+    if (cvec < 1 || cvec > 256 || (256 % cvec) != 0) return cudaErrorInvalidValue;
+    const int rpi = 256 / cvec;
+    const int blocks = bn_bwd_partial_rows(rows, C);
+    const size_t smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
+    bn_bwd_reduce_kernel<<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), static_cast<const uint4*>(act),
+                                                  static_cast<const uint4*>(y), static_cast<uint4*>(dz_out), rows,
+                                                  C, partial);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float count, const float* gamma,
+                                   const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
+                                   float* coefB, float* coefC, cudaStream_t s) {
+    const int threads = 128;
+    const int blocks = (C * 32 + threads - 1) / threads;
+    bn_bwd_finalize_kernel<<<blocks, threads, 0, s>>>(partial, prow, C, count, gamma, mean, rstd, dgamma, dbeta,
+                                                      coefA, coefB, coefC);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coefA, const float* coefB,
+                                const float* coefC, void* dy, long long rows, int C, cudaStream_t s) {
+    const long long nvec = rows * (C >> 3);
+    bn_bwd_apply_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(
+        static_cast<const uint4*>(dz), static_cast<const uint4*>(y), coefA, coefB, coefC, static_cast<uint4*>(dy),
+        nvec, C);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_head_fwd(const void* act, int N, int hw, int C, const float* W, const float* bias, int K,
+                            float* pooled, float* logits, cudaStream_t s) {
+    if (C > 1024 || (C & 31)) return cudaErrorInvalidValue;
+    head_fwd_kernel<<<N, C, C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(act), hw, C, W, bias, K, pooled,
+                                                    logits);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ce_loss(const float* logits, const long long* target, int N, int K, float* dlogits, float* loss,
+                           int* correct, cudaStream_t s) {
+    ce_loss_kernel<<<1, 1024, 0, s>>>(logits, target, N, K, dlogits, loss, correct);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const float* W, int N, int hw, int C, int K,
+                            void* dact, float* dW, float* db, cudaStream_t s) {
+    if (C > 1024) return cudaErrorInvalidValue;
+    head_bwd_act_kernel<<<N, C, 0, s>>>(dlogits, W, K, hw, C, static_cast<__nv_bfloat16*>(dact));
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    dim3 grid((C + 127) / 128, K);
+    head_bwd_param_kernel<<<grid, 128, 0, s>>>(dlogits, pooled, N, K, C, dW, db);
+    return cudaGetLastError();
+}
+
+static AugConst make_aug(const float* mean, const float* stdv) {
+    AugConst k;
+    for (int i = 0; i < 3; ++i) { k.mean[i] = mean[i]; k.std[i] = stdv[i]; }
+    return k;
+}
+
+cudaError_t launch_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out, int N,
+                                const float* mean, const float* stdv, cudaStream_t s) {
+    if (N == 0) return cudaSuccess;
+    augment_nchw_kernel<<<N, 256, 0, s>>>(data, idx, ijf, out, make_aug(mean, stdv));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out, int N,
+                                  const float* mean, const float* stdv, cudaStream_t s) {
+    if (N == 0) return cudaSuccess;
+    augment_im2col_kernel<<<N, 256, 0, s>>>(data, idx, ijf, static_cast<uint4*>(out), make_aug(mean, stdv));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s) {
+    if (N == 0) return cudaSuccess;
+    stem_im2col_kernel<<<N, 256, 0, s>>>(x, static_cast<uint4*>(out));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sgd(float* p, const float* g, float* buf, long long n, const float* hyper, cudaStream_t s) {
+    if (n & 3) return cudaErrorInvalidValue;
+    const long long nvec = n >> 2;
+    sgd_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(reinterpret_cast<float4*>(p),
+                                                          reinterpret_cast<const float4*>(g),
+                                                          reinterpret_cast<float4*>(buf), nvec, hyper);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackEntry* table_dev, int entries,
+                          cudaStream_t s) {
+    if (entries == 0) return cudaSuccess;
+    dim3 grid(64, entries);
+    repack_kernel<<<grid, 256, 0, s>>>(master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd),
+                                       table_dev);
+    return cudaGetLastError();
+}
+
+}  // namespace b2c

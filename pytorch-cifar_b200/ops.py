@@ -1,0 +1,185 @@
+"""Tensor-level wrappers over the C-ABI (include/b2c.h). torch is used only for device memory and
+streams: every wrapper extracts raw pointers, passes the current CUDA stream and raises on a non-zero
+return code. Activations are NHWC bf16 tensors; there is no fallback implementation here.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import ConvDesc, RepackEntry, check
+
+CIFAR_MEAN = (0.4914, 0.4822, 0.4465)   # reference main.py:34
+CIFAR_STD = (0.2023, 0.1994, 0.2010)    # reference main.py:34
+MAX_STAT_ROWS = 148
+
+
+def _p(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need(t, dtype, name):
+    if t is None:
+        return
+    if not t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+        raise ValueError(f"{name}: expected contiguous CUDA {dtype}, got {t.dtype} cuda={t.is_cuda} "
+                         f"contig={t.is_contiguous()}")
+
+
+def conv_desc(n, h, w, cin, cout, ksize, stride, cin_valid=0, kflat_cin=0, block_n=0, max_ctas=0):
+    return ConvDesc(n, h, w, cin, cout, ksize, stride, cin_valid, kflat_cin, block_n, max_ctas)
+
+
+def pack_weight_fprop(w_oihw):
+    """OIHW fp32 -> bf16 [tap][cout][cin] (torch-side helper for tests; the engine uses repack_weights)."""
+    co, ci, kh, kw = w_oihw.shape
+    return w_oihw.permute(2, 3, 0, 1).reshape(kh * kw, co, ci).contiguous().to(torch.bfloat16)
+
+
+def pack_weight_dgrad(w_oihw):
+    co, ci, kh, kw = w_oihw.shape
+    return w_oihw.permute(2, 3, 1, 0).reshape(kh * kw, ci, co).contiguous().to(torch.bfloat16)
+
+
+def conv_fprop(d, x, w_fprop, y, part_sum=None, part_sq=None):
+    """y = conv(x); returns the number of BatchNorm partial rows written (0 without statistics)."""
+    lib = _lib.load()
+    _need(x, torch.bfloat16, "x"); _need(w_fprop, torch.bfloat16, "w"); _need(y, torch.bfloat16, "y")
+    _need(part_sum, torch.float32, "part_sum"); _need(part_sq, torch.float32, "part_sq")
+    rows = ctypes.c_int(0)
+    check(lib.b2c_conv_fprop(ctypes.byref(d), _p(x), _p(w_fprop), _p(y), _p(part_sum), _p(part_sq),
+                             ctypes.byref(rows), _stream()), "b2c_conv_fprop")
+    return rows.value
+
+
+def conv_dgrad(d, dy, w_dgrad, dx, add_src=None):
+    lib = _lib.load()
+    _need(dy, torch.bfloat16, "dy"); _need(w_dgrad, torch.bfloat16, "w"); _need(dx, torch.bfloat16, "dx")
+    _need(add_src, torch.bfloat16, "add_src")
+    check(lib.b2c_conv_dgrad(ctypes.byref(d), _p(dy), _p(w_dgrad), _p(dx), _p(add_src), _stream()),
+          "b2c_conv_dgrad")
+
+
+def conv_wgrad(d, x, dy, dw):
+    lib = _lib.load()
+    _need(x, torch.bfloat16, "x"); _need(dy, torch.bfloat16, "dy"); _need(dw, torch.float32, "dw")
+    check(lib.b2c_conv_wgrad(ctypes.byref(d), _p(x), _p(dy), _p(dw), _stream()), "b2c_conv_wgrad")
+
+
+def bn_finalize(part_sum, part_sq, rows, channels, count, gamma, beta, eps, momentum, running_mean, running_var,
+                scale, shift, save_mean, save_rstd):
+    lib = _lib.load()
+    check(lib.b2c_bn_finalize(_p(part_sum), _p(part_sq), rows, channels, float(count), _p(gamma), _p(beta),
+                              float(eps), float(momentum), _p(running_mean), _p(running_var), _p(scale), _p(shift),
+                              _p(save_mean), _p(save_rstd), _stream()), "b2c_bn_finalize")
+
+
+def bn_eval_scale_shift(channels, gamma, beta, running_mean, running_var, eps, scale, shift):
+    lib = _lib.load()
+    check(lib.b2c_bn_eval_scale_shift(channels, _p(gamma), _p(beta), _p(running_mean), _p(running_var), float(eps),
+                                      _p(scale), _p(shift), _stream()), "b2c_bn_eval_scale_shift")
+
+
+def bn_act_apply(y, scale, shift, out, rows, channels, relu=True, res=None, res_scale=None, res_shift=None):
+    lib = _lib.load()
+    check(lib.b2c_bn_act_apply(_p(y), _p(scale), _p(shift), _p(res), _p(res_scale), _p(res_shift), _p(out),
+                               rows, channels, 1 if relu else 0, _stream()), "b2c_bn_act_apply")
+
+
+def bn_bwd_partial_rows(rows, channels):
+    lib = _lib.load()
+    r = lib.b2c_bn_bwd_partial_rows(rows, channels)
+    if r < 0:
+        check(r, "b2c_bn_bwd_partial_rows")
+    return r
+
+
+def bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial):
+    lib = _lib.load()
+    check(lib.b2c_bn_bwd_reduce(_p(dout), _p(act), _p(y), _p(dz_out), rows, channels, _p(partial), _stream()),
+          "b2c_bn_bwd_reduce")
+
+
+def bn_bwd_finalize(partial, partial_rows, channels, count, gamma, save_mean, save_rstd, dgamma, dbeta, ca, cb, cc):
+    lib = _lib.load()
+    check(lib.b2c_bn_bwd_finalize(_p(partial), partial_rows, channels, float(count), _p(gamma), _p(save_mean),
+                                  _p(save_rstd), _p(dgamma), _p(dbeta), _p(ca), _p(cb), _p(cc), _stream()),
+          "b2c_bn_bwd_finalize")
+
+
+def bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, channels):
+    lib = _lib.load()
+    check(lib.b2c_bn_bwd_apply(_p(dz), _p(y), _p(ca), _p(cb), _p(cc), _p(dy), rows, channels, _stream()),
+          "b2c_bn_bwd_apply")
+
+
+def head_fwd(act, n, hw, channels, weight, bias, classes, pooled, logits):
+    lib = _lib.load()
+    check(lib.b2c_head_fwd(_p(act), n, hw, channels, _p(weight), _p(bias), classes, _p(pooled), _p(logits),
+                           _stream()), "b2c_head_fwd")
+
+
+def ce_loss(logits, target, n, classes, dlogits, loss, correct=None):
+    lib = _lib.load()
+    _need(target, torch.int64, "target")
+    check(lib.b2c_ce_loss(_p(logits), _p(target), n, classes, _p(dlogits), _p(loss), _p(correct), _stream()),
+          "b2c_ce_loss")
+
+
+def head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, dbias):
+    lib = _lib.load()
+    check(lib.b2c_head_bwd(_p(dlogits), _p(pooled), _p(weight), n, hw, channels, classes, _p(dact), _p(dweight),
+                           _p(dbias), _stream()), "b2c_head_bwd")
+
+
+_F3 = ctypes.c_float * 3
+
+
+def augment_nchw(data_u8, idx, ijf, out, mean=CIFAR_MEAN, std=CIFAR_STD):
+    lib = _lib.load()
+    _need(data_u8, torch.uint8, "data"); _need(idx, torch.int64, "idx"); _need(ijf, torch.int8, "ijf")
+    _need(out, torch.float32, "out")
+    check(lib.b2c_augment_nchw(_p(data_u8), _p(idx), _p(ijf), _p(out), idx.numel(), _F3(*mean), _F3(*std),
+                               _stream()), "b2c_augment_nchw")
+
+
+def augment_im2col(data_u8, idx, ijf, out, mean=CIFAR_MEAN, std=CIFAR_STD):
+    lib = _lib.load()
+    _need(data_u8, torch.uint8, "data"); _need(idx, torch.int64, "idx"); _need(ijf, torch.int8, "ijf")
+    _need(out, torch.bfloat16, "out")
+    check(lib.b2c_augment_im2col(_p(data_u8), _p(idx), _p(ijf), _p(out), idx.numel(), _F3(*mean), _F3(*std),
+                                 _stream()), "b2c_augment_im2col")
+
+
+def stem_im2col(x_nchw, out):
+    lib = _lib.load()
+    _need(x_nchw, torch.float32, "x"); _need(out, torch.bfloat16, "out")
+    check(lib.b2c_stem_im2col(_p(x_nchw), _p(out), x_nchw.shape[0], _stream()), "b2c_stem_im2col")
+
+
+def sgd_step(param, grad, buf, hyper):
+    lib = _lib.load()
+    _need(param, torch.float32, "param"); _need(grad, torch.float32, "grad"); _need(buf, torch.float32, "buf")
+    _need(hyper, torch.float32, "hyper")
+    check(lib.b2c_sgd_step(_p(param), _p(grad), _p(buf), param.numel(), _p(hyper), _stream()), "b2c_sgd_step")
+
+
+def make_repack_table(entries, device):
+    """entries: list of dicts with the B2cRepackEntry fields -> device uint8 tensor holding the table."""
+    arr = (RepackEntry * len(entries))()
+    for i, e in enumerate(entries):
+        arr[i] = RepackEntry(e["src_off"], e["wf_off"], e.get("wd_off", -1), e["cout"], e["cin"], e["taps"],
+                             e["cin_pad"], e.get("kflat", 0), 0)
+    raw = bytes(arr)
+    t = torch.frombuffer(bytearray(raw), dtype=torch.uint8).clone()
+    return t.to(device)
+
+
+def repack_weights(master, wf_arena, wd_arena, table_dev, entries):
+    lib = _lib.load()
+    check(lib.b2c_repack_weights(_p(master), _p(wf_arena), _p(wd_arena), _p(table_dev), entries, _stream()),
+          "b2c_repack_weights")

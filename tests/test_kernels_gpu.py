@@ -1,0 +1,351 @@
+"""GPU parity tests of each C-ABI kernel against a plain PyTorch fp32 restatement of the same op.
+
+Every call goes through the C-ABI (ctypes -> libb2c.so). Tolerances: bf16-stored results within 1e-2
+relative (Frobenius) of the fp32 reference (BASELINE.json north_star); fp32 results within 1e-3.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+BF16_TOL = 1e-2
+F32_TOL = 1e-3
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import b200cifar
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return b200cifar.ops
+
+
+def rel_err(a, b):
+    a = a.double()
+    b = b.double()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def nhwc_bf16(n, h, w, c, seed, scale=1.0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    return (torch.randn(n, h, w, c, device="cuda", generator=g) * scale).to(torch.bfloat16).contiguous()
+
+
+def weight(cout, cin, k, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    w = torch.randn(cout, cin, k, k, device="cuda", generator=g) * (2.0 / (cin * k * k)) ** 0.5
+    return w.to(torch.bfloat16).float()  # values exactly representable in bf16
+
+
+def to_nchw(x):
+    return x.float().permute(0, 3, 1, 2).contiguous()
+
+
+CONV_SHAPES = [
+    # n, h, w, cin, cout, k, stride
+    (4, 32, 32, 64, 64, 3, 1),
+    (8, 16, 16, 128, 128, 3, 1),
+    (16, 8, 8, 256, 256, 3, 1),
+    (32, 4, 4, 512, 512, 3, 1),
+    (4, 32, 32, 64, 128, 3, 2),
+    (8, 16, 16, 128, 256, 3, 2),
+    (16, 8, 8, 256, 512, 3, 2),
+    (4, 32, 32, 64, 128, 1, 2),
+    (16, 8, 8, 256, 512, 1, 2),
+    (2, 32, 32, 64, 64, 1, 1),
+    (5, 4, 4, 512, 512, 3, 1),     # ragged: 80 pixels, one partial tile
+    (3, 8, 8, 128, 128, 3, 1),     # ragged: 192 pixels
+    (64, 2, 2, 512, 512, 3, 1),    # VGG last stage
+]
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+def test_conv_fprop(ops, shape):
+    n, h, w, cin, cout, k, stride = shape
+    x = nhwc_bf16(n, h, w, cin, 1)
+    wt = weight(cout, cin, k, 2)
+    ho, wo = h // stride, w // stride
+    y = torch.full((n, ho, wo, cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    d = ops.conv_desc(n, h, w, cin, cout, k, stride)
+    rows = ops.conv_fprop(d, x, ops.pack_weight_fprop(wt), y, ps, pq)
+    torch.cuda.synchronize()
+    ref = F.conv2d(to_nchw(x), wt, stride=stride, padding=k // 2)
+    got = to_nchw(y)
+    assert torch.isfinite(got).all()
+    assert rel_err(got, ref) < BF16_TOL
+    assert 1 <= rows <= ops.MAX_STAT_ROWS
+    s1 = ps[:rows].sum(0)
+    s2 = pq[:rows].sum(0)
+    assert rel_err(s1, ref.sum((0, 2, 3))) < 2e-3 or (s1 - ref.sum((0, 2, 3))).abs().max() < 1e-1
+    assert rel_err(s2, (ref * ref).sum((0, 2, 3))) < F32_TOL
+
+
+@pytest.mark.parametrize("bn", [64, 128, 256])
+def test_conv_fprop_block_n(ops, bn):
+    n, h, w, cin, cout, k, stride = 8, 16, 16, 128, 256, 3, 1
+    x = nhwc_bf16(n, h, w, cin, 3)
+    wt = weight(cout, cin, k, 4)
+    y = torch.empty(n, h, w, cout, device="cuda", dtype=torch.bfloat16)
+    d = ops.conv_desc(n, h, w, cin, cout, k, stride, block_n=bn)
+    ops.conv_fprop(d, x, ops.pack_weight_fprop(wt), y)
+    torch.cuda.synchronize()
+    ref = F.conv2d(to_nchw(x), wt, stride=stride, padding=1)
+    assert rel_err(to_nchw(y), ref) < BF16_TOL
+
+
+def test_conv_fprop_multi_wave(ops):
+    # more tiles than CTAs so the persistent loop, the smem ring wrap and both TMEM buffers are used
+    n, h, w, cin, cout = 64, 32, 32, 64, 64
+    x = nhwc_bf16(n, h, w, cin, 5)
+    wt = weight(cout, cin, 3, 6)
+    y = torch.empty(n, h, w, cout, device="cuda", dtype=torch.bfloat16)
+    ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    d = ops.conv_desc(n, h, w, cin, cout, 3, 1, max_ctas=37)
+    rows = ops.conv_fprop(d, x, ops.pack_weight_fprop(wt), y, ps, pq)
+    torch.cuda.synchronize()
+    ref = F.conv2d(to_nchw(x), wt, padding=1)
+    assert rel_err(to_nchw(y), ref) < BF16_TOL
+    assert rel_err(pq[:rows].sum(0), (ref * ref).sum((0, 2, 3))) < F32_TOL
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+@pytest.mark.parametrize("with_add", [False, True])
+def test_conv_dgrad(ops, shape, with_add):
+    n, h, w, cin, cout, k, stride = shape
+    ho, wo = h // stride, w // stride
+    dy = nhwc_bf16(n, ho, wo, cout, 7)
+    wt = weight(cout, cin, k, 8)
+    ref = torch.nn.grad.conv2d_input((n, cin, h, w), wt, to_nchw(dy), stride=stride, padding=k // 2)
+    dx = torch.full((n, h, w, cin), float("nan"), device="cuda", dtype=torch.bfloat16)
+    add = None
+    if with_add:
+        if k == 1 and stride == 2:
+            # in-place accumulate form
+            dx = nhwc_bf16(n, h, w, cin, 9)
+            ref = ref + to_nchw(dx)
+            add = dx
+        else:
+            add = nhwc_bf16(n, h, w, cin, 9)
+            ref = ref + to_nchw(add)
+    d = ops.conv_desc(n, h, w, cin, cout, k, stride)
+    ops.conv_dgrad(d, dy, ops.pack_weight_dgrad(wt), dx, add)
+    torch.cuda.synchronize()
+    got = to_nchw(dx)
+    assert torch.isfinite(got).all()
+    assert rel_err(got, ref) < BF16_TOL
+
+
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+def test_conv_wgrad(ops, shape):
+    n, h, w, cin, cout, k, stride = shape
+    ho, wo = h // stride, w // stride
+    x = nhwc_bf16(n, h, w, cin, 10)
+    dy = nhwc_bf16(n, ho, wo, cout, 11)
+    ref = torch.nn.grad.conv2d_weight(to_nchw(x), (cout, cin, k, k), to_nchw(dy), stride=stride, padding=k // 2)
+    dw = torch.zeros(cout, cin, k, k, device="cuda")
+    d = ops.conv_desc(n, h, w, cin, cout, k, stride)
+    ops.conv_wgrad(d, x, dy, dw)
+    torch.cuda.synchronize()
+    assert rel_err(dw, ref) < F32_TOL
+    # accumulation semantics: a second call doubles the result
+    ops.conv_wgrad(d, x, dy, dw)
+    torch.cuda.synchronize()
+    assert rel_err(dw, 2 * ref) < F32_TOL
+
+
+def test_conv_wgrad_large_k_split(ops):
+    n, h, w, cin, cout = 128, 32, 32, 64, 64
+    x = nhwc_bf16(n, h, w, cin, 12)
+    dy = nhwc_bf16(n, h, w, cout, 13, scale=0.1)
+    ref = torch.nn.grad.conv2d_weight(to_nchw(x), (cout, cin, 3, 3), to_nchw(dy), padding=1)
+    dw = torch.zeros(cout, cin, 3, 3, device="cuda")
+    ops.conv_wgrad(ops.conv_desc(n, h, w, cin, cout, 3, 1), x, dy, dw)
+    torch.cuda.synchronize()
+    assert rel_err(dw, ref) < F32_TOL
+
+
+def stem_operands(ops, n, seed):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.randn(n, 3, 32, 32, device="cuda", generator=g)
+    col = torch.empty(n, 32, 32, 64, device="cuda", dtype=torch.bfloat16)
+    ops.stem_im2col(x, col)
+    return x, col
+
+
+def test_stem_im2col_and_conv(ops):
+    n = 8
+    x, col = stem_operands(ops, n, 14)
+    torch.cuda.synchronize()
+    xb = x.to(torch.bfloat16).float()
+    unf = F.unfold(xb, 3, padding=1)                       # [n, c*9, L], index c*9 + tap
+    unf = unf.view(n, 3, 9, 32, 32).permute(0, 3, 4, 2, 1).reshape(n, 32, 32, 27)   # k = tap*3 + c
+    assert torch.equal(col[..., :27].float(), unf)
+    assert (col[..., 27:] == 0).all()
+    wt = weight(64, 3, 3, 15)
+    wf = torch.zeros(64, 64, device="cuda", dtype=torch.bfloat16)
+    wf[:, :27] = wt.permute(0, 2, 3, 1).reshape(64, 27).to(torch.bfloat16)
+    y = torch.empty(n, 32, 32, 64, device="cuda", dtype=torch.bfloat16)
+    ops.conv_fprop(ops.conv_desc(n, 32, 32, 64, 64, 1, 1), col, wf.view(1, 64, 64), y)
+    torch.cuda.synchronize()
+    ref = F.conv2d(xb, wt, padding=1)
+    assert rel_err(to_nchw(y), ref) < BF16_TOL
+    # stem wgrad through the flattened-k addressing
+    dy = nhwc_bf16(n, 32, 32, 64, 16)
+    dw = torch.zeros(64, 3, 3, 3, device="cuda")
+    ops.conv_wgrad(ops.conv_desc(n, 32, 32, 64, 64, 1, 1, cin_valid=27, kflat_cin=3), col, dy, dw)
+    torch.cuda.synchronize()
+    refw = torch.nn.grad.conv2d_weight(xb, (64, 3, 3, 3), to_nchw(dy), padding=1)
+    assert rel_err(dw, refw) < F32_TOL
+
+
+@pytest.mark.parametrize("C,rows", [(64, 4096), (128, 1000), (512, 80)])
+def test_bn_forward_chain(ops, C, rows):
+    """partials -> finalize -> apply (+residual variants) against F.batch_norm."""
+    g = torch.Generator(device="cuda").manual_seed(20)
+    y = (torch.randn(rows, C, device="cuda", generator=g) * 2 + 0.5).to(torch.bfloat16)
+    yf = y.float()
+    nrows_p = 7
+    chunks = torch.tensor_split(yf, nrows_p, 0)
+    ps = torch.stack([c.sum(0) for c in chunks])
+    pq = torch.stack([(c * c).sum(0) for c in chunks])
+    gamma = torch.rand(C, device="cuda", generator=g) + 0.5
+    beta = torch.randn(C, device="cuda", generator=g)
+    rm = torch.randn(C, device="cuda", generator=g)
+    rv = torch.rand(C, device="cuda", generator=g) + 0.5
+    rm_ref, rv_ref = rm.clone(), rv.clone()
+    scale, shift, mean, rstd = (torch.empty(C, device="cuda") for _ in range(4))
+    ops.bn_finalize(ps, pq, nrows_p, C, rows, gamma, beta, 1e-5, 0.1, rm, rv, scale, shift, mean, rstd)
+    ref = F.batch_norm(yf, rm_ref, rv_ref, gamma, beta, training=True, momentum=0.1, eps=1e-5)
+    torch.cuda.synchronize()
+    assert rel_err(rm, rm_ref) < 1e-5 and rel_err(rv, rv_ref) < 1e-5
+    assert rel_err(mean, yf.mean(0)) < 1e-4
+    out = torch.empty(rows, C, device="cuda", dtype=torch.bfloat16)
+    ops.bn_act_apply(y, scale, shift, out, rows, C, relu=True)
+    assert rel_err(out.float(), F.relu(ref)) < BF16_TOL
+    res = (torch.randn(rows, C, device="cuda", generator=g)).to(torch.bfloat16)
+    ops.bn_act_apply(y, scale, shift, out, rows, C, relu=True, res=res)
+    assert rel_err(out.float(), F.relu(ref + res.float())) < BF16_TOL
+    rs = torch.rand(C, device="cuda", generator=g) + 0.5
+    rb = torch.randn(C, device="cuda", generator=g)
+    ops.bn_act_apply(y, scale, shift, out, rows, C, relu=False, res=res, res_scale=rs, res_shift=rb)
+    assert rel_err(out.float(), ref + res.float() * rs + rb) < BF16_TOL
+    # eval-mode scale/shift
+    ops.bn_eval_scale_shift(C, gamma, beta, rm, rv, 1e-5, scale, shift)
+    ops.bn_act_apply(y, scale, shift, out, rows, C, relu=False)
+    ref_eval = F.batch_norm(yf, rm, rv, gamma, beta, training=False, eps=1e-5)
+    assert rel_err(out.float(), ref_eval) < BF16_TOL
+
+
+@pytest.mark.parametrize("C,rows", [(64, 8192), (256, 1000), (512, 2048)])
+def test_bn_relu_backward(ops, C, rows):
+    g = torch.Generator(device="cuda").manual_seed(21)
+    y = (torch.randn(rows, C, device="cuda", generator=g) * 1.5 + 0.3).to(torch.bfloat16)
+    gamma = (torch.rand(C, device="cuda", generator=g) + 0.5).requires_grad_()
+    beta = (torch.randn(C, device="cuda", generator=g) * 0.3).requires_grad_()
+    dout = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+    yf = y.float().requires_grad_()
+    act_ref = F.relu(F.batch_norm(yf, None, None, gamma, beta, training=True, eps=1e-5))
+    act_ref.backward(dout.float())
+    mean = y.float().mean(0)
+    var = y.float().var(0, unbiased=False)
+    rstd = (var + 1e-5).rsqrt()
+    act = act_ref.detach().to(torch.bfloat16)
+    prow = ops.bn_bwd_partial_rows(rows, C)
+    partial = torch.empty(prow, 2, C, device="cuda")
+    dz = torch.empty_like(dout)
+    ops.bn_bwd_reduce(dout, act, y, dz, rows, C, partial)
+    dgamma, dbeta, ca, cb, cc = (torch.empty(C, device="cuda") for _ in range(5))
+    ops.bn_bwd_finalize(partial, prow, C, rows, gamma.detach(), mean, rstd, dgamma, dbeta, ca, cb, cc)
+    dy = torch.empty_like(dout)
+    ops.bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, C)
+    torch.cuda.synchronize()
+    # the mask comes from the bf16-rounded activation: elements whose fp32 activation rounds to 0 differ; rare
+    assert rel_err(dgamma, gamma.grad) < 5e-3
+    assert rel_err(dbeta, beta.grad) < 5e-3
+    assert rel_err(dy.float(), yf.grad) < BF16_TOL
+    # in-place masking (dz_out aliases dout) and the no-activation form
+    d2 = dout.clone()
+    ops.bn_bwd_reduce(d2, act, y, d2, rows, C, partial)
+    torch.cuda.synchronize()
+    assert torch.equal(d2, dz)
+    ops.bn_bwd_reduce(dz, None, y, None, rows, C, partial)
+    ops.bn_bwd_finalize(partial, prow, C, rows, gamma.detach(), mean, rstd, dgamma, dbeta, ca, cb, cc)
+    torch.cuda.synchronize()
+    assert rel_err(dbeta, beta.grad) < 5e-3
+
+
+def test_head_and_loss(ops):
+    n, hw, C, K = 128, 16, 512, 10
+    g = torch.Generator(device="cuda").manual_seed(22)
+    act = torch.rand(n, hw, C, device="cuda", generator=g).to(torch.bfloat16)
+    W = (torch.randn(K, C, device="cuda", generator=g) * 0.05).requires_grad_()
+    b = (torch.randn(K, device="cuda", generator=g) * 0.1).requires_grad_()
+    target = torch.randint(0, K, (n,), device="cuda", generator=g)
+    pooled = torch.empty(n, C, device="cuda")
+    logits = torch.empty(n, K, device="cuda")
+    ops.head_fwd(act, n, hw, C, W.detach(), b.detach(), K, pooled, logits)
+    af = act.float().requires_grad_()
+    ref_logits = F.linear(af.mean(1), W, b)
+    loss_ref = F.cross_entropy(ref_logits, target)
+    loss_ref.backward()
+    dlogits = torch.empty(n, K, device="cuda")
+    loss = torch.empty(1, device="cuda")
+    correct = torch.zeros(1, device="cuda", dtype=torch.int32)
+    ops.ce_loss(logits, target, n, K, dlogits, loss, correct)
+    dact = torch.empty(n, hw, C, device="cuda", dtype=torch.bfloat16)
+    dW = torch.empty(K, C, device="cuda")
+    db = torch.empty(K, device="cuda")
+    ops.head_bwd(dlogits, pooled, W.detach(), n, hw, C, K, dact, dW, db)
+    torch.cuda.synchronize()
+    assert rel_err(logits, ref_logits) < 1e-4
+    assert abs(loss.item() - loss_ref.item()) < 1e-4
+    assert correct.item() == (ref_logits.argmax(1) == target).sum().item()
+    assert rel_err(dW, W.grad) < 1e-4 and rel_err(db, b.grad) < 1e-4
+    assert rel_err(dact.float(), af.grad) < BF16_TOL
+
+
+def test_sgd_step(ops):
+    nparam = 4096 * 3 + 8
+    g = torch.Generator(device="cuda").manual_seed(23)
+    p = torch.randn(nparam, device="cuda", generator=g)
+    ref_p = p.clone().requires_grad_()
+    opt = torch.optim.SGD([ref_p], lr=0.1, momentum=0.9, weight_decay=5e-4)
+    buf = torch.zeros_like(p)
+    hyper = torch.tensor([0.1, 0.9, 5e-4, 1.0, 1.0], device="cuda")
+    for step in range(3):
+        grad = torch.randn(nparam, device="cuda", generator=g)
+        ref_p.grad = grad.clone()
+        opt.step()
+        hyper[4] = 1.0 if step == 0 else 0.0
+        ops.sgd_step(p, grad, buf, hyper)
+    torch.cuda.synchronize()
+    assert (p - ref_p.detach()).abs().max().item() < 1e-6
+
+
+def test_repack_weights(ops):
+    g = torch.Generator(device="cuda").manual_seed(24)
+    w1 = torch.randn(128, 64, 3, 3, device="cuda", generator=g)
+    w2 = torch.randn(128, 64, 1, 1, device="cuda", generator=g)
+    w0 = torch.randn(64, 3, 3, 3, device="cuda", generator=g)
+    master = torch.cat([w1.flatten(), w2.flatten(), w0.flatten()])
+    wf = torch.zeros(w1.numel() + w2.numel() + 64 * 64, device="cuda", dtype=torch.bfloat16)
+    wd = torch.zeros(w1.numel() + w2.numel(), device="cuda", dtype=torch.bfloat16)
+    entries = [
+        dict(src_off=0, wf_off=0, wd_off=0, cout=128, cin=64, taps=9, cin_pad=64),
+        dict(src_off=w1.numel(), wf_off=w1.numel(), wd_off=w1.numel(), cout=128, cin=64, taps=1, cin_pad=64),
+        dict(src_off=w1.numel() + w2.numel(), wf_off=w1.numel() + w2.numel(), wd_off=-1, cout=64, cin=3, taps=9,
+             cin_pad=64, kflat=1),
+    ]
+    table = ops.make_repack_table(entries, "cuda")
+    ops.repack_weights(master, wf, wd, table, len(entries))
+    torch.cuda.synchronize()
+    assert torch.equal(wf[:w1.numel()].view(9, 128, 64), ops.pack_weight_fprop(w1))
+    assert torch.equal(wd[:w1.numel()].view(9, 64, 128), ops.pack_weight_dgrad(w1))
+    assert torch.equal(wf[w1.numel():w1.numel() + w2.numel()].view(1, 128, 64), ops.pack_weight_fprop(w2))
+    stem = wf[w1.numel() + w2.numel():].view(64, 64)
+    assert torch.equal(stem[:, :27], w0.permute(0, 2, 3, 1).reshape(64, 27).to(torch.bfloat16))
+    assert (stem[:, 27:] == 0).all()
