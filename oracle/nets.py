@@ -1,0 +1,103 @@
+"""Functional fp32 restatement of the reference's CIFAR networks (test oracle; see oracle/__init__.py).
+
+`build_resnet18_params(seed)` constructs torch.nn layers in exactly the order the reference's constructor
+does (models/resnet.py:97-117 -> BasicBlock.__init__ :19-36), so the default initialisers consume the CPU
+generator identically and the weights equal `torch.manual_seed(seed); models.resnet.ResNet18()` bit for bit.
+`resnet_forward` restates ResNet.forward / BasicBlock.forward (models/resnet.py:47-51,132-140) with
+functional ops; autograd of these fp32 ops is the backward oracle.
+"""
+from collections import OrderedDict
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+RESNET18_BLOCKS = (2, 2, 2, 2)
+RESNET_PLANES = (64, 128, 256, 512)
+
+
+def build_resnet_params(seed, num_blocks=RESNET18_BLOCKS, num_classes=10):
+    """Returns (params, buffers): OrderedDicts keyed like the reference's state_dict."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 64, 3, 1)                       # models/resnet.py:102-103
+    bn("bn1", 64)                                    # :104
+    in_planes = 64
+    for li, (nb, planes) in enumerate(zip(num_blocks, RESNET_PLANES)):   # :105-108, _make_layer :111-117
+        strides = [1 if li == 0 else 2] + [1] * (nb - 1)
+        for bi, s in enumerate(strides):
+            name = f"layer{li + 1}.{bi}"
+            conv(name + ".conv1", in_planes, planes, 3, s)     # :23-24
+            bn(name + ".bn1", planes)                          # :25
+            conv(name + ".conv2", planes, planes, 3, 1)        # :26-27
+            bn(name + ".bn2", planes)                          # :28
+            if s != 1 or in_planes != planes:                  # :31
+                conv(name + ".shortcut.0", in_planes, planes, 1, s)   # :33-34
+                bn(name + ".shortcut.1", planes)                      # :35
+            in_planes = planes
+    lin = nn.Linear(in_planes, num_classes)          # :109
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def _bn(x, name, params, buffers, training, momentum=0.1, eps=1e-5):
+    rm, rv = buffers[name + ".running_mean"], buffers[name + ".running_var"]
+    if training:
+        buffers[name + ".num_batches_tracked"] += 1
+    return F.batch_norm(x, rm, rv, params[name + ".weight"], params[name + ".bias"], training=training,
+                        momentum=momentum, eps=eps)
+
+
+def resnet_forward(x, params, buffers, training=True, num_blocks=RESNET18_BLOCKS, taps=None):
+    """x: [N,3,32,32] fp32 NCHW. `taps` (optional dict) receives named intermediate tensors."""
+    def tap(name, t):
+        if taps is not None:
+            taps[name] = t
+        return t
+
+    out = F.conv2d(x, params["conv1.weight"], padding=1)
+    tap("conv1", out)
+    out = tap("act0", F.relu(_bn(out, "bn1", params, buffers, training)))          # resnet.py:132
+    in_planes = 64
+    for li, (nb, planes) in enumerate(zip(num_blocks, RESNET_PLANES)):
+        strides = [1 if li == 0 else 2] + [1] * (nb - 1)
+        for bi, s in enumerate(strides):
+            name = f"layer{li + 1}.{bi}"
+            xin = out
+            o = tap(name + ".conv1", F.conv2d(xin, params[name + ".conv1.weight"], stride=s, padding=1))
+            o = F.relu(_bn(o, name + ".bn1", params, buffers, training))           # :47
+            o = tap(name + ".conv2", F.conv2d(o, params[name + ".conv2.weight"], padding=1))
+            o = _bn(o, name + ".bn2", params, buffers, training)                   # :48
+            if (name + ".shortcut.0.weight") in params:
+                sc = F.conv2d(xin, params[name + ".shortcut.0.weight"], stride=s)
+                sc = _bn(sc, name + ".shortcut.1", params, buffers, training)
+            else:
+                sc = xin
+            out = tap(name + ".out", F.relu(o + sc))                               # :49-50
+            in_planes = planes
+    out = F.avg_pool2d(out, 4)                                                     # :137
+    out = out.view(out.size(0), -1)                                                # :138
+    return F.linear(out, params["linear.weight"], params["linear.bias"])          # :139
+
+
+def train_step_grads(x, target, params, buffers, forward=resnet_forward, taps=None):
+    """One forward + CrossEntropy + backward (main.py:101-104). Returns (loss, logits, grads by name)."""
+    leaves = OrderedDict((k, v.detach().clone().requires_grad_(True)) for k, v in params.items())
+    logits = forward(x, leaves, buffers, training=True, taps=taps)
+    loss = F.cross_entropy(logits, target)                                         # main.py:86,103
+    grads = torch.autograd.grad(loss, list(leaves.values()))
+    return loss.detach(), logits.detach(), OrderedDict(zip(leaves.keys(), grads))

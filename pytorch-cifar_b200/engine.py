@@ -1,0 +1,369 @@
+"""Execution engine: turns a network description (the composition the reference's models/*.py express
+with nn.Conv2d / nn.BatchNorm2d / F.relu / `+=`) into a static list of kernel launches over
+pre-allocated NHWC bf16 buffers and flat fp32 parameter / gradient arenas.
+
+Everything here is host-side plumbing: torch supplies device memory and streams; all arithmetic is
+done by the sm_100a kernels behind the C-ABI (`ops`). Because buffer addresses and launch order are
+static, a whole training step can be captured into one CUDA graph (see trainer.py).
+
+Reference anchors: models/resnet.py:38-51 (BasicBlock.forward), :132-140 (ResNet.forward);
+main.py:99-105 (step order).
+"""
+from collections import OrderedDict
+
+import torch
+
+from . import ops
+
+BN_EPS = 1e-5        # nn.BatchNorm2d default, models/resnet.py:25
+BN_MOMENTUM = 0.1    # nn.BatchNorm2d default
+
+
+def _align(n, a):
+    return (n + a - 1) // a * a
+
+
+# --------------------------------------------------------------------------------------------
+# Network descriptions. A spec is a dict:
+#   params : OrderedDict name -> shape, in the reference's net.parameters() order
+#   buffers: OrderedDict name -> shape (BN running stats; num_batches_tracked handled separately)
+#   layout : model-family specific topology used by the plan builders below
+# --------------------------------------------------------------------------------------------
+def resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=10):
+    """ResNet-18/34 (BasicBlock) exactly as models/resnet.py:96-144 composes it."""
+    params, buffers, blocks = OrderedDict(), OrderedDict(), []
+
+    def conv(name, cout, cin, k):
+        params[name + ".weight"] = (cout, cin, k, k)
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    conv("conv1", 64, 3, 3)
+    bn("bn1", 64)
+    in_planes = 64
+    for li, (nb, pl) in enumerate(zip(num_blocks, planes)):
+        strides = [1 if li == 0 else 2] + [1] * (nb - 1)
+        for bi, s in enumerate(strides):
+            name = f"layer{li + 1}.{bi}"
+            conv(name + ".conv1", pl, in_planes, 3)
+            bn(name + ".bn1", pl)
+            conv(name + ".conv2", pl, pl, 3)
+            bn(name + ".bn2", pl)
+            shortcut = s != 1 or in_planes != pl
+            if shortcut:
+                conv(name + ".shortcut.0", pl, in_planes, 1)
+                bn(name + ".shortcut.1", pl)
+            blocks.append(dict(name=name, cin=in_planes, cout=pl, stride=s, shortcut=shortcut))
+            in_planes = pl
+    params["linear.weight"] = (num_classes, in_planes)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="resnet", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes,
+                feat=in_planes)
+
+
+class ConvUnit:
+    """One conv (+ the BatchNorm that follows it): descriptors, operand views, statistic buffers."""
+
+    def __init__(self, eng, name, bn_name, x, cin, cout, k, stride, H, W, stem=False):
+        N = eng.N
+        self.name, self.bn_name = name, bn_name
+        self.cin, self.cout, self.k, self.stride, self.H, self.W = cin, cout, k, stride, H, W
+        self.Ho, self.Wo = H // stride, W // stride
+        self.rows = N * self.Ho * self.Wo
+        self.stem = stem
+        self.x = x
+        self.y = eng.new_act(N, self.Ho, self.Wo, cout)
+        if stem:
+            # the 3-channel stem runs as a 1x1 GEMM over an im2col operand (k = 27 padded to 64)
+            self.desc = ops.conv_desc(N, H, W, 64, cout, 1, 1)
+            self.desc_w = ops.conv_desc(N, H, W, 64, cout, 1, 1, cin_valid=27, kflat_cin=3)
+        else:
+            self.desc = ops.conv_desc(N, H, W, cin, cout, k, stride)
+            self.desc_w = self.desc
+        self.wf = eng.wf_view(name)
+        self.wd = None if stem else eng.wd_view(name)
+        self.dw = eng.grad_view(name + ".weight")
+        if bn_name is not None:
+            self.gamma = eng.param_view(bn_name + ".weight")
+            self.beta = eng.param_view(bn_name + ".bias")
+            self.dgamma = eng.grad_view(bn_name + ".weight")
+            self.dbeta = eng.grad_view(bn_name + ".bias")
+            self.rm = eng.buffer_view(bn_name + ".running_mean")
+            self.rv = eng.buffer_view(bn_name + ".running_var")
+            self.scale, self.shift, self.mean, self.rstd = (eng.new_f32(cout) for _ in range(4))
+
+    # ---- forward pieces
+    def fprop(self, eng, stats=True):
+        ps, pq = (eng.part_sum, eng.part_sq) if stats else (None, None)
+        self.stat_rows = ops.conv_fprop(self.desc, self.x, self.wf, self.y, ps, pq)
+
+    def bn_stats(self, eng, training):
+        if training:
+            ops.bn_finalize(eng.part_sum, eng.part_sq, self.stat_rows, self.cout, self.rows, self.gamma, self.beta,
+                            BN_EPS, BN_MOMENTUM, self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd)
+        else:
+            ops.bn_eval_scale_shift(self.cout, self.gamma, self.beta, self.rm, self.rv, BN_EPS, self.scale,
+                                    self.shift)
+
+    # ---- backward pieces
+    def bn_backward(self, eng, dout, act, dz_out, dy):
+        """dout: grad w.r.t. act(bn(y)) (or w.r.t. bn(y) when act is None). Writes dz (optional) and dy."""
+        prow = ops.bn_bwd_partial_rows(self.rows, self.cout)
+        ops.bn_bwd_reduce(dout, act, self.y, dz_out, self.rows, self.cout, eng.bwd_partial)
+        ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
+                            self.dgamma, self.dbeta, eng.coef_a, eng.coef_b, eng.coef_c)
+        src = dz_out if dz_out is not None else dout
+        ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout)
+
+    def wgrad(self, dy):
+        ops.conv_wgrad(self.desc_w, self.x, dy, self.dw)
+
+    def dgrad(self, dy, dx, add_src=None):
+        ops.conv_dgrad(self.desc, dy, self.wd, dx, add_src)
+
+
+class Engine:
+    """Static execution plan for one (network, batch size) pair on one GPU."""
+
+    def __init__(self, spec, batch, device="cuda"):
+        self.spec, self.N, self.device = spec, batch, torch.device(device)
+        self._layout_params()
+        self._acts = []
+        f32 = dict(device=self.device, dtype=torch.float32)
+        self.part_sum = torch.zeros(ops.MAX_STAT_ROWS, 2048, **f32)
+        self.part_sq = torch.zeros(ops.MAX_STAT_ROWS, 2048, **f32)
+        self.bwd_partial = torch.zeros(148 * 4 * 2 * 2048, **f32)
+        self.coef_a, self.coef_b, self.coef_c = (torch.zeros(2048, **f32) for _ in range(3))
+        self.fwd_ops, self.bwd_ops = [], []
+        if spec["family"] == "resnet":
+            self._build_resnet()
+        else:
+            raise NotImplementedError(spec["family"])
+
+    # ------------------------------------------------------------------ arenas
+    def _layout_params(self):
+        spec = self.spec
+        self.p_off, off = OrderedDict(), 0
+        for name, shape in spec["params"].items():
+            n = 1
+            for s in shape:
+                n *= s
+            self.p_off[name] = (off, n, shape)
+            off = _align(off + n, 4)
+        self.n_param = _align(off, 4)
+        self.b_off, off = OrderedDict(), 0
+        for name, shape in spec["buffers"].items():
+            self.b_off[name] = (off, shape[0])
+            off = _align(off + shape[0], 4)
+        f32 = dict(device=self.device, dtype=torch.float32)
+        self.P = torch.zeros(self.n_param, **f32)      # master parameters (reference layouts: OIHW etc.)
+        self.G = torch.zeros(self.n_param, **f32)      # gradients, same layout (= the reference's .grad)
+        self.M = torch.zeros(self.n_param, **f32)      # SGD momentum buffers
+        self.B = torch.zeros(max(off, 4), **f32)       # BN running statistics
+        # bf16 GEMM operand copies of the conv weights
+        self.wf_off, self.wd_off, entries = {}, {}, []
+        wf_n = wd_n = 0
+        for name, shape in spec["params"].items():
+            if len(shape) != 4:
+                continue
+            cname = name[:-len(".weight")]
+            cout, cin, k, _ = shape
+            poff = self.p_off[name][0]
+            if cin == 3:      # stem: [cout][64], k = tap*3 + c
+                self.wf_off[cname] = (wf_n, (1, cout, 64))
+                entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=-1, cout=cout, cin=cin, taps=k * k,
+                                    cin_pad=64, kflat=1))
+                wf_n += cout * 64
+            else:
+                self.wf_off[cname] = (wf_n, (k * k, cout, cin))
+                self.wd_off[cname] = (wd_n, (k * k, cin, cout))
+                entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=wd_n, cout=cout, cin=cin, taps=k * k,
+                                    cin_pad=cin))
+                wf_n += cout * cin * k * k
+                wd_n += cout * cin * k * k
+        bf = dict(device=self.device, dtype=torch.bfloat16)
+        self.WF = torch.zeros(_align(wf_n, 8), **bf)
+        self.WD = torch.zeros(_align(max(wd_n, 8), 8), **bf)
+        self.repack_entries = len(entries)
+        self.repack_table = ops.make_repack_table(entries, self.device)
+
+    def param_view(self, name):
+        off, n, shape = self.p_off[name]
+        return self.P[off:off + n].view(shape)
+
+    def grad_view(self, name):
+        off, n, shape = self.p_off[name]
+        return self.G[off:off + n].view(shape)
+
+    def buffer_view(self, name):
+        off, n = self.b_off[name]
+        return self.B[off:off + n]
+
+    def wf_view(self, cname):
+        off, shape = self.wf_off[cname]
+        n = shape[0] * shape[1] * shape[2]
+        return self.WF[off:off + n].view(shape)
+
+    def wd_view(self, cname):
+        off, shape = self.wd_off[cname]
+        n = shape[0] * shape[1] * shape[2]
+        return self.WD[off:off + n].view(shape)
+
+    def new_act(self, n, h, w, c):
+        t = torch.zeros(n, h, w, c, device=self.device, dtype=torch.bfloat16)
+        self._acts.append(t)
+        return t
+
+    def new_f32(self, *shape):
+        return torch.zeros(*shape, device=self.device, dtype=torch.float32)
+
+    # ------------------------------------------------------------------ parameters in / out
+    def load_params(self, named_params, named_buffers=None):
+        """Copy reference-layout tensors (name -> tensor, fp32) into the arenas and refresh the bf16 copies."""
+        for name, (off, n, shape) in self.p_off.items():
+            self.P[off:off + n].copy_(named_params[name].detach().reshape(-1).to(self.device, torch.float32))
+        if named_buffers is not None:
+            for name, (off, n) in self.b_off.items():
+                self.B[off:off + n].copy_(named_buffers[name].detach().to(self.device, torch.float32))
+        self.repack()
+
+    def init_bn_buffers(self):
+        for name, (off, n) in self.b_off.items():
+            self.B[off:off + n].fill_(1.0 if name.endswith("running_var") else 0.0)
+
+    def repack(self):
+        ops.repack_weights(self.P, self.WF, self.WD, self.repack_table, self.repack_entries)
+
+    def named_grads(self):
+        return OrderedDict((name, self.grad_view(name)) for name in self.p_off)
+
+    def named_params(self):
+        return OrderedDict((name, self.param_view(name)) for name in self.p_off)
+
+    def named_buffers(self):
+        return OrderedDict((name, self.buffer_view(name)) for name in self.b_off)
+
+    # ------------------------------------------------------------------ ResNet plan
+    def _build_resnet(self):
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)            # stem im2col operand (k = 27 of 64)
+        stem = ConvUnit(self, "conv1", "bn1", self.x0, 3, 64, 3, 1, 32, 32, stem=True)
+        a0 = self.new_act(N, 32, 32, 64)
+        self.units = [stem]
+        F, Bk = self.fwd_ops, []
+
+        def fwd_stem(training):
+            stem.fprop(self, True)
+            stem.bn_stats(self, training)
+            ops.bn_act_apply(stem.y, stem.scale, stem.shift, a0, stem.rows, 64, relu=True)
+        F.append(fwd_stem)
+
+        x, H, W = a0, 32, 32
+        blocks = []
+        for b in spec["blocks"]:
+            name, cin, cout, s = b["name"], b["cin"], b["cout"], b["stride"]
+            c1 = ConvUnit(self, name + ".conv1", name + ".bn1", x, cin, cout, 3, s, H, W)
+            Ho, Wo = H // s, W // s
+            a1 = self.new_act(N, Ho, Wo, cout)
+            c2 = ConvUnit(self, name + ".conv2", name + ".bn2", a1, cout, cout, 3, 1, Ho, Wo)
+            cs = None
+            if b["shortcut"]:
+                cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W)
+            out = self.new_act(N, Ho, Wo, cout)
+            self.units += [c1, c2] + ([cs] if cs else [])
+            blocks.append((c1, a1, c2, cs, out, x))
+
+            def fwd_block(training, c1=c1, a1=a1, c2=c2, cs=cs, out=out, x=x):
+                c1.fprop(self)
+                c1.bn_stats(self, training)
+                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
+                if cs is not None:
+                    cs.fprop(self)
+                    cs.bn_stats(self, training)
+                c2.fprop(self)
+                c2.bn_stats(self, training)
+                if cs is not None:
+                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, res=cs.y,
+                                     res_scale=cs.scale, res_shift=cs.shift)
+                else:
+                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, res=x)
+            F.append(fwd_block)
+            x, H, W = out, Ho, Wo
+
+        # head
+        self.feat_act, self.feat_hw, self.feat_c = x, H * W, spec["feat"]
+        K = spec["num_classes"]
+        self.lin_w, self.lin_b = self.param_view("linear.weight"), self.param_view("linear.bias")
+        self.pooled = self.new_f32(N, self.feat_c)
+        self.logits = self.new_f32(N, K)
+        self.dlogits = self.new_f32(N, K)
+
+        def fwd_head(training):
+            ops.head_fwd(self.feat_act, N, self.feat_hw, self.feat_c, self.lin_w, self.lin_b, K, self.pooled,
+                         self.logits)
+        F.append(fwd_head)
+
+        # ---- backward: gradient buffers. g_* hold d(block output); two ping-pong sets per resolution are
+        # enough because a block's input gradient is complete before the previous block consumes it.
+        def bwd_head():
+            ops.head_bwd(self.dlogits, self.pooled, self.lin_w, N, self.feat_hw, self.feat_c, K, dout_last,
+                         self.grad_view("linear.weight"), self.grad_view("linear.bias"))
+
+        dout_last = self.new_act(*self.feat_act.shape)
+        Bk.append(bwd_head)
+        dout = dout_last
+        for (c1, a1, c2, cs, out, xin) in reversed(blocks):
+            dy2 = self.new_act(*c2.y.shape)
+            da1 = self.new_act(*a1.shape)
+            dy1 = self.new_act(*c1.y.shape)
+            dys = self.new_act(*cs.y.shape) if cs is not None else None
+            dx = self.new_act(*xin.shape)
+
+            def bwd_block(c1=c1, a1=a1, c2=c2, cs=cs, out=out, dout=dout, dy2=dy2, da1=da1, dy1=dy1, dys=dys,
+                          dx=dx):
+                # out = relu(bn2(y2) + shortcut): mask in place -> dz, then BN2 backward
+                c2.bn_backward(self, dout, out, dout, dy2)
+                if cs is not None:
+                    cs.bn_backward(self, dout, None, None, dys)
+                c2.wgrad(dy2)
+                c2.dgrad(dy2, da1)
+                # a1 = relu(bn1(y1))
+                c1.bn_backward(self, da1, a1, da1, dy1)
+                c1.wgrad(dy1)
+                if cs is not None:
+                    cs.wgrad(dys)
+                    cs.dgrad(dys, dx)                     # zero-fill + even pixels
+                    c1.dgrad(dy1, dx, add_src=dx)
+                else:
+                    c1.dgrad(dy1, dx, add_src=dout)       # identity shortcut: + dz
+            Bk.append(bwd_block)
+            dout = dx
+
+        dy0 = self.new_act(*stem.y.shape)
+
+        def bwd_stem(dout=dout, dy0=dy0):
+            stem.bn_backward(self, dout, a0, dout, dy0)
+            stem.wgrad(dy0)
+        Bk.append(bwd_stem)
+        self.bwd_ops = Bk
+
+    # ------------------------------------------------------------------ execution
+    def forward(self, training=True):
+        for op in self.fwd_ops:
+            op(training)
+        return self.logits
+
+    def backward(self):
+        """Expects self.dlogits filled and self.G zeroed (conv wgrad accumulates)."""
+        for op in self.bwd_ops:
+            op()
+
+    def zero_grad(self):
+        self.G.zero_()
+
+    def activation_bytes(self):
+        return sum(t.numel() * t.element_size() for t in self._acts)

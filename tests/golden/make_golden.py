@@ -1,0 +1,119 @@
+"""Generates the golden fixtures in this directory FROM THE REFERENCE ITSELF.
+
+Run in the build container only (it imports /root/reference/models and torchvision.transforms; neither
+travels to the GPU box):   python tests/golden/make_golden.py
+The fixtures pin oracle/ (tests/test_oracle.py) and are small enough to commit.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, "/root/reference")
+
+
+def golden_resnet18():
+    import models.resnet as ref_resnet           # the reference's own model code
+    torch.manual_seed(0)
+    net = ref_resnet.ResNet18()
+    net.train()
+    rs = np.random.RandomState(0)
+    x = torch.from_numpy(rs.standard_normal((4, 3, 32, 32)).astype(np.float32))
+    target = torch.from_numpy(rs.randint(0, 10, size=(4,)).astype(np.int64))
+    logits = net(x)                              # main.py:102
+    loss = torch.nn.CrossEntropyLoss()(logits, target)   # main.py:86,103
+    loss.backward()                              # main.py:104
+    out = dict(x=x.numpy(), target=target.numpy(), logits=logits.detach().numpy(), loss=np.float32(loss.item()))
+    names, norms, heads, wsum = [], [], [], []
+    for name, p in net.named_parameters():
+        names.append(name)
+        g = p.grad.detach().reshape(-1)
+        norms.append(g.norm().item())
+        heads.append(np.pad(g[:8].numpy(), (0, max(0, 8 - g.numel()))))
+        wsum.append(p.detach().double().sum().item())
+    out["param_names"] = np.array(names)
+    out["grad_norms"] = np.array(norms, dtype=np.float64)
+    out["grad_heads"] = np.stack(heads).astype(np.float32)
+    out["weight_sums"] = np.array(wsum, dtype=np.float64)
+    bn_names, bn_rm, bn_rv = [], [], []
+    for name, b in net.named_buffers():
+        if name.endswith("running_mean"):
+            bn_names.append(name[:-len(".running_mean")])
+            bn_rm.append(b.double().sum().item())
+        if name.endswith("running_var"):
+            bn_rv.append(b.double().sum().item())
+    out["bn_names"] = np.array(bn_names)
+    out["bn_rm_sums"] = np.array(bn_rm)
+    out["bn_rv_sums"] = np.array(bn_rv)
+    # eval-mode forward after the one training forward (running stats updated once)
+    net.eval()
+    with torch.no_grad():
+        out["logits_eval"] = net(x).numpy()
+    np.savez_compressed(os.path.join(HERE, "resnet18_seed0_n4.npz"), **out)
+    print("resnet18: loss", loss.item(), "params", len(names))
+
+
+def golden_augment():
+    import torchvision.transforms as transforms
+    from PIL import Image
+    tf = transforms.Compose([                      # main.py:30-35 verbatim
+        transforms.RandomCrop(32, padding=4),
+        transforms.RandomHorizontalFlip(),
+        transforms.ToTensor(),
+        transforms.Normalize((0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010)),
+    ])
+    rs = np.random.RandomState(7)
+    imgs = rs.randint(0, 256, size=(24, 32, 32, 3)).astype(np.uint8)
+    torch.manual_seed(123)                          # num_workers=0 semantics: the global CPU generator
+    outs = [tf(Image.fromarray(im)).numpy() for im in imgs]     # TV/datasets/cifar.py:118-121
+    np.savez_compressed(os.path.join(HERE, "augment_seed123.npz"), images=imgs, seed=np.int64(123),
+                        out=np.stack(outs).astype(np.float32))
+    print("augment: 24 samples")
+
+
+def golden_sgd():
+    torch.manual_seed(5)
+    p = torch.randn(257, requires_grad=True)
+    p0 = p.detach().clone().numpy()
+    opt = torch.optim.SGD([p], lr=0.1, momentum=0.9, weight_decay=5e-4)   # main.py:87-88
+    sched = torch.optim.lr_scheduler.CosineAnnealingLR(opt, T_max=200)     # main.py:89
+    grads, traj, lrs = [], [], []
+    for step in range(4):
+        g = torch.randn(257)
+        grads.append(g.numpy().copy())
+        p.grad = g.clone()
+        opt.step()
+        traj.append(p.detach().numpy().copy())
+    for e in range(5):
+        lrs.append(opt.param_groups[0]["lr"])
+        sched.step()
+    np.savez_compressed(os.path.join(HERE, "sgd_traj.npz"), p0=p0, grads=np.stack(grads), traj=np.stack(traj),
+                        lrs=np.array(lrs, dtype=np.float64))
+    print("sgd: 4 steps")
+
+
+def golden_sampler():
+    from torch.utils.data.distributed import DistributedSampler
+
+    class _DS:
+        def __len__(self):
+            return 50000
+    out = {}
+    for world in (1, 2, 4, 8):
+        for rank in (0, world - 1):
+            s = DistributedSampler(_DS(), num_replicas=world, rank=rank)   # main_dist.py:110, epoch stays 0
+            idx = np.array(list(iter(s)), dtype=np.int64)
+            out[f"w{world}_r{rank}_head"] = idx[:64]
+            out[f"w{world}_r{rank}_len"] = np.int64(len(idx))
+            out[f"w{world}_r{rank}_sum"] = np.int64(idx.sum())
+    np.savez_compressed(os.path.join(HERE, "sampler.npz"), **out)
+    print("sampler ok")
+
+
+if __name__ == "__main__":
+    golden_resnet18()
+    golden_augment()
+    golden_sgd()
+    golden_sampler()
