@@ -76,6 +76,31 @@ SIGNATURES = {
 }
 
 _lib = None
+recording = None   # when a list: every C-ABI call is appended as (name, args) before it is issued
+
+
+class _LibProxy:
+    """Attribute access returns the ctypes function wrapped so calls can be recorded and replayed
+    (bench.py uses this to count kernel launches and to time kernel families in isolation)."""
+
+    def __init__(self, cdll):
+        self._cdll = cdll
+        self._cache = {}
+
+    def __getattr__(self, name):
+        fn = getattr(self._cdll, name)
+        if name in ("b2c_error_string", "b2c_version", "b2c_bn_bwd_partial_rows"):
+            return fn
+
+        def call(*args):
+            if recording is not None:
+                recording.append((name, args))
+            return fn(*args)
+        self.__dict__[name] = call
+        return call
+
+    def raw(self, name):
+        return getattr(self._cdll, name)
 
 
 def load():
@@ -93,8 +118,8 @@ def load():
         fn.restype = _I
     lib.b2c_error_string.argtypes = [_I]
     lib.b2c_error_string.restype = ctypes.c_char_p
-    _lib = lib
-    return lib
+    _lib = _LibProxy(lib)
+    return _lib
 
 
 def check(code, where):

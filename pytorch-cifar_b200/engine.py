@@ -129,9 +129,11 @@ class ConvUnit:
 class Engine:
     """Static execution plan for one (network, batch size) pair on one GPU."""
 
-    def __init__(self, spec, batch, device="cuda"):
+    def __init__(self, spec, batch, device="cuda", share_from=None):
+        """share_from: another Engine of the same spec whose parameter / buffer arenas are reused (e.g. an
+        eval-batch plan next to the training plan)."""
         self.spec, self.N, self.device = spec, batch, torch.device(device)
-        self._layout_params()
+        self._layout_params(share_from)
         self._acts = []
         f32 = dict(device=self.device, dtype=torch.float32)
         self.part_sum = torch.zeros(ops.MAX_STAT_ROWS, 2048, **f32)
@@ -145,7 +147,7 @@ class Engine:
             raise NotImplementedError(spec["family"])
 
     # ------------------------------------------------------------------ arenas
-    def _layout_params(self):
+    def _layout_params(self, share_from=None):
         spec = self.spec
         self.p_off, off = OrderedDict(), 0
         for name, shape in spec["params"].items():
@@ -160,10 +162,13 @@ class Engine:
             self.b_off[name] = (off, shape[0])
             off = _align(off + shape[0], 4)
         f32 = dict(device=self.device, dtype=torch.float32)
-        self.P = torch.zeros(self.n_param, **f32)      # master parameters (reference layouts: OIHW etc.)
-        self.G = torch.zeros(self.n_param, **f32)      # gradients, same layout (= the reference's .grad)
-        self.M = torch.zeros(self.n_param, **f32)      # SGD momentum buffers
-        self.B = torch.zeros(max(off, 4), **f32)       # BN running statistics
+        if share_from is not None:
+            self.P, self.G, self.M, self.B = share_from.P, share_from.G, share_from.M, share_from.B
+        else:
+            self.P = torch.zeros(self.n_param, **f32)      # master parameters (reference layouts: OIHW etc.)
+            self.G = torch.zeros(self.n_param, **f32)      # gradients, same layout (= the reference's .grad)
+            self.M = torch.zeros(self.n_param, **f32)      # SGD momentum buffers
+            self.B = torch.zeros(max(off, 4), **f32)       # BN running statistics
         # bf16 GEMM operand copies of the conv weights
         self.wf_off, self.wd_off, entries = {}, {}, []
         wf_n = wd_n = 0
@@ -186,10 +191,13 @@ class Engine:
                 wf_n += cout * cin * k * k
                 wd_n += cout * cin * k * k
         bf = dict(device=self.device, dtype=torch.bfloat16)
-        self.WF = torch.zeros(_align(wf_n, 8), **bf)
-        self.WD = torch.zeros(_align(max(wd_n, 8), 8), **bf)
         self.repack_entries = len(entries)
-        self.repack_table = ops.make_repack_table(entries, self.device)
+        if share_from is not None:
+            self.WF, self.WD, self.repack_table = share_from.WF, share_from.WD, share_from.repack_table
+        else:
+            self.WF = torch.zeros(_align(wf_n, 8), **bf)
+            self.WD = torch.zeros(_align(max(wd_n, 8), 8), **bf)
+            self.repack_table = ops.make_repack_table(entries, self.device)
 
     def param_view(self, name):
         off, n, shape = self.p_off[name]

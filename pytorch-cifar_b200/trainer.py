@@ -1,0 +1,211 @@
+"""Whole-step trainer: the loop body of the reference's train() (main.py:99-105; main_dist.py:174-191)
+
+    inputs, targets -> optimizer.zero_grad() -> net(inputs) -> criterion -> loss.backward() -> optimizer.step()
+
+as one static sequence of kernel launches, optionally captured into a single CUDA graph. The input
+pipeline (main.py:30-35) runs on the GPU over a uint8 dataset resident in HBM, driven by host-side draws
+that reproduce torch's CPU generator (data.py). With world > 1 the gradient arena is all-reduced with
+NCCL in buckets on a side stream while backward continues (the DDP Reducer's job, main_dist.py:141-144);
+the 1/world of DDP's mean is folded into the SGD kernel.
+"""
+import numpy as np
+import torch
+
+from . import data as hostdata
+from . import ops
+from .engine import Engine
+
+
+class Trainer:
+    def __init__(self, spec, batch, device="cuda", lr=0.1, momentum=0.9, weight_decay=5e-4, world=1, rank=0,
+                 use_graph=True, resident_dataset=True, bucket_bytes=25 * 2 ** 20):
+        self.device = torch.device(device)
+        self.N, self.world, self.rank = batch, world, rank
+        self.eng = Engine(spec, batch, device)
+        self.K = spec["num_classes"]
+        dev = self.device
+        self.hyper_host = torch.tensor([lr, momentum, weight_decay, 1.0 / world, 1.0], dtype=torch.float32).pin_memory()
+        self.hyper = self.hyper_host.to(dev)
+        self.idx_dev = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.ijf_dev = torch.zeros(batch, 3, dtype=torch.int8, device=dev)
+        self.target = torch.zeros(batch, dtype=torch.int64, device=dev)
+        self.loss = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.correct = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.resident = resident_dataset
+        self.data = None
+        if not resident_dataset:
+            # e2e mode: the caller hands over host batches; they are staged here and read with idx = 0..N-1
+            self.data = torch.zeros(batch, 32, 32, 3, dtype=torch.uint8, device=dev)
+            self.idx_dev.copy_(torch.arange(batch, device=dev))
+        # pinned staging ring for per-step host inputs
+        self._ring = 4
+        self._slot = 0
+        self._pin_idx = [torch.zeros(batch, dtype=torch.int64).pin_memory() for _ in range(self._ring)]
+        self._pin_ijf = [torch.zeros(batch, 3, dtype=torch.int8).pin_memory() for _ in range(self._ring)]
+        self._pin_tgt = [torch.zeros(batch, dtype=torch.int64).pin_memory() for _ in range(self._ring)]
+        self._pin_img = None
+        self._ring_events = [None] * self._ring
+        self._loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
+        self.use_graph = use_graph
+        self.graph = None
+        self.steps_done = 0
+        self.launches_per_step = None
+        self.comm_stream = torch.cuda.Stream(device=dev) if world > 1 else None
+        self.bucket_bytes = bucket_bytes
+        self._buckets = self._plan_buckets() if world > 1 else []
+
+    # ------------------------------------------------------------------ setup
+    def load_params(self, params, buffers=None):
+        self.eng.load_params(params, buffers)
+        if buffers is None:
+            self.eng.init_bn_buffers()
+
+    def set_dataset(self, images_u8, labels):
+        """images_u8: [n,32,32,3] uint8 (numpy or tensor), copied to HBM once; labels stay on the host."""
+        assert self.resident
+        t = torch.as_tensor(images_u8)
+        assert t.dtype == torch.uint8 and tuple(t.shape[1:]) == (32, 32, 3)
+        self.data = t.contiguous().to(self.device)
+        self.labels_host = np.asarray(labels, dtype=np.int64)
+
+    def set_lr(self, lr):
+        self.hyper_host[0] = lr
+        self.hyper.copy_(self.hyper_host, non_blocking=True)
+
+    # ------------------------------------------------------------------ gradient buckets (DDP)
+    def _plan_buckets(self):
+        """Contiguous ranges of the gradient arena, grouped in backward order (last layers first) up to
+        bucket_bytes each — the Reducer's bucketing (reducer.hpp:30-31) over a pre-flattened arena."""
+        eng = self.eng
+        names = list(eng.p_off.keys())
+        # group boundaries: parameters of one backward op are contiguous in the arena
+        groups, cur = [], None
+        for name in names:
+            key = name.split(".conv")[0].split(".bn")[0].split(".shortcut")[0] if name.startswith("layer") else (
+                "head" if name.startswith("linear") else "stem")
+            if cur is None or cur[0] != key:
+                cur = [key, eng.p_off[name][0], 0]
+                groups.append(cur)
+            off, n, _ = eng.p_off[name]
+            cur[2] = off + n
+        ranges = [(g[1], g[2]) for g in groups]          # forward order
+        buckets, end, start = [], None, None
+        for a, b in reversed(ranges):                     # backward order
+            if end is None:
+                end, start = b, a
+            else:
+                start = a
+            if (end - start) * 4 >= self.bucket_bytes:
+                buckets.append((start, end))
+                end = None
+        if end is not None:
+            buckets.append((start, end))
+        # map: after backward op i (head, blocks reversed, stem) which bucket (if any) is complete
+        order = ["head"] + [g[0] for g in reversed(groups) if g[0] not in ("head", "stem")] + ["stem"]
+        first_off = {g[0]: g[1] for g in groups}
+        ready = {}
+        for bi, (a, b) in enumerate(buckets):
+            for pos, key in enumerate(order):
+                if first_off[key] == a:
+                    ready[pos] = bi
+        self._bucket_ready_after = ready
+        return buckets
+
+    # ------------------------------------------------------------------ one step
+    def _launch_step(self):
+        eng = self.eng
+        ops.augment_im2col(self.data, self.idx_dev, self.ijf_dev, eng.x0)
+        eng.zero_grad()
+        eng.forward(True)
+        ops.ce_loss(eng.logits, self.target, self.N, self.K, eng.dlogits, self.loss, self.correct)
+        if self.world == 1:
+            eng.backward()
+        else:
+            import torch.distributed as dist
+            main = torch.cuda.current_stream()
+            for pos, op in enumerate(eng.bwd_ops):
+                op()
+                bi = self._bucket_ready_after.get(pos)
+                if bi is not None:
+                    a, b = self._buckets[bi]
+                    ev = torch.cuda.Event()
+                    ev.record(main)
+                    self.comm_stream.wait_event(ev)
+                    with torch.cuda.stream(self.comm_stream):
+                        dist.all_reduce(eng.G[a:b])      # sum; the mean's 1/world is applied inside sgd_step
+            done = torch.cuda.Event()
+            done.record(self.comm_stream)
+            main.wait_event(done)
+        ops.sgd_step(eng.P, eng.G, eng.M, self.hyper)
+        eng.repack()
+
+    def _stage_inputs(self, idx, ijf, targets, images=None):
+        s = self._slot
+        self._slot = (s + 1) % self._ring
+        if self._ring_events[s] is not None:
+            self._ring_events[s].synchronize()
+        n = self.N
+        self._pin_ijf[s].numpy()[...] = ijf
+        self._pin_tgt[s].numpy()[...] = targets
+        self.ijf_dev.copy_(self._pin_ijf[s], non_blocking=True)
+        self.target.copy_(self._pin_tgt[s], non_blocking=True)
+        if images is not None:
+            if self._pin_img is None:
+                self._pin_img = [torch.zeros(n, 32, 32, 3, dtype=torch.uint8).pin_memory() for _ in range(self._ring)]
+            self._pin_img[s].numpy()[...] = images
+            self.data.copy_(self._pin_img[s], non_blocking=True)
+        else:
+            self._pin_idx[s].numpy()[...] = idx
+            self.idx_dev.copy_(self._pin_idx[s], non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._ring_events[s] = ev
+
+    def _run(self):
+        if not self.use_graph:
+            self._launch_step()
+        else:
+            if self.graph is None:
+                self._capture()
+            self.graph.replay()
+        if self.steps_done == 0:
+            self.hyper_host[4] = 0.0
+            self.hyper.copy_(self.hyper_host, non_blocking=True)
+        self.steps_done += 1
+
+    def _capture(self):
+        # warm-up outside capture is the caller's first eager step(s); here: capture only.
+        # State mutated by a step (params, momentum, BN stats) is advanced by replays only, so save/restore
+        # is unnecessary: capture itself does not execute kernels.
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._launch_step()
+        self.graph = g
+
+    def step(self, idx, ijf):
+        """One training step on dataset samples `idx` (host int64 [N]) with crop/flip draws `ijf` (int8 [N,3])."""
+        self._stage_inputs(idx, ijf, self.labels_host[idx])
+        self._run()
+        return self.loss
+
+    def step_host_batch(self, images_u8, labels, ijf):
+        """One training step on a HOST uint8 batch [N,32,32,3] (copied to the device inside the call)."""
+        assert not self.resident
+        self._stage_inputs(None, ijf, labels, images=images_u8)
+        self._run()
+        return self.loss
+
+    def read_loss(self):
+        """Device -> host read of the last step's loss (the reference's loss.item(), main.py:107)."""
+        self._loss_host.copy_(self.loss, non_blocking=False)
+        return float(self._loss_host[0])
+
+
+def make_epoch_plan(n, batch, world=1, rank=0, seed=0, distributed=False):
+    """Index batches for one epoch the way the reference's loaders produce them."""
+    if distributed:
+        idx = hostdata.distributed_indices(n, world, rank, seed=0, epoch=0)
+    else:
+        idx = hostdata.randperm(hostdata.TorchCpuMT19937(seed), n)
+    return hostdata.batches(idx, batch)
