@@ -77,8 +77,10 @@ class _Unit:
         return torch.nn.grad.conv2d_input(self.x.shape, self.wq, dy, stride=self.stride, padding=self.pad)
 
 
-def resnet_train_step(x, target, params, buffers, round_bf16, num_blocks=RESNET18_BLOCKS, taps=None):
-    """Returns (loss, logits, grads). `buffers` running stats are updated in place (pass None to skip)."""
+def resnet_train_step(x, target, params, buffers, round_bf16, num_blocks=RESNET18_BLOCKS, taps=None, trace=None):
+    """Returns (loss, logits, grads). `buffers` running stats are updated in place (pass None to skip).
+    `trace` (optional dict) receives every stored tensor of the step, forward and backward, per block, so a
+    test can teacher-force one block of the CUDA path at a time."""
     rnd = round_bf16
     P = params
     grads = OrderedDict()
@@ -128,7 +130,11 @@ def resnet_train_step(x, target, params, buffers, round_bf16, num_blocks=RESNET1
     grads["linear.bias"] = dlogits.sum(0)
     dpooled = dlogits @ P["linear.weight"]
     dout = _r((dpooled / hw).view(N, -1, 1, 1).expand_as(out).contiguous(), rnd)
+    if trace is not None:
+        trace.update(stem=stem, a0=a0, blocks=blocks, pooled=pooled, dlogits=dlogits, dout_in=[], dx_out=[])
     for (c1, a1, c2, cs, out_b) in reversed(blocks):
+        if trace is not None:
+            trace["dout_in"].append(dout)
         dz = dout * (out_b > 0).float()
         dy2 = c2.bn_backward(dz, grads)
         dys = cs.bn_backward(dz, grads) if cs is not None else None
@@ -143,6 +149,8 @@ def resnet_train_step(x, target, params, buffers, round_bf16, num_blocks=RESNET1
             dout = _r(c1.dgrad(dy1) + dx0, rnd)
         else:
             dout = _r(c1.dgrad(dy1) + dz, rnd)
+        if trace is not None:
+            trace["dx_out"].append(dout)
     dz0 = dout * (a0 > 0).float()
     dy0 = stem.bn_backward(dz0, grads)
     stem.wgrad(dy0, grads)

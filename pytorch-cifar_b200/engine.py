@@ -324,6 +324,8 @@ class Engine:
         dout_last = self.new_act(*self.feat_act.shape)
         Bk.append(bwd_head)
         dout = dout_last
+        self.stem_unit, self.a0 = stem, a0
+        self.block_bufs = []      # backward order: tensors of each block, for tests / introspection
         for (c1, a1, c2, cs, out, xin) in reversed(blocks):
             dy2 = self.new_act(*c2.y.shape)
             da1 = self.new_act(*a1.shape)
@@ -349,6 +351,7 @@ class Engine:
                 else:
                     c1.dgrad(dy1, dx, add_src=dout)       # identity shortcut: + dz
             Bk.append(bwd_block)
+            self.block_bufs.append(dict(c1=c1, a1=a1, c2=c2, cs=cs, out=out, xin=xin, dout=dout, dx=dx))
             dout = dx
 
         dy0 = self.new_act(*stem.y.shape)
