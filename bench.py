@@ -45,7 +45,7 @@ class ClockSampler:
         self.proc = None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             pass
@@ -187,10 +187,11 @@ def run_product(args):
     # this rank's sample order and crop/flip draws (DistributedSampler semantics when world > 1)
     idx_all = data.distributed_indices(n_data, world, rank) if world > 1 else data.randperm(data.TorchCpuMT19937(0), n_data)
     rng = data.TorchCpuMT19937(1000 + rank)
-    need = (K + W) * per_gpu
+    S = min(K + W, 64)                                  # distinct pre-staged steps (cycled)
+    need = S * per_gpu
     reps = -(-need // len(idx_all))
-    idx_all = np.tile(idx_all, reps)[:need].reshape(K + W, per_gpu)
-    ijf_all = data.draw_crop_flip(rng, need).reshape(K + W, per_gpu, 3)
+    idx_all = np.tile(idx_all, reps)[:need].reshape(S, per_gpu)
+    ijf_all = data.draw_crop_flip(rng, need).reshape(S, per_gpu, 3)
 
     def barrier():
         if world > 1:
@@ -217,6 +218,7 @@ def run_product(args):
     d_tgt = torch.from_numpy(labels[idx_all]).to(dev)
 
     def resident_step(k):
+        k %= S
         tr.idx_dev.copy_(d_idx[k]); tr.ijf_dev.copy_(d_ijf[k]); tr.target.copy_(d_tgt[k])
         tr._run()
 
@@ -229,10 +231,10 @@ def run_product(args):
     _lib.recording = None
     tr.use_graph = use_graph
     launches_per_step = count_launches(calls)
+    sampler = ClockSampler(local) if rank == 0 else None      # samples warm-up + timed region (all under load)
     for k in range(1, W):
         resident_step(k)
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for k in range(W, W + K):
@@ -284,17 +286,17 @@ def run_product(args):
     tr2 = trainer.Trainer(engine.resnet_spec(), per_gpu, dev, world=world, rank=rank, use_graph=not args.no_graph,
                           resident_dataset=False)
     tr2.load_params(params, bufs)
-    host_batches = [np.ascontiguousarray(images[idx_all[k]]) for k in range(min(K + W, 8))]
-    host_labels = [labels[idx_all[k]] for k in range(min(K + W, 8))]
+    host_batches = [np.ascontiguousarray(images[idx_all[k]]) for k in range(min(S, 8))]
+    host_labels = [labels[idx_all[k]] for k in range(min(S, 8))]
     for k in range(W):
-        tr2.step_host_batch(host_batches[k % len(host_batches)], host_labels[k % len(host_batches)], ijf_all[k])
+        tr2.step_host_batch(host_batches[k % len(host_batches)], host_labels[k % len(host_batches)], ijf_all[k % S])
         tr2.read_loss()
     barrier()
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     t0.record()
     for k in range(W, W + K):
         j = k % len(host_batches)
-        tr2.step_host_batch(host_batches[j], host_labels[j], ijf_all[k])
+        tr2.step_host_batch(host_batches[j], host_labels[j], ijf_all[k % S])
         tr2.read_loss()
     t1.record()
     barrier()
@@ -333,8 +335,8 @@ def run_product(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=1024, help="per-GPU batch (weak) or global batch (strong)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
