@@ -32,6 +32,7 @@ extern "C" {
 #define B2C_ERR_UNSUPPORTED (-10001) /* shape / option outside what the kernels implement */
 #define B2C_ERR_DRIVER (-10002)      /* cuTensorMapEncodeTiled unavailable or failed */
 #define B2C_ERR_ARG (-10003)         /* null / misaligned / inconsistent argument */
+#define B2C_ERR_TOO_LARGE (-10004)   /* size beyond the built-in scratch of a *_noalloc entry point */
 
 B2C_API int b2c_version(void);
 /* Human-readable text for a return code of this library (static storage). */
@@ -102,6 +103,26 @@ B2C_API int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, 
 B2C_API int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, float count, const float* gamma,
                         const float* save_mean, const float* save_rstd, float* dgamma, float* dbeta, float* coef_a,
                         float* coef_b, float* coef_c, void* stream);
+
+/* (No counterpart in the reference: this entry point exists for the embedding application, not for parity.)
+ * b2c_bn_bwd_reduce + b2c_bn_bwd_finalize in ONE call that allocates nothing and takes no scratch pointer:
+ * the partial rows between the two kernels live in a fixed array inside the library (2.3 MiB, resident on
+ * every GPU that loads libb2c.so until the process exits). Use it where a cudaMalloc is not an option around
+ * the call: device memory fully owned by another allocator or a fixed budget, a latency-bound loop that
+ * cannot absorb cudaMalloc's device synchronisation, or a plug-in that only ever receives input/output
+ * pointers. Inputs and outputs are the caller's, exactly as for the two-call form, and the results are the
+ * same. Limits and rules:
+ *   - channels <= B2C_NOALLOC_MAX_CHANNELS, otherwise B2C_ERR_TOO_LARGE (rows are not limited);
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, once per
+ *     device, with that device current); make that first call before starting any stream capture;
+ *   - all calls on a device share the one array. A call never reads what an earlier call left there
+ *     (everything it reads it has written first, so nothing needs clearing), but two calls that overlap on
+ *     the GPU (two streams, concurrent graph replays) race: serialise them. */
+#define B2C_NOALLOC_MAX_CHANNELS 512
+B2C_API int b2c_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
+                             int channels, float count, const float* gamma, const float* save_mean,
+                             const float* save_rstd, float* dgamma, float* dbeta, float* coef_a, float* coef_b,
+                             float* coef_c, void* stream);
 
 /* dy = A*dz + B*y + C per channel (bf16). */
 B2C_API int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,

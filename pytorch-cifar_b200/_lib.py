@@ -14,6 +14,7 @@ CSRC = os.path.join(_HERE, "csrc")
 B2C_ERR_UNSUPPORTED = -10001
 B2C_ERR_DRIVER = -10002
 B2C_ERR_ARG = -10003
+B2C_ERR_TOO_LARGE = -10004
 
 
 class B2cError(RuntimeError):
@@ -65,6 +66,7 @@ SIGNATURES = {
     "b2c_bn_bwd_reduce": [_P, _P, _P, _P, _LL, _I, _P, _P],
     "b2c_bn_bwd_finalize": [_P, _I, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _LL, _I, _P],
+    "b2c_bn_bwd_stats_noalloc": [_P, _P, _P, _P, _LL, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_head_fwd": [_P, _I, _I, _I, _P, _P, _I, _P, _P, _P],
     "b2c_ce_loss": [_P, _P, _I, _I, _P, _P, _P, _P],
     "b2c_head_bwd": [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P],

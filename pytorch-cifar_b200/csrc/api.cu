@@ -107,6 +107,9 @@ const char* b2c_error_string(int code) {
     if (code == B2C_ERR_UNSUPPORTED) return "b2c: shape or option not supported by the sm_100a kernels";
     if (code == B2C_ERR_DRIVER) return "b2c: cuTensorMapEncodeTiled unavailable or failed (no CUDA driver?)";
     if (code == B2C_ERR_ARG) return "b2c: invalid argument (null, misaligned or inconsistent)";
+    if (code == B2C_ERR_TOO_LARGE)
+        return "b2c: size exceeds the fixed in-library scratch of this no-allocation entry point "
+               "(channels <= B2C_NOALLOC_MAX_CHANNELS = 512); use the two-call form with a caller buffer";
     if (code < 0) return cudaGetErrorString(static_cast<cudaError_t>(-code));
     return "b2c: unknown code";
 }
@@ -383,6 +386,22 @@ int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, fl
         return B2C_ERR_ARG;
     return cuda_rc(b2c::launch_bn_bwd_finalize(partial, partial_rows, channels, count, gamma, save_mean, save_rstd,
                                                dgamma, dbeta, coef_a, coef_b, coef_c, as_stream(stream)));
+}
+
+int b2c_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
+                             int channels, float count, const float* gamma, const float* save_mean,
+                             const float* save_rstd, float* dgamma, float* dbeta, float* coef_a, float* coef_b,
+                             float* coef_c, void* stream) {
+    static_assert(B2C_NOALLOC_MAX_CHANNELS == 512, "keep in step with kNoAllocMaxChannels (elementwise.cu)");
+    if (!dout || !y || !gamma || !save_mean || !save_rstd || !dgamma || !dbeta || !coef_a || !coef_b || !coef_c ||
+        rows < 1 || count <= 0.f)
+        return B2C_ERR_ARG;
+    if (channels > b2c::bn_bwd_noalloc_max_channels()) return B2C_ERR_TOO_LARGE;
+    if (channels < 8 || (channels & 7) || (256 % (channels >> 3)) != 0) return B2C_ERR_UNSUPPORTED;
+    if (!aligned16(dout) || !aligned16(act) || !aligned16(y) || !aligned16(dz_out)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_bn_bwd_stats_noalloc(dout, act, y, dz_out, rows, channels, count, gamma, save_mean,
+                                                    save_rstd, dgamma, dbeta, coef_a, coef_b, coef_c,
+                                                    as_stream(stream)));
 }
 
 int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,

@@ -47,5 +47,10 @@ cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s)
 cudaError_t launch_sgd(float* p, const float* g, float* buf, long long n, const float* hyper, cudaStream_t s);
 cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackEntry* table_dev, int entries,
                           cudaStream_t s);
+int bn_bwd_noalloc_max_channels();
+cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, void* dz_out,
+                                        long long rows, int C, float count, const float* gamma, const float* mean,
+                                        const float* rstd, float* dgamma, float* dbeta, float* coefA, float* coefB,
+                                        float* coefC, cudaStream_t s);
 
 }  // namespace b2c

@@ -667,4 +667,62 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------------------------------------
+// Allocation-free BatchNorm-backward statistics (b2c_bn_bwd_stats_noalloc in include/b2c.h).
+//
+// Same two kernels as launch_bn_bwd_reduce + launch_bn_bwd_finalize, but the partial-row scratch between
+// them is not a caller buffer: it is the fixed array below, which lives in every GPU that loads this
+// library (2.3 MiB each) for the life of the process. That serves callers that must not, or cannot, call
+// cudaMalloc around the launch: a host application whose device memory is entirely owned by another
+// allocator or a fixed budget, a real-time loop where cudaMalloc's implicit device synchronisation and
+// unbounded latency are not acceptable, or a plug-in that is only handed input / output pointers.
+//
+// kNoAllocMaxChannels bounds the channel count; rows are unbounded (the reduce kernel's grid is capped at
+// 592 blocks, one partial row each). Every element the finalize kernel reads is written by the reduce
+// kernel of the SAME call, so nothing in the array has to start at zero and stale contents from the
+// previous call are never observed. Two calls that overlap on the GPU (different streams, or graphs
+// replayed concurrently) share the array and race; callers serialise them.
+// ------------------------------------------------------------------------------------------------
+constexpr int kNoAllocMaxChannels = 512;
+constexpr int kNoAllocMaxRows = 148 * 4;
+static __device__ __align__(256) float g_noalloc_partial[kNoAllocMaxRows * 2 * kNoAllocMaxChannels];
+
+int bn_bwd_noalloc_max_channels() { return kNoAllocMaxChannels; }
+
+// In host code `g_noalloc_partial` is only a handle for the runtime, not a device address: the address is
+// looked up once per device, with that device current, and cached. The first call on a device performs
+// this look-up (it may initialise the module on that device), so it should happen before any stream
+// capture begins.
+static cudaError_t noalloc_scratch(float** out) {
+    constexpr int kMaxDevices = 64;
+    static float* cache[kMaxDevices] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+    float* p = __atomic_load_n(&cache[dev], __ATOMIC_ACQUIRE);
+    if (p == nullptr) {
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_partial);
+        if (e != cudaSuccess) return e;
+        if (p == nullptr) return cudaErrorInvalidSymbol;
+        __atomic_store_n(&cache[dev], p, __ATOMIC_RELEASE);   // same value from every thread: benign if repeated
+    }
+    *out = p;
+    return cudaSuccess;
+}
+
+cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, void* dz_out,
+                                        long long rows, int C, float count, const float* gamma, const float* mean,
+                                        const float* rstd, float* dgamma, float* dbeta, float* coefA, float* coefB,
+                                        float* coefC, cudaStream_t s) {
+    if (C > kNoAllocMaxChannels) return cudaErrorInvalidValue;   // api layer reports B2C_ERR_TOO_LARGE first
+    float* scratch = nullptr;
+    cudaError_t e = noalloc_scratch(&scratch);
+    if (e != cudaSuccess) return e;
+    const int prow = bn_bwd_partial_rows(rows, C);               // <= kNoAllocMaxRows by construction
+    e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, s);
+    if (e != cudaSuccess) return e;
+    return launch_bn_bwd_finalize(scratch, prow, C, count, gamma, mean, rstd, dgamma, dbeta, coefA, coefB, coefC, s);
+}
+
 }  // namespace b2c

@@ -111,6 +111,19 @@ def bn_bwd_finalize(partial, partial_rows, channels, count, gamma, save_mean, sa
           "b2c_bn_bwd_finalize")
 
 
+NOALLOC_MAX_CHANNELS = 512
+
+
+def bn_bwd_stats_noalloc(dout, act, y, dz_out, rows, channels, count, gamma, save_mean, save_rstd, dgamma, dbeta,
+                         ca, cb, cc):
+    """bn_bwd_reduce + bn_bwd_finalize without any scratch argument: for callers that cannot allocate device
+    memory around the call (see include/b2c.h). channels <= NOALLOC_MAX_CHANNELS; calls must not overlap."""
+    lib = _lib.load()
+    check(lib.b2c_bn_bwd_stats_noalloc(_p(dout), _p(act), _p(y), _p(dz_out), rows, channels, float(count), _p(gamma),
+                                       _p(save_mean), _p(save_rstd), _p(dgamma), _p(dbeta), _p(ca), _p(cb), _p(cc),
+                                       _stream()), "b2c_bn_bwd_stats_noalloc")
+
+
 def bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, channels):
     lib = _lib.load()
     check(lib.b2c_bn_bwd_apply(_p(dz), _p(y), _p(ca), _p(cb), _p(cc), _p(dy), rows, channels, _stream()),
