@@ -329,19 +329,38 @@ __global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const flo
     for (int i = 0; i < hw; ++i) d[static_cast<size_t>(i) * C] = b;
 }
 // Head backward, part 2: dW[k, c] = sum_n dlogits[n,k] * pooled[n,c]; db[k] = sum_n dlogits[n,k].
-__global__ void head_bwd_param_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, int N,
-                                      int K, int C, float* __restrict__ dW, float* __restrict__ db) {
+// grid = (C/32, K); block = 32 channels x 8 batch lanes, smem tree over the lanes.
+__global__ void __launch_bounds__(256)
+head_bwd_param_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, int N,
+                      int K, int C, float* __restrict__ dW, float* __restrict__ db) {
+    __shared__ float red[8][33];
     const int k = blockIdx.y;
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c < C) {
-        float s = 0.f;
-        for (int n = 0; n < N; ++n) s = fmaf(dlogits[static_cast<size_t>(n) * K + k], pooled[static_cast<size_t>(n) * C + c], s);
-        dW[static_cast<size_t>(k) * C + c] = s;
+    const int cl = threadIdx.x & 31, nl = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + cl;
+    float s = 0.f, sb = 0.f;
+    for (int n = nl; n < N; n += 8) {
+        const float d = __ldg(dlogits + static_cast<size_t>(n) * K + k);
+        if (c < C) s = fmaf(d, __ldg(pooled + static_cast<size_t>(n) * C + c), s);
+        sb += d;
     }
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        float s = 0.f;
-        for (int n = 0; n < N; ++n) s += dlogits[static_cast<size_t>(n) * K + k];
-        db[k] = s;
+    red[nl][cl] = s;
+    __syncthreads();
+    if (nl == 0 && c < C) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += red[i][cl];
+        dW[static_cast<size_t>(k) * C + c] = t;
+    }
+    if (blockIdx.x == 0) {
+        __syncthreads();
+        if (cl == 0) red[nl][32] = sb;     // every lane of a warp holds the same sb
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float t = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) t += red[i][32];
+            db[k] = t;
+        }
     }
 }
 
@@ -501,22 +520,41 @@ sgd_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restr
 __global__ void __launch_bounds__(256)
 repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, __nv_bfloat16* __restrict__ wd,
               const RepackEntry* __restrict__ table) {
+    // One block = a 32 (cout) x 32 (cin) tile of one conv, all taps: coalesced fp32 reads of the OIHW rows,
+    // transposes through shared memory, coalesced bf16 writes of both operand layouts.
+    __shared__ float tile[32][32 * 9 + 1];
     const RepackEntry e = table[blockIdx.y];
     const int taps = e.taps;
-    const long long total = static_cast<long long>(e.cout) * e.cin * taps;
-    const float* src = master + e.src_off;
-    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
-         i += static_cast<long long>(gridDim.x) * blockDim.x) {
-        // i enumerates OIHW: o, c, t
-        const int t = static_cast<int>(i % taps);
-        const int c = static_cast<int>((i / taps) % e.cin);
-        const int o = static_cast<int>(i / (static_cast<long long>(taps) * e.cin));
-        const __nv_bfloat16 b = __float2bfloat16(src[i]);
-        if (e.kflat) {
-            wf[e.wf_off + static_cast<long long>(o) * e.cin_pad + t * e.cin + c] = b;
-        } else {
-            wf[e.wf_off + (static_cast<long long>(t) * e.cout + o) * e.cin_pad + c] = b;
-            if (e.wd_off >= 0) wd[e.wd_off + (static_cast<long long>(t) * e.cin + c) * e.cout + o] = b;
+    if (e.kflat) {
+        // stem: [cout][cin*taps] fp32 -> [cout][cin_pad] bf16 with k = tap*cin + c
+        const int row = e.cin * taps;
+        for (int i = blockIdx.x * 256 + threadIdx.x; i < e.cout * row; i += gridDim.x * 256) {
+            const int o = i / row, r = i - o * row;
+            const int c = r / taps, t = r - c * taps;
+            wf[e.wf_off + static_cast<long long>(o) * e.cin_pad + t * e.cin + c] = __float2bfloat16(master[e.src_off + i]);
+        }
+        return;
+    }
+    const int ctiles = e.cin >> 5;
+    const int ntile = (e.cout >> 5) * ctiles;
+    for (int tidx = blockIdx.x; tidx < ntile; tidx += gridDim.x) {
+        const int o0 = (tidx / ctiles) << 5, c0 = (tidx % ctiles) << 5;
+        const int w = 32 * taps;                                  // contiguous floats per cout row of the tile
+        __syncthreads();
+        for (int i = threadIdx.x; i < 32 * w; i += 256) {
+            const int o = i / w, r = i - o * w;
+            tile[o][r] = master[e.src_off + (static_cast<long long>(o0 + o) * e.cin + c0) * taps + r];
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < taps * 32 * 32; i += 256) {
+            const int t = i >> 10, a = (i >> 5) & 31, b = i & 31;
+            // fprop operand [tap][cout][cin]: b runs over cin (contiguous)
+            wf[e.wf_off + (static_cast<long long>(t) * e.cout + o0 + a) * e.cin_pad + c0 + b] =
+                __float2bfloat16(tile[a][b * taps + t]);
+            // dgrad operand [tap][cin][cout]: b runs over cout (contiguous)
+            if (e.wd_off >= 0)
+                wd[e.wd_off + (static_cast<long long>(t) * e.cin + c0 + a) * e.cout + o0 + b] =
+                    __float2bfloat16(tile[b][a * taps + t]);
         }
     }
 }
@@ -618,8 +656,8 @@ cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const flo
     head_bwd_act_kernel<<<N, C, 0, s>>>(dlogits, W, K, hw, C, static_cast<__nv_bfloat16*>(dact));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    dim3 grid((C + 127) / 128, K);
-    head_bwd_param_kernel<<<grid, 128, 0, s>>>(dlogits, pooled, N, K, C, dW, db);
+    dim3 grid((C + 31) / 32, K);
+    head_bwd_param_kernel<<<grid, 256, 0, s>>>(dlogits, pooled, N, K, C, dW, db);
     return cudaGetLastError();
 }
 
@@ -661,7 +699,7 @@ cudaError_t launch_sgd(float* p, const float* g, float* buf, long long n, const 
 cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackEntry* table_dev, int entries,
                           cudaStream_t s) {
     if (entries == 0) return cudaSuccess;
-    dim3 grid(64, entries);
+    dim3 grid(128, entries);
     repack_kernel<<<grid, 256, 0, s>>>(master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd),
                                        table_dev);
     return cudaGetLastError();

@@ -65,6 +65,55 @@ def resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes
                 feat=in_planes)
 
 
+def param_offsets(spec):
+    """Element offsets of every parameter in the flat fp32 arenas (16-byte aligned), reference order."""
+    p_off, off = OrderedDict(), 0
+    for name, shape in spec["params"].items():
+        n = 1
+        for s in shape:
+            n *= s
+        p_off[name] = (off, n, shape)
+        off = _align(off + n, 4)
+    return p_off, _align(off, 4)
+
+
+def backward_groups(spec):
+    """Parameter-name groups in the order the backward plan completes them (head, blocks reversed, stem)."""
+    def key(name):
+        if name.startswith("layer"):
+            return ".".join(name.split(".")[:2])
+        return "head" if name.startswith("linear") else "stem"
+    groups = OrderedDict()
+    for name in spec["params"]:
+        groups.setdefault(key(name), []).append(name)
+    order = ["head"] + [k for k in reversed(list(groups)) if k not in ("head", "stem")] + ["stem"]
+    return [(k, groups[k]) for k in order]
+
+
+def plan_grad_buckets(spec, bucket_bytes):
+    """Cut the gradient arena into contiguous buckets in backward order, each closed once it holds at least
+    bucket_bytes (the DDP Reducer's rule, reducer.hpp:30-31, over a pre-flattened arena).
+    Returns (buckets, ready_after): buckets = [(start, end)] element ranges; ready_after maps the index of a
+    backward op (0 = head, 1.. = blocks in reverse, last = stem) to the bucket that is complete after it."""
+    p_off, _ = param_offsets(spec)
+    buckets, ready_after = [], {}
+    start = end = None
+    for pos, (key, names) in enumerate(backward_groups(spec)):
+        a = min(p_off[n][0] for n in names)
+        b = _align(max(p_off[n][0] + p_off[n][1] for n in names), 4)   # include the alignment padding
+        if end is None:
+            end = b
+        start = a
+        if (end - start) * 4 >= bucket_bytes:
+            ready_after[pos] = len(buckets)
+            buckets.append((start, end))
+            end = None
+    if end is not None:
+        ready_after[len(backward_groups(spec)) - 1] = len(buckets)
+        buckets.append((start, end))
+    return buckets, ready_after
+
+
 class ConvUnit:
     """One conv (+ the BatchNorm that follows it): descriptors, operand views, statistic buffers."""
 
@@ -149,14 +198,7 @@ class Engine:
     # ------------------------------------------------------------------ arenas
     def _layout_params(self, share_from=None):
         spec = self.spec
-        self.p_off, off = OrderedDict(), 0
-        for name, shape in spec["params"].items():
-            n = 1
-            for s in shape:
-                n *= s
-            self.p_off[name] = (off, n, shape)
-            off = _align(off + n, 4)
-        self.n_param = _align(off, 4)
+        self.p_off, self.n_param = param_offsets(spec)
         self.b_off, off = OrderedDict(), 0
         for name, shape in spec["buffers"].items():
             self.b_off[name] = (off, shape[0])

@@ -13,7 +13,7 @@ import torch
 
 from . import data as hostdata
 from . import ops
-from .engine import Engine
+from .engine import Engine, plan_grad_buckets
 
 
 class Trainer:
@@ -74,40 +74,7 @@ class Trainer:
 
     # ------------------------------------------------------------------ gradient buckets (DDP)
     def _plan_buckets(self):
-        """Contiguous ranges of the gradient arena, grouped in backward order (last layers first) up to
-        bucket_bytes each — the Reducer's bucketing (reducer.hpp:30-31) over a pre-flattened arena."""
-        eng = self.eng
-        names = list(eng.p_off.keys())
-        # group boundaries: parameters of one backward op are contiguous in the arena
-        groups, cur = [], None
-        for name in names:
-            key = name.split(".conv")[0].split(".bn")[0].split(".shortcut")[0] if name.startswith("layer") else (
-                "head" if name.startswith("linear") else "stem")
-            if cur is None or cur[0] != key:
-                cur = [key, eng.p_off[name][0], 0]
-                groups.append(cur)
-            off, n, _ = eng.p_off[name]
-            cur[2] = off + n
-        ranges = [(g[1], g[2]) for g in groups]          # forward order
-        buckets, end, start = [], None, None
-        for a, b in reversed(ranges):                     # backward order
-            if end is None:
-                end, start = b, a
-            else:
-                start = a
-            if (end - start) * 4 >= self.bucket_bytes:
-                buckets.append((start, end))
-                end = None
-        if end is not None:
-            buckets.append((start, end))
-        # map: after backward op i (head, blocks reversed, stem) which bucket (if any) is complete
-        order = ["head"] + [g[0] for g in reversed(groups) if g[0] not in ("head", "stem")] + ["stem"]
-        first_off = {g[0]: g[1] for g in groups}
-        ready = {}
-        for bi, (a, b) in enumerate(buckets):
-            for pos, key in enumerate(order):
-                if first_off[key] == a:
-                    ready[pos] = bi
+        buckets, ready = plan_grad_buckets(self.eng.spec, self.bucket_bytes)
         self._bucket_ready_after = ready
         return buckets
 
