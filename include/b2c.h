@@ -49,6 +49,7 @@ typedef struct B2cConvDesc {
     int kflat_cin;   /* wgrad only: >0 for the im2col'ed stem, whose `cin` axis is k = tap*kflat_cin + c */
     int block_n;     /* GEMM N tile (64/128/256); 0 = choose */
     int max_ctas;    /* persistent grid cap; 0 = 148 (one CTA per SM) */
+    int flags;       /* bit 0: force the per-tap kernel (conv_gemm.cu) where the halo kernel would be chosen */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)

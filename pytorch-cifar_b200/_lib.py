@@ -27,7 +27,8 @@ class B2cError(RuntimeError):
 class ConvDesc(ctypes.Structure):
     """Mirror of B2cConvDesc (include/b2c.h)."""
     _fields_ = [(n, ctypes.c_int) for n in
-                ("n", "h", "w", "cin", "cout", "ksize", "stride", "cin_valid", "kflat_cin", "block_n", "max_ctas")]
+                ("n", "h", "w", "cin", "cout", "ksize", "stride", "cin_valid", "kflat_cin", "block_n", "max_ctas",
+                 "flags")]
 
 
 class RepackEntry(ctypes.Structure):

@@ -79,6 +79,43 @@ bool grid_tiles(int gH, int gW, int px) {
     return (img % px) == 0 || (px % img) == 0;
 }
 
+// 3x3 stride-1 convs on square 32 / 16 / 8 pixel images go to the halo-reuse kernel (conv_halo.cu).
+bool use_halo(const B2cConvDesc* d) {
+    if (d->flags & 1) return false;
+    if (d->ksize != 3 || d->stride != 1 || d->h != d->w) return false;
+    return d->w == 32 || d->w == 16 || d->w == 8;
+}
+
+int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w, int gemm_n, int bn, bool flip,
+                void* out, const void* add_src, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t st) {
+    b2c::HaloParams p = {};
+    p.N = d->n;
+    p.H = d->h;
+    p.W = d->w;
+    p.mode = d->w == 8 ? 1 : 0;
+    p.tiles_h = d->h / 16;
+    p.tiles_w = d->w / 8;
+    p.num_m_tiles = p.mode == 0 ? d->n * p.tiles_h * p.tiles_w : (d->n + 1) / 2;
+    p.num_n_tiles = gemm_n / bn;
+    p.k_chunks = act_c / 64;
+    p.flip = flip ? 1 : 0;
+    p.b_rows_per_tap = gemm_n;
+    p.out = static_cast<__nv_bfloat16*>(out);
+    p.add_src = static_cast<const __nv_bfloat16*>(add_src);
+    p.out_ld = gemm_n;
+    p.part_sum = part_sum;
+    p.part_sq = part_sq;
+    p.cout = gemm_n;
+    CUtensorMap ma, mb;
+    int rc = p.mode == 0 ? encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 18, 1, 1)
+                         : encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 8, 2, 1);
+    if (rc) return rc;
+    rc = encode_2d(&mb, w, 9LL * gemm_n, act_c, bn);
+    if (rc) return rc;
+    const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+    return cuda_rc(b2c::launch_conv_halo(bn, ma, mb, p, max_ctas, stat_rows, st));
+}
+
 int pick_bn(int requested, int n_dim) {
     if (requested != 0) return requested;
     if (n_dim % 128 == 0) return 128;
@@ -125,6 +162,9 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     const int bn = pick_bn(d->block_n, d->cout);
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
     const int taps = d->ksize * d->ksize;
+    if (use_halo(d))
+        return launch_halo(d, x, d->cin, w_fprop, d->cout, bn, false, y, nullptr, part_sum, part_sq, stat_rows,
+                           as_stream(stream));
 
     TapGemmParams p = {};
     p.m_total = d->n * ho * wo;
@@ -177,6 +217,8 @@ int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, vo
     const int taps = d->ksize * d->ksize;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
     cudaStream_t st = as_stream(stream);
+    if (use_halo(d))
+        return launch_halo(d, dy, d->cout, w_dgrad, d->cin, bn, true, dx, add_src, nullptr, nullptr, nullptr, st);
 
     TapGemmParams p = {};
     p.num_n_tiles = d->cin / bn;

@@ -56,6 +56,25 @@ struct WgradParams {
     long long o_stride, c_stride, t_stride;
 };
 
+// 3x3 stride-1 conv (fprop / dgrad) with activation-halo reuse, see conv_halo.cu.
+struct HaloParams {
+    int N, H, W;          // images, height, width (input dims == output dims)
+    int num_m_tiles, num_n_tiles, k_chunks;
+    int mode;             // 0: 16x8 tile of one image (W >= 16); 1: two whole 8x8 images (W == 8)
+    int tiles_h, tiles_w; // mode 0: tiles per image
+    int flip;             // dgrad: window position (a, b) uses weight tap (2-a, 2-b)
+    int b_rows_per_tap;   // rows of the weight matrix per tap (= GEMM N total)
+    int b_resident;       // set by the launcher: all weight slabs fit the ring and are loaded once per CTA
+    __nv_bfloat16* out;
+    const __nv_bfloat16* add_src;
+    int out_ld;
+    float* part_sum;
+    float* part_sq;
+    int cout;
+};
+
+cudaError_t launch_conv_halo(int bn, const CUtensorMap& a, const CUtensorMap& b, const HaloParams& p, int max_ctas,
+                             int* stat_rows, cudaStream_t stream);
 cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                             const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream);
 cudaError_t launch_wgrad(int bn, const CUtensorMap& x, const CUtensorMap& dy, const WgradParams& p,

@@ -30,8 +30,8 @@ def _need(t, dtype, name):
                          f"contig={t.is_contiguous()}")
 
 
-def conv_desc(n, h, w, cin, cout, ksize, stride, cin_valid=0, kflat_cin=0, block_n=0, max_ctas=0):
-    return ConvDesc(n, h, w, cin, cout, ksize, stride, cin_valid, kflat_cin, block_n, max_ctas)
+def conv_desc(n, h, w, cin, cout, ksize, stride, cin_valid=0, kflat_cin=0, block_n=0, max_ctas=0, flags=0):
+    return ConvDesc(n, h, w, cin, cout, ksize, stride, cin_valid, kflat_cin, block_n, max_ctas, flags)
 
 
 def pack_weight_fprop(w_oihw):

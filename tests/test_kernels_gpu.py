@@ -83,6 +83,24 @@ def test_conv_fprop(ops, shape):
     assert rel_err(s2, (ref * ref).sum((0, 2, 3))) < F32_TOL
 
 
+@pytest.mark.parametrize("shape", [s for s in CONV_SHAPES if s[5] == 3 and s[6] == 1 and s[1] in (8, 16, 32)])
+def test_conv_per_tap_kernel_still_covered(ops, shape):
+    """flags=1 forces the per-tap kernel on shapes that normally take the halo-reuse kernel."""
+    n, h, w, cin, cout, k, stride = shape
+    x = nhwc_bf16(n, h, w, cin, 41)
+    wt = weight(cout, cin, k, 42)
+    y = torch.empty(n, h, w, cout, device="cuda", dtype=torch.bfloat16)
+    d = ops.conv_desc(n, h, w, cin, cout, k, stride, flags=1)
+    ops.conv_fprop(d, x, ops.pack_weight_fprop(wt), y)
+    dy = nhwc_bf16(n, h, w, cout, 43)
+    dx = torch.empty(n, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    ops.conv_dgrad(d, dy, ops.pack_weight_dgrad(wt), dx)
+    torch.cuda.synchronize()
+    assert rel_err(to_nchw(y), F.conv2d(to_nchw(x), wt, padding=1)) < BF16_TOL
+    ref = torch.nn.grad.conv2d_input((n, cin, h, w), wt, to_nchw(dy), padding=1)
+    assert rel_err(to_nchw(dx), ref) < BF16_TOL
+
+
 @pytest.mark.parametrize("bn", [64, 128, 256])
 def test_conv_fprop_block_n(ops, bn):
     n, h, w, cin, cout, k, stride = 8, 16, 16, 128, 256, 3, 1
