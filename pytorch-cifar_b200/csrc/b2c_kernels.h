@@ -65,6 +65,7 @@ struct HaloParams {
     int flip;             // dgrad: window position (a, b) uses weight tap (2-a, 2-b)
     int b_rows_per_tap;   // rows of the weight matrix per tap (= GEMM N total)
     int b_resident;       // set by the launcher: all weight slabs fit the ring and are loaded once per CTA
+    int debug;            // measurement switches (tools/ only): 2 no stores, 4 no stats, 8 no MMA issue, 16 no TMEM read
     __nv_bfloat16* out;
     const __nv_bfloat16* add_src;
     int out_ld;

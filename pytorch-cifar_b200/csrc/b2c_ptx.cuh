@@ -21,6 +21,20 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One lane of the (fully active, converged) warp gets `true`. Issue tcgen05.mma / TMA / commit under this
+// predicate with the WHOLE warp running the surrounding loop: ptxas then emits the uniform-datapath
+// instruction directly. Guarding with `lane == 0` instead makes the code divergent and every UTCHMMA /
+// UTMALDG gets wrapped in an ELECT/branch loop (~70-90 cycles per issue, measured: tools/tma_bw_probe.cu).
+__device__ __forceinline__ bool elect_one_sync() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+        "elect.sync rx|px, 0xffffffff;\n\t"
+        "selp.b32 %0, 1, 0, px;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
 // ---------------------------------- mbarrier ---------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

@@ -15,8 +15,8 @@
 //   epilogue       tcgen05.ld -> optional residual add -> bf16 NHWC store, plus per-tile per-channel
 //                  sum / sum-of-squares (fp32, taken before rounding) for the following BatchNorm.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
-// warps 2..5 = epilogue (one TMEM lane quarter each).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..9 = epilogue (one TMEM lane quarter each).
 #include "b2c_kernels.h"
 #include "b2c_ptx.cuh"
 
@@ -39,7 +39,7 @@ struct TapCfg {
 };
 
 template <int BN, bool kStats>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(320, 1)
 tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
                 const __grid_constant__ CUtensorMap mapB, const __grid_constant__ TapGemmParams p) {
     using Cfg = TapCfg<BN>;
@@ -69,8 +69,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
             }
             mbar_init(&tfull[0], 1);
             mbar_init(&tfull[1], 1);
-            mbar_init(&tempty[0], 4);
-            mbar_init(&tempty[1], 4);
+            mbar_init(&tempty[0], 8);
+            mbar_init(&tempty[1], 8);
             fence_mbar_init();
         }
         __syncwarp();
@@ -86,8 +86,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
     const int img = p.gH * p.gW;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------ TMA producer ------------------------------
+        {
+            // ------------------------------ TMA producer (whole warp loops, one elected lane issues) ----
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -103,10 +103,13 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                     const int brow = p.tap_brow[t] + n_tile * BN;
                     for (int kc = 0; kc < p.k_chunks; ++kc) {
                         mbar_wait(&empty[stage], phase ^ 1u, 1);
-                        mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
-                        uint8_t* sa = smem + stage * Cfg::kStageBytes;
-                        tma_load_4d(sa, ma, &full[stage], kc * 64, cw, ch, n0);
-                        tma_load_2d(sa + kABytes, &mapB, &full[stage], kc * 64, brow);
+                        if (elect_one_sync()) {
+                            mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+                            uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                            tma_load_4d(sa, ma, &full[stage], kc * 64, cw, ch, n0);
+                            tma_load_2d(sa + kABytes, &mapB, &full[stage], kc * 64, brow);
+                        }
+                        __syncwarp();
                         if (++stage == Cfg::kStages) {
                             stage = 0;
                             phase ^= 1u;
@@ -116,8 +119,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ------------------------------ MMA issuer --------------------------------
+        {
+            // ------------------------------ MMA issuer (whole warp loops, one elected lane issues) ------
             constexpr uint32_t idesc = make_idesc_bf16(kBM, BN, 0, 0);
             int stage = 0;
             uint32_t phase = 0;
@@ -130,21 +133,25 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                 for (int it = 0; it < k_iters; ++it) {
                     mbar_wait(&full[stage], phase, 3);
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-                    const uint64_t ad = make_smem_desc_sw128(sa, 16, 1024);
-                    const uint64_t bd = make_smem_desc_sw128(sa + kABytes, 16, 1024);
+                    if (elect_one_sync()) {
+                        const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+                        const uint64_t ad = make_smem_desc_sw128(sa, 16, 1024);
+                        const uint64_t bd = make_smem_desc_sw128(sa + kABytes, 16, 1024);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        // advance 16 bf16 = 32 B along K inside the 128 B swizzle span
-                        umma_bf16(d, ad + 2u * k, bd + 2u * k, idesc, (it | k) != 0 ? 1u : 0u);
+                        for (int k = 0; k < 4; ++k) {
+                            // advance 16 bf16 = 32 B along K inside the 128 B swizzle span
+                            umma_bf16(d, ad + 2u * k, bd + 2u * k, idesc, (it | k) != 0 ? 1u : 0u);
+                        }
+                        umma_commit(&empty[stage]);
                     }
-                    umma_commit(&empty[stage]);
+                    __syncwarp();
                     if (++stage == Cfg::kStages) {
                         stage = 0;
                         phase ^= 1u;
                     }
                 }
-                umma_commit(&tfull[acc]);
+                if (elect_one_sync()) umma_commit(&tfull[acc]);
+                __syncwarp();
                 if (++acc == 2) {
                     acc = 0;
                     acc_phase ^= 1u;
@@ -155,10 +162,11 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
         // ---------------------------------- epilogue --------------------------------------
         const int q = warp & 3;  // TMEM lane quarter this warp may read
         const int row = q * 32 + lane;
+        const int half = (warp - 2) >> 2;   // two warps per TMEM lane quarter, alternating 32-column chunks
         const int et = threadIdx.x - 64;  // 0..127
         if (kStats) {
             // each (quarter, column) slot is owned by exactly one thread: no sync needed to clear it
-            for (int c = lane; c < BN; c += 32) {
+            for (int c = lane + 32 * half; c < BN; c += 64) {   // the chunks this warp owns
                 stat[(0 * 4 + q) * BN + c] = 0.f;
                 stat[(1 * 4 + q) * BN + c] = 0.f;
             }
@@ -181,7 +189,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                 static_cast<size_t>(n_tile) * BN;
             float* st = stat;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = half; c < BN / 32; c += 2) {
                 float v[32];
                 tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                                   static_cast<uint32_t>(acc * BN + c * 32),
@@ -235,10 +243,10 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
         if (kStats) {
             // gridDim.x is a multiple of num_n_tiles (see launch_one), so every tile of this CTA had
             // the same n_tile: one partial row per CTA, P = gridDim.x / num_n_tiles rows in all.
-            named_bar_sync(1, 128);
+            named_bar_sync(1, 256);
             const int n_tile = blockIdx.x % p.num_n_tiles;
             const int prow = blockIdx.x / p.num_n_tiles;
-            for (int col = et; col < BN; col += 128) {
+            for (int col = et; col < BN; col += 256) {
                 const float s1 = stat[(0 * 4 + 0) * BN + col] + stat[(0 * 4 + 1) * BN + col] +
                                  stat[(0 * 4 + 2) * BN + col] + stat[(0 * 4 + 3) * BN + col];
                 const float s2 = stat[(1 * 4 + 0) * BN + col] + stat[(1 * 4 + 1) * BN + col] +
@@ -272,7 +280,7 @@ cudaError_t launch_one(const CUtensorMap& a0, const CUtensorMap& a1, const CUten
     grid -= grid % p.num_n_tiles;  // keeps n_tile constant per CTA (per-CTA BatchNorm partial rows)
     if (grid < p.num_n_tiles) grid = p.num_n_tiles;
     if (stat_rows != nullptr) *stat_rows = grid / p.num_n_tiles;
-    kern<<<grid, 192, Cfg::kSmemBytes, stream>>>(a0, a1, b, p);
+    kern<<<grid, 320, Cfg::kSmemBytes, stream>>>(a0, a1, b, p);
     return cudaGetLastError();
 }
 

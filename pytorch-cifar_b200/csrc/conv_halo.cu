@@ -1,22 +1,24 @@
 // conv_halo.cu — 3x3 stride-1 convolution forward / data-gradient with activation-halo reuse.
 //
 // Same GEMM view, operands and epilogue as conv_gemm.cu (reference sites: models/resnet.py:23-27 and the
-// autograd dgrad of main.py:104), but built around the measured limiter of that kernel: bytes staged from
-// L2 into shared memory per MMA (profiles/r1_ncu_tap_gemm_full.txt — 45 B/clk/SM, the L2->SM ceiling, with
-// the tensor pipe 45 % active). Here the activation tile of a 64-channel chunk is loaded ONCE with its halo
-// and the taps are issued as row-shifted shared-memory descriptors over it; tcgen05 applies the 128-byte
-// swizzle to the absolute smem address, so a descriptor may start at any 128 B row and step between 8-row
-// groups by any SBO (verified on hardware: profiles/r1_umma_probe.log, P1).
+// autograd dgrad of main.py:104). Two measured limiters of that kernel shape this one:
+//   * bytes staged from L2 into shared memory per MMA (profiles/r1_ncu_tap_gemm_full.txt: ~45 B/clk/SM, the
+//     L2->SM ceiling, tensor pipe 45 % active). Here the activation tile of a 64-channel chunk is loaded ONCE
+//     with its halo and the 9 taps are issued as row-shifted shared-memory descriptors over it; tcgen05
+//     applies the 128-byte swizzle to the absolute smem address, so a descriptor may start at any 128 B row
+//     and step between 8-row groups by any SBO (verified on hardware: profiles/r1_umma_probe.log, P1).
+//   * the single warp that issues tcgen05.mma is bound by its own instruction latency (~5 cycles per dependent
+//     instruction): every instruction in the per-tap loop costs tensor time. The issue loops are therefore
+//     compile-time unrolled (mode / residency are template parameters), use one elected region per
+//     activation stage (36 or 12 MMAs), and ring positions come from uniform counters and power-of-two rings.
 //
-//   mode 0 (W >= 16): tile = 16 rows x 8 cols of one image; halo box {64 ch, 10, 18, 1}; tap (a, b) of the
+//   MODE 0 (W >= 16): tile = 16 rows x 8 cols of one image; halo box {64 ch, 10, 18, 1}; tap (a, b) of the
 //                     3x3 window starts at row a*10 + b of the tile; 8-row groups are 10 rows apart (SBO 1280).
-//   mode 1 (W == 8) : tile = two whole 8x8 images; three boxes {64 ch, 10, 8, 2}, one per window row a,
+//   MODE 1 (W == 8) : tile = two whole 8x8 images; three boxes {64 ch, 10, 8, 2}, one per window row a,
 //                     loaded at image row a-1; tap b starts at row b.
-// Activation bytes staged per output tile and chunk: 23 KB (mode 0) or 60 KB (mode 1) instead of 144 KB.
-// Weight tiles stream through their own ring; when all of them fit (cin = cout = 64: 72 KB) they are
-// loaded once per CTA and stay resident.
+//   RES             : cin = cout = 64 — all nine 8 KB weight slabs are loaded once per CTA and stay resident.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 = epilogue.
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..9 = epilogue.
 #include "b2c_kernels.h"
 #include "b2c_ptx.cuh"
 
@@ -25,31 +27,40 @@ namespace b2c {
 namespace {
 
 constexpr int kAStageBytes = 23552;  // 180 rows x 128 B rounded up to 1024
+constexpr int kBRingBytes = 128 * 1024;
 
 template <int BN>
 struct HaloCfg {
     static constexpr int kBBytes = BN * 128;
-    static constexpr int kSA = BN == 64 ? 4 : 3;
-    static constexpr int kSB = BN == 64 ? 9 : (BN == 128 ? 8 : 4);
+    static constexpr int kSA = BN == 256 ? 2 : 4;      // activation stages (power of two)
+    static constexpr int kSB = kBRingBytes / kBBytes;  // 16 / 8 / 4: power of two
     static constexpr int kTmemCols = 2 * BN;
     static constexpr int kBarBytes = 512;
     static constexpr int kStatBytes = 2 * 4 * BN * 4;
-    static constexpr int kSmemBytes = 1024 + kSA * kAStageBytes + kSB * kBBytes + kBarBytes + kStatBytes;
+    static constexpr int kSmemBytes = 1024 + kSA * kAStageBytes + kBRingBytes + kBarBytes + kStatBytes;
 };
 
-template <int BN, bool kStats>
-__global__ void __launch_bounds__(192, 1)
+template <int BN, bool kStats, int MODE, bool RES>
+__global__ void __launch_bounds__(320, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
                  const __grid_constant__ HaloParams p) {
     using Cfg = HaloCfg<BN>;
+    constexpr int kSA = Cfg::kSA;
+    constexpr int LOADS = MODE == 0 ? 1 : 3;   // activation boxes per 64-channel chunk
+    constexpr int TPL = 9 / LOADS;             // taps served by one box
+    constexpr uint32_t kABytes = MODE == 0 ? 180u * 128u : 160u * 128u;
+    constexpr uint32_t kSBmask = Cfg::kSB - 1;
+    static_assert((Cfg::kSB & (Cfg::kSB - 1)) == 0 && (kSA & (kSA - 1)) == 0, "rings are powers of two");
+    static_assert(!RES || Cfg::kSB >= 9, "resident weights need nine slots");
+
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* sA = smem;
-    uint8_t* sB = smem + Cfg::kSA * kAStageBytes;
-    uint8_t* aux = sB + Cfg::kSB * Cfg::kBBytes;
+    uint8_t* sB = smem + kSA * kAStageBytes;
+    uint8_t* aux = sB + kBRingBytes;
     uint64_t* full_a = reinterpret_cast<uint64_t*>(aux);
-    uint64_t* empty_a = full_a + Cfg::kSA;
-    uint64_t* full_b = empty_a + Cfg::kSA;
+    uint64_t* empty_a = full_a + kSA;
+    uint64_t* full_b = empty_a + kSA;
     uint64_t* empty_b = full_b + Cfg::kSB;
     uint64_t* tfull = empty_b + Cfg::kSB;
     uint64_t* tempty = tfull + 2;
@@ -65,7 +76,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     }
     if (warp == 1) {
         if (lane == 0) {
-            for (int s = 0; s < Cfg::kSA; ++s) {
+            for (int s = 0; s < kSA; ++s) {
                 mbar_init(&full_a[s], 1);
                 mbar_init(&empty_a[s], 1);
             }
@@ -75,8 +86,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
             mbar_init(&tfull[0], 1);
             mbar_init(&tfull[1], 1);
-            mbar_init(&tempty[0], 4);
-            mbar_init(&tempty[1], 4);
+            mbar_init(&tempty[0], 8);
+            mbar_init(&tempty[1], 8);
             fence_mbar_init();
         }
         __syncwarp();
@@ -88,130 +99,120 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     const uint32_t tmem_base = *tmem_ptr;
 
     const int total_tiles = p.num_m_tiles * p.num_n_tiles;
-    const int loads = p.mode == 0 ? 1 : 3;          // A boxes per chunk
-    const int taps_per_load = 9 / loads;
-    const uint32_t a_bytes = p.mode == 0 ? 180u * 128u : 160u * 128u;
-    const bool resident = p.b_resident != 0;
+    const int per_img = p.tiles_h * p.tiles_w;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------ TMA producer ------------------------------
-            int sa = 0, sb = 0;
-            uint32_t pa = 0, pb = 0;
-            bool first = true;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int m_tile = tile / p.num_n_tiles;
-                const int n_tile = tile - m_tile * p.num_n_tiles;
-                int n0, h0, w0;
-                if (p.mode == 0) {
-                    const int per_img = p.tiles_h * p.tiles_w;
-                    n0 = m_tile / per_img;
-                    const int rem = m_tile - n0 * per_img;
-                    const int th = rem / p.tiles_w;
-                    h0 = th * 16;
-                    w0 = (rem - th * p.tiles_w) * 8;
-                } else {
-                    n0 = m_tile * 2;
-                    h0 = 0;
-                    w0 = 0;
-                }
-                for (int kc = 0; kc < p.k_chunks; ++kc) {
-                    for (int l = 0; l < loads; ++l) {
-                        mbar_wait(&empty_a[sa], pa ^ 1u, 21);
-                        mbar_arrive_expect_tx(&full_a[sa], a_bytes);
+        // ------------------------------ TMA producer (whole warp loops, one elected lane issues) ----------
+        uint32_t a_cnt = 0, b_cnt = 0;   // stages / weight tiles issued so far (uniform across the warp)
+        bool first = true;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int m_tile = tile / p.num_n_tiles;
+            const int n_tile = tile - m_tile * p.num_n_tiles;
+            int n0, h0 = 0, w0 = 0;
+            if (MODE == 0) {
+                n0 = m_tile / per_img;
+                const int rem = m_tile - n0 * per_img;
+                const int th = rem / p.tiles_w;
+                h0 = th * 16;
+                w0 = (rem - th * p.tiles_w) * 8;
+            } else {
+                n0 = m_tile * 2;
+            }
+            const int brow0 = n_tile * BN;
+            for (int kc = 0; kc < p.k_chunks; ++kc) {
+#pragma unroll
+                for (int l = 0; l < LOADS; ++l) {
+                    const uint32_t sa = a_cnt & (kSA - 1);
+                    mbar_wait(&empty_a[sa], ((a_cnt / kSA) & 1u) ^ 1u, 21);
+                    if (elect_one_sync()) {
+                        mbar_arrive_expect_tx(&full_a[sa], kABytes);
                         tma_load_4d(sA + sa * kAStageBytes, &mapA, &full_a[sa], kc * 64, w0 - 1,
-                                    p.mode == 0 ? h0 - 1 : l - 1, n0);
-                        if (++sa == Cfg::kSA) {
-                            sa = 0;
-                            pa ^= 1u;
-                        }
-                        if (!resident || first) {
-                            for (int j = 0; j < taps_per_load; ++j) {
-                                const int a = p.mode == 0 ? j / 3 : l;
-                                const int b = p.mode == 0 ? j - a * 3 : j;
+                                    MODE == 0 ? h0 - 1 : l - 1, n0);
+                        if (!RES || first) {
+#pragma unroll
+                            for (int j = 0; j < TPL; ++j) {
+                                const int a = MODE == 0 ? j / 3 : l;
+                                const int b = MODE == 0 ? j % 3 : j;
                                 const int r = p.flip ? 2 - a : a;
                                 const int s = p.flip ? 2 - b : b;
-                                if (!resident) mbar_wait(&empty_b[sb], pb ^ 1u, 22);
-                                mbar_arrive_expect_tx(&full_b[sb], Cfg::kBBytes);
-                                tma_load_2d(sB + sb * Cfg::kBBytes, &mapB, &full_b[sb], kc * 64,
-                                            (r * 3 + s) * p.b_rows_per_tap + n_tile * BN);
-                                if (++sb == Cfg::kSB) {
-                                    sb = 0;
-                                    pb ^= 1u;
-                                }
+                                const uint32_t bi = RES ? static_cast<uint32_t>(l * TPL + j) : ((b_cnt + j) & kSBmask);
+                                if (!RES) mbar_wait(&empty_b[bi], (((b_cnt + j) / Cfg::kSB) & 1u) ^ 1u, 22);
+                                mbar_arrive_expect_tx(&full_b[bi], Cfg::kBBytes);
+                                tma_load_2d(sB + bi * Cfg::kBBytes, &mapB, &full_b[bi], kc * 64,
+                                            (r * 3 + s) * p.b_rows_per_tap + brow0);
                             }
                         }
                     }
+                    __syncwarp();
+                    ++a_cnt;
+                    b_cnt += TPL;
                 }
-                first = false;
             }
+            first = false;
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ------------------------------ MMA issuer --------------------------------
-            constexpr uint32_t idesc = make_idesc_bf16(128, BN, 0, 0);
-            int sa = 0, sb = 0;
-            uint32_t pa = 0, pb = 0;
-            int acc = 0;
-            uint32_t acc_phase = 0;
-            bool first = true;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                mbar_wait(&tempty[acc], acc_phase ^ 1u, 23);
-                tc_fence_after();
-                const uint32_t d = tmem_base + static_cast<uint32_t>(acc * BN);
-                uint32_t accum = 0;
-                for (int kc = 0; kc < p.k_chunks; ++kc) {
-                    for (int l = 0; l < loads; ++l) {
-                        mbar_wait(&full_a[sa], pa, 24);
-                        tc_fence_after();
-                        const uint32_t a_base = smem_u32(sA + sa * kAStageBytes);
-                        for (int j = 0; j < taps_per_load; ++j) {
-                            const int a = p.mode == 0 ? j / 3 : 0;
-                            const int b = p.mode == 0 ? j - a * 3 : j;
-                            if (!resident || first) {
-                                mbar_wait(&full_b[sb], pb, 25);
+        // ------------------------------ MMA issuer (whole warp loops, one elected lane issues) ------------
+        constexpr uint32_t idesc = make_idesc_bf16(128, BN, 0, 0);
+        uint32_t a_cnt = 0, b_cnt = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        bool first = true;
+        const uint32_t sB_u32 = smem_u32(sB);
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            mbar_wait(&tempty[acc], acc_phase ^ 1u, 23);
+            tc_fence_after();
+            const uint32_t d = tmem_base + static_cast<uint32_t>(acc * BN);
+            for (int kc = 0; kc < p.k_chunks; ++kc) {
+#pragma unroll
+                for (int l = 0; l < LOADS; ++l) {
+                    const uint32_t sa = a_cnt & (kSA - 1);
+                    mbar_wait(&full_a[sa], (a_cnt / kSA) & 1u, 24);
+                    tc_fence_after();
+                    if (elect_one_sync()) {
+                        const uint64_t ad0 = make_smem_desc_sw128(smem_u32(sA + sa * kAStageBytes), 16, 1280);
+#pragma unroll
+                        for (int j = 0; j < TPL; ++j) {
+                            const int off_rows = MODE == 0 ? (j / 3) * 10 + (j % 3) : j;
+                            const uint32_t bi = RES ? static_cast<uint32_t>(l * TPL + j) : ((b_cnt + j) & kSBmask);
+                            if (!RES) {
+                                mbar_wait(&full_b[bi], ((b_cnt + j) / Cfg::kSB) & 1u, 25);
+                                tc_fence_after();
+                            } else if (first) {
+                                mbar_wait(&full_b[bi], 0, 25);
                                 tc_fence_after();
                             }
-                            const uint64_t ad = make_smem_desc_sw128(a_base + (a * 10 + b) * 128, 16, 1280);
-                            const uint64_t bd = make_smem_desc_sw128(smem_u32(sB + sb * Cfg::kBBytes), 16, 1024);
+                            const uint64_t ad = ad0 + static_cast<uint64_t>(off_rows * 8);   // 128 B rows, >> 4
+                            const uint64_t bd = make_smem_desc_sw128(sB_u32 + bi * Cfg::kBBytes, 16, 1024);
 #pragma unroll
                             for (int k = 0; k < 4; ++k) {
-                                umma_bf16(d, ad + 2u * k, bd + 2u * k, idesc, accum);
-                                accum = 1;
+                                umma_bf16(d, ad + 2u * k, bd + 2u * k, idesc, (kc | l | j | k) != 0 ? 1u : 0u);
                             }
-                            if (!resident) umma_commit(&empty_b[sb]);
-                            if (++sb == Cfg::kSB) {
-                                sb = 0;
-                                pb ^= 1u;
-                            }
+                            if (!RES) umma_commit(&empty_b[bi]);
                         }
                         umma_commit(&empty_a[sa]);
-                        if (++sa == Cfg::kSA) {
-                            sa = 0;
-                            pa ^= 1u;
-                        }
                     }
+                    __syncwarp();
+                    ++a_cnt;
+                    b_cnt += TPL;
                 }
-                if (resident) {  // the ring never advances past the resident slabs
-                    sb = 0;
-                    pb = 0;
-                }
-                umma_commit(&tfull[acc]);
-                if (++acc == 2) {
-                    acc = 0;
-                    acc_phase ^= 1u;
-                }
-                first = false;
             }
+            if (elect_one_sync()) umma_commit(&tfull[acc]);
+            __syncwarp();
+            if (++acc == 2) {
+                acc = 0;
+                acc_phase ^= 1u;
+            }
+            first = false;
         }
     } else {
         // ---------------------------------- epilogue --------------------------------------
         const int q = warp & 3;
         const int row = q * 32 + lane;
         const int g = row >> 3, j = row & 7;
+        const int half = (warp - 2) >> 2;   // two warps per TMEM lane quarter, alternating 32-column chunks
         const int et = threadIdx.x - 64;
         if (kStats) {
-            for (int c = lane; c < BN; c += 32) {
+            for (int c = lane + 32 * half; c < BN; c += 64) {   // the chunks this warp owns
                 stat[(0 * 4 + q) * BN + c] = 0.f;
                 stat[(1 * 4 + q) * BN + c] = 0.f;
             }
@@ -222,8 +223,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             const int m_tile = tile / p.num_n_tiles;
             const int n_tile = tile - m_tile * p.num_n_tiles;
             int n, h, w;
-            if (p.mode == 0) {
-                const int per_img = p.tiles_h * p.tiles_w;
+            if (MODE == 0) {
                 n = m_tile / per_img;
                 const int rem = m_tile - n * per_img;
                 const int th = rem / p.tiles_w;
@@ -239,7 +239,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             mbar_wait(&tfull[acc], acc_phase, 26);
             tc_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = half; c < BN / 32; c += 2) {
                 float v[32];
                 tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                                   static_cast<uint32_t>(acc * BN + c * 32),
@@ -291,10 +291,10 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
             }
         }
         if (kStats) {
-            named_bar_sync(1, 128);
+            named_bar_sync(1, 256);
             const int n_tile = blockIdx.x % p.num_n_tiles;
             const int prow = blockIdx.x / p.num_n_tiles;
-            for (int col = et; col < BN; col += 128) {
+            for (int col = et; col < BN; col += 256) {
                 const float s1 = stat[(0 * 4 + 0) * BN + col] + stat[(0 * 4 + 1) * BN + col] +
                                  stat[(0 * 4 + 2) * BN + col] + stat[(0 * 4 + 3) * BN + col];
                 const float s2 = stat[(1 * 4 + 0) * BN + col] + stat[(1 * 4 + 1) * BN + col] +
@@ -312,25 +312,40 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 
-template <int BN, bool kStats>
-cudaError_t launch_one(const CUtensorMap& a, const CUtensorMap& b, HaloParams p, int max_ctas, int* stat_rows,
-                       cudaStream_t stream) {
+template <int BN, bool kStats, int MODE, bool RES>
+cudaError_t launch_inst(const CUtensorMap& a, const CUtensorMap& b, const HaloParams& p, int grid,
+                        cudaStream_t stream) {
     using Cfg = HaloCfg<BN>;
-    auto kern = conv_halo_kernel<BN, kStats>;
+    auto kern = conv_halo_kernel<BN, kStats, MODE, RES>;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    p.b_resident = (9 * p.k_chunks <= Cfg::kSB && p.num_n_tiles == 1) ? 1 : 0;
+    kern<<<grid, 320, Cfg::kSmemBytes, stream>>>(a, b, p);
+    return cudaGetLastError();
+}
+
+template <int BN, bool kStats>
+cudaError_t launch_one(const CUtensorMap& a, const CUtensorMap& b, HaloParams p, int max_ctas, int* stat_rows,
+                       cudaStream_t stream) {
     const int total = p.num_m_tiles * p.num_n_tiles;
     int grid = total < max_ctas ? total : max_ctas;
     grid -= grid % p.num_n_tiles;
     if (grid < p.num_n_tiles) grid = p.num_n_tiles;
     if (stat_rows != nullptr) *stat_rows = grid / p.num_n_tiles;
-    kern<<<grid, 192, Cfg::kSmemBytes, stream>>>(a, b, p);
-    return cudaGetLastError();
+    p.b_resident = 0;
+    if (p.mode == 0) {
+        if constexpr (BN == 64) {
+            if (p.k_chunks == 1 && p.num_n_tiles == 1) {
+                p.b_resident = 1;
+                return launch_inst<64, kStats, 0, true>(a, b, p, grid, stream);
+            }
+        }
+        return launch_inst<BN, kStats, 0, false>(a, b, p, grid, stream);
+    }
+    return launch_inst<BN, kStats, 1, false>(a, b, p, grid, stream);
 }
 
 }  // namespace

@@ -83,8 +83,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
     const int img = p.gH * p.gW;
 
     if (warp == 0) {
-        if (lane == 0) {
-            // ------------------------------ TMA producer ------------------------------
+        {
+            // ------------------------------ TMA producer (whole warp loops, one elected lane issues) ----
             int slab[2], tap[2], cb[2];
 #pragma unroll
             for (int b = 0; b < 2; ++b) {
@@ -100,18 +100,21 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
                 const int n0 = p0 / img;
                 const int h0 = (p0 - n0 * img) / p.gW;
                 mbar_wait(&empty[stage], phase ^ 1u, 11);
-                mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
-                uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                if (elect_one_sync()) {
+                    mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+                    uint8_t* sa = smem + stage * Cfg::kStageBytes;
 #pragma unroll
-                for (int b = 0; b < 2; ++b) {
-                    tma_load_4d(sa + b * kSlabBytes, &mapX, &full[stage], cb[b] * 64, p.tap_dw[tap[b]],
-                                h0 * p.in_stride + p.tap_dh[tap[b]], n0);
-                }
+                    for (int b = 0; b < 2; ++b) {
+                        tma_load_4d(sa + b * kSlabBytes, &mapX, &full[stage], cb[b] * 64, p.tap_dw[tap[b]],
+                                    h0 * p.in_stride + p.tap_dh[tap[b]], n0);
+                    }
 #pragma unroll
-                for (int nb = 0; nb < Cfg::kNSlabs; ++nb) {
-                    tma_load_4d(sa + (2 + nb) * kSlabBytes, &mapDY, &full[stage],
-                                (n_tile * Cfg::kNSlabs + nb) * 64, 0, h0, n0);
+                    for (int nb = 0; nb < Cfg::kNSlabs; ++nb) {
+                        tma_load_4d(sa + (2 + nb) * kSlabBytes, &mapDY, &full[stage],
+                                    (n_tile * Cfg::kNSlabs + nb) * 64, 0, h0, n0);
+                    }
                 }
+                __syncwarp();
                 if (++stage == Cfg::kStages) {
                     stage = 0;
                     phase ^= 1u;
@@ -119,30 +122,34 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
-            // ------------------------------ MMA issuer --------------------------------
+        {
+            // ------------------------------ MMA issuer (whole warp loops, one elected lane issues) ------
             constexpr uint32_t idesc = make_idesc_bf16(128, BN, 1, 1);  // both operands MN-major
             int stage = 0;
             uint32_t phase = 0;
             for (int it = 0; it < n_iters; ++it) {
                 mbar_wait(&full[stage], phase, 13);
                 tc_fence_after();
-                const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-                // MN-major SW128: 64-element MN blocks kSlabBytes apart (LBO), 8-pixel K groups 1024 B apart (SBO)
-                const uint64_t ad = make_smem_desc_sw128(sa, kSlabBytes, 1024);
-                const uint64_t bd = make_smem_desc_sw128(sa + 2 * kSlabBytes, kSlabBytes, 1024);
+                if (elect_one_sync()) {
+                    const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+                    // MN-major SW128: 64-element MN blocks kSlabBytes apart (LBO), 8-pixel K groups 1024 B apart (SBO)
+                    const uint64_t ad = make_smem_desc_sw128(sa, kSlabBytes, 1024);
+                    const uint64_t bd = make_smem_desc_sw128(sa + 2 * kSlabBytes, kSlabBytes, 1024);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    // advance 16 pixels = 16 rows x 128 B = 2048 B
-                    umma_bf16(tmem_base, ad + 128u * k, bd + 128u * k, idesc, (it | k) != 0 ? 1u : 0u);
+                    for (int k = 0; k < 4; ++k) {
+                        // advance 16 pixels = 16 rows x 128 B = 2048 B
+                        umma_bf16(tmem_base, ad + 128u * k, bd + 128u * k, idesc, (it | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit(&empty[stage]);
                 }
-                umma_commit(&empty[stage]);
+                __syncwarp();
                 if (++stage == Cfg::kStages) {
                     stage = 0;
                     phase ^= 1u;
                 }
             }
-            umma_commit(&tfull[0]);
+            if (elect_one_sync()) umma_commit(&tfull[0]);
+            __syncwarp();
         }
     } else {
         // ---------------------------------- epilogue --------------------------------------
