@@ -54,10 +54,12 @@ typedef struct B2cConvDesc {
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)
  * at models/resnet.py:47-48,102-103,132. `w_fprop` is bf16 [tap][cout][cin] (see b2c_repack_weights).
- * If part_sum/part_sq are non-null the epilogue also writes per-CTA per-channel sums of y and y^2
- * (fp32, rows*cout each, rows <= 148 returned in *stat_rows (host int)) for b2c_bn_finalize. */
-B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, void* y, float* part_sum,
-                   float* part_sq, int* stat_rows, void* stream);
+ * add_src (optional, bf16, y's shape) is added before the store: the pre-activation residual
+ * `out += shortcut` of models/preact_resnet.py:33. If part_sum/part_sq are non-null the epilogue also writes
+ * per-CTA per-channel sums of y and y^2 (after the add; fp32, rows*cout each, rows <= 148 returned in
+ * *stat_rows (host int)) for b2c_bn_finalize. */
+B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, void* y, const void* add_src,
+                   float* part_sum, float* part_sq, int* stat_rows, void* stream);
 
 /* dx[n,h,w,cin] = conv_transpose(dy, w) (+ add_src). Replaces cudnn_convolution_backward_input reached
  * from loss.backward(), main.py:104. `w_dgrad` is bf16 [tap][cin][cout]. add_src (optional, bf16, dx's
@@ -125,9 +127,16 @@ B2C_API int b2c_bn_bwd_stats_noalloc(const void* dout, const void* act, const vo
                              const float* save_rstd, float* dgamma, float* dbeta, float* coef_a, float* coef_b,
                              float* coef_c, void* stream);
 
-/* dy = A*dz + B*y + C per channel (bf16). */
+/* dy = A*dz + B*y + C per channel (+ add, optional bf16 tensor of dy's shape: the gradient that bypasses
+ * the BatchNorm through an identity shortcut, models/preact_resnet.py:29-33). bf16 out. */
 B2C_API int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,
-                     void* dy, long long rows, int channels, void* stream);
+                     const void* add, void* dy, long long rows, int channels, void* stream);
+
+/* nn.MaxPool2d(kernel_size=2, stride=2), models/vgg.py:31, on NHWC bf16 [n,h,w,c] -> [n,h/2,w/2,c]. */
+B2C_API int b2c_maxpool2x2_fwd(const void* x, void* y, int n, int h, int w, int channels, void* stream);
+/* Its backward: dx[n,h,w,c] = dy of the window if x is the window's first maximum (torch's tie rule), else 0. */
+B2C_API int b2c_maxpool2x2_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int channels,
+                       void* stream);
 
 /* Head: F.avg_pool2d(out, 4) -> view -> nn.Linear, models/resnet.py:137-139. act is [n, hw, channels]
  * bf16; pooled [n, channels] and logits [n, classes] are fp32 outputs. */

@@ -101,3 +101,122 @@ def train_step_grads(x, target, params, buffers, forward=resnet_forward, taps=No
     loss = F.cross_entropy(logits, target)                                         # main.py:86,103
     grads = torch.autograd.grad(loss, list(leaves.values()))
     return loss.detach(), logits.detach(), OrderedDict(zip(leaves.keys(), grads))
+
+
+# ------------------------------------------------------------------------------------------------
+# VGG (models/vgg.py) — BASELINE config 3
+# ------------------------------------------------------------------------------------------------
+VGG_CFG = {
+    "VGG11": [64, "M", 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"],
+    "VGG13": [64, 64, "M", 128, 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"],
+    "VGG16": [64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512, "M", 512, 512, 512, "M"],
+    "VGG19": [64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512, 512, 512, 512, "M"],
+}
+
+
+def build_vgg_params(seed, name="VGG16"):
+    """Same construction order as VGG.__init__ (models/vgg.py:15-18): features first, then the classifier."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+    i, cin = 0, 3
+    for x in VGG_CFG[name]:                                        # _make_layers, vgg.py:26-38
+        if x == "M":
+            i += 1
+            continue
+        conv = nn.Conv2d(cin, x, kernel_size=3, padding=1)         # bias=True (vgg.py:33)
+        bn = nn.BatchNorm2d(x)
+        params[f"features.{i}.weight"] = conv.weight.detach().clone()
+        params[f"features.{i}.bias"] = conv.bias.detach().clone()
+        params[f"features.{i + 1}.weight"] = bn.weight.detach().clone()
+        params[f"features.{i + 1}.bias"] = bn.bias.detach().clone()
+        buffers[f"features.{i + 1}.running_mean"] = bn.running_mean.clone()
+        buffers[f"features.{i + 1}.running_var"] = bn.running_var.clone()
+        buffers[f"features.{i + 1}.num_batches_tracked"] = bn.num_batches_tracked.clone()
+        cin = x
+        i += 3
+    lin = nn.Linear(512, 10)                                       # vgg.py:18
+    params["classifier.weight"] = lin.weight.detach().clone()
+    params["classifier.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def vgg_forward(x, params, buffers, training=True, name="VGG16", taps=None):
+    out, i = x, 0
+    for c in VGG_CFG[name]:
+        if c == "M":
+            out = F.max_pool2d(out, kernel_size=2, stride=2)       # vgg.py:31
+            i += 1
+            continue
+        out = F.conv2d(out, params[f"features.{i}.weight"], params[f"features.{i}.bias"], padding=1)
+        if taps is not None:
+            taps[f"features.{i}"] = out
+        out = F.relu(_bn(out, f"features.{i + 1}", params, buffers, training))     # vgg.py:33-35
+        i += 3
+    out = out.view(out.size(0), -1)                                # AvgPool2d(1,1) is the identity; vgg.py:22
+    return F.linear(out, params["classifier.weight"], params["classifier.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
+# PreActResNet-18 (models/preact_resnet.py) — BASELINE config 4
+# ------------------------------------------------------------------------------------------------
+def build_preact_params(seed, num_blocks=RESNET18_BLOCKS):
+    """Construction order of PreActResNet.__init__ / PreActBlock.__init__ (preact_resnet.py:16-26,68-75)."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 64, 3, 1)
+    in_planes = 64
+    for li, (nb, planes) in enumerate(zip(num_blocks, RESNET_PLANES)):
+        strides = [1 if li == 0 else 2] + [1] * (nb - 1)
+        for bi, s in enumerate(strides):
+            name = f"layer{li + 1}.{bi}"
+            bn(name + ".bn1", in_planes)                           # :18
+            conv(name + ".conv1", in_planes, planes, 3, s)         # :19
+            bn(name + ".bn2", planes)                              # :20
+            conv(name + ".conv2", planes, planes, 3, 1)            # :21
+            if s != 1 or in_planes != planes:                      # :23-26
+                conv(name + ".shortcut.0", in_planes, planes, 1, s)
+            in_planes = planes
+    lin = nn.Linear(in_planes, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def preact_forward(x, params, buffers, training=True, num_blocks=RESNET18_BLOCKS, taps=None):
+    out = F.conv2d(x, params["conv1.weight"], padding=1)           # preact_resnet.py:86
+    if taps is not None:
+        taps["conv1"] = out
+    for li, (nb, planes) in enumerate(zip(num_blocks, RESNET_PLANES)):
+        strides = [1 if li == 0 else 2] + [1] * (nb - 1)
+        for bi, s in enumerate(strides):
+            name = f"layer{li + 1}.{bi}"
+            xin = out
+            o = F.relu(_bn(xin, name + ".bn1", params, buffers, training))          # :29
+            if (name + ".shortcut.0.weight") in params:
+                sc = F.conv2d(o, params[name + ".shortcut.0.weight"], stride=s)     # :30
+            else:
+                sc = xin
+            o = F.conv2d(o, params[name + ".conv1.weight"], stride=s, padding=1)    # :31
+            if taps is not None:
+                taps[name + ".conv1"] = o
+            o = F.conv2d(F.relu(_bn(o, name + ".bn2", params, buffers, training)),
+                         params[name + ".conv2.weight"], padding=1)                 # :32
+            out = o + sc                                                            # :33
+            if taps is not None:
+                taps[name + ".out"] = out
+    out = F.avg_pool2d(out, 4)                                                      # :91
+    out = out.view(out.size(0), -1)
+    return F.linear(out, params["linear.weight"], params["linear.bias"])

@@ -57,7 +57,7 @@ _LL = ctypes.c_longlong
 # name -> argtypes; every function returns int except b2c_error_string
 SIGNATURES = {
     "b2c_version": [],
-    "b2c_conv_fprop": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P, ctypes.POINTER(_I), _P],
+    "b2c_conv_fprop": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, ctypes.POINTER(_I), _P],
     "b2c_conv_dgrad": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P],
     "b2c_conv_wgrad": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P],
     "b2c_bn_finalize": [_P, _P, _I, _I, _F, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P],
@@ -66,7 +66,9 @@ SIGNATURES = {
     "b2c_bn_bwd_partial_rows": [_LL, _I],
     "b2c_bn_bwd_reduce": [_P, _P, _P, _P, _LL, _I, _P, _P],
     "b2c_bn_bwd_finalize": [_P, _I, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],
-    "b2c_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _LL, _I, _P],
+    "b2c_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _P, _LL, _I, _P],
+    "b2c_maxpool2x2_fwd": [_P, _P, _I, _I, _I, _I, _P],
+    "b2c_maxpool2x2_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "b2c_bn_bwd_stats_noalloc": [_P, _P, _P, _P, _LL, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_head_fwd": [_P, _I, _I, _I, _P, _P, _I, _P, _P, _P],
     "b2c_ce_loss": [_P, _P, _I, _I, _P, _P, _P, _P],

@@ -155,11 +155,12 @@ const char* b2c_error_string(int code) {
     return "b2c: unknown code";
 }
 
-int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, void* y, float* part_sum,
-                   float* part_sq, int* stat_rows, void* stream) {
+int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, void* y, const void* add_src,
+                   float* part_sum, float* part_sq, int* stat_rows, void* stream) {
     int rc = check_conv(d);
     if (rc) return rc;
-    if (!x || !w_fprop || !y || !aligned16(x) || !aligned16(w_fprop) || !aligned16(y)) return B2C_ERR_ARG;
+    if (!x || !w_fprop || !y || !aligned16(x) || !aligned16(w_fprop) || !aligned16(y) || !aligned16(add_src))
+        return B2C_ERR_ARG;
     if ((part_sum == nullptr) != (part_sq == nullptr)) return B2C_ERR_ARG;
     const int ho = d->h / d->stride, wo = d->w / d->stride;
     if (!grid_tiles(ho, wo, 128)) return B2C_ERR_UNSUPPORTED;
@@ -170,7 +171,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
     const int taps = d->ksize * d->ksize;
     if (halo)
-        return launch_halo(d, x, d->cin, w_fprop, d->cout, bn, false, y, nullptr, part_sum, part_sq, stat_rows,
+        return launch_halo(d, x, d->cin, w_fprop, d->cout, bn, false, y, add_src, part_sum, part_sq, stat_rows,
                            as_stream(stream));
 
     TapGemmParams p = {};
@@ -190,7 +191,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
         p.tap_brow[t] = t * d->cout;
     }
     p.out = static_cast<__nv_bfloat16*>(y);
-    p.add_src = nullptr;
+    p.add_src = static_cast<const __nv_bfloat16*>(add_src);
     p.out_H = ho;
     p.out_W = wo;
     p.out_ld = d->cout;
@@ -457,12 +458,28 @@ int b2c_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, v
 }
 
 int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,
-                     void* dy, long long rows, int channels, void* stream) {
+                     const void* add, void* dy, long long rows, int channels, void* stream) {
     if (!dz || !y || !coef_a || !coef_b || !coef_c || !dy || rows < 0 || channels < 8 || (channels & 7))
         return B2C_ERR_ARG;
-    if (!aligned16(dz) || !aligned16(y) || !aligned16(dy)) return B2C_ERR_ARG;
+    if (!aligned16(dz) || !aligned16(y) || !aligned16(dy) || !aligned16(add)) return B2C_ERR_ARG;
     if (rows == 0) return 0;
-    return cuda_rc(b2c::launch_bn_bwd_apply(dz, y, coef_a, coef_b, coef_c, dy, rows, channels, as_stream(stream)));
+    return cuda_rc(b2c::launch_bn_bwd_apply(dz, y, coef_a, coef_b, coef_c, add, dy, rows, channels,
+                                            as_stream(stream)));
+}
+
+int b2c_maxpool2x2_fwd(const void* x, void* y, int n, int h, int w, int channels, void* stream) {
+    if (!x || !y || n < 1 || h < 2 || w < 2 || (h & 1) || (w & 1) || channels < 8 || (channels & 7) ||
+        !aligned16(x) || !aligned16(y))
+        return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_maxpool_fwd(x, y, n, h, w, channels, as_stream(stream)));
+}
+
+int b2c_maxpool2x2_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int channels,
+                       void* stream) {
+    if (!x || !y || !dy || !dx || n < 1 || h < 2 || w < 2 || (h & 1) || (w & 1) || channels < 8 || (channels & 7) ||
+        !aligned16(x) || !aligned16(y) || !aligned16(dy) || !aligned16(dx))
+        return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_maxpool_bwd(x, y, dy, dx, n, h, w, channels, as_stream(stream)));
 }
 
 int b2c_head_fwd(const void* act, int n, int hw, int channels, const float* weight, const float* bias,

@@ -32,7 +32,10 @@ cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float 
                                    const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
                                    float* coefB, float* coefC, cudaStream_t s);
 cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coefA, const float* coefB,
-                                const float* coefC, void* dy, long long rows, int C, cudaStream_t s);
+                                const float* coefC, const void* add, void* dy, long long rows, int C, cudaStream_t s);
+cudaError_t launch_maxpool_fwd(const void* x, void* y, int n, int h, int w, int C, cudaStream_t s);
+cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int C,
+                               cudaStream_t s);
 cudaError_t launch_head_fwd(const void* act, int N, int hw, int C, const float* W, const float* bias, int K,
                             float* pooled, float* logits, cudaStream_t s);
 cudaError_t launch_ce_loss(const float* logits, const long long* target, int N, int K, float* dlogits, float* loss,

@@ -217,11 +217,11 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int pr
     }
 }
 
-// Pass 3: dy = A*dz + B*y + Cc (bf16 out).
+// Pass 3: dy = A*dz + B*y + Cc (+ add) (bf16 out).
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, const float* __restrict__ coefA,
-                    const float* __restrict__ coefB, const float* __restrict__ coefC, uint4* __restrict__ dy,
-                    long long nvec, int C) {
+                    const float* __restrict__ coefB, const float* __restrict__ coefC, const uint4* __restrict__ add,
+                    uint4* __restrict__ dy, long long nvec, int C) {
     const int cvec = C >> 3;
     for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec;
          v += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -233,7 +233,82 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, c
         for (int e = 0; e < 8; ++e) {
             o[e] = fmaf(__ldg(coefA + c0 + e), d[e], fmaf(__ldg(coefB + c0 + e), yy[e], __ldg(coefC + c0 + e)));
         }
+        if (add != nullptr) {
+            float a[8];
+            unpack8(ld_stream(add + v), a);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] += a[e];
+        }
         dy[v] = pack8(o);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// nn.MaxPool2d(2, 2) forward / backward on NHWC bf16 (models/vgg.py:31). One thread = 8 channels of one
+// output pixel. Backward routes the gradient to the FIRST maximum of the window in (row, col) scan order,
+// which is what torch's max_pool2d_with_indices records.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, long long nvec_out, int Ho, int Wo, int C) {
+    const int cvec = C >> 3;
+    for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec_out;
+         v += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int cv = static_cast<int>(v % cvec);
+        long long pix = v / cvec;
+        const int wo = static_cast<int>(pix % Wo);
+        pix /= Wo;
+        const int ho = static_cast<int>(pix % Ho);
+        const long long n = pix / Ho;
+        const long long W = 2LL * Wo;
+        const long long base = ((n * 2 * Ho + 2 * ho) * W + 2 * wo) * cvec + cv;
+        float a[8], b[8], c[8], d[8], m[8];
+        unpack8(ld_stream(x + base), a);
+        unpack8(ld_stream(x + base + cvec), b);
+        unpack8(ld_stream(x + base + W * cvec), c);
+        unpack8(ld_stream(x + base + W * cvec + cvec), d);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) m[e] = fmaxf(fmaxf(a[e], b[e]), fmaxf(c[e], d[e]));
+        y[v] = pack8(m);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y, const uint4* __restrict__ dy,
+                   uint4* __restrict__ dx, long long nvec_out, int Ho, int Wo, int C) {
+    const int cvec = C >> 3;
+    for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec_out;
+         v += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int cv = static_cast<int>(v % cvec);
+        long long pix = v / cvec;
+        const int wo = static_cast<int>(pix % Wo);
+        pix /= Wo;
+        const int ho = static_cast<int>(pix % Ho);
+        const long long n = pix / Ho;
+        const long long W = 2LL * Wo;
+        const long long base = ((n * 2 * Ho + 2 * ho) * W + 2 * wo) * cvec + cv;
+        float a[8], b[8], c[8], d[8], m[8], g[8];
+        unpack8(ld_stream(x + base), a);
+        unpack8(ld_stream(x + base + cvec), b);
+        unpack8(ld_stream(x + base + W * cvec), c);
+        unpack8(ld_stream(x + base + W * cvec + cvec), d);
+        unpack8(ld_stream(y + v), m);
+        unpack8(ld_stream(dy + v), g);
+        float oa[8], ob[8], oc[8], od[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const bool ha = a[e] == m[e];
+            const bool hb = !ha && b[e] == m[e];
+            const bool hc = !ha && !hb && c[e] == m[e];
+            const bool hd = !ha && !hb && !hc;
+            oa[e] = ha ? g[e] : 0.f;
+            ob[e] = hb ? g[e] : 0.f;
+            oc[e] = hc ? g[e] : 0.f;
+            od[e] = hd ? g[e] : 0.f;
+        }
+        dx[base] = pack8(oa);
+        dx[base + cvec] = pack8(ob);
+        dx[base + W * cvec] = pack8(oc);
+        dx[base + W * cvec + cvec] = pack8(od);
     }
 }
 
@@ -628,11 +703,28 @@ cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float 
 }
 
 cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coefA, const float* coefB,
-                                const float* coefC, void* dy, long long rows, int C, cudaStream_t s) {
+                                const float* coefC, const void* add, void* dy, long long rows, int C,
+                                cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
     bn_bwd_apply_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(
-        static_cast<const uint4*>(dz), static_cast<const uint4*>(y), coefA, coefB, coefC, static_cast<uint4*>(dy),
-        nvec, C);
+        static_cast<const uint4*>(dz), static_cast<const uint4*>(y), coefA, coefB, coefC,
+        static_cast<const uint4*>(add), static_cast<uint4*>(dy), nvec, C);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_maxpool_fwd(const void* x, void* y, int n, int h, int w, int C, cudaStream_t s) {
+    const long long nvec = static_cast<long long>(n) * (h / 2) * (w / 2) * (C >> 3);
+    maxpool_fwd_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(static_cast<const uint4*>(x),
+                                                                   static_cast<uint4*>(y), nvec, h / 2, w / 2, C);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int C,
+                               cudaStream_t s) {
+    const long long nvec = static_cast<long long>(n) * (h / 2) * (w / 2) * (C >> 3);
+    maxpool_bwd_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(
+        static_cast<const uint4*>(x), static_cast<const uint4*>(y), static_cast<const uint4*>(dy),
+        static_cast<uint4*>(dx), nvec, h / 2, w / 2, C);
     return cudaGetLastError();
 }
 

@@ -65,6 +65,69 @@ def resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes
                 feat=in_planes)
 
 
+VGG_CFG = {   # models/vgg.py:6-11
+    "VGG11": [64, "M", 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"],
+    "VGG13": [64, 64, "M", 128, 128, "M", 256, 256, "M", 512, 512, "M", 512, 512, "M"],
+    "VGG16": [64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512, "M", 512, 512, 512, "M"],
+    "VGG19": [64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512, 512, 512, 512, "M"],
+}
+
+
+def vgg_spec(name="VGG16", num_classes=10):
+    """VGG as models/vgg.py:14-38 composes it: [Conv3x3(bias) -> BN -> ReLU]* with MaxPool2d(2,2) between
+    stages, a no-op AvgPool2d(1,1), Linear(512, 10). Sequential indices give the state_dict names."""
+    params, buffers, layers = OrderedDict(), OrderedDict(), []
+    i, cin = 0, 3
+    for x in VGG_CFG[name]:
+        if x == "M":
+            layers.append(("pool",))
+            i += 1
+            continue
+        params[f"features.{i}.weight"] = (x, cin, 3, 3)
+        params[f"features.{i}.bias"] = (x,)          # cancelled by the BatchNorm that follows (SURVEY F12)
+        params[f"features.{i + 1}.weight"] = (x,)
+        params[f"features.{i + 1}.bias"] = (x,)
+        buffers[f"features.{i + 1}.running_mean"] = (x,)
+        buffers[f"features.{i + 1}.running_var"] = (x,)
+        layers.append(("conv", f"features.{i}", f"features.{i + 1}", cin, x))
+        cin = x
+        i += 3
+    params["classifier.weight"] = (num_classes, 512)
+    params["classifier.bias"] = (num_classes,)
+    return dict(family="vgg", params=params, buffers=buffers, layers=layers, num_classes=num_classes, feat=512)
+
+
+def preact_resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=10):
+    """PreActResNet-18/34 as models/preact_resnet.py:12-34,64-94 composes it."""
+    params, buffers, blocks = OrderedDict(), OrderedDict(), []
+    params["conv1.weight"] = (64, 3, 3, 3)
+    in_planes = 64
+    for li, (nb, pl) in enumerate(zip(num_blocks, planes)):
+        strides = [1 if li == 0 else 2] + [1] * (nb - 1)
+        for bi, s in enumerate(strides):
+            name = f"layer{li + 1}.{bi}"
+            for bn, c in ((".bn1", in_planes),):
+                params[name + bn + ".weight"] = (c,)
+                params[name + bn + ".bias"] = (c,)
+                buffers[name + bn + ".running_mean"] = (c,)
+                buffers[name + bn + ".running_var"] = (c,)
+            params[name + ".conv1.weight"] = (pl, in_planes, 3, 3)
+            params[name + ".bn2.weight"] = (pl,)
+            params[name + ".bn2.bias"] = (pl,)
+            buffers[name + ".bn2.running_mean"] = (pl,)
+            buffers[name + ".bn2.running_var"] = (pl,)
+            params[name + ".conv2.weight"] = (pl, pl, 3, 3)
+            shortcut = s != 1 or in_planes != pl
+            if shortcut:
+                params[name + ".shortcut.0.weight"] = (pl, in_planes, 1, 1)
+            blocks.append(dict(name=name, cin=in_planes, cout=pl, stride=s, shortcut=shortcut))
+            in_planes = pl
+    params["linear.weight"] = (num_classes, in_planes)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="preact", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes,
+                feat=in_planes)
+
+
 def param_offsets(spec):
     """Element offsets of every parameter in the flat fp32 arenas (16-byte aligned), reference order."""
     p_off, off = OrderedDict(), 0
@@ -79,10 +142,17 @@ def param_offsets(spec):
 
 def backward_groups(spec):
     """Parameter-name groups in the order the backward plan completes them (head, blocks reversed, stem)."""
+    first_conv = next(n for n, sh in spec["params"].items() if len(sh) == 4)[:-len(".weight")]
+
     def key(name):
         if name.startswith("layer"):
             return ".".join(name.split(".")[:2])
-        return "head" if name.startswith("linear") else "stem"
+        if name.startswith("features."):
+            idx = int(name.split(".")[1])
+            owner = idx if f"features.{idx}.weight" in spec["params"] and len(spec["params"][f"features.{idx}.weight"]) == 4 \
+                else idx - 1
+            return "stem" if f"features.{owner}" == first_conv else f"features.{owner}"
+        return "head" if name.startswith(("linear", "classifier")) else "stem"
     groups = OrderedDict()
     for name in spec["params"]:
         groups.setdefault(key(name), []).append(name)
@@ -146,9 +216,9 @@ class ConvUnit:
             self.scale, self.shift, self.mean, self.rstd = (eng.new_f32(cout) for _ in range(4))
 
     # ---- forward pieces
-    def fprop(self, eng, stats=True):
+    def fprop(self, eng, stats=True, add_src=None):
         ps, pq = (eng.part_sum, eng.part_sq) if stats else (None, None)
-        self.stat_rows = ops.conv_fprop(self.desc, self.x, self.wf, self.y, ps, pq)
+        self.stat_rows = ops.conv_fprop(self.desc, self.x, self.wf, self.y, ps, pq, add_src=add_src)
 
     def bn_stats(self, eng, training):
         if training:
@@ -159,14 +229,15 @@ class ConvUnit:
                                     self.shift)
 
     # ---- backward pieces
-    def bn_backward(self, eng, dout, act, dz_out, dy):
-        """dout: grad w.r.t. act(bn(y)) (or w.r.t. bn(y) when act is None). Writes dz (optional) and dy."""
+    def bn_backward(self, eng, dout, act, dz_out, dy, add=None):
+        """dout: grad w.r.t. act(bn(y)) (or w.r.t. bn(y) when act is None). Writes dz (optional) and
+        dy = dBN/dy (+ add)."""
         prow = ops.bn_bwd_partial_rows(self.rows, self.cout)
         ops.bn_bwd_reduce(dout, act, self.y, dz_out, self.rows, self.cout, eng.bwd_partial)
         ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
                             self.dgamma, self.dbeta, eng.coef_a, eng.coef_b, eng.coef_c)
         src = dz_out if dz_out is not None else dout
-        ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout)
+        ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add)
 
     def wgrad(self, dy):
         ops.conv_wgrad(self.desc_w, self.x, dy, self.dw)
@@ -192,6 +263,10 @@ class Engine:
         self.fwd_ops, self.bwd_ops = [], []
         if spec["family"] == "resnet":
             self._build_resnet()
+        elif spec["family"] == "vgg":
+            self._build_vgg()
+        elif spec["family"] == "preact":
+            self._build_preact()
         else:
             raise NotImplementedError(spec["family"])
 
@@ -402,6 +477,157 @@ class Engine:
             stem.bn_backward(self, dout, a0, dout, dy0)
             stem.wgrad(dy0)
         Bk.append(bwd_stem)
+        self.bwd_ops = Bk
+
+    # ------------------------------------------------------------------ shared head (pool + linear)
+    def _build_head(self, x, H, W, wname, bname):
+        spec, N = self.spec, self.N
+        self.feat_act, self.feat_hw, self.feat_c = x, H * W, spec["feat"]
+        K = spec["num_classes"]
+        self.lin_w, self.lin_b = self.param_view(wname), self.param_view(bname)
+        self.pooled = self.new_f32(N, self.feat_c)
+        self.logits = self.new_f32(N, K)
+        self.dlogits = self.new_f32(N, K)
+        dout_last = self.new_act(*x.shape)
+
+        def fwd_head(training):
+            ops.head_fwd(self.feat_act, N, self.feat_hw, self.feat_c, self.lin_w, self.lin_b, K, self.pooled,
+                         self.logits)
+
+        def bwd_head():
+            ops.head_bwd(self.dlogits, self.pooled, self.lin_w, N, self.feat_hw, self.feat_c, K, dout_last,
+                         self.grad_view(wname), self.grad_view(bname))
+        return fwd_head, bwd_head, dout_last
+
+    # ------------------------------------------------------------------ VGG plan (models/vgg.py:20-38)
+    def _build_vgg(self):
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        self.units = []
+        F, stages = self.fwd_ops, []
+        x, H, W = self.x0, 32, 32
+        layers = spec["layers"]
+        for li, layer in enumerate(layers):
+            if layer[0] != "conv":
+                continue
+            _, cname, bname, cin, cout = layer
+            u = ConvUnit(self, cname, bname, x, cin, cout, 3, 1, H, W, stem=(cin == 3))
+            act = self.new_act(N, H, W, cout)
+            pooled = None
+            if li + 1 < len(layers) and layers[li + 1][0] == "pool":
+                pooled = self.new_act(N, H // 2, W // 2, cout)
+            self.units.append(u)
+            stages.append((u, act, pooled, x))
+
+            def fwd(training, u=u, act=act, pooled=pooled):
+                u.fprop(self)
+                u.bn_stats(self, training)
+                ops.bn_act_apply(u.y, u.scale, u.shift, act, u.rows, u.cout, relu=True)
+                if pooled is not None:
+                    ops.maxpool2x2_fwd(act, pooled)
+            F.append(fwd)
+            if pooled is not None:
+                x, H, W = pooled, H // 2, W // 2
+            else:
+                x = act
+        fwd_head, bwd_head, dout = self._build_head(x, H, W, "classifier.weight", "classifier.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        for si in range(len(stages) - 1, -1, -1):
+            u, act, pooled, xin = stages[si]
+            dact = self.new_act(*act.shape) if pooled is not None else None
+            dy = self.new_act(*u.y.shape)
+            dx = self.new_act(*xin.shape) if si > 0 else None
+
+            def bwd(u=u, act=act, pooled=pooled, dout=dout, dact=dact, dy=dy, dx=dx):
+                g = dout
+                if pooled is not None:
+                    ops.maxpool2x2_bwd(act, pooled, dout, dact)
+                    g = dact
+                u.bn_backward(self, g, act, g, dy)
+                u.wgrad(dy)
+                if dx is not None:
+                    u.dgrad(dy, dx)
+            Bk.append(bwd)
+            dout = dx
+        self.bwd_ops = Bk
+
+    # ------------------------------------------------------------------ PreActResNet plan
+    def _build_preact(self):
+        """models/preact_resnet.py:28-34: out = relu(bn1(x)); sc = shortcut(out) | x; out = conv1(out);
+        out = conv2(relu(bn2(out))); out += sc. BatchNorm sits BEFORE each conv, so a BN's statistics come
+        from the epilogue of whichever conv produced its input (conv2's epilogue includes the residual add)."""
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        stem = ConvUnit(self, "conv1", None, self.x0, 3, 64, 3, 1, 32, 32, stem=True)
+        self.units = [stem]
+        F, blocks = self.fwd_ops, []
+
+        class PreBN:
+            """BatchNorm applied to tensor `y` produced by `producer` (whose epilogue emitted the statistics)."""
+            def __init__(s, eng, bn_name, y, C, rows):
+                s.y, s.cout, s.rows = y, C, rows
+                s.gamma, s.beta = eng.param_view(bn_name + ".weight"), eng.param_view(bn_name + ".bias")
+                s.dgamma, s.dbeta = eng.grad_view(bn_name + ".weight"), eng.grad_view(bn_name + ".bias")
+                s.rm, s.rv = eng.buffer_view(bn_name + ".running_mean"), eng.buffer_view(bn_name + ".running_var")
+                s.scale, s.shift, s.mean, s.rstd = (eng.new_f32(C) for _ in range(4))
+            stat_rows = 0
+            bn_stats = ConvUnit.bn_stats
+            bn_backward = ConvUnit.bn_backward
+
+        F.append(lambda training: stem.fprop(self, True))
+        x, H, W, producer = stem.y, 32, 32, stem
+        nblk = len(spec["blocks"])
+        for bi, b in enumerate(spec["blocks"]):
+            name, cin, cout, s = b["name"], b["cin"], b["cout"], b["stride"]
+            bn1 = PreBN(self, name + ".bn1", x, cin, N * H * W)
+            a = self.new_act(N, H, W, cin)
+            c1 = ConvUnit(self, name + ".conv1", name + ".bn2", a, cin, cout, 3, s, H, W)
+            Ho, Wo = H // s, W // s
+            a2 = self.new_act(N, Ho, Wo, cout)
+            c2 = ConvUnit(self, name + ".conv2", None, a2, cout, cout, 3, 1, Ho, Wo)
+            cs = ConvUnit(self, name + ".shortcut.0", None, a, cin, cout, 1, s, H, W) if b["shortcut"] else None
+            last = bi == nblk - 1
+            self.units += [c1, c2] + ([cs] if cs else [])
+            blocks.append((bn1, a, c1, a2, c2, cs, x))
+
+            def fwd(training, bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, cs=cs, x=x, producer=producer, last=last):
+                bn1.stat_rows = producer.stat_rows
+                bn1.bn_stats(self, training)
+                ops.bn_act_apply(x, bn1.scale, bn1.shift, a, bn1.rows, bn1.cout, relu=True)
+                if cs is not None:
+                    cs.fprop(self, stats=False)
+                c1.fprop(self)
+                c1.bn_stats(self, training)
+                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a2, c1.rows, c1.cout, relu=True)
+                c2.fprop(self, stats=not last, add_src=(cs.y if cs is not None else x))
+            F.append(fwd)
+            x, H, W, producer = c2.y, Ho, Wo, c2
+        fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        for (bn1, a, c1, a2, c2, cs, xin) in reversed(blocks):
+            da2 = self.new_act(*a2.shape)
+            dy1 = self.new_act(*c1.y.shape)
+            da = self.new_act(*a.shape)
+            dx = self.new_act(*xin.shape)
+
+            def bwd(bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, cs=cs, dout=dout, da2=da2, dy1=dy1, da=da, dx=dx):
+                c2.wgrad(dout)                              # d(conv2 out) = d(block out)
+                c2.dgrad(dout, da2)
+                c1.bn_backward(self, da2, a2, da2, dy1)     # a2 = relu(bn2(conv1 out))
+                c1.wgrad(dy1)
+                if cs is not None:
+                    cs.wgrad(dout)
+                    cs.dgrad(dout, da)                      # zero-fill + even pixels
+                    c1.dgrad(dy1, da, add_src=da)
+                    bn1.bn_backward(self, da, a, da, dx)    # a = relu(bn1(x)); no identity path
+                else:
+                    c1.dgrad(dy1, da)
+                    bn1.bn_backward(self, da, a, da, dx, add=dout)   # + gradient through the identity shortcut
+            Bk.append(bwd)
+            dout = dx
+        Bk.append(lambda dout=dout: stem.wgrad(dout))
         self.bwd_ops = Bk
 
     # ------------------------------------------------------------------ execution

@@ -45,13 +45,14 @@ def pack_weight_dgrad(w_oihw):
     return w_oihw.permute(2, 3, 1, 0).reshape(kh * kw, ci, co).contiguous().to(torch.bfloat16)
 
 
-def conv_fprop(d, x, w_fprop, y, part_sum=None, part_sq=None):
-    """y = conv(x); returns the number of BatchNorm partial rows written (0 without statistics)."""
+def conv_fprop(d, x, w_fprop, y, part_sum=None, part_sq=None, add_src=None):
+    """y = conv(x) (+ add_src); returns the number of BatchNorm partial rows written (0 without statistics)."""
     lib = _lib.load()
     _need(x, torch.bfloat16, "x"); _need(w_fprop, torch.bfloat16, "w"); _need(y, torch.bfloat16, "y")
     _need(part_sum, torch.float32, "part_sum"); _need(part_sq, torch.float32, "part_sq")
     rows = ctypes.c_int(0)
-    check(lib.b2c_conv_fprop(ctypes.byref(d), _p(x), _p(w_fprop), _p(y), _p(part_sum), _p(part_sq),
+    _need(add_src, torch.bfloat16, "add_src")
+    check(lib.b2c_conv_fprop(ctypes.byref(d), _p(x), _p(w_fprop), _p(y), _p(add_src), _p(part_sum), _p(part_sq),
                              ctypes.byref(rows), _stream()), "b2c_conv_fprop")
     return rows.value
 
@@ -124,10 +125,23 @@ def bn_bwd_stats_noalloc(dout, act, y, dz_out, rows, channels, count, gamma, sav
                                        _stream()), "b2c_bn_bwd_stats_noalloc")
 
 
-def bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, channels):
+def bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, channels, add=None):
     lib = _lib.load()
-    check(lib.b2c_bn_bwd_apply(_p(dz), _p(y), _p(ca), _p(cb), _p(cc), _p(dy), rows, channels, _stream()),
+    check(lib.b2c_bn_bwd_apply(_p(dz), _p(y), _p(ca), _p(cb), _p(cc), _p(add), _p(dy), rows, channels, _stream()),
           "b2c_bn_bwd_apply")
+
+
+def maxpool2x2_fwd(x, y):
+    lib = _lib.load()
+    n, h, w, c = x.shape
+    _need(x, torch.bfloat16, "x"); _need(y, torch.bfloat16, "y")
+    check(lib.b2c_maxpool2x2_fwd(_p(x), _p(y), n, h, w, c, _stream()), "b2c_maxpool2x2_fwd")
+
+
+def maxpool2x2_bwd(x, y, dy, dx):
+    lib = _lib.load()
+    n, h, w, c = x.shape
+    check(lib.b2c_maxpool2x2_bwd(_p(x), _p(y), _p(dy), _p(dx), n, h, w, c, _stream()), "b2c_maxpool2x2_bwd")
 
 
 def head_fwd(act, n, hw, channels, weight, bias, classes, pooled, logits):

@@ -55,6 +55,31 @@ def golden_resnet18():
     print("resnet18: loss", loss.item(), "params", len(names))
 
 
+def golden_other_nets():
+    """VGG-16 and PreActResNet-18 (BASELINE configs 3, 4): init sums, logits, loss, gradient norms at N=4."""
+    import models.vgg as ref_vgg
+    import models.preact_resnet as ref_pre
+    rs = np.random.RandomState(2)
+    x = torch.from_numpy(rs.standard_normal((4, 3, 32, 32)).astype(np.float32))
+    target = torch.from_numpy(rs.randint(0, 10, size=(4,)).astype(np.int64))
+    out = dict(x=x.numpy(), target=target.numpy())
+    for tag, ctor in (("vgg16", lambda: ref_vgg.VGG("VGG16")), ("preact18", ref_pre.PreActResNet18)):
+        torch.manual_seed(0)
+        net = ctor()
+        net.train()
+        logits = net(x)
+        loss = torch.nn.CrossEntropyLoss()(logits, target)
+        loss.backward()
+        names = [n for n, _ in net.named_parameters()]
+        out[tag + "_names"] = np.array(names)
+        out[tag + "_wsum"] = np.array([p.detach().double().sum().item() for _, p in net.named_parameters()])
+        out[tag + "_gnorm"] = np.array([p.grad.norm().item() for _, p in net.named_parameters()])
+        out[tag + "_logits"] = logits.detach().numpy()
+        out[tag + "_loss"] = np.float32(loss.item())
+        print(tag, "loss", loss.item(), "params", len(names))
+    np.savez_compressed(os.path.join(HERE, "other_nets_seed0_n4.npz"), **out)
+
+
 def golden_augment():
     import torchvision.transforms as transforms
     from PIL import Image
@@ -114,6 +139,7 @@ def golden_sampler():
 
 if __name__ == "__main__":
     golden_resnet18()
+    golden_other_nets()
     golden_augment()
     golden_sgd()
     golden_sampler()

@@ -1,0 +1,178 @@
+"""GPU parity for the other model families of BASELINE.json (config 3: VGG-16, config 4: PreActResNet-18) and
+the kernels only they use (max-pool, residual add in the conv epilogue, identity-bypass add in BN backward).
+
+New kernels: tight against fp32 torch on identical inputs. Whole models: forward against the fp32 oracle
+(oracle/nets.py, pinned to the reference in tests/test_oracle.py); gradients end to end are compared the way
+tests/test_network_gpu.py explains — the layers nearest the loss tightly, every tensor by direction (cosine),
+and the overall error level against stock torch bf16 autocast on the same inputs.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def cos(a, b):
+    a, b = a.double().flatten(), b.double().flatten()
+    return (a @ b / (a.norm() * b.norm()).clamp_min(1e-30)).item()
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import b200cifar
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    return b200cifar.ops
+
+
+def test_maxpool_fwd_bwd(ops):
+    g = torch.Generator(device="cuda").manual_seed(50)
+    for (n, h, w, c) in [(4, 32, 32, 64), (3, 4, 4, 512), (2, 2, 2, 512)]:
+        x = torch.randn(n, h, w, c, device="cuda", generator=g).clamp_min(0).to(torch.bfloat16)   # many ties at 0
+        y = torch.empty(n, h // 2, w // 2, c, device="cuda", dtype=torch.bfloat16)
+        ops.maxpool2x2_fwd(x, y)
+        xr = x.float().permute(0, 3, 1, 2).requires_grad_()
+        yr = F.max_pool2d(xr, 2, 2)
+        dy = torch.randn(n, h // 2, w // 2, c, device="cuda", generator=g).to(torch.bfloat16)
+        yr.backward(dy.float().permute(0, 3, 1, 2))
+        dx = torch.empty_like(x)
+        ops.maxpool2x2_bwd(x, y, dy, dx)
+        torch.cuda.synchronize()
+        assert torch.equal(y.float().permute(0, 3, 1, 2), yr.detach())
+        assert torch.equal(dx.float().permute(0, 3, 1, 2), xr.grad)
+
+
+def test_conv_fprop_residual_add_and_stats(ops):
+    n, h, w, cin, cout = 8, 16, 16, 128, 128
+    g = torch.Generator(device="cuda").manual_seed(51)
+    x = torch.randn(n, h, w, cin, device="cuda", generator=g).to(torch.bfloat16)
+    add = torch.randn(n, h, w, cout, device="cuda", generator=g).to(torch.bfloat16)
+    wt = (torch.randn(cout, cin, 3, 3, device="cuda", generator=g) * 0.03).to(torch.bfloat16).float()
+    for flags in (0, 1):                       # halo kernel and per-tap kernel
+        y = torch.empty(n, h, w, cout, device="cuda", dtype=torch.bfloat16)
+        ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+        pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+        rows = ops.conv_fprop(ops.conv_desc(n, h, w, cin, cout, 3, 1, flags=flags), x, ops.pack_weight_fprop(wt), y,
+                              ps, pq, add_src=add)
+        torch.cuda.synchronize()
+        ref = F.conv2d(x.float().permute(0, 3, 1, 2), wt, padding=1) + add.float().permute(0, 3, 1, 2)
+        assert rel(y.float().permute(0, 3, 1, 2), ref) < 1e-2
+        assert rel(pq[:rows].sum(0), (ref * ref).sum((0, 2, 3))) < 1e-3     # statistics include the add
+
+
+def test_bn_bwd_apply_with_bypass_add(ops):
+    rows, C = 2048, 128
+    g = torch.Generator(device="cuda").manual_seed(52)
+    dz = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+    y = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+    add = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+    ca, cb, cc = (torch.randn(C, device="cuda", generator=g) for _ in range(3))
+    dy = torch.empty_like(dz)
+    ops.bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, C, add=add)
+    torch.cuda.synchronize()
+    assert rel(dy.float(), ca * dz.float() + cb * y.float() + cc + add.float()) < 1e-2
+
+
+MODELS = {
+    "vgg16": ("vgg_spec", "build_vgg_params", "vgg_forward", "features.0", ["classifier.weight", "features.41.weight",
+                                                                              "features.40.weight"]),
+    "preact18": ("preact_resnet_spec", "build_preact_params", "preact_forward", "conv1",
+                 ["linear.weight", "layer4.1.conv2.weight", "layer4.1.bn2.weight"]),
+}
+
+
+@pytest.mark.parametrize("model", list(MODELS))
+def test_model_training_step(ops, model):
+    from b200cifar import engine
+    from oracle import nets
+    spec_fn, build_fn, fwd_fn, first_conv, near_loss = MODELS[model]
+    N = 128
+    params, buffers = getattr(nets, build_fn)(0)
+    forward = getattr(nets, fwd_fn)
+    rs = np.random.RandomState(4)
+    x = torch.from_numpy(rs.standard_normal((N, 3, 32, 32)).astype(np.float32)).cuda()
+    target = torch.from_numpy(rs.randint(0, 10, size=(N,)).astype(np.int64)).cuda()
+    cp = {k: v.cuda() for k, v in params.items()}
+    cb = {k: v.cuda() for k, v in buffers.items()}
+    taps = {}
+    loss_ref, logits_ref, grads_ref = nets.train_step_grads(x, target, cp, cb, forward=forward, taps=taps)
+    eng = engine.Engine(getattr(engine, spec_fn)(), N)
+    eng.load_params(params, {k: v for k, v in buffers.items() if not k.endswith("num_batches_tracked")})
+    ops.stem_im2col(x, eng.x0)
+    eng.zero_grad()
+    eng.forward(True)
+    loss = torch.zeros(1, device="cuda")
+    ops.ce_loss(eng.logits, target, N, 10, eng.dlogits, loss)
+    eng.backward()
+    torch.cuda.synchronize()
+    fwd_err = {u.name: rel(u.y.float().permute(0, 3, 1, 2), taps[u.name].detach()) for u in eng.units if u.name in taps}
+    grads = eng.named_grads()
+    g_rel = {k: rel(grads[k], v) for k, v in grads_ref.items() if v.norm().item() > 1e-6}
+    g_cos = {k: cos(grads[k], v) for k, v in grads_ref.items() if v.norm().item() > 1e-6}
+    # stock bf16 autocast for context
+    leaves = {k: v.detach().clone().requires_grad_(True) for k, v in cp.items()}
+    ab = {k: v.clone().cuda() for k, v in buffers.items()}
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        ls = F.cross_entropy(forward(x, leaves, ab, training=True).float(), target)
+    ag = torch.autograd.grad(ls, list(leaves.values()))
+    a_rel = {k: rel(g.float(), grads_ref[k]) for k, g in zip(leaves, ag) if grads_ref[k].norm().item() > 1e-6}
+    os.makedirs("gpurun_out", exist_ok=True)
+    json.dump(dict(forward=fwd_err, logits=rel(eng.logits, logits_ref), grad_rel=g_rel, grad_cos=g_cos,
+                   autocast_grad_rel=a_rel), open(f"gpurun_out/parity_{model}.json", "w"), indent=1)
+    assert fwd_err[first_conv] < 1e-2                                   # first layer: no compounding yet
+    assert rel(eng.logits, logits_ref) < 5e-2 and abs(loss.item() - loss_ref.item()) < 2e-2
+    for k in near_loss:                                                 # nearest the loss: tight
+        assert g_rel[k] < 6e-2, (k, g_rel[k])
+    assert min(g_cos.values()) > 0.7, sorted(g_cos.items(), key=lambda kv: kv[1])[:5]
+    assert np.median(list(g_rel.values())) < 1.5 * np.median(list(a_rel.values())) + 1e-2
+    for name, b in eng.named_buffers().items():                         # BN running statistics
+        if name.endswith("running_var"):
+            assert rel(b, cb[name]) < 3e-2, name
+
+
+@pytest.mark.parametrize("model", list(MODELS))
+def test_model_trains(ops, model):
+    """A few SGD steps on one batch through the Trainer (CUDA graph): the loss must fall like the fp32 oracle's."""
+    from b200cifar import data, engine, trainer
+    from oracle import nets
+    spec_fn, build_fn, fwd_fn, _, _ = MODELS[model]
+    N = 128
+    params, buffers = getattr(nets, build_fn)(0)
+    forward = getattr(nets, fwd_fn)
+    images, labels = data.learnable_cifar(512, seed=3)
+    tr = trainer.Trainer(getattr(engine, spec_fn)(), N, lr=0.02)
+    tr.load_params(params, {k: v for k, v in buffers.items() if not k.endswith("num_batches_tracked")})
+    tr.set_dataset(images, labels)
+    idx = np.arange(N)
+    ijf = np.tile(np.array([[4, 4, 0]], dtype=np.int8), (N, 1))        # identity crop, no flip
+    losses = []
+    for _ in range(8):
+        tr.step(idx, ijf)
+        losses.append(tr.read_loss())
+    # fp32 oracle on the same batch
+    from oracle import augment as oaug
+    xb = torch.from_numpy(oaug.normalize_only(images[:N])).cuda()
+    tb = torch.from_numpy(labels[:N]).cuda()
+    leaves = {k: v.detach().clone().cuda().requires_grad_(True) for k, v in params.items()}
+    cb = {k: v.clone().cuda() for k, v in buffers.items()}
+    opt = torch.optim.SGD(list(leaves.values()), lr=0.02, momentum=0.9, weight_decay=5e-4)
+    ref = []
+    for _ in range(8):
+        opt.zero_grad()
+        l = F.cross_entropy(forward(xb, leaves, cb, training=True), tb)
+        l.backward()
+        opt.step()
+        ref.append(l.item())
+    json.dump(dict(ours=losses, oracle=ref), open(f"gpurun_out/train_curve_{model}.json", "w"))
+    assert abs(losses[0] - ref[0]) < 3e-2
+    assert losses[-1] < 0.7 * losses[0] and abs(losses[-1] - ref[-1]) < 0.35 * ref[0]
