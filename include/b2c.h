@@ -75,15 +75,19 @@ B2C_API int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, 
 
 /* Training-mode BatchNorm statistics -> per-channel scale/shift, saved mean/rstd, running-stat update.
  * Replaces the statistics half of F.batch_norm for nn.BatchNorm2d, models/resnet.py:25,28,35,104.
- * running_mean/var may be NULL (no update). count = n*h*w. */
+ * running_mean/var may be NULL (no update). count = n*h*w. conv_bias (optional, [channels]): bias of the
+ * preceding conv (models/vgg.py:33). The kernels never add it to the stored conv output — BatchNorm cancels
+ * it — but the reference's running_mean tracks mean(conv)+bias, so it is added there to keep checkpoints
+ * interchangeable. */
 B2C_API int b2c_bn_finalize(const float* part_sum, const float* part_sq, int rows, int channels, float count,
-                    const float* gamma, const float* beta, float eps, float momentum, float* running_mean,
-                    float* running_var, float* scale, float* shift, float* save_mean, float* save_rstd,
-                    void* stream);
+                    const float* gamma, const float* beta, const float* conv_bias, float eps, float momentum,
+                    float* running_mean, float* running_var, float* scale, float* shift, float* save_mean,
+                    float* save_rstd, void* stream);
 
-/* Eval-mode BatchNorm: scale/shift from running statistics (net.eval(), main.py:118). */
-B2C_API int b2c_bn_eval_scale_shift(int channels, const float* gamma, const float* beta, const float* running_mean,
-                            const float* running_var, float eps, float* scale, float* shift, void* stream);
+/* Eval-mode BatchNorm: scale/shift from running statistics (net.eval(), main.py:118); conv_bias as above. */
+B2C_API int b2c_bn_eval_scale_shift(int channels, const float* gamma, const float* beta, const float* conv_bias,
+                            const float* running_mean, const float* running_var, float eps, float* scale,
+                            float* shift, void* stream);
 
 /* out = act(y*scale + shift + residual'), residual' = res (identity shortcut) or res*res_scale+res_shift
  * (conv shortcut's own BatchNorm). Replaces F.relu(bn(..)), `out += self.shortcut(x)`, F.relu(out),

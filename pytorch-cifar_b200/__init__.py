@@ -5,5 +5,6 @@ The directory name follows the project convention and is not a valid Python iden
 """
 from . import _lib  # noqa: F401
 from . import ops  # noqa: F401
+from . import data, engine, trainer, accelerate  # noqa: F401
 
-__all__ = ["_lib", "ops"]
+__all__ = ["_lib", "ops", "data", "engine", "trainer", "accelerate"]

@@ -1,0 +1,175 @@
+"""Drop-in surface: keep the reference's nn.Module / autograd / optimizer API, run the B200 kernels underneath.
+
+    net = ResNet18().cuda()                 # the reference's unmodified models/resnet.py
+    net = accelerate(net)                   # same object: same parameters, state_dict keys, train()/eval()
+    outputs = net(inputs)                   # main.py:102  — fp32 NCHW in, fp32 [N,10] logits out
+    loss = criterion(outputs, targets); loss.backward(); optimizer.step()      # main.py:103-105
+
+What changes: `net.forward` becomes one torch.autograd.Function whose forward/backward run the static kernel
+plan of engine.py; every nn.Parameter / BN buffer becomes a view into the engine's flat fp32 arenas (same
+names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad` tensors handed to autograd
+are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
+Supported compositions: ResNet with BasicBlock (models/resnet.py), VGG (models/vgg.py), PreActResNet with
+PreActBlock (models/preact_resnet.py); anything else raises — there is no fallback path.
+
+Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
+shadows class names across files and the reference tree may sit anywhere on sys.path.
+"""
+import torch
+import torch.nn as nn
+
+from . import ops
+from .engine import Engine, preact_resnet_spec, resnet_spec, vgg_spec, VGG_CFG
+
+
+def _is(m, name):
+    return type(m).__name__ == name
+
+
+def spec_from_module(net):
+    """Derive the engine spec from a reference-style module by structure."""
+    if _is(net, "ResNet") and hasattr(net, "layer4") and hasattr(net, "linear") and hasattr(net, "bn1"):
+        blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
+        if not all(_is(b, "BasicBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):
+            raise NotImplementedError("accelerate: only BasicBlock ResNets (ResNet-18/34) are supported")
+        return resnet_spec(tuple(blocks), num_classes=net.linear.out_features)
+    if _is(net, "PreActResNet") and hasattr(net, "layer4"):
+        blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
+        if not all(_is(b, "PreActBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):
+            raise NotImplementedError("accelerate: only PreActBlock PreActResNets are supported")
+        return preact_resnet_spec(tuple(blocks), num_classes=net.linear.out_features)
+    if _is(net, "VGG") and hasattr(net, "features") and hasattr(net, "classifier"):
+        cfg = []
+        for m in net.features:
+            if isinstance(m, nn.Conv2d):
+                cfg.append(m.out_channels)
+            elif isinstance(m, nn.MaxPool2d):
+                cfg.append("M")
+        for name, ref in VGG_CFG.items():
+            if ref == cfg:
+                return vgg_spec(name, num_classes=net.classifier.out_features)
+    raise NotImplementedError(f"accelerate: unsupported module {type(net).__module__}.{type(net).__name__}")
+
+
+class _PlanFn(torch.autograd.Function):
+    """forward/backward of the whole network as one autograd node (parameters are explicit inputs so that
+    autograd — and DDP's hooks on AccumulateGrad — see a gradient for each of them)."""
+
+    @staticmethod
+    def forward(ctx, state, x, *params):
+        eng = state.engine_for(x.shape[0])
+        ctx.state, ctx.eng = state, eng
+        eng.repack()                                     # parameters may have changed (optimizer, load_state_dict)
+        ops.stem_im2col(x.contiguous().float(), eng.x0)
+        eng.forward(training=state.net.training)
+        if state.net.training:
+            state.bump_batches_tracked()
+        return eng.logits.clone()
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        eng = ctx.eng
+        eng.dlogits.copy_(dlogits)
+        eng.zero_grad()
+        eng.backward()
+        grads = [eng.grad_view(name) for name in ctx.state.param_names]
+        return (None, None, *grads)
+
+
+class _State:
+    def __init__(self, net, spec):
+        self.net, self.spec = net, spec
+        self.engines = {}
+        self.param_names = list(spec["params"].keys())
+        self.named = dict(net.named_parameters())
+        missing = [n for n in self.param_names if n not in self.named]
+        if missing or len(self.named) != len(self.param_names):
+            raise NotImplementedError(f"accelerate: parameter names do not match the reference layout: {missing[:3]}")
+        self.params = [self.named[n] for n in self.param_names]
+        self.nbt = [b for n, b in net.named_buffers() if n.endswith("num_batches_tracked")]
+        self.base = None
+
+    def engine_for(self, batch):
+        eng = self.engines.get(batch)
+        if eng is None:
+            dev = self.params[0].device
+            eng = Engine(self.spec, batch, dev, share_from=self.base)
+            if self.base is None:
+                self.base = eng
+                self._adopt(eng)
+            self.engines[batch] = eng
+        return eng
+
+    def _adopt(self, eng):
+        """Move parameters and BN running statistics into the arenas and re-point the module at them."""
+        with torch.no_grad():
+            for name, p in zip(self.param_names, self.params):
+                view = eng.param_view(name)
+                view.copy_(p.detach().to(view.dtype))
+                p.data = view
+            for name, b in self.net.named_buffers():
+                if name in eng.b_off:
+                    view = eng.buffer_view(name)
+                    view.copy_(b.detach().to(view.dtype))
+                    mod, attr = name.rsplit(".", 1)
+                    self.net.get_submodule(mod)._buffers[attr] = view
+
+    def bump_batches_tracked(self):
+        if self.nbt:
+            torch._foreach_add_(self.nbt, 1)              # nn.BatchNorm2d.num_batches_tracked += 1
+
+
+def accelerate(net):
+    """Replace net.forward with the B200 plan. Call after `net.to('cuda')`; returns the same object."""
+    if not next(net.parameters()).is_cuda:
+        raise RuntimeError("accelerate(net): move the network to a CUDA device first (there is no CPU path)")
+    spec = spec_from_module(net)
+    state = _State(net, spec)
+
+    def forward(x):
+        if x.dim() != 4 or tuple(x.shape[1:]) != (3, 32, 32):
+            raise ValueError(f"accelerate: expected [N,3,32,32] input, got {tuple(x.shape)}")
+        if torch.is_grad_enabled() and net.training:
+            return _PlanFn.apply(state, x, *state.params)
+        with torch.no_grad():
+            return _PlanFn.forward(_Ctx(), state, x)
+    net.forward = forward
+    net._b2c_state = state
+    return net
+
+
+class _Ctx:
+    """Stand-in ctx for the no-grad path."""
+    pass
+
+
+class FusedSGD(torch.optim.Optimizer):
+    """optim.SGD(params, lr, momentum, weight_decay) (main.py:87-88) as ONE kernel over the parameter arena of an
+    accelerated network. Same constructor arguments and param_groups (so lr schedulers work); dampening 0, no
+    Nesterov, as the reference uses it."""
+
+    def __init__(self, net, lr=0.1, momentum=0.9, weight_decay=5e-4):
+        state = getattr(net, "_b2c_state", None)
+        if state is None:
+            raise ValueError("FusedSGD needs a network returned by accelerate()")
+        super().__init__(list(net.parameters()), dict(lr=lr, momentum=momentum, weight_decay=weight_decay))
+        self._state = state
+        self._hyper = None
+        self._steps = 0
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        eng = self._state.base
+        if eng is None:
+            raise RuntimeError("FusedSGD.step() before the first forward/backward")
+        g = self.param_groups[0]
+        vals = [g["lr"], g["momentum"], g["weight_decay"], 1.0, 1.0 if self._steps == 0 else 0.0]
+        if self._hyper is None:
+            self._hyper = torch.tensor(vals, dtype=torch.float32, device=eng.device)
+        else:
+            self._hyper.copy_(torch.tensor(vals, dtype=torch.float32), non_blocking=True)
+        ops.sgd_step(eng.P, eng.G, eng.M, self._hyper)
+        self._steps += 1
+
+    def zero_grad(self, set_to_none=True):
+        super().zero_grad(set_to_none=set_to_none)

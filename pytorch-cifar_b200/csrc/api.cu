@@ -385,22 +385,23 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
 }
 
 int b2c_bn_finalize(const float* part_sum, const float* part_sq, int rows, int channels, float count,
-                    const float* gamma, const float* beta, float eps, float momentum, float* running_mean,
-                    float* running_var, float* scale, float* shift, float* save_mean, float* save_rstd,
-                    void* stream) {
+                    const float* gamma, const float* beta, const float* conv_bias, float eps, float momentum,
+                    float* running_mean, float* running_var, float* scale, float* shift, float* save_mean,
+                    float* save_rstd, void* stream) {
     if (!part_sum || !part_sq || !gamma || !beta || !scale || !shift || !save_mean || !save_rstd || rows < 1 ||
         channels < 1 || count <= 0.f)
         return B2C_ERR_ARG;
     if ((running_mean == nullptr) != (running_var == nullptr)) return B2C_ERR_ARG;
-    return cuda_rc(b2c::launch_bn_finalize(part_sum, part_sq, rows, channels, count, gamma, beta, eps, momentum,
+    return cuda_rc(b2c::launch_bn_finalize(part_sum, part_sq, rows, channels, count, gamma, beta, conv_bias, eps, momentum,
                                            running_mean, running_var, scale, shift, save_mean, save_rstd,
                                            as_stream(stream)));
 }
 
-int b2c_bn_eval_scale_shift(int channels, const float* gamma, const float* beta, const float* running_mean,
-                            const float* running_var, float eps, float* scale, float* shift, void* stream) {
+int b2c_bn_eval_scale_shift(int channels, const float* gamma, const float* beta, const float* conv_bias,
+                            const float* running_mean, const float* running_var, float eps, float* scale,
+                            float* shift, void* stream) {
     if (!gamma || !beta || !running_mean || !running_var || !scale || !shift || channels < 1) return B2C_ERR_ARG;
-    return cuda_rc(b2c::launch_bn_eval_scale_shift(channels, gamma, beta, running_mean, running_var, eps, scale,
+    return cuda_rc(b2c::launch_bn_eval_scale_shift(channels, gamma, beta, conv_bias, running_mean, running_var, eps, scale,
                                                    shift, as_stream(stream)));
 }
 

@@ -17,10 +17,11 @@ struct RepackEntry {
 };
 
 cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int rows, int C, float count,
-                               const float* gamma, const float* beta, float eps, float momentum,
-                               float* running_mean, float* running_var, float* scale, float* shift, float* mean,
-                               float* rstd, cudaStream_t s);
-cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* beta, const float* rm,
+                               const float* gamma, const float* beta, const float* conv_bias, float eps,
+                               float momentum, float* running_mean, float* running_var, float* scale, float* shift,
+                               float* mean, float* rstd, cudaStream_t s);
+cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* beta, const float* conv_bias,
+                                       const float* rm,
                                        const float* rv, float eps, float* scale, float* shift, cudaStream_t s);
 cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
                                 const float* res_scale, const float* res_shift, void* out, long long rows, int C,

@@ -35,7 +35,8 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
 // ------------------------------------------------------------------------------------------------
 __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const float* __restrict__ part_sq, int rows,
                                    int C, float count, const float* __restrict__ gamma,
-                                   const float* __restrict__ beta, float eps, float momentum,
+                                   const float* __restrict__ beta, const float* __restrict__ conv_bias, float eps,
+                                   float momentum,
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
                                    float* __restrict__ scale, float* __restrict__ shift,
                                    float* __restrict__ mean_out, float* __restrict__ rstd_out) {
@@ -66,7 +67,8 @@ __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const flo
         rstd_out[warp] = rstd;
         if (running_mean != nullptr) {
             const double unbiased = n > 1.0 ? var * n / (n - 1.0) : var;
-            running_mean[warp] = (1.f - momentum) * running_mean[warp] + momentum * static_cast<float>(mean);
+            const float bias = conv_bias != nullptr ? conv_bias[warp] : 0.f;   // reference tracks mean(conv + bias)
+            running_mean[warp] = (1.f - momentum) * running_mean[warp] + momentum * (static_cast<float>(mean) + bias);
             running_var[warp] = (1.f - momentum) * running_var[warp] + momentum * static_cast<float>(unbiased);
         }
     }
@@ -74,6 +76,7 @@ __global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const flo
 
 // Eval-mode BatchNorm: fold the running statistics into scale / shift (main.py:116-134 `net.eval()`).
 __global__ void bn_eval_scale_shift_kernel(int C, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                           const float* __restrict__ conv_bias,
                                            const float* __restrict__ running_mean,
                                            const float* __restrict__ running_var, float eps,
                                            float* __restrict__ scale, float* __restrict__ shift) {
@@ -81,7 +84,8 @@ __global__ void bn_eval_scale_shift_kernel(int C, const float* __restrict__ gamm
     if (c >= C) return;
     const float sc = gamma[c] / sqrtf(running_var[c] + eps);
     scale[c] = sc;
-    shift[c] = beta[c] - running_mean[c] * sc;
+    const float bias = conv_bias != nullptr ? conv_bias[c] : 0.f;
+    shift[c] = beta[c] - (running_mean[c] - bias) * sc;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -645,19 +649,20 @@ inline int grid_for(long long work_items, int block, int max_blocks) {
 
 // ---------------------------------------- launchers ---------------------------------------------
 cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int rows, int C, float count,
-                               const float* gamma, const float* beta, float eps, float momentum,
-                               float* running_mean, float* running_var, float* scale, float* shift, float* mean,
-                               float* rstd, cudaStream_t s) {
+                               const float* gamma, const float* beta, const float* conv_bias, float eps,
+                               float momentum, float* running_mean, float* running_var, float* scale, float* shift,
+                               float* mean, float* rstd, cudaStream_t s) {
     const int threads = 128;
     const int blocks = (C * 32 + threads - 1) / threads;
-    bn_finalize_kernel<<<blocks, threads, 0, s>>>(part_sum, part_sq, rows, C, count, gamma, beta, eps, momentum,
+    bn_finalize_kernel<<<blocks, threads, 0, s>>>(part_sum, part_sq, rows, C, count, gamma, beta, conv_bias, eps, momentum,
                                                   running_mean, running_var, scale, shift, mean, rstd);
     return cudaGetLastError();
 }
 
-cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* beta, const float* rm,
-                                       const float* rv, float eps, float* scale, float* shift, cudaStream_t s) {
-    bn_eval_scale_shift_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, gamma, beta, rm, rv, eps, scale, shift);
+cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* beta, const float* conv_bias,
+                                       const float* rm, const float* rv, float eps, float* scale, float* shift,
+                                       cudaStream_t s) {
+    bn_eval_scale_shift_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, gamma, beta, conv_bias, rm, rv, eps, scale, shift);
     return cudaGetLastError();
 }
 

@@ -214,6 +214,8 @@ class ConvUnit:
             self.rm = eng.buffer_view(bn_name + ".running_mean")
             self.rv = eng.buffer_view(bn_name + ".running_var")
             self.scale, self.shift, self.mean, self.rstd = (eng.new_f32(cout) for _ in range(4))
+        # a conv bias (VGG) is never added to y — the BatchNorm cancels it — but the running mean tracks it
+        self.conv_bias = eng.param_view(name + ".bias") if (name + ".bias") in eng.p_off else None
 
     # ---- forward pieces
     def fprop(self, eng, stats=True, add_src=None):
@@ -223,10 +225,11 @@ class ConvUnit:
     def bn_stats(self, eng, training):
         if training:
             ops.bn_finalize(eng.part_sum, eng.part_sq, self.stat_rows, self.cout, self.rows, self.gamma, self.beta,
-                            BN_EPS, BN_MOMENTUM, self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd)
+                            BN_EPS, BN_MOMENTUM, self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd,
+                            conv_bias=getattr(self, "conv_bias", None))
         else:
             ops.bn_eval_scale_shift(self.cout, self.gamma, self.beta, self.rm, self.rv, BN_EPS, self.scale,
-                                    self.shift)
+                                    self.shift, conv_bias=getattr(self, "conv_bias", None))
 
     # ---- backward pieces
     def bn_backward(self, eng, dout, act, dz_out, dy, add=None):

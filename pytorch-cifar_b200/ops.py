@@ -72,16 +72,17 @@ def conv_wgrad(d, x, dy, dw):
 
 
 def bn_finalize(part_sum, part_sq, rows, channels, count, gamma, beta, eps, momentum, running_mean, running_var,
-                scale, shift, save_mean, save_rstd):
+                scale, shift, save_mean, save_rstd, conv_bias=None):
     lib = _lib.load()
     check(lib.b2c_bn_finalize(_p(part_sum), _p(part_sq), rows, channels, float(count), _p(gamma), _p(beta),
-                              float(eps), float(momentum), _p(running_mean), _p(running_var), _p(scale), _p(shift),
+                              _p(conv_bias), float(eps), float(momentum), _p(running_mean), _p(running_var), _p(scale), _p(shift),
                               _p(save_mean), _p(save_rstd), _stream()), "b2c_bn_finalize")
 
 
-def bn_eval_scale_shift(channels, gamma, beta, running_mean, running_var, eps, scale, shift):
+def bn_eval_scale_shift(channels, gamma, beta, running_mean, running_var, eps, scale, shift, conv_bias=None):
     lib = _lib.load()
-    check(lib.b2c_bn_eval_scale_shift(channels, _p(gamma), _p(beta), _p(running_mean), _p(running_var), float(eps),
+    check(lib.b2c_bn_eval_scale_shift(channels, _p(gamma), _p(beta), _p(conv_bias), _p(running_mean), _p(running_var),
+                                      float(eps),
                                       _p(scale), _p(shift), _stream()), "b2c_bn_eval_scale_shift")
 
 

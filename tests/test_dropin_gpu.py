@@ -1,0 +1,112 @@
+"""GPU test of the drop-in surface (pytorch-cifar_b200/accelerate.py): the reference's module trees keep their
+nn.Module / autograd / optimizer / state_dict behaviour while the B200 plan runs underneath.
+Replays the body of train() and test() from the reference (main.py:99-105,116-134) on module trees that are
+pinned to the reference's (oracle/ref_modules.py, tests/test_oracle.py)."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def make(family):
+    from oracle import ref_modules
+    torch.manual_seed(0)
+    return {"resnet18": ref_modules.ResNet18, "vgg16": lambda: ref_modules.VGG("VGG16"),
+            "preact18": ref_modules.PreActResNet18}[family]().cuda()
+
+
+def batch(n, seed):
+    rs = np.random.RandomState(seed)
+    x = torch.from_numpy(rs.standard_normal((n, 3, 32, 32)).astype(np.float32)).cuda()
+    t = torch.from_numpy(rs.randint(0, 10, size=(n,)).astype(np.int64)).cuda()
+    return x, t
+
+
+@pytest.mark.parametrize("family", ["resnet18", "vgg16", "preact18"])
+def test_train_eval_checkpoint_roundtrip(family):
+    import b200cifar
+    from b200cifar.accelerate import accelerate
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ref = make(family)
+    net = copy.deepcopy(ref)
+    keys_before = list(net.state_dict().keys())
+    assert accelerate(net) is net
+    assert list(net.state_dict().keys()) == keys_before
+    x, t = batch(128, 5)
+    crit = nn.CrossEntropyLoss()                                                 # main.py:86
+    opt = torch.optim.SGD(net.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)        # main.py:87-88
+    opt_ref = torch.optim.SGD(ref.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)
+    losses, losses_ref = [], []
+    net.train(); ref.train()
+    for _ in range(4):                                                           # main.py:99-107
+        opt.zero_grad()
+        out = net(x)
+        loss = crit(out, t)
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+        _, pred = out.max(1)                                                     # main.py:108
+        assert pred.shape == (128,)
+        opt_ref.zero_grad()
+        l2 = crit(ref(x), t)
+        l2.backward()
+        opt_ref.step()
+        losses_ref.append(l2.item())
+    assert abs(losses[0] - losses_ref[0]) < 3e-2
+    assert losses[-1] < losses[0] and abs(losses[-1] - losses_ref[-1]) < 0.2 * losses_ref[0]
+    nbt = [b for n, b in net.named_buffers() if n.endswith("num_batches_tracked")]
+    assert all(int(b) == 4 for b in nbt)
+    assert all(p.grad is not None and p.grad.shape == p.shape for p in net.parameters())
+    # test() of the reference: eval mode, no_grad, batch 100 (main.py:116-126) — a second plan, same arenas
+    net.eval()
+    xe, _ = batch(100, 6)
+    with torch.no_grad():
+        oe = net(xe)
+    # checkpoint round trip (main.py:138-147, 77-84): our state_dict into a plain fp32 module and back
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    plain = make(family)
+    plain.load_state_dict(sd)
+    plain.eval()
+    with torch.no_grad():
+        op = plain(xe)
+    assert rel(oe, op) < 6e-2 and (oe.argmax(1) == op.argmax(1)).float().mean().item() > 0.9
+    net.load_state_dict(ref.state_dict())                                        # a reference-trained checkpoint
+    ref.eval()
+    with torch.no_grad():
+        assert rel(net(xe), ref(xe)) < 6e-2
+
+
+def test_fused_sgd_matches_torch_sgd():
+    import b200cifar
+    from b200cifar.accelerate import FusedSGD, accelerate
+    a, b = accelerate(make("resnet18")), accelerate(make("resnet18"))
+    x, t = batch(64, 7)
+    oa = torch.optim.SGD(a.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+    ob = FusedSGD(b, lr=0.05, momentum=0.9, weight_decay=5e-4)
+    crit = nn.CrossEntropyLoss()
+    # wgrad combines split-K partials with fp32 atomics, so two runs agree to round-off, not bitwise; after the
+    # second step that round-off has been through a bf16 forward pass, hence the looser bound there
+    for step, tol in ((0, 2e-6), (1, 5e-3)):
+        for net, opt in ((a, oa), (b, ob)):
+            opt.zero_grad()
+            crit(net(x), t).backward()
+            opt.step()
+        for (n1, p1), (_, p2) in zip(a.named_parameters(), b.named_parameters()):
+            assert (p1 - p2).abs().max().item() < tol * max(1.0, p1.abs().max().item()), (step, n1)
+
+
+def test_unsupported_module_is_an_error():
+    import b200cifar
+    from b200cifar.accelerate import accelerate
+    with pytest.raises(NotImplementedError):
+        accelerate(nn.Sequential(nn.Conv2d(3, 8, 3), nn.ReLU()).cuda())
