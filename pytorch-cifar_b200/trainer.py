@@ -163,6 +163,39 @@ class Trainer:
         self._run()
         return self.loss
 
+    # ------------------------------------------------------------------ evaluation (test(), main.py:116-134)
+    def evaluate(self, images_u8, labels, batch=100):
+        """Top-1 accuracy and mean loss over a host uint8 set with transform_test (ToTensor + Normalize only,
+        main.py:37-40), BatchNorm in eval mode (running statistics), batches of `batch` like the reference's
+        testloader (main.py:49-50). Runs on a second plan that shares this trainer's parameter arenas."""
+        images_u8 = np.ascontiguousarray(images_u8)
+        labels = np.asarray(labels, dtype=np.int64)
+        n = len(labels)
+        correct, loss_sum = 0, 0.0
+        for s in range(0, n, batch):
+            b = min(batch, n - s)
+            ev = self._eval_plans.get(b) if hasattr(self, "_eval_plans") else None
+            if ev is None:
+                if not hasattr(self, "_eval_plans"):
+                    self._eval_plans = {}
+                eng = Engine(self.eng.spec, b, self.device, share_from=self.eng)
+                ev = dict(eng=eng, data=torch.zeros(b, 32, 32, 3, dtype=torch.uint8, device=self.device),
+                          idx=torch.arange(b, device=self.device),
+                          ijf=torch.tensor([[4, 4, 0]] * b, dtype=torch.int8, device=self.device),  # identity crop
+                          tgt=torch.zeros(b, dtype=torch.int64, device=self.device),
+                          loss=torch.zeros(1, device=self.device),
+                          correct=torch.zeros(1, dtype=torch.int32, device=self.device))
+                self._eval_plans[b] = ev
+            eng = ev["eng"]
+            ev["data"].copy_(torch.from_numpy(images_u8[s:s + b]))
+            ev["tgt"].copy_(torch.from_numpy(labels[s:s + b]))
+            ops.augment_im2col(ev["data"], ev["idx"], ev["ijf"], eng.x0)
+            eng.forward(False)
+            ops.ce_loss(eng.logits, ev["tgt"], b, self.K, eng.dlogits, ev["loss"], ev["correct"])
+            correct += int(ev["correct"].item())
+            loss_sum += float(ev["loss"].item()) * b
+        return correct / n, loss_sum / n
+
     def read_loss(self):
         """Device -> host read of the last step's loss (the reference's loss.item(), main.py:107)."""
         self._loss_host.copy_(self.loss, non_blocking=False)
