@@ -46,6 +46,7 @@ typedef struct B2cConvDesc {
     int ksize;       /* 1 or 3 */
     int stride;      /* 1 or 2 */
     int cin_valid;   /* wgrad only: real input channels (<= cin); 0 means cin */
+    int cout_valid;  /* wgrad only: real output channels (<= cout); 0 means cout */
     int kflat_cin;   /* wgrad only: >0 for the im2col'ed stem, whose `cin` axis is k = tap*kflat_cin + c */
     int block_n;     /* GEMM N tile (64/128/256); 0 = choose */
     int max_ctas;    /* persistent grid cap; 0 = 148 (one CTA per SM) */
@@ -68,10 +69,23 @@ B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fp
 B2C_API int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
                    void* stream);
 
-/* dw[cout,cin_valid,k,k] (fp32, OIHW = the reference's .grad layout) += sum over pixels of x * dy.
+/* dw[cout_valid,cin_valid,k,k] (fp32, OIHW = the reference's .grad layout) += sum over pixels of x * dy.
  * Replaces cudnn_convolution_backward_weight, main.py:104. Accumulates with fp32 atomics: the caller
  * zero-fills dw (optimizer.zero_grad(), main.py:101). */
 B2C_API int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, void* stream);
+
+/* Depthwise 3x3 convolution, nn.Conv2d(C, C, 3, stride, padding=1, groups=C, bias=False), models/mobilenetv2.py:20,
+ * and its two gradients (main.py:104). x [n,h,w,channels] bf16, weight = the fp32 master tensor [c_valid,1,3,3];
+ * channels is the padded layout width (multiple of 8), channels >= c_valid are treated as zero weights.
+ * fprop optionally writes BatchNorm partial sums like b2c_conv_fprop, one row per block:
+ * b2c_dwconv_stat_rows(out_pixels, channels) rows (<= 592). wgrad accumulates with fp32 atomics into dw. */
+B2C_API int b2c_dwconv_stat_rows(long long out_pixels, int channels);
+B2C_API int b2c_dwconv_fprop(const void* x, const float* weight, void* y, int n, int h, int w, int channels, int c_valid,
+                     int stride, float* part_sum, float* part_sq, int* stat_rows, void* stream);
+B2C_API int b2c_dwconv_dgrad(const void* dy, const float* weight, void* dx, int n, int h, int w, int channels, int c_valid,
+                     int stride, void* stream);
+B2C_API int b2c_dwconv_wgrad(const void* x, const void* dy, float* dweight, int n, int h, int w, int channels, int c_valid,
+                     int stride, void* stream);
 
 /* Training-mode BatchNorm statistics -> per-channel scale/shift, saved mean/rstd, running-stat update.
  * Replaces the statistics half of F.batch_norm for nn.BatchNorm2d, models/resnet.py:25,28,35,104.
@@ -180,7 +194,7 @@ typedef struct B2cRepackEntry {
     long long wd_off;  /* element offset of the dgrad operand [tap][cin][cout]; <0: none */
     int cout, cin, taps, cin_pad;
     int kflat;         /* stem: fprop operand is [cout][cin_pad], k = tap*cin + c */
-    int pad_;
+    int pad_;          /* cout_pad: rows per tap of the fprop operand / row pitch of the dgrad operand; 0 = cout */
 } B2cRepackEntry;
 
 /* fp32 OIHW master weights (the reference's state_dict layout) -> bf16 GEMM operands, all convs in

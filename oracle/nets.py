@@ -220,3 +220,85 @@ def preact_forward(x, params, buffers, training=True, num_blocks=RESNET18_BLOCKS
     out = F.avg_pool2d(out, 4)                                                      # :91
     out = out.view(out.size(0), -1)
     return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
+# MobileNetV2 (models/mobilenetv2.py) — BASELINE config 5
+# ------------------------------------------------------------------------------------------------
+MOBILENETV2_CFG = [(1, 16, 1, 1), (6, 24, 2, 1), (6, 32, 3, 2), (6, 64, 4, 2), (6, 96, 3, 1), (6, 160, 3, 2),
+                   (6, 320, 1, 1)]        # mobilenetv2.py:42-48
+
+
+def _mbv2_blocks():
+    cin, i = 32, 0
+    for expansion, cout, nb, stride in MOBILENETV2_CFG:
+        for s in [stride] + [1] * (nb - 1):
+            yield f"layers.{i}", cin, cout, expansion * cin, s
+            cin = cout
+            i += 1
+
+
+def build_mobilenetv2_params(seed):
+    """Construction order of MobileNetV2.__init__ / Block.__init__ (mobilenetv2.py:13-30,50-58)."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride, groups=1):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, groups=groups, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 32, 3, 1)                                   # :52
+    bn("bn1", 32)
+    for name, cin, cout, planes, s in _mbv2_blocks():
+        conv(name + ".conv1", cin, planes, 1, 1)                 # :18
+        bn(name + ".bn1", planes)
+        conv(name + ".conv2", planes, planes, 3, s, groups=planes)   # :20 depthwise
+        bn(name + ".bn2", planes)
+        conv(name + ".conv3", planes, cout, 1, 1)                # :22
+        bn(name + ".bn3", cout)
+        if s == 1 and cin != cout:                               # :26-30
+            conv(name + ".shortcut.0", cin, cout, 1, 1)
+            bn(name + ".shortcut.1", cout)
+    conv("conv2", 320, 1280, 1, 1)                               # :55
+    bn("bn2", 1280)
+    lin = nn.Linear(1280, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def mobilenetv2_forward(x, params, buffers, training=True, taps=None):
+    out = F.conv2d(x, params["conv1.weight"], padding=1)
+    if taps is not None:
+        taps["conv1"] = out
+    out = F.relu(_bn(out, "bn1", params, buffers, training))                                   # :70
+    for name, cin, cout, planes, s in _mbv2_blocks():
+        xin = out
+        o = F.conv2d(xin, params[name + ".conv1.weight"])
+        if taps is not None:
+            taps[name + ".conv1"] = o
+        o = F.relu(_bn(o, name + ".bn1", params, buffers, training))                           # :33
+        o = F.conv2d(o, params[name + ".conv2.weight"], stride=s, padding=1, groups=planes)
+        if taps is not None:
+            taps[name + ".conv2"] = o
+        o = F.relu(_bn(o, name + ".bn2", params, buffers, training))                           # :34
+        o = _bn(F.conv2d(o, params[name + ".conv3.weight"]), name + ".bn3", params, buffers, training)   # :35
+        if s == 1:                                                                             # :36
+            if (name + ".shortcut.0.weight") in params:
+                sc = _bn(F.conv2d(xin, params[name + ".shortcut.0.weight"]), name + ".shortcut.1", params, buffers,
+                         training)
+            else:
+                sc = xin
+            o = o + sc
+        out = o
+    out = F.relu(_bn(F.conv2d(out, params["conv2.weight"]), "bn2", params, buffers, training)) # :72
+    out = F.avg_pool2d(out, 4).view(out.size(0), -1)                                           # :74-75
+    return F.linear(out, params["linear.weight"], params["linear.bias"])

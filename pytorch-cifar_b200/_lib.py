@@ -27,7 +27,7 @@ class B2cError(RuntimeError):
 class ConvDesc(ctypes.Structure):
     """Mirror of B2cConvDesc (include/b2c.h)."""
     _fields_ = [(n, ctypes.c_int) for n in
-                ("n", "h", "w", "cin", "cout", "ksize", "stride", "cin_valid", "kflat_cin", "block_n", "max_ctas",
+                ("n", "h", "w", "cin", "cout", "ksize", "stride", "cin_valid", "cout_valid", "kflat_cin", "block_n", "max_ctas",
                  "flags")]
 
 
@@ -60,6 +60,10 @@ SIGNATURES = {
     "b2c_conv_fprop": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, ctypes.POINTER(_I), _P],
     "b2c_conv_dgrad": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P],
     "b2c_conv_wgrad": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P],
+    "b2c_dwconv_stat_rows": [_LL, _I],
+    "b2c_dwconv_fprop": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, ctypes.POINTER(_I), _P],
+    "b2c_dwconv_dgrad": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
+    "b2c_dwconv_wgrad": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
     "b2c_bn_finalize": [_P, _P, _I, _I, _F, _P, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P],
     "b2c_bn_eval_scale_shift": [_I, _P, _P, _P, _P, _P, _F, _P, _P, _P],
     "b2c_bn_act_apply": [_P, _P, _P, _P, _P, _P, _P, _LL, _I, _I, _P],
@@ -94,7 +98,7 @@ class _LibProxy:
 
     def __getattr__(self, name):
         fn = getattr(self._cdll, name)
-        if name in ("b2c_error_string", "b2c_version", "b2c_bn_bwd_partial_rows"):
+        if name in ("b2c_error_string", "b2c_version", "b2c_bn_bwd_partial_rows", "b2c_dwconv_stat_rows"):
             return fn
 
         def call(*args):

@@ -331,7 +331,8 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
     const int taps = d->ksize * d->ksize;
     const int cin_valid = d->cin_valid > 0 ? d->cin_valid : d->cin;
-    if (cin_valid > d->cin) return B2C_ERR_ARG;
+    const int cout_valid = d->cout_valid > 0 ? d->cout_valid : d->cout;
+    if (cin_valid > d->cin || cout_valid > d->cout) return B2C_ERR_ARG;
     if (d->kflat_cin > 0 && (taps != 1 || (cin_valid % d->kflat_cin) != 0)) return B2C_ERR_ARG;
 
     WgradParams p = {};
@@ -360,6 +361,7 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
     p.cin = d->cin;
     p.cout = d->cout;
     p.cin_valid = cin_valid;
+    p.cout_valid = cout_valid;
     p.kflat_cin = d->kflat_cin;
     p.dw = dw;
     if (d->kflat_cin > 0) {
@@ -382,6 +384,45 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
     rc = encode_nhwc(&mdy, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
     if (rc) return rc;
     return cuda_rc(b2c::launch_wgrad(bn, mx, mdy, p, as_stream(stream)));
+}
+
+static int check_dw(const void* a, const void* b, const void* c, int n, int h, int w, int channels, int c_valid,
+                    int stride) {
+    if (!a || !b || !c || n < 1 || h < 1 || w < 1) return B2C_ERR_ARG;
+    if (channels < 8 || (channels & 7) || (channels >> 3) > 256 || c_valid < 1 || c_valid > channels)
+        return B2C_ERR_UNSUPPORTED;
+    if ((stride != 1 && stride != 2) || (stride == 2 && ((h | w) & 1))) return B2C_ERR_UNSUPPORTED;
+    return 0;
+}
+
+int b2c_dwconv_stat_rows(long long out_pixels, int channels) {
+    if (channels < 8 || (channels & 7) || (channels >> 3) > 256 || out_pixels < 1) return B2C_ERR_UNSUPPORTED;
+    return b2c::dw_fprop_partial_rows(out_pixels, channels);
+}
+
+int b2c_dwconv_fprop(const void* x, const float* weight, void* y, int n, int h, int w, int channels, int c_valid,
+                     int stride, float* part_sum, float* part_sq, int* stat_rows, void* stream) {
+    int rc = check_dw(x, weight, y, n, h, w, channels, c_valid, stride);
+    if (rc) return rc;
+    if (!aligned16(x) || !aligned16(y) || (part_sum == nullptr) != (part_sq == nullptr)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_dw_fprop(x, weight, y, n, h, w, channels, c_valid, stride, part_sum, part_sq, stat_rows,
+                                        as_stream(stream)));
+}
+
+int b2c_dwconv_dgrad(const void* dy, const float* weight, void* dx, int n, int h, int w, int channels, int c_valid,
+                     int stride, void* stream) {
+    int rc = check_dw(dy, weight, dx, n, h, w, channels, c_valid, stride);
+    if (rc) return rc;
+    if (!aligned16(dy) || !aligned16(dx)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_dw_dgrad(dy, weight, dx, n, h, w, channels, c_valid, stride, as_stream(stream)));
+}
+
+int b2c_dwconv_wgrad(const void* x, const void* dy, float* dweight, int n, int h, int w, int channels, int c_valid,
+                     int stride, void* stream) {
+    int rc = check_dw(x, dy, dweight, n, h, w, channels, c_valid, stride);
+    if (rc) return rc;
+    if (!aligned16(x) || !aligned16(dy)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_dw_wgrad(x, dy, dweight, n, h, w, channels, c_valid, stride, as_stream(stream)));
 }
 
 int b2c_bn_finalize(const float* part_sum, const float* part_sq, int rows, int channels, float count,
@@ -419,15 +460,14 @@ int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, cons
 }
 
 int b2c_bn_bwd_partial_rows(long long rows, int channels) {
-    if (channels < 8 || (channels & 7) || (256 % (channels >> 3)) != 0) return B2C_ERR_UNSUPPORTED;
+    if (channels < 8 || (channels & 7) || (channels >> 3) > 256) return B2C_ERR_UNSUPPORTED;
     return b2c::bn_bwd_partial_rows(rows, channels);
 }
 
 int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
                       int channels, float* partial, void* stream) {
     if (!dout || !y || !partial || rows < 1) return B2C_ERR_ARG;
-    if (channels < 8 || (channels & 7) || (channels >> 3) > 256 || (256 % (channels >> 3)) != 0)
-        return B2C_ERR_UNSUPPORTED;
+    if (channels < 8 || (channels & 7) || (channels >> 3) > 256) return B2C_ERR_UNSUPPORTED;
     if (!aligned16(dout) || !aligned16(act) || !aligned16(y) || !aligned16(dz_out)) return B2C_ERR_ARG;
     return cuda_rc(b2c::launch_bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, as_stream(stream)));
 }
@@ -451,7 +491,7 @@ int b2c_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, v
         rows < 1 || count <= 0.f)
         return B2C_ERR_ARG;
     if (channels > b2c::bn_bwd_noalloc_max_channels()) return B2C_ERR_TOO_LARGE;
-    if (channels < 8 || (channels & 7) || (256 % (channels >> 3)) != 0) return B2C_ERR_UNSUPPORTED;
+    if (channels < 8 || (channels & 7)) return B2C_ERR_UNSUPPORTED;
     if (!aligned16(dout) || !aligned16(act) || !aligned16(y) || !aligned16(dz_out)) return B2C_ERR_ARG;
     return cuda_rc(b2c::launch_bn_bwd_stats_noalloc(dout, act, y, dz_out, rows, channels, count, gamma, save_mean,
                                                     save_rstd, dgamma, dbeta, coef_a, coef_b, coef_c,
@@ -486,7 +526,7 @@ int b2c_maxpool2x2_bwd(const void* x, const void* y, const void* dy, void* dx, i
 int b2c_head_fwd(const void* act, int n, int hw, int channels, const float* weight, const float* bias,
                  int classes, float* pooled, float* logits, void* stream) {
     if (!act || !weight || !bias || !pooled || !logits || n < 1 || hw < 1 || classes < 1) return B2C_ERR_ARG;
-    if (channels > 1024 || (channels & 31)) return B2C_ERR_UNSUPPORTED;
+    if (channels > 4096 || (channels & 31)) return B2C_ERR_UNSUPPORTED;
     return cuda_rc(b2c::launch_head_fwd(act, n, hw, channels, weight, bias, classes, pooled, logits,
                                         as_stream(stream)));
 }
@@ -501,7 +541,7 @@ int b2c_head_bwd(const float* dlogits, const float* pooled, const float* weight,
                  int classes, void* dact, float* dweight, float* dbias, void* stream) {
     if (!dlogits || !pooled || !weight || !dact || !dweight || !dbias || n < 1 || hw < 1 || classes < 1)
         return B2C_ERR_ARG;
-    if (channels > 1024 || (channels & 31)) return B2C_ERR_UNSUPPORTED;
+    if (channels > 4096 || (channels & 31)) return B2C_ERR_UNSUPPORTED;
     return cuda_rc(b2c::launch_head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, dbias,
                                         as_stream(stream)));
 }

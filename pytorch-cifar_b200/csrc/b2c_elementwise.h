@@ -13,7 +13,7 @@ struct RepackEntry {
     long long wd_off;   // element offset of the dgrad operand [tap][cin][cout]; < 0: none
     int cout, cin, taps, cin_pad;
     int kflat;          // stem: fprop operand is [cout][cin_pad] with k = tap*cin + c
-    int pad_;
+    int pad_;           // cout_pad (0: cout)
 };
 
 cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int rows, int C, float count,
@@ -51,6 +51,13 @@ cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s)
 cudaError_t launch_sgd(float* p, const float* g, float* buf, long long n, const float* hyper, cudaStream_t s);
 cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackEntry* table_dev, int entries,
                           cudaStream_t s);
+int dw_fprop_partial_rows(long long out_pixels, int C);
+cudaError_t launch_dw_fprop(const void* x, const float* w, void* y, int N, int H, int W, int C, int c_valid, int stride,
+                            float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s);
+cudaError_t launch_dw_dgrad(const void* dy, const float* w, void* dx, int N, int H, int W, int C, int c_valid,
+                            int stride, cudaStream_t s);
+cudaError_t launch_dw_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int c_valid,
+                            int stride, cudaStream_t s);
 int bn_bwd_noalloc_max_channels();
 cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, void* dz_out,
                                         long long rows, int C, float count, const float* gamma, const float* mean,

@@ -51,6 +51,7 @@ struct WgradParams {
     int num_taps;
     int cin, cout;
     int cin_valid;        // real input channels (stem: 27 of 64)
+    int cout_valid;       // real output channels (channel-padded layouts)
     int kflat_cin;        // >0: the cin axis is k = tap*kflat_cin + c (im2col'ed stem); address from (c, tap)
     float* dw;            // fp32 gradient, element (o, c, t) at o*o_stride + c*c_stride + t*t_stride
     long long o_stride, c_stride, t_stride;

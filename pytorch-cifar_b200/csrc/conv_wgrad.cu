@@ -176,7 +176,8 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
             if (valid) {
 #pragma unroll
                 for (int e = 0; e < 32; ++e) {
-                    atomicAdd(base + static_cast<long long>(c * 32 + e) * p.o_stride, v[e]);
+                    if (n_tile * BN + c * 32 + e < p.cout_valid)
+                        atomicAdd(base + static_cast<long long>(c * 32 + e) * p.o_stride, v[e]);
                 }
             }
         }

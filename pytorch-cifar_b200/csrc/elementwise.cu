@@ -147,13 +147,14 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ a
                      uint4* __restrict__ dz_out, long long rows, int C, float* __restrict__ partial) {
     extern __shared__ float red[];  // [rows_per_iter][2][C]
     const int cvec = C >> 3;
-    const int rpi = 256 / cvec;     // rows handled per block iteration (cvec <= 256, divides 256)
+    const int rpi = 256 / cvec;     // rows handled per block iteration (cvec <= 256); threads past rpi*cvec idle
     const int cv = threadIdx.x % cvec;
     const int rl = threadIdx.x / cvec;
+    const bool active = rl < rpi;
     float s1[8], s2[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) { s1[e] = 0.f; s2[e] = 0.f; }
-    for (long long r = static_cast<long long>(blockIdx.x) * rpi + rl; r < rows;
+    for (long long r = static_cast<long long>(blockIdx.x) * rpi + rl; active && r < rows;
          r += static_cast<long long>(gridDim.x) * rpi) {
         const long long v = r * cvec + cv;
         float d[8], yy[8];
@@ -173,10 +174,12 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ a
         }
     }
     // block reduce over the rl dimension
+    if (active) {
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-        red[(rl * 2 + 0) * C + cv * 8 + e] = s1[e];
-        red[(rl * 2 + 1) * C + cv * 8 + e] = s2[e];
+        for (int e = 0; e < 8; ++e) {
+            red[(rl * 2 + 0) * C + cv * 8 + e] = s1[e];
+            red[(rl * 2 + 1) * C + cv * 8 + e] = s2[e];
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < 2 * C; i += 256) {
@@ -325,13 +328,14 @@ __global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ act, int hw, i
                                 float* __restrict__ logits) {
     extern __shared__ float sp[];  // [C]
     const int n = blockIdx.x;
-    const int c = threadIdx.x;
-    float s = 0.f;
-    const __nv_bfloat16* a = act + static_cast<size_t>(n) * hw * C + c;
-    for (int i = 0; i < hw; ++i) s += __bfloat162float(a[static_cast<size_t>(i) * C]);
-    s *= 1.f / static_cast<float>(hw);
-    sp[c] = s;
-    pooled[static_cast<size_t>(n) * C + c] = s;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float s = 0.f;
+        const __nv_bfloat16* a = act + static_cast<size_t>(n) * hw * C + c;
+        for (int i = 0; i < hw; ++i) s += __bfloat162float(a[static_cast<size_t>(i) * C]);
+        s *= 1.f / static_cast<float>(hw);
+        sp[c] = s;
+        pooled[static_cast<size_t>(n) * C + c] = s;
+    }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
     for (int k = warp; k < K; k += nwarps) {
@@ -399,13 +403,15 @@ __global__ void ce_loss_kernel(const float* __restrict__ logits, const long long
 __global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const float* __restrict__ W, int K, int hw,
                                     int C, __nv_bfloat16* __restrict__ dact) {
     const int n = blockIdx.x;
-    const int c = threadIdx.x;
-    float g = 0.f;
-    for (int k = 0; k < K; ++k) g = fmaf(dlogits[static_cast<size_t>(n) * K + k], __ldg(W + static_cast<size_t>(k) * C + c), g);
-    g *= 1.f / static_cast<float>(hw);
-    const __nv_bfloat16 b = __float2bfloat16(g);
-    __nv_bfloat16* d = dact + static_cast<size_t>(n) * hw * C + c;
-    for (int i = 0; i < hw; ++i) d[static_cast<size_t>(i) * C] = b;
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float g = 0.f;
+        for (int k = 0; k < K; ++k)
+            g = fmaf(dlogits[static_cast<size_t>(n) * K + k], __ldg(W + static_cast<size_t>(k) * C + c), g);
+        g *= 1.f / static_cast<float>(hw);
+        const __nv_bfloat16 b = __float2bfloat16(g);
+        __nv_bfloat16* d = dact + static_cast<size_t>(n) * hw * C + c;
+        for (int i = 0; i < hw; ++i) d[static_cast<size_t>(i) * C] = b;
+    }
 }
 // Head backward, part 2: dW[k, c] = sum_n dlogits[n,k] * pooled[n,c]; db[k] = sum_n dlogits[n,k].
 // grid = (C/32, K); block = 32 channels x 8 batch lanes, smem tree over the lanes.
@@ -614,25 +620,28 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
         }
         return;
     }
-    const int ctiles = e.cin >> 5;
-    const int ntile = (e.cout >> 5) * ctiles;
+    const int cout_pad = e.pad_ > 0 ? e.pad_ : e.cout;      // pad_ carries cout_pad (0: no padding)
+    const int ctiles = (e.cin + 31) >> 5;
+    const int ntile = ((e.cout + 31) >> 5) * ctiles;
     for (int tidx = blockIdx.x; tidx < ntile; tidx += gridDim.x) {
         const int o0 = (tidx / ctiles) << 5, c0 = (tidx % ctiles) << 5;
-        const int w = 32 * taps;                                  // contiguous floats per cout row of the tile
+        const int no = min(32, e.cout - o0), nc = min(32, e.cin - c0);
+        const int w = nc * taps;                                  // contiguous floats per cout row of the tile
         __syncthreads();
-        for (int i = threadIdx.x; i < 32 * w; i += 256) {
+        for (int i = threadIdx.x; i < no * w; i += 256) {
             const int o = i / w, r = i - o * w;
             tile[o][r] = master[e.src_off + (static_cast<long long>(o0 + o) * e.cin + c0) * taps + r];
         }
         __syncthreads();
         for (int i = threadIdx.x; i < taps * 32 * 32; i += 256) {
             const int t = i >> 10, a = (i >> 5) & 31, b = i & 31;
-            // fprop operand [tap][cout][cin]: b runs over cin (contiguous)
-            wf[e.wf_off + (static_cast<long long>(t) * e.cout + o0 + a) * e.cin_pad + c0 + b] =
-                __float2bfloat16(tile[a][b * taps + t]);
-            // dgrad operand [tap][cin][cout]: b runs over cout (contiguous)
-            if (e.wd_off >= 0)
-                wd[e.wd_off + (static_cast<long long>(t) * e.cin + c0 + a) * e.cout + o0 + b] =
+            // fprop operand [tap][cout_pad][cin_pad]: b runs over cin (contiguous)
+            if (a < no && b < nc)
+                wf[e.wf_off + (static_cast<long long>(t) * cout_pad + o0 + a) * e.cin_pad + c0 + b] =
+                    __float2bfloat16(tile[a][b * taps + t]);
+            // dgrad operand [tap][cin_pad][cout_pad]: b runs over cout (contiguous)
+            if (e.wd_off >= 0 && a < nc && b < no)
+                wd[e.wd_off + (static_cast<long long>(t) * e.cin_pad + c0 + a) * cout_pad + o0 + b] =
                     __float2bfloat16(tile[b][a * taps + t]);
         }
     }
@@ -687,7 +696,7 @@ int bn_bwd_partial_rows(long long rows, int C) {
 cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
                                  int C, float* partial, cudaStream_t s) {
     const int cvec = C >> 3;
-    if (cvec < 1 || cvec > 256 || (256 % cvec) != 0) return cudaErrorInvalidValue;
+    if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     const int rpi = 256 / cvec;
     const int blocks = bn_bwd_partial_rows(rows, C);
     const size_t smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
@@ -735,8 +744,8 @@ cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, voi
 
 cudaError_t launch_head_fwd(const void* act, int N, int hw, int C, const float* W, const float* bias, int K,
                             float* pooled, float* logits, cudaStream_t s) {
-    if (C > 1024 || (C & 31)) return cudaErrorInvalidValue;
-    head_fwd_kernel<<<N, C, C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(act), hw, C, W, bias, K, pooled,
+    if (C > 4096 || (C & 31)) return cudaErrorInvalidValue;
+    head_fwd_kernel<<<N, C < 512 ? C : 512, C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(act), hw, C, W, bias, K, pooled,
                                                     logits);
     return cudaGetLastError();
 }
@@ -749,8 +758,8 @@ cudaError_t launch_ce_loss(const float* logits, const long long* target, int N, 
 
 cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const float* W, int N, int hw, int C, int K,
                             void* dact, float* dW, float* db, cudaStream_t s) {
-    if (C > 1024) return cudaErrorInvalidValue;
-    head_bwd_act_kernel<<<N, C, 0, s>>>(dlogits, W, K, hw, C, static_cast<__nv_bfloat16*>(dact));
+    if (C > 4096) return cudaErrorInvalidValue;
+    head_bwd_act_kernel<<<N, C < 512 ? C : 512, 0, s>>>(dlogits, W, K, hw, C, static_cast<__nv_bfloat16*>(dact));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     dim3 grid((C + 31) / 32, K);

@@ -128,15 +128,64 @@ def preact_resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_
                 feat=in_planes)
 
 
+MOBILENETV2_CFG = [(1, 16, 1, 1), (6, 24, 2, 1), (6, 32, 3, 2), (6, 64, 4, 2), (6, 96, 3, 1), (6, 160, 3, 2),
+                   (6, 320, 1, 1)]      # (expansion, out_planes, num_blocks, stride), models/mobilenetv2.py:42-48
+
+
+def mobilenetv2_spec(num_classes=10):
+    """MobileNetV2 as models/mobilenetv2.py:11-77 composes it (CIFAR strides, F.relu not ReLU6)."""
+    params, buffers, blocks, depthwise = OrderedDict(), OrderedDict(), [], set()
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    params["conv1.weight"] = (32, 3, 3, 3)
+    bn("bn1", 32)
+    cin, i = 32, 0
+    for expansion, cout, nb, stride in MOBILENETV2_CFG:
+        for s in [stride] + [1] * (nb - 1):
+            name, planes = f"layers.{i}", expansion * cin
+            params[name + ".conv1.weight"] = (planes, cin, 1, 1)
+            bn(name + ".bn1", planes)
+            params[name + ".conv2.weight"] = (planes, 1, 3, 3)
+            depthwise.add(name + ".conv2.weight")
+            bn(name + ".bn2", planes)
+            params[name + ".conv3.weight"] = (cout, planes, 1, 1)
+            bn(name + ".bn3", cout)
+            shortcut = s == 1 and cin != cout
+            if shortcut:
+                params[name + ".shortcut.0.weight"] = (cout, cin, 1, 1)
+                bn(name + ".shortcut.1", cout)
+            blocks.append(dict(name=name, cin=cin, cout=cout, planes=planes, stride=s, shortcut=shortcut))
+            cin = cout
+            i += 1
+    params["conv2.weight"] = (1280, 320, 1, 1)
+    bn("bn2", 1280)
+    params["linear.weight"] = (num_classes, 1280)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="mobilenetv2", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes,
+                feat=1280, depthwise=depthwise, head_prefixes=("linear", "conv2", "bn2"))
+
+
+def _pad64(c):
+    return _align(c, 64)
+
+
 def param_offsets(spec):
-    """Element offsets of every parameter in the flat fp32 arenas (16-byte aligned), reference order."""
+    """Element offsets of every parameter in the flat fp32 arenas (16-byte aligned), reference order.
+    Per-channel vectors (BatchNorm weight / bias) are ALLOCATED padded to the 64-channel layout width the kernels
+    use; the padding stays zero (zero gradient, zero weight decay), the named views cover the true shape."""
     p_off, off = OrderedDict(), 0
     for name, shape in spec["params"].items():
         n = 1
         for s in shape:
             n *= s
         p_off[name] = (off, n, shape)
-        off = _align(off + n, 4)
+        alloc = _pad64(n) if len(shape) == 1 and not name.startswith(("linear", "classifier")) else n
+        off = _align(off + alloc, 4)
     return p_off, _align(off, 4)
 
 
@@ -152,7 +201,7 @@ def backward_groups(spec):
             owner = idx if f"features.{idx}.weight" in spec["params"] and len(spec["params"][f"features.{idx}.weight"]) == 4 \
                 else idx - 1
             return "stem" if f"features.{owner}" == first_conv else f"features.{owner}"
-        return "head" if name.startswith(("linear", "classifier")) else "stem"
+        return "head" if name.startswith(spec.get("head_prefixes", ("linear", "classifier"))) else "stem"
     groups = OrderedDict()
     for name in spec["params"]:
         groups.setdefault(key(name), []).append(name)
@@ -184,36 +233,42 @@ def plan_grad_buckets(spec, bucket_bytes):
     return buckets, ready_after
 
 
+def _bn_views(u, eng, bn_name, C):
+    """Padded-width views of a BatchNorm's parameters / statistics for the kernels."""
+    u.gamma, u.beta = eng.param_vec(bn_name + ".weight", C), eng.param_vec(bn_name + ".bias", C)
+    u.dgamma, u.dbeta = eng.grad_vec(bn_name + ".weight", C), eng.grad_vec(bn_name + ".bias", C)
+    u.rm, u.rv = eng.buffer_vec(bn_name + ".running_mean", C), eng.buffer_vec(bn_name + ".running_var", C)
+    u.scale, u.shift, u.mean, u.rstd = (eng.new_f32(C) for _ in range(4))
+
+
 class ConvUnit:
-    """One conv (+ the BatchNorm that follows it): descriptors, operand views, statistic buffers."""
+    """One conv (+ the BatchNorm that follows it): descriptors, operand views, statistic buffers.
+    Channel counts are the reference's; tensors are laid out with channels padded to multiples of 64
+    (self.cin / self.cout are those layout widths, *_true the reference's)."""
 
     def __init__(self, eng, name, bn_name, x, cin, cout, k, stride, H, W, stem=False):
         N = eng.N
         self.name, self.bn_name = name, bn_name
-        self.cin, self.cout, self.k, self.stride, self.H, self.W = cin, cout, k, stride, H, W
+        self.cin_true, self.cout_true = cin, cout
+        cin_p, cout_p = (64 if stem else _pad64(cin)), _pad64(cout)
+        self.cin, self.cout, self.k, self.stride, self.H, self.W = cin_p, cout_p, k, stride, H, W
         self.Ho, self.Wo = H // stride, W // stride
         self.rows = N * self.Ho * self.Wo
         self.stem = stem
         self.x = x
-        self.y = eng.new_act(N, self.Ho, self.Wo, cout)
+        self.y = eng.new_act(N, self.Ho, self.Wo, cout_p)
         if stem:
             # the 3-channel stem runs as a 1x1 GEMM over an im2col operand (k = 27 padded to 64)
-            self.desc = ops.conv_desc(N, H, W, 64, cout, 1, 1)
-            self.desc_w = ops.conv_desc(N, H, W, 64, cout, 1, 1, cin_valid=27, kflat_cin=3)
+            self.desc = ops.conv_desc(N, H, W, 64, cout_p, 1, 1)
+            self.desc_w = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, cin_valid=27, kflat_cin=3, cout_valid=cout)
         else:
-            self.desc = ops.conv_desc(N, H, W, cin, cout, k, stride)
-            self.desc_w = self.desc
+            self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride)
+            self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout)
         self.wf = eng.wf_view(name)
         self.wd = None if stem else eng.wd_view(name)
         self.dw = eng.grad_view(name + ".weight")
         if bn_name is not None:
-            self.gamma = eng.param_view(bn_name + ".weight")
-            self.beta = eng.param_view(bn_name + ".bias")
-            self.dgamma = eng.grad_view(bn_name + ".weight")
-            self.dbeta = eng.grad_view(bn_name + ".bias")
-            self.rm = eng.buffer_view(bn_name + ".running_mean")
-            self.rv = eng.buffer_view(bn_name + ".running_var")
-            self.scale, self.shift, self.mean, self.rstd = (eng.new_f32(cout) for _ in range(4))
+            _bn_views(self, eng, bn_name, cout_p)
         # a conv bias (VGG) is never added to y — the BatchNorm cancels it — but the running mean tracks it
         self.conv_bias = eng.param_view(name + ".bias") if (name + ".bias") in eng.p_off else None
 
@@ -249,6 +304,32 @@ class ConvUnit:
         ops.conv_dgrad(self.desc, dy, self.wd, dx, add_src)
 
 
+class DwUnit:
+    """Depthwise 3x3 conv + BatchNorm (models/mobilenetv2.py:20-21)."""
+
+    def __init__(self, eng, name, bn_name, x, C, stride, H, W):
+        N = eng.N
+        self.name, self.c_true, self.stride, self.H, self.W = name, C, stride, H, W
+        self.cout = _pad64(C)
+        self.Ho, self.Wo = H // stride, W // stride
+        self.rows = N * self.Ho * self.Wo
+        self.x = x
+        self.y = eng.new_act(N, self.Ho, self.Wo, self.cout)
+        self.w = eng.param_view(name + ".weight")
+        self.dw = eng.grad_view(name + ".weight")
+        self.conv_bias = None
+        _bn_views(self, eng, bn_name, self.cout)
+
+    def fprop(self, eng):
+        self.stat_rows = ops.dwconv_fprop(self.x, self.w, self.y, self.c_true, self.stride, eng.part_sum, eng.part_sq)
+
+    def wgrad(self, dy):
+        ops.dwconv_wgrad(self.x, dy, self.dw, self.c_true, self.stride)
+
+    def dgrad(self, dy, dx):
+        ops.dwconv_dgrad(dy, self.w, dx, self.c_true, self.stride)
+
+
 class Engine:
     """Static execution plan for one (network, batch size) pair on one GPU."""
 
@@ -259,8 +340,9 @@ class Engine:
         self._layout_params(share_from)
         self._acts = []
         f32 = dict(device=self.device, dtype=torch.float32)
-        self.part_sum = torch.zeros(ops.MAX_STAT_ROWS, 2048, **f32)
-        self.part_sq = torch.zeros(ops.MAX_STAT_ROWS, 2048, **f32)
+        stat_rows = ops.MAX_DW_STAT_ROWS if spec["family"] == "mobilenetv2" else ops.MAX_STAT_ROWS
+        self.part_sum = torch.zeros(stat_rows, 2048, **f32)
+        self.part_sq = torch.zeros(stat_rows, 2048, **f32)
         self.bwd_partial = torch.zeros(148 * 4 * 2 * 2048, **f32)
         self.coef_a, self.coef_b, self.coef_c = (torch.zeros(2048, **f32) for _ in range(3))
         self.fwd_ops, self.bwd_ops = [], []
@@ -270,6 +352,8 @@ class Engine:
             self._build_vgg()
         elif spec["family"] == "preact":
             self._build_preact()
+        elif spec["family"] == "mobilenetv2":
+            self._build_mobilenetv2()
         else:
             raise NotImplementedError(spec["family"])
 
@@ -280,7 +364,7 @@ class Engine:
         self.b_off, off = OrderedDict(), 0
         for name, shape in spec["buffers"].items():
             self.b_off[name] = (off, shape[0])
-            off = _align(off + shape[0], 4)
+            off = _align(off + _pad64(shape[0]), 4)          # padded like the per-channel parameters
         f32 = dict(device=self.device, dtype=torch.float32)
         if share_from is not None:
             self.P, self.G, self.M, self.B = share_from.P, share_from.G, share_from.M, share_from.B
@@ -293,23 +377,24 @@ class Engine:
         self.wf_off, self.wd_off, entries = {}, {}, []
         wf_n = wd_n = 0
         for name, shape in spec["params"].items():
-            if len(shape) != 4:
-                continue
+            if len(shape) != 4 or name in spec.get("depthwise", ()):
+                continue                                  # depthwise kernels read the fp32 master weights directly
             cname = name[:-len(".weight")]
             cout, cin, k, _ = shape
+            cout_p, cin_p = _pad64(cout), _pad64(cin)
             poff = self.p_off[name][0]
-            if cin == 3:      # stem: [cout][64], k = tap*3 + c
-                self.wf_off[cname] = (wf_n, (1, cout, 64))
+            if cin == 3:      # stem: [cout_pad][64], k = tap*3 + c
+                self.wf_off[cname] = (wf_n, (1, cout_p, 64))
                 entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=-1, cout=cout, cin=cin, taps=k * k,
                                     cin_pad=64, kflat=1))
-                wf_n += cout * 64
+                wf_n += cout_p * 64
             else:
-                self.wf_off[cname] = (wf_n, (k * k, cout, cin))
-                self.wd_off[cname] = (wd_n, (k * k, cin, cout))
+                self.wf_off[cname] = (wf_n, (k * k, cout_p, cin_p))
+                self.wd_off[cname] = (wd_n, (k * k, cin_p, cout_p))
                 entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=wd_n, cout=cout, cin=cin, taps=k * k,
-                                    cin_pad=cin))
-                wf_n += cout * cin * k * k
-                wd_n += cout * cin * k * k
+                                    cin_pad=cin_p, cout_pad=cout_p))
+                wf_n += cout_p * cin_p * k * k
+                wd_n += cout_p * cin_p * k * k
         bf = dict(device=self.device, dtype=torch.bfloat16)
         self.repack_entries = len(entries)
         if share_from is not None:
@@ -330,6 +415,19 @@ class Engine:
     def buffer_view(self, name):
         off, n = self.b_off[name]
         return self.B[off:off + n]
+
+    # padded-width views of per-channel vectors, for the kernels (the tail beyond the true length stays zero)
+    def param_vec(self, name, C):
+        off = self.p_off[name][0]
+        return self.P[off:off + C]
+
+    def grad_vec(self, name, C):
+        off = self.p_off[name][0]
+        return self.G[off:off + C]
+
+    def buffer_vec(self, name, C):
+        off = self.b_off[name][0]
+        return self.B[off:off + C]
 
     def wf_view(self, cname):
         off, shape = self.wf_off[cname]
@@ -570,10 +668,7 @@ class Engine:
             """BatchNorm applied to tensor `y` produced by `producer` (whose epilogue emitted the statistics)."""
             def __init__(s, eng, bn_name, y, C, rows):
                 s.y, s.cout, s.rows = y, C, rows
-                s.gamma, s.beta = eng.param_view(bn_name + ".weight"), eng.param_view(bn_name + ".bias")
-                s.dgamma, s.dbeta = eng.grad_view(bn_name + ".weight"), eng.grad_view(bn_name + ".bias")
-                s.rm, s.rv = eng.buffer_view(bn_name + ".running_mean"), eng.buffer_view(bn_name + ".running_var")
-                s.scale, s.shift, s.mean, s.rstd = (eng.new_f32(C) for _ in range(4))
+                _bn_views(s, eng, bn_name, C)
             stat_rows = 0
             bn_stats = ConvUnit.bn_stats
             bn_backward = ConvUnit.bn_backward
@@ -633,6 +728,116 @@ class Engine:
         Bk.append(lambda dout=dout: stem.wgrad(dout))
         self.bwd_ops = Bk
 
+    # ------------------------------------------------------------------ MobileNetV2 plan
+    def _build_mobilenetv2(self):
+        """models/mobilenetv2.py:32-37,69-77: per block 1x1 expand + BN + ReLU -> depthwise 3x3 + BN + ReLU ->
+        1x1 project + BN (linear); `out + shortcut(x)` only when stride == 1 (identity, or 1x1 conv + BN when the
+        channel count changes). Head: 1x1 320->1280 + BN + ReLU, avg_pool2d(4), Linear(1280, 10)."""
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        stem = ConvUnit(self, "conv1", "bn1", self.x0, 3, 32, 3, 1, 32, 32, stem=True)
+        a0 = self.new_act(N, 32, 32, stem.cout)
+        self.units = [stem]
+        F, blocks = self.fwd_ops, []
+
+        def fwd_stem(training):
+            stem.fprop(self, True)
+            stem.bn_stats(self, training)
+            ops.bn_act_apply(stem.y, stem.scale, stem.shift, a0, stem.rows, stem.cout, relu=True)
+        F.append(fwd_stem)
+        x, H, W = a0, 32, 32
+        for b in spec["blocks"]:
+            name, cin, cout, planes, s = b["name"], b["cin"], b["cout"], b["planes"], b["stride"]
+            c1 = ConvUnit(self, name + ".conv1", name + ".bn1", x, cin, planes, 1, 1, H, W)
+            a1 = self.new_act(N, H, W, c1.cout)
+            dw = DwUnit(self, name + ".conv2", name + ".bn2", a1, planes, s, H, W)
+            Ho, Wo = H // s, W // s
+            a2 = self.new_act(N, Ho, Wo, dw.cout)
+            c3 = ConvUnit(self, name + ".conv3", name + ".bn3", a2, planes, cout, 1, 1, Ho, Wo)
+            cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, 1, H, W) \
+                if b["shortcut"] else None
+            identity = s == 1 and cs is None
+            out = self.new_act(N, Ho, Wo, c3.cout)
+            self.units += [c1, dw, c3] + ([cs] if cs else [])
+            blocks.append((c1, a1, dw, a2, c3, cs, identity, out, x))
+
+            def fwd(training, c1=c1, a1=a1, dw=dw, a2=a2, c3=c3, cs=cs, identity=identity, out=out, x=x):
+                c1.fprop(self)
+                c1.bn_stats(self, training)
+                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
+                dw.fprop(self)
+                dw.bn_stats(self, training)
+                ops.bn_act_apply(dw.y, dw.scale, dw.shift, a2, dw.rows, dw.cout, relu=True)
+                c3.fprop(self)
+                c3.bn_stats(self, training)
+                if cs is not None:
+                    cs.fprop(self)
+                    cs.bn_stats(self, training)
+                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=False, res=cs.y,
+                                     res_scale=cs.scale, res_shift=cs.shift)
+                else:
+                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=False,
+                                     res=(x if identity else None))
+            F.append(fwd)
+            x, H, W = out, Ho, Wo
+        ch = ConvUnit(self, "conv2", "bn2", x, 320, 1280, 1, 1, H, W)
+        ah = self.new_act(N, H, W, ch.cout)
+        self.units.append(ch)
+
+        def fwd_last(training):
+            ch.fprop(self)
+            ch.bn_stats(self, training)
+            ops.bn_act_apply(ch.y, ch.scale, ch.shift, ah, ch.rows, ch.cout, relu=True)
+        F.append(fwd_last)
+        fwd_head, bwd_head, dout = self._build_head(ah, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        dyh = self.new_act(*ch.y.shape)
+        dxh = self.new_act(*x.shape)
+
+        def bwd_last(dout=dout):
+            ch.bn_backward(self, dout, ah, dout, dyh)
+            ch.wgrad(dyh)
+            ch.dgrad(dyh, dxh)
+        Bk.append(bwd_last)
+        dout = dxh
+        for (c1, a1, dw, a2, c3, cs, identity, out, xin) in reversed(blocks):
+            dy3 = self.new_act(*c3.y.shape)
+            dys = self.new_act(*cs.y.shape) if cs is not None else None
+            da2 = self.new_act(*a2.shape)
+            dy2 = self.new_act(*dw.y.shape)
+            da1 = self.new_act(*a1.shape)
+            dy1 = self.new_act(*c1.y.shape)
+            dx = self.new_act(*xin.shape)
+
+            def bwd(c1=c1, a1=a1, dw=dw, a2=a2, c3=c3, cs=cs, identity=identity, dout=dout, dy3=dy3, dys=dys,
+                    da2=da2, dy2=dy2, da1=da1, dy1=dy1, dx=dx):
+                c3.bn_backward(self, dout, None, None, dy3)          # block output has no ReLU
+                if cs is not None:
+                    cs.bn_backward(self, dout, None, None, dys)
+                c3.wgrad(dy3)
+                c3.dgrad(dy3, da2)
+                dw.bn_backward(self, da2, a2, da2, dy2)
+                dw.wgrad(dy2)
+                dw.dgrad(dy2, da1)
+                c1.bn_backward(self, da1, a1, da1, dy1)
+                c1.wgrad(dy1)
+                if cs is not None:
+                    cs.wgrad(dys)
+                    cs.dgrad(dys, dx)
+                    c1.dgrad(dy1, dx, add_src=dx)
+                else:
+                    c1.dgrad(dy1, dx, add_src=(dout if identity else None))
+            Bk.append(bwd)
+            dout = dx
+        dy0 = self.new_act(*stem.y.shape)
+
+        def bwd_stem(dout=dout):
+            stem.bn_backward(self, dout, a0, dout, dy0)
+            stem.wgrad(dy0)
+        Bk.append(bwd_stem)
+        self.bwd_ops = Bk
+
     # ------------------------------------------------------------------ execution
     def forward(self, training=True):
         for op in self.fwd_ops:
@@ -649,3 +854,7 @@ class Engine:
 
     def activation_bytes(self):
         return sum(t.numel() * t.element_size() for t in self._acts)
+
+
+DwUnit.bn_stats = ConvUnit.bn_stats
+DwUnit.bn_backward = ConvUnit.bn_backward

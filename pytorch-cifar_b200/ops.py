@@ -11,7 +11,8 @@ from ._lib import ConvDesc, RepackEntry, check
 
 CIFAR_MEAN = (0.4914, 0.4822, 0.4465)   # reference main.py:34
 CIFAR_STD = (0.2023, 0.1994, 0.2010)    # reference main.py:34
-MAX_STAT_ROWS = 148
+MAX_STAT_ROWS = 148          # conv epilogue partial rows (one per CTA)
+MAX_DW_STAT_ROWS = 592       # depthwise fprop partial rows (one per block)
 
 
 def _p(t):
@@ -30,8 +31,9 @@ def _need(t, dtype, name):
                          f"contig={t.is_contiguous()}")
 
 
-def conv_desc(n, h, w, cin, cout, ksize, stride, cin_valid=0, kflat_cin=0, block_n=0, max_ctas=0, flags=0):
-    return ConvDesc(n, h, w, cin, cout, ksize, stride, cin_valid, kflat_cin, block_n, max_ctas, flags)
+def conv_desc(n, h, w, cin, cout, ksize, stride, cin_valid=0, kflat_cin=0, block_n=0, max_ctas=0, flags=0,
+              cout_valid=0):
+    return ConvDesc(n, h, w, cin, cout, ksize, stride, cin_valid, cout_valid, kflat_cin, block_n, max_ctas, flags)
 
 
 def pack_weight_fprop(w_oihw):
@@ -69,6 +71,30 @@ def conv_wgrad(d, x, dy, dw):
     lib = _lib.load()
     _need(x, torch.bfloat16, "x"); _need(dy, torch.bfloat16, "dy"); _need(dw, torch.float32, "dw")
     check(lib.b2c_conv_wgrad(ctypes.byref(d), _p(x), _p(dy), _p(dw), _stream()), "b2c_conv_wgrad")
+
+
+def dwconv_fprop(x, weight, y, c_valid, stride, part_sum=None, part_sq=None):
+    """Depthwise 3x3 (groups == channels); returns the number of BatchNorm partial rows written."""
+    lib = _lib.load()
+    n, h, w, c = x.shape
+    _need(x, torch.bfloat16, "x"); _need(y, torch.bfloat16, "y"); _need(weight, torch.float32, "weight")
+    rows = ctypes.c_int(0)
+    check(lib.b2c_dwconv_fprop(_p(x), _p(weight), _p(y), n, h, w, c, c_valid, stride, _p(part_sum), _p(part_sq),
+                               ctypes.byref(rows), _stream()), "b2c_dwconv_fprop")
+    return rows.value
+
+
+def dwconv_dgrad(dy, weight, dx, c_valid, stride):
+    lib = _lib.load()
+    n, h, w, c = dx.shape
+    check(lib.b2c_dwconv_dgrad(_p(dy), _p(weight), _p(dx), n, h, w, c, c_valid, stride, _stream()), "b2c_dwconv_dgrad")
+
+
+def dwconv_wgrad(x, dy, dweight, c_valid, stride):
+    lib = _lib.load()
+    n, h, w, c = x.shape
+    _need(dweight, torch.float32, "dweight")
+    check(lib.b2c_dwconv_wgrad(_p(x), _p(dy), _p(dweight), n, h, w, c, c_valid, stride, _stream()), "b2c_dwconv_wgrad")
 
 
 def bn_finalize(part_sum, part_sq, rows, channels, count, gamma, beta, eps, momentum, running_mean, running_var,
@@ -201,7 +227,7 @@ def make_repack_table(entries, device):
     arr = (RepackEntry * len(entries))()
     for i, e in enumerate(entries):
         arr[i] = RepackEntry(e["src_off"], e["wf_off"], e.get("wd_off", -1), e["cout"], e["cin"], e["taps"],
-                             e["cin_pad"], e.get("kflat", 0), 0)
+                             e["cin_pad"], e.get("kflat", 0), e.get("cout_pad", 0))
     raw = bytes(arr)
     t = torch.frombuffer(bytearray(raw), dtype=torch.uint8).clone()
     return t.to(device)

@@ -63,7 +63,9 @@ def golden_other_nets():
     x = torch.from_numpy(rs.standard_normal((4, 3, 32, 32)).astype(np.float32))
     target = torch.from_numpy(rs.randint(0, 10, size=(4,)).astype(np.int64))
     out = dict(x=x.numpy(), target=target.numpy())
-    for tag, ctor in (("vgg16", lambda: ref_vgg.VGG("VGG16")), ("preact18", ref_pre.PreActResNet18)):
+    import models.mobilenetv2 as ref_mb
+    for tag, ctor in (("vgg16", lambda: ref_vgg.VGG("VGG16")), ("preact18", ref_pre.PreActResNet18),
+                      ("mobilenetv2", ref_mb.MobileNetV2)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

@@ -68,4 +68,4 @@ def test_c_abi_exports_every_declared_symbol():
     l = _lib.load()
     assert l.b2c_version() >= 100
     assert b"not supported" in l.b2c_error_string(_lib.B2C_ERR_UNSUPPORTED)
-    assert ctypes.sizeof(_lib.ConvDesc) == 48 and ctypes.sizeof(_lib.RepackEntry) == 48
+    assert ctypes.sizeof(_lib.ConvDesc) == 52 and ctypes.sizeof(_lib.RepackEntry) == 48

@@ -83,11 +83,77 @@ def test_bn_bwd_apply_with_bypass_add(ops):
     assert rel(dy.float(), ca * dz.float() + cb * y.float() + cc + add.float()) < 1e-2
 
 
+@pytest.mark.parametrize("shape", [(4, 32, 32, 96, 96, 1), (4, 32, 32, 192, 144, 2), (8, 8, 8, 384, 384, 1),
+                                   (8, 8, 8, 576, 576, 2), (16, 4, 4, 960, 960, 1), (2, 32, 32, 64, 32, 1)])
+def test_depthwise_conv(ops, shape):
+    n, h, w, cpad, c, stride = shape
+    g = torch.Generator(device="cuda").manual_seed(60)
+    x = torch.zeros(n, h, w, cpad, device="cuda", dtype=torch.bfloat16)
+    x[..., :c] = torch.randn(n, h, w, c, device="cuda", generator=g).to(torch.bfloat16)
+    wt = torch.randn(c, 1, 3, 3, device="cuda", generator=g) * 0.3
+    ho, wo = h // stride, w // stride
+    y = torch.full((n, ho, wo, cpad), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ps = torch.zeros(ops.MAX_DW_STAT_ROWS, cpad, device="cuda")
+    pq = torch.zeros(ops.MAX_DW_STAT_ROWS, cpad, device="cuda")
+    rows = ops.dwconv_fprop(x, wt, y, c, stride, ps, pq)
+    xr = x[..., :c].float().permute(0, 3, 1, 2).requires_grad_()
+    wr = wt.clone().requires_grad_()
+    yr = F.conv2d(xr, wr, stride=stride, padding=1, groups=c)
+    dy = torch.zeros(n, ho, wo, cpad, device="cuda", dtype=torch.bfloat16)
+    dy[..., :c] = torch.randn(n, ho, wo, c, device="cuda", generator=g).to(torch.bfloat16)
+    yr.backward(dy[..., :c].float().permute(0, 3, 1, 2))
+    dx = torch.full((n, h, w, cpad), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ops.dwconv_dgrad(dy, wt, dx, c, stride)
+    dw = torch.zeros(c, 1, 3, 3, device="cuda")
+    ops.dwconv_wgrad(x, dy, dw, c, stride)
+    torch.cuda.synchronize()
+    assert rel(y[..., :c].float().permute(0, 3, 1, 2), yr.detach()) < 1e-2
+    assert (y[..., c:] == 0).all() and (dx[..., c:] == 0).all()            # padded channels stay zero
+    assert rel(ps[:rows].sum(0)[:c], yr.detach().sum((0, 2, 3))) < 5e-3
+    assert rel(pq[:rows].sum(0)[:c], (yr.detach() ** 2).sum((0, 2, 3))) < 1e-3
+    assert rel(dx[..., :c].float().permute(0, 3, 1, 2), xr.grad) < 1e-2
+    assert rel(dw, wr.grad) < 1e-3
+
+
+def test_pointwise_conv_with_padded_channels(ops):
+    """1x1 conv 24 -> 144 in the 64-padded layout (64 -> 192): padded weights are zero, wgrad masks them."""
+    n, hw, cin, cout, cin_p, cout_p = 4, 32, 24, 144, 64, 192
+    g = torch.Generator(device="cuda").manual_seed(61)
+    x = torch.zeros(n, hw, hw, cin_p, device="cuda", dtype=torch.bfloat16)
+    x[..., :cin] = torch.randn(n, hw, hw, cin, device="cuda", generator=g).to(torch.bfloat16)
+    wt = (torch.randn(cout, cin, 1, 1, device="cuda", generator=g) * 0.2)
+    master = wt.flatten().contiguous()
+    wf = torch.zeros(cout_p * cin_p, device="cuda", dtype=torch.bfloat16)
+    wd = torch.zeros(cout_p * cin_p, device="cuda", dtype=torch.bfloat16)
+    table = ops.make_repack_table([dict(src_off=0, wf_off=0, wd_off=0, cout=cout, cin=cin, taps=1, cin_pad=cin_p,
+                                        cout_pad=cout_p)], "cuda")
+    ops.repack_weights(master, wf, wd, table, 1)
+    y = torch.empty(n, hw, hw, cout_p, device="cuda", dtype=torch.bfloat16)
+    d = ops.conv_desc(n, hw, hw, cin_p, cout_p, 1, 1, cin_valid=cin, cout_valid=cout)
+    ops.conv_fprop(d, x, wf.view(1, cout_p, cin_p), y)
+    wq = wt.to(torch.bfloat16).float()
+    ref = F.conv2d(x[..., :cin].float().permute(0, 3, 1, 2), wq)
+    dy = torch.zeros(n, hw, hw, cout_p, device="cuda", dtype=torch.bfloat16)
+    dy[..., :cout] = torch.randn(n, hw, hw, cout, device="cuda", generator=g).to(torch.bfloat16)
+    dx = torch.empty(n, hw, hw, cin_p, device="cuda", dtype=torch.bfloat16)
+    ops.conv_dgrad(d, dy, wd.view(1, cin_p, cout_p), dx)
+    dw = torch.zeros(cout, cin, 1, 1, device="cuda")
+    ops.conv_wgrad(d, x, dy, dw)
+    torch.cuda.synchronize()
+    assert rel(y[..., :cout].float().permute(0, 3, 1, 2), ref) < 1e-2 and (y[..., cout:] == 0).all()
+    dyr = dy[..., :cout].float().permute(0, 3, 1, 2)
+    assert rel(dx[..., :cin].float().permute(0, 3, 1, 2), torch.nn.grad.conv2d_input((n, cin, hw, hw), wq, dyr)) < 1e-2
+    assert (dx[..., cin:] == 0).all()
+    assert rel(dw, torch.nn.grad.conv2d_weight(x[..., :cin].float().permute(0, 3, 1, 2), (cout, cin, 1, 1), dyr)) < 1e-3
+
+
 MODELS = {
     "vgg16": ("vgg_spec", "build_vgg_params", "vgg_forward", "features.0", ["classifier.weight", "features.41.weight",
                                                                               "features.41.bias"]),
     "preact18": ("preact_resnet_spec", "build_preact_params", "preact_forward", "conv1",
                  ["linear.weight", "layer4.1.conv2.weight", "layer4.1.bn2.weight"]),
+    "mobilenetv2": ("mobilenetv2_spec", "build_mobilenetv2_params", "mobilenetv2_forward", "conv1",
+                    ["linear.weight", "bn2.weight", "bn2.bias"]),
 }
 
 
@@ -119,7 +185,8 @@ def test_model_training_step(ops, model):
         t = taps[name].detach()
         b = cp.get(name + ".bias")      # VGG convs carry a bias that the following BatchNorm cancels; the CUDA path
         return t if b is None else t - b.view(1, -1, 1, 1)     # leaves it out of the stored conv output
-    fwd_err = {u.name: rel(u.y.float().permute(0, 3, 1, 2), ref_conv_out(u.name)) for u in eng.units if u.name in taps}
+    fwd_err = {u.name: rel(u.y[..., :taps[u.name].shape[1]].float().permute(0, 3, 1, 2), ref_conv_out(u.name))
+               for u in eng.units if u.name in taps}
     grads = eng.named_grads()
     # a conv bias followed by BatchNorm has a mathematically zero gradient (fp32 shows round-off noise, we write 0)
     skip = {k for k in grads_ref if k.endswith(".bias") and cp[k[:-5] + ".weight"].dim() == 4}
