@@ -11,7 +11,7 @@ accelerate() recognises module trees structurally, by class and attribute names.
 import torch.nn as nn
 import torch.nn.functional as F
 
-from .nets import VGG_CFG
+from .nets import MOBILENETV2_CFG, VGG_CFG
 
 
 def _conv(cin, cout, k, stride):
@@ -102,6 +102,45 @@ class VGG(nn.Module):
 
     def forward(self, x):
         return self.classifier(self.features(x).flatten(1))
+
+
+class Block(nn.Module):
+    """MobileNetV2 inverted residual (models/mobilenetv2.py:11-37)."""
+
+    def __init__(self, cin, cout, expansion, stride):
+        super().__init__()
+        self.stride, p = stride, expansion * cin
+        self.conv1, self.bn1 = _conv(cin, p, 1, 1), nn.BatchNorm2d(p)
+        self.conv2 = nn.Conv2d(p, p, kernel_size=3, stride=stride, padding=1, groups=p, bias=False)
+        self.bn2 = nn.BatchNorm2d(p)
+        self.conv3, self.bn3 = _conv(p, cout, 1, 1), nn.BatchNorm2d(cout)
+        self.shortcut = nn.Sequential()
+        if stride == 1 and cin != cout:
+            self.shortcut = nn.Sequential(_conv(cin, cout, 1, 1), nn.BatchNorm2d(cout))
+
+    def forward(self, x):
+        y = F.relu(self.bn2(self.conv2(F.relu(self.bn1(self.conv1(x))))))
+        y = self.bn3(self.conv3(y))
+        return y + self.shortcut(x) if self.stride == 1 else y
+
+
+class MobileNetV2(nn.Module):
+    def __init__(self, num_classes=10):
+        super().__init__()
+        self.conv1, self.bn1 = _conv(3, 32, 3, 1), nn.BatchNorm2d(32)
+        seq, cin = [], 32
+        for e, cout, n, stride in MOBILENETV2_CFG:
+            for s in [stride] + [1] * (n - 1):
+                seq.append(Block(cin, cout, e, s))
+                cin = cout
+        self.layers = nn.Sequential(*seq)
+        self.conv2, self.bn2 = _conv(320, 1280, 1, 1), nn.BatchNorm2d(1280)
+        self.linear = nn.Linear(1280, num_classes)
+
+    def forward(self, x):
+        y = self.layers(F.relu(self.bn1(self.conv1(x))))
+        y = F.relu(self.bn2(self.conv2(y)))
+        return self.linear(F.avg_pool2d(y, 4).flatten(1))
 
 
 def ResNet18():

@@ -21,7 +21,7 @@ def make(family):
     from oracle import ref_modules
     torch.manual_seed(0)
     return {"resnet18": ref_modules.ResNet18, "vgg16": lambda: ref_modules.VGG("VGG16"),
-            "preact18": ref_modules.PreActResNet18}[family]().cuda()
+            "preact18": ref_modules.PreActResNet18, "mobilenetv2": ref_modules.MobileNetV2}[family]().cuda()
 
 
 def batch(n, seed):
@@ -31,7 +31,7 @@ def batch(n, seed):
     return x, t
 
 
-@pytest.mark.parametrize("family", ["resnet18", "vgg16", "preact18"])
+@pytest.mark.parametrize("family", ["resnet18", "vgg16", "preact18", "mobilenetv2"])
 def test_train_eval_checkpoint_roundtrip(family):
     import b200cifar
     from b200cifar.accelerate import accelerate
@@ -79,11 +79,12 @@ def test_train_eval_checkpoint_roundtrip(family):
     plain.eval()
     with torch.no_grad():
         op = plain(xe)
-    assert rel(oe, op) < 6e-2 and (oe.argmax(1) == op.argmax(1)).float().mean().item() > 0.9
+    tol = 0.25 if family == "mobilenetv2" else 6e-2      # 52 bf16 layers deep (tests/test_models_gpu.py BOUNDS)
+    assert rel(oe, op) < tol and (oe.argmax(1) == op.argmax(1)).float().mean().item() > (0.7 if family == "mobilenetv2" else 0.9)
     net.load_state_dict(ref.state_dict())                                        # a reference-trained checkpoint
     ref.eval()
     with torch.no_grad():
-        assert rel(net(xe), ref(xe)) < 6e-2
+        assert rel(net(xe), ref(xe)) < tol
 
 
 def test_fused_sgd_matches_torch_sgd():
