@@ -548,6 +548,7 @@ int b2c_head_bwd(const float* dlogits, const float* pooled, const float* weight,
 
 int b2c_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out_nchw_f32, int n,
                      const float* mean_host, const float* std_host, void* stream) {
+    if (n == 0) return 0;   // empty batch: nothing to do (zero-size tensors have null pointers)
     if (!data || !idx || !ijf || !out_nchw_f32 || !mean_host || !std_host || n < 0 || !aligned16(data))
         return B2C_ERR_ARG;
     return cuda_rc(b2c::launch_augment_nchw(data, idx, ijf, out_nchw_f32, n, mean_host, std_host, as_stream(stream)));
@@ -555,6 +556,7 @@ int b2c_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ij
 
 int b2c_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out_im2col_bf16,
                        int n, const float* mean_host, const float* std_host, void* stream) {
+    if (n == 0) return 0;   // empty batch: nothing to do (zero-size tensors have null pointers)
     if (!data || !idx || !ijf || !out_im2col_bf16 || !mean_host || !std_host || n < 0 || !aligned16(data) ||
         !aligned16(out_im2col_bf16))
         return B2C_ERR_ARG;
@@ -563,6 +565,7 @@ int b2c_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* 
 }
 
 int b2c_stem_im2col(const float* x_nchw_f32, void* out_im2col_bf16, int n, void* stream) {
+    if (n == 0) return 0;   // empty batch: nothing to do (zero-size tensors have null pointers)
     if (!x_nchw_f32 || !out_im2col_bf16 || n < 0 || !aligned16(out_im2col_bf16)) return B2C_ERR_ARG;
     return cuda_rc(b2c::launch_stem_im2col(x_nchw_f32, out_im2col_bf16, n, as_stream(stream)));
 }
