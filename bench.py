@@ -245,6 +245,12 @@ def run_product(args):
     clocks = sampler.stop() if sampler else None
     value = global_batch * K / (ms * 1e-3)
     final_loss = tr.read_loss()
+    in_sync = None
+    if world > 1:      # DDP invariant (main_dist.py:141-144): every replica holds the same parameters after training
+        chk = torch.stack([tr.eng.P.double().sum(), tr.eng.P.double().abs().sum()])
+        allchk = [torch.zeros_like(chk) for _ in range(world)]
+        dist.all_gather(allchk, chk)
+        in_sync = bool(all(torch.equal(allchk[0], c) for c in allchk))
 
     # ---------------- roofline of the dominant kernel family (tap GEMM = conv fprop + dgrad), timed live with
     # CUDA events on the launching stream: every fprop/dgrad launch of one step, back to back, same buffers.
@@ -320,7 +326,7 @@ def run_product(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * K,
             "launches_per_step": launches_per_step, "roofline": roofline,
             "tensor_frac_whole_step": value / world * RESNET18_TRAIN_FLOP_PER_IMG / 1e12 / peaks["tf_sustained"],
-            "final_loss": final_loss,
+            "final_loss": final_loss, "replicas_in_sync": in_sync,
         }
         if cpu_rate is not None:
             line["cpu_baseline"] = {"value": cpu_rate, "unit": UNIT, "cores": cores, "kind": "port",

@@ -326,8 +326,9 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
     if (rc) return rc;
     if (!x || !dy || !dw || !aligned16(x) || !aligned16(dy)) return B2C_ERR_ARG;
     const int ho = d->h / d->stride, wo = d->w / d->stride;
-    if (!grid_tiles(ho, wo, 64)) return B2C_ERR_UNSUPPORTED;
     const int bn = pick_bn(d->block_n, d->cout, 1 << 20);
+    const int kpx = (bn <= 128 && grid_tiles(ho, wo, 128)) ? 128 : 64;     // pixels per k-step
+    if (!grid_tiles(ho, wo, kpx)) return B2C_ERR_UNSUPPORTED;
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
     const int taps = d->ksize * d->ksize;
     const int cin_valid = d->cin_valid > 0 ? d->cin_valid : d->cin;
@@ -337,7 +338,8 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
 
     WgradParams p = {};
     const long long pixels = static_cast<long long>(d->n) * ho * wo;
-    p.k_chunks_total = static_cast<int>((pixels + 63) / 64);
+    p.k_pixels = kpx;
+    p.k_chunks_total = static_cast<int>((pixels + kpx - 1) / kpx);
     p.cin_blocks = d->cin / 64;
     p.num_slabs = taps * p.cin_blocks;
     p.num_m_blocks = (p.num_slabs + 1) / 2;
@@ -376,8 +378,8 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
         p.t_stride = 1;
     }
 
-    const int bh = (64 / wo) < ho ? (64 / wo) : ho;
-    const int bnb = 64 / (wo * bh);
+    const int bh = (kpx / wo) < ho ? (kpx / wo) : ho;
+    const int bnb = kpx / (wo * bh);
     CUtensorMap mx, mdy;
     rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
     if (rc) return rc;

@@ -37,7 +37,8 @@ struct TapGemmParams {
 // wgrad: dW[cout, cin, tap] += sum_pixels dY[pixel, cout] * X[pixel + shift_tap, cin]
 // D rows = two 64-channel (tap, cin-block) slabs, D cols = cout tile, reduction = pixels.
 struct WgradParams {
-    int k_chunks_total;   // ceil(pixels / 64)
+    int k_pixels;         // pixels per k-step: 64 or 128
+    int k_chunks_total;   // ceil(pixels / k_pixels)
     int splits;           // split-K factor; CTA handles chunks [s*per, min((s+1)*per, total))
     int chunks_per_split;
     int num_m_blocks;     // ceil(num_slabs / 2)

@@ -6,7 +6,8 @@
 //   GEMM view   dW[(tap, cin), cout] = sum_pixels X[pixel shifted by tap, cin] * dY[pixel, cout]
 //   Both operands have the reduction (pixels) as the strided dimension and channels contiguous
 //   (NHWC), so both are fed to tcgen05.mma as MN-major SWIZZLE_128B tiles straight from TMA:
-//   a k-step is a box of 64 pixels x 64 channels (8 KB); D rows = two 64-channel (tap, cin-block)
+//   a k-step is a box of 64 or 128 pixels x 64 channels (8 / 16 KB; 128 wherever the
+//   image tiles that way and cout <= 128 — fewer, larger pipeline steps keep the single issuing warp ahead); D rows = two 64-channel (tap, cin-block)
 //   slabs of X, D columns = a BN-wide slice of cout, taken from BN/64 slabs of dY.
 //   The pixel reduction is split across CTAs (split-K); partial tiles are combined with fp32
 //   `red.global.add` straight into the caller's zero-initialised gradient tensor, at the
@@ -21,23 +22,23 @@ namespace b2c {
 
 namespace {
 
-constexpr int kSlabBytes = 64 * 128;  // 64 pixels x 64 bf16 channels
-
-template <int BN>
+template <int BN, int KC>
 struct WgCfg {
+    static constexpr int kSlabBytes = KC * 128;  // KC pixels x 64 bf16 channels
     static constexpr int kNSlabs = BN / 64;
     static constexpr int kStageBytes = (2 + kNSlabs) * kSlabBytes;
-    static constexpr int kStages = BN == 64 ? 8 : (BN == 128 ? 6 : 4);
+    static constexpr int kStages = (208 * 1024) / kStageBytes < 8 ? (208 * 1024) / kStageBytes : 8;
     static constexpr int kTmemCols = BN;
     static constexpr int kBarBytes = 256;
     static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes;
 };
 
-template <int BN>
+template <int BN, int KC>
 __global__ void __launch_bounds__(192, 1)
 wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapDY,
              const __grid_constant__ WgradParams p) {
-    using Cfg = WgCfg<BN>;
+    using Cfg = WgCfg<BN, KC>;
+    constexpr int kSlabBytes = Cfg::kSlabBytes;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* aux = smem + Cfg::kStages * Cfg::kStageBytes;
@@ -96,7 +97,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
             int stage = 0;
             uint32_t phase = 0;
             for (int kc = k_begin; kc < k_end; ++kc) {
-                const int p0 = kc * 64;
+                const int p0 = kc * KC;
                 const int n0 = p0 / img;
                 const int h0 = (p0 - n0 * img) / p.gW;
                 mbar_wait(&empty[stage], phase ^ 1u, 11);
@@ -136,7 +137,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
                     const uint64_t ad = make_smem_desc_sw128(sa, kSlabBytes, 1024);
                     const uint64_t bd = make_smem_desc_sw128(sa + 2 * kSlabBytes, kSlabBytes, 1024);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
+                    for (int k = 0; k < KC / 16; ++k) {
                         // advance 16 pixels = 16 rows x 128 B = 2048 B
                         umma_bf16(tmem_base, ad + 128u * k, bd + 128u * k, idesc, (it | k) != 0 ? 1u : 0u);
                     }
@@ -189,10 +190,10 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
     if (warp == 1) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 
-template <int BN>
+template <int BN, int KC>
 cudaError_t launch_one(const CUtensorMap& x, const CUtensorMap& dy, const WgradParams& p, cudaStream_t stream) {
-    using Cfg = WgCfg<BN>;
-    auto kern = wgrad_kernel<BN>;
+    using Cfg = WgCfg<BN, KC>;
+    auto kern = wgrad_kernel<BN, KC>;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
@@ -208,10 +209,17 @@ cudaError_t launch_one(const CUtensorMap& x, const CUtensorMap& dy, const WgradP
 
 cudaError_t launch_wgrad(int bn, const CUtensorMap& x, const CUtensorMap& dy, const WgradParams& p,
                          cudaStream_t stream) {
+    if (p.k_pixels == 128) {
+        switch (bn) {
+            case 64: return launch_one<64, 128>(x, dy, p, stream);
+            case 128: return launch_one<128, 128>(x, dy, p, stream);
+            default: return cudaErrorInvalidValue;
+        }
+    }
     switch (bn) {
-        case 64: return launch_one<64>(x, dy, p, stream);
-        case 128: return launch_one<128>(x, dy, p, stream);
-        case 256: return launch_one<256>(x, dy, p, stream);
+        case 64: return launch_one<64, 64>(x, dy, p, stream);
+        case 128: return launch_one<128, 64>(x, dy, p, stream);
+        case 256: return launch_one<256, 64>(x, dy, p, stream);
         default: return cudaErrorInvalidValue;
     }
 }
