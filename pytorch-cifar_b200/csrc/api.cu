@@ -452,7 +452,8 @@ int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, cons
                      const float* res_scale, const float* res_shift, void* out, long long rows, int channels,
                      int relu, void* stream) {
     if (!y || !scale || !shift || !out || rows < 0 || channels < 8 || (channels & 7)) return B2C_ERR_ARG;
-    if (!aligned16(y) || !aligned16(out) || !aligned16(res) || !aligned16(scale) || !aligned16(shift))
+    if (!aligned16(y) || !aligned16(out) || !aligned16(res) || !aligned16(scale) || !aligned16(shift) ||
+        !aligned16(res_scale) || !aligned16(res_shift))
         return B2C_ERR_ARG;
     if ((res_scale == nullptr) != (res_shift == nullptr)) return B2C_ERR_ARG;
     if (res_scale != nullptr && res == nullptr) return B2C_ERR_ARG;
@@ -504,7 +505,9 @@ int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const f
                      const void* add, void* dy, long long rows, int channels, void* stream) {
     if (!dz || !y || !coef_a || !coef_b || !coef_c || !dy || rows < 0 || channels < 8 || (channels & 7))
         return B2C_ERR_ARG;
-    if (!aligned16(dz) || !aligned16(y) || !aligned16(dy) || !aligned16(add)) return B2C_ERR_ARG;
+    if (!aligned16(dz) || !aligned16(y) || !aligned16(dy) || !aligned16(add) || !aligned16(coef_a) ||
+        !aligned16(coef_b) || !aligned16(coef_c))
+        return B2C_ERR_ARG;
     if (rows == 0) return 0;
     return cuda_rc(b2c::launch_bn_bwd_apply(dz, y, coef_a, coef_b, coef_c, add, dy, rows, channels,
                                             as_stream(stream)));

@@ -93,36 +93,46 @@ __global__ void bn_eval_scale_shift_kernel(int C, const float* __restrict__ gamm
 // `F.relu(out)` models/resnet.py:47-50. 16-byte vectors of 8 channels; C % 8 == 0.
 //   out = act( y*scale + shift  [+ res]  or  [+ res*res_scale + res_shift] )
 // ------------------------------------------------------------------------------------------------
+template <bool kUniform>
 __global__ void __launch_bounds__(256)
 bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
                     const uint4* __restrict__ res, const float* __restrict__ res_scale,
                     const float* __restrict__ res_shift, uint4* __restrict__ out, long long nvec, int C, int relu) {
+    // kUniform: the grid stride is a multiple of C/8, so a thread sees the same 8 channels in every iteration and
+    // keeps their scale / shift in registers (no 64-bit modulo, no per-element parameter loads in the loop).
     const int cvec = C >> 3;
-    for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec;
-         v += static_cast<long long>(gridDim.x) * blockDim.x) {
-        const int c0 = static_cast<int>(v % cvec) << 3;
-        float f[8];
-        unpack8(ld_stream(y + v), f);
+    const long long start = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    float sc[8], sh[8], rs[8], rb[8];
+    auto load_params = [&](int c0) {
         const float4 sa = __ldg(reinterpret_cast<const float4*>(scale + c0));
         const float4 sb = __ldg(reinterpret_cast<const float4*>(scale + c0 + 4));
         const float4 ha = __ldg(reinterpret_cast<const float4*>(shift + c0));
         const float4 hb = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
-        f[0] = fmaf(f[0], sa.x, ha.x); f[1] = fmaf(f[1], sa.y, ha.y);
-        f[2] = fmaf(f[2], sa.z, ha.z); f[3] = fmaf(f[3], sa.w, ha.w);
-        f[4] = fmaf(f[4], sb.x, hb.x); f[5] = fmaf(f[5], sb.y, hb.y);
-        f[6] = fmaf(f[6], sb.z, hb.z); f[7] = fmaf(f[7], sb.w, hb.w);
+        sc[0] = sa.x; sc[1] = sa.y; sc[2] = sa.z; sc[3] = sa.w; sc[4] = sb.x; sc[5] = sb.y; sc[6] = sb.z; sc[7] = sb.w;
+        sh[0] = ha.x; sh[1] = ha.y; sh[2] = ha.z; sh[3] = ha.w; sh[4] = hb.x; sh[5] = hb.y; sh[6] = hb.z; sh[7] = hb.w;
+        if (res_scale != nullptr) {
+            const float4 ra = __ldg(reinterpret_cast<const float4*>(res_scale + c0));
+            const float4 rc = __ldg(reinterpret_cast<const float4*>(res_scale + c0 + 4));
+            const float4 ta = __ldg(reinterpret_cast<const float4*>(res_shift + c0));
+            const float4 tb = __ldg(reinterpret_cast<const float4*>(res_shift + c0 + 4));
+            rs[0] = ra.x; rs[1] = ra.y; rs[2] = ra.z; rs[3] = ra.w; rs[4] = rc.x; rs[5] = rc.y; rs[6] = rc.z; rs[7] = rc.w;
+            rb[0] = ta.x; rb[1] = ta.y; rb[2] = ta.z; rb[3] = ta.w; rb[4] = tb.x; rb[5] = tb.y; rb[6] = tb.z; rb[7] = tb.w;
+        }
+    };
+    if (kUniform) load_params(static_cast<int>(start % cvec) << 3);
+    for (long long v = start; v < nvec; v += step) {
+        if (!kUniform) load_params(static_cast<int>(v % cvec) << 3);
+        float f[8];
+        unpack8(ld_stream(y + v), f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[e], sh[e]);
         if (res != nullptr) {
             float r[8];
             unpack8(ld_stream(res + v), r);
             if (res_scale != nullptr) {
-                const float4 ra = __ldg(reinterpret_cast<const float4*>(res_scale + c0));
-                const float4 rb = __ldg(reinterpret_cast<const float4*>(res_scale + c0 + 4));
-                const float4 ta = __ldg(reinterpret_cast<const float4*>(res_shift + c0));
-                const float4 tb = __ldg(reinterpret_cast<const float4*>(res_shift + c0 + 4));
-                r[0] = fmaf(r[0], ra.x, ta.x); r[1] = fmaf(r[1], ra.y, ta.y);
-                r[2] = fmaf(r[2], ra.z, ta.z); r[3] = fmaf(r[3], ra.w, ta.w);
-                r[4] = fmaf(r[4], rb.x, tb.x); r[5] = fmaf(r[5], rb.y, tb.y);
-                r[6] = fmaf(r[6], rb.z, tb.z); r[7] = fmaf(r[7], rb.w, tb.w);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) r[e] = fmaf(r[e], rs[e], rb[e]);
             }
 #pragma unroll
             for (int e = 0; e < 8; ++e) f[e] += r[e];
@@ -224,22 +234,35 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int pr
     }
 }
 
-// Pass 3: dy = A*dz + B*y + Cc (+ add) (bf16 out).
+// Pass 3: dy = A*dz + B*y + Cc (+ add) (bf16 out). kUniform as in bn_act_apply_kernel.
+template <bool kUniform>
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, const float* __restrict__ coefA,
                     const float* __restrict__ coefB, const float* __restrict__ coefC, const uint4* __restrict__ add,
                     uint4* __restrict__ dy, long long nvec, int C) {
     const int cvec = C >> 3;
-    for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec;
-         v += static_cast<long long>(gridDim.x) * blockDim.x) {
-        const int c0 = static_cast<int>(v % cvec) << 3;
+    const long long start = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    float ca[8], cb[8], cc[8];
+    auto load_params = [&](int c0) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float4 a4 = __ldg(reinterpret_cast<const float4*>(coefA + c0 + 4 * h));
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(coefB + c0 + 4 * h));
+            const float4 c4 = __ldg(reinterpret_cast<const float4*>(coefC + c0 + 4 * h));
+            ca[4 * h] = a4.x; ca[4 * h + 1] = a4.y; ca[4 * h + 2] = a4.z; ca[4 * h + 3] = a4.w;
+            cb[4 * h] = b4.x; cb[4 * h + 1] = b4.y; cb[4 * h + 2] = b4.z; cb[4 * h + 3] = b4.w;
+            cc[4 * h] = c4.x; cc[4 * h + 1] = c4.y; cc[4 * h + 2] = c4.z; cc[4 * h + 3] = c4.w;
+        }
+    };
+    if (kUniform) load_params(static_cast<int>(start % cvec) << 3);
+    for (long long v = start; v < nvec; v += step) {
+        if (!kUniform) load_params(static_cast<int>(v % cvec) << 3);
         float d[8], yy[8], o[8];
         unpack8(ld_stream(dz + v), d);
         unpack8(ld_stream(y + v), yy);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            o[e] = fmaf(__ldg(coefA + c0 + e), d[e], fmaf(__ldg(coefB + c0 + e), yy[e], __ldg(coefC + c0 + e)));
-        }
+        for (int e = 0; e < 8; ++e) o[e] = fmaf(ca[e], d[e], fmaf(cb[e], yy[e], cc[e]));
         if (add != nullptr) {
             float a[8];
             unpack8(ld_stream(add + v), a);
@@ -679,9 +702,15 @@ cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* 
                                 const float* res_scale, const float* res_shift, void* out, long long rows, int C,
                                 int relu, cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
-    bn_act_apply_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(
-        static_cast<const uint4*>(y), scale, shift, static_cast<const uint4*>(res), res_scale, res_shift,
-        static_cast<uint4*>(out), nvec, C, relu);
+    const int grid = grid_for(nvec, 256, 148 * 8);
+    if ((static_cast<long long>(grid) * 256) % (C >> 3) == 0)
+        bn_act_apply_kernel<true><<<grid, 256, 0, s>>>(static_cast<const uint4*>(y), scale, shift,
+                                                       static_cast<const uint4*>(res), res_scale, res_shift,
+                                                       static_cast<uint4*>(out), nvec, C, relu);
+    else
+        bn_act_apply_kernel<false><<<grid, 256, 0, s>>>(static_cast<const uint4*>(y), scale, shift,
+                                                        static_cast<const uint4*>(res), res_scale, res_shift,
+                                                        static_cast<uint4*>(out), nvec, C, relu);
     return cudaGetLastError();
 }
 
@@ -720,9 +749,15 @@ cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coef
                                 const float* coefC, const void* add, void* dy, long long rows, int C,
                                 cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
-    bn_bwd_apply_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(
-        static_cast<const uint4*>(dz), static_cast<const uint4*>(y), coefA, coefB, coefC,
-        static_cast<const uint4*>(add), static_cast<uint4*>(dy), nvec, C);
+    const int grid = grid_for(nvec, 256, 148 * 8);
+    if ((static_cast<long long>(grid) * 256) % (C >> 3) == 0)
+        bn_bwd_apply_kernel<true><<<grid, 256, 0, s>>>(static_cast<const uint4*>(dz), static_cast<const uint4*>(y),
+                                                       coefA, coefB, coefC, static_cast<const uint4*>(add),
+                                                       static_cast<uint4*>(dy), nvec, C);
+    else
+        bn_bwd_apply_kernel<false><<<grid, 256, 0, s>>>(static_cast<const uint4*>(dz), static_cast<const uint4*>(y),
+                                                        coefA, coefB, coefC, static_cast<const uint4*>(add),
+                                                        static_cast<uint4*>(dy), nvec, C);
     return cudaGetLastError();
 }
 
