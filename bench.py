@@ -137,6 +137,11 @@ def count_launches(calls):
         if name == "b2c_conv_dgrad":
             d = a[0]._obj
             n += 4 if (d.stride == 2 and d.ksize == 3) else 1
+        elif name == "b2c_conv_wgrad":
+            d = a[0]._obj      # halo kernel + split reduction when a scratch buffer is passed and the shape qualifies
+            halo = a[4] is not None and d.ksize == 3 and d.stride == 1 and d.h == d.w and d.w in (16, 32) \
+                and ((d.cin == 64 and d.cout == 64) or (d.flags & 2)) and d.kflat_cin == 0 and d.cin_valid in (0, d.cin) and d.cout_valid in (0, d.cout)
+            n += 2 if halo else 1
         else:
             n += LAUNCHES[name]
     return n

@@ -50,7 +50,8 @@ typedef struct B2cConvDesc {
     int kflat_cin;   /* wgrad only: >0 for the im2col'ed stem, whose `cin` axis is k = tap*kflat_cin + c */
     int block_n;     /* GEMM N tile (64/128/256); 0 = choose */
     int max_ctas;    /* persistent grid cap; 0 = 148 (one CTA per SM) */
-    int flags;       /* bit 0: force the per-tap kernel (conv_gemm.cu) where the halo kernel would be chosen */
+    int flags;       /* bit 0: force the per-tap kernels where a halo-reuse kernel would be chosen;
+                        bit 1: wgrad: take the halo-reuse kernel for any qualifying shape, not just 64x64 channels */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)
@@ -72,7 +73,12 @@ B2C_API int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_d
 /* dw[cout_valid,cin_valid,k,k] (fp32, OIHW = the reference's .grad layout) += sum over pixels of x * dy.
  * Replaces cudnn_convolution_backward_weight, main.py:104. Accumulates with fp32 atomics: the caller
  * zero-fills dw (optimizer.zero_grad(), main.py:101). */
-B2C_API int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, void* stream);
+B2C_API int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, float* scratch,
+                   long long scratch_floats, void* stream);
+/* scratch (optional): with at least 40960 floats (ideally 148*40960 = 24 MB) 3x3 stride-1 convs on 16- or
+ * 32-pixel images take the halo-reuse kernel, which writes split-K partial tiles there and sums them into dw
+ * with a second small kernel (no atomics, run-to-run deterministic). Without it, or for other shapes, split-K
+ * partials are combined with fp32 atomics directly in dw. */
 
 /* Depthwise 3x3 convolution, nn.Conv2d(C, C, 3, stride, padding=1, groups=C, bias=False), models/mobilenetv2.py:20,
  * and its two gradients (main.py:104). x [n,h,w,channels] bf16, weight = the fp32 master tensor [c_valid,1,3,3];

@@ -321,11 +321,43 @@ int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, vo
     return 0;
 }
 
-int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, void* stream) {
+int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, float* scratch,
+                   long long scratch_floats, void* stream) {
     int rc = check_conv(d);
     if (rc) return rc;
-    if (!x || !dy || !dw || !aligned16(x) || !aligned16(dy)) return B2C_ERR_ARG;
+    if (!x || !dy || !dw || !aligned16(x) || !aligned16(dy) || !aligned16(scratch)) return B2C_ERR_ARG;
     const int ho = d->h / d->stride, wo = d->w / d->stride;
+    // halo-reuse kernel: 3x3 stride 1, square 16/32-pixel images, unpadded channel counts, scratch provided.
+    // Measured (profiles/r1b_conv_layer_times.json): a win for 64x64 channel slabs (125 -> 103 us), not for 128x128
+    // (95 -> 103 us, the N=64 MMAs are shared-memory-operand bound), so larger layers keep the atomic kernel unless
+    // flags bit 1 asks for the halo kernel.
+    if (scratch != nullptr && !(d->flags & 1) && ((d->cin == 64 && d->cout == 64) || (d->flags & 2)) && d->ksize == 3 && d->stride == 1 && d->h == d->w &&
+        (d->w == 16 || d->w == 32) && (d->cin_valid == 0 || d->cin_valid == d->cin) &&
+        (d->cout_valid == 0 || d->cout_valid == d->cout) && d->kflat_cin == 0) {
+        b2c::WgradHaloParams hp = {};
+        hp.cin_slabs = d->cin / 64;
+        hp.cout_slabs = d->cout / 64;
+        hp.tiles_h = d->h / 16;
+        hp.tiles_w = d->w / 8;
+        hp.num_tiles = d->n * hp.tiles_h * hp.tiles_w;
+        const int units = hp.cin_slabs * hp.cout_slabs;
+        const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+        long long splits = max_ctas / units;
+        const long long fit = scratch_floats / (static_cast<long long>(units) * 5 * 128 * 64);
+        if (splits > fit) splits = fit;
+        if (splits > hp.num_tiles) splits = hp.num_tiles;
+        if (splits >= 1) {
+            hp.tiles_per_split = static_cast<int>((hp.num_tiles + splits - 1) / splits);
+            hp.splits = (hp.num_tiles + hp.tiles_per_split - 1) / hp.tiles_per_split;
+            hp.partial = scratch;
+            CUtensorMap mx, mdy;
+            rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, 10, 18, 1, 1);
+            if (rc) return rc;
+            rc = encode_nhwc(&mdy, dy, d->n, d->h, d->w, d->cout, 8, 16, 1, 1);
+            if (rc) return rc;
+            return cuda_rc(b2c::launch_wgrad_halo(mx, mdy, hp, dw, as_stream(stream)));
+        }
+    }
     const int bn = pick_bn(d->block_n, d->cout, 1 << 20);
     const int kpx = (bn <= 128 && grid_tiles(ho, wo, 128)) ? 128 : 64;     // pixels per k-step
     if (!grid_tiles(ho, wo, kpx)) return B2C_ERR_UNSUPPORTED;

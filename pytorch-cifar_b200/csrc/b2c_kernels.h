@@ -80,6 +80,16 @@ cudaError_t launch_conv_halo(int bn, const CUtensorMap& a, const CUtensorMap& b,
                              int* stat_rows, cudaStream_t stream);
 cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                             const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream);
+// 3x3 stride-1 wgrad with halo reuse (conv_wgrad_halo.cu)
+struct WgradHaloParams {
+    int cin_slabs, cout_slabs;   // 64-channel slabs
+    int splits, tiles_per_split; // split-K over 16x8-pixel tiles
+    int num_tiles, tiles_h, tiles_w;
+    float* partial;              // [cin_slabs*cout_slabs][splits][5][128][64] fp32
+};
+size_t wgrad_halo_scratch_floats(int cin, int cout, int splits);
+cudaError_t launch_wgrad_halo(const CUtensorMap& x, const CUtensorMap& dy, const WgradHaloParams& p, float* dw,
+                              cudaStream_t stream);
 cudaError_t launch_wgrad(int bn, const CUtensorMap& x, const CUtensorMap& dy, const WgradParams& p,
                          cudaStream_t stream);
 

@@ -264,6 +264,7 @@ class ConvUnit:
         else:
             self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride)
             self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout)
+        self.eng_scratch = eng.wgrad_scratch
         self.wf = eng.wf_view(name)
         self.wd = None if stem else eng.wd_view(name)
         self.dw = eng.grad_view(name + ".weight")
@@ -298,7 +299,7 @@ class ConvUnit:
         ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add)
 
     def wgrad(self, dy):
-        ops.conv_wgrad(self.desc_w, self.x, dy, self.dw)
+        ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch)
 
     def dgrad(self, dy, dx, add_src=None):
         ops.conv_dgrad(self.desc, dy, self.wd, dx, add_src)
@@ -345,6 +346,8 @@ class Engine:
         self.part_sq = torch.zeros(stat_rows, 2048, **f32)
         self.bwd_partial = torch.zeros(148 * 4 * 2 * 2048, **f32)
         self.coef_a, self.coef_b, self.coef_c = (torch.zeros(2048, **f32) for _ in range(3))
+        self.wgrad_scratch = share_from.wgrad_scratch if share_from is not None else \
+            torch.zeros(ops.WGRAD_SCRATCH_FLOATS, **f32)
         self.fwd_ops, self.bwd_ops = [], []
         if spec["family"] == "resnet":
             self._build_resnet()

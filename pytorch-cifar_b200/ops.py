@@ -67,10 +67,15 @@ def conv_dgrad(d, dy, w_dgrad, dx, add_src=None):
           "b2c_conv_dgrad")
 
 
-def conv_wgrad(d, x, dy, dw):
+WGRAD_SCRATCH_FLOATS = 148 * 5 * 128 * 64      # 24 MB: one partial tile set per CTA of the halo wgrad kernel
+
+
+def conv_wgrad(d, x, dy, dw, scratch=None):
     lib = _lib.load()
     _need(x, torch.bfloat16, "x"); _need(dy, torch.bfloat16, "dy"); _need(dw, torch.float32, "dw")
-    check(lib.b2c_conv_wgrad(ctypes.byref(d), _p(x), _p(dy), _p(dw), _stream()), "b2c_conv_wgrad")
+    _need(scratch, torch.float32, "scratch")
+    check(lib.b2c_conv_wgrad(ctypes.byref(d), _p(x), _p(dy), _p(dw), _p(scratch),
+                             0 if scratch is None else scratch.numel(), _stream()), "b2c_conv_wgrad")
 
 
 def dwconv_fprop(x, weight, y, c_valid, stride, part_sum=None, part_sq=None):

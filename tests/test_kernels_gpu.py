@@ -175,6 +175,29 @@ def test_conv_wgrad(ops, shape):
     assert rel_err(dw, 2 * ref) < F32_TOL
 
 
+@pytest.mark.parametrize("shape", [(4, 32, 32, 64, 64), (8, 16, 16, 128, 128), (3, 16, 16, 64, 128), (64, 32, 32, 64, 64)])
+def test_conv_wgrad_halo_kernel(ops, shape):
+    """With a scratch buffer the 3x3 stride-1 wgrad on 16/32-pixel images takes the halo-reuse kernel."""
+    n, h, w, cin, cout = shape
+    x = nhwc_bf16(n, h, w, cin, 30)
+    dy = nhwc_bf16(n, h, w, cout, 31, scale=0.2)
+    ref = torch.nn.grad.conv2d_weight(to_nchw(x), (cout, cin, 3, 3), to_nchw(dy), padding=1)
+    d = ops.conv_desc(n, h, w, cin, cout, 3, 1, flags=2)
+    for floats in (ops.WGRAD_SCRATCH_FLOATS, 3 * (cin // 64) * (cout // 64) * 5 * 128 * 64):   # full and tight scratch
+        scratch = torch.full((floats,), float("nan"), device="cuda")
+        dw = torch.zeros(cout, cin, 3, 3, device="cuda")
+        ops.conv_wgrad(d, x, dy, dw, scratch=scratch)
+        torch.cuda.synchronize()
+        assert rel_err(dw, ref) < F32_TOL
+        ops.conv_wgrad(d, x, dy, dw, scratch=scratch)              # accumulates like the atomic kernel
+        torch.cuda.synchronize()
+        assert rel_err(dw, 2 * ref) < F32_TOL
+    dw2 = torch.zeros(cout, cin, 3, 3, device="cuda")
+    ops.conv_wgrad(d, x, dy, dw2)                                  # no scratch: atomic kernel, same answer
+    torch.cuda.synchronize()
+    assert rel_err(dw2, ref) < F32_TOL
+
+
 def test_conv_wgrad_large_k_split(ops):
     n, h, w, cin, cout = 128, 32, 32, 64, 64
     x = nhwc_bf16(n, h, w, cin, 12)

@@ -11,6 +11,7 @@ shapes = [(32, 64, 64, 3, 1), (32, 64, 128, 3, 2), (32, 64, 128, 1, 2), (16, 128
           (16, 128, 256, 1, 2), (8, 256, 256, 3, 1), (8, 256, 512, 3, 2), (8, 256, 512, 1, 2), (4, 512, 512, 3, 1),
           (32, 64, 64, 1, 1)]
 flush = torch.empty(256 * 2 ** 20, dtype=torch.uint8, device="cuda")
+scratch = torch.zeros(ops.WGRAD_SCRATCH_FLOATS, device="cuda")
 
 
 def timeit(fn, reps=5):
@@ -50,6 +51,8 @@ for (hw, cin, cout, k, s) in shapes:
                 row[f"err_{tag}"] = str(e)[:60]
     d = ops.conv_desc(N, hw, hw, cin, cout, k, s)
     t = timeit(lambda: ops.conv_wgrad(d, x, dy, dw))
+    row["wgrad_atomic_us"] = round(t, 1); row["wgrad_atomic_tf"] = round(fl / t / 1e6, 0)
+    t = timeit(lambda: ops.conv_wgrad(d, x, dy, dw, scratch=scratch))
     row["wgrad_us"] = round(t, 1); row["wgrad_tf"] = round(fl / t / 1e6, 0)
     out.append(row)
     print(json.dumps(row), flush=True)
