@@ -302,3 +302,77 @@ def mobilenetv2_forward(x, params, buffers, training=True, taps=None):
     out = F.relu(_bn(F.conv2d(out, params["conv2.weight"]), "bn2", params, buffers, training)) # :72
     out = F.avg_pool2d(out, 4).view(out.size(0), -1)                                           # :74-75
     return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
+# Bottleneck ResNets (models/resnet.py:54-93,150-160) — ResNet-50/101/152; main_dist.py:136 builds ResNet152
+# ------------------------------------------------------------------------------------------------
+RESNET50_BLOCKS = (3, 4, 6, 3)
+
+
+def _bottleneck_blocks(num_blocks):
+    cin = 64
+    for li, (nb, planes) in enumerate(zip(num_blocks, RESNET_PLANES)):
+        for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+            yield f"layer{li + 1}.{bi}", cin, planes, 4 * planes, s
+            cin = 4 * planes
+
+
+def build_bottleneck_params(seed, num_blocks=RESNET50_BLOCKS):
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 64, 3, 1)
+    bn("bn1", 64)
+    cin_final = 64
+    for name, cin, planes, cout, s in _bottleneck_blocks(num_blocks):
+        conv(name + ".conv1", cin, planes, 1, 1)          # resnet.py:61
+        bn(name + ".bn1", planes)
+        conv(name + ".conv2", planes, planes, 3, s)       # :63-64
+        bn(name + ".bn2", planes)
+        conv(name + ".conv3", planes, cout, 1, 1)         # :66-67
+        bn(name + ".bn3", cout)
+        if s != 1 or cin != cout:                         # :71-76
+            conv(name + ".shortcut.0", cin, cout, 1, s)
+            bn(name + ".shortcut.1", cout)
+        cin_final = cout
+    lin = nn.Linear(cin_final, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def bottleneck_forward(x, params, buffers, training=True, num_blocks=RESNET50_BLOCKS, taps=None):
+    out = F.conv2d(x, params["conv1.weight"], padding=1)
+    if taps is not None:
+        taps["conv1"] = out
+    out = F.relu(_bn(out, "bn1", params, buffers, training))
+    for name, cin, planes, cout, s in _bottleneck_blocks(num_blocks):
+        xin = out
+        o = F.conv2d(xin, params[name + ".conv1.weight"])
+        if taps is not None:
+            taps[name + ".conv1"] = o
+        o = F.relu(_bn(o, name + ".bn1", params, buffers, training))                                  # :87
+        o = F.relu(_bn(F.conv2d(o, params[name + ".conv2.weight"], stride=s, padding=1), name + ".bn2", params,
+                       buffers, training))                                                            # :88
+        o = _bn(F.conv2d(o, params[name + ".conv3.weight"]), name + ".bn3", params, buffers, training)   # :89
+        if (name + ".shortcut.0.weight") in params:
+            sc = _bn(F.conv2d(xin, params[name + ".shortcut.0.weight"], stride=s), name + ".shortcut.1", params, buffers,
+                     training)
+        else:
+            sc = xin
+        out = F.relu(o + sc)                                                                          # :90-91
+    out = F.avg_pool2d(out, 4).view(out.size(0), -1)
+    return F.linear(out, params["linear.weight"], params["linear.bias"])

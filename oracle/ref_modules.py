@@ -50,23 +50,41 @@ class PreActBlock(nn.Module):
         return self.conv2(F.relu(self.bn2(self.conv1(a)))) + skip
 
 
+class Bottleneck(nn.Module):
+    expansion = 4
+
+    def __init__(self, cin, planes, stride):
+        super().__init__()
+        cout = 4 * planes
+        self.conv1, self.bn1 = _conv(cin, planes, 1, 1), nn.BatchNorm2d(planes)
+        self.conv2, self.bn2 = _conv(planes, planes, 3, stride), nn.BatchNorm2d(planes)
+        self.conv3, self.bn3 = _conv(planes, cout, 1, 1), nn.BatchNorm2d(cout)
+        self.shortcut = nn.Sequential()
+        if stride != 1 or cin != cout:
+            self.shortcut = nn.Sequential(_conv(cin, cout, 1, stride), nn.BatchNorm2d(cout))
+
+    def forward(self, x):
+        y = F.relu(self.bn2(self.conv2(F.relu(self.bn1(self.conv1(x))))))
+        return F.relu(self.bn3(self.conv3(y)) + self.shortcut(x))
+
+
 def _stages(block, counts):
     widths, cin, out = (64, 128, 256, 512), 64, []
     for i, (n, w) in enumerate(zip(counts, widths)):
         seq = []
         for j in range(n):
             seq.append(block(cin, w, (1 if i == 0 else 2) if j == 0 else 1))
-            cin = w
+            cin = w * block.expansion
         out.append(nn.Sequential(*seq))
     return out
 
 
 class ResNet(nn.Module):
-    def __init__(self, counts=(2, 2, 2, 2), num_classes=10):
+    def __init__(self, counts=(2, 2, 2, 2), num_classes=10, block=BasicBlock):
         super().__init__()
         self.conv1, self.bn1 = _conv(3, 64, 3, 1), nn.BatchNorm2d(64)
-        self.layer1, self.layer2, self.layer3, self.layer4 = _stages(BasicBlock, counts)
-        self.linear = nn.Linear(512, num_classes)
+        self.layer1, self.layer2, self.layer3, self.layer4 = _stages(block, counts)
+        self.linear = nn.Linear(512 * block.expansion, num_classes)
 
     def forward(self, x):
         y = F.relu(self.bn1(self.conv1(x)))
@@ -145,6 +163,10 @@ class MobileNetV2(nn.Module):
 
 def ResNet18():
     return ResNet((2, 2, 2, 2))
+
+
+def ResNet50():
+    return ResNet((3, 4, 6, 3), block=Bottleneck)
 
 
 def PreActResNet18():

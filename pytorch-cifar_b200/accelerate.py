@@ -9,7 +9,7 @@ What changes: `net.forward` becomes one torch.autograd.Function whose forward/ba
 plan of engine.py; every nn.Parameter / BN buffer becomes a view into the engine's flat fp32 arenas (same
 names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad` tensors handed to autograd
 are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
-Supported compositions: ResNet with BasicBlock (models/resnet.py), VGG (models/vgg.py), PreActResNet with
+Supported compositions: ResNet with BasicBlock or Bottleneck (models/resnet.py), VGG (models/vgg.py), PreActResNet with
 PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py); anything else raises — there is no fallback path.
 
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
@@ -30,9 +30,12 @@ def spec_from_module(net):
     """Derive the engine spec from a reference-style module by structure."""
     if _is(net, "ResNet") and hasattr(net, "layer4") and hasattr(net, "linear") and hasattr(net, "bn1"):
         blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
-        if not all(_is(b, "BasicBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):
-            raise NotImplementedError("accelerate: only BasicBlock ResNets (ResNet-18/34) are supported")
-        return resnet_spec(tuple(blocks), num_classes=net.linear.out_features)
+        kinds = {type(b).__name__ for i in range(1, 5) for b in getattr(net, f"layer{i}")}
+        if kinds == {"BasicBlock"}:
+            return resnet_spec(tuple(blocks), num_classes=net.linear.out_features)
+        if kinds == {"Bottleneck"}:                       # ResNet-50/101/152: what main_dist.py:136 hard-codes
+            return resnet_spec(tuple(blocks), num_classes=net.linear.out_features, bottleneck=True)
+        raise NotImplementedError(f"accelerate: unsupported ResNet block types {sorted(kinds)}")
     if _is(net, "PreActResNet") and hasattr(net, "layer4"):
         blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
         if not all(_is(b, "PreActBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):

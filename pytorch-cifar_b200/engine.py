@@ -29,8 +29,11 @@ def _align(n, a):
 #   buffers: OrderedDict name -> shape (BN running stats; num_batches_tracked handled separately)
 #   layout : model-family specific topology used by the plan builders below
 # --------------------------------------------------------------------------------------------
-def resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=10):
-    """ResNet-18/34 (BasicBlock) exactly as models/resnet.py:96-144 composes it."""
+def resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=10, bottleneck=False):
+    """ResNet-18/34 (BasicBlock) or, with bottleneck=True, ResNet-50/101/152 (Bottleneck, expansion 4) exactly as
+    models/resnet.py:16-93,96-160 composes them."""
+    if bottleneck:
+        return _bottleneck_spec(num_blocks, planes, num_classes)
     params, buffers, blocks = OrderedDict(), OrderedDict(), []
 
     def conv(name, cout, cin, k):
@@ -241,6 +244,42 @@ def _bn_views(u, eng, bn_name, C):
     u.scale, u.shift, u.mean, u.rstd = (eng.new_f32(C) for _ in range(4))
 
 
+def resnet50_spec(num_classes=10):
+    return resnet_spec((3, 4, 6, 3), num_classes=num_classes, bottleneck=True)
+
+
+def _bottleneck_spec(num_blocks, planes, num_classes):
+    params, buffers, blocks = OrderedDict(), OrderedDict(), []
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    params["conv1.weight"] = (64, 3, 3, 3)
+    bn("bn1", 64)
+    cin = 64
+    for li, (nb, pl) in enumerate(zip(num_blocks, planes)):
+        for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+            name, cout = f"layer{li + 1}.{bi}", 4 * pl
+            params[name + ".conv1.weight"] = (pl, cin, 1, 1)
+            bn(name + ".bn1", pl)
+            params[name + ".conv2.weight"] = (pl, pl, 3, 3)
+            bn(name + ".bn2", pl)
+            params[name + ".conv3.weight"] = (cout, pl, 1, 1)
+            bn(name + ".bn3", cout)
+            shortcut = s != 1 or cin != cout
+            if shortcut:
+                params[name + ".shortcut.0.weight"] = (cout, cin, 1, 1)
+                bn(name + ".shortcut.1", cout)
+            blocks.append(dict(name=name, cin=cin, planes=pl, cout=cout, stride=s, shortcut=shortcut))
+            cin = cout
+    params["linear.weight"] = (num_classes, cin)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="bottleneck", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin)
+
+
 class ConvUnit:
     """One conv (+ the BatchNorm that follows it): descriptors, operand views, statistic buffers.
     Channel counts are the reference's; tensors are laid out with channels padded to multiples of 64
@@ -357,6 +396,8 @@ class Engine:
             self._build_preact()
         elif spec["family"] == "mobilenetv2":
             self._build_mobilenetv2()
+        elif spec["family"] == "bottleneck":
+            self._build_bottleneck()
         else:
             raise NotImplementedError(spec["family"])
 
@@ -729,6 +770,95 @@ class Engine:
             Bk.append(bwd)
             dout = dx
         Bk.append(lambda dout=dout: stem.wgrad(dout))
+        self.bwd_ops = Bk
+
+    # ------------------------------------------------------------------ Bottleneck ResNet plan
+    def _build_bottleneck(self):
+        """models/resnet.py:87-92: relu(bn1(conv1 1x1)) -> relu(bn2(conv2 3x3, stride)) -> bn3(conv3 1x1, x4)
+        -> += shortcut(x) (identity, or 1x1 conv(stride) + BN) -> relu. ResNet-50/101/152 (main_dist.py:136)."""
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        stem = ConvUnit(self, "conv1", "bn1", self.x0, 3, 64, 3, 1, 32, 32, stem=True)
+        a0 = self.new_act(N, 32, 32, 64)
+        self.units = [stem]
+        F, blocks = self.fwd_ops, []
+
+        def fwd_stem(training):
+            stem.fprop(self, True)
+            stem.bn_stats(self, training)
+            ops.bn_act_apply(stem.y, stem.scale, stem.shift, a0, stem.rows, 64, relu=True)
+        F.append(fwd_stem)
+        x, H, W = a0, 32, 32
+        for b in spec["blocks"]:
+            name, cin, pl, cout, s = b["name"], b["cin"], b["planes"], b["cout"], b["stride"]
+            c1 = ConvUnit(self, name + ".conv1", name + ".bn1", x, cin, pl, 1, 1, H, W)
+            a1 = self.new_act(N, H, W, pl)
+            c2 = ConvUnit(self, name + ".conv2", name + ".bn2", a1, pl, pl, 3, s, H, W)
+            Ho, Wo = H // s, W // s
+            a2 = self.new_act(N, Ho, Wo, pl)
+            c3 = ConvUnit(self, name + ".conv3", name + ".bn3", a2, pl, cout, 1, 1, Ho, Wo)
+            cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W) \
+                if b["shortcut"] else None
+            out = self.new_act(N, Ho, Wo, cout)
+            self.units += [c1, c2, c3] + ([cs] if cs else [])
+            blocks.append((c1, a1, c2, a2, c3, cs, out, x))
+
+            def fwd(training, c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, x=x):
+                c1.fprop(self)
+                c1.bn_stats(self, training)
+                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
+                c2.fprop(self)
+                c2.bn_stats(self, training)
+                ops.bn_act_apply(c2.y, c2.scale, c2.shift, a2, c2.rows, c2.cout, relu=True)
+                c3.fprop(self)
+                c3.bn_stats(self, training)
+                if cs is not None:
+                    cs.fprop(self)
+                    cs.bn_stats(self, training)
+                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=cs.y,
+                                     res_scale=cs.scale, res_shift=cs.shift)
+                else:
+                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=x)
+            F.append(fwd)
+            x, H, W = out, Ho, Wo
+        fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        for (c1, a1, c2, a2, c3, cs, out, xin) in reversed(blocks):
+            dy3 = self.new_act(*c3.y.shape)
+            dys = self.new_act(*cs.y.shape) if cs is not None else None
+            da2 = self.new_act(*a2.shape)
+            dy2 = self.new_act(*c2.y.shape)
+            da1 = self.new_act(*a1.shape)
+            dy1 = self.new_act(*c1.y.shape)
+            dx = self.new_act(*xin.shape)
+
+            def bwd(c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, dout=dout, dy3=dy3, dys=dys, da2=da2,
+                    dy2=dy2, da1=da1, dy1=dy1, dx=dx):
+                c3.bn_backward(self, dout, out, dout, dy3)            # mask in place -> dz
+                if cs is not None:
+                    cs.bn_backward(self, dout, None, None, dys)
+                c3.wgrad(dy3)
+                c3.dgrad(dy3, da2)
+                c2.bn_backward(self, da2, a2, da2, dy2)
+                c2.wgrad(dy2)
+                c2.dgrad(dy2, da1)
+                c1.bn_backward(self, da1, a1, da1, dy1)
+                c1.wgrad(dy1)
+                if cs is not None:
+                    cs.wgrad(dys)
+                    cs.dgrad(dys, dx)
+                    c1.dgrad(dy1, dx, add_src=dx)
+                else:
+                    c1.dgrad(dy1, dx, add_src=dout)
+            Bk.append(bwd)
+            dout = dx
+        dy0 = self.new_act(*stem.y.shape)
+
+        def bwd_stem(dout=dout):
+            stem.bn_backward(self, dout, a0, dout, dy0)
+            stem.wgrad(dy0)
+        Bk.append(bwd_stem)
         self.bwd_ops = Bk
 
     # ------------------------------------------------------------------ MobileNetV2 plan

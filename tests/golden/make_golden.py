@@ -65,7 +65,7 @@ def golden_other_nets():
     out = dict(x=x.numpy(), target=target.numpy())
     import models.mobilenetv2 as ref_mb
     for tag, ctor in (("vgg16", lambda: ref_vgg.VGG("VGG16")), ("preact18", ref_pre.PreActResNet18),
-                      ("mobilenetv2", ref_mb.MobileNetV2)):
+                      ("mobilenetv2", ref_mb.MobileNetV2), ("resnet50", __import__("models.resnet", fromlist=["x"]).ResNet50)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

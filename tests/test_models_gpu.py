@@ -149,9 +149,13 @@ def test_pointwise_conv_with_padded_channels(ops):
 
 # per-model bounds for the END-TO-END comparison with fp32 (see the module docstring): MobileNetV2 is 52 convs deep
 # with 4x4 feature maps at batch 128, where stock torch bf16 autocast itself is 85 % off on the median gradient.
-BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, min_cos=0.7, drop=0.7),
-          "preact18": dict(logits=5e-2, near=6e-2, min_cos=0.7, drop=0.7),
-          "mobilenetv2": dict(logits=0.25, near=0.15, min_cos=None, drop=0.92)}
+# ResNet-50 (49 convs, 4x expansion) at random init is worse still: stock autocast shows 24 % on the logits and
+# > 100 % on the early-layer gradients, and with lr 0.02 the fp32 oracle itself diverges on this batch (the CUDA
+# path follows the same diverging trajectory step for step) — so it trains with lr 0.002 here.
+BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop=0.7, lr=0.02),
+          "preact18": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop=0.7, lr=0.02),
+          "mobilenetv2": dict(logits=0.25, near=0.15, near_cos=0.99, min_cos=None, drop=0.92, lr=0.02),
+          "resnet50": dict(logits=0.3, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002)}
 
 MODELS = {
     "vgg16": ("vgg_spec", "build_vgg_params", "vgg_forward", "features.0", ["classifier.weight", "features.41.weight",
@@ -160,6 +164,8 @@ MODELS = {
                  ["linear.weight", "layer4.1.conv2.weight", "layer4.1.bn2.weight"]),
     "mobilenetv2": ("mobilenetv2_spec", "build_mobilenetv2_params", "mobilenetv2_forward", "conv1",
                     ["linear.weight", "bn2.weight", "bn2.bias"]),
+    "resnet50": ("resnet50_spec", "build_bottleneck_params", "bottleneck_forward", "conv1",
+                 ["linear.weight", "layer4.2.bn3.weight", "layer4.2.bn3.bias"]),
 }
 
 
@@ -214,7 +220,7 @@ def test_model_training_step(ops, model):
     bnd = BOUNDS[model]
     assert rel(eng.logits, logits_ref) < bnd["logits"] and abs(loss.item() - loss_ref.item()) < 2e-2
     for k in near_loss:                                                 # nearest the loss: tight
-        assert g_rel[k] < bnd["near"] and g_cos[k] > 0.99, (k, g_rel[k], g_cos[k])
+        assert g_rel[k] < bnd["near"] and g_cos[k] > bnd["near_cos"], (k, g_rel[k], g_cos[k])
     if bnd["min_cos"] is not None:
         assert min(g_cos.values()) > bnd["min_cos"], sorted(g_cos.items(), key=lambda kv: kv[1])[:5]
     assert np.median(list(g_rel.values())) < 1.5 * np.median(list(a_rel.values())) + 1e-2
@@ -233,7 +239,8 @@ def test_model_trains(ops, model):
     params, buffers = getattr(nets, build_fn)(0)
     forward = getattr(nets, fwd_fn)
     images, labels = data.learnable_cifar(512, seed=3)
-    tr = trainer.Trainer(getattr(engine, spec_fn)(), N, lr=0.02)
+    lr = BOUNDS[model]["lr"]
+    tr = trainer.Trainer(getattr(engine, spec_fn)(), N, lr=lr)
     tr.load_params(params, {k: v for k, v in buffers.items() if not k.endswith("num_batches_tracked")})
     tr.set_dataset(images, labels)
     idx = np.arange(N)
@@ -248,7 +255,7 @@ def test_model_trains(ops, model):
     tb = torch.from_numpy(labels[:N]).cuda()
     leaves = {k: v.detach().clone().cuda().requires_grad_(True) for k, v in params.items()}
     cb = {k: v.clone().cuda() for k, v in buffers.items()}
-    opt = torch.optim.SGD(list(leaves.values()), lr=0.02, momentum=0.9, weight_decay=5e-4)
+    opt = torch.optim.SGD(list(leaves.values()), lr=lr, momentum=0.9, weight_decay=5e-4)
     ref = []
     for _ in range(8):
         opt.zero_grad()
