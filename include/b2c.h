@@ -122,9 +122,12 @@ B2C_API int b2c_bn_bwd_partial_rows(long long rows, int channels);
 
 /* BatchNorm(+ReLU) backward, reduction pass: per-channel sums of dz and dz*y with dz = dout*[act>0]
  * (act NULL: dz = dout). If dz_out is non-NULL the masked gradient is stored there (may alias dout).
- * Replaces the reductions of cudnn_batch_norm_backward + relu backward, main.py:104. */
+ * Replaces the reductions of cudnn_batch_norm_backward + relu backward, main.py:104.
+ * relu_scale/relu_shift (optional, with act == NULL): the unit is a plain F.relu(bn(y)) whose forward scale/shift
+ * these are; the mask is then recomputed as fma(y, scale, shift) > 0 and neither act nor dz touch memory
+ * (pass the same pair to b2c_bn_bwd_apply, which then takes dout in place of dz). */
 B2C_API int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
-                      int channels, float* partial, void* stream);
+                      int channels, float* partial, const float* relu_scale, const float* relu_shift, void* stream);
 
 /* Combine partial rows: dgamma, dbeta (fp32, written) and the coefficients of dy = A*dz + B*y + C. */
 B2C_API int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, float count, const float* gamma,
@@ -154,7 +157,8 @@ B2C_API int b2c_bn_bwd_stats_noalloc(const void* dout, const void* act, const vo
 /* dy = A*dz + B*y + C per channel (+ add, optional bf16 tensor of dy's shape: the gradient that bypasses
  * the BatchNorm through an identity shortcut, models/preact_resnet.py:29-33). bf16 out. */
 B2C_API int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,
-                     const void* add, void* dy, long long rows, int channels, void* stream);
+                     const void* add, void* dy, long long rows, int channels, const float* relu_scale,
+                     const float* relu_shift, void* stream);
 
 /* nn.MaxPool2d(kernel_size=2, stride=2), models/vgg.py:31, on NHWC bf16 [n,h,w,c] -> [n,h/2,w/2,c]. */
 B2C_API int b2c_maxpool2x2_fwd(const void* x, void* y, int n, int h, int w, int channels, void* stream);

@@ -500,11 +500,14 @@ int b2c_bn_bwd_partial_rows(long long rows, int channels) {
 }
 
 int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
-                      int channels, float* partial, void* stream) {
+                      int channels, float* partial, const float* relu_scale, const float* relu_shift, void* stream) {
     if (!dout || !y || !partial || rows < 1) return B2C_ERR_ARG;
+    if ((relu_scale == nullptr) != (relu_shift == nullptr) || (relu_scale != nullptr && act != nullptr))
+        return B2C_ERR_ARG;
     if (channels < 8 || (channels & 7) || (channels >> 3) > 256) return B2C_ERR_UNSUPPORTED;
     if (!aligned16(dout) || !aligned16(act) || !aligned16(y) || !aligned16(dz_out)) return B2C_ERR_ARG;
-    return cuda_rc(b2c::launch_bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, as_stream(stream)));
+    return cuda_rc(b2c::launch_bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, relu_scale, relu_shift,
+                                             as_stream(stream)));
 }
 
 int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, float count, const float* gamma,
@@ -534,15 +537,17 @@ int b2c_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, v
 }
 
 int b2c_bn_bwd_apply(const void* dz, const void* y, const float* coef_a, const float* coef_b, const float* coef_c,
-                     const void* add, void* dy, long long rows, int channels, void* stream) {
+                     const void* add, void* dy, long long rows, int channels, const float* relu_scale,
+                     const float* relu_shift, void* stream) {
+    if ((relu_scale == nullptr) != (relu_shift == nullptr)) return B2C_ERR_ARG;
     if (!dz || !y || !coef_a || !coef_b || !coef_c || !dy || rows < 0 || channels < 8 || (channels & 7))
         return B2C_ERR_ARG;
     if (!aligned16(dz) || !aligned16(y) || !aligned16(dy) || !aligned16(add) || !aligned16(coef_a) ||
         !aligned16(coef_b) || !aligned16(coef_c))
         return B2C_ERR_ARG;
     if (rows == 0) return 0;
-    return cuda_rc(b2c::launch_bn_bwd_apply(dz, y, coef_a, coef_b, coef_c, add, dy, rows, channels,
-                                            as_stream(stream)));
+    return cuda_rc(b2c::launch_bn_bwd_apply(dz, y, coef_a, coef_b, coef_c, add, dy, rows, channels, relu_scale,
+                                            relu_shift, as_stream(stream)));
 }
 
 int b2c_maxpool2x2_fwd(const void* x, void* y, int n, int h, int w, int channels, void* stream) {

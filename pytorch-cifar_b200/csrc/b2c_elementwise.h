@@ -28,12 +28,14 @@ cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* 
                                 int relu, cudaStream_t s);
 int bn_bwd_partial_rows(long long rows, int C);
 cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
-                                 int C, float* partial, cudaStream_t s);
+                                 int C, float* partial, const float* relu_scale, const float* relu_shift,
+                                 cudaStream_t s);
 cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float count, const float* gamma,
                                    const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
                                    float* coefB, float* coefC, cudaStream_t s);
 cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coefA, const float* coefB,
-                                const float* coefC, const void* add, void* dy, long long rows, int C, cudaStream_t s);
+                                const float* coefC, const void* add, void* dy, long long rows, int C,
+                                const float* relu_scale, const float* relu_shift, cudaStream_t s);
 cudaError_t launch_maxpool_fwd(const void* x, void* y, int n, int h, int w, int C, cudaStream_t s);
 cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int C,
                                cudaStream_t s);

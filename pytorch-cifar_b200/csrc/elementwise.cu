@@ -26,6 +26,25 @@ __device__ __forceinline__ uint4 ld_stream(const uint4* p) {
                  : "l"(p));
     return r;
 }
+// Per-channel parameters re-read every iteration (L1 hit) instead of living in registers: `volatile` keeps the
+// compiler from hoisting the load out of the row loop, which would cost 16 registers and a resident block per SM.
+__device__ __forceinline__ float4 ld_param4(const float* p) {
+    float4 r;
+    asm volatile("ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+// ReLU mask recomputed from the conv output: act = relu(fma(y, scale, shift)) > 0  <=>  fma(y, scale, shift) > 0.
+__device__ __forceinline__ void mask_from_y8(float (&d)[8], const float (&yy)[8], const float* scale,
+                                             const float* shift) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const float4 sc = ld_param4(scale + 4 * h), sh = ld_param4(shift + 4 * h);
+        d[4 * h + 0] = fmaf(yy[4 * h + 0], sc.x, sh.x) > 0.f ? d[4 * h + 0] : 0.f;
+        d[4 * h + 1] = fmaf(yy[4 * h + 1], sc.y, sh.y) > 0.f ? d[4 * h + 1] : 0.f;
+        d[4 * h + 2] = fmaf(yy[4 * h + 2], sc.z, sh.z) > 0.f ? d[4 * h + 2] : 0.f;
+        d[4 * h + 3] = fmaf(yy[4 * h + 3], sc.w, sh.w) > 0.f ? d[4 * h + 3] : 0.f;
+    }
+}
 
 // ------------------------------------------------------------------------------------------------
 // BatchNorm finalize (training statistics). Reference: nn.BatchNorm2d in train mode,
@@ -152,9 +171,11 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
 // branch read dz directly). Each block writes one partial row [2][C]; bn_bwd_finalize combines them.
 // Thread layout: blockDim = 256; thread t owns channel vector (t % cvec) and walks rows.
 // ------------------------------------------------------------------------------------------------
+template <bool kMaskY>
 __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ act, const uint4* __restrict__ y,
-                     uint4* __restrict__ dz_out, long long rows, int C, float* __restrict__ partial) {
+                     uint4* __restrict__ dz_out, long long rows, int C, float* __restrict__ partial,
+                     const float* __restrict__ relu_scale, const float* __restrict__ relu_shift) {
     extern __shared__ float red[];  // [rows_per_iter][2][C]
     const int cvec = C >> 3;
     const int rpi = 256 / cvec;     // rows handled per block iteration (cvec <= 256); threads past rpi*cvec idle
@@ -164,13 +185,16 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ a
     float s1[8], s2[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) { s1[e] = 0.f; s2[e] = 0.f; }
+    // mask from y (the forward's own expression): neither the activation nor a materialised dz is read or written
+    // for plain BN+ReLU units
     for (long long r = static_cast<long long>(blockIdx.x) * rpi + rl; active && r < rows;
          r += static_cast<long long>(gridDim.x) * rpi) {
         const long long v = r * cvec + cv;
         float d[8], yy[8];
         unpack8(ld_stream(dout + v), d);
         unpack8(ld_stream(y + v), yy);
-        if (act != nullptr) {
+        if (kMaskY) mask_from_y8(d, yy, relu_scale + cv * 8, relu_shift + cv * 8);
+        if (!kMaskY && act != nullptr) {
             float a[8];
             unpack8(ld_stream(act + v), a);
 #pragma unroll
@@ -235,16 +259,19 @@ __global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int pr
 }
 
 // Pass 3: dy = A*dz + B*y + Cc (+ add) (bf16 out). kUniform as in bn_act_apply_kernel.
-template <bool kUniform>
+template <bool kUniform, bool kMaskY>
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, const float* __restrict__ coefA,
                     const float* __restrict__ coefB, const float* __restrict__ coefC, const uint4* __restrict__ add,
-                    uint4* __restrict__ dy, long long nvec, int C) {
+                    uint4* __restrict__ dy, long long nvec, int C, const float* __restrict__ relu_scale,
+                    const float* __restrict__ relu_shift) {
     const int cvec = C >> 3;
     const long long start = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
     float ca[8], cb[8], cc[8];
+    int cur_c0 = 0;
     auto load_params = [&](int c0) {
+        cur_c0 = c0;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const float4 a4 = __ldg(reinterpret_cast<const float4*>(coefA + c0 + 4 * h));
@@ -261,6 +288,8 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, c
         float d[8], yy[8], o[8];
         unpack8(ld_stream(dz + v), d);
         unpack8(ld_stream(y + v), yy);
+        // dz was not materialised: apply the ReLU mask here (same expression as the reduce pass)
+        if (kMaskY) mask_from_y8(d, yy, relu_scale + cur_c0, relu_shift + cur_c0);
 #pragma unroll
         for (int e = 0; e < 8; ++e) o[e] = fmaf(ca[e], d[e], fmaf(cb[e], yy[e], cc[e]));
         if (add != nullptr) {
@@ -723,15 +752,22 @@ int bn_bwd_partial_rows(long long rows, int C) {
 }
 
 cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
-                                 int C, float* partial, cudaStream_t s) {
+                                 int C, float* partial, const float* relu_scale, const float* relu_shift,
+                                 cudaStream_t s) {
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     const int rpi = 256 / cvec;
     const int blocks = bn_bwd_partial_rows(rows, C);
     const size_t smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
-    bn_bwd_reduce_kernel<<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), static_cast<const uint4*>(act),
-                                                  static_cast<const uint4*>(y), static_cast<uint4*>(dz_out), rows,
-                                                  C, partial);
+    if (act == nullptr && relu_scale != nullptr)
+        bn_bwd_reduce_kernel<true><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), nullptr,
+                                                            static_cast<const uint4*>(y), nullptr, rows, C, partial,
+                                                            relu_scale, relu_shift);
+    else
+        bn_bwd_reduce_kernel<false><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout),
+                                                             static_cast<const uint4*>(act),
+                                                             static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
+                                                             rows, C, partial, nullptr, nullptr);
     return cudaGetLastError();
 }
 
@@ -747,17 +783,20 @@ cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float 
 
 cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coefA, const float* coefB,
                                 const float* coefC, const void* add, void* dy, long long rows, int C,
-                                cudaStream_t s) {
+                                const float* relu_scale, const float* relu_shift, cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
     const int grid = grid_for(nvec, 256, 148 * 8);
-    if ((static_cast<long long>(grid) * 256) % (C >> 3) == 0)
-        bn_bwd_apply_kernel<true><<<grid, 256, 0, s>>>(static_cast<const uint4*>(dz), static_cast<const uint4*>(y),
-                                                       coefA, coefB, coefC, static_cast<const uint4*>(add),
-                                                       static_cast<uint4*>(dy), nvec, C);
-    else
-        bn_bwd_apply_kernel<false><<<grid, 256, 0, s>>>(static_cast<const uint4*>(dz), static_cast<const uint4*>(y),
-                                                        coefA, coefB, coefC, static_cast<const uint4*>(add),
-                                                        static_cast<uint4*>(dy), nvec, C);
+    const bool uniform = (static_cast<long long>(grid) * 256) % (C >> 3) == 0;
+    const bool masky = relu_scale != nullptr;
+    auto go = [&](auto kern) {
+        kern<<<grid, 256, 0, s>>>(static_cast<const uint4*>(dz), static_cast<const uint4*>(y), coefA, coefB, coefC,
+                                  static_cast<const uint4*>(add), static_cast<uint4*>(dy), nvec, C, relu_scale,
+                                  relu_shift);
+    };
+    if (uniform && masky) go(bn_bwd_apply_kernel<true, true>);
+    else if (uniform) go(bn_bwd_apply_kernel<true, false>);
+    else if (masky) go(bn_bwd_apply_kernel<false, true>);
+    else go(bn_bwd_apply_kernel<false, false>);
     return cudaGetLastError();
 }
 
@@ -899,7 +938,7 @@ cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const
     cudaError_t e = noalloc_scratch(&scratch);
     if (e != cudaSuccess) return e;
     const int prow = bn_bwd_partial_rows(rows, C);               // <= kNoAllocMaxRows by construction
-    e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, s);
+    e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, nullptr, nullptr, s);
     if (e != cudaSuccess) return e;
     return launch_bn_bwd_finalize(scratch, prow, C, count, gamma, mean, rstd, dgamma, dbeta, coefA, coefB, coefC, s);
 }

@@ -327,15 +327,21 @@ class ConvUnit:
                                     self.shift, conv_bias=getattr(self, "conv_bias", None))
 
     # ---- backward pieces
-    def bn_backward(self, eng, dout, act, dz_out, dy, add=None):
+    def bn_backward(self, eng, dout, act, dz_out, dy, add=None, relu_from_y=False):
         """dout: grad w.r.t. act(bn(y)) (or w.r.t. bn(y) when act is None). Writes dz (optional) and
-        dy = dBN/dy (+ add)."""
+        dy = dBN/dy (+ add). relu_from_y: the unit is a plain relu(bn(y)) and nothing else needs dz: the mask is
+        recomputed from y with this BN's own scale/shift, so neither `act` is read nor dz written."""
         prow = ops.bn_bwd_partial_rows(self.rows, self.cout)
-        ops.bn_bwd_reduce(dout, act, self.y, dz_out, self.rows, self.cout, eng.bwd_partial)
+        if relu_from_y:
+            ops.bn_bwd_reduce(dout, None, self.y, None, self.rows, self.cout, eng.bwd_partial, self.scale, self.shift)
+        else:
+            ops.bn_bwd_reduce(dout, act, self.y, dz_out, self.rows, self.cout, eng.bwd_partial)
         ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
                             self.dgamma, self.dbeta, eng.coef_a, eng.coef_b, eng.coef_c)
-        src = dz_out if dz_out is not None else dout
-        ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add)
+        src = dz_out if (dz_out is not None and not relu_from_y) else dout
+        ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add,
+                         relu_scale=self.scale if relu_from_y else None,
+                         relu_shift=self.shift if relu_from_y else None)
 
     def wgrad(self, dy):
         ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch)
@@ -604,7 +610,7 @@ class Engine:
                 c2.wgrad(dy2)
                 c2.dgrad(dy2, da1)
                 # a1 = relu(bn1(y1))
-                c1.bn_backward(self, da1, a1, da1, dy1)
+                c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dys)
@@ -619,7 +625,7 @@ class Engine:
         dy0 = self.new_act(*stem.y.shape)
 
         def bwd_stem(dout=dout, dy0=dy0):
-            stem.bn_backward(self, dout, a0, dout, dy0)
+            stem.bn_backward(self, dout, a0, dout, dy0, relu_from_y=True)
             stem.wgrad(dy0)
         Bk.append(bwd_stem)
         self.bwd_ops = Bk
@@ -689,7 +695,7 @@ class Engine:
                 if pooled is not None:
                     ops.maxpool2x2_bwd(act, pooled, dout, dact)
                     g = dact
-                u.bn_backward(self, g, act, g, dy)
+                u.bn_backward(self, g, act, g, dy, relu_from_y=True)
                 u.wgrad(dy)
                 if dx is not None:
                     u.dgrad(dy, dx)
@@ -757,16 +763,16 @@ class Engine:
             def bwd(bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, cs=cs, dout=dout, da2=da2, dy1=dy1, da=da, dx=dx):
                 c2.wgrad(dout)                              # d(conv2 out) = d(block out)
                 c2.dgrad(dout, da2)
-                c1.bn_backward(self, da2, a2, da2, dy1)     # a2 = relu(bn2(conv1 out))
+                c1.bn_backward(self, da2, a2, da2, dy1, relu_from_y=True)     # a2 = relu(bn2(conv1 out))
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dout)
                     cs.dgrad(dout, da)                      # zero-fill + even pixels
                     c1.dgrad(dy1, da, add_src=da)
-                    bn1.bn_backward(self, da, a, da, dx)    # a = relu(bn1(x)); no identity path
+                    bn1.bn_backward(self, da, a, da, dx, relu_from_y=True)    # a = relu(bn1(x)); no identity path
                 else:
                     c1.dgrad(dy1, da)
-                    bn1.bn_backward(self, da, a, da, dx, add=dout)   # + gradient through the identity shortcut
+                    bn1.bn_backward(self, da, a, da, dx, add=dout, relu_from_y=True)   # + gradient through the identity shortcut
             Bk.append(bwd)
             dout = dx
         Bk.append(lambda dout=dout: stem.wgrad(dout))
@@ -840,10 +846,10 @@ class Engine:
                     cs.bn_backward(self, dout, None, None, dys)
                 c3.wgrad(dy3)
                 c3.dgrad(dy3, da2)
-                c2.bn_backward(self, da2, a2, da2, dy2)
+                c2.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
                 c2.wgrad(dy2)
                 c2.dgrad(dy2, da1)
-                c1.bn_backward(self, da1, a1, da1, dy1)
+                c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dys)
@@ -856,7 +862,7 @@ class Engine:
         dy0 = self.new_act(*stem.y.shape)
 
         def bwd_stem(dout=dout):
-            stem.bn_backward(self, dout, a0, dout, dy0)
+            stem.bn_backward(self, dout, a0, dout, dy0, relu_from_y=True)
             stem.wgrad(dy0)
         Bk.append(bwd_stem)
         self.bwd_ops = Bk
@@ -929,7 +935,7 @@ class Engine:
         dxh = self.new_act(*x.shape)
 
         def bwd_last(dout=dout):
-            ch.bn_backward(self, dout, ah, dout, dyh)
+            ch.bn_backward(self, dout, ah, dout, dyh, relu_from_y=True)
             ch.wgrad(dyh)
             ch.dgrad(dyh, dxh)
         Bk.append(bwd_last)
@@ -950,10 +956,10 @@ class Engine:
                     cs.bn_backward(self, dout, None, None, dys)
                 c3.wgrad(dy3)
                 c3.dgrad(dy3, da2)
-                dw.bn_backward(self, da2, a2, da2, dy2)
+                dw.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
                 dw.wgrad(dy2)
                 dw.dgrad(dy2, da1)
-                c1.bn_backward(self, da1, a1, da1, dy1)
+                c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dys)
@@ -966,7 +972,7 @@ class Engine:
         dy0 = self.new_act(*stem.y.shape)
 
         def bwd_stem(dout=dout):
-            stem.bn_backward(self, dout, a0, dout, dy0)
+            stem.bn_backward(self, dout, a0, dout, dy0, relu_from_y=True)
             stem.wgrad(dy0)
         Bk.append(bwd_stem)
         self.bwd_ops = Bk

@@ -131,10 +131,10 @@ def bn_bwd_partial_rows(rows, channels):
     return r
 
 
-def bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial):
+def bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, relu_scale=None, relu_shift=None):
     lib = _lib.load()
-    check(lib.b2c_bn_bwd_reduce(_p(dout), _p(act), _p(y), _p(dz_out), rows, channels, _p(partial), _stream()),
-          "b2c_bn_bwd_reduce")
+    check(lib.b2c_bn_bwd_reduce(_p(dout), _p(act), _p(y), _p(dz_out), rows, channels, _p(partial), _p(relu_scale),
+                                _p(relu_shift), _stream()), "b2c_bn_bwd_reduce")
 
 
 def bn_bwd_finalize(partial, partial_rows, channels, count, gamma, save_mean, save_rstd, dgamma, dbeta, ca, cb, cc):
@@ -157,10 +157,10 @@ def bn_bwd_stats_noalloc(dout, act, y, dz_out, rows, channels, count, gamma, sav
                                        _stream()), "b2c_bn_bwd_stats_noalloc")
 
 
-def bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, channels, add=None):
+def bn_bwd_apply(dz, y, ca, cb, cc, dy, rows, channels, add=None, relu_scale=None, relu_shift=None):
     lib = _lib.load()
-    check(lib.b2c_bn_bwd_apply(_p(dz), _p(y), _p(ca), _p(cb), _p(cc), _p(add), _p(dy), rows, channels, _stream()),
-          "b2c_bn_bwd_apply")
+    check(lib.b2c_bn_bwd_apply(_p(dz), _p(y), _p(ca), _p(cb), _p(cc), _p(add), _p(dy), rows, channels,
+                               _p(relu_scale), _p(relu_shift), _stream()), "b2c_bn_bwd_apply")
 
 
 def maxpool2x2_fwd(x, y):

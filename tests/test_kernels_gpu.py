@@ -317,6 +317,25 @@ def test_bn_relu_backward(ops, C, rows):
     ops.bn_bwd_finalize(partial, prow, C, rows, gamma.detach(), mean, rstd, dgamma, dbeta, ca, cb, cc)
     torch.cuda.synchronize()
     assert rel_err(dbeta, beta.grad) < 5e-3
+    # mask recomputed from y (no act read, no dz written): the forward kernel's own act decides the expected mask,
+    # so the result must equal the act-based path bit for bit
+    scale = (gamma.detach() * rstd).contiguous()
+    shift = (beta.detach() - mean * scale).contiguous()
+    act_k = torch.empty_like(y)
+    ops.bn_act_apply(y, scale, shift, act_k, rows, C, relu=True)
+    ref = [torch.empty(C, device="cuda") for _ in range(5)]
+    new = [torch.empty(C, device="cuda") for _ in range(5)]
+    dy_ref, dy_new = torch.empty_like(dout), torch.empty_like(dout)
+    ops.bn_bwd_reduce(dout, act_k, y, dz, rows, C, partial)
+    ops.bn_bwd_finalize(partial, prow, C, rows, gamma.detach(), mean, rstd, *ref)
+    ops.bn_bwd_apply(dz, y, ref[2], ref[3], ref[4], dy_ref, rows, C)
+    ops.bn_bwd_reduce(dout, None, y, None, rows, C, partial, scale, shift)
+    ops.bn_bwd_finalize(partial, prow, C, rows, gamma.detach(), mean, rstd, *new)
+    ops.bn_bwd_apply(dout, y, new[2], new[3], new[4], dy_new, rows, C, relu_scale=scale, relu_shift=shift)
+    torch.cuda.synchronize()
+    for a, b in zip(ref, new):
+        assert torch.equal(a, b)
+    assert torch.equal(dy_ref, dy_new)
 
 
 def test_head_and_loss(ops):

@@ -106,6 +106,10 @@ def test_backward_teacher_forced_per_block(setup):
 
     def force_unit(u, ref):
         u.y.copy_(_nhwc(ref.y)); u.mean.copy_(ref.mean); u.rstd.copy_(ref.rstd)
+        # the forward's scale/shift (what bn_finalize would have left): plain BN+ReLU units recompute their mask
+        # from y with them
+        u.scale[:u.gamma.numel()].copy_(u.gamma * u.rstd[:u.gamma.numel()])
+        u.shift[:u.gamma.numel()].copy_(u.beta - u.mean[:u.gamma.numel()] * u.scale[:u.gamma.numel()])
 
     # forward state of the whole net from the oracle
     ops.stem_im2col(x, eng.x0)
