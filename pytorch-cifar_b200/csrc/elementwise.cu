@@ -49,29 +49,63 @@ __device__ __forceinline__ void mask_from_y8(float (&d)[8], const float (&yy)[8]
 // ------------------------------------------------------------------------------------------------
 // BatchNorm finalize (training statistics). Reference: nn.BatchNorm2d in train mode,
 // models/resnet.py:25,28,35,104 -> F.batch_norm: biased variance for normalisation, unbiased for the
-// running estimate, momentum 0.1, eps 1e-5. One warp per channel; lanes stride over the per-CTA
-// partial rows the conv epilogue wrote and combine with a shuffle tree in fp64.
+// running estimate, momentum 0.1, eps 1e-5. One block per 32 channels; its 32 warps stride over the per-CTA
+// partial rows the conv epilogue wrote and combine in fp64 (colsum2_block).
 // ------------------------------------------------------------------------------------------------
-__global__ void bn_finalize_kernel(const float* __restrict__ part_sum, const float* __restrict__ part_sq, int rows,
+// Column sums of two [rows][stride] fp32 matrices for the 32 channels of this block, in fp64. 32 warps walk the
+// rows (one coalesced 128-byte read per warp and row, four rows in flight), then combine through shared memory.
+// Latency matters more than bandwidth here: the inputs are a few hundred KB but the kernel sits on the critical path
+// between two full-tensor passes, 40 times per step.
+constexpr int kFinWarps = 32;
+__device__ __forceinline__ void colsum2_block(const float* __restrict__ a, const float* __restrict__ b, size_t stride,
+                                              int rows, bool valid, double& s1, double& s2) {
+    __shared__ double sm[2][kFinWarps][32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    double d1 = 0.0, d2 = 0.0;
+    if (valid) {
+        int r = w;
+        for (; r + 3 * kFinWarps < rows; r += 4 * kFinWarps) {
+            float x[4], z[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                x[u] = a[static_cast<size_t>(r + u * kFinWarps) * stride];
+                z[u] = b[static_cast<size_t>(r + u * kFinWarps) * stride];
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { d1 += static_cast<double>(x[u]); d2 += static_cast<double>(z[u]); }
+        }
+        for (; r < rows; r += kFinWarps) {
+            d1 += static_cast<double>(a[static_cast<size_t>(r) * stride]);
+            d2 += static_cast<double>(b[static_cast<size_t>(r) * stride]);
+        }
+    }
+    sm[0][w][lane] = d1;
+    sm[1][w][lane] = d2;
+    __syncthreads();
+    if (w < 2) {                       // warp 0 folds the first matrix, warp 1 the second
+        double t = 0.0;
+#pragma unroll 8
+        for (int k = 0; k < kFinWarps; ++k) t += sm[w][k][lane];
+        sm[w][0][lane] = t;
+    }
+    __syncthreads();
+    s1 = sm[0][0][lane];
+    s2 = sm[1][0][lane];
+}
+
+__global__ void __launch_bounds__(kFinWarps * 32)
+bn_finalize_kernel(const float* __restrict__ part_sum, const float* __restrict__ part_sq, int rows,
                                    int C, float count, const float* __restrict__ gamma,
                                    const float* __restrict__ beta, const float* __restrict__ conv_bias, float eps,
                                    float momentum,
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
                                    float* __restrict__ scale, float* __restrict__ shift,
                                    float* __restrict__ mean_out, float* __restrict__ rstd_out) {
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
+    const int warp = blockIdx.x * 32 + (threadIdx.x & 31);      // channel (name kept from the warp-per-channel form)
+    double s1, s2;
+    colsum2_block(part_sum + warp, part_sq + warp, static_cast<size_t>(C), rows, warp < C, s1, s2);
     if (warp >= C) return;
-    double s1 = 0.0, s2 = 0.0;
-    for (int r = lane; r < rows; r += 32) {
-        s1 += static_cast<double>(part_sum[static_cast<size_t>(r) * C + warp]);
-        s2 += static_cast<double>(part_sq[static_cast<size_t>(r) * C + warp]);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-    }
+    const int lane = threadIdx.x >> 5;                            // 0 for the warp that writes the results
     if (lane == 0) {
         const double n = static_cast<double>(count);
         const double mean = s1 / n;
@@ -112,13 +146,14 @@ __global__ void bn_eval_scale_shift_kernel(int C, const float* __restrict__ gamm
 // `F.relu(out)` models/resnet.py:47-50. 16-byte vectors of 8 channels; C % 8 == 0.
 //   out = act( y*scale + shift  [+ res]  or  [+ res*res_scale + res_shift] )
 // ------------------------------------------------------------------------------------------------
-template <bool kUniform>
+template <bool kUniform, bool kResAffine>
 __global__ void __launch_bounds__(256)
 bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
                     const uint4* __restrict__ res, const float* __restrict__ res_scale,
                     const float* __restrict__ res_shift, uint4* __restrict__ out, long long nvec, int C, int relu) {
     // kUniform: the grid stride is a multiple of C/8, so a thread sees the same 8 channels in every iteration and
-    // keeps their scale / shift in registers (no 64-bit modulo, no per-element parameter loads in the loop).
+    // keeps their scale / shift in registers (no 64-bit modulo, no per-element parameter loads in the loop); two
+    // grid strides are then in flight per iteration (all loads issued before the first use).
     const int cvec = C >> 3;
     const long long start = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -130,7 +165,7 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
         const float4 hb = __ldg(reinterpret_cast<const float4*>(shift + c0 + 4));
         sc[0] = sa.x; sc[1] = sa.y; sc[2] = sa.z; sc[3] = sa.w; sc[4] = sb.x; sc[5] = sb.y; sc[6] = sb.z; sc[7] = sb.w;
         sh[0] = ha.x; sh[1] = ha.y; sh[2] = ha.z; sh[3] = ha.w; sh[4] = hb.x; sh[5] = hb.y; sh[6] = hb.z; sh[7] = hb.w;
-        if (res_scale != nullptr) {
+        if (kResAffine) {
             const float4 ra = __ldg(reinterpret_cast<const float4*>(res_scale + c0));
             const float4 rc = __ldg(reinterpret_cast<const float4*>(res_scale + c0 + 4));
             const float4 ta = __ldg(reinterpret_cast<const float4*>(res_shift + c0));
@@ -139,17 +174,15 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
             rb[0] = ta.x; rb[1] = ta.y; rb[2] = ta.z; rb[3] = ta.w; rb[4] = tb.x; rb[5] = tb.y; rb[6] = tb.z; rb[7] = tb.w;
         }
     };
-    if (kUniform) load_params(static_cast<int>(start % cvec) << 3);
-    for (long long v = start; v < nvec; v += step) {
-        if (!kUniform) load_params(static_cast<int>(v % cvec) << 3);
+    auto finish = [&](const uint4 yraw, const uint4 rraw, long long v) {
         float f[8];
-        unpack8(ld_stream(y + v), f);
+        unpack8(yraw, f);
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[e], sh[e]);
         if (res != nullptr) {
             float r[8];
-            unpack8(ld_stream(res + v), r);
-            if (res_scale != nullptr) {
+            unpack8(rraw, r);
+            if (kResAffine) {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) r[e] = fmaf(r[e], rs[e], rb[e]);
             }
@@ -161,6 +194,25 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
         }
         out[v] = pack8(f);
+    };
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    if (kUniform) {
+        load_params(static_cast<int>(start % cvec) << 3);
+        for (long long v = start; v < nvec; v += 2 * step) {
+            const long long v2 = v + step;
+            const bool two = v2 < nvec;
+            const uint4 y0 = ld_stream(y + v);
+            const uint4 y1 = two ? ld_stream(y + v2) : zero;
+            const uint4 r0 = res != nullptr ? ld_stream(res + v) : zero;
+            const uint4 r1 = (res != nullptr && two) ? ld_stream(res + v2) : zero;
+            finish(y0, r0, v);
+            if (two) finish(y1, r1, v2);
+        }
+    } else {
+        for (long long v = start; v < nvec; v += step) {
+            load_params(static_cast<int>(v % cvec) << 3);
+            finish(ld_stream(y + v), res != nullptr ? ld_stream(res + v) : zero, v);
+        }
     }
 }
 
@@ -225,24 +277,17 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ a
 
 // Pass 2 (tiny): combine partial rows, emit dgamma / dbeta and the per-channel coefficients of
 //   dy = A*dz + B*y + Cc   (= gamma*rstd*(dz - dbeta/n - xhat*dgamma/n), xhat = (y-mean)*rstd).
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int prow, int C, float count,
+__global__ void __launch_bounds__(kFinWarps * 32)
+bn_bwd_finalize_kernel(const float* __restrict__ partial, int prow, int C, float count,
                                        const float* __restrict__ gamma, const float* __restrict__ mean,
                                        const float* __restrict__ rstd, float* __restrict__ dgamma,
                                        float* __restrict__ dbeta, float* __restrict__ coefA,
                                        float* __restrict__ coefB, float* __restrict__ coefC) {
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
+    const int warp = blockIdx.x * 32 + (threadIdx.x & 31);      // channel
+    double s1, s2;
+    colsum2_block(partial + warp, partial + C + warp, static_cast<size_t>(2) * C, prow, warp < C, s1, s2);
     if (warp >= C) return;
-    double s1 = 0.0, s2 = 0.0;
-    for (int r = lane; r < prow; r += 32) {
-        s1 += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + warp]);
-        s2 += static_cast<double>(partial[static_cast<size_t>(r) * 2 * C + C + warp]);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        s1 += __shfl_xor_sync(0xffffffffu, s1, o);
-        s2 += __shfl_xor_sync(0xffffffffu, s2, o);
-    }
+    const int lane = threadIdx.x >> 5;
     if (lane == 0) {
         const double mu = mean[warp], rs = rstd[warp], g = gamma[warp], n = count;
         const double db = s1;
@@ -466,38 +511,46 @@ __global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const flo
     }
 }
 // Head backward, part 2: dW[k, c] = sum_n dlogits[n,k] * pooled[n,c]; db[k] = sum_n dlogits[n,k].
-// grid = (C/32, K); block = 32 channels x 8 batch lanes, smem tree over the lanes.
-__global__ void __launch_bounds__(256)
+// grid = (C/32, K); block = 32 channels x 32 batch lanes (four samples in flight per lane), smem fold over the lanes.
+__global__ void __launch_bounds__(1024)
 head_bwd_param_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, int N,
                       int K, int C, float* __restrict__ dW, float* __restrict__ db) {
-    __shared__ float red[8][33];
+    __shared__ float red[32][33];
     const int k = blockIdx.y;
     const int cl = threadIdx.x & 31, nl = threadIdx.x >> 5;
     const int c = blockIdx.x * 32 + cl;
+    const bool valid = c < C;
+    const float* pc = pooled + (valid ? c : 0);
     float s = 0.f, sb = 0.f;
-    for (int n = nl; n < N; n += 8) {
+    int n = nl;
+    for (; n + 96 < N; n += 128) {
+        float d[4], q[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            d[u] = __ldg(dlogits + static_cast<size_t>(n + 32 * u) * K + k);
+            q[u] = __ldg(pc + static_cast<size_t>(n + 32 * u) * C);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { s = fmaf(d[u], q[u], s); sb += d[u]; }
+    }
+    for (; n < N; n += 32) {
         const float d = __ldg(dlogits + static_cast<size_t>(n) * K + k);
-        if (c < C) s = fmaf(d, __ldg(pooled + static_cast<size_t>(n) * C + c), s);
+        s = fmaf(d, __ldg(pc + static_cast<size_t>(n) * C), s);
         sb += d;
     }
     red[nl][cl] = s;
+    if (cl == 0) red[nl][32] = sb;         // every lane of a warp holds the same sb
     __syncthreads();
-    if (nl == 0 && c < C) {
+    if (nl == 0) {
         float t = 0.f;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) t += red[i][cl];
-        dW[static_cast<size_t>(k) * C + c] = t;
-    }
-    if (blockIdx.x == 0) {
-        __syncthreads();
-        if (cl == 0) red[nl][32] = sb;     // every lane of a warp holds the same sb
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            float t = 0.f;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) t += red[i][32];
-            db[k] = t;
-        }
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) t += red[i][cl];
+        if (valid) dW[static_cast<size_t>(k) * C + c] = t;
+    } else if (nl == 1 && cl == 0 && blockIdx.x == 0) {
+        float t = 0.f;
+#pragma unroll 8
+        for (int i = 0; i < 32; ++i) t += red[i][32];
+        db[k] = t;
     }
 }
 
@@ -713,9 +766,7 @@ cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int 
                                const float* gamma, const float* beta, const float* conv_bias, float eps,
                                float momentum, float* running_mean, float* running_var, float* scale, float* shift,
                                float* mean, float* rstd, cudaStream_t s) {
-    const int threads = 128;
-    const int blocks = (C * 32 + threads - 1) / threads;
-    bn_finalize_kernel<<<blocks, threads, 0, s>>>(part_sum, part_sq, rows, C, count, gamma, beta, conv_bias, eps, momentum,
+    bn_finalize_kernel<<<(C + 31) / 32, kFinWarps * 32, 0, s>>>(part_sum, part_sq, rows, C, count, gamma, beta, conv_bias, eps, momentum,
                                                   running_mean, running_var, scale, shift, mean, rstd);
     return cudaGetLastError();
 }
@@ -732,14 +783,16 @@ cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* 
                                 int relu, cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
     const int grid = grid_for(nvec, 256, 148 * 8);
-    if ((static_cast<long long>(grid) * 256) % (C >> 3) == 0)
-        bn_act_apply_kernel<true><<<grid, 256, 0, s>>>(static_cast<const uint4*>(y), scale, shift,
-                                                       static_cast<const uint4*>(res), res_scale, res_shift,
-                                                       static_cast<uint4*>(out), nvec, C, relu);
-    else
-        bn_act_apply_kernel<false><<<grid, 256, 0, s>>>(static_cast<const uint4*>(y), scale, shift,
-                                                        static_cast<const uint4*>(res), res_scale, res_shift,
-                                                        static_cast<uint4*>(out), nvec, C, relu);
+    const bool uniform = (static_cast<long long>(grid) * 256) % (C >> 3) == 0;
+    const bool affine = res != nullptr && res_scale != nullptr;
+    auto go = [&](auto kern) {
+        kern<<<grid, 256, 0, s>>>(static_cast<const uint4*>(y), scale, shift, static_cast<const uint4*>(res), res_scale,
+                                  res_shift, static_cast<uint4*>(out), nvec, C, relu);
+    };
+    if (uniform && affine) go(bn_act_apply_kernel<true, true>);
+    else if (uniform) go(bn_act_apply_kernel<true, false>);
+    else if (affine) go(bn_act_apply_kernel<false, true>);
+    else go(bn_act_apply_kernel<false, false>);
     return cudaGetLastError();
 }
 
@@ -774,9 +827,7 @@ cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* 
 cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float count, const float* gamma,
                                    const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
                                    float* coefB, float* coefC, cudaStream_t s) {
-    const int threads = 128;
-    const int blocks = (C * 32 + threads - 1) / threads;
-    bn_bwd_finalize_kernel<<<blocks, threads, 0, s>>>(partial, prow, C, count, gamma, mean, rstd, dgamma, dbeta,
+    bn_bwd_finalize_kernel<<<(C + 31) / 32, kFinWarps * 32, 0, s>>>(partial, prow, C, count, gamma, mean, rstd, dgamma, dbeta,
                                                       coefA, coefB, coefC);
     return cudaGetLastError();
 }
@@ -837,7 +888,7 @@ cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const flo
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     dim3 grid((C + 31) / 32, K);
-    head_bwd_param_kernel<<<grid, 256, 0, s>>>(dlogits, pooled, N, K, C, dW, db);
+    head_bwd_param_kernel<<<grid, 1024, 0, s>>>(dlogits, pooled, N, K, C, dW, db);
     return cudaGetLastError();
 }
 

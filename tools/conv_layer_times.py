@@ -10,6 +10,8 @@ N = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 shapes = [(32, 64, 64, 3, 1), (32, 64, 128, 3, 2), (32, 64, 128, 1, 2), (16, 128, 128, 3, 1), (16, 128, 256, 3, 2),
           (16, 128, 256, 1, 2), (8, 256, 256, 3, 1), (8, 256, 512, 3, 2), (8, 256, 512, 1, 2), (4, 512, 512, 3, 1),
           (32, 64, 64, 1, 1)]
+if os.environ.get("ONLY"):                 # e.g. ONLY=1,2 to profile two shapes under ncu
+    shapes = [shapes[int(i)] for i in os.environ["ONLY"].split(",")]
 flush = torch.empty(256 * 2 ** 20, dtype=torch.uint8, device="cuda")
 scratch = torch.zeros(ops.WGRAD_SCRATCH_FLOATS, device="cuda")
 
