@@ -51,7 +51,9 @@ typedef struct B2cConvDesc {
     int block_n;     /* GEMM N tile (64/128/256); 0 = choose */
     int max_ctas;    /* persistent grid cap; 0 = 148 (one CTA per SM) */
     int flags;       /* bit 0: force the per-tap kernels where a halo-reuse kernel would be chosen;
-                        bit 1: wgrad: take the halo-reuse kernel for any qualifying shape, not just 64x64 channels */
+                        bit 1: wgrad: take the halo-reuse kernel for any qualifying shape, not just 64x64 channels;
+                        bit 2: stride 2: address x with a TMA traversal stride instead of the split-W map
+                               (measurement aid: same result, twice the L2->SM operand bytes) */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)
@@ -69,6 +71,14 @@ B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fp
  * or equal to dx (accumulate in place). */
 B2C_API int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
                    void* stream);
+
+/* dx = dgrad3x3s2(dy, w[0..8]) + dgrad1x1s2(dy_shortcut, w[9]) (+ add_src) in one launch: the backward of a
+ * down-sampling block's fan-out `conv1(x)` / `shortcut(x)`, models/resnet.py:23,33-34,47-49 and
+ * models/preact_resnet.py:27-31 (autograd sums the two input gradients, main.py:104). d describes the 3x3
+ * stride-2 conv; the 1x1 stride-2 shortcut conv has the same cin/cout. `w_dgrad10` is bf16 [10][cin][cout]: the
+ * 3x3's nine tap slabs followed by the shortcut's single slab. */
+B2C_API int b2c_conv_dgrad_with_shortcut(const B2cConvDesc* d, const void* dy, const void* dy_shortcut,
+                                 const void* w_dgrad10, void* dx, const void* add_src, void* stream);
 
 /* dw[cout_valid,cin_valid,k,k] (fp32, OIHW = the reference's .grad layout) += sum over pixels of x * dy.
  * Replaces cudnn_convolution_backward_weight, main.py:104. Accumulates with fp32 atomics: the caller

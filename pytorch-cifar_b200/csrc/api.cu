@@ -56,6 +56,34 @@ int encode_nhwc(CUtensorMap* m, const void* base, int n, int h, int w, int c, in
     return r == CUDA_SUCCESS ? 0 : B2C_ERR_DRIVER;
 }
 
+// Stride-2 view of an NHWC bf16 tensor for TMA: the W axis is split into (w/2, parity) so that a box takes ONE
+// parity of bw consecutive w/2 positions — plain tiled addressing. A traversal stride on W instead makes the
+// TMA unit fetch the whole 2*bw bounding row from L2 and drop every other pixel (ncu: 604 MB of L2->SM reads
+// for 302 MB of operand on the 64->128 stride-2 layer). The H axis keeps the traversal stride (rows are
+// separate lines anyway). Dims {c, parity, w/2, h, n}; coordinates of pixel column w: (w & 1, w >> 1).
+int encode_nhwc_s2(CUtensorMap* m, const void* base, int n, int h, int w, int c, int bw, int bh, int bn) {
+    EncodeTiledFn enc = get_encode();
+    if (enc == nullptr) return B2C_ERR_DRIVER;
+    cuuint64_t dims[5] = {static_cast<cuuint64_t>(c), 2u, static_cast<cuuint64_t>(w / 2), static_cast<cuuint64_t>(h),
+                          static_cast<cuuint64_t>(n)};
+    cuuint64_t strides[4] = {static_cast<cuuint64_t>(c) * 2, static_cast<cuuint64_t>(c) * 4,
+                             static_cast<cuuint64_t>(w) * c * 2, static_cast<cuuint64_t>(h) * w * c * 2};
+    cuuint32_t box[5] = {64u, 1u, static_cast<cuuint32_t>(bw), static_cast<cuuint32_t>(bh * 2),
+                         static_cast<cuuint32_t>(bn)};
+    cuuint32_t estr[5] = {1u, 1u, 1u, 2u, 1u};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : B2C_ERR_DRIVER;
+}
+
+void single_phase(b2c::TapGemmParams& p) {
+    p.num_phases = 1;
+    p.phase_begin[0] = 0;
+    p.phase_begin[1] = static_cast<uint8_t>(p.num_taps);
+    p.phase_py[0] = p.phase_px[0] = 0;
+}
+
 // Row-major bf16 matrix [rows, cols] -> 2-D map, box {64 cols, brows}.
 int encode_2d(CUtensorMap* m, const void* base, long long rows, int cols, int brows) {
     EncodeTiledFn enc = get_encode();
@@ -196,7 +224,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     p.out_W = wo;
     p.out_ld = d->cout;
     p.sy = p.sx = 1;
-    p.py = p.px = 0;
+    single_phase(p);
     p.part_sum = part_sum;
     p.part_sq = part_sq;
     p.cout = d->cout;
@@ -204,7 +232,9 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     const int bh = (128 / wo) < ho ? (128 / wo) : ho;
     const int bnb = 128 / (wo * bh);
     CUtensorMap ma, mb;
-    rc = encode_nhwc(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
+    p.a_split_w = d->stride == 2 && !(d->flags & 4);      // flags & 4: traversal-stride map (A/B measurements)
+    rc = p.a_split_w ? encode_nhwc_s2(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb)
+                     : encode_nhwc(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
     if (rc) return rc;
     rc = encode_2d(&mb, w_fprop, static_cast<long long>(taps) * d->cout, d->cin, bn);
     if (rc) return rc;
@@ -212,8 +242,8 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
 }
 
-int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
-                   void* stream) {
+static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_shortcut, const void* w_dgrad,
+                           void* dx, const void* add_src, void* stream) {
     int rc = check_conv(d);
     if (rc) return rc;
     if (!dy || !w_dgrad || !dx || !aligned16(dy) || !aligned16(w_dgrad) || !aligned16(dx) || !aligned16(add_src))
@@ -245,7 +275,8 @@ int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, vo
     p.cout = d->cin;
 
     CUtensorMap ma, mb;
-    rc = encode_2d(&mb, w_dgrad, static_cast<long long>(taps) * d->cin, d->cout, bn);
+    rc = encode_2d(&mb, w_dgrad, static_cast<long long>(taps + (dy_shortcut != nullptr ? 1 : 0)) * d->cin, d->cout,
+                   bn);
     if (rc) return rc;
 
     if (d->stride == 1) {
@@ -267,7 +298,7 @@ int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, vo
             p.tap_brow[t] = t * d->cin;
         }
         p.sy = p.sx = 1;
-        p.py = p.px = 0;
+        single_phase(p);
         return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st));
     }
 
@@ -294,12 +325,18 @@ int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, vo
         p.tap_dw[0] = 0;
         p.tap_a[0] = 0;
         p.tap_brow[0] = 0;
-        p.py = p.px = 0;
+        single_phase(p);
         return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st));
     }
+    // 3x3: all four parity phases in ONE launch (tiles = phase x pixel tile): dy is read from HBM once and the
+    // phases, which differ in tap count (1, 2, 2, 4), balance across the persistent CTAs.
+    CUtensorMap ma1 = ma;
+    int nt = 0, np = 0;
     for (int ph = 0; ph < 2; ++ph) {
         for (int pw = 0; pw < 2; ++pw) {
-            int nt = 0;
+            p.phase_begin[np] = static_cast<uint8_t>(nt);
+            p.phase_py[np] = static_cast<uint8_t>(ph);
+            p.phase_px[np] = static_cast<uint8_t>(pw);
             for (int r = 0; r < 3; ++r) {
                 if (((ph + 1 - r) & 1) != 0) continue;
                 for (int s = 0; s < 3; ++s) {
@@ -311,14 +348,36 @@ int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, vo
                     ++nt;
                 }
             }
-            p.num_taps = nt;
-            p.py = ph;
-            p.px = pw;
-            cudaError_t e = b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st);
-            if (e != cudaSuccess) return cuda_rc(e);
+            if (np == 0 && dy_shortcut != nullptr) {
+                // the 1x1 stride-2 shortcut conv reads x[2i, 2j]: its dgrad lands on phase (0, 0) only, as one more
+                // tap whose A operand is the shortcut's dy and whose weights are slab 9 of the B matrix
+                rc = encode_nhwc(&ma1, dy_shortcut, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+                if (rc) return rc;
+                p.tap_dh[nt] = 0;
+                p.tap_dw[nt] = 0;
+                p.tap_a[nt] = 1;
+                p.tap_brow[nt] = 9 * d->cin;
+                ++nt;
+            }
+            ++np;
         }
     }
-    return 0;
+    p.phase_begin[4] = static_cast<uint8_t>(nt);
+    p.num_taps = nt;
+    p.num_phases = 4;
+    return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma1, mb, p, max_ctas, nullptr, st));
+}
+
+int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
+                   void* stream) {
+    return conv_dgrad_impl(d, dy, nullptr, w_dgrad, dx, add_src, stream);
+}
+
+int b2c_conv_dgrad_with_shortcut(const B2cConvDesc* d, const void* dy, const void* dy_shortcut, const void* w_dgrad10,
+                                 void* dx, const void* add_src, void* stream) {
+    if (d == nullptr || d->ksize != 3 || d->stride != 2) return B2C_ERR_UNSUPPORTED;
+    if (!dy_shortcut || !aligned16(dy_shortcut)) return B2C_ERR_ARG;
+    return conv_dgrad_impl(d, dy, dy_shortcut, w_dgrad10, dx, add_src, stream);
 }
 
 int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* dw, float* scratch,
@@ -413,7 +472,9 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
     const int bh = (kpx / wo) < ho ? (kpx / wo) : ho;
     const int bnb = kpx / (wo * bh);
     CUtensorMap mx, mdy;
-    rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
+    p.x_split_w = d->stride == 2 && !(d->flags & 4);
+    rc = p.x_split_w ? encode_nhwc_s2(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb)
+                     : encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
     if (rc) return rc;
     rc = encode_nhwc(&mdy, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
     if (rc) return rc;

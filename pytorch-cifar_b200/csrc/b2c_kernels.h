@@ -24,11 +24,17 @@ struct TapGemmParams {
     int8_t tap_dw[kMaxTaps];
     uint8_t tap_a[kMaxTaps];   // which A tensor map (0 or 1) the tap reads
     int tap_brow[kMaxTaps];    // first row of the tap's weight slab in the B matrix
+    // Output phases (stride-2 dgrad): a tile belongs to one phase = a sub-range of the tap list and an output
+    // pixel offset. num_phases == 1 for everything else (phase_begin = {0, num_taps}).
+    int num_phases;
+    uint8_t phase_begin[5];
+    uint8_t phase_py[4], phase_px[4];
+    int a_split_w;             // A maps are 5-D with the W axis split into (w/2, parity): stride-2 fprop
     // epilogue
     __nv_bfloat16* out;
     const __nv_bfloat16* add_src;  // optional, same addressing as out
     int out_H, out_W, out_ld;      // output tensor pixel dims and channel pitch
-    int sy, sx, py, px;            // output pixel = (i * sy + py, j * sx + px)
+    int sy, sx;                    // output pixel = (i * sy + phase_py, j * sx + phase_px)
     float* part_sum;               // optional [stat_rows][cout] per-CTA column sums (stat_rows <= 148)
     float* part_sq;                // optional [stat_rows][cout] per-CTA column sums of squares
     int cout;
@@ -47,6 +53,7 @@ struct WgradParams {
     int cin_blocks;       // cin / 64
     int gH, gW;           // dY pixel grid
     int in_stride;
+    int x_split_w;        // X map is 5-D with the W axis split into (parity, w/2): stride-2 convs
     int8_t tap_dh[kMaxTaps];
     int8_t tap_dw[kMaxTaps];
     int num_taps;

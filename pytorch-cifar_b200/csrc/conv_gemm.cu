@@ -81,9 +81,21 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
 
-    const int total_tiles = p.num_m_tiles * p.num_n_tiles;
-    const int k_iters = p.num_taps * p.k_chunks;
+    const int total_tiles = p.num_m_tiles * p.num_n_tiles * p.num_phases;
     const int img = p.gH * p.gW;
+    // tile -> (m_tile, phase, n_tile), n_tile fastest. The phase is rotated by m_tile so that a CTA whose tile
+    // stride is a multiple of num_phases still sees every phase (they differ in tap count).
+    auto decode = [&](int tile, int& m_tile, int& n_tile, int& ph) {
+        const int rest = tile / p.num_n_tiles;
+        n_tile = tile - rest * p.num_n_tiles;
+        if (p.num_phases == 1) {
+            m_tile = rest;
+            ph = 0;
+        } else {
+            m_tile = rest / p.num_phases;
+            ph = (rest - m_tile * p.num_phases + m_tile) % p.num_phases;
+        }
+    };
 
     if (warp == 0) {
         {
@@ -91,12 +103,13 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int m_tile = tile / p.num_n_tiles;
-                const int n_tile = tile - m_tile * p.num_n_tiles;
+                int m_tile, n_tile, ph;
+                decode(tile, m_tile, n_tile, ph);
                 const int p0 = m_tile * kBM;
                 const int n0 = p0 / img;
                 const int h0 = (p0 - n0 * img) / p.gW;
-                for (int t = 0; t < p.num_taps; ++t) {
+                const int t_end = p.phase_begin[ph + 1];
+                for (int t = p.phase_begin[ph]; t < t_end; ++t) {
                     const CUtensorMap* ma = p.tap_a[t] ? &mapA1 : &mapA0;
                     const int cw = p.tap_dw[t];
                     const int ch = h0 * p.in_stride + p.tap_dh[t];
@@ -106,7 +119,10 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                         if (elect_one_sync()) {
                             mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
                             uint8_t* sa = smem + stage * Cfg::kStageBytes;
-                            tma_load_4d(sa, ma, &full[stage], kc * 64, cw, ch, n0);
+                            if (p.a_split_w)     // w = 2*w2 + parity: {c, parity, w2, h, n}; -1 -> (1, -1)
+                                tma_load_5d(sa, ma, &full[stage], kc * 64, cw & 1, cw >> 1, ch, n0);
+                            else
+                                tma_load_4d(sa, ma, &full[stage], kc * 64, cw, ch, n0);
                             tma_load_2d(sa + kABytes, &mapB, &full[stage], kc * 64, brow);
                         }
                         __syncwarp();
@@ -127,6 +143,9 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
             int acc = 0;
             uint32_t acc_phase = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                int m_tile, n_tile, ph;
+                decode(tile, m_tile, n_tile, ph);
+                const int k_iters = (p.phase_begin[ph + 1] - p.phase_begin[ph]) * p.k_chunks;
                 mbar_wait(&tempty[acc], acc_phase ^ 1u, 2);
                 tc_fence_after();
                 const uint32_t d = tmem_base + static_cast<uint32_t>(acc * BN);
@@ -174,8 +193,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const int m_tile = tile / p.num_n_tiles;
-            const int n_tile = tile - m_tile * p.num_n_tiles;
+            int m_tile, n_tile, ph;
+            decode(tile, m_tile, n_tile, ph);
             mbar_wait(&tfull[acc], acc_phase, 4);
             tc_fence_after();
             const int pix = m_tile * kBM + row;
@@ -185,7 +204,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
             const int i = rem / p.gW;
             const int j = rem - i * p.gW;
             const size_t off =
-                (static_cast<size_t>(n * p.out_H + i * p.sy + p.py) * p.out_W + (j * p.sx + p.px)) * p.out_ld +
+                (static_cast<size_t>(n * p.out_H + i * p.sy + p.phase_py[ph]) * p.out_W + (j * p.sx + p.phase_px[ph])) *
+                    p.out_ld +
                 static_cast<size_t>(n_tile) * BN;
             float* st = stat;
 #pragma unroll 1

@@ -106,8 +106,13 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
                     uint8_t* sa = smem + stage * Cfg::kStageBytes;
 #pragma unroll
                     for (int b = 0; b < 2; ++b) {
-                        tma_load_4d(sa + b * kSlabBytes, &mapX, &full[stage], cb[b] * 64, p.tap_dw[tap[b]],
-                                    h0 * p.in_stride + p.tap_dh[tap[b]], n0);
+                        const int cw = p.tap_dw[tap[b]];
+                        if (p.x_split_w)     // stride 2: W axis split into (parity, w/2), see encode_nhwc_s2
+                            tma_load_5d(sa + b * kSlabBytes, &mapX, &full[stage], cb[b] * 64, cw & 1, cw >> 1,
+                                        h0 * p.in_stride + p.tap_dh[tap[b]], n0);
+                        else
+                            tma_load_4d(sa + b * kSlabBytes, &mapX, &full[stage], cb[b] * 64, cw,
+                                        h0 * p.in_stride + p.tap_dh[tap[b]], n0);
                     }
 #pragma unroll
                     for (int nb = 0; nb < Cfg::kNSlabs; ++nb) {

@@ -306,6 +306,7 @@ class ConvUnit:
         self.eng_scratch = eng.wgrad_scratch
         self.wf = eng.wf_view(name)
         self.wd = None if stem else eng.wd_view(name)
+        self.wd10 = None if stem else eng.wd10_view(name)
         self.dw = eng.grad_view(name + ".weight")
         if bn_name is not None:
             _bn_views(self, eng, bn_name, cout_p)
@@ -348,6 +349,15 @@ class ConvUnit:
 
     def dgrad(self, dy, dx, add_src=None):
         ops.conv_dgrad(self.desc, dy, self.wd, dx, add_src)
+
+    def dgrad_with_shortcut(self, dy, dy_sc, sc, dx):
+        """dx = dgrad(self, dy) + dgrad(sc, dy_sc): the two consumers of a down-sampling block's input
+        (models/resnet.py:47-49). One launch when self is the 3x3 stride-2 conv paired with the 1x1 shortcut."""
+        if self.wd10 is not None and self.k == 3 and self.stride == 2 and sc.k == 1 and sc.stride == 2:
+            ops.conv_dgrad_with_shortcut(self.desc, dy, dy_sc, self.wd10, dx)
+        else:
+            sc.dgrad(dy_sc, dx)                       # (stride 2: zero-fill + even pixels)
+            self.dgrad(dy, dx, add_src=dx)
 
 
 class DwUnit:
@@ -425,10 +435,26 @@ class Engine:
             self.B = torch.zeros(max(off, 4), **f32)       # BN running statistics
         # bf16 GEMM operand copies of the conv weights
         self.wf_off, self.wd_off, entries = {}, {}, []
+        self.wd_pair = {}      # 3x3 stride-2 conv1 -> its block's 1x1 shortcut conv, stored right behind it in WD
         wf_n = wd_n = 0
-        for name, shape in spec["params"].items():
-            if len(shape) != 4 or name in spec.get("depthwise", ()):
-                continue                                  # depthwise kernels read the fp32 master weights directly
+        convs = [(name, shape) for name, shape in spec["params"].items()
+                 if len(shape) == 4 and name not in spec.get("depthwise", ())]
+        # A down-sampling block's `conv1` (3x3) and `shortcut.0` (1x1) read the same input and have the same
+        # channel counts: their dgrad operands sit back to back so ONE 10-slab matrix serves the fused dgrad
+        # (b2c_conv_dgrad_with_shortcut).
+        shapes = dict(convs)
+        order, placed = [], set()
+        for name, shape in convs:
+            if name in placed:
+                continue
+            order.append(name); placed.add(name)
+            if name.endswith(".conv1.weight") and shape[2] == 3:
+                sc = name[:-len("conv1.weight")] + "shortcut.0.weight"
+                if sc in shapes and shapes[sc][:2] == shape[:2] and shapes[sc][2] == 1 and sc not in placed:
+                    order.append(sc); placed.add(sc)
+                    self.wd_pair[name[:-len(".weight")]] = sc[:-len(".weight")]
+        for name in order:
+            shape = shapes[name]
             cname = name[:-len(".weight")]
             cout, cin, k, _ = shape
             cout_p, cin_p = _pad64(cout), _pad64(cin)
@@ -453,6 +479,15 @@ class Engine:
             self.WF = torch.zeros(_align(wf_n, 8), **bf)
             self.WD = torch.zeros(_align(max(wd_n, 8), 8), **bf)
             self.repack_table = ops.make_repack_table(entries, self.device)
+
+    def wd10_view(self, cname):
+        """[10][cin][cout] dgrad operand of a paired conv1 + shortcut (None if `cname` has no pair)."""
+        if cname not in self.wd_pair:
+            return None
+        off, (taps, cin_p, cout_p) = self.wd_off[cname]
+        off2, _ = self.wd_off[self.wd_pair[cname]]
+        assert taps == 9 and off2 == off + 9 * cin_p * cout_p
+        return self.WD[off:off + 10 * cin_p * cout_p].view(10, cin_p, cout_p)
 
     def param_view(self, name):
         off, n, shape = self.p_off[name]
@@ -614,8 +649,7 @@ class Engine:
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dys)
-                    cs.dgrad(dys, dx)                     # zero-fill + even pixels
-                    c1.dgrad(dy1, dx, add_src=dx)
+                    c1.dgrad_with_shortcut(dy1, dys, cs, dx)
                 else:
                     c1.dgrad(dy1, dx, add_src=dout)       # identity shortcut: + dz
             Bk.append(bwd_block)
@@ -767,8 +801,7 @@ class Engine:
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dout)
-                    cs.dgrad(dout, da)                      # zero-fill + even pixels
-                    c1.dgrad(dy1, da, add_src=da)
+                    c1.dgrad_with_shortcut(dy1, dout, cs, da)
                     bn1.bn_backward(self, da, a, da, dx, relu_from_y=True)    # a = relu(bn1(x)); no identity path
                 else:
                     c1.dgrad(dy1, da)

@@ -67,6 +67,15 @@ def conv_dgrad(d, dy, w_dgrad, dx, add_src=None):
           "b2c_conv_dgrad")
 
 
+def conv_dgrad_with_shortcut(d, dy, dy_shortcut, w_dgrad10, dx, add_src=None):
+    """3x3 stride-2 dgrad + the 1x1 stride-2 shortcut's dgrad in one launch; w_dgrad10 = [10][cin][cout]."""
+    lib = _lib.load()
+    _need(dy, torch.bfloat16, "dy"); _need(dy_shortcut, torch.bfloat16, "dy_shortcut")
+    _need(w_dgrad10, torch.bfloat16, "w"); _need(dx, torch.bfloat16, "dx"); _need(add_src, torch.bfloat16, "add_src")
+    check(lib.b2c_conv_dgrad_with_shortcut(ctypes.byref(d), _p(dy), _p(dy_shortcut), _p(w_dgrad10), _p(dx),
+                                           _p(add_src), _stream()), "b2c_conv_dgrad_with_shortcut")
+
+
 WGRAD_SCRATCH_FLOATS = 148 * 5 * 128 * 64      # 24 MB: one partial tile set per CTA of the halo wgrad kernel
 
 

@@ -157,6 +157,49 @@ def test_conv_dgrad(ops, shape, with_add):
     assert rel_err(got, ref) < BF16_TOL
 
 
+@pytest.mark.parametrize("n,h,cin,cout", [(8, 32, 64, 128), (16, 16, 128, 256), (64, 8, 256, 512), (3, 16, 64, 64)])
+@pytest.mark.parametrize("with_add", [False, True])
+def test_conv_dgrad_with_shortcut(ops, n, h, cin, cout, with_add):
+    """3x3 stride-2 dgrad + 1x1 stride-2 shortcut dgrad as one launch (four output phases as tiles) against the sum
+    of the two torch input gradients; and the same 3x3 dgrad alone must agree with the traversal-free path."""
+    ho = h // 2
+    dy, dys = nhwc_bf16(n, ho, ho, cout, 31), nhwc_bf16(n, ho, ho, cout, 32)
+    w3, w1 = weight(cout, cin, 3, 33), weight(cout, cin, 1, 34)
+    ref = (torch.nn.grad.conv2d_input((n, cin, h, h), w3, to_nchw(dy), stride=2, padding=1) +
+           torch.nn.grad.conv2d_input((n, cin, h, h), w1, to_nchw(dys), stride=2, padding=0))
+    add = None
+    if with_add:
+        add = nhwc_bf16(n, h, h, cin, 35)
+        ref = ref + to_nchw(add)
+    w10 = torch.cat([ops.pack_weight_dgrad(w3), ops.pack_weight_dgrad(w1)], 0).contiguous()
+    assert w10.shape == (10, cin, cout)
+    dx = torch.full((n, h, h, cin), float("nan"), device="cuda", dtype=torch.bfloat16)
+    d = ops.conv_desc(n, h, h, cin, cout, 3, 2)
+    ops.conv_dgrad_with_shortcut(d, dy, dys, w10, dx, add)
+    torch.cuda.synchronize()
+    got = to_nchw(dx)
+    assert torch.isfinite(got).all()
+    assert rel_err(got, ref) < BF16_TOL
+    with pytest.raises(RuntimeError):
+        ops.conv_dgrad_with_shortcut(ops.conv_desc(n, h, h, cin, cout, 3, 1), dy, dys, w10, dx, add)
+
+
+@pytest.mark.parametrize("shape", [(8, 32, 32, 64, 128, 3, 2), (8, 16, 16, 128, 256, 1, 2)])
+def test_stride2_split_w_map_equals_traversal_stride(ops, shape):
+    """flags bit 2 selects the TMA traversal-stride addressing of x; the default split-W map must give the same
+    bits (same operands, same MMA order)."""
+    n, h, w, cin, cout, k, stride = shape
+    x = nhwc_bf16(n, h, w, cin, 41)
+    wt = weight(cout, cin, k, 42)
+    ys = []
+    for flags in (0, 4):
+        y = torch.empty(n, h // 2, w // 2, cout, device="cuda", dtype=torch.bfloat16)
+        ops.conv_fprop(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=flags), x, ops.pack_weight_fprop(wt), y)
+        ys.append(y)
+    torch.cuda.synchronize()
+    assert torch.equal(ys[0], ys[1])
+
+
 @pytest.mark.parametrize("shape", CONV_SHAPES)
 def test_conv_wgrad(ops, shape):
     n, h, w, cin, cout, k, stride = shape
