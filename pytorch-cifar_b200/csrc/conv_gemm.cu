@@ -35,7 +35,8 @@ struct TapCfg {
     static constexpr int kTmemCols = 2 * BN;
     static constexpr int kBarBytes = 256;                       // (2*stages + 4) mbarriers + tmem ptr
     static constexpr int kStatBytes = 2 * 4 * BN * 4;           // [sum|sq][quarter][BN] fp32 running sums
-    static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes + kStatBytes;
+    static constexpr int kStoreBytes = 8 * 2048;                // per-epilogue-warp store staging (32 rows x 64 B)
+    static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kBarBytes + kStatBytes + kStoreBytes;
 };
 
 template <int BN, bool kStats>
@@ -44,7 +45,9 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                 const __grid_constant__ CUtensorMap mapB, const __grid_constant__ TapGemmParams p) {
     using Cfg = TapCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // (offset arithmetic on the shared pointer itself keeps the address space visible to the compiler: plain
+    // loads / stores below become LDS / STS instead of generic accesses)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* aux = smem + Cfg::kStages * Cfg::kStageBytes;
     uint64_t* full = reinterpret_cast<uint64_t*>(aux);
     uint64_t* empty = full + Cfg::kStages;
@@ -52,6 +55,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
     float* stat = reinterpret_cast<float*>(aux + Cfg::kBarBytes);
+    uint8_t* store_stage = aux + Cfg::kBarBytes + Cfg::kStatBytes;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -230,16 +234,17 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                             v[g * 8 + 7] += bf16hi(u.w);
                         }
                     }
-                    uint4* dst = reinterpret_cast<uint4*>(p.out + off + c * 32);
+                }
+                {
+                    uint4 u[4];
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
-                        uint4 u;
-                        u.x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
-                        u.y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
-                        u.z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
-                        u.w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
-                        dst[g] = u;
+                        u[g].x = pack_bf16x2(v[g * 8 + 0], v[g * 8 + 1]);
+                        u[g].y = pack_bf16x2(v[g * 8 + 2], v[g * 8 + 3]);
+                        u[g].z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
+                        u[g].w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
                     }
+                    store_chunk_staged(store_stage + (warp - 2) * 2048, p.out, off + c * 32, valid, u, lane);
                 }
                 if (kStats) {
                     // rows past m_total were zero-filled by TMA, so they add nothing

@@ -27,17 +27,18 @@ namespace b2c {
 namespace {
 
 constexpr int kAStageBytes = 23552;  // 180 rows x 128 B rounded up to 1024
-constexpr int kBRingBytes = 128 * 1024;
 
 template <int BN>
 struct HaloCfg {
     static constexpr int kBBytes = BN * 128;
     static constexpr int kSA = BN == 256 ? 2 : 4;      // activation stages (power of two)
-    static constexpr int kSB = kBRingBytes / kBBytes;  // 16 / 8 / 4: power of two
+    static constexpr int kBRingBytes = (BN == 256 ? 128 : 112) * 1024;
+    static constexpr int kSB = kBRingBytes / kBBytes;  // 14 / 7 / 4 weight-tile slots
     static constexpr int kTmemCols = 2 * BN;
     static constexpr int kBarBytes = 512;
     static constexpr int kStatBytes = 2 * 4 * BN * 4;
-    static constexpr int kSmemBytes = 1024 + kSA * kAStageBytes + kBRingBytes + kBarBytes + kStatBytes;
+    static constexpr int kStoreBytes = 8 * 2048;       // per-epilogue-warp store staging (store_chunk_staged)
+    static constexpr int kSmemBytes = 1024 + kSA * kAStageBytes + kBRingBytes + kBarBytes + kStatBytes + kStoreBytes;
 };
 
 template <int BN, bool kStats, int MODE, bool RES>
@@ -49,15 +50,17 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     constexpr int LOADS = MODE == 0 ? 1 : 3;   // activation boxes per 64-channel chunk
     constexpr int TPL = 9 / LOADS;             // taps served by one box
     constexpr uint32_t kABytes = MODE == 0 ? 180u * 128u : 160u * 128u;
-    constexpr uint32_t kSBmask = Cfg::kSB - 1;
-    static_assert((Cfg::kSB & (Cfg::kSB - 1)) == 0 && (kSA & (kSA - 1)) == 0, "rings are powers of two");
+    constexpr uint32_t kSB = Cfg::kSB;
+    static_assert((kSA & (kSA - 1)) == 0, "the activation ring is a power of two");
+    static_assert((2 * kSA + 2 * Cfg::kSB + 4) * 8 + 4 <= Cfg::kBarBytes, "barrier block");
     static_assert(!RES || Cfg::kSB >= 9, "resident weights need nine slots");
 
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    // (offset arithmetic on the shared pointer keeps the address space visible: LDS / STS, not generic accesses)
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* sA = smem;
     uint8_t* sB = smem + kSA * kAStageBytes;
-    uint8_t* aux = sB + kBRingBytes;
+    uint8_t* aux = sB + Cfg::kBRingBytes;
     uint64_t* full_a = reinterpret_cast<uint64_t*>(aux);
     uint64_t* empty_a = full_a + kSA;
     uint64_t* full_b = empty_a + kSA;
@@ -66,6 +69,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
     float* stat = reinterpret_cast<float*>(aux + Cfg::kBarBytes);
+    uint8_t* store_stage = aux + Cfg::kBarBytes + Cfg::kStatBytes;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -135,8 +139,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                                 const int b = MODE == 0 ? j % 3 : j;
                                 const int r = p.flip ? 2 - a : a;
                                 const int s = p.flip ? 2 - b : b;
-                                const uint32_t bi = RES ? static_cast<uint32_t>(l * TPL + j) : ((b_cnt + j) & kSBmask);
-                                if (!RES) mbar_wait(&empty_b[bi], (((b_cnt + j) / Cfg::kSB) & 1u) ^ 1u, 22);
+                                const uint32_t bi = RES ? static_cast<uint32_t>(l * TPL + j) : ((b_cnt + j) % kSB);
+                                if (!RES) mbar_wait(&empty_b[bi], (((b_cnt + j) / kSB) & 1u) ^ 1u, 22);
                                 mbar_arrive_expect_tx(&full_b[bi], Cfg::kBBytes);
                                 tma_load_2d(sB + bi * Cfg::kBBytes, &mapB, &full_b[bi], kc * 64,
                                             (r * 3 + s) * p.b_rows_per_tap + brow0);
@@ -173,9 +177,9 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
 #pragma unroll
                         for (int j = 0; j < TPL; ++j) {
                             const int off_rows = MODE == 0 ? (j / 3) * 10 + (j % 3) : j;
-                            const uint32_t bi = RES ? static_cast<uint32_t>(l * TPL + j) : ((b_cnt + j) & kSBmask);
+                            const uint32_t bi = RES ? static_cast<uint32_t>(l * TPL + j) : ((b_cnt + j) % kSB);
                             if (!RES) {
-                                mbar_wait(&full_b[bi], ((b_cnt + j) / Cfg::kSB) & 1u, 25);
+                                mbar_wait(&full_b[bi], ((b_cnt + j) / kSB) & 1u, 25);
                                 tc_fence_after();
                             } else if (first) {
                                 mbar_wait(&full_b[bi], 0, 25);
@@ -260,16 +264,17 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                             v[gg * 8 + 7] += bf16hi(u.w);
                         }
                     }
-                    uint4* dst = reinterpret_cast<uint4*>(p.out + off + c * 32);
+                }
+                {
+                    uint4 u[4];
 #pragma unroll
                     for (int gg = 0; gg < 4; ++gg) {
-                        uint4 u;
-                        u.x = pack_bf16x2(v[gg * 8 + 0], v[gg * 8 + 1]);
-                        u.y = pack_bf16x2(v[gg * 8 + 2], v[gg * 8 + 3]);
-                        u.z = pack_bf16x2(v[gg * 8 + 4], v[gg * 8 + 5]);
-                        u.w = pack_bf16x2(v[gg * 8 + 6], v[gg * 8 + 7]);
-                        dst[gg] = u;
+                        u[gg].x = pack_bf16x2(v[gg * 8 + 0], v[gg * 8 + 1]);
+                        u[gg].y = pack_bf16x2(v[gg * 8 + 2], v[gg * 8 + 3]);
+                        u[gg].z = pack_bf16x2(v[gg * 8 + 4], v[gg * 8 + 5]);
+                        u[gg].w = pack_bf16x2(v[gg * 8 + 6], v[gg * 8 + 7]);
                     }
+                    store_chunk_staged(store_stage + (warp - 2) * 2048, p.out, off + c * 32, valid, u, lane);
                 }
                 if (kStats) {
                     // rows of images past N were zero-filled by TMA, so they add nothing
