@@ -215,6 +215,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
         const int g = row >> 3, j = row & 7;
         const int half = (warp - 2) >> 2;   // two warps per TMEM lane quarter, alternating 32-column chunks
         const int et = threadIdx.x - 64;
+        // BN == 64: a warp owns the same 32 channels in every tile, so the per-channel sums run in registers (one
+        // add + one fma per element) and the cross-lane reduction happens once, after the last tile.
+        constexpr bool kRegStats = kStats && BN == 64;
+        float rs1[32], rs2[32];
+        if constexpr (kRegStats) {
+#pragma unroll
+            for (int e = 0; e < 32; ++e) { rs1[e] = 0.f; rs2[e] = 0.f; }
+        }
         if (kStats) {
             for (int c = lane + 32 * half; c < BN; c += 64) {   // the chunks this warp owns
                 stat[(0 * 4 + q) * BN + c] = 0.f;
@@ -276,8 +284,14 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     }
                     store_chunk_staged(store_stage + (warp - 2) * 2048, p.out, off + c * 32, valid, u, lane);
                 }
-                if (kStats) {
-                    // rows of images past N were zero-filled by TMA, so they add nothing
+                if constexpr (kRegStats) {
+                    // (rows past the end were zero-filled by TMA, so they add nothing)
+#pragma unroll
+                    for (int e = 0; e < 32; ++e) {
+                        rs1[e] += v[e];
+                        rs2[e] = fmaf(v[e], v[e], rs2[e]);
+                    }
+                } else if (kStats) {
                     float sq[32];
 #pragma unroll
                     for (int e = 0; e < 32; ++e) sq[e] = v[e] * v[e];
@@ -294,6 +308,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 acc = 0;
                 acc_phase ^= 1u;
             }
+        }
+        if constexpr (kRegStats) {
+            const float s1 = warp_colsum32(rs1, lane);
+            const float s2 = warp_colsum32(rs2, lane);
+            stat[(0 * 4 + q) * BN + half * 32 + lane] = s1;
+            stat[(1 * 4 + q) * BN + half * 32 + lane] = s2;
         }
         if (kStats) {
             named_bar_sync(1, 256);
