@@ -128,7 +128,7 @@ def run_reference(args):
 LAUNCHES = {"b2c_conv_fprop": 1, "b2c_conv_wgrad": 1, "b2c_bn_finalize": 1, "b2c_bn_eval_scale_shift": 1,
             "b2c_bn_act_apply": 1, "b2c_bn_bwd_reduce": 1, "b2c_bn_bwd_finalize": 1, "b2c_bn_bwd_apply": 1,
             "b2c_head_fwd": 1, "b2c_ce_loss": 1, "b2c_head_bwd": 2, "b2c_augment_im2col": 1, "b2c_augment_nchw": 1,
-            "b2c_stem_im2col": 1, "b2c_sgd_step": 1, "b2c_repack_weights": 1, "b2c_conv_dgrad_with_shortcut": 1}
+            "b2c_stem_im2col": 1, "b2c_sgd_step": 1, "b2c_repack_weights": 1, "b2c_conv_dgrad_with_shortcut": 1, "b2c_conv_dgrad_bn": 1}
 
 
 def count_launches(calls):
@@ -265,7 +265,7 @@ def run_product(args):
     peaks = load_peaks()
     raw = _lib.load()
     tap_calls = [(n, a) for n, a in calls
-                 if n in ("b2c_conv_fprop", "b2c_conv_dgrad", "b2c_conv_dgrad_with_shortcut")]
+                 if n in ("b2c_conv_fprop", "b2c_conv_dgrad", "b2c_conv_dgrad_with_shortcut", "b2c_conv_dgrad_bn")]
     wg_calls = [(n, a) for n, a in calls if n == "b2c_conv_wgrad"]
     tap_fl, wg_fl = conv_flops(calls)
 

@@ -72,6 +72,17 @@ B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fp
 B2C_API int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
                    void* stream);
 
+/* b2c_conv_dgrad whose result is the gradient w.r.t. relu(bn(y_bn)) — `out = F.relu(self.bn1(self.conv1(x)))`,
+ * models/resnet.py:47 — with that ReLU/BatchNorm backward's first pass fused into the epilogue:
+ *   dz = (conv_transpose(dy, w) [+ add_src]) * [fma(y_bn, scale, shift) > 0]      (written to `dz`, bf16)
+ *   partial[r][0][c] = sum over the pixels CTA r handled of dz,  partial[r][1][c] = ... of dz * y_bn   (fp32)
+ * *stat_rows (host int) receives the number of rows r (<= 148); pass `partial` and it to b2c_bn_bwd_finalize, then
+ * b2c_bn_bwd_apply(dz, y_bn, ...). Replaces b2c_conv_dgrad + b2c_bn_bwd_reduce: one full read of dz and y less.
+ * scale/shift are the forward b2c_bn_finalize outputs of that BatchNorm. Not for ksize==1 && stride==2. */
+B2C_API int b2c_conv_dgrad_bn(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dz, const void* add_src,
+                      const void* y_bn, const float* scale, const float* shift, float* partial, int* stat_rows,
+                      void* stream);
+
 /* dx = dgrad3x3s2(dy, w[0..8]) + dgrad1x1s2(dy_shortcut, w[9]) (+ add_src) in one launch: the backward of a
  * down-sampling block's fan-out `conv1(x)` / `shortcut(x)`, models/resnet.py:23,33-34,47-49 and
  * models/preact_resnet.py:27-31 (autograd sums the two input gradients, main.py:104). d describes the 3x3

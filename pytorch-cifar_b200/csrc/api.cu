@@ -107,6 +107,15 @@ bool grid_tiles(int gH, int gW, int px) {
     return (img % px) == 0 || (px % img) == 0;
 }
 
+// Operands of the fused BatchNorm backward of b2c_conv_dgrad_bn (null pointer = plain dgrad).
+struct BnFuse {
+    const void* y;         // the BatchNorm's input (the conv output of the forward pass), dx's shape
+    const float* scale;    // forward scale / shift of that BatchNorm (relu mask = fma(y, scale, shift) > 0)
+    const float* shift;
+    float* partial;        // [rows][2][cin] fp32 partial sums for b2c_bn_bwd_finalize
+    int* stat_rows;
+};
+
 // 3x3 stride-1 convs on square 32 / 16 / 8 pixel images go to the halo-reuse kernel (conv_halo.cu).
 bool use_halo(const B2cConvDesc* d) {
     if (d->flags & 1) return false;
@@ -115,7 +124,8 @@ bool use_halo(const B2cConvDesc* d) {
 }
 
 int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w, int gemm_n, int bn, bool flip,
-                void* out, const void* add_src, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t st) {
+                void* out, const void* add_src, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t st,
+                const BnFuse* bn_fuse = nullptr) {
     b2c::HaloParams p = {};
     p.N = d->n;
     p.H = d->h;
@@ -134,6 +144,16 @@ int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w,
     p.part_sum = part_sum;
     p.part_sq = part_sq;
     p.cout = gemm_n;
+    p.stat_ld = gemm_n;
+    if (bn_fuse != nullptr) {
+        p.bwd_y = static_cast<const __nv_bfloat16*>(bn_fuse->y);
+        p.bwd_scale = bn_fuse->scale;
+        p.bwd_shift = bn_fuse->shift;
+        p.part_sum = bn_fuse->partial;
+        p.part_sq = bn_fuse->partial + gemm_n;
+        p.stat_ld = 2 * gemm_n;
+        stat_rows = bn_fuse->stat_rows;
+    }
     p.debug = d->flags & 0x3e;
     CUtensorMap ma, mb;
     int rc = p.mode == 0 ? encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 18, 1, 1)
@@ -228,6 +248,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     p.part_sum = part_sum;
     p.part_sq = part_sq;
     p.cout = d->cout;
+    p.stat_ld = d->cout;
 
     const int bh = (128 / wo) < ho ? (128 / wo) : ho;
     const int bnb = 128 / (wo * bh);
@@ -243,7 +264,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
 }
 
 static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_shortcut, const void* w_dgrad,
-                           void* dx, const void* add_src, void* stream) {
+                           void* dx, const void* add_src, void* stream, const BnFuse* bn_fuse = nullptr) {
     int rc = check_conv(d);
     if (rc) return rc;
     if (!dy || !w_dgrad || !dx || !aligned16(dy) || !aligned16(w_dgrad) || !aligned16(dx) || !aligned16(add_src))
@@ -259,7 +280,8 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
     cudaStream_t st = as_stream(stream);
     if (halo)
-        return launch_halo(d, dy, d->cout, w_dgrad, d->cin, bn, true, dx, add_src, nullptr, nullptr, nullptr, st);
+        return launch_halo(d, dy, d->cout, w_dgrad, d->cin, bn, true, dx, add_src, nullptr, nullptr, nullptr, st,
+                           bn_fuse);
 
     TapGemmParams p = {};
     p.num_n_tiles = d->cin / bn;
@@ -273,6 +295,17 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     p.part_sum = nullptr;
     p.part_sq = nullptr;
     p.cout = d->cin;
+    p.stat_ld = d->cin;
+    int* stat_rows = nullptr;
+    if (bn_fuse != nullptr) {
+        p.bwd_y = static_cast<const __nv_bfloat16*>(bn_fuse->y);
+        p.bwd_scale = bn_fuse->scale;
+        p.bwd_shift = bn_fuse->shift;
+        p.part_sum = bn_fuse->partial;
+        p.part_sq = bn_fuse->partial + d->cin;
+        p.stat_ld = 2 * d->cin;
+        stat_rows = bn_fuse->stat_rows;
+    }
 
     CUtensorMap ma, mb;
     rc = encode_2d(&mb, w_dgrad, static_cast<long long>(taps + (dy_shortcut != nullptr ? 1 : 0)) * d->cin, d->cout,
@@ -299,7 +332,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         }
         p.sy = p.sx = 1;
         single_phase(p);
-        return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st));
+        return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, st));
     }
 
     // stride 2: one GEMM per output parity phase (ph, pw); dx[2i+ph, 2j+pw] only sees taps with
@@ -315,6 +348,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     p.gW = wo;
     p.sy = p.sx = 2;
     if (d->ksize == 1) {
+        if (bn_fuse != nullptr) return B2C_ERR_UNSUPPORTED;
         if (add_src != nullptr && add_src != dx) return B2C_ERR_UNSUPPORTED;
         if (add_src == nullptr) {
             cudaError_t e = cudaMemsetAsync(dx, 0, static_cast<size_t>(d->n) * d->h * d->w * d->cin * 2, st);
@@ -365,12 +399,20 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     p.phase_begin[4] = static_cast<uint8_t>(nt);
     p.num_taps = nt;
     p.num_phases = 4;
-    return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma1, mb, p, max_ctas, nullptr, st));
+    return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma1, mb, p, max_ctas, stat_rows, st));
 }
 
 int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
                    void* stream) {
     return conv_dgrad_impl(d, dy, nullptr, w_dgrad, dx, add_src, stream);
+}
+
+int b2c_conv_dgrad_bn(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dz, const void* add_src,
+                      const void* y_bn, const float* scale, const float* shift, float* partial, int* stat_rows,
+                      void* stream) {
+    if (!y_bn || !scale || !shift || !partial || !stat_rows || !aligned16(y_bn)) return B2C_ERR_ARG;
+    BnFuse f = {y_bn, scale, shift, partial, stat_rows};
+    return conv_dgrad_impl(d, dy, nullptr, w_dgrad, dz, add_src, stream, &f);
 }
 
 int b2c_conv_dgrad_with_shortcut(const B2cConvDesc* d, const void* dy, const void* dy_shortcut, const void* w_dgrad10,

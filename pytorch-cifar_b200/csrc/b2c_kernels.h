@@ -38,6 +38,12 @@ struct TapGemmParams {
     float* part_sum;               // optional [stat_rows][cout] per-CTA column sums (stat_rows <= 148)
     float* part_sq;                // optional [stat_rows][cout] per-CTA column sums of squares
     int cout;
+    // Fused BatchNorm backward (dgrad feeding relu(bn(y))): when bwd_y is set the epilogue masks the result with
+    // fma(y, bwd_scale, bwd_shift) > 0 before the store and the two statistics become sum(dz), sum(dz * y).
+    const __nv_bfloat16* bwd_y;
+    const float* bwd_scale;
+    const float* bwd_shift;
+    int stat_ld;                   // row pitch of part_sum / part_sq (floats)
 };
 
 // wgrad: dW[cout, cin, tap] += sum_pixels dY[pixel, cout] * X[pixel + shift_tap, cin]
@@ -81,6 +87,12 @@ struct HaloParams {
     float* part_sum;
     float* part_sq;
     int cout;
+    // Fused BatchNorm backward (dgrad feeding relu(bn(y))): when bwd_y is set the epilogue masks the result with
+    // fma(y, bwd_scale, bwd_shift) > 0 before the store and the two statistics become sum(dz), sum(dz * y).
+    const __nv_bfloat16* bwd_y;
+    const float* bwd_scale;
+    const float* bwd_shift;
+    int stat_ld;                   // row pitch of part_sum / part_sq (floats)
 };
 
 cudaError_t launch_conv_halo(int bn, const CUtensorMap& a, const CUtensorMap& b, const HaloParams& p, int max_ctas,

@@ -36,7 +36,7 @@ struct HaloCfg {
     static constexpr int kSB = kBRingBytes / kBBytes;  // 14 / 7 / 4 weight-tile slots
     static constexpr int kTmemCols = 2 * BN;
     static constexpr int kBarBytes = 512;
-    static constexpr int kStatBytes = 2 * 4 * BN * 4;
+    static constexpr int kStatBytes = 2 * 4 * BN * 4 + 2 * BN * 4;   // running sums + fused-BN-backward scale|shift
     static constexpr int kStoreBytes = 8 * 2048;       // per-epilogue-warp store staging (store_chunk_staged)
     static constexpr int kSmemBytes = 1024 + kSA * kAStageBytes + kBRingBytes + kBarBytes + kStatBytes + kStoreBytes;
 };
@@ -69,6 +69,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     uint64_t* tempty = tfull + 2;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
     float* stat = reinterpret_cast<float*>(aux + Cfg::kBarBytes);
+    float* bwd_sc = stat + 2 * 4 * BN;          // [scale | shift] of this CTA's channels (fused BN backward)
     uint8_t* store_stage = aux + Cfg::kBarBytes + Cfg::kStatBytes;
 
     const int warp = threadIdx.x >> 5;
@@ -229,6 +230,15 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                 stat[(1 * 4 + q) * BN + c] = 0.f;
             }
         }
+        const bool bwd_fused = kStats && p.bwd_y != nullptr;
+        if (bwd_fused) {
+            const int ch0 = (blockIdx.x % p.num_n_tiles) * BN;     // constant per CTA (see the launcher)
+            for (int i = et; i < BN; i += 256) {
+                bwd_sc[i] = __ldg(p.bwd_scale + ch0 + i);
+                bwd_sc[BN + i] = __ldg(p.bwd_shift + ch0 + i);
+            }
+            named_bar_sync(1, 256);
+        }
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -273,6 +283,43 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                         }
                     }
                 }
+                float sq[32];      // second statistic operand (BN > 64 only; 64-wide tiles accumulate in registers)
+                if (kStats) {
+                    if (bwd_fused) {
+                        const uint4* ysrc = reinterpret_cast<const uint4*>(p.bwd_y + off + c * 32);
+                        const float* scs = bwd_sc + c * 32;
+                        const float* shs = bwd_sc + BN + c * 32;
+#pragma unroll
+                        for (int g4 = 0; g4 < 4; ++g4) {
+                            const uint4 yu = valid ? __ldg(ysrc + g4) : make_uint4(0u, 0u, 0u, 0u);
+                            const float yy[8] = {bf16lo(yu.x), bf16hi(yu.x), bf16lo(yu.y), bf16hi(yu.y),
+                                                 bf16lo(yu.z), bf16hi(yu.z), bf16lo(yu.w), bf16hi(yu.w)};
+#pragma unroll
+                            for (int k8 = 0; k8 < 8; ++k8) {
+                                const int e = g4 * 8 + k8;
+                                const float dz = fmaf(yy[k8], scs[e], shs[e]) > 0.f ? v[e] : 0.f;
+                                v[e] = dz;
+                                if constexpr (kRegStats) {
+                                    rs1[e] += dz;
+                                    rs2[e] = fmaf(dz, yy[k8], rs2[e]);
+                                } else {
+                                    sq[e] = dz * yy[k8];
+                                }
+                            }
+                        }
+                    } else {
+                        // (rows past the end were zero-filled by TMA, so they add nothing)
+#pragma unroll
+                        for (int e = 0; e < 32; ++e) {
+                            if constexpr (kRegStats) {
+                                rs1[e] += v[e];
+                                rs2[e] = fmaf(v[e], v[e], rs2[e]);
+                            } else {
+                                sq[e] = v[e] * v[e];
+                            }
+                        }
+                    }
+                }
                 {
                     uint4 u[4];
 #pragma unroll
@@ -284,17 +331,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                     }
                     store_chunk_staged(store_stage + (warp - 2) * 2048, p.out, off + c * 32, valid, u, lane);
                 }
-                if constexpr (kRegStats) {
-                    // (rows past the end were zero-filled by TMA, so they add nothing)
-#pragma unroll
-                    for (int e = 0; e < 32; ++e) {
-                        rs1[e] += v[e];
-                        rs2[e] = fmaf(v[e], v[e], rs2[e]);
-                    }
-                } else if (kStats) {
-                    float sq[32];
-#pragma unroll
-                    for (int e = 0; e < 32; ++e) sq[e] = v[e] * v[e];
+                if constexpr (kStats && !kRegStats) {
                     const float s1 = warp_colsum32(v, lane);
                     const float s2 = warp_colsum32(sq, lane);
                     stat[(0 * 4 + q) * BN + c * 32 + lane] += s1;
@@ -324,7 +361,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
                                  stat[(0 * 4 + 2) * BN + col] + stat[(0 * 4 + 3) * BN + col];
                 const float s2 = stat[(1 * 4 + 0) * BN + col] + stat[(1 * 4 + 1) * BN + col] +
                                  stat[(1 * 4 + 2) * BN + col] + stat[(1 * 4 + 3) * BN + col];
-                const size_t o = static_cast<size_t>(prow) * p.cout + n_tile * BN + col;
+                const size_t o = static_cast<size_t>(prow) * p.stat_ld + n_tile * BN + col;
                 p.part_sum[o] = s1;
                 p.part_sq[o] = s2;
             }

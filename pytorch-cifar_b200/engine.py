@@ -11,6 +11,8 @@ main.py:99-105 (step order).
 """
 from collections import OrderedDict
 
+import os
+
 import torch
 
 from . import ops
@@ -280,6 +282,10 @@ def _bottleneck_spec(num_blocks, planes, num_classes):
     return dict(family="bottleneck", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin)
 
 
+# measurement switch (A/B runs on one box): 0 = separate dgrad and bn_bwd_reduce launches
+FUSE_DGRAD_BN = os.environ.get("B2C_FUSE_DGRAD_BN", "1") != "0"
+
+
 class ConvUnit:
     """One conv (+ the BatchNorm that follows it): descriptors, operand views, statistic buffers.
     Channel counts are the reference's; tensors are laid out with channels padded to multiples of 64
@@ -349,6 +355,19 @@ class ConvUnit:
 
     def dgrad(self, dy, dx, add_src=None):
         ops.conv_dgrad(self.desc, dy, self.wd, dx, add_src)
+
+    def dgrad_bn(self, eng, dy, dz, bn_unit, add_src=None):
+        """dgrad whose result is the gradient w.r.t. relu(bn(bn_unit.y)): the epilogue applies that ReLU's mask
+        and emits the BatchNorm-backward partial sums (b2c_conv_dgrad_bn). Returns the partial-row count for
+        bn_unit.bn_backward_from_partial."""
+        return ops.conv_dgrad_bn(self.desc, dy, self.wd, dz, bn_unit.y, bn_unit.scale, bn_unit.shift,
+                                 eng.bwd_partial, add_src)
+
+    def bn_backward_from_partial(self, eng, dz, dy, prow, add=None):
+        """Second half of bn_backward when the producer of dz already masked it and reduced it (dgrad_bn)."""
+        ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
+                            self.dgamma, self.dbeta, eng.coef_a, eng.coef_b, eng.coef_c)
+        ops.bn_bwd_apply(dz, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add)
 
     def dgrad_with_shortcut(self, dy, dy_sc, sc, dx):
         """dx = dgrad(self, dy) + dgrad(sc, dy_sc): the two consumers of a down-sampling block's input
@@ -643,9 +662,13 @@ class Engine:
                 if cs is not None:
                     cs.bn_backward(self, dout, None, None, dys)
                 c2.wgrad(dy2)
-                c2.dgrad(dy2, da1)
-                # a1 = relu(bn1(y1))
-                c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
+                # a1 = relu(bn1(y1)): its mask and BN-backward sums come out of conv2's dgrad epilogue
+                if FUSE_DGRAD_BN:
+                    prow = c2.dgrad_bn(self, dy2, da1, c1)
+                    c1.bn_backward_from_partial(self, da1, dy1, prow)
+                else:
+                    c2.dgrad(dy2, da1)
+                    c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dys)
@@ -756,6 +779,7 @@ class Engine:
             stat_rows = 0
             bn_stats = ConvUnit.bn_stats
             bn_backward = ConvUnit.bn_backward
+            bn_backward_from_partial = ConvUnit.bn_backward_from_partial
 
         F.append(lambda training: stem.fprop(self, True))
         x, H, W, producer = stem.y, 32, 32, stem
@@ -1030,3 +1054,4 @@ class Engine:
 
 DwUnit.bn_stats = ConvUnit.bn_stats
 DwUnit.bn_backward = ConvUnit.bn_backward
+DwUnit.bn_backward_from_partial = ConvUnit.bn_backward_from_partial

@@ -67,6 +67,18 @@ def conv_dgrad(d, dy, w_dgrad, dx, add_src=None):
           "b2c_conv_dgrad")
 
 
+def conv_dgrad_bn(d, dy, w_dgrad, dz, y_bn, scale, shift, partial, add_src=None):
+    """dgrad + the reduce pass of the following relu(bn(y_bn)) backward; returns the partial-row count."""
+    lib = _lib.load()
+    _need(dy, torch.bfloat16, "dy"); _need(w_dgrad, torch.bfloat16, "w"); _need(dz, torch.bfloat16, "dz")
+    _need(y_bn, torch.bfloat16, "y_bn"); _need(add_src, torch.bfloat16, "add_src")
+    _need(scale, torch.float32, "scale"); _need(shift, torch.float32, "shift"); _need(partial, torch.float32, "partial")
+    rows = ctypes.c_int(0)
+    check(lib.b2c_conv_dgrad_bn(ctypes.byref(d), _p(dy), _p(w_dgrad), _p(dz), _p(add_src), _p(y_bn), _p(scale),
+                                _p(shift), _p(partial), ctypes.byref(rows), _stream()), "b2c_conv_dgrad_bn")
+    return rows.value
+
+
 def conv_dgrad_with_shortcut(d, dy, dy_shortcut, w_dgrad10, dx, add_src=None):
     """3x3 stride-2 dgrad + the 1x1 stride-2 shortcut's dgrad in one launch; w_dgrad10 = [10][cin][cout]."""
     lib = _lib.load()

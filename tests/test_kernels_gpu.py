@@ -184,6 +184,46 @@ def test_conv_dgrad_with_shortcut(ops, n, h, cin, cout, with_add):
         ops.conv_dgrad_with_shortcut(ops.conv_desc(n, h, h, cin, cout, 3, 1), dy, dys, w10, dx, add)
 
 
+@pytest.mark.parametrize("shape", [(4, 32, 32, 64, 64, 3, 1), (8, 16, 16, 128, 128, 3, 1), (16, 8, 8, 256, 256, 3, 1),
+                                   (32, 4, 4, 512, 512, 3, 1), (8, 16, 16, 64, 128, 3, 2), (4, 16, 16, 64, 256, 1, 1),
+                                   (3, 8, 8, 128, 128, 3, 1), (5, 4, 4, 64, 64, 3, 1)])
+def test_conv_dgrad_bn_fused(ops, shape):
+    """b2c_conv_dgrad_bn == b2c_conv_dgrad followed by b2c_bn_bwd_reduce with the mask taken from y: the masked
+    gradient must be bit-identical, the partial sums equal up to fp32 summation order (and the fused sums see
+    the gradient before its bf16 rounding)."""
+    n, h, w, cin, cout, k, stride = shape
+    ho, wo = h // stride, w // stride
+    dy = nhwc_bf16(n, ho, wo, cout, 51)
+    wd = ops.pack_weight_dgrad(weight(cout, cin, k, 52))
+    y_bn = nhwc_bf16(n, h, w, cin, 53)
+    g = torch.Generator(device="cuda").manual_seed(54)
+    scale = torch.rand(cin, device="cuda", generator=g) + 0.5
+    shift = torch.randn(cin, device="cuda", generator=g) * 0.3
+    d = ops.conv_desc(n, h, w, cin, cout, k, stride)
+    rows = n * h * w
+    # two-pass reference through the unfused entry points
+    dx = torch.empty(n, h, w, cin, device="cuda", dtype=torch.bfloat16)
+    ops.conv_dgrad(d, dy, wd, dx)
+    prow_ref = ops.bn_bwd_partial_rows(rows, cin)
+    part_ref = torch.zeros(prow_ref, 2, cin, device="cuda")
+    ops.bn_bwd_reduce(dx, None, y_bn, None, rows, cin, part_ref, scale, shift)
+    z = y_bn.double() * scale.double() + shift.double()
+    eps = 1e-6 * (y_bn.double().abs() * scale.double().abs() + shift.double().abs())
+    # fused
+    dz = torch.full_like(dx, float("nan"))
+    part = torch.full((148, 2, cin), float("nan"), device="cuda")
+    prow = ops.conv_dgrad_bn(d, dy, wd, dz, y_bn, scale, shift, part)
+    torch.cuda.synchronize()
+    assert 1 <= prow <= 148
+    assert torch.isfinite(dz.float()).all() and torch.isfinite(part[:prow]).all()
+    on, off = z > eps, z < -eps                     # (the few elements within rounding of 0 may go either way)
+    assert torch.equal(dz[on], dx[on]) and (dz[off] == 0).all()
+    assert (on | off).float().mean() > 0.999
+    got, ref = part[:prow].double().sum(0), part_ref.double().sum(0)
+    scale_ = ref.abs().max()
+    assert (got - ref).abs().max() <= 2e-3 * scale_ + 1e-3, ((got - ref).abs().max().item(), scale_.item())
+
+
 @pytest.mark.parametrize("shape", [(8, 32, 32, 64, 128, 3, 2), (8, 16, 16, 128, 256, 1, 2)])
 def test_stride2_split_w_map_equals_traversal_stride(ops, shape):
     """flags bit 2 selects the TMA traversal-stride addressing of x; the default split-W map must give the same
