@@ -747,15 +747,29 @@ class Engine:
             dy = self.new_act(*u.y.shape)
             dx = self.new_act(*xin.shape) if si > 0 else None
 
-            def bwd(u=u, act=act, pooled=pooled, dout=dout, dact=dact, dy=dy, dx=dx):
+            # the unit below (si-1) takes its BN-backward sums from this unit's dgrad epilogue when no max-pool
+            # sits between them; `fused_in` says whether the unit above did that for us
+            prev = stages[si - 1] if si > 0 else None
+            fuse_out = FUSE_DGRAD_BN and prev is not None and prev[2] is None
+            fused_in = FUSE_DGRAD_BN and si + 1 < len(stages) and pooled is None
+            prow_box = self._vgg_prow = getattr(self, "_vgg_prow", {})
+
+            def bwd(u=u, act=act, pooled=pooled, dout=dout, dact=dact, dy=dy, dx=dx, si=si, prev=prev,
+                    fuse_out=fuse_out, fused_in=fused_in):
                 g = dout
                 if pooled is not None:
                     ops.maxpool2x2_bwd(act, pooled, dout, dact)
                     g = dact
-                u.bn_backward(self, g, act, g, dy, relu_from_y=True)
+                if fused_in:
+                    u.bn_backward_from_partial(self, g, dy, prow_box[si])
+                else:
+                    u.bn_backward(self, g, act, g, dy, relu_from_y=True)
                 u.wgrad(dy)
                 if dx is not None:
-                    u.dgrad(dy, dx)
+                    if fuse_out:
+                        prow_box[si - 1] = u.dgrad_bn(self, dy, dx, prev[0])
+                    else:
+                        u.dgrad(dy, dx)
             Bk.append(bwd)
             dout = dx
         self.bwd_ops = Bk
@@ -820,8 +834,11 @@ class Engine:
 
             def bwd(bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, cs=cs, dout=dout, da2=da2, dy1=dy1, da=da, dx=dx):
                 c2.wgrad(dout)                              # d(conv2 out) = d(block out)
-                c2.dgrad(dout, da2)
-                c1.bn_backward(self, da2, a2, da2, dy1, relu_from_y=True)     # a2 = relu(bn2(conv1 out))
+                if FUSE_DGRAD_BN:                           # a2 = relu(bn2(conv1 out))
+                    c1.bn_backward_from_partial(self, da2, dy1, c2.dgrad_bn(self, dout, da2, c1))
+                else:
+                    c2.dgrad(dout, da2)
+                    c1.bn_backward(self, da2, a2, da2, dy1, relu_from_y=True)
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dout)
@@ -902,11 +919,17 @@ class Engine:
                 if cs is not None:
                     cs.bn_backward(self, dout, None, None, dys)
                 c3.wgrad(dy3)
-                c3.dgrad(dy3, da2)
-                c2.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
+                if FUSE_DGRAD_BN:
+                    c2.bn_backward_from_partial(self, da2, dy2, c3.dgrad_bn(self, dy3, da2, c2))
+                else:
+                    c3.dgrad(dy3, da2)
+                    c2.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
                 c2.wgrad(dy2)
-                c2.dgrad(dy2, da1)
-                c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
+                if FUSE_DGRAD_BN:
+                    c1.bn_backward_from_partial(self, da1, dy1, c2.dgrad_bn(self, dy2, da1, c1))
+                else:
+                    c2.dgrad(dy2, da1)
+                    c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
                 c1.wgrad(dy1)
                 if cs is not None:
                     cs.wgrad(dys)
@@ -1012,8 +1035,11 @@ class Engine:
                 if cs is not None:
                     cs.bn_backward(self, dout, None, None, dys)
                 c3.wgrad(dy3)
-                c3.dgrad(dy3, da2)
-                dw.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
+                if FUSE_DGRAD_BN:
+                    dw.bn_backward_from_partial(self, da2, dy2, c3.dgrad_bn(self, dy3, da2, dw))
+                else:
+                    c3.dgrad(dy3, da2)
+                    dw.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
                 dw.wgrad(dy2)
                 dw.dgrad(dy2, da1)
                 c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
