@@ -243,30 +243,61 @@ __device__ __forceinline__ float warp_colsum32(float (&v)[32], int lane) {
     return v[0];
 }
 
-// Epilogue store of one warp's 32 (rows = lanes) x 32 (channels) bf16 chunk, u[4] = this lane's row as four 16-byte
-// pieces. A direct store has every lane writing 16 bytes to its own output row: 32 lines per instruction, and the
-// store queue backs up into the register file (ncu: the top epilogue stall was the WAR wait on the STG source
-// registers). Instead the chunk goes through a 2 KB per-warp shared-memory buffer and leaves as four stores that
-// each cover 8 rows x 64 contiguous bytes. The 16-byte pieces are XOR-swizzled by (row >> 1) so both the row-wise
-// write and the 8-row read are bank-conflict free. `off` = element offset of this lane's row chunk in `out`
-// (ignored when !valid). All 32 lanes must call.
-__device__ __forceinline__ void store_chunk_staged(uint8_t* stg, __nv_bfloat16* out, size_t off, bool valid,
+// Epilogue global accesses of one warp's 32 (rows = lanes) x 32 (channels) bf16 chunk. A direct access has every
+// lane touching 16 bytes of its own output row: 32 lines per instruction, and the load/store queue backs up into
+// the register file (ncu: the top epilogue stall was the WAR wait on the STG source registers). Instead the chunk
+// goes through a 2 KB per-warp shared-memory buffer: global instructions cover 8 rows x 64 contiguous bytes each,
+// lanes read / write their own row in shared memory. The 16-byte pieces are XOR-swizzled by (row >> 1) so both
+// the row-wise and the 8-row accesses are bank-conflict free.
+//   rowoff[it] = element offset of row (it*8 + lane/4) in the tensor, ~0 for rows past the end (chunk_rowoffs)
+//   col        = first channel of the chunk
+// All 32 lanes must call.
+__device__ __forceinline__ void chunk_rowoffs(size_t off, bool valid, int lane, unsigned long long (&rowoff)[4]) {
+    const unsigned long long mine = valid ? static_cast<unsigned long long>(off) : ~0ull;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) rowoff[it] = __shfl_sync(0xffffffffu, mine, it * 8 + (lane >> 2));
+}
+
+__device__ __forceinline__ void store_chunk_staged(uint8_t* stg, __nv_bfloat16* out,
+                                                   const unsigned long long (&rowoff)[4], int col,
                                                    const uint4 (&u)[4], int lane) {
-    __syncwarp();                                   // the previous chunk's reads of the buffer are done
+    __syncwarp();                                   // earlier reads of the buffer are done
     uint4* row = reinterpret_cast<uint4*>(stg + lane * 64);
     const int sw = (lane >> 1) & 3;
 #pragma unroll
     for (int g = 0; g < 4; ++g) row[g ^ sw] = u[g];
     __syncwarp();
-    const unsigned long long mine = valid ? static_cast<unsigned long long>(off) : ~0ull;
     const int piece = lane & 3;
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
         const int r = it * 8 + (lane >> 2);
-        const unsigned long long o = __shfl_sync(0xffffffffu, mine, r);
         const uint4 val = *reinterpret_cast<const uint4*>(stg + r * 64 + ((piece ^ ((r >> 1) & 3)) << 4));
-        if (o != ~0ull) *reinterpret_cast<uint4*>(out + o + piece * 8) = val;
+        if (rowoff[it] != ~0ull) *reinterpret_cast<uint4*>(out + rowoff[it] + col + piece * 8) = val;
     }
+}
+
+// The reverse: u[4] = this lane's row of a bf16 tensor chunk (zeros for rows past the end).
+__device__ __forceinline__ void load_chunk_staged(uint8_t* stg, const __nv_bfloat16* src,
+                                                  const unsigned long long (&rowoff)[4], int col, uint4 (&u)[4],
+                                                  int lane) {
+    const int piece = lane & 3;
+    uint4 val[4];
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+        val[it] = make_uint4(0u, 0u, 0u, 0u);
+        if (rowoff[it] != ~0ull) val[it] = __ldg(reinterpret_cast<const uint4*>(src + rowoff[it] + col + piece * 8));
+    }
+    __syncwarp();                                   // earlier reads of the buffer are done
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+        const int r = it * 8 + (lane >> 2);
+        *reinterpret_cast<uint4*>(stg + r * 64 + ((piece ^ ((r >> 1) & 3)) << 4)) = val[it];
+    }
+    __syncwarp();
+    const uint4* row = reinterpret_cast<const uint4*>(stg + lane * 64);
+    const int sw = (lane >> 1) & 3;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) u[g] = row[g ^ sw];
 }
 
 }  // namespace b2c

@@ -227,8 +227,11 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
             const int j = rem - i * p.gW;
             const size_t off =
                 (static_cast<size_t>(n * p.out_H + i * p.sy + p.phase_py[ph]) * p.out_W + (j * p.sx + p.phase_px[ph])) *
-                    p.out_ld +
-                static_cast<size_t>(n_tile) * BN;
+                p.out_ld;
+            const int col0 = n_tile * BN;
+            unsigned long long rowoff[4];
+            chunk_rowoffs(off, valid, lane, rowoff);
+            uint8_t* stg_w = store_stage + (warp - 2) * 2048;
             float* st = stat;
 #pragma unroll 1
             for (int c = half; c < BN / 32; c += 2) {
@@ -236,32 +239,31 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                 tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                                   static_cast<uint32_t>(acc * BN + c * 32),
                               v);
-                if (valid) {
-                    if (p.add_src != nullptr) {
-                        const uint4* src = reinterpret_cast<const uint4*>(p.add_src + off + c * 32);
+                if (p.add_src != nullptr) {
+                    uint4 au[4];
+                    load_chunk_staged(stg_w, p.add_src, rowoff, col0 + c * 32, au, lane);
 #pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            const uint4 u = __ldg(src + g);
-                            v[g * 8 + 0] += bf16lo(u.x);
-                            v[g * 8 + 1] += bf16hi(u.x);
-                            v[g * 8 + 2] += bf16lo(u.y);
-                            v[g * 8 + 3] += bf16hi(u.y);
-                            v[g * 8 + 4] += bf16lo(u.z);
-                            v[g * 8 + 5] += bf16hi(u.z);
-                            v[g * 8 + 6] += bf16lo(u.w);
-                            v[g * 8 + 7] += bf16hi(u.w);
-                        }
+                    for (int g4 = 0; g4 < 4; ++g4) {
+                        v[g4 * 8 + 0] += bf16lo(au[g4].x);
+                        v[g4 * 8 + 1] += bf16hi(au[g4].x);
+                        v[g4 * 8 + 2] += bf16lo(au[g4].y);
+                        v[g4 * 8 + 3] += bf16hi(au[g4].y);
+                        v[g4 * 8 + 4] += bf16lo(au[g4].z);
+                        v[g4 * 8 + 5] += bf16hi(au[g4].z);
+                        v[g4 * 8 + 6] += bf16lo(au[g4].w);
+                        v[g4 * 8 + 7] += bf16hi(au[g4].w);
                     }
                 }
                 float sq[32];      // second statistic operand (BN > 64 only; 64-wide tiles accumulate in registers)
                 if (kStats) {
                     if (bwd_fused) {
-                        const uint4* ysrc = reinterpret_cast<const uint4*>(p.bwd_y + off + c * 32);
                         const float* scs = bwd_sc + c * 32;
                         const float* shs = bwd_sc + BN + c * 32;
+                        uint4 yall[4];
+                        load_chunk_staged(stg_w, p.bwd_y, rowoff, col0 + c * 32, yall, lane);
 #pragma unroll
                         for (int g4 = 0; g4 < 4; ++g4) {
-                            const uint4 yu = valid ? __ldg(ysrc + g4) : make_uint4(0u, 0u, 0u, 0u);
+                            const uint4 yu = yall[g4];
                             const float yy[8] = {bf16lo(yu.x), bf16hi(yu.x), bf16lo(yu.y), bf16hi(yu.y),
                                                  bf16lo(yu.z), bf16hi(yu.z), bf16lo(yu.w), bf16hi(yu.w)};
 #pragma unroll
@@ -299,7 +301,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                         u[g].z = pack_bf16x2(v[g * 8 + 4], v[g * 8 + 5]);
                         u[g].w = pack_bf16x2(v[g * 8 + 6], v[g * 8 + 7]);
                     }
-                    store_chunk_staged(store_stage + (warp - 2) * 2048, p.out, off + c * 32, valid, u, lane);
+                    store_chunk_staged(stg_w, p.out, rowoff, col0 + c * 32, u, lane);
                 }
                 if constexpr (kStats && !kRegStats) {
                     const float s1 = warp_colsum32(v, lane);
