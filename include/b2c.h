@@ -132,10 +132,11 @@ B2C_API int b2c_bn_eval_scale_shift(int channels, const float* gamma, const floa
 
 /* out = act(y*scale + shift + residual'), residual' = res (identity shortcut) or res*res_scale+res_shift
  * (conv shortcut's own BatchNorm). Replaces F.relu(bn(..)), `out += self.shortcut(x)`, F.relu(out),
- * models/resnet.py:47-50. rows = n*h*w; tensors are [rows, channels] bf16. */
+ * models/resnet.py:47-50. rows = n*h*w; tensors are [rows, channels] bf16. relu_bits (optional,
+ * rows*channels/8 bytes): bit e of byte i = [out[8*i + e] > 0], the ReLU mask for b2c_bn_bwd_reduce. */
 B2C_API int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
                      const float* res_scale, const float* res_shift, void* out, long long rows, int channels,
-                     int relu, void* stream);
+                     int relu, unsigned char* relu_bits, void* stream);
 
 /* Number of partial rows b2c_bn_bwd_reduce writes for (rows, channels): size `partial` as
  * rows_returned * 2 * channels floats. Host-only arithmetic. */
@@ -146,9 +147,12 @@ B2C_API int b2c_bn_bwd_partial_rows(long long rows, int channels);
  * Replaces the reductions of cudnn_batch_norm_backward + relu backward, main.py:104.
  * relu_scale/relu_shift (optional, with act == NULL): the unit is a plain F.relu(bn(y)) whose forward scale/shift
  * these are; the mask is then recomputed as fma(y, scale, shift) > 0 and neither act nor dz touch memory
- * (pass the same pair to b2c_bn_bwd_apply, which then takes dout in place of dz). */
+ * (pass the same pair to b2c_bn_bwd_apply, which then takes dout in place of dz).
+ * relu_bits (optional, instead of act and relu_scale/shift): the bit mask b2c_bn_act_apply wrote — an eighth of
+ * a byte per element instead of re-reading the activation. */
 B2C_API int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
-                      int channels, float* partial, const float* relu_scale, const float* relu_shift, void* stream);
+                      int channels, float* partial, const float* relu_scale, const float* relu_shift,
+                      const unsigned char* relu_bits, void* stream);
 
 /* Combine partial rows: dgamma, dbeta (fp32, written) and the coefficients of dy = A*dz + B*y + C. */
 B2C_API int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, float count, const float* gamma,

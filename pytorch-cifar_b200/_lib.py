@@ -68,9 +68,9 @@ SIGNATURES = {
     "b2c_dwconv_wgrad": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
     "b2c_bn_finalize": [_P, _P, _I, _I, _F, _P, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P],
     "b2c_bn_eval_scale_shift": [_I, _P, _P, _P, _P, _P, _F, _P, _P, _P],
-    "b2c_bn_act_apply": [_P, _P, _P, _P, _P, _P, _P, _LL, _I, _I, _P],
+    "b2c_bn_act_apply": [_P, _P, _P, _P, _P, _P, _P, _LL, _I, _I, _P, _P],
     "b2c_bn_bwd_partial_rows": [_LL, _I],
-    "b2c_bn_bwd_reduce": [_P, _P, _P, _P, _LL, _I, _P, _P, _P, _P],
+    "b2c_bn_bwd_reduce": [_P, _P, _P, _P, _LL, _I, _P, _P, _P, _P, _P],
     "b2c_bn_bwd_finalize": [_P, _I, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_bn_bwd_apply": [_P, _P, _P, _P, _P, _P, _P, _LL, _I, _P, _P, _P],
     "b2c_maxpool2x2_fwd": [_P, _P, _I, _I, _I, _I, _P],

@@ -585,7 +585,7 @@ int b2c_bn_eval_scale_shift(int channels, const float* gamma, const float* beta,
 
 int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
                      const float* res_scale, const float* res_shift, void* out, long long rows, int channels,
-                     int relu, void* stream) {
+                     int relu, unsigned char* relu_bits, void* stream) {
     if (!y || !scale || !shift || !out || rows < 0 || channels < 8 || (channels & 7)) return B2C_ERR_ARG;
     if (!aligned16(y) || !aligned16(out) || !aligned16(res) || !aligned16(scale) || !aligned16(shift) ||
         !aligned16(res_scale) || !aligned16(res_shift))
@@ -594,7 +594,7 @@ int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, cons
     if (res_scale != nullptr && res == nullptr) return B2C_ERR_ARG;
     if (rows == 0) return 0;
     return cuda_rc(b2c::launch_bn_act_apply(y, scale, shift, res, res_scale, res_shift, out, rows, channels, relu,
-                                            as_stream(stream)));
+                                            relu_bits, as_stream(stream)));
 }
 
 int b2c_bn_bwd_partial_rows(long long rows, int channels) {
@@ -603,14 +603,16 @@ int b2c_bn_bwd_partial_rows(long long rows, int channels) {
 }
 
 int b2c_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
-                      int channels, float* partial, const float* relu_scale, const float* relu_shift, void* stream) {
+                      int channels, float* partial, const float* relu_scale, const float* relu_shift,
+                      const unsigned char* relu_bits, void* stream) {
     if (!dout || !y || !partial || rows < 1) return B2C_ERR_ARG;
+    if (relu_bits != nullptr && (act != nullptr || relu_scale != nullptr)) return B2C_ERR_ARG;
     if ((relu_scale == nullptr) != (relu_shift == nullptr) || (relu_scale != nullptr && act != nullptr))
         return B2C_ERR_ARG;
     if (channels < 8 || (channels & 7) || (channels >> 3) > 256) return B2C_ERR_UNSUPPORTED;
     if (!aligned16(dout) || !aligned16(act) || !aligned16(y) || !aligned16(dz_out)) return B2C_ERR_ARG;
     return cuda_rc(b2c::launch_bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, relu_scale, relu_shift,
-                                             as_stream(stream)));
+                                             relu_bits, as_stream(stream)));
 }
 
 int b2c_bn_bwd_finalize(const float* partial, int partial_rows, int channels, float count, const float* gamma,

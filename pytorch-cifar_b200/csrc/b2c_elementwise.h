@@ -25,11 +25,12 @@ cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* b
                                        const float* rv, float eps, float* scale, float* shift, cudaStream_t s);
 cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
                                 const float* res_scale, const float* res_shift, void* out, long long rows, int C,
-                                int relu, cudaStream_t s);
+                                int relu, uint8_t* relu_bits,
+                                cudaStream_t s);
 int bn_bwd_partial_rows(long long rows, int C);
 cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
                                  int C, float* partial, const float* relu_scale, const float* relu_shift,
-                                 cudaStream_t s);
+                                 const uint8_t* relu_bits, cudaStream_t s);
 cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float count, const float* gamma,
                                    const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
                                    float* coefB, float* coefC, cudaStream_t s);

@@ -150,7 +150,8 @@ template <bool kUniform, bool kResAffine>
 __global__ void __launch_bounds__(256)
 bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale, const float* __restrict__ shift,
                     const uint4* __restrict__ res, const float* __restrict__ res_scale,
-                    const float* __restrict__ res_shift, uint4* __restrict__ out, long long nvec, int C, int relu) {
+                    const float* __restrict__ res_shift, uint4* __restrict__ out, long long nvec, int C, int relu,
+                    uint8_t* __restrict__ relu_bits) {
     // kUniform: the grid stride is a multiple of C/8, so a thread sees the same 8 channels in every iteration and
     // keeps their scale / shift in registers (no 64-bit modulo, no per-element parameter loads in the loop); two
     // grid strides are then in flight per iteration (all loads issued before the first use).
@@ -194,6 +195,12 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
             for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
         }
         out[v] = pack8(f);
+        if (relu_bits != nullptr) {      // one byte per 8 channels: bit e = [out[e] > 0], for the backward pass
+            unsigned bits = 0;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) bits |= (f[e] > 0.f ? 1u : 0u) << e;
+            relu_bits[v] = static_cast<uint8_t>(bits);
+        }
     };
     const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
     if (kUniform) {
@@ -223,11 +230,13 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
 // branch read dz directly). Each block writes one partial row [2][C]; bn_bwd_finalize combines them.
 // Thread layout: blockDim = 256; thread t owns channel vector (t % cvec) and walks rows.
 // ------------------------------------------------------------------------------------------------
-template <bool kMaskY>
+// kMask: 0 = mask from `act` (or none), 1 = recomputed from y, 2 = from the forward pass's bit mask
+template <int kMask>
 __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ act, const uint4* __restrict__ y,
                      uint4* __restrict__ dz_out, long long rows, int C, float* __restrict__ partial,
-                     const float* __restrict__ relu_scale, const float* __restrict__ relu_shift) {
+                     const float* __restrict__ relu_scale, const float* __restrict__ relu_shift,
+                     const uint8_t* __restrict__ relu_bits) {
     extern __shared__ float red[];  // [rows_per_iter][2][C]
     const int cvec = C >> 3;
     const int rpi = 256 / cvec;     // rows handled per block iteration (cvec <= 256); threads past rpi*cvec idle
@@ -245,8 +254,14 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ a
         float d[8], yy[8];
         unpack8(ld_stream(dout + v), d);
         unpack8(ld_stream(y + v), yy);
-        if (kMaskY) mask_from_y8(d, yy, relu_scale + cv * 8, relu_shift + cv * 8);
-        if (!kMaskY && act != nullptr) {
+        if (kMask == 1) mask_from_y8(d, yy, relu_scale + cv * 8, relu_shift + cv * 8);
+        if (kMask == 2) {
+            const unsigned bits = relu_bits[v];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) d[e] = (bits >> e) & 1u ? d[e] : 0.f;
+            if (dz_out != nullptr) dz_out[v] = pack8(d);
+        }
+        if (kMask == 0 && act != nullptr) {
             float a[8];
             unpack8(ld_stream(act + v), a);
 #pragma unroll
@@ -780,14 +795,14 @@ cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* b
 
 cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
                                 const float* res_scale, const float* res_shift, void* out, long long rows, int C,
-                                int relu, cudaStream_t s) {
+                                int relu, uint8_t* relu_bits, cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
     const int grid = grid_for(nvec, 256, 148 * 8);
     const bool uniform = (static_cast<long long>(grid) * 256) % (C >> 3) == 0;
     const bool affine = res != nullptr && res_scale != nullptr;
     auto go = [&](auto kern) {
         kern<<<grid, 256, 0, s>>>(static_cast<const uint4*>(y), scale, shift, static_cast<const uint4*>(res), res_scale,
-                                  res_shift, static_cast<uint4*>(out), nvec, C, relu);
+                                  res_shift, static_cast<uint4*>(out), nvec, C, relu, relu_bits);
     };
     if (uniform && affine) go(bn_act_apply_kernel<true, true>);
     else if (uniform) go(bn_act_apply_kernel<true, false>);
@@ -806,21 +821,25 @@ int bn_bwd_partial_rows(long long rows, int C) {
 
 cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
                                  int C, float* partial, const float* relu_scale, const float* relu_shift,
-                                 cudaStream_t s) {
+                                 const uint8_t* relu_bits, cudaStream_t s) {
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     const int rpi = 256 / cvec;
     const int blocks = bn_bwd_partial_rows(rows, C);
     const size_t smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
-    if (act == nullptr && relu_scale != nullptr)
-        bn_bwd_reduce_kernel<true><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), nullptr,
-                                                            static_cast<const uint4*>(y), nullptr, rows, C, partial,
-                                                            relu_scale, relu_shift);
+    if (relu_bits != nullptr)
+        bn_bwd_reduce_kernel<2><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), nullptr,
+                                                         static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
+                                                         rows, C, partial, nullptr, nullptr, relu_bits);
+    else if (act == nullptr && relu_scale != nullptr)
+        bn_bwd_reduce_kernel<1><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), nullptr,
+                                                         static_cast<const uint4*>(y), nullptr, rows, C, partial,
+                                                         relu_scale, relu_shift, nullptr);
     else
-        bn_bwd_reduce_kernel<false><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout),
-                                                             static_cast<const uint4*>(act),
-                                                             static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
-                                                             rows, C, partial, nullptr, nullptr);
+        bn_bwd_reduce_kernel<0><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout),
+                                                         static_cast<const uint4*>(act),
+                                                         static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
+                                                         rows, C, partial, nullptr, nullptr, nullptr);
     return cudaGetLastError();
 }
 
@@ -989,7 +1008,7 @@ cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const
     cudaError_t e = noalloc_scratch(&scratch);
     if (e != cudaSuccess) return e;
     const int prow = bn_bwd_partial_rows(rows, C);               // <= kNoAllocMaxRows by construction
-    e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, nullptr, nullptr, s);
+    e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, nullptr, nullptr, nullptr, s);
     if (e != cudaSuccess) return e;
     return launch_bn_bwd_finalize(scratch, prow, C, count, gamma, mean, rstd, dgamma, dbeta, coefA, coefB, coefC, s);
 }

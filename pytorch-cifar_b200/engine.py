@@ -284,6 +284,8 @@ def _bottleneck_spec(num_blocks, planes, num_classes):
 
 # measurement switch (A/B runs on one box): 0 = separate dgrad and bn_bwd_reduce launches
 FUSE_DGRAD_BN = os.environ.get("B2C_FUSE_DGRAD_BN", "1") != "0"
+# 0 = residual units take their ReLU mask from the activation instead of the forward pass's bit mask
+RELU_BITS = os.environ.get("B2C_RELU_BITS", "1") != "0"
 
 
 class ConvUnit:
@@ -334,13 +336,15 @@ class ConvUnit:
                                     self.shift, conv_bias=getattr(self, "conv_bias", None))
 
     # ---- backward pieces
-    def bn_backward(self, eng, dout, act, dz_out, dy, add=None, relu_from_y=False):
+    def bn_backward(self, eng, dout, act, dz_out, dy, add=None, relu_from_y=False, relu_bits=None):
         """dout: grad w.r.t. act(bn(y)) (or w.r.t. bn(y) when act is None). Writes dz (optional) and
         dy = dBN/dy (+ add). relu_from_y: the unit is a plain relu(bn(y)) and nothing else needs dz: the mask is
         recomputed from y with this BN's own scale/shift, so neither `act` is read nor dz written."""
         prow = ops.bn_bwd_partial_rows(self.rows, self.cout)
         if relu_from_y:
             ops.bn_bwd_reduce(dout, None, self.y, None, self.rows, self.cout, eng.bwd_partial, self.scale, self.shift)
+        elif relu_bits is not None:        # mask saved by the forward apply pass: `act` is not read
+            ops.bn_bwd_reduce(dout, None, self.y, dz_out, self.rows, self.cout, eng.bwd_partial, relu_bits=relu_bits)
         else:
             ops.bn_bwd_reduce(dout, act, self.y, dz_out, self.rows, self.cout, eng.bwd_partial)
         ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
@@ -604,10 +608,11 @@ class Engine:
             if b["shortcut"]:
                 cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W)
             out = self.new_act(N, Ho, Wo, cout)
+            bits = torch.zeros(out.numel() // 8, dtype=torch.uint8, device=self.device) if RELU_BITS else None
             self.units += [c1, c2] + ([cs] if cs else [])
-            blocks.append((c1, a1, c2, cs, out, x))
+            blocks.append((c1, a1, c2, cs, out, x, bits))
 
-            def fwd_block(training, c1=c1, a1=a1, c2=c2, cs=cs, out=out, x=x):
+            def fwd_block(training, c1=c1, a1=a1, c2=c2, cs=cs, out=out, x=x, bits=bits):
                 c1.fprop(self)
                 c1.bn_stats(self, training)
                 ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
@@ -617,10 +622,10 @@ class Engine:
                 c2.fprop(self)
                 c2.bn_stats(self, training)
                 if cs is not None:
-                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, res=cs.y,
+                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, relu_bits=bits, res=cs.y,
                                      res_scale=cs.scale, res_shift=cs.shift)
                 else:
-                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, res=x)
+                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, relu_bits=bits, res=x)
             F.append(fwd_block)
             x, H, W = out, Ho, Wo
 
@@ -648,7 +653,7 @@ class Engine:
         dout = dout_last
         self.stem_unit, self.a0 = stem, a0
         self.block_bufs = []      # backward order: tensors of each block, for tests / introspection
-        for (c1, a1, c2, cs, out, xin) in reversed(blocks):
+        for (c1, a1, c2, cs, out, xin, bits) in reversed(blocks):
             dy2 = self.new_act(*c2.y.shape)
             da1 = self.new_act(*a1.shape)
             dy1 = self.new_act(*c1.y.shape)
@@ -656,9 +661,9 @@ class Engine:
             dx = self.new_act(*xin.shape)
 
             def bwd_block(c1=c1, a1=a1, c2=c2, cs=cs, out=out, dout=dout, dy2=dy2, da1=da1, dy1=dy1, dys=dys,
-                          dx=dx):
+                          dx=dx, bits=bits):
                 # out = relu(bn2(y2) + shortcut): mask in place -> dz, then BN2 backward
-                c2.bn_backward(self, dout, out, dout, dy2)
+                c2.bn_backward(self, dout, out, dout, dy2, relu_bits=bits)
                 if cs is not None:
                     cs.bn_backward(self, dout, None, None, dys)
                 c2.wgrad(dy2)
@@ -676,7 +681,7 @@ class Engine:
                 else:
                     c1.dgrad(dy1, dx, add_src=dout)       # identity shortcut: + dz
             Bk.append(bwd_block)
-            self.block_bufs.append(dict(c1=c1, a1=a1, c2=c2, cs=cs, out=out, xin=xin, dout=dout, dx=dx))
+            self.block_bufs.append(dict(c1=c1, a1=a1, c2=c2, cs=cs, out=out, xin=xin, dout=dout, dx=dx, bits=bits))
             dout = dx
 
         dy0 = self.new_act(*stem.y.shape)
@@ -880,10 +885,11 @@ class Engine:
             cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W) \
                 if b["shortcut"] else None
             out = self.new_act(N, Ho, Wo, cout)
+            bits = torch.zeros(out.numel() // 8, dtype=torch.uint8, device=self.device) if RELU_BITS else None
             self.units += [c1, c2, c3] + ([cs] if cs else [])
-            blocks.append((c1, a1, c2, a2, c3, cs, out, x))
+            blocks.append((c1, a1, c2, a2, c3, cs, out, x, bits))
 
-            def fwd(training, c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, x=x):
+            def fwd(training, c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, x=x, bits=bits):
                 c1.fprop(self)
                 c1.bn_stats(self, training)
                 ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
@@ -896,15 +902,16 @@ class Engine:
                     cs.fprop(self)
                     cs.bn_stats(self, training)
                     ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=cs.y,
-                                     res_scale=cs.scale, res_shift=cs.shift)
+                                     res_scale=cs.scale, res_shift=cs.shift, relu_bits=bits)
                 else:
-                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=x)
+                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=x,
+                                     relu_bits=bits)
             F.append(fwd)
             x, H, W = out, Ho, Wo
         fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
         F.append(fwd_head)
         Bk = [bwd_head]
-        for (c1, a1, c2, a2, c3, cs, out, xin) in reversed(blocks):
+        for (c1, a1, c2, a2, c3, cs, out, xin, bits) in reversed(blocks):
             dy3 = self.new_act(*c3.y.shape)
             dys = self.new_act(*cs.y.shape) if cs is not None else None
             da2 = self.new_act(*a2.shape)
@@ -914,8 +921,8 @@ class Engine:
             dx = self.new_act(*xin.shape)
 
             def bwd(c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, dout=dout, dy3=dy3, dys=dys, da2=da2,
-                    dy2=dy2, da1=da1, dy1=dy1, dx=dx):
-                c3.bn_backward(self, dout, out, dout, dy3)            # mask in place -> dz
+                    dy2=dy2, da1=da1, dy1=dy1, dx=dx, bits=bits):
+                c3.bn_backward(self, dout, out, dout, dy3, relu_bits=bits)      # mask in place -> dz
                 if cs is not None:
                     cs.bn_backward(self, dout, None, None, dys)
                 c3.wgrad(dy3)

@@ -138,10 +138,13 @@ def bn_eval_scale_shift(channels, gamma, beta, running_mean, running_var, eps, s
                                       _p(scale), _p(shift), _stream()), "b2c_bn_eval_scale_shift")
 
 
-def bn_act_apply(y, scale, shift, out, rows, channels, relu=True, res=None, res_scale=None, res_shift=None):
+def bn_act_apply(y, scale, shift, out, rows, channels, relu=True, res=None, res_scale=None, res_shift=None,
+                 relu_bits=None):
+    """relu_bits: optional uint8 [rows*channels/8] receiving the ReLU mask (one bit per element)."""
     lib = _lib.load()
+    _need(relu_bits, torch.uint8, "relu_bits")
     check(lib.b2c_bn_act_apply(_p(y), _p(scale), _p(shift), _p(res), _p(res_scale), _p(res_shift), _p(out),
-                               rows, channels, 1 if relu else 0, _stream()), "b2c_bn_act_apply")
+                               rows, channels, 1 if relu else 0, _p(relu_bits), _stream()), "b2c_bn_act_apply")
 
 
 def bn_bwd_partial_rows(rows, channels):
@@ -152,10 +155,11 @@ def bn_bwd_partial_rows(rows, channels):
     return r
 
 
-def bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, relu_scale=None, relu_shift=None):
+def bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, relu_scale=None, relu_shift=None, relu_bits=None):
     lib = _lib.load()
+    _need(relu_bits, torch.uint8, "relu_bits")
     check(lib.b2c_bn_bwd_reduce(_p(dout), _p(act), _p(y), _p(dz_out), rows, channels, _p(partial), _p(relu_scale),
-                                _p(relu_shift), _stream()), "b2c_bn_bwd_reduce")
+                                _p(relu_shift), _p(relu_bits), _stream()), "b2c_bn_bwd_reduce")
 
 
 def bn_bwd_finalize(partial, partial_rows, channels, count, gamma, save_mean, save_rstd, dgamma, dbeta, ca, cb, cc):

@@ -419,6 +419,18 @@ def test_bn_relu_backward(ops, C, rows):
     for a, b in zip(ref, new):
         assert torch.equal(a, b)
     assert torch.equal(dy_ref, dy_new)
+    # mask taken from the bit mask the forward apply pass writes (residual units): same sums, same dz
+    bits = torch.zeros(rows * C // 8, dtype=torch.uint8, device="cuda")
+    res = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+    ops.bn_act_apply(y, scale, shift, act_k, rows, C, relu=True, res=res, relu_bits=bits)
+    w8 = (1 << torch.arange(8, device="cuda")).to(torch.int32)
+    assert torch.equal(bits, ((act_k.view(-1, 8) > 0).to(torch.int32) * w8).sum(1).to(torch.uint8))
+    dz_a, dz_b = torch.empty_like(dout), torch.empty_like(dout)
+    pa, pb = torch.empty_like(partial), torch.empty_like(partial)
+    ops.bn_bwd_reduce(dout, act_k, y, dz_a, rows, C, pa)
+    ops.bn_bwd_reduce(dout, None, y, dz_b, rows, C, pb, relu_bits=bits)
+    torch.cuda.synchronize()
+    assert torch.equal(dz_a, dz_b) and torch.equal(pa, pb)
 
 
 def test_head_and_loss(ops):

@@ -116,6 +116,9 @@ def test_backward_teacher_forced_per_block(setup):
     force_unit(eng.stem_unit, trace["stem"]); eng.a0.copy_(_nhwc(trace["a0"]))
     for bb, (c1, a1, c2, cs, out) in zip(reversed(eng.block_bufs), trace["blocks"]):
         force_unit(bb["c1"], c1); bb["a1"].copy_(_nhwc(a1)); force_unit(bb["c2"], c2); bb["out"].copy_(_nhwc(out))
+        # the ReLU bit mask the forward apply pass would have written next to `out` (bit e of byte i = out[8i+e] > 0)
+        w8 = (1 << torch.arange(8, device="cuda")).to(torch.int32)
+        bb["bits"].copy_(((bb["out"].view(-1, 8) > 0).to(torch.int32) * w8).sum(1).to(torch.uint8))
         if cs is not None:
             force_unit(bb["cs"], cs)
     eng.pooled.copy_(trace["pooled"]); eng.dlogits.copy_(trace["dlogits"])
