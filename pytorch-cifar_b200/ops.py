@@ -3,6 +3,7 @@ streams: every wrapper extracts raw pointers, passes the current CUDA stream and
 return code. Activations are NHWC bf16 tensors; there is no fallback implementation here.
 """
 import ctypes
+import os
 
 import torch
 
@@ -123,12 +124,17 @@ def dwconv_wgrad(x, dy, dweight, c_valid, stride):
     check(lib.b2c_dwconv_wgrad(_p(x), _p(dy), _p(dweight), n, h, w, c, c_valid, stride, _stream()), "b2c_dwconv_wgrad")
 
 
+# measurement aid: >1 issues each finalize kernel that many times (their in-graph cost = the step-time difference)
+_FINALIZE_REPEAT = int(os.environ.get("B2C_EXPERIMENT_FINALIZE_REPEAT", "1"))
+
+
 def bn_finalize(part_sum, part_sq, rows, channels, count, gamma, beta, eps, momentum, running_mean, running_var,
                 scale, shift, save_mean, save_rstd, conv_bias=None):
     lib = _lib.load()
-    check(lib.b2c_bn_finalize(_p(part_sum), _p(part_sq), rows, channels, float(count), _p(gamma), _p(beta),
-                              _p(conv_bias), float(eps), float(momentum), _p(running_mean), _p(running_var), _p(scale), _p(shift),
-                              _p(save_mean), _p(save_rstd), _stream()), "b2c_bn_finalize")
+    for _ in range(_FINALIZE_REPEAT):
+        check(lib.b2c_bn_finalize(_p(part_sum), _p(part_sq), rows, channels, float(count), _p(gamma), _p(beta),
+                                  _p(conv_bias), float(eps), float(momentum), _p(running_mean), _p(running_var),
+                                  _p(scale), _p(shift), _p(save_mean), _p(save_rstd), _stream()), "b2c_bn_finalize")
 
 
 def bn_eval_scale_shift(channels, gamma, beta, running_mean, running_var, eps, scale, shift, conv_bias=None):
@@ -164,9 +170,10 @@ def bn_bwd_reduce(dout, act, y, dz_out, rows, channels, partial, relu_scale=None
 
 def bn_bwd_finalize(partial, partial_rows, channels, count, gamma, save_mean, save_rstd, dgamma, dbeta, ca, cb, cc):
     lib = _lib.load()
-    check(lib.b2c_bn_bwd_finalize(_p(partial), partial_rows, channels, float(count), _p(gamma), _p(save_mean),
-                                  _p(save_rstd), _p(dgamma), _p(dbeta), _p(ca), _p(cb), _p(cc), _stream()),
-          "b2c_bn_bwd_finalize")
+    for _ in range(_FINALIZE_REPEAT):
+        check(lib.b2c_bn_bwd_finalize(_p(partial), partial_rows, channels, float(count), _p(gamma), _p(save_mean),
+                                      _p(save_rstd), _p(dgamma), _p(dbeta), _p(ca), _p(cb), _p(cc), _stream()),
+              "b2c_bn_bwd_finalize")
 
 
 NOALLOC_MAX_CHANNELS = 512
