@@ -260,14 +260,24 @@ def run_product(args):
         dist.all_gather(allchk, chk)
         in_sync = bool(all(torch.equal(allchk[0], c) for c in allchk))
 
-    # ---------------- roofline of the dominant kernel family (tap GEMM = conv fprop + dgrad), timed live with
-    # CUDA events on the launching stream: every fprop/dgrad launch of one step, back to back, same buffers.
+    # ---------------- roofline of the dominant kernel (conv_halo_kernel: every 3x3 stride-1 fprop / dgrad), timed
+    # live with CUDA events on the launching stream: all its launches of one step, back to back, same buffers.
+    # The other two conv kernel families (per-tap GEMM, wgrad) are timed the same way and reported beside it.
     peaks = load_peaks()
     raw = _lib.load()
-    tap_calls = [(n, a) for n, a in calls
-                 if n in ("b2c_conv_fprop", "b2c_conv_dgrad", "b2c_conv_dgrad_with_shortcut", "b2c_conv_dgrad_bn")]
+
+    def is_halo(n, a):        # api.cu use_halo(): 3x3 stride-1 convs on 32/16/8-pixel images -> conv_halo_kernel
+        d = a[0]._obj
+        return n in ("b2c_conv_fprop", "b2c_conv_dgrad", "b2c_conv_dgrad_bn") and d.ksize == 3 and d.stride == 1 \
+            and d.h == d.w and d.w in (32, 16, 8) and not (d.flags & 1)
+
+    fd = ("b2c_conv_fprop", "b2c_conv_dgrad", "b2c_conv_dgrad_with_shortcut", "b2c_conv_dgrad_bn")
+    halo_calls = [(n, a) for n, a in calls if n in fd and is_halo(n, a)]
+    tap_calls = [(n, a) for n, a in calls if n in fd and not is_halo(n, a)]
     wg_calls = [(n, a) for n, a in calls if n == "b2c_conv_wgrad"]
-    tap_fl, wg_fl = conv_flops(calls)
+    halo_fl, _ = conv_flops(halo_calls)
+    tap_fl, _ = conv_flops(tap_calls)
+    _, wg_fl = conv_flops(wg_calls)
 
     def time_family(fam, reps=5):
         for n, a in fam:
@@ -282,18 +292,31 @@ def run_product(args):
         torch.cuda.synchronize()
         return a0.elapsed_time(a1) / reps
 
+    halo_ms = time_family(halo_calls)
     tap_ms = time_family(tap_calls)
     wg_ms = time_family(wg_calls)
-    tap_launches = count_launches(tap_calls)
-    achieved = tap_fl / (tap_ms * 1e-3) / 1e12
-    roofline = {"bound": "tensor", "kernel": "tap_gemm_kernel (conv fprop + dgrad)", "achieved": achieved,
-                "peak": peaks["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / peaks["tf_sustained"],
-                "traffic": None, "peak_source": peaks["source"] + " bf16_tflops_sustained",
-                "launches_per_step": tap_launches, "avg_launch_us": tap_ms * 1e3 / tap_launches,
-                "flop_per_launch_avg": tap_fl / tap_launches,
+    halo_launches = count_launches(halo_calls)
+    achieved = halo_fl / (halo_ms * 1e-3) / 1e12
+    traffic = None          # DRAM bytes per launch of the same kernel from the committed ncu --set full capture
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles",
+                               "r1d_ncu_conv_halo_step.json")) as f:
+            traffic = json.load(f)["avg_dram_bytes_per_launch"]
+    except Exception:
+        pass
+    tf = peaks["tf_sustained"]
+    roofline = {"bound": "tensor", "kernel": "conv_halo_kernel (3x3 stride-1 conv fprop + dgrad, halo reuse)",
+                "achieved": achieved, "peak": tf, "unit": "TFLOP/s", "frac": achieved / tf,
+                "traffic": traffic, "traffic_source": "profiles/r1d_ncu_conv_halo_step.json (dram read+write, avg per launch)",
+                "peak_source": peaks["source"] + " bf16_tflops_sustained",
+                "launches_per_step": halo_launches, "avg_launch_us": halo_ms * 1e3 / halo_launches,
+                "flop_per_launch_avg": halo_fl / halo_launches, "ms_per_step": halo_ms,
+                "tap_gemm": {"achieved": tap_fl / (tap_ms * 1e-3) / 1e12, "ms_per_step": tap_ms,
+                             "frac": tap_fl / (tap_ms * 1e-3) / 1e12 / tf,
+                             "launches_per_step": count_launches(tap_calls)},
                 "wgrad": {"achieved": wg_fl / (wg_ms * 1e-3) / 1e12, "ms_per_step": wg_ms,
-                          "frac": wg_fl / (wg_ms * 1e-3) / 1e12 / peaks["tf_sustained"]},
-                "conv_ms_per_step": tap_ms + wg_ms}
+                          "frac": wg_fl / (wg_ms * 1e-3) / 1e12 / tf, "launches_per_step": count_launches(wg_calls)},
+                "conv_ms_per_step": halo_ms + tap_ms + wg_ms}
     del tr
     torch.cuda.empty_cache()
 
@@ -306,12 +329,17 @@ def run_product(args):
     for k in range(W):
         tr2.step_host_batch(host_batches[k % len(host_batches)], host_labels[k % len(host_batches)], ijf_all[k % S])
         tr2.read_loss()
+    # timed region: every step = swap-in of the staged batch + the step + staging of the NEXT host batch (pinned copy
+    # and H2D on a copy stream, overlapping the step the way DataLoader workers do, main.py:44-45) + loss D2H
+    j = W % len(host_batches)
+    tr2.prefetch_host_batch(host_batches[j], host_labels[j], ijf_all[W % S])
     barrier()
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     t0.record()
     for k in range(W, W + K):
-        j = k % len(host_batches)
-        tr2.step_host_batch(host_batches[j], host_labels[j], ijf_all[k % S])
+        tr2.step_prefetched()
+        j = (k + 1) % len(host_batches)
+        tr2.prefetch_host_batch(host_batches[j], host_labels[j], ijf_all[(k + 1) % S])
         tr2.read_loss()
     t1.record()
     barrier()

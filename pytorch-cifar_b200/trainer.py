@@ -163,6 +163,52 @@ class Trainer:
         self._run()
         return self.loss
 
+    # ------------------------------------------------------------------ pipelined host input (DataLoader prefetch)
+    def prefetch_host_batch(self, images_u8, labels, ijf):
+        """Stage the NEXT step's host batch while the current step runs on the GPU — what the reference gets from
+        DataLoader(num_workers=2) + `.to(device)` (main.py:44-45,100): host copy into pinned memory, then H2D on a
+        copy stream into staging buffers. `step_prefetched()` swaps them in (device-to-device) and runs the step."""
+        assert not self.resident
+        if not hasattr(self, "_copy_stream"):
+            dev = self.device
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._stg_img = torch.zeros_like(self.data)
+            self._stg_ijf = torch.zeros_like(self.ijf_dev)
+            self._stg_tgt = torch.zeros_like(self.target)
+            self._h2d_done, self._swap_done = torch.cuda.Event(), None
+        s = self._slot
+        self._slot = (s + 1) % self._ring
+        if self._ring_events[s] is not None:
+            self._ring_events[s].synchronize()
+        if self._pin_img is None:
+            self._pin_img = [torch.zeros(self.N, 32, 32, 3, dtype=torch.uint8).pin_memory() for _ in range(self._ring)]
+        self._pin_img[s].numpy()[...] = images_u8
+        self._pin_ijf[s].numpy()[...] = ijf
+        self._pin_tgt[s].numpy()[...] = labels
+        cs = self._copy_stream
+        if self._swap_done is not None:
+            cs.wait_event(self._swap_done)            # the previous swap has read the staging buffers
+        with torch.cuda.stream(cs):
+            self._stg_img.copy_(self._pin_img[s], non_blocking=True)
+            self._stg_ijf.copy_(self._pin_ijf[s], non_blocking=True)
+            self._stg_tgt.copy_(self._pin_tgt[s], non_blocking=True)
+            self._h2d_done.record(cs)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        self._ring_events[s] = ev
+
+    def step_prefetched(self):
+        """One training step on the batch staged by the last prefetch_host_batch()."""
+        main = torch.cuda.current_stream()
+        main.wait_event(self._h2d_done)
+        self.data.copy_(self._stg_img, non_blocking=True)
+        self.ijf_dev.copy_(self._stg_ijf, non_blocking=True)
+        self.target.copy_(self._stg_tgt, non_blocking=True)
+        self._swap_done = torch.cuda.Event()
+        self._swap_done.record(main)
+        self._run()
+        return self.loss
+
     # ------------------------------------------------------------------ evaluation (test(), main.py:116-134)
     def evaluate(self, images_u8, labels, batch=100):
         """Top-1 accuracy and mean loss over a host uint8 set with transform_test (ToTensor + Normalize only,

@@ -267,3 +267,44 @@ def test_model_trains(ops, model):
     assert abs(losses[0] - ref[0]) < 3e-2
     assert losses[-1] < BOUNDS[model]["drop"] * losses[0] and abs(losses[-1] - ref[-1]) < 0.35 * ref[0]
     assert max(abs(a - b) for a, b in zip(losses[:4], ref[:4])) < 0.05 * ref[0]      # same early trajectory
+
+
+def test_prefetched_host_batches_match_resident_dataset(ops):
+    """The three input paths of the Trainer — dataset resident in HBM (step), host batch copied inside the call
+    (step_host_batch) and host batch staged one step ahead on a copy stream (prefetch_host_batch +
+    step_prefetched) — see the same samples, crops and labels: identical first-step loss, same trajectory."""
+    from b200cifar import data, engine, trainer
+    from oracle import nets
+    N, steps = 128, 4
+    params, buffers = nets.build_resnet_params(0)
+    bufs = {k: v for k, v in buffers.items() if not k.endswith("num_batches_tracked")}
+    images, labels = data.learnable_cifar(1024, seed=5)
+    rng = data.TorchCpuMT19937(11)
+    perm = data.randperm(rng, 1024)
+    idx = [perm[k * N:(k + 1) * N] for k in range(steps)]
+    ijf = [data.draw_crop_flip(rng, N).reshape(N, 3) for _ in range(steps)]
+    out = {}
+    for mode in ("resident", "host", "prefetch"):
+        tr = trainer.Trainer(engine.resnet_spec(), N, lr=0.02, resident_dataset=(mode == "resident"))
+        tr.load_params(params, bufs)
+        losses = []
+        if mode == "resident":
+            tr.set_dataset(images, labels)
+            for k in range(steps):
+                tr.step(idx[k], ijf[k]); losses.append(tr.read_loss())
+        elif mode == "host":
+            for k in range(steps):
+                tr.step_host_batch(images[idx[k]], labels[idx[k]], ijf[k]); losses.append(tr.read_loss())
+        else:
+            tr.prefetch_host_batch(images[idx[0]], labels[idx[0]], ijf[0])
+            for k in range(steps):
+                tr.step_prefetched()
+                if k + 1 < steps:
+                    tr.prefetch_host_batch(images[idx[k + 1]], labels[idx[k + 1]], ijf[k + 1])
+                losses.append(tr.read_loss())
+        out[mode] = losses
+        del tr
+    assert out["resident"][0] == out["host"][0] == out["prefetch"][0]
+    for k in range(steps):     # later steps differ only by the summation order of the fp32 wgrad atomics
+        assert abs(out["host"][k] - out["resident"][k]) < 2e-2 * out["resident"][0]
+        assert abs(out["prefetch"][k] - out["resident"][k]) < 2e-2 * out["resident"][0]
