@@ -214,7 +214,8 @@ def run_product(args):
         return t.item()
 
     # ---------------- device-resident arm: `value`
-    tr = trainer.Trainer(engine.resnet_spec(), per_gpu, dev, world=world, rank=rank, use_graph=not args.no_graph)
+    tr = trainer.Trainer(engine.resnet_spec(), per_gpu, dev, world=world, rank=rank, use_graph=not args.no_graph,
+                         bucket_bytes=int(args.bucket_mb * 2 ** 20))
     tr.load_params(params, bufs)
     if world > 1:
         dist.broadcast(tr.eng.P, 0)
@@ -322,6 +323,7 @@ def run_product(args):
 
     # ---------------- end-to-end arm: host uint8 batches through the public API, H2D + loss D2H every step
     tr2 = trainer.Trainer(engine.resnet_spec(), per_gpu, dev, world=world, rank=rank, use_graph=not args.no_graph,
+                          bucket_bytes=int(args.bucket_mb * 2 ** 20),
                           resident_dataset=False)
     tr2.load_params(params, bufs)
     host_batches = [np.ascontiguousarray(images[idx_all[k]]) for k in range(min(S, 8))]
@@ -384,6 +386,7 @@ def main():
     ap.add_argument("--batch", type=int, default=1024, help="per-GPU batch (weak) or global batch (strong)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--bucket-mb", type=float, default=25.0, help="gradient all-reduce bucket size (MiB), N > 1")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
