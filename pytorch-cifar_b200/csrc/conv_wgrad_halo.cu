@@ -152,22 +152,42 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constan
     if (warp == 1) tmem_dealloc<kTmemCols>(tmem_base);
 }
 
-// dw[cout, cin, tap] += sum over splits of the partial tiles. One thread per (tap, cin, cout) element;
-// consecutive threads walk cout (the contiguous axis of the partial tiles).
+// dw[cout, cin, tap] += sum over splits of the partial tiles. Block = 64 consecutive (tap, cin, cout) elements
+// (cout fastest = the contiguous axis of the partial tiles) x 4 split lanes; every lane sums its quarter of the
+// splits with eight loads in flight, the four partial sums meet in shared memory in a fixed order (deterministic).
 __global__ void __launch_bounds__(256)
 wgrad_halo_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int cin, int cout, int cout_slabs,
                          int splits) {
+    __shared__ float red[4][64];
+    const int x = threadIdx.x & 63, y = threadIdx.x >> 6;
     const long long total = 9LL * cin * cout;
-    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
-        const int o = static_cast<int>(i % cout);
-        const int c = static_cast<int>((i / cout) % cin);
-        const int t = static_cast<int>(i / (static_cast<long long>(cout) * cin));
-        const int unit = (c >> 6) * cout_slabs + (o >> 6);
-        const int mb = t >> 1, row = (t & 1) * 64 + (c & 63), col = o & 63;
-        const float* src = partial + ((static_cast<size_t>(unit) * splits * 5 + mb) * 128 + row) * 64 + col;
+    const size_t split_stride = static_cast<size_t>(5) * 128 * 64;
+    for (long long base = blockIdx.x * 64LL; base < total; base += static_cast<long long>(gridDim.x) * 64) {
+        const long long i = base + x;
         float s = 0.f;
-        for (int k = 0; k < splits; ++k) s += src[static_cast<size_t>(k) * 5 * 128 * 64];
-        dw[(static_cast<size_t>(o) * cin + c) * 9 + t] += s;
+        int o = 0, c = 0, t = 0;
+        if (i < total) {
+            o = static_cast<int>(i % cout);
+            c = static_cast<int>((i / cout) % cin);
+            t = static_cast<int>(i / (static_cast<long long>(cout) * cin));
+            const int unit = (c >> 6) * cout_slabs + (o >> 6);
+            const int mb = t >> 1, row = (t & 1) * 64 + (c & 63), col = o & 63;
+            const float* src = partial + ((static_cast<size_t>(unit) * splits * 5 + mb) * 128 + row) * 64 + col;
+            int k = y;
+            float a[8];
+            for (; k + 28 < splits; k += 32) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u) a[u] = src[static_cast<size_t>(k + 4 * u) * split_stride];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) s += a[u];
+            }
+            for (; k < splits; k += 4) s += src[static_cast<size_t>(k) * split_stride];
+        }
+        red[y][x] = s;
+        __syncthreads();
+        if (y == 0 && i < total)
+            dw[(static_cast<size_t>(o) * cin + c) * 9 + t] += (red[0][x] + red[1][x]) + (red[2][x] + red[3][x]);
+        __syncthreads();
     }
 }
 
@@ -190,7 +210,7 @@ cudaError_t launch_wgrad_halo(const CUtensorMap& x, const CUtensorMap& dy, const
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const long long total = 9LL * p.cin_slabs * 64 * p.cout_slabs * 64;
-    int rgrid = static_cast<int>((total + 255) / 256);
+    int rgrid = static_cast<int>((total + 63) / 64);
     if (rgrid > 148 * 8) rgrid = 148 * 8;
     wgrad_halo_reduce_kernel<<<rgrid, 256, 0, stream>>>(p.partial, dw, p.cin_slabs * 64, p.cout_slabs * 64, p.cout_slabs,
                                                         p.splits);

@@ -753,16 +753,32 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
             tile[o][r] = master[e.src_off + (static_cast<long long>(o0 + o) * e.cin + c0) * taps + r];
         }
         __syncthreads();
-        for (int i = threadIdx.x; i < taps * 32 * 32; i += 256) {
-            const int t = i >> 10, a = (i >> 5) & 31, b = i & 31;
+        // two adjacent channels per thread: one 4-byte bf16x2 store per operand layout (channel counts are even)
+        const bool even = !((nc | no | cout_pad | e.cin_pad) & 1) && !((e.wf_off | (e.wd_off < 0 ? 0 : e.wd_off)) & 1);
+        for (int i = threadIdx.x; i < taps * 32 * 16; i += 256) {
+            const int t = i >> 9, a = (i >> 4) & 31, b = (i & 15) * 2;
             // fprop operand [tap][cout_pad][cin_pad]: b runs over cin (contiguous)
-            if (a < no && b < nc)
-                wf[e.wf_off + (static_cast<long long>(t) * cout_pad + o0 + a) * e.cin_pad + c0 + b] =
-                    __float2bfloat16(tile[a][b * taps + t]);
+            if (a < no && b < nc) {
+                __nv_bfloat16* dst = wf + e.wf_off + (static_cast<long long>(t) * cout_pad + o0 + a) * e.cin_pad + c0 + b;
+                if (even) {
+                    *reinterpret_cast<__nv_bfloat162*>(dst) =
+                        __floats2bfloat162_rn(tile[a][b * taps + t], tile[a][(b + 1) * taps + t]);
+                } else {
+                    dst[0] = __float2bfloat16(tile[a][b * taps + t]);
+                    if (b + 1 < nc) dst[1] = __float2bfloat16(tile[a][(b + 1) * taps + t]);
+                }
+            }
             // dgrad operand [tap][cin_pad][cout_pad]: b runs over cout (contiguous)
-            if (e.wd_off >= 0 && a < nc && b < no)
-                wd[e.wd_off + (static_cast<long long>(t) * e.cin_pad + c0 + a) * cout_pad + o0 + b] =
-                    __float2bfloat16(tile[b][a * taps + t]);
+            if (e.wd_off >= 0 && a < nc && b < no) {
+                __nv_bfloat16* dst = wd + e.wd_off + (static_cast<long long>(t) * e.cin_pad + c0 + a) * cout_pad + o0 + b;
+                if (even) {
+                    *reinterpret_cast<__nv_bfloat162*>(dst) =
+                        __floats2bfloat162_rn(tile[b][a * taps + t], tile[b + 1][a * taps + t]);
+                } else {
+                    dst[0] = __float2bfloat16(tile[b][a * taps + t]);
+                    if (b + 1 < no) dst[1] = __float2bfloat16(tile[b + 1][a * taps + t]);
+                }
+            }
         }
     }
 }
