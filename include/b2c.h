@@ -53,7 +53,10 @@ typedef struct B2cConvDesc {
     int flags;       /* bit 0: force the per-tap kernels where a halo-reuse kernel would be chosen;
                         bit 1: wgrad: take the halo-reuse kernel for any qualifying shape, not just 64x64 channels;
                         bit 2: stride 2: address x with a TMA traversal stride instead of the split-W map
-                               (measurement aid: same result, twice the L2->SM operand bytes) */
+                               (measurement aid: same result, twice the L2->SM operand bytes);
+                        bits 3,4: wgrad measurement switches (plain stores / no stores instead of reductions);
+                        bit 5: wgrad: dw is laid out [tap][cin_valid][cout_valid] instead of OIHW, which lets the
+                               epilogue reduce 4 rows x 128 contiguous bytes per instruction */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)
@@ -228,7 +231,8 @@ typedef struct B2cRepackEntry {
     long long wf_off;  /* element offset of the fprop operand [tap][cout][cin_pad] */
     long long wd_off;  /* element offset of the dgrad operand [tap][cin][cout]; <0: none */
     int cout, cin, taps, cin_pad;
-    int kflat;         /* stem: fprop operand is [cout][cin_pad], k = tap*cin + c */
+    int kflat;         /* 0: master OIHW; 1: stem, fprop operand is [cout][cin_pad], k = tap*cin + c;
+                          2: master is [tap][cin][cout] (the layout flags bit 5 of b2c_conv_wgrad writes) */
     int pad_;          /* cout_pad: rows per tap of the fprop operand / row pitch of the dgrad operand; 0 = cout */
 } B2cRepackEntry;
 

@@ -456,6 +456,7 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
             if (rc) return rc;
             rc = encode_nhwc(&mdy, dy, d->n, d->h, d->w, d->cout, 8, 16, 1, 1);
             if (rc) return rc;
+            hp.tco = (d->flags & 32) ? 1 : 0;
             return cuda_rc(b2c::launch_wgrad_halo(mx, mdy, hp, dw, as_stream(stream)));
         }
     }
@@ -505,6 +506,10 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
         p.o_stride = static_cast<long long>(cin_valid);
         p.c_stride = ftaps;
         p.t_stride = 1;
+    } else if (d->flags & 32) {      // dw is [tap][cin_valid][cout_valid] (coalesced vector reductions)
+        p.o_stride = 1;
+        p.c_stride = cout_valid;
+        p.t_stride = static_cast<long long>(cin_valid) * cout_valid;
     } else {
         p.o_stride = static_cast<long long>(cin_valid) * taps;
         p.c_stride = taps;
@@ -514,6 +519,7 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
     const int bh = (kpx / wo) < ho ? (kpx / wo) : ho;
     const int bnb = kpx / (wo * bh);
     CUtensorMap mx, mdy;
+    p.debug = d->flags & 0x18;
     p.x_split_w = d->stride == 2 && !(d->flags & 4);
     rc = p.x_split_w ? encode_nhwc_s2(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb)
                      : encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);

@@ -59,6 +59,7 @@ struct WgradParams {
     int cin_blocks;       // cin / 64
     int gH, gW;           // dY pixel grid
     int in_stride;
+    int debug;            // measurement switches (tools/ only): 8 plain stores instead of atomics, 16 no stores
     int x_split_w;        // X map is 5-D with the W axis split into (parity, w/2): stride-2 convs
     int8_t tap_dh[kMaxTaps];
     int8_t tap_dw[kMaxTaps];
@@ -105,6 +106,7 @@ struct WgradHaloParams {
     int splits, tiles_per_split; // split-K over 16x8-pixel tiles
     int num_tiles, tiles_h, tiles_w;
     float* partial;              // [cin_slabs*cout_slabs][splits][5][128][64] fp32
+    int tco;                     // dW layout: 0 = OIHW, 1 = [tap][cin][cout]
 };
 size_t wgrad_halo_scratch_floats(int cin, int cout, int splits);
 cudaError_t launch_wgrad_halo(const CUtensorMap& x, const CUtensorMap& dy, const WgradHaloParams& p, float* dw,

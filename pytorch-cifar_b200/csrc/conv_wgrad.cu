@@ -40,7 +40,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
     using Cfg = WgCfg<BN, KC>;
     constexpr int kSlabBytes = Cfg::kSlabBytes;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* aux = smem + Cfg::kStages * Cfg::kStageBytes;
     uint64_t* full = reinterpret_cast<uint64_t*>(aux);
     uint64_t* empty = full + Cfg::kStages;
@@ -175,6 +175,42 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
         }
         float* base = p.dw + static_cast<long long>(gc) * p.c_stride + static_cast<long long>(gt) * p.t_stride +
                       static_cast<long long>(n_tile) * BN * p.o_stride;
+        if (p.o_stride == 1 && p.debug == 0 && !(p.cout_valid & 3)) {
+            // dW laid out [tap][cin][cout]: a row of the accumulator tile is contiguous in memory. Each 32x32 fp32
+            // chunk is transposed through a 4 KB per-warp stage (the pipeline's shared memory is idle by now) so that
+            // one red.global.add.v4.f32 covers 4 rows x 128 contiguous bytes: 4 lines per instruction instead of one
+            // scattered 4-byte atomic per lane and element.
+            uint8_t* stg = smem + q * 4096;
+            const long long mine = valid ? (static_cast<long long>(gc) * p.c_stride + static_cast<long long>(gt) * p.t_stride)
+                                         : -1;
+            long long rowoff[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it) rowoff[it] = __shfl_sync(0xffffffffu, mine, it * 4 + (lane >> 3));
+            const int piece = lane & 7;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                float v[32];
+                tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(c * 32), v);
+                __syncwarp();
+                float4* rowp = reinterpret_cast<float4*>(stg + lane * 128);
+                const int sw = lane & 7;
+#pragma unroll
+                for (int g = 0; g < 8; ++g) rowp[g ^ sw] = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+                __syncwarp();
+                const int col = n_tile * BN + c * 32 + piece * 4;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int r = it * 4 + (lane >> 3);
+                    const float4 val = *reinterpret_cast<const float4*>(stg + r * 128 + ((piece ^ (r & 7)) << 4));
+                    if (rowoff[it] >= 0 && col < p.cout_valid) {
+                        float* dst = p.dw + rowoff[it] + col;
+                        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(val.x),
+                                     "f"(val.y), "f"(val.z), "f"(val.w)
+                                     : "memory");
+                    }
+                }
+            }
+        } else {
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
             float v[32];
@@ -182,10 +218,14 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
             if (valid) {
 #pragma unroll
                 for (int e = 0; e < 32; ++e) {
-                    if (n_tile * BN + c * 32 + e < p.cout_valid)
-                        atomicAdd(base + static_cast<long long>(c * 32 + e) * p.o_stride, v[e]);
+                    if (n_tile * BN + c * 32 + e < p.cout_valid) {
+                        float* dst = base + static_cast<long long>(c * 32 + e) * p.o_stride;
+                        if (p.debug == 0) atomicAdd(dst, v[e]);
+                        else if (p.debug & 8) *dst = v[e];          // measurement only: plain store, wrong sums
+                    }
                 }
             }
+        }
         }
     }
 

@@ -157,7 +157,7 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constan
 // splits with eight loads in flight, the four partial sums meet in shared memory in a fixed order (deterministic).
 __global__ void __launch_bounds__(256)
 wgrad_halo_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int cin, int cout, int cout_slabs,
-                         int splits) {
+                         int splits, int tco) {
     __shared__ float red[4][64];
     const int x = threadIdx.x & 63, y = threadIdx.x >> 6;
     const long long total = 9LL * cin * cout;
@@ -185,8 +185,11 @@ wgrad_halo_reduce_kernel(const float* __restrict__ partial, float* __restrict__ 
         }
         red[y][x] = s;
         __syncthreads();
-        if (y == 0 && i < total)
-            dw[(static_cast<size_t>(o) * cin + c) * 9 + t] += (red[0][x] + red[1][x]) + (red[2][x] + red[3][x]);
+        if (y == 0 && i < total) {
+            // i = (t * cin + c) * cout + o is itself the [tap][cin][cout] index
+            const size_t di = tco ? static_cast<size_t>(i) : (static_cast<size_t>(o) * cin + c) * 9 + t;
+            dw[di] += (red[0][x] + red[1][x]) + (red[2][x] + red[3][x]);
+        }
         __syncthreads();
     }
 }
@@ -213,7 +216,7 @@ cudaError_t launch_wgrad_halo(const CUtensorMap& x, const CUtensorMap& dy, const
     int rgrid = static_cast<int>((total + 63) / 64);
     if (rgrid > 148 * 8) rgrid = 148 * 8;
     wgrad_halo_reduce_kernel<<<rgrid, 256, 0, stream>>>(p.partial, dw, p.cin_slabs * 64, p.cout_slabs * 64, p.cout_slabs,
-                                                        p.splits);
+                                                        p.splits, p.tco);
     return cudaGetLastError();
 }
 

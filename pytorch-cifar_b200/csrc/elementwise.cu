@@ -730,7 +730,7 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
     __shared__ float tile[32][32 * 9 + 1];
     const RepackEntry e = table[blockIdx.y];
     const int taps = e.taps;
-    if (e.kflat) {
+    if (e.kflat == 1) {
         // stem: [cout][cin*taps] fp32 -> [cout][cin_pad] bf16 with k = tap*cin + c
         const int row = e.cin * taps;
         for (int i = blockIdx.x * 256 + threadIdx.x; i < e.cout * row; i += gridDim.x * 256) {
@@ -741,6 +741,38 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
         return;
     }
     const int cout_pad = e.pad_ > 0 ? e.pad_ : e.cout;      // pad_ carries cout_pad (0: no padding)
+    if (e.kflat == 2) {
+        // master is [tap][cin][cout] fp32 (the engine's internal layout of conv weights, which the wgrad kernels
+        // write with coalesced vector reductions): the dgrad operand is a straight bf16 conversion, the fprop
+        // operand a 32x32 transpose per tap. Channel counts are even; pairs go out as bf16x2.
+        float (*t2)[33] = reinterpret_cast<float (*)[33]>(&tile[0][0]);
+        const int ct = (e.cin + 31) >> 5, ot = (e.cout + 31) >> 5;
+        const int ntile2 = taps * ct * ot;
+        for (int tidx = blockIdx.x; tidx < ntile2; tidx += gridDim.x) {
+            const int t = tidx / (ct * ot);
+            const int rem = tidx - t * ct * ot;
+            const int c0 = (rem / ot) << 5, o0 = (rem % ot) << 5;
+            const int nc = min(32, e.cin - c0), no = min(32, e.cout - o0);
+            __syncthreads();
+            for (int i = threadIdx.x; i < 32 * 32; i += 256) {
+                const int a = i >> 5, b = i & 31;
+                t2[a][b] = (a < nc && b < no)
+                               ? master[e.src_off + (static_cast<long long>(t) * e.cin + c0 + a) * e.cout + o0 + b]
+                               : 0.f;
+            }
+            __syncthreads();
+            for (int i = threadIdx.x; i < 32 * 16; i += 256) {
+                const int a = i >> 4, b = (i & 15) * 2;
+                if (e.wd_off >= 0 && a < nc && b < no)
+                    *reinterpret_cast<__nv_bfloat162*>(wd + e.wd_off + (static_cast<long long>(t) * e.cin_pad + c0 + a) * cout_pad + o0 + b) =
+                        __floats2bfloat162_rn(t2[a][b], t2[a][b + 1]);
+                if (a < no && b < nc)
+                    *reinterpret_cast<__nv_bfloat162*>(wf + e.wf_off + (static_cast<long long>(t) * cout_pad + o0 + a) * e.cin_pad + c0 + b) =
+                        __floats2bfloat162_rn(t2[b][a], t2[b + 1][a]);
+            }
+        }
+        return;
+    }
     const int ctiles = (e.cin + 31) >> 5;
     const int ntile = ((e.cout + 31) >> 5) * ctiles;
     for (int tidx = blockIdx.x; tidx < ntile; tidx += gridDim.x) {

@@ -286,6 +286,8 @@ def _bottleneck_spec(num_blocks, planes, num_classes):
 FUSE_DGRAD_BN = os.environ.get("B2C_FUSE_DGRAD_BN", "1") != "0"
 # 0 = residual units take their ReLU mask from the activation instead of the forward pass's bit mask
 RELU_BITS = os.environ.get("B2C_RELU_BITS", "1") != "0"
+# 0 = conv weights / gradients stored OIHW in the arenas (scattered 4-byte wgrad atomics)
+TCO_LAYOUT = os.environ.get("B2C_TCO_LAYOUT", "1") != "0"
 
 
 class ConvUnit:
@@ -310,12 +312,13 @@ class ConvUnit:
             self.desc_w = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, cin_valid=27, kflat_cin=3, cout_valid=cout)
         else:
             self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride)
-            self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout)
+            self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout,
+                                        flags=32 if (name + ".weight") in eng.tco else 0)
         self.eng_scratch = eng.wgrad_scratch
         self.wf = eng.wf_view(name)
         self.wd = None if stem else eng.wd_view(name)
         self.wd10 = None if stem else eng.wd10_view(name)
-        self.dw = eng.grad_view(name + ".weight")
+        self.dw = eng.grad_flat(name + ".weight")      # storage order: OIHW, or [tap][cin][cout] (eng.tco)
         if bn_name is not None:
             _bn_views(self, eng, bn_name, cout_p)
         # a conv bias (VGG) is never added to y — the BatchNorm cancels it — but the running mean tracks it
@@ -458,6 +461,12 @@ class Engine:
             self.B = torch.zeros(max(off, 4), **f32)       # BN running statistics
         # bf16 GEMM operand copies of the conv weights
         self.wf_off, self.wd_off, entries = {}, {}, []
+        # conv weights stored [tap][cin][cout] in the P / G / M arenas (see _arena_view): every dense conv except the
+        # 3-channel stem (its wgrad addresses the im2col'ed k axis) with channel counts the vector path can take
+        self.tco = set() if not TCO_LAYOUT else {
+            name for name, shape in spec["params"].items()
+            if len(shape) == 4 and name not in spec.get("depthwise", ()) and shape[1] != 3
+            and shape[0] % 4 == 0 and shape[1] % 2 == 0}
         self.wd_pair = {}      # 3x3 stride-2 conv1 -> its block's 1x1 shortcut conv, stored right behind it in WD
         wf_n = wd_n = 0
         convs = [(name, shape) for name, shape in spec["params"].items()
@@ -491,7 +500,7 @@ class Engine:
                 self.wf_off[cname] = (wf_n, (k * k, cout_p, cin_p))
                 self.wd_off[cname] = (wd_n, (k * k, cin_p, cout_p))
                 entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=wd_n, cout=cout, cin=cin, taps=k * k,
-                                    cin_pad=cin_p, cout_pad=cout_p))
+                                    cin_pad=cin_p, cout_pad=cout_p, kflat=2 if name in self.tco else 0))
                 wf_n += cout_p * cin_p * k * k
                 wd_n += cout_p * cin_p * k * k
         bf = dict(device=self.device, dtype=torch.bfloat16)
@@ -512,13 +521,28 @@ class Engine:
         assert taps == 9 and off2 == off + 9 * cin_p * cout_p
         return self.WD[off:off + 10 * cin_p * cout_p].view(10, cin_p, cout_p)
 
-    def param_view(self, name):
+    def _arena_view(self, arena, name):
+        """The reference-shaped (OIHW, ...) tensor `name` inside an arena. Conv weights in self.tco are STORED
+        [kh][kw][cin][cout] (the order the wgrad kernels reduce into with coalesced vector atomics, and the dgrad
+        operand's own order); the view handed out is that storage permuted back to OIHW, so every consumer of
+        state_dict / .grad semantics (load_params, named_params, accelerate(), optimizers, checkpoints) sees the
+        reference's shape and element meaning. Element-wise arena kernels (SGD, all-reduce) do not care."""
         off, n, shape = self.p_off[name]
-        return self.P[off:off + n].view(shape)
+        if name in self.tco:
+            co, ci, kh, kw = shape
+            return arena[off:off + n].view(kh, kw, ci, co).permute(3, 2, 0, 1)
+        return arena[off:off + n].view(shape)
+
+    def param_view(self, name):
+        return self._arena_view(self.P, name)
 
     def grad_view(self, name):
-        off, n, shape = self.p_off[name]
-        return self.G[off:off + n].view(shape)
+        return self._arena_view(self.G, name)
+
+    def grad_flat(self, name):
+        """Contiguous storage of a parameter's gradient (what the kernels write)."""
+        off, n, _ = self.p_off[name]
+        return self.G[off:off + n]
 
     def buffer_view(self, name):
         off, n = self.b_off[name]
@@ -559,7 +583,7 @@ class Engine:
     def load_params(self, named_params, named_buffers=None):
         """Copy reference-layout tensors (name -> tensor, fp32) into the arenas and refresh the bf16 copies."""
         for name, (off, n, shape) in self.p_off.items():
-            self.P[off:off + n].copy_(named_params[name].detach().reshape(-1).to(self.device, torch.float32))
+            self.param_view(name).copy_(named_params[name].detach().reshape(shape).to(self.device, torch.float32))
         if named_buffers is not None:
             for name, (off, n) in self.b_off.items():
                 self.B[off:off + n].copy_(named_buffers[name].detach().to(self.device, torch.float32))

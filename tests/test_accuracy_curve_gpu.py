@@ -22,7 +22,9 @@ def test_top1_curve_matches_fp32_oracle():
     from oracle import nets
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
-    N, epochs, lr0 = 128, 6, 0.05
+    # lr 0.02: at 0.05 the first epochs of this init are chaotic (the loss spikes to 3.6 before it falls) and two runs
+    # of EITHER implementation end up to 1.5 pt apart; at 0.02 both settle and the 0.5 pt bound is meaningful
+    N, epochs, lr0 = 128, 8, 0.02
     images, labels = data.learnable_cifar(8192 + 2000, seed=1, noise=56.0)
     tr_x, tr_y, te_x, te_y = images[:8192], labels[:8192], images[8192:], labels[8192:]
     # CosineAnnealingLR stepped per epoch like main.py:89,154 (T_max = number of epochs of this short run)

@@ -240,6 +240,56 @@ def test_stride2_split_w_map_equals_traversal_stride(ops, shape):
     assert torch.equal(ys[0], ys[1])
 
 
+@pytest.mark.parametrize("shape", [(4, 32, 32, 64, 64, 3, 1), (8, 16, 16, 128, 128, 3, 1), (16, 8, 8, 256, 512, 3, 2),
+                                   (32, 4, 4, 512, 512, 3, 1), (8, 16, 16, 128, 256, 1, 2), (3, 8, 8, 128, 128, 3, 1),
+                                   (4, 16, 16, 64, 128, 1, 1)])
+def test_conv_wgrad_tap_cin_cout_layout(ops, shape):
+    """flags bit 5: the weight gradient lands in [tap][cin][cout] order (vector reductions, 4 rows x 128 B per
+    instruction) and must equal the OIHW result permuted; it accumulates on top of existing contents."""
+    n, h, w, cin, cout, k, stride = shape
+    ho, wo = h // stride, w // stride
+    x = nhwc_bf16(n, h, w, cin, 61)
+    dy = nhwc_bf16(n, ho, wo, cout, 62)
+    ref = torch.nn.grad.conv2d_weight(to_nchw(x), (cout, cin, k, k), to_nchw(dy), stride=stride, padding=k // 2)
+    scratch = torch.zeros(ops.WGRAD_SCRATCH_FLOATS, device="cuda")
+    for use_scratch in (False, True):
+        dw = torch.full((k * k, cin, cout), 0.5, device="cuda")
+        d = ops.conv_desc(n, h, w, cin, cout, k, stride, flags=32)
+        ops.conv_wgrad(d, x, dy, dw, scratch=scratch if use_scratch else None)
+        torch.cuda.synchronize()
+        got = (dw - 0.5).view(k, k, cin, cout).permute(3, 2, 0, 1)
+        assert rel_err(got, ref) < 2e-3
+
+
+def test_repack_from_tap_cin_cout_master(ops):
+    """B2cRepackEntry.kflat == 2: master weights stored [tap][cin][cout] give the same two bf16 operands as the
+    OIHW master."""
+    g = torch.Generator(device="cuda").manual_seed(63)
+    entries, masters, offs = [], [], 0
+    wf_n = wd_n = 0
+    shapes = [(64, 64, 3), (128, 64, 1), (96, 24, 1), (512, 256, 3)]
+    for cout, cin, k in shapes:
+        w = torch.randn(cout, cin, k, k, device="cuda", generator=g)
+        masters.append(w)
+        cin_p, cout_p = (cin + 63) // 64 * 64, (cout + 63) // 64 * 64
+        entries.append(dict(src_off=offs, wf_off=wf_n, wd_off=wd_n, cout=cout, cin=cin, taps=k * k, cin_pad=cin_p,
+                            cout_pad=cout_p, kflat=2))
+        offs += w.numel(); wf_n += cout_p * cin_p * k * k; wd_n += cout_p * cin_p * k * k
+    master = torch.cat([w.permute(2, 3, 1, 0).reshape(-1) for w in masters]).contiguous()
+    wf = torch.zeros(wf_n, device="cuda", dtype=torch.bfloat16)
+    wd = torch.zeros(wd_n, device="cuda", dtype=torch.bfloat16)
+    ops.repack_weights(master, wf, wd, ops.make_repack_table(entries, "cuda"), len(entries))
+    torch.cuda.synchronize()
+    for e, w in zip(entries, masters):
+        cout, cin, kk = e["cout"], e["cin"], e["taps"]
+        f = wf[e["wf_off"]:e["wf_off"] + kk * e["cout_pad"] * e["cin_pad"]].view(kk, e["cout_pad"], e["cin_pad"])
+        d = wd[e["wd_off"]:e["wd_off"] + kk * e["cout_pad"] * e["cin_pad"]].view(kk, e["cin_pad"], e["cout_pad"])
+        assert torch.equal(f[:, :cout, :cin], ops.pack_weight_fprop(w))
+        assert torch.equal(d[:, :cin, :cout], ops.pack_weight_dgrad(w))
+        assert f[:, cout:].abs().sum() == 0 and f[:, :, cin:].abs().sum() == 0
+        assert d[:, cin:].abs().sum() == 0 and d[:, :, cout:].abs().sum() == 0
+
+
 @pytest.mark.parametrize("shape", CONV_SHAPES)
 def test_conv_wgrad(ops, shape):
     n, h, w, cin, cout, k, stride = shape

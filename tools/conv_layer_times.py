@@ -56,6 +56,10 @@ for (hw, cin, cout, k, s) in shapes:
     row["wgrad_atomic_us"] = round(t, 1); row["wgrad_atomic_tf"] = round(fl / t / 1e6, 0)
     t = timeit(lambda: ops.conv_wgrad(d, x, dy, dw, scratch=scratch))
     row["wgrad_us"] = round(t, 1); row["wgrad_tf"] = round(fl / t / 1e6, 0)
+    if os.environ.get("WGRAD_DEBUG"):      # epilogue cost: plain stores (8) / no stores (16) instead of atomics
+        for fl_dbg in (8, 16):
+            dd = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=1 | fl_dbg)
+            row[f"wgrad_dbg{fl_dbg}_us"] = round(timeit(lambda: ops.conv_wgrad(dd, x, dy, dw)), 1)
     out.append(row)
     print(json.dumps(row), flush=True)
 os.makedirs("gpurun_out", exist_ok=True)
