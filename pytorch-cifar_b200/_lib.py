@@ -8,7 +8,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2c.so")
+# B2C_LIB: measurement aid (tools/), an alternative build of the same library; the product path is the in-tree file
+LIB_PATH = os.environ.get("B2C_LIB") or os.path.join(_HERE, "libb2c.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 B2C_ERR_UNSUPPORTED = -10001

@@ -109,6 +109,30 @@ __device__ __forceinline__ void tma_load_5d(void* dst, const CUtensorMap* m, uin
         : "memory");
 }
 
+// ---------------------------------- programmatic dependent launch (b2c_launch.h) ----------
+// pdl_launch_dependents(): the next kernel in the stream may be scheduled once every CTA of this grid has got here.
+// pdl_wait(): blocks until the previous kernel in the stream has completed and its global writes are visible;
+// nothing before it may touch global memory that another kernel writes. Both are no-ops without the launch attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// Which kernel classes release their successor early (compile-time policy): tensor-core kernels (BIG), full-tensor
+// element-wise passes (EW), latency-bound kernels of a few CTAs (TINY). Measured on one box, ms per step at batch
+// 1024 / 128 per GPU: no PDL 5.389 / 1.375; all classes 5.506 / 1.354; TINY only 5.370 / 1.354; BIG+TINY 5.449 / 1.364;
+// EW+TINY 5.387 / 1.336. Early successors of the tensor-core kernels take SM resources from CTAs that still have
+// work, so those keep the implicit trigger at exit.
+#ifndef B2C_PDL_BIG
+#define B2C_PDL_BIG 0
+#endif
+#ifndef B2C_PDL_EW
+#define B2C_PDL_EW 1
+#endif
+#ifndef B2C_PDL_TINY
+#define B2C_PDL_TINY 1
+#endif
+__device__ __forceinline__ void pdl_trigger_big() { if (B2C_PDL_BIG) pdl_launch_dependents(); }
+__device__ __forceinline__ void pdl_trigger_ew() { if (B2C_PDL_EW) pdl_launch_dependents(); }
+__device__ __forceinline__ void pdl_trigger_tiny() { if (B2C_PDL_TINY) pdl_launch_dependents(); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------- tcgen05 ----------------------------------------------
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }

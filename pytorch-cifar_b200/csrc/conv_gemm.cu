@@ -18,6 +18,7 @@
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
 // warps 2..9 = epilogue (one TMEM lane quarter each).
 #include "b2c_kernels.h"
+#include "b2c_launch.h"
 #include "b2c_ptx.cuh"
 
 namespace b2c {
@@ -44,6 +45,7 @@ __global__ void __launch_bounds__(320, 1)
 tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
                 const __grid_constant__ CUtensorMap mapB, const __grid_constant__ TapGemmParams p) {
     using Cfg = TapCfg<BN>;
+    pdl_trigger_big();
     extern __shared__ uint8_t smem_raw[];
     // (offset arithmetic on the shared pointer itself keeps the address space visible to the compiler: plain
     // loads / stores below become LDS / STS instead of generic accesses)
@@ -85,6 +87,7 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();      // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
 
     const int total_tiles = p.num_m_tiles * p.num_n_tiles * p.num_phases;
     const int img = p.gH * p.gW;
@@ -364,7 +367,7 @@ cudaError_t launch_one(const CUtensorMap& a0, const CUtensorMap& a1, const CUten
     grid -= grid % p.num_n_tiles;  // keeps n_tile constant per CTA (per-CTA BatchNorm partial rows)
     if (grid < p.num_n_tiles) grid = p.num_n_tiles;
     if (stat_rows != nullptr) *stat_rows = grid / p.num_n_tiles;
-    kern<<<grid, 320, Cfg::kSmemBytes, stream>>>(a0, a1, b, p);
+    B2C_LAUNCH(kern, grid, 320, Cfg::kSmemBytes, stream, a0, a1, b, p);
     return cudaGetLastError();
 }
 

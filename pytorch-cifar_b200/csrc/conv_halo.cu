@@ -20,6 +20,7 @@
 //
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..9 = epilogue.
 #include "b2c_kernels.h"
+#include "b2c_launch.h"
 #include "b2c_ptx.cuh"
 
 namespace b2c {
@@ -55,6 +56,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     static_assert((2 * kSA + 2 * Cfg::kSB + 4) * 8 + 4 <= Cfg::kBarBytes, "barrier block");
     static_assert(!RES || Cfg::kSB >= 9, "resident weights need nine slots");
 
+    pdl_trigger_big();
     extern __shared__ uint8_t smem_raw[];
     // (offset arithmetic on the shared pointer keeps the address space visible: LDS / STS, not generic accesses)
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -102,6 +104,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();      // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
 
     const int total_tiles = p.num_m_tiles * p.num_n_tiles;
     const int per_img = p.tiles_h * p.tiles_w;
@@ -388,7 +391,7 @@ cudaError_t launch_inst(const CUtensorMap& a, const CUtensorMap& b, const HaloPa
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    kern<<<grid, 320, Cfg::kSmemBytes, stream>>>(a, b, p);
+    B2C_LAUNCH(kern, grid, 320, Cfg::kSmemBytes, stream, a, b, p);
     return cudaGetLastError();
 }
 

@@ -16,6 +16,7 @@
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
 // warps 2..5 = epilogue.
 #include "b2c_kernels.h"
+#include "b2c_launch.h"
 #include "b2c_ptx.cuh"
 
 namespace b2c {
@@ -39,6 +40,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
              const __grid_constant__ WgradParams p) {
     using Cfg = WgCfg<BN, KC>;
     constexpr int kSlabBytes = Cfg::kSlabBytes;
+    pdl_trigger_big();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* aux = smem + Cfg::kStages * Cfg::kStageBytes;
@@ -81,6 +83,7 @@ wgrad_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ C
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();      // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
     const int img = p.gH * p.gW;
 
     if (warp == 0) {
@@ -246,7 +249,7 @@ cudaError_t launch_one(const CUtensorMap& x, const CUtensorMap& dy, const WgradP
         attr_done = true;
     }
     const int grid = p.num_n_tiles * p.num_m_blocks * p.splits;
-    kern<<<grid, 192, Cfg::kSmemBytes, stream>>>(x, dy, p);
+    B2C_LAUNCH(kern, grid, 192, Cfg::kSmemBytes, stream, x, dy, p);
     return cudaGetLastError();
 }
 

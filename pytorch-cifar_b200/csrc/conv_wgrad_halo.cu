@@ -15,6 +15,7 @@
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer, warps 2..5 = epilogue.
 #include "b2c_kernels.h"
+#include "b2c_launch.h"
 #include "b2c_ptx.cuh"
 
 namespace b2c {
@@ -32,6 +33,7 @@ constexpr int kTmemCols = 512;
 __global__ void __launch_bounds__(192, 1)
 wgrad_halo_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constant__ CUtensorMap mapDY,
                   const __grid_constant__ WgradHaloParams p) {
+    pdl_trigger_big();
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* aux = smem + kStages * kStageBytes;
@@ -73,6 +75,7 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constan
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
+    pdl_wait();      // everything above (barriers, TMEM, descriptor prefetch) overlaps the previous kernel's tail
     const int per_img = p.tiles_h * p.tiles_w;
 
     if (warp == 0) {
@@ -158,6 +161,8 @@ wgrad_halo_kernel(const __grid_constant__ CUtensorMap mapX, const __grid_constan
 __global__ void __launch_bounds__(256)
 wgrad_halo_reduce_kernel(const float* __restrict__ partial, float* __restrict__ dw, int cin, int cout, int cout_slabs,
                          int splits, int tco) {
+    pdl_trigger_tiny();
+    pdl_wait();
     __shared__ float red[4][64];
     const int x = threadIdx.x & 63, y = threadIdx.x >> 6;
     const long long total = 9LL * cin * cout;
@@ -209,13 +214,13 @@ cudaError_t launch_wgrad_halo(const CUtensorMap& x, const CUtensorMap& dy, const
         attr_done = true;
     }
     const int grid = p.cin_slabs * p.cout_slabs * p.splits;
-    wgrad_halo_kernel<<<grid, 192, kSmemBytes, stream>>>(x, dy, p);
+    B2C_LAUNCH(wgrad_halo_kernel, grid, 192, kSmemBytes, stream, x, dy, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     const long long total = 9LL * p.cin_slabs * 64 * p.cout_slabs * 64;
     int rgrid = static_cast<int>((total + 63) / 64);
     if (rgrid > 148 * 8) rgrid = 148 * 8;
-    wgrad_halo_reduce_kernel<<<rgrid, 256, 0, stream>>>(p.partial, dw, p.cin_slabs * 64, p.cout_slabs * 64, p.cout_slabs,
+    B2C_LAUNCH(wgrad_halo_reduce_kernel, rgrid, 256, 0, stream, p.partial, dw, p.cin_slabs * 64, p.cout_slabs * 64, p.cout_slabs,
                                                         p.splits, p.tco);
     return cudaGetLastError();
 }

@@ -12,6 +12,7 @@
 // fprop also reduces per-channel sum / sum of squares of its fp32 results for the following BatchNorm
 // (one partial row per block, same format as the conv epilogue's).
 #include "b2c_elementwise.h"
+#include "b2c_launch.h"
 #include "b2c_ptx.cuh"
 
 namespace b2c {
@@ -42,6 +43,8 @@ __device__ __forceinline__ void load_w(const float* __restrict__ wt, int c0, int
 __global__ void __launch_bounds__(256)
 dw_fprop_kernel(const uint4* __restrict__ x, const float* __restrict__ wt, uint4* __restrict__ y, int N, int H, int W,
                 int C, int c_valid, int stride, float* __restrict__ part_sum, float* __restrict__ part_sq) {
+    pdl_trigger_ew();
+    pdl_wait();
     extern __shared__ float red[];  // [rpi][2][C]
     const int cvec = C >> 3;
     const int rpi = 256 / cvec;
@@ -104,6 +107,8 @@ dw_fprop_kernel(const uint4* __restrict__ x, const float* __restrict__ wt, uint4
 __global__ void __launch_bounds__(256)
 dw_dgrad_kernel(const uint4* __restrict__ dy, const float* __restrict__ wt, uint4* __restrict__ dx, int N, int H, int W,
                 int C, int c_valid, int stride) {
+    pdl_trigger_ew();
+    pdl_wait();
     const int cvec = C >> 3;
     const int rpi = 256 / cvec;
     const int cv = threadIdx.x % cvec, rl = threadIdx.x / cvec;
@@ -146,6 +151,8 @@ dw_dgrad_kernel(const uint4* __restrict__ dy, const float* __restrict__ wt, uint
 __global__ void __launch_bounds__(256)
 dw_wgrad_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, float* __restrict__ dw, int N, int H, int W,
                 int C, int c_valid, int stride) {
+    pdl_trigger_ew();
+    pdl_wait();
     extern __shared__ float red[];  // [rpi][9][C]
     const int cvec = C >> 3;
     const int rpi = 256 / cvec;
@@ -214,7 +221,7 @@ cudaError_t launch_dw_fprop(const void* x, const float* w, void* y, int N, int H
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * (H / stride) * (W / stride), C);
     if (stat_rows != nullptr) *stat_rows = blocks;
     const size_t smem = part_sum != nullptr ? static_cast<size_t>(rpi) * 2 * C * sizeof(float) : 0;
-    dw_fprop_kernel<<<blocks, 256, smem, s>>>(static_cast<const uint4*>(x), w, static_cast<uint4*>(y), N, H, W, C,
+    B2C_LAUNCH(dw_fprop_kernel, blocks, 256, smem, s, static_cast<const uint4*>(x), w, static_cast<uint4*>(y), N, H, W, C,
                                               c_valid, stride, part_sum, part_sq);
     return cudaGetLastError();
 }
@@ -224,7 +231,7 @@ cudaError_t launch_dw_dgrad(const void* dy, const float* w, void* dx, int N, int
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * H * W, C);
-    dw_dgrad_kernel<<<blocks * 2 > 148 * 8 ? 148 * 8 : blocks * 2, 256, 0, s>>>(
+    B2C_LAUNCH(dw_dgrad_kernel, blocks * 2 > 148 * 8 ? 148 * 8 : blocks * 2, 256, 0, s, 
         static_cast<const uint4*>(dy), w, static_cast<uint4*>(dx), N, H, W, C, c_valid, stride);
     return cudaGetLastError();
 }
@@ -242,7 +249,7 @@ cudaError_t launch_dw_wgrad(const void* x, const void* dy, float* dw, int N, int
         attr_done = true;
     }
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * (H / stride) * (W / stride), C);
-    dw_wgrad_kernel<<<blocks > 296 ? 296 : blocks, 256, smem, s>>>(static_cast<const uint4*>(x),
+    B2C_LAUNCH(dw_wgrad_kernel, blocks > 296 ? 296 : blocks, 256, smem, s, static_cast<const uint4*>(x),
                                                                    static_cast<const uint4*>(dy), dw, N, H, W, C,
                                                                    c_valid, stride);
     return cudaGetLastError();

@@ -3,6 +3,7 @@
 // augmentation, fused SGD and the weight re-layout. Each kernel states the reference call site it
 // replaces; all of them are judged against HBM bandwidth, not the tensor pipe.
 #include "b2c_elementwise.h"
+#include "b2c_launch.h"
 #include "b2c_ptx.cuh"
 
 namespace b2c {
@@ -101,6 +102,8 @@ bn_finalize_kernel(const float* __restrict__ part_sum, const float* __restrict__
                                    float* __restrict__ running_mean, float* __restrict__ running_var,
                                    float* __restrict__ scale, float* __restrict__ shift,
                                    float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+    pdl_trigger_tiny();
+    pdl_wait();
     const int warp = blockIdx.x * 32 + (threadIdx.x & 31);      // channel (name kept from the warp-per-channel form)
     double s1, s2;
     colsum2_block(part_sum + warp, part_sq + warp, static_cast<size_t>(C), rows, warp < C, s1, s2);
@@ -133,6 +136,8 @@ __global__ void bn_eval_scale_shift_kernel(int C, const float* __restrict__ gamm
                                            const float* __restrict__ running_mean,
                                            const float* __restrict__ running_var, float eps,
                                            float* __restrict__ scale, float* __restrict__ shift) {
+    pdl_trigger_tiny();
+    pdl_wait();
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     const float sc = gamma[c] / sqrtf(running_var[c] + eps);
@@ -152,6 +157,8 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
                     const uint4* __restrict__ res, const float* __restrict__ res_scale,
                     const float* __restrict__ res_shift, uint4* __restrict__ out, long long nvec, int C, int relu,
                     uint8_t* __restrict__ relu_bits) {
+    pdl_trigger_ew();
+    pdl_wait();
     // kUniform: the grid stride is a multiple of C/8, so a thread sees the same 8 channels in every iteration and
     // keeps their scale / shift in registers (no 64-bit modulo, no per-element parameter loads in the loop); two
     // grid strides are then in flight per iteration (all loads issued before the first use).
@@ -237,6 +244,8 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ a
                      uint4* __restrict__ dz_out, long long rows, int C, float* __restrict__ partial,
                      const float* __restrict__ relu_scale, const float* __restrict__ relu_shift,
                      const uint8_t* __restrict__ relu_bits) {
+    pdl_trigger_ew();
+    pdl_wait();
     extern __shared__ float red[];  // [rows_per_iter][2][C]
     const int cvec = C >> 3;
     const int rpi = 256 / cvec;     // rows handled per block iteration (cvec <= 256); threads past rpi*cvec idle
@@ -298,6 +307,8 @@ bn_bwd_finalize_kernel(const float* __restrict__ partial, int prow, int C, float
                                        const float* __restrict__ rstd, float* __restrict__ dgamma,
                                        float* __restrict__ dbeta, float* __restrict__ coefA,
                                        float* __restrict__ coefB, float* __restrict__ coefC) {
+    pdl_trigger_tiny();
+    pdl_wait();
     const int warp = blockIdx.x * 32 + (threadIdx.x & 31);      // channel
     double s1, s2;
     colsum2_block(partial + warp, partial + C + warp, static_cast<size_t>(2) * C, prow, warp < C, s1, s2);
@@ -325,6 +336,8 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, c
                     const float* __restrict__ coefB, const float* __restrict__ coefC, const uint4* __restrict__ add,
                     uint4* __restrict__ dy, long long nvec, int C, const float* __restrict__ relu_scale,
                     const float* __restrict__ relu_shift) {
+    pdl_trigger_ew();
+    pdl_wait();
     const int cvec = C >> 3;
     const long long start = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
     const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
@@ -369,6 +382,8 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, c
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, long long nvec_out, int Ho, int Wo, int C) {
+    pdl_trigger_ew();
+    pdl_wait();
     const int cvec = C >> 3;
     for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec_out;
          v += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -394,6 +409,8 @@ maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, long long
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y, const uint4* __restrict__ dy,
                    uint4* __restrict__ dx, long long nvec_out, int Ho, int Wo, int C) {
+    pdl_trigger_ew();
+    pdl_wait();
     const int cvec = C >> 3;
     for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec_out;
          v += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -438,6 +455,8 @@ maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y, con
 __global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ act, int hw, int C, const float* __restrict__ W,
                                 const float* __restrict__ bias, int K, float* __restrict__ pooled,
                                 float* __restrict__ logits) {
+    pdl_trigger_tiny();
+    pdl_wait();
     extern __shared__ float sp[];  // [C]
     const int n = blockIdx.x;
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
@@ -464,6 +483,8 @@ __global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ act, int hw, i
 __global__ void ce_loss_kernel(const float* __restrict__ logits, const long long* __restrict__ target, int N, int K,
                                float* __restrict__ dlogits, float* __restrict__ loss_out,
                                int* __restrict__ correct_out) {
+    pdl_trigger_tiny();
+    pdl_wait();
     __shared__ float sl[32];
     __shared__ int sc[32];
     float local = 0.f;
@@ -514,6 +535,8 @@ __global__ void ce_loss_kernel(const float* __restrict__ logits, const long long
 // Head backward, part 1: gradient w.r.t. the last activation (avg-pool + linear backward), bf16 NHWC.
 __global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const float* __restrict__ W, int K, int hw,
                                     int C, __nv_bfloat16* __restrict__ dact) {
+    pdl_trigger_tiny();
+    pdl_wait();
     const int n = blockIdx.x;
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
         float g = 0.f;
@@ -530,6 +553,8 @@ __global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const flo
 __global__ void __launch_bounds__(1024)
 head_bwd_param_kernel(const float* __restrict__ dlogits, const float* __restrict__ pooled, int N,
                       int K, int C, float* __restrict__ dW, float* __restrict__ db) {
+    pdl_trigger_tiny();
+    pdl_wait();
     __shared__ float red[32][33];
     const int k = blockIdx.y;
     const int cl = threadIdx.x & 31, nl = threadIdx.x >> 5;
@@ -598,6 +623,8 @@ __device__ __forceinline__ float aug_value(const uint8_t* simg, int y, int x, in
 __global__ void __launch_bounds__(256)
 augment_nchw_kernel(const uint8_t* __restrict__ data, const long long* __restrict__ idx,
                     const int8_t* __restrict__ ijf, float* __restrict__ out, AugConst k) {
+    pdl_trigger_ew();
+    pdl_wait();
     __shared__ __align__(16) uint8_t simg[3072];
     const int n = blockIdx.x;
     const uint4* src = reinterpret_cast<const uint4*>(data + static_cast<size_t>(idx[n]) * 3072);
@@ -616,6 +643,8 @@ augment_nchw_kernel(const uint8_t* __restrict__ data, const long long* __restric
 __global__ void __launch_bounds__(256)
 augment_im2col_kernel(const uint8_t* __restrict__ data, const long long* __restrict__ idx,
                       const int8_t* __restrict__ ijf, uint4* __restrict__ out, AugConst k) {
+    pdl_trigger_ew();
+    pdl_wait();
     __shared__ __align__(16) uint8_t simg[3072];
     __shared__ __nv_bfloat16 saug[34 * 34 * 3];  // augmented image with the conv's 1-px zero border
     const int n = blockIdx.x;
@@ -654,6 +683,8 @@ augment_im2col_kernel(const uint8_t* __restrict__ data, const long long* __restr
 // Drop-in path: fp32 NCHW network input (what the reference's DataLoader yields) -> stem im2col operand.
 __global__ void __launch_bounds__(256)
 stem_im2col_kernel(const float* __restrict__ x, uint4* __restrict__ out) {
+    pdl_trigger_ew();
+    pdl_wait();
     __shared__ __nv_bfloat16 saug[34 * 34 * 3];
     const int n = blockIdx.x;
     const float* xi = x + static_cast<size_t>(n) * 3072;
@@ -694,6 +725,8 @@ stem_im2col_kernel(const float* __restrict__ x, uint4* __restrict__ out) {
 __global__ void __launch_bounds__(256)
 sgd_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restrict__ buf, long long nvec,
            const float* __restrict__ hyper) {
+    pdl_trigger_ew();
+    pdl_wait();
     const float lr = hyper[0], mom = hyper[1], wd = hyper[2], gs = hyper[3];
     const bool first = hyper[4] != 0.f;
     for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec;
@@ -725,6 +758,8 @@ sgd_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restr
 __global__ void __launch_bounds__(256)
 repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, __nv_bfloat16* __restrict__ wd,
               const RepackEntry* __restrict__ table) {
+    pdl_trigger_ew();
+    pdl_wait();
     // One block = a 32 (cout) x 32 (cin) tile of one conv, all taps: coalesced fp32 reads of the OIHW rows,
     // transposes through shared memory, coalesced bf16 writes of both operand layouts.
     __shared__ float tile[32][32 * 9 + 1];
@@ -829,7 +864,7 @@ cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int 
                                const float* gamma, const float* beta, const float* conv_bias, float eps,
                                float momentum, float* running_mean, float* running_var, float* scale, float* shift,
                                float* mean, float* rstd, cudaStream_t s) {
-    bn_finalize_kernel<<<(C + 31) / 32, kFinWarps * 32, 0, s>>>(part_sum, part_sq, rows, C, count, gamma, beta, conv_bias, eps, momentum,
+    B2C_LAUNCH(bn_finalize_kernel, (C + 31) / 32, kFinWarps * 32, 0, s, part_sum, part_sq, rows, C, count, gamma, beta, conv_bias, eps, momentum,
                                                   running_mean, running_var, scale, shift, mean, rstd);
     return cudaGetLastError();
 }
@@ -837,7 +872,7 @@ cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int 
 cudaError_t launch_bn_eval_scale_shift(int C, const float* gamma, const float* beta, const float* conv_bias,
                                        const float* rm, const float* rv, float eps, float* scale, float* shift,
                                        cudaStream_t s) {
-    bn_eval_scale_shift_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, gamma, beta, conv_bias, rm, rv, eps, scale, shift);
+    B2C_LAUNCH(bn_eval_scale_shift_kernel, (C + 127) / 128, 128, 0, s, C, gamma, beta, conv_bias, rm, rv, eps, scale, shift);
     return cudaGetLastError();
 }
 
@@ -849,7 +884,7 @@ cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* 
     const bool uniform = (static_cast<long long>(grid) * 256) % (C >> 3) == 0;
     const bool affine = res != nullptr && res_scale != nullptr;
     auto go = [&](auto kern) {
-        kern<<<grid, 256, 0, s>>>(static_cast<const uint4*>(y), scale, shift, static_cast<const uint4*>(res), res_scale,
+        B2C_LAUNCH(kern, grid, 256, 0, s, static_cast<const uint4*>(y), scale, shift, static_cast<const uint4*>(res), res_scale,
                                   res_shift, static_cast<uint4*>(out), nvec, C, relu, relu_bits);
     };
     if (uniform && affine) go(bn_act_apply_kernel<true, true>);
@@ -876,15 +911,15 @@ cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* 
     const int blocks = bn_bwd_partial_rows(rows, C);
     const size_t smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
     if (relu_bits != nullptr)
-        bn_bwd_reduce_kernel<2><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), nullptr,
+        B2C_LAUNCH(bn_bwd_reduce_kernel<2>, blocks, 256, smem, s, static_cast<const uint4*>(dout), nullptr,
                                                          static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
                                                          rows, C, partial, nullptr, nullptr, relu_bits);
     else if (act == nullptr && relu_scale != nullptr)
-        bn_bwd_reduce_kernel<1><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout), nullptr,
+        B2C_LAUNCH(bn_bwd_reduce_kernel<1>, blocks, 256, smem, s, static_cast<const uint4*>(dout), nullptr,
                                                          static_cast<const uint4*>(y), nullptr, rows, C, partial,
                                                          relu_scale, relu_shift, nullptr);
     else
-        bn_bwd_reduce_kernel<0><<<blocks, 256, smem, s>>>(static_cast<const uint4*>(dout),
+        B2C_LAUNCH(bn_bwd_reduce_kernel<0>, blocks, 256, smem, s, static_cast<const uint4*>(dout),
                                                          static_cast<const uint4*>(act),
                                                          static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
                                                          rows, C, partial, nullptr, nullptr, nullptr);
@@ -894,7 +929,7 @@ cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* 
 cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float count, const float* gamma,
                                    const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
                                    float* coefB, float* coefC, cudaStream_t s) {
-    bn_bwd_finalize_kernel<<<(C + 31) / 32, kFinWarps * 32, 0, s>>>(partial, prow, C, count, gamma, mean, rstd, dgamma, dbeta,
+    B2C_LAUNCH(bn_bwd_finalize_kernel, (C + 31) / 32, kFinWarps * 32, 0, s, partial, prow, C, count, gamma, mean, rstd, dgamma, dbeta,
                                                       coefA, coefB, coefC);
     return cudaGetLastError();
 }
@@ -907,7 +942,7 @@ cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coef
     const bool uniform = (static_cast<long long>(grid) * 256) % (C >> 3) == 0;
     const bool masky = relu_scale != nullptr;
     auto go = [&](auto kern) {
-        kern<<<grid, 256, 0, s>>>(static_cast<const uint4*>(dz), static_cast<const uint4*>(y), coefA, coefB, coefC,
+        B2C_LAUNCH(kern, grid, 256, 0, s, static_cast<const uint4*>(dz), static_cast<const uint4*>(y), coefA, coefB, coefC,
                                   static_cast<const uint4*>(add), static_cast<uint4*>(dy), nvec, C, relu_scale,
                                   relu_shift);
     };
@@ -920,7 +955,7 @@ cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coef
 
 cudaError_t launch_maxpool_fwd(const void* x, void* y, int n, int h, int w, int C, cudaStream_t s) {
     const long long nvec = static_cast<long long>(n) * (h / 2) * (w / 2) * (C >> 3);
-    maxpool_fwd_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(static_cast<const uint4*>(x),
+    B2C_LAUNCH(maxpool_fwd_kernel, grid_for(nvec, 256, 148 * 8), 256, 0, s, static_cast<const uint4*>(x),
                                                                    static_cast<uint4*>(y), nvec, h / 2, w / 2, C);
     return cudaGetLastError();
 }
@@ -928,7 +963,7 @@ cudaError_t launch_maxpool_fwd(const void* x, void* y, int n, int h, int w, int 
 cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int C,
                                cudaStream_t s) {
     const long long nvec = static_cast<long long>(n) * (h / 2) * (w / 2) * (C >> 3);
-    maxpool_bwd_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(
+    B2C_LAUNCH(maxpool_bwd_kernel, grid_for(nvec, 256, 148 * 8), 256, 0, s, 
         static_cast<const uint4*>(x), static_cast<const uint4*>(y), static_cast<const uint4*>(dy),
         static_cast<uint4*>(dx), nvec, h / 2, w / 2, C);
     return cudaGetLastError();
@@ -937,25 +972,25 @@ cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, voi
 cudaError_t launch_head_fwd(const void* act, int N, int hw, int C, const float* W, const float* bias, int K,
                             float* pooled, float* logits, cudaStream_t s) {
     if (C > 4096 || (C & 31)) return cudaErrorInvalidValue;
-    head_fwd_kernel<<<N, C < 512 ? C : 512, C * sizeof(float), s>>>(static_cast<const __nv_bfloat16*>(act), hw, C, W, bias, K, pooled,
+    B2C_LAUNCH(head_fwd_kernel, N, C < 512 ? C : 512, C * sizeof(float), s, static_cast<const __nv_bfloat16*>(act), hw, C, W, bias, K, pooled,
                                                     logits);
     return cudaGetLastError();
 }
 
 cudaError_t launch_ce_loss(const float* logits, const long long* target, int N, int K, float* dlogits, float* loss,
                            int* correct, cudaStream_t s) {
-    ce_loss_kernel<<<1, 1024, 0, s>>>(logits, target, N, K, dlogits, loss, correct);
+    B2C_LAUNCH(ce_loss_kernel, 1, 1024, 0, s, logits, target, N, K, dlogits, loss, correct);
     return cudaGetLastError();
 }
 
 cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const float* W, int N, int hw, int C, int K,
                             void* dact, float* dW, float* db, cudaStream_t s) {
     if (C > 4096) return cudaErrorInvalidValue;
-    head_bwd_act_kernel<<<N, C < 512 ? C : 512, 0, s>>>(dlogits, W, K, hw, C, static_cast<__nv_bfloat16*>(dact));
+    B2C_LAUNCH(head_bwd_act_kernel, N, C < 512 ? C : 512, 0, s, dlogits, W, K, hw, C, static_cast<__nv_bfloat16*>(dact));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     dim3 grid((C + 31) / 32, K);
-    head_bwd_param_kernel<<<grid, 1024, 0, s>>>(dlogits, pooled, N, K, C, dW, db);
+    B2C_LAUNCH(head_bwd_param_kernel, grid, 1024, 0, s, dlogits, pooled, N, K, C, dW, db);
     return cudaGetLastError();
 }
 
@@ -968,27 +1003,27 @@ static AugConst make_aug(const float* mean, const float* stdv) {
 cudaError_t launch_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out, int N,
                                 const float* mean, const float* stdv, cudaStream_t s) {
     if (N == 0) return cudaSuccess;
-    augment_nchw_kernel<<<N, 256, 0, s>>>(data, idx, ijf, out, make_aug(mean, stdv));
+    B2C_LAUNCH(augment_nchw_kernel, N, 256, 0, s, data, idx, ijf, out, make_aug(mean, stdv));
     return cudaGetLastError();
 }
 
 cudaError_t launch_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out, int N,
                                   const float* mean, const float* stdv, cudaStream_t s) {
     if (N == 0) return cudaSuccess;
-    augment_im2col_kernel<<<N, 256, 0, s>>>(data, idx, ijf, static_cast<uint4*>(out), make_aug(mean, stdv));
+    B2C_LAUNCH(augment_im2col_kernel, N, 256, 0, s, data, idx, ijf, static_cast<uint4*>(out), make_aug(mean, stdv));
     return cudaGetLastError();
 }
 
 cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s) {
     if (N == 0) return cudaSuccess;
-    stem_im2col_kernel<<<N, 256, 0, s>>>(x, static_cast<uint4*>(out));
+    B2C_LAUNCH(stem_im2col_kernel, N, 256, 0, s, x, static_cast<uint4*>(out));
     return cudaGetLastError();
 }
 
 cudaError_t launch_sgd(float* p, const float* g, float* buf, long long n, const float* hyper, cudaStream_t s) {
     if (n & 3) return cudaErrorInvalidValue;
     const long long nvec = n >> 2;
-    sgd_kernel<<<grid_for(nvec, 256, 148 * 8), 256, 0, s>>>(reinterpret_cast<float4*>(p),
+    B2C_LAUNCH(sgd_kernel, grid_for(nvec, 256, 148 * 8), 256, 0, s, reinterpret_cast<float4*>(p),
                                                           reinterpret_cast<const float4*>(g),
                                                           reinterpret_cast<float4*>(buf), nvec, hyper);
     return cudaGetLastError();
@@ -998,7 +1033,7 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
                           cudaStream_t s) {
     if (entries == 0) return cudaSuccess;
     dim3 grid(128, entries);
-    repack_kernel<<<grid, 256, 0, s>>>(master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd),
+    B2C_LAUNCH(repack_kernel, grid, 256, 0, s, master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd),
                                        table_dev);
     return cudaGetLastError();
 }
