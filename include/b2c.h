@@ -56,7 +56,9 @@ typedef struct B2cConvDesc {
                                (measurement aid: same result, twice the L2->SM operand bytes);
                         bits 3,4: wgrad measurement switches (plain stores / no stores instead of reductions);
                         bit 5: wgrad: dw is laid out [tap][cin_valid][cout_valid] instead of OIHW, which lets the
-                               epilogue reduce 4 rows x 128 contiguous bytes per instruction */
+                               epilogue reduce 4 rows x 128 contiguous bytes per instruction;
+                        bit 6: wgrad: keep the per-tap kernel where the row kernel (conv_wgrad_row.cu) would be
+                               chosen (measurement aid) */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)

@@ -460,6 +460,34 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
             return cuda_rc(b2c::launch_wgrad_halo(mx, mdy, hp, dw, as_stream(stream)));
         }
     }
+    // row kernel (conv_wgrad_row.cu): 3x3 stride 1 on 16x16 / 8x8 images, channels in units of 128, [tap][cin][cout]
+    // gradient layout. flags bit 6 keeps the per-tap kernel (A/B measurements).
+    if ((d->flags & 32) && !(d->flags & (1 | 64)) && d->ksize == 3 && d->stride == 1 && d->h == d->w &&
+        (d->w == 16 || d->w == 8) && (d->cin % 128) == 0 && (d->cout % 128) == 0 &&
+        (d->cin_valid == 0 || d->cin_valid == d->cin) && (d->cout_valid == 0 || d->cout_valid == d->cout) &&
+        d->kflat_cin == 0) {
+        b2c::WgradRowParams rp = {};
+        rp.cin_pairs = d->cin / 128;
+        rp.cout_slabs = d->cout / 128;
+        rp.cin = d->cin;
+        rp.cout = d->cout;
+        rp.dw = dw;
+        const bool w16 = d->w == 16;
+        rp.num_steps = w16 ? d->n * 4 : d->n;
+        const int units = 3 * rp.cin_pairs * rp.cout_slabs;
+        const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+        int splits = max_ctas / units;
+        if (splits < 1) splits = 1;
+        if (splits > rp.num_steps) splits = rp.num_steps;
+        rp.steps_per_split = (rp.num_steps + splits - 1) / splits;
+        rp.splits = (rp.num_steps + rp.steps_per_split - 1) / rp.steps_per_split;
+        CUtensorMap mx, mdy;
+        rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, d->w + 2, w16 ? 4 : 8, 1, 1);
+        if (rc) return rc;
+        rc = encode_nhwc(&mdy, dy, d->n, d->h, d->w, d->cout, d->w, w16 ? 4 : 8, 1, 1);
+        if (rc) return rc;
+        return cuda_rc(b2c::launch_wgrad_row(mx, mdy, rp, w16 ? 1 : 0, as_stream(stream)));
+    }
     const int bn = pick_bn(d->block_n, d->cout, 1 << 20);
     const int kpx = (bn <= 128 && grid_tiles(ho, wo, 128)) ? 128 : 64;     // pixels per k-step
     if (!grid_tiles(ho, wo, kpx)) return B2C_ERR_UNSUPPORTED;

@@ -108,6 +108,16 @@ struct WgradHaloParams {
     float* partial;              // [cin_slabs*cout_slabs][splits][5][128][64] fp32
     int tco;                     // dW layout: 0 = OIHW, 1 = [tap][cin][cout]
 };
+// 3x3 stride-1 wgrad, one kernel row of taps per CTA (conv_wgrad_row.cu); dW in [tap][cin][cout] order
+struct WgradRowParams {
+    int cin_pairs, cout_slabs;   // 128-channel units
+    int splits, steps_per_split; // split-K over 64-pixel k-steps
+    int num_steps;
+    int cin, cout;
+    float* dw;
+};
+cudaError_t launch_wgrad_row(const CUtensorMap& x, const CUtensorMap& dy, const WgradRowParams& p, int w16,
+                             cudaStream_t stream);
 size_t wgrad_halo_scratch_floats(int cin, int cout, int splits);
 cudaError_t launch_wgrad_halo(const CUtensorMap& x, const CUtensorMap& dy, const WgradHaloParams& p, float* dw,
                               cudaStream_t stream);

@@ -242,7 +242,8 @@ def test_stride2_split_w_map_equals_traversal_stride(ops, shape):
 
 @pytest.mark.parametrize("shape", [(4, 32, 32, 64, 64, 3, 1), (8, 16, 16, 128, 128, 3, 1), (16, 8, 8, 256, 512, 3, 2),
                                    (32, 4, 4, 512, 512, 3, 1), (8, 16, 16, 128, 256, 1, 2), (3, 8, 8, 128, 128, 3, 1),
-                                   (4, 16, 16, 64, 128, 1, 1)])
+                                   (4, 16, 16, 64, 128, 1, 1), (16, 8, 8, 256, 256, 3, 1), (2, 16, 16, 128, 256, 3, 1),
+                                   (40, 16, 16, 256, 128, 3, 1), (300, 8, 8, 128, 128, 3, 1)])
 def test_conv_wgrad_tap_cin_cout_layout(ops, shape):
     """flags bit 5: the weight gradient lands in [tap][cin][cout] order (vector reductions, 4 rows x 128 B per
     instruction) and must equal the OIHW result permuted; it accumulates on top of existing contents."""
@@ -259,6 +260,11 @@ def test_conv_wgrad_tap_cin_cout_layout(ops, shape):
         torch.cuda.synchronize()
         got = (dw - 0.5).view(k, k, cin, cout).permute(3, 2, 0, 1)
         assert rel_err(got, ref) < 2e-3
+    # the row kernel (16x16 / 8x8 images, 128-channel units) against the per-tap kernel (flags bit 6)
+    dw2 = torch.zeros(k * k, cin, cout, device="cuda")
+    ops.conv_wgrad(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=32 | 64), x, dy, dw2)
+    torch.cuda.synchronize()
+    assert rel_err(dw2.view(k, k, cin, cout).permute(3, 2, 0, 1), ref) < 2e-3
 
 
 def test_repack_from_tap_cin_cout_master(ops):

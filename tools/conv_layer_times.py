@@ -56,6 +56,12 @@ for (hw, cin, cout, k, s) in shapes:
     row["wgrad_atomic_us"] = round(t, 1); row["wgrad_atomic_tf"] = round(fl / t / 1e6, 0)
     t = timeit(lambda: ops.conv_wgrad(d, x, dy, dw, scratch=scratch))
     row["wgrad_us"] = round(t, 1); row["wgrad_tf"] = round(fl / t / 1e6, 0)
+    dt = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=32)          # [tap][cin][cout] gradient layout (engine default)
+    t = timeit(lambda: ops.conv_wgrad(dt, x, dy, dw, scratch=scratch))
+    row["wgrad_tco_us"] = round(t, 1); row["wgrad_tco_tf"] = round(fl / t / 1e6, 0)
+    dt2 = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=32 | 64)    # ... with the per-tap kernel
+    t = timeit(lambda: ops.conv_wgrad(dt2, x, dy, dw, scratch=scratch))
+    row["wgrad_tco_tap_us"] = round(t, 1)
     if os.environ.get("WGRAD_DEBUG"):      # epilogue cost: plain stores (8) / no stores (16) instead of atomics
         for fl_dbg in (8, 16):
             dd = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=1 | fl_dbg)
