@@ -203,6 +203,186 @@ dw_wgrad_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, float
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Stride-1 variants: a thread owns 4 channels of one output column and walks a strip of T consecutive rows with a
+// 3x3 window held in registers — every input vector is loaded and converted to fp32 once per thread (3 loads per
+// output instead of 9, and the horizontal neighbours come from L1). The per-pixel kernels above issue ~250
+// instructions per 8-channel output and are instruction-bound at a third of the HBM roofline.
+//   MODE 0: fprop (+ BatchNorm partial sums)   MODE 1: dgrad (the same correlation with the weights flipped)
+//   MODE 2: wgrad (window of x, one dy vector per row, 36 accumulators, block reduction + fp32 atomics)
+// Work item = (image, strip, column); thread t owns channel quad t % (C/4); blockDim 256.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void unpack4(const uint2& u, float (&f)[4]) {
+    f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
+}
+
+template <int MODE, int T>
+__global__ void __launch_bounds__(256)
+dw_strip_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, const float* __restrict__ wt,
+                uint2* __restrict__ out, float* __restrict__ dw, int N, int H, int W, int C, int c_valid,
+                float* __restrict__ part_sum, float* __restrict__ part_sq) {
+    pdl_trigger_ew();
+    pdl_wait();
+    extern __shared__ float red[];   // MODE 0: [rpi][2][C]; MODE 2: [rpi][9][C]
+    const int cq_n = C >> 2;
+    const int rpi = 256 / cq_n;
+    const int cq = threadIdx.x % cq_n, rl = threadIdx.x / cq_n;
+    const bool active = rl < rpi;
+    const int strips = H / T;
+    const long long items = static_cast<long long>(N) * strips * W;
+
+    float w[9][4];       // MODE 0/1: weights (flipped for dgrad); MODE 2: accumulators
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            if (MODE == 2) w[t][e] = 0.f;
+            else w[t][e] = (cq * 4 + e < c_valid) ? __ldg(wt + (cq * 4 + e) * 9 + (MODE == 1 ? 8 - t : t)) : 0.f;
+        }
+    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    const uint2 zero = make_uint2(0u, 0u);
+
+    for (long long it = static_cast<long long>(blockIdx.x) * rpi + rl; active && it < items;
+         it += static_cast<long long>(gridDim.x) * rpi) {
+        const int wo = static_cast<int>(it % W);
+        const int st = static_cast<int>((it / W) % strips);
+        const long long n = it / (static_cast<long long>(W) * strips);
+        const int h0 = st * T;
+        const bool left = wo > 0, right = wo + 1 < W;
+        // row pointer arithmetic in units of uint2 (4 channels)
+        const uint2* base = in + ((n * H) * W + wo) * cq_n + cq;
+        const long long row_pitch = static_cast<long long>(W) * cq_n;
+        auto load_row = [&](int h, uint2 (&r)[3]) {
+            if (h < 0 || h >= H) { r[0] = zero; r[1] = zero; r[2] = zero; return; }
+            const uint2* p = base + h * row_pitch;
+            r[0] = left ? __ldg(p - cq_n) : zero;
+            r[1] = __ldg(p);
+            r[2] = right ? __ldg(p + cq_n) : zero;
+        };
+        float win[3][3][4];      // [row slot][col][channel]; slot = input row modulo 3 (static after unrolling)
+        uint2 raw[3];
+        load_row(h0 - 1, raw);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) unpack4(raw[c], win[0][c]);
+        load_row(h0, raw);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) unpack4(raw[c], win[1][c]);
+        load_row(h0 + 1, raw);               // prefetched one row ahead of its use
+#pragma unroll
+        for (int i = 0; i < T; ++i) {
+            // rows h0+i-1, h0+i, h0+i+1 live in slots i%3, (i+1)%3, (i+2)%3
+#pragma unroll
+            for (int c = 0; c < 3; ++c) unpack4(raw[c], win[(i + 2) % 3][c]);
+            if (i + 1 < T) load_row(h0 + i + 2, raw);
+            const long long opix = ((n * H + h0 + i) * W + wo) * cq_n + cq;
+            if (MODE == 2) {
+                float g[4];
+                unpack4(__ldg(in2 + opix), g);
+#pragma unroll
+                for (int r = 0; r < 3; ++r)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            w[r * 3 + c][e] = fmaf(win[(i + r) % 3][c][e], g[e], w[r * 3 + c][e]);
+            } else {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int r = 0; r < 3; ++r)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc[e] = fmaf(win[(i + r) % 3][c][e], w[r * 3 + c][e], acc[e]);
+                uint2 o;
+                o.x = pack_bf16x2(acc[0], acc[1]);
+                o.y = pack_bf16x2(acc[2], acc[3]);
+                out[opix] = o;
+                if (MODE == 0) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        s1[e] += acc[e];
+                        s2[e] = fmaf(acc[e], acc[e], s2[e]);
+                    }
+                }
+            }
+        }
+    }
+    if (MODE == 0) {
+        if (part_sum == nullptr) return;
+        if (active) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                red[(rl * 2 + 0) * C + cq * 4 + e] = s1[e];
+                red[(rl * 2 + 1) * C + cq * 4 + e] = s2[e];
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 2 * C; i += 256) {
+            float s = 0.f;
+            for (int k = 0; k < rpi; ++k) s += red[k * 2 * C + i];
+            if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
+            else part_sq[static_cast<size_t>(blockIdx.x) * C + (i - C)] = s;
+        }
+    } else if (MODE == 2) {
+        if (active) {
+#pragma unroll
+            for (int t = 0; t < 9; ++t)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) red[(rl * 9 + t) * C + cq * 4 + e] = w[t][e];
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 9 * C; i += 256) {
+            const int t = i / C, c = i - t * C;
+            if (c >= c_valid) continue;
+            float s = 0.f;
+            for (int k = 0; k < rpi; ++k) s += red[(k * 9 + t) * C + c];
+            atomicAdd(dw + c * 9 + t, s);
+        }
+    }
+}
+
+// stride-1 strip kernels: T = 8 rows (images of 8 pixels and more) or 4
+inline bool dw_strip_ok(int H, int W, int C, int stride) {
+    return stride == 1 && (C & 3) == 0 && (C >> 2) <= 256 && H >= 4 && (H % 4) == 0 && W >= 2;
+}
+
+template <int MODE>
+cudaError_t launch_dw_strip(const void* in, const void* in2, const float* w, void* out, float* dw, int N, int H, int W,
+                            int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s) {
+    const int cq_n = C >> 2;
+    const int rpi = 256 / cq_n;
+    const int T = (H % 8) == 0 ? 8 : 4;
+    const long long items = static_cast<long long>(N) * (H / T) * W;
+    long long blocks = (items + rpi - 1) / rpi;
+    const int cap = MODE == 2 ? 296 : 148 * 4;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    if (stat_rows != nullptr) *stat_rows = static_cast<int>(blocks);
+    size_t smem = 0;
+    if (MODE == 0 && part_sum != nullptr) smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
+    if (MODE == 2) smem = static_cast<size_t>(rpi) * 9 * C * sizeof(float);
+    auto k8 = dw_strip_kernel<MODE, 8>;
+    auto k4 = dw_strip_kernel<MODE, 4>;
+    if (MODE == 2) {
+        static bool attr_done = false;
+        if (!attr_done) {
+            cudaError_t e = cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            if (e != cudaSuccess) return e;
+            attr_done = true;
+        }
+    }
+    if (T == 8)
+        B2C_LAUNCH(k8, static_cast<int>(blocks), 256, smem, s, static_cast<const uint2*>(in),
+                   static_cast<const uint2*>(in2), w, static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum,
+                   part_sq);
+    else
+        B2C_LAUNCH(k4, static_cast<int>(blocks), 256, smem, s, static_cast<const uint2*>(in),
+                   static_cast<const uint2*>(in2), w, static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum,
+                   part_sq);
+    return cudaGetLastError();
+}
+
 }  // namespace
 
 int dw_fprop_partial_rows(long long out_pixels, int C) {
@@ -217,6 +397,8 @@ cudaError_t launch_dw_fprop(const void* x, const float* w, void* y, int N, int H
                             float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s) {
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
+    if (dw_strip_ok(H, W, C, stride))
+        return launch_dw_strip<0>(x, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s);
     const int rpi = 256 / cvec;
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * (H / stride) * (W / stride), C);
     if (stat_rows != nullptr) *stat_rows = blocks;
@@ -230,6 +412,8 @@ cudaError_t launch_dw_dgrad(const void* dy, const float* w, void* dx, int N, int
                             int stride, cudaStream_t s) {
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
+    if (dw_strip_ok(H, W, C, stride))
+        return launch_dw_strip<1>(dy, nullptr, w, dx, nullptr, N, H, W, C, c_valid, nullptr, nullptr, nullptr, s);
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * H * W, C);
     B2C_LAUNCH(dw_dgrad_kernel, blocks * 2 > 148 * 8 ? 148 * 8 : blocks * 2, 256, 0, s, 
         static_cast<const uint4*>(dy), w, static_cast<uint4*>(dx), N, H, W, C, c_valid, stride);
@@ -240,6 +424,8 @@ cudaError_t launch_dw_wgrad(const void* x, const void* dy, float* dw, int N, int
                             int stride, cudaStream_t s) {
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
+    if (dw_strip_ok(H, W, C, stride))
+        return launch_dw_strip<2>(x, dy, nullptr, nullptr, dw, N, H, W, C, c_valid, nullptr, nullptr, nullptr, s);
     const int rpi = 256 / cvec;
     const size_t smem = static_cast<size_t>(rpi) * 9 * C * sizeof(float);      // 72 KB at most
     static bool attr_done = false;

@@ -84,7 +84,8 @@ def test_bn_bwd_apply_with_bypass_add(ops):
 
 
 @pytest.mark.parametrize("shape", [(4, 32, 32, 96, 96, 1), (4, 32, 32, 192, 144, 2), (8, 8, 8, 384, 384, 1),
-                                   (8, 8, 8, 576, 576, 2), (16, 4, 4, 960, 960, 1), (2, 32, 32, 64, 32, 1)])
+                                   (8, 8, 8, 576, 576, 2), (16, 4, 4, 960, 960, 1), (2, 32, 32, 64, 32, 1),
+                                   (5, 16, 16, 192, 144, 1), (3, 16, 16, 192, 192, 2), (40, 8, 8, 64, 64, 1)])
 def test_depthwise_conv(ops, shape):
     n, h, w, cpad, c, stride = shape
     g = torch.Generator(device="cuda").manual_seed(60)
