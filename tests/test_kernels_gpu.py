@@ -3,6 +3,7 @@
 Every call goes through the C-ABI (ctypes -> libb2c.so). Tolerances: bf16-stored results within 1e-2
 relative (Frobenius) of the fp32 reference (BASELINE.json north_star); fp32 results within 1e-3.
 """
+import numpy as np
 import pytest
 import torch
 import torch.nn.functional as F
@@ -560,3 +561,91 @@ def test_repack_weights(ops):
     stem = wf[w1.numel() + w2.numel():].view(64, 64)
     assert torch.equal(stem[:, :27], w0.permute(0, 2, 3, 1).reshape(64, 27).to(torch.bfloat16))
     assert (stem[:, 27:] == 0).all()
+
+
+# ------------------------------------------------------------------------------------------------
+# Guard bands: every output of the newer kernels sits inside a larger sentinel-filled allocation; nothing outside
+# the tensor may change (compute-sanitizer is not available on the GPU pool, so out-of-bounds stores are caught here).
+# ------------------------------------------------------------------------------------------------
+class _Guarded:
+    PAD = 4096        # elements on either side
+
+    def __init__(self, shape, dtype, fill):
+        n = int(np.prod(shape))
+        self.raw = torch.empty(n + 2 * self.PAD, device="cuda", dtype=dtype)
+        self.sentinel = 123 if dtype == torch.uint8 else -7777.0
+        self.raw.fill_(self.sentinel)
+        self.t = self.raw[self.PAD:self.PAD + n].view(shape)
+        self.t.fill_(fill)
+
+    def intact(self):
+        return bool((self.raw[:self.PAD] == self.sentinel).all() and (self.raw[-self.PAD:] == self.sentinel).all())
+
+
+def test_outputs_stay_inside_their_tensors(ops):
+    n, h, cin, cout = 5, 16, 128, 256                 # odd batch: ragged last tile in every kernel
+    g = torch.Generator(device="cuda").manual_seed(71)
+    bad = []
+
+    def check(name, *gs):
+        torch.cuda.synchronize()
+        for i, gd in enumerate(gs):
+            if not gd.intact():
+                bad.append(f"{name}[{i}]")
+
+    # fprop (+stats), dgrad (+add), fused dgrad+BN, stride-2 dgrad with shortcut
+    for (hh, ci, co, k, s) in [(16, 128, 128, 3, 1), (8, 256, 256, 3, 1), (32, 64, 64, 3, 1), (16, 128, 256, 3, 2),
+                               (16, 128, 256, 1, 2), (4, 512, 512, 3, 1), (32, 64, 64, 1, 1)]:
+        ho = hh // s
+        x = nhwc_bf16(n, hh, hh, ci, 72)
+        wt = weight(co, ci, k, 73)
+        d = ops.conv_desc(n, hh, hh, ci, co, k, s)
+        y = _Guarded((n, ho, ho, co), torch.bfloat16, 0.0)
+        ps, pq = _Guarded((148, co), torch.float32, 0.0), _Guarded((148, co), torch.float32, 0.0)
+        ops.conv_fprop(d, x, ops.pack_weight_fprop(wt), y.t, ps.t, pq.t)
+        check(f"fprop{(hh, ci, co, k, s)}", y, ps, pq)
+        dy = nhwc_bf16(n, ho, ho, co, 74)
+        dx = _Guarded((n, hh, hh, ci), torch.bfloat16, 0.0)
+        ops.conv_dgrad(d, dy, ops.pack_weight_dgrad(wt), dx.t)
+        check(f"dgrad{(hh, ci, co, k, s)}", dx)
+        if not (k == 1 and s == 2):
+            dz = _Guarded((n, hh, hh, ci), torch.bfloat16, 0.0)
+            part = _Guarded((148, 2, ci), torch.float32, 0.0)
+            sc = torch.rand(ci, device="cuda", generator=g) + 0.5
+            sh = torch.randn(ci, device="cuda", generator=g)
+            ops.conv_dgrad_bn(d, dy, ops.pack_weight_dgrad(wt), dz.t, x, sc, sh, part.t)
+            check(f"dgrad_bn{(hh, ci, co, k, s)}", dz, part)
+        if k == 3 and s == 2:
+            w10 = torch.cat([ops.pack_weight_dgrad(wt), ops.pack_weight_dgrad(weight(co, ci, 1, 75))], 0).contiguous()
+            dx2 = _Guarded((n, hh, hh, ci), torch.bfloat16, 0.0)
+            ops.conv_dgrad_with_shortcut(d, dy, nhwc_bf16(n, ho, ho, co, 76), w10, dx2.t)
+            check("dgrad_shortcut", dx2)
+        for flags in (0, 32, 32 | 64):
+            dw = _Guarded((co * ci * k * k,), torch.float32, 0.0)
+            ops.conv_wgrad(ops.conv_desc(n, hh, hh, ci, co, k, s, flags=flags), x, dy, dw.t)
+            check(f"wgrad{(hh, ci, co, k, s, flags)}", dw)
+    # BN apply with bit mask, BN backward reduce/apply
+    rows, C = n * 16 * 16, 128
+    yb = nhwc_bf16(n, 16, 16, C, 77).view(rows, C)
+    sc = torch.rand(C, device="cuda", generator=g) + 0.5
+    sh = torch.randn(C, device="cuda", generator=g)
+    out, bits = _Guarded((rows, C), torch.bfloat16, 0.0), _Guarded((rows * C // 8,), torch.uint8, 0)
+    ops.bn_act_apply(yb, sc, sh, out.t, rows, C, relu=True, res=yb, relu_bits=bits.t)
+    check("bn_act_apply", out, bits)
+    prow = ops.bn_bwd_partial_rows(rows, C)
+    part, dzg = _Guarded((prow, 2, C), torch.float32, 0.0), _Guarded((rows, C), torch.bfloat16, 0.0)
+    ops.bn_bwd_reduce(yb, None, yb, dzg.t, rows, C, part.t, relu_bits=bits.t)
+    check("bn_bwd_reduce", part, dzg)
+    # depthwise strip kernels
+    for (hh, C) in [(32, 96), (16, 192), (8, 384), (4, 960)]:
+        x = nhwc_bf16(n, hh, hh, C, 78)
+        wt = torch.randn(C, 1, 3, 3, device="cuda", generator=g)
+        y = _Guarded((n, hh, hh, C), torch.bfloat16, 0.0)
+        ps, pq = _Guarded((ops.MAX_DW_STAT_ROWS, C), torch.float32, 0.0), _Guarded((ops.MAX_DW_STAT_ROWS, C), torch.float32, 0.0)
+        ops.dwconv_fprop(x, wt, y.t, C, 1, ps.t, pq.t)
+        dx = _Guarded((n, hh, hh, C), torch.bfloat16, 0.0)
+        ops.dwconv_dgrad(x, wt, dx.t, C, 1)
+        dw = _Guarded((C, 1, 3, 3), torch.float32, 0.0)
+        ops.dwconv_wgrad(x, x, dw.t, C, 1)
+        check(f"dw{(hh, C)}", y, ps, pq, dx, dw)
+    assert not bad, bad
