@@ -341,9 +341,256 @@ dw_strip_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, con
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Stride-2 variants of the strip kernels (models/mobilenetv2.py:20 with stride 2: three layers).
+// fprop / wgrad: a thread owns 4 channels of one OUTPUT column and walks T output rows; output row ho reads input
+// rows 2ho-1 .. 2ho+1, the last of which is the next output row's first: 6 loads per output instead of 9.
+//   MODE 0: fprop (+ BatchNorm partial sums)   MODE 2: wgrad
+// ------------------------------------------------------------------------------------------------
+template <int MODE, int T>
+__global__ void __launch_bounds__(256)
+dw_strip2_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, const float* __restrict__ wt,
+                 uint2* __restrict__ out, float* __restrict__ dw, int N, int H, int W, int C, int c_valid,
+                 float* __restrict__ part_sum, float* __restrict__ part_sq) {
+    pdl_trigger_ew();
+    pdl_wait();
+    extern __shared__ float red[];   // MODE 0: [rpi][2][C]; MODE 2: [rpi][9][C]
+    const int cq_n = C >> 2;
+    const int rpi = 256 / cq_n;
+    const int cq = threadIdx.x % cq_n, rl = threadIdx.x / cq_n;
+    const bool active = rl < rpi;
+    const int Ho = H >> 1, Wo = W >> 1;
+    const int strips = Ho / T;
+    const long long items = static_cast<long long>(N) * strips * Wo;
+
+    float w[9][4];       // MODE 0: weights; MODE 2: accumulators
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            if (MODE == 2) w[t][e] = 0.f;
+            else w[t][e] = (cq * 4 + e < c_valid) ? __ldg(wt + (cq * 4 + e) * 9 + t) : 0.f;
+        }
+    float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+    const uint2 zero = make_uint2(0u, 0u);
+
+    for (long long it = static_cast<long long>(blockIdx.x) * rpi + rl; active && it < items;
+         it += static_cast<long long>(gridDim.x) * rpi) {
+        const int wo = static_cast<int>(it % Wo);
+        const int st = static_cast<int>((it / Wo) % strips);
+        const long long n = it / (static_cast<long long>(Wo) * strips);
+        const int ho0 = st * T;
+        const bool left = wo > 0;
+        const uint2* base = in + ((n * H) * W + 2 * wo) * cq_n + cq;     // input pixel (row 0, col 2*wo)
+        const long long row_pitch = static_cast<long long>(W) * cq_n;
+        auto load_row = [&](int h, float (&r)[3][4]) {
+            uint2 a = zero, b = zero, c = zero;
+            if (h >= 0) {                        // h <= H-1 always (H even, h <= 2*Ho-1)
+                const uint2* p = base + h * row_pitch;
+                if (left) a = __ldg(p - cq_n);
+                b = __ldg(p);
+                c = __ldg(p + cq_n);             // column 2*wo+1 <= W-1
+            }
+            unpack4(a, r[0]); unpack4(b, r[1]); unpack4(c, r[2]);
+        };
+        float win[3][3][4];                      // rows 2ho-1, 2ho, 2ho+1
+        load_row(2 * ho0 - 1, win[0]);
+#pragma unroll
+        for (int i = 0; i < T; ++i) {
+            const int ho = ho0 + i;
+            load_row(2 * ho, win[1]);
+            load_row(2 * ho + 1, win[2]);
+            const long long opix = ((n * Ho + ho) * Wo + wo) * cq_n + cq;
+            if (MODE == 2) {
+                float g[4];
+                unpack4(__ldg(in2 + opix), g);
+#pragma unroll
+                for (int r = 0; r < 3; ++r)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) w[r * 3 + c][e] = fmaf(win[r][c][e], g[e], w[r * 3 + c][e]);
+            } else {
+                float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int r = 0; r < 3; ++r)
+#pragma unroll
+                    for (int c = 0; c < 3; ++c)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc[e] = fmaf(win[r][c][e], w[r * 3 + c][e], acc[e]);
+                uint2 o;
+                o.x = pack_bf16x2(acc[0], acc[1]);
+                o.y = pack_bf16x2(acc[2], acc[3]);
+                out[opix] = o;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    s1[e] += acc[e];
+                    s2[e] = fmaf(acc[e], acc[e], s2[e]);
+                }
+            }
+            // input row 2ho+1 is the next output row's top row
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) win[0][c][e] = win[2][c][e];
+        }
+    }
+    if (MODE == 0) {
+        if (part_sum == nullptr) return;
+        if (active) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                red[(rl * 2 + 0) * C + cq * 4 + e] = s1[e];
+                red[(rl * 2 + 1) * C + cq * 4 + e] = s2[e];
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 2 * C; i += 256) {
+            float s = 0.f;
+            for (int k = 0; k < rpi; ++k) s += red[k * 2 * C + i];
+            if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
+            else part_sq[static_cast<size_t>(blockIdx.x) * C + (i - C)] = s;
+        }
+    } else {
+        if (active) {
+#pragma unroll
+            for (int t = 0; t < 9; ++t)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) red[(rl * 9 + t) * C + cq * 4 + e] = w[t][e];
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 9 * C; i += 256) {
+            const int t = i / C, c = i - t * C;
+            if (c >= c_valid) continue;
+            float s = 0.f;
+            for (int k = 0; k < rpi; ++k) s += red[(k * 9 + t) * C + c];
+            atomicAdd(dw + c * 9 + t, s);
+        }
+    }
+}
+
+// Stride-2 dgrad: a thread owns 4 channels of one 2x2 block column of dx and walks T block rows. Block (i, j) =
+// dx[2i..2i+1][2j..2j+1] reads dy[i..i+1][j..j+1] — the 1 / 2 / 2 / 4 taps that reach each parity phase, 9 MACs
+// per block and channel, no divisions or modulo; dy row i+1 is the next block row's row i (2 loads per 4 outputs).
+template <int T>
+__global__ void __launch_bounds__(256)
+dw_strip2_dgrad_kernel(const uint2* __restrict__ dy, const float* __restrict__ wt, uint2* __restrict__ dx, int N,
+                       int H, int W, int C, int c_valid) {
+    pdl_trigger_ew();
+    pdl_wait();
+    const int cq_n = C >> 2;
+    const int rpi = 256 / cq_n;
+    const int cq = threadIdx.x % cq_n, rl = threadIdx.x / cq_n;
+    if (rl >= rpi) return;
+    const int Ho = H >> 1, Wo = W >> 1;
+    const int strips = Ho / T;
+    const long long items = static_cast<long long>(N) * strips * Wo;
+    float w[9][4];
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) w[t][e] = (cq * 4 + e < c_valid) ? __ldg(wt + (cq * 4 + e) * 9 + t) : 0.f;
+    const uint2 zero = make_uint2(0u, 0u);
+    for (long long it = static_cast<long long>(blockIdx.x) * rpi + rl; it < items;
+         it += static_cast<long long>(gridDim.x) * rpi) {
+        const int j = static_cast<int>(it % Wo);
+        const int st = static_cast<int>((it / Wo) % strips);
+        const long long n = it / (static_cast<long long>(Wo) * strips);
+        const int i0 = st * T;
+        const bool right = j + 1 < Wo;
+        const uint2* base = dy + ((n * Ho) * Wo + j) * cq_n + cq;
+        const long long row_pitch = static_cast<long long>(Wo) * cq_n;
+        auto load_row = [&](int i, float (&a)[4], float (&b)[4]) {      // dy[i][j], dy[i][j+1]
+            uint2 ua = zero, ub = zero;
+            if (i < Ho) {
+                const uint2* p = base + i * row_pitch;
+                ua = __ldg(p);
+                if (right) ub = __ldg(p + cq_n);
+            }
+            unpack4(ua, a); unpack4(ub, b);
+        };
+        float a0[4], b0[4], a1[4], b1[4];        // rows i (a0, b0) and i+1 (a1, b1); a = column j, b = column j+1
+        load_row(i0, a0, b0);
+#pragma unroll
+        for (int k = 0; k < T; ++k) {
+            const int i = i0 + k;
+            load_row(i + 1, a1, b1);
+            float o00[4], o01[4], o10[4], o11[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                o00[e] = a0[e] * w[4][e];                                                   // (r, s) = (1, 1)
+                o01[e] = fmaf(b0[e], w[3][e], a0[e] * w[5][e]);                             // (1, 0), (1, 2)
+                o10[e] = fmaf(a1[e], w[1][e], a0[e] * w[7][e]);                             // (0, 1), (2, 1)
+                o11[e] = fmaf(b1[e], w[0][e], fmaf(a1[e], w[2][e], fmaf(b0[e], w[6][e], a0[e] * w[8][e])));
+            }
+            uint2* q = dx + ((n * H + 2 * i) * W + 2 * j) * cq_n + cq;
+            uint2 u;
+            u.x = pack_bf16x2(o00[0], o00[1]); u.y = pack_bf16x2(o00[2], o00[3]); q[0] = u;
+            u.x = pack_bf16x2(o01[0], o01[1]); u.y = pack_bf16x2(o01[2], o01[3]); q[cq_n] = u;
+            q += static_cast<long long>(W) * cq_n;
+            u.x = pack_bf16x2(o10[0], o10[1]); u.y = pack_bf16x2(o10[2], o10[3]); q[0] = u;
+            u.x = pack_bf16x2(o11[0], o11[1]); u.y = pack_bf16x2(o11[2], o11[3]); q[cq_n] = u;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) { a0[e] = a1[e]; b0[e] = b1[e]; }
+        }
+    }
+}
+
 // stride-1 strip kernels: T = 8 rows (images of 8 pixels and more) or 4
 inline bool dw_strip_ok(int H, int W, int C, int stride) {
     return stride == 1 && (C & 3) == 0 && (C >> 2) <= 256 && H >= 4 && (H % 4) == 0 && W >= 2;
+}
+
+inline bool dw_strip2_ok(int H, int W, int C, int stride) {
+    return stride == 2 && (C & 3) == 0 && (C >> 2) <= 256 && !(H & 1) && !(W & 1) && (H >> 1) >= 4 && ((H >> 1) % 4) == 0;
+}
+
+// MODE 0 fprop, 1 dgrad, 2 wgrad (stride 2)
+template <int MODE>
+cudaError_t launch_dw_strip2(const void* in, const void* in2, const float* w, void* out, float* dw, int N, int H, int W,
+                             int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s) {
+    const int cq_n = C >> 2;
+    const int rpi = 256 / cq_n;
+    const int Ho = H >> 1, Wo = W >> 1;
+    const int T = (Ho % 8) == 0 ? 8 : 4;
+    const long long items = static_cast<long long>(N) * (Ho / T) * Wo;
+    long long blocks = (items + rpi - 1) / rpi;
+    const int cap = MODE == 2 ? 296 : 148 * 4;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    if (stat_rows != nullptr) *stat_rows = static_cast<int>(blocks);
+    const int grid = static_cast<int>(blocks);
+    if (MODE == 1) {
+        if (T == 8)
+            B2C_LAUNCH(dw_strip2_dgrad_kernel<8>, grid, 256, 0, s, static_cast<const uint2*>(in), w,
+                       static_cast<uint2*>(out), N, H, W, C, c_valid);
+        else
+            B2C_LAUNCH(dw_strip2_dgrad_kernel<4>, grid, 256, 0, s, static_cast<const uint2*>(in), w,
+                       static_cast<uint2*>(out), N, H, W, C, c_valid);
+        return cudaGetLastError();
+    }
+    constexpr int M = MODE == 1 ? 0 : MODE;
+    size_t smem = 0;
+    if (M == 0 && part_sum != nullptr) smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
+    if (M == 2) smem = static_cast<size_t>(rpi) * 9 * C * sizeof(float);
+    auto k8 = dw_strip2_kernel<M, 8>;
+    auto k4 = dw_strip2_kernel<M, 4>;
+    if (M == 2) {
+        static bool attr_done = false;
+        if (!attr_done) {
+            cudaError_t e = cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            if (e != cudaSuccess) return e;
+            attr_done = true;
+        }
+    }
+    if (T == 8)
+        B2C_LAUNCH(k8, grid, 256, smem, s, static_cast<const uint2*>(in), static_cast<const uint2*>(in2), w,
+                   static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum, part_sq);
+    else
+        B2C_LAUNCH(k4, grid, 256, smem, s, static_cast<const uint2*>(in), static_cast<const uint2*>(in2), w,
+                   static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum, part_sq);
+    return cudaGetLastError();
 }
 
 template <int MODE>
@@ -399,6 +646,8 @@ cudaError_t launch_dw_fprop(const void* x, const float* w, void* y, int N, int H
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     if (dw_strip_ok(H, W, C, stride))
         return launch_dw_strip<0>(x, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s);
+    if (dw_strip2_ok(H, W, C, stride))
+        return launch_dw_strip2<0>(x, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s);
     const int rpi = 256 / cvec;
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * (H / stride) * (W / stride), C);
     if (stat_rows != nullptr) *stat_rows = blocks;
@@ -414,6 +663,8 @@ cudaError_t launch_dw_dgrad(const void* dy, const float* w, void* dx, int N, int
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     if (dw_strip_ok(H, W, C, stride))
         return launch_dw_strip<1>(dy, nullptr, w, dx, nullptr, N, H, W, C, c_valid, nullptr, nullptr, nullptr, s);
+    if (dw_strip2_ok(H, W, C, stride))
+        return launch_dw_strip2<1>(dy, nullptr, w, dx, nullptr, N, H, W, C, c_valid, nullptr, nullptr, nullptr, s);
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * H * W, C);
     B2C_LAUNCH(dw_dgrad_kernel, blocks * 2 > 148 * 8 ? 148 * 8 : blocks * 2, 256, 0, s, 
         static_cast<const uint4*>(dy), w, static_cast<uint4*>(dx), N, H, W, C, c_valid, stride);
@@ -426,6 +677,8 @@ cudaError_t launch_dw_wgrad(const void* x, const void* dy, float* dw, int N, int
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     if (dw_strip_ok(H, W, C, stride))
         return launch_dw_strip<2>(x, dy, nullptr, nullptr, dw, N, H, W, C, c_valid, nullptr, nullptr, nullptr, s);
+    if (dw_strip2_ok(H, W, C, stride))
+        return launch_dw_strip2<2>(x, dy, nullptr, nullptr, dw, N, H, W, C, c_valid, nullptr, nullptr, nullptr, s);
     const int rpi = 256 / cvec;
     const size_t smem = static_cast<size_t>(rpi) * 9 * C * sizeof(float);      // 72 KB at most
     static bool attr_done = false;

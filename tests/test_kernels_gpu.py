@@ -648,4 +648,12 @@ def test_outputs_stay_inside_their_tensors(ops):
         dw = _Guarded((C, 1, 3, 3), torch.float32, 0.0)
         ops.dwconv_wgrad(x, x, dw.t, C, 1)
         check(f"dw{(hh, C)}", y, ps, pq, dx, dw)
+        if hh >= 8:                                   # stride-2 strip kernels
+            y2 = _Guarded((n, hh // 2, hh // 2, C), torch.bfloat16, 0.0)
+            ops.dwconv_fprop(x, wt, y2.t, C, 2, ps.t, pq.t)
+            dx2 = _Guarded((n, hh, hh, C), torch.bfloat16, 0.0)
+            ops.dwconv_dgrad(y2.t, wt, dx2.t, C, 2)
+            dw2 = _Guarded((C, 1, 3, 3), torch.float32, 0.0)
+            ops.dwconv_wgrad(x, y2.t, dw2.t, C, 2)
+            check(f"dw_s2{(hh, C)}", y2, ps, pq, dx2, dw2)
     assert not bad, bad
