@@ -288,6 +288,9 @@ FUSE_DGRAD_BN = os.environ.get("B2C_FUSE_DGRAD_BN", "1") != "0"
 RELU_BITS = os.environ.get("B2C_RELU_BITS", "1") != "0"
 # 0 = conv weights / gradients stored OIHW in the arenas (scattered 4-byte wgrad atomics)
 TCO_LAYOUT = os.environ.get("B2C_TCO_LAYOUT", "1") != "0"
+# 1 = weight-gradient kernels run on a side stream, concurrently with the data-gradient chain that does not
+# depend on them (fork after the BN backward that produced dy, join before the optimizer / the bucket's all-reduce)
+ASYNC_WGRAD = os.environ.get("B2C_ASYNC_WGRAD", "1") != "0"
 
 
 class ConvUnit:
@@ -315,6 +318,7 @@ class ConvUnit:
             self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout,
                                         flags=32 if (name + ".weight") in eng.tco else 0)
         self.eng_scratch = eng.wgrad_scratch
+        self.eng = eng
         self.wf = eng.wf_view(name)
         self.wd = None if stem else eng.wd_view(name)
         self.wd10 = None if stem else eng.wd10_view(name)
@@ -358,7 +362,7 @@ class ConvUnit:
                          relu_shift=self.shift if relu_from_y else None)
 
     def wgrad(self, dy):
-        ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch)
+        self.eng.run_side(lambda: ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch))
 
     def dgrad(self, dy, dx, add_src=None):
         ops.conv_dgrad(self.desc, dy, self.wd, dx, add_src)
@@ -399,6 +403,7 @@ class DwUnit:
         self.y = eng.new_act(N, self.Ho, self.Wo, self.cout)
         self.w = eng.param_view(name + ".weight")
         self.dw = eng.grad_view(name + ".weight")
+        self.eng = eng
         self.conv_bias = None
         _bn_views(self, eng, bn_name, self.cout)
 
@@ -406,7 +411,7 @@ class DwUnit:
         self.stat_rows = ops.dwconv_fprop(self.x, self.w, self.y, self.c_true, self.stride, eng.part_sum, eng.part_sq)
 
     def wgrad(self, dy):
-        ops.dwconv_wgrad(self.x, dy, self.dw, self.c_true, self.stride)
+        self.eng.run_side(lambda: ops.dwconv_wgrad(self.x, dy, self.dw, self.c_true, self.stride))
 
     def dgrad(self, dy, dx):
         ops.dwconv_dgrad(dy, self.w, dx, self.c_true, self.stride)
@@ -421,6 +426,7 @@ class Engine:
         self.spec, self.N, self.device = spec, batch, torch.device(device)
         self._layout_params(share_from)
         self._acts = []
+        self._side, self._side_dirty = None, False
         f32 = dict(device=self.device, dtype=torch.float32)
         stat_rows = ops.MAX_DW_STAT_ROWS if spec["family"] == "mobilenetv2" else ops.MAX_STAT_ROWS
         self.part_sum = torch.zeros(stat_rows, 2048, **f32)
@@ -1097,10 +1103,43 @@ class Engine:
             op(training)
         return self.logits
 
+    # ---- side stream for work off the critical path (weight gradients)
+    def run_side(self, fn):
+        """Run fn() on the side stream, ordered after everything enqueued on the current stream so far. Its results
+        may be used only after join_side() / side_marker(). Work submitted this way is serialised among itself (one
+        side stream), which is what the shared halo-wgrad scratch buffer needs."""
+        if not ASYNC_WGRAD:
+            fn()
+            return
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=self.device)
+        main = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._side.wait_event(ev)
+        with torch.cuda.stream(self._side):
+            fn()
+        self._side_dirty = True
+
+    def side_marker(self):
+        """Event after the side-stream work submitted so far (None if there is none outstanding)."""
+        if not self._side_dirty:
+            return None
+        ev = torch.cuda.Event()
+        ev.record(self._side)
+        return ev
+
+    def join_side(self):
+        ev = self.side_marker()
+        if ev is not None:
+            torch.cuda.current_stream().wait_event(ev)
+            self._side_dirty = False
+
     def backward(self):
         """Expects self.dlogits filled and self.G zeroed (conv wgrad accumulates)."""
         for op in self.bwd_ops:
             op()
+        self.join_side()
 
     def zero_grad(self):
         self.G.zero_()

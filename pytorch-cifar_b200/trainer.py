@@ -98,8 +98,12 @@ class Trainer:
                     ev = torch.cuda.Event()
                     ev.record(main)
                     self.comm_stream.wait_event(ev)
+                    side = eng.side_marker()              # weight gradients of this bucket run on the side stream
+                    if side is not None:
+                        self.comm_stream.wait_event(side)
                     with torch.cuda.stream(self.comm_stream):
                         dist.all_reduce(eng.G[a:b])      # sum; the mean's 1/world is applied inside sgd_step
+            eng.join_side()
             done = torch.cuda.Event()
             done.record(self.comm_stream)
             main.wait_event(done)
