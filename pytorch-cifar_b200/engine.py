@@ -298,7 +298,7 @@ class ConvUnit:
     Channel counts are the reference's; tensors are laid out with channels padded to multiples of 64
     (self.cin / self.cout are those layout widths, *_true the reference's)."""
 
-    def __init__(self, eng, name, bn_name, x, cin, cout, k, stride, H, W, stem=False):
+    def __init__(self, eng, name, bn_name, x, cin, cout, k, stride, H, W, stem=False, private_stats=False):
         N = eng.N
         self.name, self.bn_name = name, bn_name
         self.cin_true, self.cout_true = cin, cout
@@ -319,6 +319,13 @@ class ConvUnit:
                                         flags=32 if (name + ".weight") in eng.tco else 0)
         self.eng_scratch = eng.wgrad_scratch
         self.eng = eng
+        # BatchNorm partial-sum scratch: shared by the units of the main chain (used strictly one after the other);
+        # a shortcut conv that runs concurrently on the side stream gets its own
+        if private_stats:
+            self.ps = torch.zeros(ops.MAX_STAT_ROWS, _pad64(cout), device=eng.device)
+            self.pq = torch.zeros(ops.MAX_STAT_ROWS, _pad64(cout), device=eng.device)
+        else:
+            self.ps, self.pq = eng.part_sum, eng.part_sq
         self.wf = eng.wf_view(name)
         self.wd = None if stem else eng.wd_view(name)
         self.wd10 = None if stem else eng.wd10_view(name)
@@ -330,12 +337,12 @@ class ConvUnit:
 
     # ---- forward pieces
     def fprop(self, eng, stats=True, add_src=None):
-        ps, pq = (eng.part_sum, eng.part_sq) if stats else (None, None)
+        ps, pq = (self.ps, self.pq) if stats else (None, None)
         self.stat_rows = ops.conv_fprop(self.desc, self.x, self.wf, self.y, ps, pq, add_src=add_src)
 
     def bn_stats(self, eng, training):
         if training:
-            ops.bn_finalize(eng.part_sum, eng.part_sq, self.stat_rows, self.cout, self.rows, self.gamma, self.beta,
+            ops.bn_finalize(self.ps, self.pq, self.stat_rows, self.cout, self.rows, self.gamma, self.beta,
                             BN_EPS, BN_MOMENTUM, self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd,
                             conv_bias=getattr(self, "conv_bias", None))
         else:
@@ -404,6 +411,7 @@ class DwUnit:
         self.w = eng.param_view(name + ".weight")
         self.dw = eng.grad_view(name + ".weight")
         self.eng = eng
+        self.ps, self.pq = eng.part_sum, eng.part_sq
         self.conv_bias = None
         _bn_views(self, eng, bn_name, self.cout)
 
@@ -636,22 +644,23 @@ class Engine:
             c2 = ConvUnit(self, name + ".conv2", name + ".bn2", a1, cout, cout, 3, 1, Ho, Wo)
             cs = None
             if b["shortcut"]:
-                cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W)
+                cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W,
+                              private_stats=True)
             out = self.new_act(N, Ho, Wo, cout)
             bits = torch.zeros(out.numel() // 8, dtype=torch.uint8, device=self.device) if RELU_BITS else None
             self.units += [c1, c2] + ([cs] if cs else [])
             blocks.append((c1, a1, c2, cs, out, x, bits))
 
             def fwd_block(training, c1=c1, a1=a1, c2=c2, cs=cs, out=out, x=x, bits=bits):
+                if cs is not None:          # the shortcut branch (own statistics scratch) overlaps conv1 -> conv2
+                    self.run_side(lambda: (cs.fprop(self), cs.bn_stats(self, training)))
                 c1.fprop(self)
                 c1.bn_stats(self, training)
                 ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
-                if cs is not None:
-                    cs.fprop(self)
-                    cs.bn_stats(self, training)
                 c2.fprop(self)
                 c2.bn_stats(self, training)
                 if cs is not None:
+                    self.join_side()
                     ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, relu_bits=bits, res=cs.y,
                                      res_scale=cs.scale, res_shift=cs.shift)
                 else:
@@ -824,6 +833,7 @@ class Engine:
             """BatchNorm applied to tensor `y` produced by `producer` (whose epilogue emitted the statistics)."""
             def __init__(s, eng, bn_name, y, C, rows):
                 s.y, s.cout, s.rows = y, C, rows
+                s.ps, s.pq = eng.part_sum, eng.part_sq
                 _bn_views(s, eng, bn_name, C)
             stat_rows = 0
             bn_stats = ConvUnit.bn_stats
@@ -850,11 +860,13 @@ class Engine:
                 bn1.stat_rows = producer.stat_rows
                 bn1.bn_stats(self, training)
                 ops.bn_act_apply(x, bn1.scale, bn1.shift, a, bn1.rows, bn1.cout, relu=True)
-                if cs is not None:
-                    cs.fprop(self, stats=False)
+                if cs is not None:          # the shortcut conv overlaps conv1 on the side stream
+                    self.run_side(lambda: cs.fprop(self, stats=False))
                 c1.fprop(self)
                 c1.bn_stats(self, training)
                 ops.bn_act_apply(c1.y, c1.scale, c1.shift, a2, c1.rows, c1.cout, relu=True)
+                if cs is not None:
+                    self.join_side()
                 c2.fprop(self, stats=not last, add_src=(cs.y if cs is not None else x))
             F.append(fwd)
             x, H, W, producer = c2.y, Ho, Wo, c2
@@ -912,14 +924,16 @@ class Engine:
             Ho, Wo = H // s, W // s
             a2 = self.new_act(N, Ho, Wo, pl)
             c3 = ConvUnit(self, name + ".conv3", name + ".bn3", a2, pl, cout, 1, 1, Ho, Wo)
-            cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W) \
-                if b["shortcut"] else None
+            cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W,
+                          private_stats=True) if b["shortcut"] else None
             out = self.new_act(N, Ho, Wo, cout)
             bits = torch.zeros(out.numel() // 8, dtype=torch.uint8, device=self.device) if RELU_BITS else None
             self.units += [c1, c2, c3] + ([cs] if cs else [])
             blocks.append((c1, a1, c2, a2, c3, cs, out, x, bits))
 
             def fwd(training, c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, x=x, bits=bits):
+                if cs is not None:          # shortcut branch on the side stream (own statistics scratch)
+                    self.run_side(lambda: (cs.fprop(self), cs.bn_stats(self, training)))
                 c1.fprop(self)
                 c1.bn_stats(self, training)
                 ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
@@ -929,8 +943,7 @@ class Engine:
                 c3.fprop(self)
                 c3.bn_stats(self, training)
                 if cs is not None:
-                    cs.fprop(self)
-                    cs.bn_stats(self, training)
+                    self.join_side()
                     ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=cs.y,
                                      res_scale=cs.scale, res_shift=cs.shift, relu_bits=bits)
                 else:
@@ -1010,14 +1023,16 @@ class Engine:
             Ho, Wo = H // s, W // s
             a2 = self.new_act(N, Ho, Wo, dw.cout)
             c3 = ConvUnit(self, name + ".conv3", name + ".bn3", a2, planes, cout, 1, 1, Ho, Wo)
-            cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, 1, H, W) \
-                if b["shortcut"] else None
+            cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, 1, H, W,
+                          private_stats=True) if b["shortcut"] else None
             identity = s == 1 and cs is None
             out = self.new_act(N, Ho, Wo, c3.cout)
             self.units += [c1, dw, c3] + ([cs] if cs else [])
             blocks.append((c1, a1, dw, a2, c3, cs, identity, out, x))
 
             def fwd(training, c1=c1, a1=a1, dw=dw, a2=a2, c3=c3, cs=cs, identity=identity, out=out, x=x):
+                if cs is not None:          # shortcut branch on the side stream (own statistics scratch)
+                    self.run_side(lambda: (cs.fprop(self), cs.bn_stats(self, training)))
                 c1.fprop(self)
                 c1.bn_stats(self, training)
                 ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
@@ -1027,8 +1042,7 @@ class Engine:
                 c3.fprop(self)
                 c3.bn_stats(self, training)
                 if cs is not None:
-                    cs.fprop(self)
-                    cs.bn_stats(self, training)
+                    self.join_side()
                     ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=False, res=cs.y,
                                      res_scale=cs.scale, res_shift=cs.shift)
                 else:
