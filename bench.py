@@ -281,6 +281,11 @@ def run_product(args):
     _, wg_fl = conv_flops(wg_calls)
 
     def time_family(fam, reps=5):
+        # the recorded argument tuples end with the stream the call was issued on (weight gradients: the engine's
+        # side stream); for this measurement every launch goes to the bench stream, where the events are recorded
+        import ctypes
+        here = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        fam = [(n, tuple(a[:-1]) + (here,)) for n, a in fam]
         for n, a in fam:
             raw.raw(n)(*a)
         torch.cuda.synchronize()
