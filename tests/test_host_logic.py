@@ -69,3 +69,63 @@ def test_c_abi_exports_every_declared_symbol():
     assert l.b2c_version() >= 100
     assert b"not supported" in l.b2c_error_string(_lib.B2C_ERR_UNSUPPORTED)
     assert ctypes.sizeof(_lib.ConvDesc) == 52 and ctypes.sizeof(_lib.RepackEntry) == 48
+
+
+def test_spec_parameter_counts_match_the_reference():
+    """parameter totals of every supported family (the arenas are laid out from them)."""
+    want = {"resnet_spec": 11173962, "vgg_spec": 14728266, "preact_resnet_spec": 11171146,
+            "mobilenetv2_spec": 2296922, "resnet50_spec": 23520842}
+    for fn, n in want.items():
+        spec = getattr(engine, fn)()
+        assert sum(int(np.prod(s)) for s in spec["params"].values()) == n, fn
+        off, total = engine.param_offsets(spec)
+        # offsets are 16-byte aligned, in parameter order, non-overlapping
+        prev_end = 0
+        for name, (o, cnt, shape) in off.items():
+            assert o % 4 == 0 and o >= prev_end and cnt == int(np.prod(shape)), name
+            prev_end = o + cnt
+        assert total >= prev_end
+
+
+def test_c_abi_rejects_bad_arguments_without_touching_the_gpu():
+    """Error convention of include/b2c.h: every entry point validates before its first CUDA call, so these return
+    codes can be checked on a machine without a GPU. Nothing here launches a kernel."""
+    l = _lib.load()
+    fake = ctypes.c_void_p(0x10000)                     # aligned, never dereferenced on these paths
+    odd = ctypes.c_void_p(0x10008)                      # not 16-byte aligned
+    rows = ctypes.c_int(0)
+
+    def desc(**kw):
+        base = dict(n=4, h=32, w=32, cin=64, cout=64, ksize=3, stride=1, cin_valid=0, cout_valid=0, kflat_cin=0,
+                    block_n=0, max_ctas=0, flags=0)
+        base.update(kw)
+        return _lib.ConvDesc(*[base[f] for f, _ in _lib.ConvDesc._fields_])
+
+    raw = l.raw if hasattr(l, "raw") else (lambda name: getattr(l, name))
+    fprop, dgrad, wgrad = raw("b2c_conv_fprop"), raw("b2c_conv_dgrad"), raw("b2c_conv_wgrad")
+    U, A = _lib.B2C_ERR_UNSUPPORTED, _lib.B2C_ERR_ARG
+    assert fprop(None, fake, fake, fake, None, None, None, ctypes.byref(rows), None) == A
+    for bad in (dict(cin=48), dict(cout=96 + 8), dict(ksize=5), dict(stride=3), dict(stride=2, h=31)):
+        assert fprop(ctypes.byref(desc(**bad)), fake, fake, fake, None, None, None, ctypes.byref(rows), None) == U, bad
+    assert fprop(ctypes.byref(desc(block_n=96)), fake, fake, fake, None, None, None, ctypes.byref(rows), None) == A
+    assert fprop(ctypes.byref(desc()), None, fake, fake, None, None, None, ctypes.byref(rows), None) == A
+    assert fprop(ctypes.byref(desc()), odd, fake, fake, None, None, None, ctypes.byref(rows), None) == A
+    assert fprop(ctypes.byref(desc()), fake, fake, fake, None, fake, None, ctypes.byref(rows), None) == A   # sum w/o sq
+    assert dgrad(ctypes.byref(desc()), fake, fake, None, None, None) == A
+    assert wgrad(ctypes.byref(desc()), fake, None, fake, None, 0, None) == A
+    assert raw("b2c_conv_dgrad_with_shortcut")(ctypes.byref(desc()), fake, fake, fake, fake, None, None) == U  # s1
+    assert raw("b2c_conv_dgrad_bn")(ctypes.byref(desc()), fake, fake, fake, None, None, fake, fake, fake,
+                                    ctypes.byref(rows), None) == A
+    assert raw("b2c_sgd_step")(fake, fake, fake, 6, fake, None) == A                      # n % 4 != 0
+    assert raw("b2c_sgd_step")(fake, fake, fake, 0, fake, None) == 0                      # empty arena: no launch
+    assert raw("b2c_bn_finalize")(fake, fake, 0, 64, 1.0, fake, fake, None, 1e-5, 0.1, None, None, fake, fake, fake,
+                                  fake, None) == A                                        # rows < 1
+    assert raw("b2c_bn_bwd_partial_rows")(1 << 20, 64) == 148 * 4
+    assert raw("b2c_bn_bwd_partial_rows")(10, 64) == 1
+    assert raw("b2c_bn_bwd_partial_rows")(10, 12) == U
+    noalloc = raw("b2c_bn_bwd_stats_noalloc")
+    args = [fake, None, fake, None, 1024, 1024, 1024.0] + [fake] * 8 + [None]
+    assert noalloc(*args) == _lib.B2C_ERR_TOO_LARGE
+    for code, word in ((U, b"not supported"), (A, b"invalid argument"), (_lib.B2C_ERR_TOO_LARGE, b"exceeds"),
+                       (0, b"success")):
+        assert word in l.b2c_error_string(code)
