@@ -58,7 +58,9 @@ typedef struct B2cConvDesc {
                         bit 5: wgrad: dw is laid out [tap][cin_valid][cout_valid] instead of OIHW, which lets the
                                epilogue reduce 4 rows x 128 contiguous bytes per instruction;
                         bit 6: wgrad: keep the per-tap kernel where the row kernel (conv_wgrad_row.cu) would be
-                               chosen (measurement aid) */
+                               chosen (measurement aid);
+                        bit 7: fprop / stride-1 dgrad: CTA-pair kernel (tcgen05.mma.cta_group::2, conv_gemm2.cu)
+                               instead of the halo / per-tap kernels */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)

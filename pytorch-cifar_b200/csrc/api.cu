@@ -118,7 +118,7 @@ struct BnFuse {
 
 // 3x3 stride-1 convs on square 32 / 16 / 8 pixel images go to the halo-reuse kernel (conv_halo.cu).
 bool use_halo(const B2cConvDesc* d) {
-    if (d->flags & 1) return false;
+    if (d->flags & (1 | 128)) return false;
     if (d->ksize != 3 || d->stride != 1 || d->h != d->w) return false;
     return d->w == 32 || d->w == 16 || d->w == 8;
 }
@@ -257,9 +257,11 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     rc = p.a_split_w ? encode_nhwc_s2(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb)
                      : encode_nhwc(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
     if (rc) return rc;
-    rc = encode_2d(&mb, w_fprop, static_cast<long long>(taps) * d->cout, d->cin, bn);
+    const bool pair = (d->flags & 128) != 0;      // CTA-pair kernel (conv_gemm2.cu): each CTA loads half a weight tile
+    rc = encode_2d(&mb, w_fprop, static_cast<long long>(taps) * d->cout, d->cin, pair ? bn / 2 : bn);
     if (rc) return rc;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+    if (pair) return cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
     return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
 }
 
@@ -308,8 +310,9 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     }
 
     CUtensorMap ma, mb;
+    const bool pair = (d->flags & 128) != 0 && d->stride == 1 && dy_shortcut == nullptr;   // conv_gemm2.cu
     rc = encode_2d(&mb, w_dgrad, static_cast<long long>(taps + (dy_shortcut != nullptr ? 1 : 0)) * d->cin, d->cout,
-                   bn);
+                   pair ? bn / 2 : bn);
     if (rc) return rc;
 
     if (d->stride == 1) {
@@ -332,6 +335,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         }
         p.sy = p.sx = 1;
         single_phase(p);
+        if (pair) return cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, st));
         return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, st));
     }
 

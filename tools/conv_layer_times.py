@@ -51,6 +51,17 @@ for (hw, cin, cout, k, s) in shapes:
                 row[f"dgrad_{tag}_us"] = round(t, 1); row[f"dgrad_{tag}_tf"] = round(fl / t / 1e6, 0)
             except Exception as e:
                 row[f"err_{tag}"] = str(e)[:60]
+    for bn in ((0,) if cout < 256 and cin < 256 else (0, 128, 256)):      # CTA-pair kernel (flags bit 7)
+        dp = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=128, block_n=bn)
+        tag = f"pair{'_bn%d' % bn if bn else ''}"
+        try:
+            t = timeit(lambda: ops.conv_fprop(dp, x, wf, y, ps, pq))
+            row[f"fprop_{tag}_us"] = round(t, 1); row[f"fprop_{tag}_tf"] = round(fl / t / 1e6, 0)
+            if s == 1:
+                t = timeit(lambda: ops.conv_dgrad(dp, dy, wd, dx))
+                row[f"dgrad_{tag}_us"] = round(t, 1); row[f"dgrad_{tag}_tf"] = round(fl / t / 1e6, 0)
+        except Exception as e:
+            row[f"err_{tag}"] = str(e)[:60]
     d = ops.conv_desc(N, hw, hw, cin, cout, k, s)
     t = timeit(lambda: ops.conv_wgrad(d, x, dy, dw))
     row["wgrad_atomic_us"] = round(t, 1); row["wgrad_atomic_tf"] = round(fl / t / 1e6, 0)
