@@ -59,8 +59,8 @@ typedef struct B2cConvDesc {
                                epilogue reduce 4 rows x 128 contiguous bytes per instruction;
                         bit 6: wgrad: keep the per-tap kernel where the row kernel (conv_wgrad_row.cu) would be
                                chosen (measurement aid);
-                        bit 7: fprop / stride-1 dgrad: CTA-pair kernel (tcgen05.mma.cta_group::2, conv_gemm2.cu)
-                               instead of the halo / per-tap kernels */
+                        bit 7: fprop / stride-1 dgrad: CTA-pair kernels (tcgen05.mma.cta_group::2): conv_halo2.cu where
+                               the halo kernel would run, conv_gemm2.cu otherwise (or with bit 0) */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)

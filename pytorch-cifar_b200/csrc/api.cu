@@ -118,7 +118,7 @@ struct BnFuse {
 
 // 3x3 stride-1 convs on square 32 / 16 / 8 pixel images go to the halo-reuse kernel (conv_halo.cu).
 bool use_halo(const B2cConvDesc* d) {
-    if (d->flags & (1 | 128)) return false;
+    if (d->flags & 1) return false;
     if (d->ksize != 3 || d->stride != 1 || d->h != d->w) return false;
     return d->w == 32 || d->w == 16 || d->w == 8;
 }
@@ -159,9 +159,11 @@ int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w,
     int rc = p.mode == 0 ? encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 18, 1, 1)
                          : encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 8, 2, 1);
     if (rc) return rc;
-    rc = encode_2d(&mb, w, 9LL * gemm_n, act_c, bn);
+    const bool pair = (d->flags & 128) != 0;      // CTA-pair kernel (conv_halo2.cu): each CTA loads half a weight tile
+    rc = encode_2d(&mb, w, 9LL * gemm_n, act_c, pair ? bn / 2 : bn);
     if (rc) return rc;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
+    if (pair) return cuda_rc(b2c::launch_conv_halo2(bn, ma, mb, p, max_ctas, stat_rows, st));
     return cuda_rc(b2c::launch_conv_halo(bn, ma, mb, p, max_ctas, stat_rows, st));
 }
 

@@ -8,9 +8,7 @@
 // N = 128 (profiles/r1g_umma2_probe.log).
 //
 // Cross-CTA synchronisation (all mbarriers live at the same offsets in both CTAs):
-//   full[s]     local: this CTA's TMA bytes of stage s have landed
-//   pfull[s]    in the leader: the peer's stage s has landed (the peer's otherwise idle MMA warp relays its local
-//               full[s] with a remote mbarrier.arrive.release.cluster)
+//   full[s]     in the LEADER: both CTAs' TMA loads (cp.async.bulk.tensor.cta_group::2) signal their bytes there
 //   empty[s]    both CTAs, arrived by the leader's tcgen05.commit multicast: stage s has been consumed
 //   tfull[a]    both CTAs, commit multicast: accumulator a is complete (each CTA reads its own 128 rows from TMEM)
 //   tempty[a]   leader: its own epilogue warps drained accumulator a;  ptempty[a]: the peer's (remote arrive)
@@ -53,6 +51,37 @@ __device__ __forceinline__ void mbar_arrive_remote(uint64_t* bar, uint32_t targe
     uint32_t raddr;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_u32(bar)), "r"(target));
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(raddr) : "memory");
+}
+// TMA loads of a CTA pair: the data lands in THIS CTA's shared memory, the transaction bytes are signalled on the
+// barrier at the same offset in the LEADER CTA (rank 0), which the MMA issuer waits on — no relay through the peer.
+__device__ __forceinline__ uint32_t cluster_addr(const void* p, uint32_t rank) {
+    uint32_t raddr;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(raddr) : "r"(smem_u32(p)), "r"(rank));
+    return raddr;
+}
+__device__ __forceinline__ void tma2_load_4d(uint32_t dst_cluster, const CUtensorMap* m, uint32_t bar_cluster, int c0,
+                                             int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst_cluster),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void tma2_load_5d(uint32_t dst_cluster, const CUtensorMap* m, uint32_t bar_cluster, int c0,
+                                             int c1, int c2, int c3, int c4) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4, %5, %6, %7}], [%2];" ::"r"(dst_cluster),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+}
+__device__ __forceinline__ void tma2_load_2d(uint32_t dst_cluster, const CUtensorMap* m, uint32_t bar_cluster, int c0,
+                                             int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+        " [%0], [%1, {%3, %4}], [%2];" ::"r"(dst_cluster),
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster), "r"(c0), "r"(c1)
+        : "memory");
 }
 __device__ __forceinline__ void umma2_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                            uint32_t accumulate) {
@@ -157,13 +186,15 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
                 for (int kc = 0; kc < p.k_chunks; ++kc) {
                     mbar_wait(&empty[stage], phase ^ 1u, 51);
                     if (elect_one_sync()) {
-                        mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+                        // the leader's barrier collects both CTAs' bytes
+                        if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::kStageBytes);
                         uint8_t* sa = smem + stage * Cfg::kStageBytes;
+                        const uint32_t bar = cluster_addr(&full[stage], 0);
                         if (p.a_split_w)
-                            tma_load_5d(sa, &mapA0, &full[stage], kc * 64, cw & 1, cw >> 1, ch, n0);
+                            tma2_load_5d(cluster_addr(sa, rank), &mapA0, bar, kc * 64, cw & 1, cw >> 1, ch, n0);
                         else
-                            tma_load_4d(sa, &mapA0, &full[stage], kc * 64, cw, ch, n0);
-                        tma_load_2d(sa + kABytes, &mapB, &full[stage], kc * 64, brow);
+                            tma2_load_4d(cluster_addr(sa, rank), &mapA0, bar, kc * 64, cw, ch, n0);
+                        tma2_load_2d(cluster_addr(sa + kABytes, rank), &mapB, bar, kc * 64, brow);
                     }
                     __syncwarp();
                     if (++stage == Cfg::kStages) {
@@ -174,20 +205,7 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
             }
         }
     } else if (warp == 1 && rank == 1) {
-        // ------------------------------ peer: relay "my stage has landed" to the leader ----------
-        int stage = 0;
-        uint32_t phase = 0;
-        for (int tile = pair; tile < total_tiles; tile += num_pairs) {
-            for (int it = 0; it < k_iters; ++it) {
-                mbar_wait(&full[stage], phase, 52);
-                if (elect_one_sync()) mbar_arrive_remote(&pfull[stage], 0);
-                __syncwarp();
-                if (++stage == Cfg::kStages) {
-                    stage = 0;
-                    phase ^= 1u;
-                }
-            }
-        }
+        // the peer's MMA warp has nothing to do: its TMA loads signal the leader's barriers directly
     } else if (warp == 1) {
         // ------------------------------ leader: MMA issuer for the pair (M = 256) ----------------
         constexpr uint32_t idesc = make_idesc_bf16(2 * kBM, BN, 0, 0);
@@ -202,7 +220,6 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
             const uint32_t d = tmem_base + static_cast<uint32_t>(acc * BN);
             for (int it = 0; it < k_iters; ++it) {
                 mbar_wait(&full[stage], phase, 55);
-                mbar_wait(&pfull[stage], phase, 56);
                 tc_fence_after();
                 if (elect_one_sync()) {
                     const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);

@@ -291,6 +291,9 @@ TCO_LAYOUT = os.environ.get("B2C_TCO_LAYOUT", "1") != "0"
 # 1 = weight-gradient kernels run on a side stream, concurrently with the data-gradient chain that does not
 # depend on them (fork after the BN backward that produced dy, join before the optimizer / the bucket's all-reduce)
 ASYNC_WGRAD = os.environ.get("B2C_ASYNC_WGRAD", "1") != "0"
+# CTA-pair (tcgen05.mma.cta_group::2) fprop / dgrad kernels: "halo" = where the halo kernel runs (3x3 stride 1 on
+# 32/16/8-pixel images), "all" = the per-tap kernel's shapes too, "0" = single-CTA kernels everywhere
+CTA_PAIR = os.environ.get("B2C_CTA_PAIR", "all")
 
 
 class ConvUnit:
@@ -314,7 +317,9 @@ class ConvUnit:
             self.desc = ops.conv_desc(N, H, W, 64, cout_p, 1, 1)
             self.desc_w = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, cin_valid=27, kflat_cin=3, cout_valid=cout)
         else:
-            self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride)
+            halo_shape = k == 3 and stride == 1 and H == W and W in (32, 16, 8)
+            pair = CTA_PAIR == "all" or (CTA_PAIR == "halo" and halo_shape)
+            self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, flags=128 if pair else 0)
             self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout,
                                         flags=32 if (name + ".weight") in eng.tco else 0)
         self.eng_scratch = eng.wgrad_scratch

@@ -663,35 +663,37 @@ def test_outputs_stay_inside_their_tensors(ops):
                                    (2, 32, 32, 64, 64, 1, 1), (5, 4, 4, 512, 512, 3, 1), (3, 8, 8, 256, 256, 3, 1),
                                    (64, 8, 8, 128, 256, 3, 2), (300, 4, 4, 256, 256, 3, 1)])
 def test_conv_cta_pair_kernel(ops, shape):
-    """flags bit 7: the CTA-pair kernel (tcgen05.mma.cta_group::2, conv_gemm2.cu) against the single-CTA per-tap kernel
-    on the same operands: same K order and fp32 accumulation, so outputs and BatchNorm sums must agree to rounding
-    of the last bit; odd tile counts leave the peer CTA of the last pair without a tile."""
+    """flags bit 7: the CTA-pair kernels (tcgen05.mma.cta_group::2) against their single-CTA counterparts on the same
+    operands — conv_halo2.cu vs conv_halo.cu (flags 128 vs 0), conv_gemm2.cu vs conv_gemm.cu (flags 129 vs 1): same K
+    order and fp32 accumulation, so outputs and BatchNorm sums agree to the last bit's rounding; odd tile counts
+    leave the peer CTA of the last pair without a tile."""
     n, h, w, cin, cout, k, stride = shape
     ho, wo = h // stride, w // stride
     x = nhwc_bf16(n, h, w, cin, 81)
     wt = weight(cout, cin, k, 82)
     wf, wd = ops.pack_weight_fprop(wt), ops.pack_weight_dgrad(wt)
-    outs, sums = [], []
-    for flags in (1, 128):
-        y = torch.full((n, ho, wo, cout), float("nan"), device="cuda", dtype=torch.bfloat16)
-        ps, pq = torch.zeros(148, cout, device="cuda"), torch.zeros(148, cout, device="cuda")
-        rows = ops.conv_fprop(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=flags), x, wf, y, ps, pq)
-        torch.cuda.synchronize()
-        assert 1 <= rows <= 148
-        outs.append(y); sums.append((ps[:rows].double().sum(0), pq[:rows].double().sum(0)))
-    assert torch.isfinite(outs[1].float()).all()
-    assert rel_err(outs[1].float(), outs[0].float()) < 1e-5
-    assert rel_err(sums[1][0], sums[0][0]) < 1e-5 and rel_err(sums[1][1], sums[0][1]) < 1e-5
     ref = F.conv2d(to_nchw(x), wt.to(torch.bfloat16).float(), stride=stride, padding=k // 2)
-    assert rel_err(to_nchw(outs[1]), ref) < BF16_TOL
-    if stride == 1:
-        dy = nhwc_bf16(n, ho, wo, cout, 83)
-        add = nhwc_bf16(n, h, w, cin, 84)
-        dxs = []
-        for flags in (1, 128):
-            dx = torch.full((n, h, w, cin), float("nan"), device="cuda", dtype=torch.bfloat16)
-            ops.conv_dgrad(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=flags), dy, wd, dx, add)
+    dy = nhwc_bf16(n, ho, wo, cout, 83)
+    add = nhwc_bf16(n, h, w, cin, 84)
+    for single, pair in ((1, 129), (0, 128)):
+        outs, sums = [], []
+        for flags in (single, pair):
+            y = torch.full((n, ho, wo, cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+            ps, pq = torch.zeros(148, cout, device="cuda"), torch.zeros(148, cout, device="cuda")
+            rows = ops.conv_fprop(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=flags), x, wf, y, ps, pq)
             torch.cuda.synchronize()
-            dxs.append(dx)
-        assert torch.isfinite(dxs[1].float()).all()
-        assert rel_err(dxs[1].float(), dxs[0].float()) < 1e-5
+            assert 1 <= rows <= 148
+            outs.append(y); sums.append((ps[:rows].double().sum(0), pq[:rows].double().sum(0)))
+        assert torch.isfinite(outs[1].float()).all(), pair
+        assert rel_err(outs[1].float(), outs[0].float()) < 1e-5, pair
+        assert rel_err(sums[1][0], sums[0][0]) < 1e-5 and rel_err(sums[1][1], sums[0][1]) < 1e-5, pair
+        assert rel_err(to_nchw(outs[1]), ref) < BF16_TOL
+        if stride == 1:
+            dxs = []
+            for flags in (single, pair):
+                dx = torch.full((n, h, w, cin), float("nan"), device="cuda", dtype=torch.bfloat16)
+                ops.conv_dgrad(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=flags), dy, wd, dx, add)
+                torch.cuda.synchronize()
+                dxs.append(dx)
+            assert torch.isfinite(dxs[1].float()).all(), pair
+            assert rel_err(dxs[1].float(), dxs[0].float()) < 1e-5, pair
