@@ -311,9 +311,9 @@ def run_product(args):
     except Exception:
         pass
     tf = peaks["tf_sustained"]
-    roofline = {"bound": "tensor", "kernel": "conv_halo_kernel (3x3 stride-1 conv fprop + dgrad, halo reuse)",
+    roofline = {"bound": "tensor", "kernel": "conv_halo2_kernel (3x3 stride-1 conv fprop + dgrad, halo reuse, CTA pair / tcgen05.mma.cta_group::2)",
                 "achieved": achieved, "peak": tf, "unit": "TFLOP/s", "frac": achieved / tf,
-                "traffic": traffic, "traffic_source": "profiles/r1d_ncu_conv_halo_step.json (dram read+write, avg per launch)",
+                "traffic": traffic, "traffic_source": "profiles/r1d_ncu_conv_halo_step.json (dram read+write, avg per launch; captured on the single-CTA conv_halo_kernel, same tensors and tiles)",
                 "peak_source": peaks["source"] + " bf16_tflops_sustained",
                 "launches_per_step": halo_launches, "avg_launch_us": halo_ms * 1e3 / halo_launches,
                 "flop_per_launch_avg": halo_fl / halo_launches, "ms_per_step": halo_ms,
