@@ -60,7 +60,9 @@ typedef struct B2cConvDesc {
                         bit 6: wgrad: keep the per-tap kernel where the row kernel (conv_wgrad_row.cu) would be
                                chosen (measurement aid);
                         bit 7: fprop / stride-1 dgrad: CTA-pair kernels (tcgen05.mma.cta_group::2): conv_halo2.cu where
-                               the halo kernel would run, conv_gemm2.cu otherwise (or with bit 0) */
+                               the halo kernel would run, conv_gemm2.cu otherwise (or with bit 0); wgrad: the pair
+                               row kernel (conv_wgrad_row2.cu) where cin is a multiple of 256;
+                        bit 8: wgrad: the pair row kernel for any cin the row kernel takes (test aid) */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)

@@ -123,6 +123,9 @@ struct WgradRowParams {
 };
 cudaError_t launch_wgrad_row(const CUtensorMap& x, const CUtensorMap& dy, const WgradRowParams& p, int w16,
                              cudaStream_t stream);
+// CTA-pair version (conv_wgrad_row2.cu); the dY map's box holds ONE 64-channel slab
+cudaError_t launch_wgrad_row2(const CUtensorMap& x, const CUtensorMap& dy, const WgradRowParams& p, int w16,
+                              cudaStream_t stream);
 size_t wgrad_halo_scratch_floats(int cin, int cout, int splits);
 cudaError_t launch_wgrad_halo(const CUtensorMap& x, const CUtensorMap& dy, const WgradHaloParams& p, float* dw,
                               cudaStream_t stream);

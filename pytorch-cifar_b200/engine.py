@@ -321,7 +321,7 @@ class ConvUnit:
             pair = CTA_PAIR == "all" or (CTA_PAIR == "halo" and halo_shape)
             self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, flags=128 if pair else 0)
             self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout,
-                                        flags=32 if (name + ".weight") in eng.tco else 0)
+                                        flags=(32 | (128 if CTA_PAIR != "0" else 0)) if (name + ".weight") in eng.tco else 0)
         self.eng_scratch = eng.wgrad_scratch
         self.eng = eng
         # BatchNorm partial-sum scratch: shared by the units of the main chain (used strictly one after the other);

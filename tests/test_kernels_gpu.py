@@ -266,6 +266,11 @@ def test_conv_wgrad_tap_cin_cout_layout(ops, shape):
     ops.conv_wgrad(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=32 | 64), x, dy, dw2)
     torch.cuda.synchronize()
     assert rel_err(dw2.view(k, k, cin, cout).permute(3, 2, 0, 1), ref) < 2e-3
+    # ... and the CTA-pair row kernel (flags bit 7; odd unit counts leave the last pair's peer without rows)
+    dw3 = torch.zeros(k * k, cin, cout, device="cuda")
+    ops.conv_wgrad(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=32 | 128 | 256), x, dy, dw3)
+    torch.cuda.synchronize()
+    assert rel_err(dw3.view(k, k, cin, cout).permute(3, 2, 0, 1), ref) < 2e-3
 
 
 def test_repack_from_tap_cin_cout_master(ops):

@@ -73,6 +73,9 @@ for (hw, cin, cout, k, s) in shapes:
     dt2 = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=32 | 64)    # ... with the per-tap kernel
     t = timeit(lambda: ops.conv_wgrad(dt2, x, dy, dw, scratch=scratch))
     row["wgrad_tco_tap_us"] = round(t, 1)
+    dt3 = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=32 | 128)   # ... with the CTA-pair row kernel
+    t = timeit(lambda: ops.conv_wgrad(dt3, x, dy, dw, scratch=scratch))
+    row["wgrad_tco_pair_us"] = round(t, 1); row["wgrad_tco_pair_tf"] = round(fl / t / 1e6, 0)
     if os.environ.get("WGRAD_DEBUG"):      # epilogue cost: plain stores (8) / no stores (16) instead of atomics
         for fl_dbg in (8, 16):
             dd = ops.conv_desc(N, hw, hw, cin, cout, k, s, flags=1 | fl_dbg)
