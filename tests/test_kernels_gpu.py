@@ -625,7 +625,19 @@ def test_outputs_stay_inside_their_tensors(ops):
             dx2 = _Guarded((n, hh, hh, ci), torch.bfloat16, 0.0)
             ops.conv_dgrad_with_shortcut(d, dy, nhwc_bf16(n, ho, ho, co, 76), w10, dx2.t)
             check("dgrad_shortcut", dx2)
-        for flags in (0, 32, 32 | 64):
+        for pf in (128, 129):                          # CTA-pair kernels (halo / per-tap)
+            dp = ops.conv_desc(n, hh, hh, ci, co, k, s, flags=pf)
+            y2 = _Guarded((n, ho, ho, co), torch.bfloat16, 0.0)
+            ops.conv_fprop(dp, x, ops.pack_weight_fprop(wt), y2.t, ps.t, pq.t)
+            check(f"pair_fprop{(hh, ci, co, k, s, pf)}", y2, ps, pq)
+            if s == 1:
+                dx3 = _Guarded((n, hh, hh, ci), torch.bfloat16, 0.0)
+                ops.conv_dgrad(dp, dy, ops.pack_weight_dgrad(wt), dx3.t)
+                dz3 = _Guarded((n, hh, hh, ci), torch.bfloat16, 0.0)
+                part3 = _Guarded((148, 2, ci), torch.float32, 0.0)
+                ops.conv_dgrad_bn(dp, dy, ops.pack_weight_dgrad(wt), dz3.t, x, sc, sh, part3.t)
+                check(f"pair_dgrad{(hh, ci, co, k, s, pf)}", dx3, dz3, part3)
+        for flags in (0, 32, 32 | 64, 32 | 128 | 256):
             dw = _Guarded((co * ci * k * k,), torch.float32, 0.0)
             ops.conv_wgrad(ops.conv_desc(n, hh, hh, ci, co, k, s, flags=flags), x, dy, dw.t)
             check(f"wgrad{(hh, ci, co, k, s, flags)}", dw)
