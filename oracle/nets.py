@@ -79,11 +79,11 @@ def resnet_forward(x, params, buffers, training=True, num_blocks=RESNET18_BLOCKS
             name = f"layer{li + 1}.{bi}"
             xin = out
             o = tap(name + ".conv1", F.conv2d(xin, params[name + ".conv1.weight"], stride=s, padding=1))
-            o = F.relu(_bn(o, name + ".bn1", params, buffers, training))           # :47
+            o = tap(name + ".a1", F.relu(_bn(o, name + ".bn1", params, buffers, training)))   # :47
             o = tap(name + ".conv2", F.conv2d(o, params[name + ".conv2.weight"], padding=1))
             o = _bn(o, name + ".bn2", params, buffers, training)                   # :48
             if (name + ".shortcut.0.weight") in params:
-                sc = F.conv2d(xin, params[name + ".shortcut.0.weight"], stride=s)
+                sc = tap(name + ".shortcut.0", F.conv2d(xin, params[name + ".shortcut.0.weight"], stride=s))
                 sc = _bn(sc, name + ".shortcut.1", params, buffers, training)
             else:
                 sc = xin

@@ -15,11 +15,13 @@ PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py); anyt
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
 shadows class names across files and the reference tree may sit anywhere on sys.path.
 """
+import threading
+
 import torch
 import torch.nn as nn
 
 from . import ops
-from .engine import Engine, mobilenetv2_spec, preact_resnet_spec, resnet_spec, vgg_spec, VGG_CFG
+from .engine import Engine, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, resnet_spec, vgg_spec, VGG_CFG
 
 
 def _is(m, name):
@@ -73,11 +75,30 @@ class _PlanFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dlogits):
-        eng = ctx.eng
+        eng, state = ctx.eng, ctx.state
         eng.dlogits.copy_(dlogits)
+        # The tensors returned below are views of the gradient arena G. When a parameter has no .grad yet,
+        # AccumulateGrad adopts the view as .grad (no copy) — the fast path, and what zero_grad(set_to_none=True)
+        # (main.py:101) gives every step. If a .grad that ALIASES G survives into this backward
+        # (zero_grad(set_to_none=False), p.grad.zero_(), gradient accumulation, two backwards before a step),
+        # recomputing into G would wipe it and AccumulateGrad's `.grad += view` would then add the new gradient
+        # to itself. In that case the new gradient is computed in G, moved to a private copy, G is restored, and
+        # autograd accumulates the copy into the surviving .grad (= G) as usual.
+        g_store = eng.G.untyped_storage().data_ptr()
+        aliased = any(p.grad is not None and p.grad.untyped_storage().data_ptr() == g_store for p in state.params)
+        keep = eng.G.clone() if aliased else None
         eng.zero_grad()
-        eng.backward()
-        grads = [eng.grad_view(name) for name in ctx.state.param_names]
+        if state.ddp is not None:
+            d = state.ddp
+            eng.backward_allreduce(d["buckets"], d["ready_after"], d["comm_stream"], group=d["group"], average=True)
+        else:
+            eng.backward()
+        if aliased:
+            fresh = eng.G.clone()
+            eng.G.copy_(keep)
+            grads = [eng._arena_view(fresh, name) for name in state.param_names]
+        else:
+            grads = [eng.grad_view(name) for name in state.param_names]
         return (None, None, *grads)
 
 
@@ -92,16 +113,21 @@ class _State:
             raise NotImplementedError(f"accelerate: parameter names do not match the reference layout: {missing[:3]}")
         self.params = [self.named[n] for n in self.param_names]
         self.nbt = [b for n, b in net.named_buffers() if n.endswith("num_batches_tracked")]
-        self.base = None
+        self.ddp = None                      # set by attach_ddp(): gradient buckets are all-reduced inside backward
+        self.lock = threading.Lock()         # one forward at a time: the plan's buffers are not re-entrant
+        self.device = self.params[0].device
+        # The arenas exist from here on (a minimal plan owns them; per-batch-size plans share them), and the
+        # module's parameters / BN buffers are views of them BEFORE anything else looks at the module — in
+        # particular DistributedDataParallel's constructor (main_dist.py:141-144), whose Reducer records parameter
+        # strides and broadcasts parameter storage.
+        self.base = Engine(spec, 2, self.device)
+        self.engines[2] = self.base
+        self._adopt(self.base)
 
     def engine_for(self, batch):
         eng = self.engines.get(batch)
         if eng is None:
-            dev = self.params[0].device
-            eng = Engine(self.spec, batch, dev, share_from=self.base)
-            if self.base is None:
-                self.base = eng
-                self._adopt(eng)
+            eng = Engine(self.spec, batch, self.device, share_from=self.base)
             self.engines[batch] = eng
         return eng
 
@@ -134,10 +160,23 @@ def accelerate(net):
     def forward(x):
         if x.dim() != 4 or tuple(x.shape[1:]) != (3, 32, 32):
             raise ValueError(f"accelerate: expected [N,3,32,32] input, got {tuple(x.shape)}")
-        if torch.is_grad_enabled() and net.training:
-            return _PlanFn.apply(state, x, *state.params)
-        with torch.no_grad():
-            return _PlanFn.forward(_Ctx(), state, x)
+        if x.device != state.device:
+            raise RuntimeError(
+                f"accelerate: input on {x.device} but the network's arenas live on {state.device}. An accelerated "
+                "network is bound to ONE GPU: nn.DataParallel over several GPUs (main.py:73-75, main_dist.py without "
+                "--dist) replicates the module and would drive this plan from every replica thread. Run with one "
+                "visible GPU (CUDA_VISIBLE_DEVICES=0) or use DistributedDataParallel, one process per GPU "
+                "(main_dist.py --dist).")
+        if not state.lock.acquire(blocking=False):
+            raise RuntimeError("accelerate: forward() re-entered from another thread (nn.DataParallel replicas?); "
+                               "the kernel plan owns one set of buffers and runs one forward at a time")
+        try:
+            if torch.is_grad_enabled() and net.training:
+                return _PlanFn.apply(state, x, *state.params)
+            with torch.no_grad():
+                return _PlanFn.forward(_Ctx(), state, x)
+        finally:
+            state.lock.release()
     net.forward = forward
     net._b2c_state = state
     return net
@@ -146,6 +185,37 @@ def accelerate(net):
 class _Ctx:
     """Stand-in ctx for the no-grad path."""
     pass
+
+
+def _ddp_passthrough_hook(_state, bucket):
+    """DDP communication hook of an attached network: the bucket already holds averaged gradients (they were
+    all-reduced as arena buckets while backward was still running), so the Reducer has nothing left to send."""
+    fut = torch.futures.Future()
+    fut.set_result(bucket.buffer())
+    return fut
+
+
+def attach_ddp(ddp_net, bucket_bytes=25 * 2 ** 20):
+    """Call on `DistributedDataParallel(accelerate(net), device_ids=[gpu])` (main_dist.py:141-144). Without it
+    DDP works as for any module, but the whole network is ONE autograd node, so the Reducer sees every gradient
+    at the same instant — at the end of backward — and its all-reduce overlaps nothing. After attach_ddp the
+    gradient arena is all-reduced (NCCL average over ddp_net.process_group) in buckets on a side stream from
+    INSIDE the backward plan, each bucket as soon as its last weight gradient is enqueued (what the Reducer does
+    for a layer-by-layer autograd graph), and a communication hook tells the Reducer the buckets are done.
+    Returns ddp_net."""
+    import torch.distributed as dist
+    net = ddp_net.module
+    state = getattr(net, "_b2c_state", None)
+    if state is None:
+        raise ValueError("attach_ddp needs DistributedDataParallel around a network returned by accelerate()")
+    group = ddp_net.process_group
+    if dist.get_backend(group) != "nccl":
+        raise RuntimeError("attach_ddp: the process group must use the nccl backend")
+    buckets, ready_after = plan_grad_buckets(state.spec, bucket_bytes)
+    state.ddp = dict(group=group, buckets=buckets, ready_after=ready_after,
+                     comm_stream=torch.cuda.Stream(device=state.device))
+    ddp_net.register_comm_hook(None, _ddp_passthrough_hook)
+    return ddp_net
 
 
 class FusedSGD(torch.optim.Optimizer):

@@ -169,10 +169,15 @@ int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w,
 
 // GEMM N tile: the widest tile that still gives every SM work. tcgen05.mma reads both operands from shared
 // memory, so N = 256 halves the operand bytes per FLOP of N = 128 (measured +20-25 % on the 512-channel layers).
-int pick_bn(int requested, int n_dim, long long m_tiles) {
+// `cap` is the widest tile the kernel family takes for this layer (the halo-reuse kernels keep N <= 128 up to 256
+// channels). When even N = 128 leaves most SMs without a tile — the 4x4 / 8x8 layers at 128 images per GPU, the
+// reference's own per-GPU batch at 8 GPUs (main_dist.py:111): 16 pixel tiles x 4 = 64 tiles on 148 SMs — N = 64
+// doubles the tile count; a CTA pair still runs N = 64 MMAs at 74 % of the tensor peak (profiles/r1g_umma2_probe.log),
+// which beats idle SMs.
+int pick_bn(int requested, int n_dim, int cap, long long m_tiles) {
     if (requested != 0) return requested;
-    if (n_dim % 256 == 0 && m_tiles * (n_dim / 256) >= 120) return 256;
-    if (n_dim % 128 == 0) return 128;
+    if (cap >= 256 && n_dim % 256 == 0 && m_tiles * (n_dim / 256) >= 120) return 256;
+    if (n_dim % 128 == 0 && (m_tiles * (n_dim / 128) >= 100 || m_tiles * (n_dim / 64) <= 16)) return 128;
     return 64;
 }
 
@@ -216,8 +221,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     if (!grid_tiles(ho, wo, 128)) return B2C_ERR_UNSUPPORTED;
     const long long m_tiles = (static_cast<long long>(d->n) * ho * wo + 127) / 128;
     const bool halo = use_halo(d);
-    const int bn = pick_bn(d->block_n, halo && d->cout <= 256 && d->block_n == 0 ? (d->cout % 128 == 0 ? 128 : 64) : d->cout,
-                           m_tiles);
+    const int bn = pick_bn(d->block_n, d->cout, halo && d->cout <= 256 ? 128 : 256, m_tiles);
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
     const int taps = d->ksize * d->ksize;
     if (halo)
@@ -277,8 +281,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     // GEMM: rows = dx pixels (per output phase for stride 2), N = cin, K = cout
     const long long m_tiles = (static_cast<long long>(d->n) * (d->stride == 1 ? d->h * d->w : ho * wo) + 127) / 128;
     const bool halo = use_halo(d);
-    const int bn = pick_bn(d->block_n, halo && d->cin <= 256 && d->block_n == 0 ? (d->cin % 128 == 0 ? 128 : 64) : d->cin,
-                           m_tiles);
+    const int bn = pick_bn(d->block_n, d->cin, halo && d->cin <= 256 ? 128 : 256, m_tiles);
     if (d->cin % bn) return B2C_ERR_UNSUPPORTED;
     const int taps = d->ksize * d->ksize;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
@@ -498,7 +501,7 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
         if (pair) return cuda_rc(b2c::launch_wgrad_row2(mx, mdy, rp, w16 ? 1 : 0, as_stream(stream)));
         return cuda_rc(b2c::launch_wgrad_row(mx, mdy, rp, w16 ? 1 : 0, as_stream(stream)));
     }
-    const int bn = pick_bn(d->block_n, d->cout, 1 << 20);
+    const int bn = pick_bn(d->block_n, d->cout, 256, 1 << 20);
     const int kpx = (bn <= 128 && grid_tiles(ho, wo, 128)) ? 128 : 64;     // pixels per k-step
     if (!grid_tiles(ho, wo, kpx)) return B2C_ERR_UNSUPPORTED;
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;

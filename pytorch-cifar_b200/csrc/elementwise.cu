@@ -894,10 +894,14 @@ cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* 
     return cudaGetLastError();
 }
 
+// Upper bound of the partial rows bn_bwd_reduce writes (= its grid): one constant shared by the grid cap below and by
+// the fixed scratch of the no-allocation entry point, so raising one cannot silently overrun the other.
+constexpr int kBnBwdMaxPartialRows = 148 * 4;
+
 int bn_bwd_partial_rows(long long rows, int C) {
     const int rpi = 256 / (C >> 3);
     long long blocks = (rows + rpi - 1) / rpi;
-    if (blocks > 148 * 4) blocks = 148 * 4;
+    if (blocks > kBnBwdMaxPartialRows) blocks = kBnBwdMaxPartialRows;
     if (blocks < 1) blocks = 1;
     return static_cast<int>(blocks);
 }
@@ -1055,7 +1059,7 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
 // replayed concurrently) share the array and race; callers serialise them.
 // ------------------------------------------------------------------------------------------------
 constexpr int kNoAllocMaxChannels = 512;
-constexpr int kNoAllocMaxRows = 148 * 4;
+constexpr int kNoAllocMaxRows = kBnBwdMaxPartialRows;
 static __device__ __align__(256) float g_noalloc_partial[kNoAllocMaxRows * 2 * kNoAllocMaxChannels];
 
 int bn_bwd_noalloc_max_channels() { return kNoAllocMaxChannels; }
@@ -1090,7 +1094,8 @@ cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const
     float* scratch = nullptr;
     cudaError_t e = noalloc_scratch(&scratch);
     if (e != cudaSuccess) return e;
-    const int prow = bn_bwd_partial_rows(rows, C);               // <= kNoAllocMaxRows by construction
+    const int prow = bn_bwd_partial_rows(rows, C);               // capped at kBnBwdMaxPartialRows == kNoAllocMaxRows
+    if (prow > kNoAllocMaxRows) return cudaErrorInvalidValue;    // never with the shared constant; guards a future edit
     e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, nullptr, nullptr, nullptr, s);
     if (e != cudaSuccess) return e;
     return launch_bn_bwd_finalize(scratch, prow, C, count, gamma, mean, rstd, dgamma, dbeta, coefA, coefB, coefC, s);

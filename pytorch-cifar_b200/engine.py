@@ -238,6 +238,40 @@ def plan_grad_buckets(spec, bucket_bytes):
     return buckets, ready_after
 
 
+def init_params(spec, seed=0):
+    """Seeded initial parameters and BatchNorm buffers of `spec`, equal bit for bit to
+    `torch.manual_seed(seed); net = <reference constructor>()` (e.g. models/resnet.py:143-144): the reference's
+    constructors create their layers in `net.parameters()` order and each layer draws from torch's global CPU
+    generator in nn.Conv2d / nn.Linear.reset_parameters (kaiming_uniform_(a=sqrt(5)) for the weight, then
+    U(-1/sqrt(fan_in), 1/sqrt(fan_in)) for a bias); BatchNorm draws nothing (weight 1, bias 0, running_var 1).
+    Returns (params, buffers): OrderedDicts of CPU fp32 tensors keyed and shaped like the reference's state_dict
+    (without num_batches_tracked)."""
+    import math
+    torch.manual_seed(seed)
+    params = OrderedDict()
+    shapes = spec["params"]
+    for name, shape in shapes.items():
+        if name.endswith(".weight") and len(shape) >= 2:
+            w = torch.empty(*shape)
+            torch.nn.init.kaiming_uniform_(w, a=math.sqrt(5))
+            params[name] = w
+        elif name.endswith(".weight"):
+            params[name] = torch.ones(*shape)
+        else:                                              # a bias: conv / linear (drawn) or BatchNorm (zero)
+            wshape = shapes[name[:-len("bias")] + "weight"]
+            if len(wshape) >= 2:
+                fan_in = 1
+                for d in wshape[1:]:
+                    fan_in *= d
+                bound = 1.0 / math.sqrt(fan_in)
+                params[name] = torch.empty(*shape).uniform_(-bound, bound)
+            else:
+                params[name] = torch.zeros(*shape)
+    buffers = OrderedDict((name, torch.ones(*shape) if name.endswith("running_var") else torch.zeros(*shape))
+                          for name, shape in spec["buffers"].items())
+    return params, buffers
+
+
 def _bn_views(u, eng, bn_name, C):
     """Padded-width views of a BatchNorm's parameters / statistics for the kernels."""
     u.gamma, u.beta = eng.param_vec(bn_name + ".weight", C), eng.param_vec(bn_name + ".bias", C)
@@ -1159,6 +1193,34 @@ class Engine:
         for op in self.bwd_ops:
             op()
         self.join_side()
+
+    def backward_allreduce(self, buckets, ready_after, comm_stream, group=None, average=False):
+        """backward() with the DDP Reducer's job interleaved (main_dist.py:141-144): as soon as the backward op
+        that completes a bucket of the gradient arena has been enqueued, that bucket is all-reduced with NCCL on
+        `comm_stream` while the remaining backward kernels keep running; returns after making the current stream
+        wait for the last bucket. buckets / ready_after come from plan_grad_buckets(). average=False leaves the
+        SUM in G (the trainer folds 1/world into its SGD kernel); True makes NCCL average, as DDP hands .grad
+        to a torch optimizer."""
+        import torch.distributed as dist
+        main = torch.cuda.current_stream()
+        op_kind = dist.ReduceOp.AVG if average else dist.ReduceOp.SUM
+        for pos, op in enumerate(self.bwd_ops):
+            op()
+            bi = ready_after.get(pos)
+            if bi is not None:
+                a, b = buckets[bi]
+                ev = torch.cuda.Event()
+                ev.record(main)
+                comm_stream.wait_event(ev)
+                side = self.side_marker()              # weight gradients of this bucket run on the side stream
+                if side is not None:
+                    comm_stream.wait_event(side)
+                with torch.cuda.stream(comm_stream):
+                    dist.all_reduce(self.G[a:b], op=op_kind, group=group)
+        self.join_side()
+        done = torch.cuda.Event()
+        done.record(comm_stream)
+        main.wait_event(done)
 
     def zero_grad(self):
         self.G.zero_()

@@ -24,7 +24,10 @@ class Trainer:
         self.eng = Engine(spec, batch, device)
         self.K = spec["num_classes"]
         dev = self.device
-        self.hyper_host = torch.tensor([lr, momentum, weight_decay, 1.0 / world, 1.0], dtype=torch.float32).pin_memory()
+        # {lr, momentum, weight_decay, 1/world, first_step}: host values in pageable memory; every update is a
+        # blocking 20-byte copy of a private snapshot, so a value written here can never reach steps that were
+        # enqueued earlier (an async copy from one shared pinned buffer could)
+        self.hyper_host = torch.tensor([lr, momentum, weight_decay, 1.0 / world, 1.0], dtype=torch.float32)
         self.hyper = self.hyper_host.to(dev)
         self.idx_dev = torch.zeros(batch, dtype=torch.int64, device=dev)
         self.ijf_dev = torch.zeros(batch, 3, dtype=torch.int8, device=dev)
@@ -47,7 +50,11 @@ class Trainer:
         self._ring_events = [None] * self._ring
         self._loss_host = torch.zeros(1, dtype=torch.float32).pin_memory()
         self.use_graph = use_graph
-        self.graph = None
+        # launch plans by batch size: the full batch, plus one per ragged last batch met so far (the reference's
+        # loaders keep it: drop_last=False, 50000 = 390*128 + 80, main.py:45; 6250 = 48*128 + 106 per rank,
+        # main_dist.py:111). A tail plan shares every parameter / gradient / momentum / BN-buffer arena.
+        self._main = dict(eng=self.eng, idx=self.idx_dev, ijf=self.ijf_dev, tgt=self.target, graph=None)
+        self._plans = {batch: self._main}
         self.steps_done = 0
         self.launches_per_step = None
         self.comm_stream = torch.cuda.Stream(device=dev) if world > 1 else None
@@ -68,9 +75,13 @@ class Trainer:
         self.data = t.contiguous().to(self.device)
         self.labels_host = np.asarray(labels, dtype=np.int64)
 
+    def _push_hyper(self):
+        self.hyper.copy_(self.hyper_host.clone(), non_blocking=False)
+
     def set_lr(self, lr):
+        """Learning rate for the steps issued from now on (the scheduler stays on the host, main.py:89,154)."""
         self.hyper_host[0] = lr
-        self.hyper.copy_(self.hyper_host, non_blocking=True)
+        self._push_hyper()
 
     # ------------------------------------------------------------------ gradient buckets (DDP)
     def _plan_buckets(self):
@@ -79,92 +90,111 @@ class Trainer:
         return buckets
 
     # ------------------------------------------------------------------ one step
-    def _launch_step(self):
-        eng = self.eng
-        ops.augment_im2col(self.data, self.idx_dev, self.ijf_dev, eng.x0)
+    def _forward_loss(self, pl=None):
+        pl = pl or self._main
+        eng = pl["eng"]
+        ops.augment_im2col(self.data, pl["idx"], pl["ijf"], eng.x0)
         eng.zero_grad()
         eng.forward(True)
-        ops.ce_loss(eng.logits, self.target, self.N, self.K, eng.dlogits, self.loss, self.correct)
+        ops.ce_loss(eng.logits, pl["tgt"], eng.N, self.K, eng.dlogits, self.loss, self.correct)
+
+    def _backward_reduce(self, pl=None):
+        """loss.backward() including DDP's gradient all-reduce; leaves the SUM over ranks in the arena."""
+        eng = (pl or self._main)["eng"]
         if self.world == 1:
             eng.backward()
         else:
-            import torch.distributed as dist
-            main = torch.cuda.current_stream()
-            for pos, op in enumerate(eng.bwd_ops):
-                op()
-                bi = self._bucket_ready_after.get(pos)
-                if bi is not None:
-                    a, b = self._buckets[bi]
-                    ev = torch.cuda.Event()
-                    ev.record(main)
-                    self.comm_stream.wait_event(ev)
-                    side = eng.side_marker()              # weight gradients of this bucket run on the side stream
-                    if side is not None:
-                        self.comm_stream.wait_event(side)
-                    with torch.cuda.stream(self.comm_stream):
-                        dist.all_reduce(eng.G[a:b])      # sum; the mean's 1/world is applied inside sgd_step
-            eng.join_side()
-            done = torch.cuda.Event()
-            done.record(self.comm_stream)
-            main.wait_event(done)
-        ops.sgd_step(eng.P, eng.G, eng.M, self.hyper)
+            eng.backward_allreduce(self._buckets, self._bucket_ready_after, self.comm_stream)
+
+    def _optimizer_step(self, pl=None):
+        eng = (pl or self._main)["eng"]
+        ops.sgd_step(eng.P, eng.G, eng.M, self.hyper)      # hyper[3] = 1/world: DDP's mean
         eng.repack()
 
+    def _launch_step(self, pl=None):
+        self._forward_loss(pl)
+        self._backward_reduce(pl)
+        self._optimizer_step(pl)
+
+    def _plan_for(self, n):
+        """The launch plan for a batch of n <= N samples (built on first use)."""
+        pl = self._plans.get(n)
+        if pl is None:
+            if not (0 < n < self.N):
+                raise ValueError(f"batch of {n} samples: the trainer was built for {self.N} (smaller tails are allowed)")
+            dev = self.device
+            pl = dict(eng=Engine(self.eng.spec, n, dev, share_from=self.eng),
+                      idx=torch.arange(n, dtype=torch.int64, device=dev),
+                      ijf=torch.zeros(n, 3, dtype=torch.int8, device=dev),
+                      tgt=torch.zeros(n, dtype=torch.int64, device=dev), graph=None, eager_first=True)
+            self._plans[n] = pl
+        return pl
+
     def _stage_inputs(self, idx, ijf, targets, images=None):
+        n = len(ijf)
+        pl = self._plan_for(n)
+        if len(targets) != n or (idx is not None and len(idx) != n) or (images is not None and len(images) != n):
+            raise ValueError("idx / ijf / targets / images must have the same length")
         s = self._slot
         self._slot = (s + 1) % self._ring
         if self._ring_events[s] is not None:
             self._ring_events[s].synchronize()
-        n = self.N
-        self._pin_ijf[s].numpy()[...] = ijf
-        self._pin_tgt[s].numpy()[...] = targets
-        self.ijf_dev.copy_(self._pin_ijf[s], non_blocking=True)
-        self.target.copy_(self._pin_tgt[s], non_blocking=True)
+        self._pin_ijf[s].numpy()[:n] = ijf
+        self._pin_tgt[s].numpy()[:n] = targets
+        pl["ijf"].copy_(self._pin_ijf[s][:n], non_blocking=True)
+        pl["tgt"].copy_(self._pin_tgt[s][:n], non_blocking=True)
         if images is not None:
             if self._pin_img is None:
-                self._pin_img = [torch.zeros(n, 32, 32, 3, dtype=torch.uint8).pin_memory() for _ in range(self._ring)]
-            self._pin_img[s].numpy()[...] = images
-            self.data.copy_(self._pin_img[s], non_blocking=True)
+                self._pin_img = [torch.zeros(self.N, 32, 32, 3, dtype=torch.uint8).pin_memory()
+                                 for _ in range(self._ring)]
+            self._pin_img[s].numpy()[:n] = images
+            self.data[:n].copy_(self._pin_img[s][:n], non_blocking=True)
         else:
-            self._pin_idx[s].numpy()[...] = idx
-            self.idx_dev.copy_(self._pin_idx[s], non_blocking=True)
+            self._pin_idx[s].numpy()[:n] = idx
+            pl["idx"].copy_(self._pin_idx[s][:n], non_blocking=True)
         ev = torch.cuda.Event()
         ev.record()
         self._ring_events[s] = ev
+        return pl
 
-    def _run(self):
-        if not self.use_graph:
-            self._launch_step()
+    @property
+    def graph(self):
+        return self._main["graph"]
+
+    def _run(self, pl=None):
+        pl = pl or self._main
+        if not self.use_graph or pl.get("eager_first"):
+            pl["eager_first"] = False        # a tail plan's first step runs eagerly (kernel attributes), then it is captured
+            self._launch_step(pl)
         else:
-            if self.graph is None:
-                self._capture()
-            self.graph.replay()
+            if pl["graph"] is None:
+                self._capture(pl)
+            pl["graph"].replay()
         if self.steps_done == 0:
             self.hyper_host[4] = 0.0
-            self.hyper.copy_(self.hyper_host, non_blocking=True)
+            self._push_hyper()
         self.steps_done += 1
 
-    def _capture(self):
+    def _capture(self, pl):
         # warm-up outside capture is the caller's first eager step(s); here: capture only.
         # State mutated by a step (params, momentum, BN stats) is advanced by replays only, so save/restore
         # is unnecessary: capture itself does not execute kernels.
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            self._launch_step()
-        self.graph = g
+            self._launch_step(pl)
+        pl["graph"] = g
 
     def step(self, idx, ijf):
-        """One training step on dataset samples `idx` (host int64 [N]) with crop/flip draws `ijf` (int8 [N,3])."""
-        self._stage_inputs(idx, ijf, self.labels_host[idx])
-        self._run()
+        """One training step on dataset samples `idx` (host int64 [n]) with crop/flip draws `ijf` (int8 [n,3]);
+        n = N, or fewer for the ragged last batch of an epoch (its own plan and graph, built on first use)."""
+        self._run(self._stage_inputs(idx, ijf, self.labels_host[idx]))
         return self.loss
 
     def step_host_batch(self, images_u8, labels, ijf):
         """One training step on a HOST uint8 batch [N,32,32,3] (copied to the device inside the call)."""
         assert not self.resident
-        self._stage_inputs(None, ijf, labels, images=images_u8)
-        self._run()
+        self._run(self._stage_inputs(None, ijf, labels, images=images_u8))
         return self.loss
 
     # ------------------------------------------------------------------ pipelined host input (DataLoader prefetch)
@@ -255,7 +285,7 @@ class Trainer:
 def make_epoch_plan(n, batch, world=1, rank=0, seed=0, distributed=False):
     """Index batches for one epoch the way the reference's loaders produce them."""
     if distributed:
-        idx = hostdata.distributed_indices(n, world, rank, seed=0, epoch=0)
+        idx = hostdata.distributed_indices(n, world, rank, seed=seed, epoch=0)    # the reference never calls set_epoch
     else:
         idx = hostdata.randperm(hostdata.TorchCpuMT19937(seed), n)
     return hostdata.batches(idx, batch)

@@ -113,3 +113,79 @@ def test_unsupported_module_is_an_error():
     from b200cifar.accelerate import accelerate
     with pytest.raises(NotImplementedError):
         accelerate(nn.Sequential(nn.Conv2d(3, 8, 3), nn.ReLU()).cuda())
+
+
+def test_gradients_survive_in_place_zeroing_and_accumulate():
+    """The .grad tensors autograd adopts from an accelerated network are views of the gradient arena. Two reference
+    idioms keep such a .grad alive into the next backward and must behave as with any module:
+    optimizer.zero_grad(set_to_none=False) (the old default) and gradient accumulation over micro-batches."""
+    import b200cifar
+    from b200cifar.accelerate import accelerate
+    net = accelerate(make("resnet18"))
+    crit = nn.CrossEntropyLoss()
+    (x1, t1), (x2, t2) = batch(64, 21), batch(64, 22)
+    opt = torch.optim.SGD(net.parameters(), lr=0.1)
+
+    def grads_of(x, t):
+        opt.zero_grad(set_to_none=True)
+        crit(net(x), t).backward()
+        return [p.grad.clone() for p in net.parameters()]
+    g1, g2 = grads_of(x1, t1), grads_of(x2, t2)
+    # zero in place, then backward: the result is the new gradient, not twice it and not zero
+    opt.zero_grad(set_to_none=False)
+    assert all(p.grad is not None and float(p.grad.abs().sum()) == 0.0 for p in net.parameters())
+    crit(net(x1), t1).backward()
+    for p, a in zip(net.parameters(), g1):
+        assert rel(p.grad, a) < 1e-4
+    # accumulate a second micro-batch on top (no zero_grad in between)
+    crit(net(x2), t2).backward()
+    for (n, p), a, b in zip(net.named_parameters(), g1, g2):
+        assert rel(p.grad, a + b) < 1e-4, n
+    # the arena still backs .grad: the fused optimizer and DDP read the same memory
+    eng = net._b2c_state.base
+    assert all(p.grad.untyped_storage().data_ptr() == eng.G.untyped_storage().data_ptr() for p in net.parameters())
+
+
+def test_wrong_device_and_data_parallel_are_refused():
+    """An accelerated network is bound to one GPU; inputs from elsewhere (what nn.DataParallel replicas on other
+    GPUs would feed it, main.py:73-75) raise instead of corrupting the plan's buffers."""
+    import b200cifar
+    from b200cifar.accelerate import accelerate
+    net = accelerate(make("resnet18"))
+    with pytest.raises(RuntimeError, match="bound to ONE GPU"):
+        net(torch.zeros(4, 3, 32, 32))                    # CPU tensor
+    dp = nn.DataParallel(net, device_ids=[0])             # a single device: DataParallel calls the module directly
+    x, _ = batch(8, 23)
+    assert dp(x).shape == (8, 10)
+
+
+def test_checkpoint_file_with_module_prefix(tmp_path):
+    """The file the reference writes and reads — {'net': state_dict, 'acc', 'epoch'} saved through the DataParallel /
+    DDP wrapper, so every key starts with `module.` (main.py:138-147, 77-84; main_dist.py:243-250) — round-trips
+    between an accelerated network and a plain fp32 one in both directions."""
+    import b200cifar
+    from b200cifar.accelerate import accelerate
+    net = nn.DataParallel(accelerate(make("resnet18")), device_ids=[0])
+    x, t = batch(128, 24)
+    opt = torch.optim.SGD(net.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)
+    for _ in range(2):
+        opt.zero_grad()
+        nn.functional.cross_entropy(net(x), t).backward()
+        opt.step()
+    path = str(tmp_path / "ckpt.pth")
+    torch.save({"net": net.state_dict(), "acc": 12.5, "epoch": 3}, path)          # main.py:138-147
+    ck = torch.load(path)
+    assert sorted(ck) == ["acc", "epoch", "net"] and len(ck["net"]) == 122
+    assert all(k.startswith("module.") for k in ck["net"])
+    plain = nn.DataParallel(make("resnet18"), device_ids=[0])
+    plain.load_state_dict(ck["net"])                                              # main.py:82
+    other = nn.DataParallel(accelerate(make("resnet18")), device_ids=[0])
+    other.load_state_dict(ck["net"])
+    for (k, a), (_, b), (_, c) in zip(net.state_dict().items(), plain.state_dict().items(),
+                                      other.state_dict().items()):
+        assert torch.equal(a, b) and torch.equal(a, c), k
+    xe, _ = batch(100, 25)
+    net.eval(); plain.eval(); other.eval()
+    with torch.no_grad():
+        assert torch.equal(net(xe), other(xe))
+        assert rel(net(xe), plain(xe)) < 6e-2

@@ -129,3 +129,44 @@ def test_c_abi_rejects_bad_arguments_without_touching_the_gpu():
     for code, word in ((U, b"not supported"), (A, b"invalid argument"), (_lib.B2C_ERR_TOO_LARGE, b"exceeds"),
                        (0, b"success")):
         assert word in l.b2c_error_string(code)
+
+
+def test_package_initialiser_matches_reference_order():
+    """engine.init_params reproduces `torch.manual_seed(s); <reference constructor>()` bit for bit: checked against the
+    oracle's builders, which tests/test_oracle.py pins to fixtures generated by the reference's own modules."""
+    import torch
+    from b200cifar import engine
+    from oracle import nets
+    cases = [(engine.resnet_spec(), nets.build_resnet_params), (engine.vgg_spec("VGG16"), nets.build_vgg_params),
+             (engine.preact_resnet_spec(), nets.build_preact_params),
+             (engine.mobilenetv2_spec(), nets.build_mobilenetv2_params),
+             (engine.resnet50_spec(), nets.build_bottleneck_params)]
+    for spec, build in cases:
+        for seed in (0, 3):
+            p, b = engine.init_params(spec, seed)
+            rp, rb = build(seed)
+            assert list(p) == list(rp), spec["family"]
+            assert all(torch.equal(p[k], rp[k]) for k in p), spec["family"]
+            assert all(torch.equal(b[k], rb[k]) for k in b), spec["family"]
+
+
+def test_epoch_plan_batches_and_seed():
+    """make_epoch_plan: DataLoader batching with the ragged tail kept (main.py:45, main_dist.py:111-127)."""
+    from b200cifar import data, trainer
+    plan = trainer.make_epoch_plan(50000, 128)
+    assert len(plan) == 391 and len(plan[-1]) == 80
+    d0 = trainer.make_epoch_plan(50000, 128, world=8, rank=3, seed=0, distributed=True)
+    assert len(d0) == 49 and len(d0[-1]) == 106
+    assert np.array_equal(np.concatenate(d0), data.distributed_indices(50000, 8, 3, seed=0))
+    d1 = trainer.make_epoch_plan(50000, 128, world=8, rank=3, seed=1, distributed=True)
+    assert not np.array_equal(np.concatenate(d0), np.concatenate(d1))
+
+
+def test_bench_algorithmic_bytes():
+    """bench.py's HBM-roofline numerator for MobileNetV2 = 3 x the fused-minimum forward traffic of SURVEY.md §8a
+    (880 MB per 128 images)."""
+    import bench
+    from b200cifar import engine
+    per_img = bench.algorithmic_bytes_per_image(engine.mobilenetv2_spec(), engine)
+    assert abs(per_img * 128 / 3 / 1e6 - 880) < 5
+    assert abs(bench.algorithmic_bytes_per_image(engine.resnet_spec(), engine) * 128 / 3 / 1e6 - 327.9) < 1

@@ -84,6 +84,62 @@ def test_conv_fprop(ops, shape):
     assert rel_err(s2, (ref * ref).sum((0, 2, 3))) < F32_TOL
 
 
+# The batch bench.py is quoted on (BASELINE config 2 on one GPU: 1024 images): tile counts, persistent-loop wave
+# counts, wgrad split-K depth (K = 1 048 576 pixels on layer 1) and halo-wgrad scratch use all differ from the
+# small cases above, so the same three kernels are checked at that size with the flags the engine passes.
+BENCH_SHAPES = [
+    (1024, 32, 32, 64, 64, 3, 1),      # layer1 conv (conv_halo2 RES, wgrad_halo)
+    (1024, 32, 32, 64, 128, 3, 2),     # layer2.0.conv1
+    (1024, 32, 32, 64, 128, 1, 2),     # layer2.0.shortcut
+    (1024, 16, 16, 128, 128, 3, 1),    # layer2 conv (conv_halo2 BN=128, wgrad_row)
+    (1024, 8, 8, 256, 256, 3, 1),      # layer3 conv (MODE 1 tiles, wgrad_row2)
+    (1024, 4, 4, 512, 512, 3, 1),      # layer4 conv (tap_gemm2 BN=256)
+]
+
+
+@pytest.mark.parametrize("shape", BENCH_SHAPES)
+def test_conv_at_bench_batch(ops, shape):
+    n, h, w, cin, cout, k, stride = shape
+    ho, wo = h // stride, w // stride
+    x = nhwc_bf16(n, h, w, cin, 71)
+    dy = nhwc_bf16(n, ho, wo, cout, 72, scale=0.1)
+    wt = weight(cout, cin, k, 73)
+    xf, dyf = to_nchw(x), to_nchw(dy)
+    pair = 128
+    d = ops.conv_desc(n, h, w, cin, cout, k, stride, flags=pair)
+    # fprop + BatchNorm partial sums
+    y = torch.full((n, ho, wo, cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    rows = ops.conv_fprop(d, x, ops.pack_weight_fprop(wt), y, ps, pq)
+    torch.cuda.synchronize()
+    ref = F.conv2d(xf, wt, stride=stride, padding=k // 2)
+    assert torch.isfinite(to_nchw(y)).all() and rel_err(to_nchw(y), ref) < BF16_TOL
+    assert rel_err(pq[:rows].sum(0), (ref * ref).sum((0, 2, 3))) < F32_TOL
+    assert (ps[:rows].sum(0) - ref.sum((0, 2, 3))).abs().max() < 2e-3 * ref.abs().sum((0, 2, 3)).max()
+    del ref
+    # dgrad
+    dx = torch.full((n, h, w, cin), float("nan"), device="cuda", dtype=torch.bfloat16)
+    if k == 1 and stride == 2:
+        ops.conv_dgrad(d, dy, ops.pack_weight_dgrad(wt), dx)
+    else:
+        add = nhwc_bf16(n, h, w, cin, 74, scale=0.1)
+        ops.conv_dgrad(d, dy, ops.pack_weight_dgrad(wt), dx, add)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_input((n, cin, h, w), wt, dyf, stride=stride, padding=k // 2)
+    if not (k == 1 and stride == 2):
+        ref = ref + to_nchw(add)
+    assert torch.isfinite(to_nchw(dx)).all() and rel_err(to_nchw(dx), ref) < BF16_TOL
+    del ref
+    # wgrad, [tap][cin][cout] layout + scratch, as the engine calls it
+    refw = torch.nn.grad.conv2d_weight(xf, (cout, cin, k, k), dyf, stride=stride, padding=k // 2)
+    scratch = torch.zeros(ops.WGRAD_SCRATCH_FLOATS, device="cuda")
+    dw = torch.zeros(k * k, cin, cout, device="cuda")
+    ops.conv_wgrad(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=32 | pair), x, dy, dw, scratch=scratch)
+    torch.cuda.synchronize()
+    assert rel_err(dw.view(k, k, cin, cout).permute(3, 2, 0, 1), refw) < 2e-3
+
+
 @pytest.mark.parametrize("shape", [s for s in CONV_SHAPES if s[5] == 3 and s[6] == 1 and s[1] in (8, 16, 32)])
 def test_conv_per_tap_kernel_still_covered(ops, shape):
     """flags=1 forces the per-tap kernel on shapes that normally take the halo-reuse kernel."""

@@ -1,0 +1,92 @@
+"""GPU tests of trainer.Trainer beyond the fixed-size step: an epoch whose last batch is ragged, as the reference's
+loaders produce it (drop_last=False: 50000 = 390*128 + 80, main.py:45; 6250 = 48*128 + 106 per rank,
+main_dist.py:111), and learning-rate updates between enqueued steps."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
+
+
+def _trainer(use_graph, N=128):
+    import b200cifar
+    from b200cifar import data, engine, trainer
+    spec = engine.resnet_spec()
+    params, bufs = engine.init_params(spec, 0)
+    tr = trainer.Trainer(spec, N, lr=0.02, use_graph=use_graph)
+    tr.load_params(params, bufs)
+    images, labels = data.learnable_cifar(300, seed=5)
+    tr.set_dataset(images, labels)
+    return tr, images, labels
+
+
+def test_epoch_with_ragged_last_batch():
+    import b200cifar
+    from b200cifar import data, ops
+    from oracle import nets_manual
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    rng = data.TorchCpuMT19937(9)
+    perm = data.randperm(rng, 300)
+    batches = data.batches(perm, 128)                     # 128, 128, 44
+    assert [len(b) for b in batches] == [128, 128, 44]
+    draws = [data.draw_crop_flip(rng, len(b)) for b in batches]
+    runs = {}
+    for use_graph in (True, False):
+        tr, images, labels = _trainer(use_graph)
+        for rep in range(2):                              # twice: the tail plan's eager first step, then its graph
+            losses = []
+            for b, d in zip(batches, draws):
+                if rep == 1 and len(b) == 44:             # state right before the last ragged step, for the oracle
+                    before = ({k: v.clone() for k, v in tr.eng.named_params().items()},
+                              {k: v.clone() for k, v in tr.eng.named_buffers().items()})
+                tr.step(b, d)
+                losses.append(tr.read_loss())
+        runs[use_graph] = (tr, losses, before)
+    (tg, lg, before), (te, le, _) = runs[True], runs[False]
+    assert len(tg._plans) == 2 and 44 in tg._plans
+    assert np.allclose(lg, le, atol=2e-2), (lg, le)       # graph replay == eager (weight-gradient atomics reorder sums)
+    assert rel(tg.eng.P, te.eng.P) < 1e-2
+    # the ragged step against the bf16-storage oracle on the same 44 samples, parameters and BN buffers
+    b, d = batches[-1], draws[-1]
+    x = torch.empty(44, 3, 32, 32, device="cuda")
+    ops.augment_nchw(tg.data, torch.from_numpy(b).cuda(), torch.from_numpy(d).cuda(), x)
+    tgt = torch.from_numpy(labels[b]).cuda()
+    P, B = before
+    B = dict(B, **{k.replace("running_mean", "num_batches_tracked"): torch.zeros((), dtype=torch.long, device="cuda")
+                   for k in B if k.endswith("running_mean")})
+    with torch.no_grad():
+        loss_ref, _, grads_ref = nets_manual.resnet_train_step(x, tgt, P, B, True)
+    assert abs(lg[-1] - loss_ref.item()) < 2e-2, (lg[-1], loss_ref.item())
+    gw = tg._plans[44]["eng"].grad_view("linear.weight")  # the arena still holds the last step's gradient
+    assert rel(gw, grads_ref["linear.weight"]) < 5e-2
+    with pytest.raises(ValueError):
+        tg.step(np.arange(200), data.draw_crop_flip(rng, 200))      # larger than the trainer's batch
+
+
+def test_set_lr_applies_from_the_next_step():
+    """lr is a device scalar read by the SGD kernel; set_lr() between steps must change exactly the steps issued after
+    it, also while earlier steps are still queued on the GPU."""
+    import b200cifar
+    from b200cifar import data
+    tr, images, labels = _trainer(True)
+    rng = data.TorchCpuMT19937(3)
+    idx, ijf = np.arange(128), data.draw_crop_flip(rng, 128)
+    tr.set_lr(0.0)
+    tr.step(idx, ijf)
+    tr.step(idx, ijf)
+    torch.cuda.synchronize()
+    p0 = tr.eng.P.clone()
+    for _ in range(3):                                    # queued with lr = 0: parameters only move by weight decay * 0
+        tr.step(idx, ijf)
+    tr.set_lr(0.05)                                       # must not reach the three steps above
+    torch.cuda.synchronize()
+    assert torch.equal(tr.eng.P, p0)
+    tr.step(idx, ijf)
+    torch.cuda.synchronize()
+    assert not torch.equal(tr.eng.P, p0)
