@@ -62,7 +62,12 @@ typedef struct B2cConvDesc {
                         bit 7: fprop / stride-1 dgrad: CTA-pair kernels (tcgen05.mma.cta_group::2): conv_halo2.cu where
                                the halo kernel would run, conv_gemm2.cu otherwise (or with bit 0); wgrad: the pair
                                row kernel (conv_wgrad_row2.cu) where cin is a multiple of 256;
-                        bit 8: wgrad: the pair row kernel for any cin the row kernel takes (test aid) */
+                        bit 8: wgrad: the pair row kernel for any cin the row kernel takes (test aid);
+                        bit 9: fprop / dgrad_bn: the per-channel statistics are ACCUMULATED (fp32 atomics) into ONE row
+                               — part_sum[cout], part_sq[cout], resp. partial[2][cin] — that the caller zero-filled,
+                               instead of one row per CTA; *stat_rows = 1. The consumers are b2c_bn_act_apply_stats /
+                               b2c_bn_bwd_apply_stats, which finalize the statistics themselves (no finalize launch).
+                               Sums of ~148 per-CTA partials in arrival order: run-to-run differences of a few ulp. */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)
@@ -118,6 +123,10 @@ B2C_API int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, 
 B2C_API int b2c_dwconv_stat_rows(long long out_pixels, int channels);
 B2C_API int b2c_dwconv_fprop(const void* x, const float* weight, void* y, int n, int h, int w, int channels, int c_valid,
                      int stride, float* part_sum, float* part_sq, int* stat_rows, void* stream);
+/* b2c_dwconv_fprop whose BatchNorm sums are accumulated (fp32 atomics) into ONE zero-filled row sum[channels] /
+ * sumsq[channels], for b2c_bn_act_apply_stats. */
+B2C_API int b2c_dwconv_fprop_acc(const void* x, const float* weight, void* y, int n, int h, int w, int channels, int c_valid,
+                         int stride, float* sum, float* sumsq, void* stream);
 B2C_API int b2c_dwconv_dgrad(const void* dy, const float* weight, void* dx, int n, int h, int w, int channels, int c_valid,
                      int stride, void* stream);
 B2C_API int b2c_dwconv_wgrad(const void* x, const void* dy, float* dweight, int n, int h, int w, int channels, int c_valid,
@@ -146,6 +155,47 @@ B2C_API int b2c_bn_eval_scale_shift(int channels, const float* gamma, const floa
 B2C_API int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, const void* res,
                      const float* res_scale, const float* res_shift, void* out, long long rows, int channels,
                      int relu, unsigned char* relu_bits, void* stream);
+
+/* One training-mode BatchNorm whose batch statistics arrive as ONE accumulated row (B2cConvDesc.flags bit 9,
+ * b2c_dwconv_fprop_acc): everything b2c_bn_finalize takes and produces. sum/sumsq/gamma/beta/conv_bias are inputs,
+ * [channels] fp32; running_mean/var (both or neither) are updated in place; scale/shift/save_mean/save_rstd are
+ * written for the backward pass. count = n*h*w. */
+typedef struct B2cBnStats {
+    const float* sum;
+    const float* sumsq;
+    const float* gamma;
+    const float* beta;
+    const float* conv_bias; /* optional, see b2c_bn_finalize */
+    float* running_mean;
+    float* running_var;
+    float* scale;
+    float* shift;
+    float* save_mean;
+    float* save_rstd;
+    float count, eps, momentum;
+} B2cBnStats;
+
+/* b2c_bn_finalize + b2c_bn_act_apply in ONE launch — F.relu(self.bn1(self.conv1(x))) and
+ * F.relu(self.bn2(..) + self.shortcut(x)), models/resnet.py:47-50, given the conv's accumulated statistics: every
+ * block derives scale / shift for all channels in its prologue (2*channels floats from L2), block 0 publishes them
+ * and updates the running statistics. res_bn (optional, needs res): the shortcut conv's own BatchNorm
+ * (models/resnet.py:33-35), finalized the same way; res without res_bn is an identity shortcut. Saves the 20 + 20
+ * finalize launches of a ResNet-18 step together with b2c_bn_bwd_apply_stats. channels <= 4096. */
+B2C_API int b2c_bn_act_apply_stats(const void* y, const B2cBnStats* bn, const void* res, const B2cBnStats* res_bn,
+                           void* out, long long rows, int channels, int relu, unsigned char* relu_bits, void* stream);
+
+/* b2c_bn_bwd_reduce that ACCUMULATES (fp32 atomics) into one zero-filled row sums[2][channels] (sum dz | sum dz*y)
+ * instead of writing one row per block; same masking options. For b2c_bn_bwd_apply_stats. */
+B2C_API int b2c_bn_bwd_reduce_acc(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
+                          int channels, float* sums, const float* relu_scale, const float* relu_shift,
+                          const unsigned char* relu_bits, void* stream);
+
+/* b2c_bn_bwd_finalize + b2c_bn_bwd_apply in ONE launch, from one accumulated row sums[2][channels]: dgamma / dbeta
+ * are written by block 0, dy = A*dz + B*y + C (+ add) by everyone (cudnn_batch_norm_backward, main.py:104). */
+B2C_API int b2c_bn_bwd_apply_stats(const void* dz, const void* y, const float* sums, float count, const float* gamma,
+                           const float* save_mean, const float* save_rstd, float* dgamma, float* dbeta,
+                           const void* add, void* dy, long long rows, int channels, const float* relu_scale,
+                           const float* relu_shift, void* stream);
 
 /* Number of partial rows b2c_bn_bwd_reduce writes for (rows, channels): size `partial` as
  * rows_returned * 2 * channels floats. Host-only arithmetic. */

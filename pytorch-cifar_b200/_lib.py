@@ -32,6 +32,13 @@ class ConvDesc(ctypes.Structure):
                  "flags")]
 
 
+class BnStats(ctypes.Structure):
+    """Mirror of B2cBnStats (include/b2c.h)."""
+    _fields_ = [(n, ctypes.c_void_p) for n in
+                ("sum", "sumsq", "gamma", "beta", "conv_bias", "running_mean", "running_var", "scale", "shift",
+                 "save_mean", "save_rstd")] + [(n, ctypes.c_float) for n in ("count", "eps", "momentum")]
+
+
 class RepackEntry(ctypes.Structure):
     """Mirror of B2cRepackEntry (include/b2c.h)."""
     _fields_ = [("src_off", ctypes.c_longlong), ("wf_off", ctypes.c_longlong), ("wd_off", ctypes.c_longlong),
@@ -70,6 +77,10 @@ SIGNATURES = {
     "b2c_bn_finalize": [_P, _P, _I, _I, _F, _P, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P],
     "b2c_bn_eval_scale_shift": [_I, _P, _P, _P, _P, _P, _F, _P, _P, _P],
     "b2c_bn_act_apply": [_P, _P, _P, _P, _P, _P, _P, _LL, _I, _I, _P, _P],
+    "b2c_bn_act_apply_stats": [_P, ctypes.POINTER(BnStats), _P, ctypes.POINTER(BnStats), _P, _LL, _I, _I, _P, _P],
+    "b2c_bn_bwd_reduce_acc": [_P, _P, _P, _P, _LL, _I, _P, _P, _P, _P, _P],
+    "b2c_bn_bwd_apply_stats": [_P, _P, _P, _F, _P, _P, _P, _P, _P, _P, _P, _LL, _I, _P, _P, _P],
+    "b2c_dwconv_fprop_acc": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P],
     "b2c_bn_bwd_partial_rows": [_LL, _I],
     "b2c_bn_bwd_reduce": [_P, _P, _P, _P, _LL, _I, _P, _P, _P, _P, _P],
     "b2c_bn_bwd_finalize": [_P, _I, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],

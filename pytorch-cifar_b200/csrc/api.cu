@@ -154,6 +154,8 @@ int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w,
         p.stat_ld = 2 * gemm_n;
         stat_rows = bn_fuse->stat_rows;
     }
+    const bool acc = (d->flags & 512) != 0;       // statistics accumulated into one zero-filled row (fp32 atomics)
+    if (acc) p.stat_ld = 0;
     p.debug = d->flags & 0x3e;
     CUtensorMap ma, mb;
     int rc = p.mode == 0 ? encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 18, 1, 1)
@@ -163,8 +165,10 @@ int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w,
     rc = encode_2d(&mb, w, 9LL * gemm_n, act_c, pair ? bn / 2 : bn);
     if (rc) return rc;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
-    if (pair) return cuda_rc(b2c::launch_conv_halo2(bn, ma, mb, p, max_ctas, stat_rows, st));
-    return cuda_rc(b2c::launch_conv_halo(bn, ma, mb, p, max_ctas, stat_rows, st));
+    rc = pair ? cuda_rc(b2c::launch_conv_halo2(bn, ma, mb, p, max_ctas, stat_rows, st))
+              : cuda_rc(b2c::launch_conv_halo(bn, ma, mb, p, max_ctas, stat_rows, st));
+    if (acc && stat_rows != nullptr) *stat_rows = 1;
+    return rc;
 }
 
 // GEMM N tile: the widest tile that still gives every SM work. tcgen05.mma reads both operands from shared
@@ -254,7 +258,8 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     p.part_sum = part_sum;
     p.part_sq = part_sq;
     p.cout = d->cout;
-    p.stat_ld = d->cout;
+    const bool acc = (d->flags & 512) != 0;       // statistics accumulated into one zero-filled row (fp32 atomics)
+    p.stat_ld = acc ? 0 : d->cout;
 
     const int bh = (128 / wo) < ho ? (128 / wo) : ho;
     const int bnb = 128 / (wo * bh);
@@ -267,8 +272,10 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     rc = encode_2d(&mb, w_fprop, static_cast<long long>(taps) * d->cout, d->cin, pair ? bn / 2 : bn);
     if (rc) return rc;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
-    if (pair) return cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
-    return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
+    rc = pair ? cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, as_stream(stream)))
+              : cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
+    if (acc && stat_rows != nullptr) *stat_rows = 1;
+    return rc;
 }
 
 static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_shortcut, const void* w_dgrad,
@@ -310,7 +317,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         p.bwd_shift = bn_fuse->shift;
         p.part_sum = bn_fuse->partial;
         p.part_sq = bn_fuse->partial + d->cin;
-        p.stat_ld = 2 * d->cin;
+        p.stat_ld = (d->flags & 512) ? 0 : 2 * d->cin;      // flags bit 9: one accumulated row
         stat_rows = bn_fuse->stat_rows;
     }
 
@@ -340,8 +347,10 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         }
         p.sy = p.sx = 1;
         single_phase(p);
-        if (pair) return cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, st));
-        return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, st));
+        rc = pair ? cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, st))
+                  : cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, st));
+        if ((d->flags & 512) && stat_rows != nullptr) *stat_rows = 1;
+        return rc;
     }
 
     // stride 2: one GEMM per output parity phase (ph, pw); dx[2i+ph, 2j+pw] only sees taps with
@@ -408,7 +417,9 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     p.phase_begin[4] = static_cast<uint8_t>(nt);
     p.num_taps = nt;
     p.num_phases = 4;
-    return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma1, mb, p, max_ctas, stat_rows, st));
+    rc = cuda_rc(b2c::launch_tap_gemm(bn, ma, ma1, mb, p, max_ctas, stat_rows, st));
+    if ((d->flags & 512) && stat_rows != nullptr) *stat_rows = 1;
+    return rc;
 }
 
 int b2c_conv_dgrad(const B2cConvDesc* d, const void* dy, const void* w_dgrad, void* dx, const void* add_src,
@@ -593,6 +604,15 @@ int b2c_dwconv_fprop(const void* x, const float* weight, void* y, int n, int h, 
                                         as_stream(stream)));
 }
 
+int b2c_dwconv_fprop_acc(const void* x, const float* weight, void* y, int n, int h, int w, int channels, int c_valid,
+                         int stride, float* sum, float* sumsq, void* stream) {
+    int rc = check_dw(x, weight, y, n, h, w, channels, c_valid, stride);
+    if (rc) return rc;
+    if (!aligned16(x) || !aligned16(y) || !sum || !sumsq) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_dw_fprop(x, weight, y, n, h, w, channels, c_valid, stride, sum, sumsq, nullptr,
+                                        as_stream(stream), 1));
+}
+
 int b2c_dwconv_dgrad(const void* dy, const float* weight, void* dx, int n, int h, int w, int channels, int c_valid,
                      int stride, void* stream) {
     int rc = check_dw(dy, weight, dx, n, h, w, channels, c_valid, stride);
@@ -642,6 +662,50 @@ int b2c_bn_act_apply(const void* y, const float* scale, const float* shift, cons
     if (rows == 0) return 0;
     return cuda_rc(b2c::launch_bn_act_apply(y, scale, shift, res, res_scale, res_shift, out, rows, channels, relu,
                                             relu_bits, as_stream(stream)));
+}
+
+static bool bn_stats_ok(const B2cBnStats* b) {
+    return b && b->sum && b->sumsq && b->gamma && b->beta && b->scale && b->shift && b->save_mean && b->save_rstd &&
+           b->count > 0.f && (b->running_mean == nullptr) == (b->running_var == nullptr);
+}
+
+int b2c_bn_act_apply_stats(const void* y, const B2cBnStats* bn, const void* res, const B2cBnStats* res_bn, void* out,
+                           long long rows, int channels, int relu, unsigned char* relu_bits, void* stream) {
+    static_assert(sizeof(B2cBnStats) == sizeof(b2c::BnStatArgs), "ABI struct mismatch");
+    if (!y || !out || rows < 0 || channels < 8 || (channels & 7) || channels > 4096) return B2C_ERR_ARG;
+    if (!bn_stats_ok(bn) || (res_bn != nullptr && (!bn_stats_ok(res_bn) || res == nullptr))) return B2C_ERR_ARG;
+    if (!aligned16(y) || !aligned16(out) || !aligned16(res)) return B2C_ERR_ARG;
+    if (rows == 0) return 0;
+    return cuda_rc(b2c::launch_bn_act_apply_stats(y, *reinterpret_cast<const b2c::BnStatArgs*>(bn), res,
+                                                  reinterpret_cast<const b2c::BnStatArgs*>(res_bn), out, rows, channels,
+                                                  relu, relu_bits, as_stream(stream)));
+}
+
+int b2c_bn_bwd_reduce_acc(const void* dout, const void* act, const void* y, void* dz_out, long long rows, int channels,
+                          float* sums, const float* relu_scale, const float* relu_shift,
+                          const unsigned char* relu_bits, void* stream) {
+    if (!dout || !y || !sums || rows < 1) return B2C_ERR_ARG;
+    if (relu_bits != nullptr && (act != nullptr || relu_scale != nullptr)) return B2C_ERR_ARG;
+    if ((relu_scale == nullptr) != (relu_shift == nullptr) || (relu_scale != nullptr && act != nullptr))
+        return B2C_ERR_ARG;
+    if (channels < 8 || (channels & 7) || (channels >> 3) > 256) return B2C_ERR_UNSUPPORTED;
+    if (!aligned16(dout) || !aligned16(act) || !aligned16(y) || !aligned16(dz_out)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_bn_bwd_reduce(dout, act, y, dz_out, rows, channels, sums, relu_scale, relu_shift,
+                                             relu_bits, as_stream(stream), 1));
+}
+
+int b2c_bn_bwd_apply_stats(const void* dz, const void* y, const float* sums, float count, const float* gamma,
+                           const float* save_mean, const float* save_rstd, float* dgamma, float* dbeta,
+                           const void* add, void* dy, long long rows, int channels, const float* relu_scale,
+                           const float* relu_shift, void* stream) {
+    if ((relu_scale == nullptr) != (relu_shift == nullptr)) return B2C_ERR_ARG;
+    if (!dz || !y || !sums || !gamma || !save_mean || !save_rstd || !dgamma || !dbeta || !dy || rows < 0 ||
+        channels < 8 || (channels & 7) || channels > 4096 || count <= 0.f)
+        return B2C_ERR_ARG;
+    if (!aligned16(dz) || !aligned16(y) || !aligned16(dy) || !aligned16(add)) return B2C_ERR_ARG;
+    if (rows == 0) return 0;
+    return cuda_rc(b2c::launch_bn_bwd_apply_stats(dz, y, sums, count, gamma, save_mean, save_rstd, dgamma, dbeta, add,
+                                                  dy, rows, channels, relu_scale, relu_shift, as_stream(stream)));
 }
 
 int b2c_bn_bwd_partial_rows(long long rows, int channels) {

@@ -16,6 +16,23 @@ struct RepackEntry {
     int pad_;           // cout_pad (0: cout)
 };
 
+// One BatchNorm whose batch statistics arrive as ONE accumulated row (sum, sum of squares) and are finalized inside
+// the kernel that applies it (bn_act_apply_stats). Mirrors B2cBnStats in include/b2c.h (same field order and types).
+struct BnStatArgs {
+    const float* sum;
+    const float* sumsq;
+    const float* gamma;
+    const float* beta;
+    const float* conv_bias;
+    float* running_mean;
+    float* running_var;
+    float* scale;
+    float* shift;
+    float* save_mean;
+    float* save_rstd;
+    float count, eps, momentum;
+};
+
 cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int rows, int C, float count,
                                const float* gamma, const float* beta, const float* conv_bias, float eps,
                                float momentum, float* running_mean, float* running_var, float* scale, float* shift,
@@ -30,7 +47,13 @@ cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* 
 int bn_bwd_partial_rows(long long rows, int C);
 cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
                                  int C, float* partial, const float* relu_scale, const float* relu_shift,
-                                 const uint8_t* relu_bits, cudaStream_t s);
+                                 const uint8_t* relu_bits, cudaStream_t s, int accumulate = 0);
+cudaError_t launch_bn_act_apply_stats(const void* y, const BnStatArgs& st, const void* res, const BnStatArgs* rst,
+                                      void* out, long long rows, int C, int relu, uint8_t* relu_bits, cudaStream_t s);
+cudaError_t launch_bn_bwd_apply_stats(const void* dz, const void* y, const float* sums, float count,
+                                      const float* gamma, const float* mean, const float* rstd, float* dgamma,
+                                      float* dbeta, const void* add, void* dy, long long rows, int C,
+                                      const float* relu_scale, const float* relu_shift, cudaStream_t s);
 cudaError_t launch_bn_bwd_finalize(const float* partial, int prow, int C, float count, const float* gamma,
                                    const float* mean, const float* rstd, float* dgamma, float* dbeta, float* coefA,
                                    float* coefB, float* coefC, cudaStream_t s);
@@ -56,7 +79,7 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
                           cudaStream_t s);
 int dw_fprop_partial_rows(long long out_pixels, int C);
 cudaError_t launch_dw_fprop(const void* x, const float* w, void* y, int N, int H, int W, int C, int c_valid, int stride,
-                            float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s);
+                            float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s, int stat_acc = 0);
 cudaError_t launch_dw_dgrad(const void* dy, const float* w, void* dx, int N, int H, int W, int C, int c_valid,
                             int stride, cudaStream_t s);
 cudaError_t launch_dw_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int c_valid,

@@ -452,8 +452,13 @@ conv_halo2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 const float s2 = stat[(1 * 4 + 0) * BN + col] + stat[(1 * 4 + 1) * BN + col] +
                                  stat[(1 * 4 + 2) * BN + col] + stat[(1 * 4 + 3) * BN + col];
                 const size_t o = static_cast<size_t>(prow) * p.stat_ld + n_tile * BN + col;
-                p.part_sum[o] = s1;
-                p.part_sq[o] = s2;
+                if (p.stat_ld == 0) {      // one accumulated row (flags bit 9): the caller zero-filled it
+                    atomicAdd(p.part_sum + o, s1);
+                    atomicAdd(p.part_sq + o, s2);
+                } else {
+                    p.part_sum[o] = s1;
+                    p.part_sq[o] = s2;
+                }
             }
         }
     }

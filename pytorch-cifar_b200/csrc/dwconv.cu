@@ -42,7 +42,7 @@ __device__ __forceinline__ void load_w(const float* __restrict__ wt, int c0, int
 // y[n, ho, wo, c] = sum_{r,s} x[n, ho*stride + r - 1, wo*stride + s - 1, c] * w[c, r, s]
 __global__ void __launch_bounds__(256)
 dw_fprop_kernel(const uint4* __restrict__ x, const float* __restrict__ wt, uint4* __restrict__ y, int N, int H, int W,
-                int C, int c_valid, int stride, float* __restrict__ part_sum, float* __restrict__ part_sq) {
+                int C, int c_valid, int stride, float* __restrict__ part_sum, float* __restrict__ part_sq, int stat_acc) {
     pdl_trigger_ew();
     pdl_wait();
     extern __shared__ float red[];  // [rpi][2][C]
@@ -98,7 +98,8 @@ dw_fprop_kernel(const uint4* __restrict__ x, const float* __restrict__ wt, uint4
     for (int i = threadIdx.x; i < 2 * C; i += 256) {
         float s = 0.f;
         for (int k = 0; k < rpi; ++k) s += red[k * 2 * C + i];
-        if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
+        if (stat_acc) atomicAdd(i < C ? part_sum + i : part_sq + (i - C), s);      // one accumulated row
+        else if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
         else part_sq[static_cast<size_t>(blockIdx.x) * C + (i - C)] = s;
     }
 }
@@ -220,7 +221,7 @@ template <int MODE, int T>
 __global__ void __launch_bounds__(256)
 dw_strip_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, const float* __restrict__ wt,
                 uint2* __restrict__ out, float* __restrict__ dw, int N, int H, int W, int C, int c_valid,
-                float* __restrict__ part_sum, float* __restrict__ part_sq) {
+                float* __restrict__ part_sum, float* __restrict__ part_sq, int stat_acc) {
     pdl_trigger_ew();
     pdl_wait();
     extern __shared__ float red[];   // MODE 0: [rpi][2][C]; MODE 2: [rpi][9][C]
@@ -320,7 +321,8 @@ dw_strip_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, con
         for (int i = threadIdx.x; i < 2 * C; i += 256) {
             float s = 0.f;
             for (int k = 0; k < rpi; ++k) s += red[k * 2 * C + i];
-            if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
+            if (stat_acc) atomicAdd(i < C ? part_sum + i : part_sq + (i - C), s);      // one accumulated row
+            else if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
             else part_sq[static_cast<size_t>(blockIdx.x) * C + (i - C)] = s;
         }
     } else if (MODE == 2) {
@@ -351,7 +353,7 @@ template <int MODE, int T>
 __global__ void __launch_bounds__(256)
 dw_strip2_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, const float* __restrict__ wt,
                  uint2* __restrict__ out, float* __restrict__ dw, int N, int H, int W, int C, int c_valid,
-                 float* __restrict__ part_sum, float* __restrict__ part_sq) {
+                 float* __restrict__ part_sum, float* __restrict__ part_sq, int stat_acc) {
     pdl_trigger_ew();
     pdl_wait();
     extern __shared__ float red[];   // MODE 0: [rpi][2][C]; MODE 2: [rpi][9][C]
@@ -448,7 +450,8 @@ dw_strip2_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, co
         for (int i = threadIdx.x; i < 2 * C; i += 256) {
             float s = 0.f;
             for (int k = 0; k < rpi; ++k) s += red[k * 2 * C + i];
-            if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
+            if (stat_acc) atomicAdd(i < C ? part_sum + i : part_sq + (i - C), s);      // one accumulated row
+            else if (i < C) part_sum[static_cast<size_t>(blockIdx.x) * C + i] = s;
             else part_sq[static_cast<size_t>(blockIdx.x) * C + (i - C)] = s;
         }
     } else {
@@ -548,7 +551,7 @@ inline bool dw_strip2_ok(int H, int W, int C, int stride) {
 // MODE 0 fprop, 1 dgrad, 2 wgrad (stride 2)
 template <int MODE>
 cudaError_t launch_dw_strip2(const void* in, const void* in2, const float* w, void* out, float* dw, int N, int H, int W,
-                             int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s) {
+                             int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s, int stat_acc = 0) {
     const int cq_n = C >> 2;
     const int rpi = 256 / cq_n;
     const int Ho = H >> 1, Wo = W >> 1;
@@ -558,7 +561,7 @@ cudaError_t launch_dw_strip2(const void* in, const void* in2, const float* w, vo
     const int cap = MODE == 2 ? 296 : 148 * 4;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    if (stat_rows != nullptr) *stat_rows = static_cast<int>(blocks);
+    if (stat_rows != nullptr) *stat_rows = stat_acc ? 1 : static_cast<int>(blocks);
     const int grid = static_cast<int>(blocks);
     if (MODE == 1) {
         if (T == 8)
@@ -586,16 +589,16 @@ cudaError_t launch_dw_strip2(const void* in, const void* in2, const float* w, vo
     }
     if (T == 8)
         B2C_LAUNCH(k8, grid, 256, smem, s, static_cast<const uint2*>(in), static_cast<const uint2*>(in2), w,
-                   static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum, part_sq);
+                   static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum, part_sq, stat_acc);
     else
         B2C_LAUNCH(k4, grid, 256, smem, s, static_cast<const uint2*>(in), static_cast<const uint2*>(in2), w,
-                   static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum, part_sq);
+                   static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum, part_sq, stat_acc);
     return cudaGetLastError();
 }
 
 template <int MODE>
 cudaError_t launch_dw_strip(const void* in, const void* in2, const float* w, void* out, float* dw, int N, int H, int W,
-                            int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s) {
+                            int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s, int stat_acc = 0) {
     const int cq_n = C >> 2;
     const int rpi = 256 / cq_n;
     const int T = (H % 8) == 0 ? 8 : 4;
@@ -604,7 +607,7 @@ cudaError_t launch_dw_strip(const void* in, const void* in2, const float* w, voi
     const int cap = MODE == 2 ? 296 : 148 * 4;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    if (stat_rows != nullptr) *stat_rows = static_cast<int>(blocks);
+    if (stat_rows != nullptr) *stat_rows = stat_acc ? 1 : static_cast<int>(blocks);
     size_t smem = 0;
     if (MODE == 0 && part_sum != nullptr) smem = static_cast<size_t>(rpi) * 2 * C * sizeof(float);
     if (MODE == 2) smem = static_cast<size_t>(rpi) * 9 * C * sizeof(float);
@@ -622,11 +625,11 @@ cudaError_t launch_dw_strip(const void* in, const void* in2, const float* w, voi
     if (T == 8)
         B2C_LAUNCH(k8, static_cast<int>(blocks), 256, smem, s, static_cast<const uint2*>(in),
                    static_cast<const uint2*>(in2), w, static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum,
-                   part_sq);
+                   part_sq, stat_acc);
     else
         B2C_LAUNCH(k4, static_cast<int>(blocks), 256, smem, s, static_cast<const uint2*>(in),
                    static_cast<const uint2*>(in2), w, static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum,
-                   part_sq);
+                   part_sq, stat_acc);
     return cudaGetLastError();
 }
 
@@ -641,19 +644,19 @@ int dw_fprop_partial_rows(long long out_pixels, int C) {
 }
 
 cudaError_t launch_dw_fprop(const void* x, const float* w, void* y, int N, int H, int W, int C, int c_valid, int stride,
-                            float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s) {
+                            float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s, int stat_acc) {
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     if (dw_strip_ok(H, W, C, stride))
-        return launch_dw_strip<0>(x, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s);
+        return launch_dw_strip<0>(x, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s, stat_acc);
     if (dw_strip2_ok(H, W, C, stride))
-        return launch_dw_strip2<0>(x, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s);
+        return launch_dw_strip2<0>(x, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s, stat_acc);
     const int rpi = 256 / cvec;
     const int blocks = dw_fprop_partial_rows(static_cast<long long>(N) * (H / stride) * (W / stride), C);
-    if (stat_rows != nullptr) *stat_rows = blocks;
+    if (stat_rows != nullptr) *stat_rows = stat_acc ? 1 : blocks;
     const size_t smem = part_sum != nullptr ? static_cast<size_t>(rpi) * 2 * C * sizeof(float) : 0;
     B2C_LAUNCH(dw_fprop_kernel, blocks, 256, smem, s, static_cast<const uint4*>(x), w, static_cast<uint4*>(y), N, H, W, C,
-                                              c_valid, stride, part_sum, part_sq);
+                                              c_valid, stride, part_sum, part_sq, stat_acc);
     return cudaGetLastError();
 }
 

@@ -231,6 +231,106 @@ bn_act_apply_kernel(const uint4* __restrict__ y, const float* __restrict__ scale
 }
 
 // ------------------------------------------------------------------------------------------------
+// The same pass with the BatchNorm finalize folded into its prologue (b2c_bn_act_apply_stats): the producing conv
+// ACCUMULATED its per-channel sum / sum of squares into one row (fp32 atomics, B2cConvDesc.flags bit 9), so scale and
+// shift are a few operations per channel. Every block derives them for all C channels into shared memory (2*C floats
+// read from L2 per block); block 0 also publishes scale / shift / mean / rstd and updates the running statistics —
+// what bn_finalize_kernel did as a launch of its own, 20 times per ResNet-18 forward.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void bn_stats_to_smem(const BnStatArgs& st, int C, float* s_scale, float* s_shift,
+                                                 bool publish) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const double n = static_cast<double>(st.count);
+        const double mean = static_cast<double>(st.sum[c]) / n;
+        double var = static_cast<double>(st.sumsq[c]) / n - mean * mean;
+        if (var < 0.0) var = 0.0;
+        const float rstd = static_cast<float>(1.0 / sqrt(var + static_cast<double>(st.eps)));
+        const float sc = st.gamma[c] * rstd;
+        const float sh = st.beta[c] - static_cast<float>(mean) * sc;
+        s_scale[c] = sc;
+        s_shift[c] = sh;
+        if (publish) {
+            st.scale[c] = sc;
+            st.shift[c] = sh;
+            st.save_mean[c] = static_cast<float>(mean);
+            st.save_rstd[c] = rstd;
+            if (st.running_mean != nullptr) {
+                const double unbiased = n > 1.0 ? var * n / (n - 1.0) : var;
+                const float bias = st.conv_bias != nullptr ? st.conv_bias[c] : 0.f;   // reference tracks mean(conv + bias)
+                st.running_mean[c] = (1.f - st.momentum) * st.running_mean[c] + st.momentum * (static_cast<float>(mean) + bias);
+                st.running_var[c] = (1.f - st.momentum) * st.running_var[c] + st.momentum * static_cast<float>(unbiased);
+            }
+        }
+    }
+}
+
+template <bool kResAffine>
+__global__ void __launch_bounds__(256)
+bn_act_apply_stats_kernel(const uint4* __restrict__ y, const BnStatArgs st, const uint4* __restrict__ res,
+                          const BnStatArgs rst, uint4* __restrict__ out, long long nvec, int C, int relu,
+                          uint8_t* __restrict__ relu_bits) {
+    pdl_trigger_ew();
+    pdl_wait();
+    extern __shared__ float s_par[];      // [scale | shift | res_scale | res_shift], C floats each
+    float* s_scale = s_par;
+    float* s_shift = s_par + C;
+    bn_stats_to_smem(st, C, s_scale, s_shift, blockIdx.x == 0);
+    if (kResAffine) bn_stats_to_smem(rst, C, s_par + 2 * C, s_par + 3 * C, blockIdx.x == 0);
+    __syncthreads();
+    const int cvec = C >> 3;
+    const long long start = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    // the launcher makes the grid stride a multiple of C/8: a thread keeps its 8 channels' parameters in registers
+    const int c0 = static_cast<int>(start % cvec) << 3;
+    float sc[8], sh[8], rs[8], rb[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        sc[e] = s_scale[c0 + e];
+        sh[e] = s_shift[c0 + e];
+        rs[e] = kResAffine ? s_par[2 * C + c0 + e] : 1.f;
+        rb[e] = kResAffine ? s_par[3 * C + c0 + e] : 0.f;
+    }
+    auto finish = [&](const uint4 yraw, const uint4 rraw, long long v) {
+        float f[8];
+        unpack8(yraw, f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = fmaf(f[e], sc[e], sh[e]);
+        if (res != nullptr) {
+            float r[8];
+            unpack8(rraw, r);
+            if (kResAffine) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) r[e] = fmaf(r[e], rs[e], rb[e]);
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] += r[e];
+        }
+        if (relu) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = fmaxf(f[e], 0.f);
+        }
+        out[v] = pack8(f);
+        if (relu_bits != nullptr) {
+            unsigned bits = 0;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) bits |= (f[e] > 0.f ? 1u : 0u) << e;
+            relu_bits[v] = static_cast<uint8_t>(bits);
+        }
+    };
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    for (long long v = start; v < nvec; v += 2 * step) {
+        const long long v2 = v + step;
+        const bool two = v2 < nvec;
+        const uint4 y0 = ld_stream(y + v);
+        const uint4 y1 = two ? ld_stream(y + v2) : zero;
+        const uint4 r0 = res != nullptr ? ld_stream(res + v) : zero;
+        const uint4 r1 = (res != nullptr && two) ? ld_stream(res + v2) : zero;
+        finish(y0, r0, v);
+        if (two) finish(y1, r1, v2);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // BN(+ReLU) backward, pass 1: per-channel sums of dz and dz*y, where dz = dout * [act > 0].
 // Reference: autograd of F.relu + nn.BatchNorm2d (cudnn_batch_norm_backward), main.py:104.
 // If `dz_out` is given, the masked gradient is written back (so later passes and the shortcut
@@ -243,7 +343,7 @@ __global__ void __launch_bounds__(256)
 bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ act, const uint4* __restrict__ y,
                      uint4* __restrict__ dz_out, long long rows, int C, float* __restrict__ partial,
                      const float* __restrict__ relu_scale, const float* __restrict__ relu_shift,
-                     const uint8_t* __restrict__ relu_bits) {
+                     const uint8_t* __restrict__ relu_bits, int accumulate) {
     pdl_trigger_ew();
     pdl_wait();
     extern __shared__ float red[];  // [rows_per_iter][2][C]
@@ -295,7 +395,8 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ dout, const uint4* __restrict__ a
     for (int i = threadIdx.x; i < 2 * C; i += 256) {
         float s = 0.f;
         for (int k = 0; k < rpi; ++k) s += red[k * 2 * C + i];
-        partial[static_cast<size_t>(blockIdx.x) * 2 * C + i] = s;
+        if (accumulate) atomicAdd(partial + i, s);      // one row [2][C], zero-filled by the caller
+        else partial[static_cast<size_t>(blockIdx.x) * 2 * C + i] = s;
     }
 }
 
@@ -363,6 +464,58 @@ bn_bwd_apply_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, c
         unpack8(ld_stream(y + v), yy);
         // dz was not materialised: apply the ReLU mask here (same expression as the reduce pass)
         if (kMaskY) mask_from_y8(d, yy, relu_scale + cur_c0, relu_shift + cur_c0);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = fmaf(ca[e], d[e], fmaf(cb[e], yy[e], cc[e]));
+        if (add != nullptr) {
+            float a[8];
+            unpack8(ld_stream(add + v), a);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] += a[e];
+        }
+        dy[v] = pack8(o);
+    }
+}
+
+// Pass 3 with pass 2 folded into its prologue (b2c_bn_bwd_apply_stats): `sums` is ONE accumulated row [2][C]
+// (sum dz | sum dz*y). Every block derives A, B, Cc for all channels into shared memory; block 0 writes dgamma / dbeta.
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_stats_kernel(const uint4* __restrict__ dz, const uint4* __restrict__ y, const float* __restrict__ sums,
+                          float count, const float* __restrict__ gamma, const float* __restrict__ mean,
+                          const float* __restrict__ rstd, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                          const uint4* __restrict__ add, uint4* __restrict__ dy, long long nvec, int C,
+                          const float* __restrict__ relu_scale, const float* __restrict__ relu_shift) {
+    pdl_trigger_ew();
+    pdl_wait();
+    extern __shared__ float s_coef[];     // [A | B | Cc], C floats each
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        const double s1 = sums[c], s2 = sums[C + c];
+        const double mu = mean[c], rs = rstd[c], g = gamma[c], n = count;
+        const double dg = rs * (s2 - mu * s1);
+        if (blockIdx.x == 0) {
+            dgamma[c] = static_cast<float>(dg);
+            dbeta[c] = static_cast<float>(s1);
+        }
+        s_coef[c] = static_cast<float>(g * rs);
+        s_coef[C + c] = static_cast<float>(-g * rs * rs * dg / n);
+        s_coef[2 * C + c] = static_cast<float>(-g * rs * s1 / n + g * rs * rs * mu * dg / n);
+    }
+    __syncthreads();
+    const int cvec = C >> 3;
+    const long long start = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+    const long long step = static_cast<long long>(gridDim.x) * blockDim.x;
+    const int c0 = static_cast<int>(start % cvec) << 3;      // grid stride is a multiple of C/8 (launcher)
+    float ca[8], cb[8], cc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        ca[e] = s_coef[c0 + e];
+        cb[e] = s_coef[C + c0 + e];
+        cc[e] = s_coef[2 * C + c0 + e];
+    }
+    for (long long v = start; v < nvec; v += step) {
+        float d[8], yy[8], o[8];
+        unpack8(ld_stream(dz + v), d);
+        unpack8(ld_stream(y + v), yy);
+        if (relu_scale != nullptr) mask_from_y8(d, yy, relu_scale + c0, relu_shift + c0);
 #pragma unroll
         for (int e = 0; e < 8; ++e) o[e] = fmaf(ca[e], d[e], fmaf(cb[e], yy[e], cc[e]));
         if (add != nullptr) {
@@ -908,7 +1061,7 @@ int bn_bwd_partial_rows(long long rows, int C) {
 
 cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* y, void* dz_out, long long rows,
                                  int C, float* partial, const float* relu_scale, const float* relu_shift,
-                                 const uint8_t* relu_bits, cudaStream_t s) {
+                                 const uint8_t* relu_bits, cudaStream_t s, int accumulate) {
     const int cvec = C >> 3;
     if (cvec < 1 || cvec > 256) return cudaErrorInvalidValue;
     const int rpi = 256 / cvec;
@@ -917,16 +1070,16 @@ cudaError_t launch_bn_bwd_reduce(const void* dout, const void* act, const void* 
     if (relu_bits != nullptr)
         B2C_LAUNCH(bn_bwd_reduce_kernel<2>, blocks, 256, smem, s, static_cast<const uint4*>(dout), nullptr,
                                                          static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
-                                                         rows, C, partial, nullptr, nullptr, relu_bits);
+                                                         rows, C, partial, nullptr, nullptr, relu_bits, accumulate);
     else if (act == nullptr && relu_scale != nullptr)
         B2C_LAUNCH(bn_bwd_reduce_kernel<1>, blocks, 256, smem, s, static_cast<const uint4*>(dout), nullptr,
                                                          static_cast<const uint4*>(y), nullptr, rows, C, partial,
-                                                         relu_scale, relu_shift, nullptr);
+                                                         relu_scale, relu_shift, nullptr, accumulate);
     else
         B2C_LAUNCH(bn_bwd_reduce_kernel<0>, blocks, 256, smem, s, static_cast<const uint4*>(dout),
                                                          static_cast<const uint4*>(act),
                                                          static_cast<const uint4*>(y), static_cast<uint4*>(dz_out),
-                                                         rows, C, partial, nullptr, nullptr, nullptr);
+                                                         rows, C, partial, nullptr, nullptr, nullptr, accumulate);
     return cudaGetLastError();
 }
 
@@ -954,6 +1107,46 @@ cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coef
     else if (uniform) go(bn_bwd_apply_kernel<true, false>);
     else if (masky) go(bn_bwd_apply_kernel<false, true>);
     else go(bn_bwd_apply_kernel<false, false>);
+    return cudaGetLastError();
+}
+
+// Grid whose stride (grid * 256 threads) is a multiple of C/8 vectors, so a thread meets the same 8 channels in every
+// iteration: round the preferred grid down to a multiple of cvec / gcd(cvec, 256).
+static int uniform_grid(long long nvec, int cvec) {
+    int g = grid_for(nvec, 256, 148 * 8);
+    int a = cvec, b = 256;
+    while (b != 0) { const int t = a % b; a = b; b = t; }
+    const int unit = cvec / a;
+    if (g >= unit) g -= g % unit;
+    else g = unit;
+    return g;
+}
+
+cudaError_t launch_bn_act_apply_stats(const void* y, const BnStatArgs& st, const void* res, const BnStatArgs* rst,
+                                      void* out, long long rows, int C, int relu, uint8_t* relu_bits, cudaStream_t s) {
+    const long long nvec = rows * (C >> 3);
+    const int grid = uniform_grid(nvec, C >> 3);
+    const bool affine = res != nullptr && rst != nullptr;
+    const size_t smem = static_cast<size_t>(affine ? 4 : 2) * C * sizeof(float);
+    const BnStatArgs none = {};
+    if (affine)
+        B2C_LAUNCH(bn_act_apply_stats_kernel<true>, grid, 256, smem, s, static_cast<const uint4*>(y), st,
+                   static_cast<const uint4*>(res), *rst, static_cast<uint4*>(out), nvec, C, relu, relu_bits);
+    else
+        B2C_LAUNCH(bn_act_apply_stats_kernel<false>, grid, 256, smem, s, static_cast<const uint4*>(y), st,
+                   static_cast<const uint4*>(res), none, static_cast<uint4*>(out), nvec, C, relu, relu_bits);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_bn_bwd_apply_stats(const void* dz, const void* y, const float* sums, float count,
+                                      const float* gamma, const float* mean, const float* rstd, float* dgamma,
+                                      float* dbeta, const void* add, void* dy, long long rows, int C,
+                                      const float* relu_scale, const float* relu_shift, cudaStream_t s) {
+    const long long nvec = rows * (C >> 3);
+    const int grid = uniform_grid(nvec, C >> 3);
+    B2C_LAUNCH(bn_bwd_apply_stats_kernel, grid, 256, static_cast<size_t>(3) * C * sizeof(float), s,
+               static_cast<const uint4*>(dz), static_cast<const uint4*>(y), sums, count, gamma, mean, rstd, dgamma,
+               dbeta, static_cast<const uint4*>(add), static_cast<uint4*>(dy), nvec, C, relu_scale, relu_shift);
     return cudaGetLastError();
 }
 
@@ -1096,7 +1289,7 @@ cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const
     if (e != cudaSuccess) return e;
     const int prow = bn_bwd_partial_rows(rows, C);               // capped at kBnBwdMaxPartialRows == kNoAllocMaxRows
     if (prow > kNoAllocMaxRows) return cudaErrorInvalidValue;    // never with the shared constant; guards a future edit
-    e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, nullptr, nullptr, nullptr, s);
+    e = launch_bn_bwd_reduce(dout, act, y, dz_out, rows, C, scratch, nullptr, nullptr, nullptr, s, 0);
     if (e != cudaSuccess) return e;
     return launch_bn_bwd_finalize(scratch, prow, C, count, gamma, mean, rstd, dgamma, dbeta, coefA, coefB, coefC, s);
 }

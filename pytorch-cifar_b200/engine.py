@@ -278,6 +278,10 @@ def _bn_views(u, eng, bn_name, C):
     u.dgamma, u.dbeta = eng.grad_vec(bn_name + ".weight", C), eng.grad_vec(bn_name + ".bias", C)
     u.rm, u.rv = eng.buffer_vec(bn_name + ".running_mean", C), eng.buffer_vec(bn_name + ".running_var", C)
     u.scale, u.shift, u.mean, u.rstd = (eng.new_f32(C) for _ in range(4))
+    if not hasattr(u, "fsum"):
+        u.fsum = eng.new_stat(2 * C, forward=True)     # [sum | sum of squares] of y, accumulated by its producer
+    u.bsum = eng.new_stat(2 * C, forward=False)        # [sum dz | sum dz*y] of the backward pass
+    u.make_stat_rec()
 
 
 def resnet50_spec(num_classes=10):
@@ -330,7 +334,81 @@ ASYNC_WGRAD = os.environ.get("B2C_ASYNC_WGRAD", "1") != "0"
 CTA_PAIR = os.environ.get("B2C_CTA_PAIR", "all")
 
 
-class ConvUnit:
+# 1 = BatchNorm statistics are accumulated into one row per BatchNorm (fp32 atomics in the producing kernel's epilogue)
+# and finalized in the prologue of the pass that applies them (b2c_bn_act_apply_stats / b2c_bn_bwd_apply_stats): no
+# bn_finalize / bn_bwd_finalize launches (40 of a ResNet-18 step's 156); 0 = per-CTA partial rows + finalize kernels
+FUSED_FINALIZE = os.environ.get("B2C_FUSED_FINALIZE", "0") != "0"
+
+
+class _BNOps:
+    """BatchNorm forward apply / backward of a unit that has y, rows, cout and the _bn_views fields."""
+
+    def make_stat_rec(self):
+        C = self.cout
+        self.stat_rec = ops.bn_stats(self.fsum[:C], self.fsum[C:], self.gamma, self.beta, self.rows, BN_EPS, BN_MOMENTUM,
+                                     self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd,
+                                     conv_bias=getattr(self, "conv_bias", None))
+
+    def bn_stats(self, eng, training):
+        if training:
+            ops.bn_finalize(self.ps, self.pq, self.stat_rows, self.cout, self.rows, self.gamma, self.beta,
+                            BN_EPS, BN_MOMENTUM, self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd,
+                            conv_bias=getattr(self, "conv_bias", None))
+        else:
+            ops.bn_eval_scale_shift(self.cout, self.gamma, self.beta, self.rm, self.rv, BN_EPS, self.scale,
+                                    self.shift, conv_bias=getattr(self, "conv_bias", None))
+
+    def bn_apply(self, eng, training, out, relu=True, res=None, res_unit=None, relu_bits=None):
+        """out = act(bn(y) + residual), residual = `res` (identity shortcut) or res_unit's own BatchNorm of
+        res_unit.y (conv shortcut) — models/resnet.py:47-50. With FUSED_FINALIZE (training) one launch finalizes
+        the statistics of both BatchNorms and applies them; otherwise bn_stats() (for res_unit: issued by the
+        caller, on the side stream) followed by the apply pass."""
+        if FUSED_FINALIZE and training:
+            ops.bn_act_apply_stats(self.y, self.stat_rec, out, self.rows, self.cout, relu=relu,
+                                   res=res_unit.y if res_unit is not None else res,
+                                   res_bn=res_unit.stat_rec if res_unit is not None else None, relu_bits=relu_bits)
+            return
+        self.bn_stats(eng, training)
+        if res_unit is not None:
+            ops.bn_act_apply(self.y, self.scale, self.shift, out, self.rows, self.cout, relu=relu, relu_bits=relu_bits,
+                             res=res_unit.y, res_scale=res_unit.scale, res_shift=res_unit.shift)
+        else:
+            ops.bn_act_apply(self.y, self.scale, self.shift, out, self.rows, self.cout, relu=relu, relu_bits=relu_bits,
+                             res=res)
+
+    def bn_backward(self, eng, dout, act, dz_out, dy, add=None, relu_from_y=False, relu_bits=None):
+        """dout: grad w.r.t. act(bn(y)) (or w.r.t. bn(y) when act is None). Writes dz (optional) and
+        dy = dBN/dy (+ add). relu_from_y: the unit is a plain relu(bn(y)) and nothing else needs dz: the mask is
+        recomputed from y with this BN's own scale/shift, so neither `act` is read nor dz written."""
+        reduce = ops.bn_bwd_reduce_acc if FUSED_FINALIZE else ops.bn_bwd_reduce
+        part = self.bsum if FUSED_FINALIZE else eng.bwd_partial
+        if relu_from_y:
+            reduce(dout, None, self.y, None, self.rows, self.cout, part, self.scale, self.shift)
+        elif relu_bits is not None:        # mask saved by the forward apply pass: `act` is not read
+            reduce(dout, None, self.y, dz_out, self.rows, self.cout, part, relu_bits=relu_bits)
+        else:
+            reduce(dout, act, self.y, dz_out, self.rows, self.cout, part)
+        src = dz_out if (dz_out is not None and not relu_from_y) else dout
+        self._bn_bwd_finish(eng, src, dy, ops.bn_bwd_partial_rows(self.rows, self.cout), add,
+                            self.scale if relu_from_y else None, self.shift if relu_from_y else None)
+
+    def bn_backward_from_partial(self, eng, dz, dy, prow, add=None):
+        """Second half of bn_backward when the producer of dz already masked it and reduced it (dgrad_bn)."""
+        self._bn_bwd_finish(eng, dz, dy, prow, add, None, None)
+
+    def _bn_bwd_finish(self, eng, src, dy, prow, add, relu_scale, relu_shift):
+        if FUSED_FINALIZE:
+            ops.bn_bwd_apply_stats(src, self.y, self.bsum, self.rows, self.gamma, self.mean, self.rstd, self.dgamma,
+                                   self.dbeta, dy, self.rows, self.cout, add=add, relu_scale=relu_scale,
+                                   relu_shift=relu_shift)
+            return
+        ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
+                            self.dgamma, self.dbeta, eng.coef_a, eng.coef_b, eng.coef_c)
+        ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add,
+                         relu_scale=relu_scale, relu_shift=relu_shift)
+
+
+class ConvUnit(_BNOps):
     """One conv (+ the BatchNorm that follows it): descriptors, operand views, statistic buffers.
     Channel counts are the reference's; tensors are laid out with channels padded to multiples of 64
     (self.cin / self.cout are those layout widths, *_true the reference's)."""
@@ -348,12 +426,13 @@ class ConvUnit:
         self.y = eng.new_act(N, self.Ho, self.Wo, cout_p)
         if stem:
             # the 3-channel stem runs as a 1x1 GEMM over an im2col operand (k = 27 padded to 64)
-            self.desc = ops.conv_desc(N, H, W, 64, cout_p, 1, 1)
+            self.desc = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, flags=512 if FUSED_FINALIZE else 0)
             self.desc_w = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, cin_valid=27, kflat_cin=3, cout_valid=cout)
         else:
             halo_shape = k == 3 and stride == 1 and H == W and W in (32, 16, 8)
             pair = CTA_PAIR == "all" or (CTA_PAIR == "halo" and halo_shape)
-            self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, flags=128 if pair else 0)
+            self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride,
+                                      flags=(128 if pair else 0) | (512 if FUSED_FINALIZE else 0))
             self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout,
                                         flags=(32 | (128 if CTA_PAIR != "0" else 0)) if (name + ".weight") in eng.tco else 0)
         self.eng_scratch = eng.wgrad_scratch
@@ -365,48 +444,25 @@ class ConvUnit:
             self.pq = torch.zeros(ops.MAX_STAT_ROWS, _pad64(cout), device=eng.device)
         else:
             self.ps, self.pq = eng.part_sum, eng.part_sq
+        self.fsum = eng.new_stat(2 * cout_p, forward=True)     # statistics of y (also read by a PreAct block's bn1)
         self.wf = eng.wf_view(name)
         self.wd = None if stem else eng.wd_view(name)
         self.wd10 = None if stem else eng.wd10_view(name)
         self.dw = eng.grad_flat(name + ".weight")      # storage order: OIHW, or [tap][cin][cout] (eng.tco)
-        if bn_name is not None:
-            _bn_views(self, eng, bn_name, cout_p)
         # a conv bias (VGG) is never added to y — the BatchNorm cancels it — but the running mean tracks it
         self.conv_bias = eng.param_view(name + ".bias") if (name + ".bias") in eng.p_off else None
+        if bn_name is not None:
+            _bn_views(self, eng, bn_name, cout_p)
 
     # ---- forward pieces
     def fprop(self, eng, stats=True, add_src=None):
-        ps, pq = (self.ps, self.pq) if stats else (None, None)
+        if FUSED_FINALIZE:
+            ps, pq = (self.fsum[:self.cout], self.fsum[self.cout:]) if stats else (None, None)
+        else:
+            ps, pq = (self.ps, self.pq) if stats else (None, None)
         self.stat_rows = ops.conv_fprop(self.desc, self.x, self.wf, self.y, ps, pq, add_src=add_src)
 
-    def bn_stats(self, eng, training):
-        if training:
-            ops.bn_finalize(self.ps, self.pq, self.stat_rows, self.cout, self.rows, self.gamma, self.beta,
-                            BN_EPS, BN_MOMENTUM, self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd,
-                            conv_bias=getattr(self, "conv_bias", None))
-        else:
-            ops.bn_eval_scale_shift(self.cout, self.gamma, self.beta, self.rm, self.rv, BN_EPS, self.scale,
-                                    self.shift, conv_bias=getattr(self, "conv_bias", None))
-
     # ---- backward pieces
-    def bn_backward(self, eng, dout, act, dz_out, dy, add=None, relu_from_y=False, relu_bits=None):
-        """dout: grad w.r.t. act(bn(y)) (or w.r.t. bn(y) when act is None). Writes dz (optional) and
-        dy = dBN/dy (+ add). relu_from_y: the unit is a plain relu(bn(y)) and nothing else needs dz: the mask is
-        recomputed from y with this BN's own scale/shift, so neither `act` is read nor dz written."""
-        prow = ops.bn_bwd_partial_rows(self.rows, self.cout)
-        if relu_from_y:
-            ops.bn_bwd_reduce(dout, None, self.y, None, self.rows, self.cout, eng.bwd_partial, self.scale, self.shift)
-        elif relu_bits is not None:        # mask saved by the forward apply pass: `act` is not read
-            ops.bn_bwd_reduce(dout, None, self.y, dz_out, self.rows, self.cout, eng.bwd_partial, relu_bits=relu_bits)
-        else:
-            ops.bn_bwd_reduce(dout, act, self.y, dz_out, self.rows, self.cout, eng.bwd_partial)
-        ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
-                            self.dgamma, self.dbeta, eng.coef_a, eng.coef_b, eng.coef_c)
-        src = dz_out if (dz_out is not None and not relu_from_y) else dout
-        ops.bn_bwd_apply(src, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add,
-                         relu_scale=self.scale if relu_from_y else None,
-                         relu_shift=self.shift if relu_from_y else None)
-
     def wgrad(self, dy):
         self.eng.run_side(lambda: ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch))
 
@@ -418,13 +474,7 @@ class ConvUnit:
         and emits the BatchNorm-backward partial sums (b2c_conv_dgrad_bn). Returns the partial-row count for
         bn_unit.bn_backward_from_partial."""
         return ops.conv_dgrad_bn(self.desc, dy, self.wd, dz, bn_unit.y, bn_unit.scale, bn_unit.shift,
-                                 eng.bwd_partial, add_src)
-
-    def bn_backward_from_partial(self, eng, dz, dy, prow, add=None):
-        """Second half of bn_backward when the producer of dz already masked it and reduced it (dgrad_bn)."""
-        ops.bn_bwd_finalize(eng.bwd_partial, prow, self.cout, self.rows, self.gamma, self.mean, self.rstd,
-                            self.dgamma, self.dbeta, eng.coef_a, eng.coef_b, eng.coef_c)
-        ops.bn_bwd_apply(dz, self.y, eng.coef_a, eng.coef_b, eng.coef_c, dy, self.rows, self.cout, add=add)
+                                 bn_unit.bsum if FUSED_FINALIZE else eng.bwd_partial, add_src)
 
     def dgrad_with_shortcut(self, dy, dy_sc, sc, dx):
         """dx = dgrad(self, dy) + dgrad(sc, dy_sc): the two consumers of a down-sampling block's input
@@ -436,7 +486,7 @@ class ConvUnit:
             self.dgrad(dy, dx, add_src=dx)
 
 
-class DwUnit:
+class DwUnit(_BNOps):
     """Depthwise 3x3 conv + BatchNorm (models/mobilenetv2.py:20-21)."""
 
     def __init__(self, eng, name, bn_name, x, C, stride, H, W):
@@ -455,7 +505,13 @@ class DwUnit:
         _bn_views(self, eng, bn_name, self.cout)
 
     def fprop(self, eng):
-        self.stat_rows = ops.dwconv_fprop(self.x, self.w, self.y, self.c_true, self.stride, eng.part_sum, eng.part_sq)
+        if FUSED_FINALIZE:
+            ops.dwconv_fprop_acc(self.x, self.w, self.y, self.c_true, self.stride, self.fsum[:self.cout],
+                                 self.fsum[self.cout:])
+            self.stat_rows = 1
+        else:
+            self.stat_rows = ops.dwconv_fprop(self.x, self.w, self.y, self.c_true, self.stride, eng.part_sum,
+                                              eng.part_sq)
 
     def wgrad(self, dy):
         self.eng.run_side(lambda: ops.dwconv_wgrad(self.x, dy, self.dw, self.c_true, self.stride))
@@ -482,6 +538,13 @@ class Engine:
         self.coef_a, self.coef_b, self.coef_c = (torch.zeros(2048, **f32) for _ in range(3))
         self.wgrad_scratch = share_from.wgrad_scratch if share_from is not None else \
             torch.zeros(ops.WGRAD_SCRATCH_FLOATS, **f32)
+        # BatchNorm statistic accumulators (FUSED_FINALIZE): [sum | sumsq] per BatchNorm for the forward pass, zeroed by
+        # forward(); [sum dz | sum dz*y] for the backward pass, zeroed by zero_grad().
+        nstat = sum(2 * _pad64(sh[0]) for name, sh in spec["buffers"].items() if name.endswith("running_mean"))
+        nconv = sum(2 * _pad64(sh[0]) for name, sh in spec["params"].items() if len(sh) == 4)
+        self._stat_f = torch.zeros(nstat + nconv + 64, **f32)
+        self._stat_b = torch.zeros(nstat + 64, **f32)
+        self._stat_used = [0, 0]
         self.fwd_ops, self.bwd_ops = [], []
         if spec["family"] == "resnet":
             self._build_resnet()
@@ -632,6 +695,15 @@ class Engine:
     def new_f32(self, *shape):
         return torch.zeros(*shape, device=self.device, dtype=torch.float32)
 
+    def new_stat(self, n, forward):
+        """n floats of the forward / backward statistic accumulator arena (16-byte aligned)."""
+        arena, k = (self._stat_f, 0) if forward else (self._stat_b, 1)
+        off = self._stat_used[k]
+        if off + n > arena.numel():
+            raise RuntimeError("statistic arena too small for this plan")
+        self._stat_used[k] = _align(off + n, 4)
+        return arena[off:off + n]
+
     # ------------------------------------------------------------------ parameters in / out
     def load_params(self, named_params, named_buffers=None):
         """Copy reference-layout tensors (name -> tensor, fp32) into the arenas and refresh the bf16 copies."""
@@ -669,8 +741,7 @@ class Engine:
 
         def fwd_stem(training):
             stem.fprop(self, True)
-            stem.bn_stats(self, training)
-            ops.bn_act_apply(stem.y, stem.scale, stem.shift, a0, stem.rows, 64, relu=True)
+            stem.bn_apply(self, training, a0)
         F.append(fwd_stem)
 
         x, H, W = a0, 32, 32
@@ -692,18 +763,15 @@ class Engine:
 
             def fwd_block(training, c1=c1, a1=a1, c2=c2, cs=cs, out=out, x=x, bits=bits):
                 if cs is not None:          # the shortcut branch (own statistics scratch) overlaps conv1 -> conv2
-                    self.run_side(lambda: (cs.fprop(self), cs.bn_stats(self, training)))
+                    self.run_side(lambda: (cs.fprop(self), None if (FUSED_FINALIZE and training) else cs.bn_stats(self, training)))
                 c1.fprop(self)
-                c1.bn_stats(self, training)
-                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
+                c1.bn_apply(self, training, a1)
                 c2.fprop(self)
-                c2.bn_stats(self, training)
                 if cs is not None:
                     self.join_side()
-                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, relu_bits=bits, res=cs.y,
-                                     res_scale=cs.scale, res_shift=cs.shift)
+                    c2.bn_apply(self, training, out, res_unit=cs, relu_bits=bits)
                 else:
-                    ops.bn_act_apply(c2.y, c2.scale, c2.shift, out, c2.rows, c2.cout, relu=True, relu_bits=bits, res=x)
+                    c2.bn_apply(self, training, out, res=x, relu_bits=bits)
             F.append(fwd_block)
             x, H, W = out, Ho, Wo
 
@@ -812,8 +880,7 @@ class Engine:
 
             def fwd(training, u=u, act=act, pooled=pooled):
                 u.fprop(self)
-                u.bn_stats(self, training)
-                ops.bn_act_apply(u.y, u.scale, u.shift, act, u.rows, u.cout, relu=True)
+                u.bn_apply(self, training, act)
                 if pooled is not None:
                     ops.maxpool2x2_fwd(act, pooled)
             F.append(fwd)
@@ -868,23 +935,21 @@ class Engine:
         self.units = [stem]
         F, blocks = self.fwd_ops, []
 
-        class PreBN:
+        class PreBN(_BNOps):
             """BatchNorm applied to tensor `y` produced by `producer` (whose epilogue emitted the statistics)."""
-            def __init__(s, eng, bn_name, y, C, rows):
-                s.y, s.cout, s.rows = y, C, rows
+            def __init__(s, eng, bn_name, producer, C, rows):
+                s.y, s.cout, s.rows = producer.y, C, rows
                 s.ps, s.pq = eng.part_sum, eng.part_sq
+                s.fsum = producer.fsum
                 _bn_views(s, eng, bn_name, C)
             stat_rows = 0
-            bn_stats = ConvUnit.bn_stats
-            bn_backward = ConvUnit.bn_backward
-            bn_backward_from_partial = ConvUnit.bn_backward_from_partial
 
         F.append(lambda training: stem.fprop(self, True))
         x, H, W, producer = stem.y, 32, 32, stem
         nblk = len(spec["blocks"])
         for bi, b in enumerate(spec["blocks"]):
             name, cin, cout, s = b["name"], b["cin"], b["cout"], b["stride"]
-            bn1 = PreBN(self, name + ".bn1", x, cin, N * H * W)
+            bn1 = PreBN(self, name + ".bn1", producer, cin, N * H * W)
             a = self.new_act(N, H, W, cin)
             c1 = ConvUnit(self, name + ".conv1", name + ".bn2", a, cin, cout, 3, s, H, W)
             Ho, Wo = H // s, W // s
@@ -897,13 +962,11 @@ class Engine:
 
             def fwd(training, bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, cs=cs, x=x, producer=producer, last=last):
                 bn1.stat_rows = producer.stat_rows
-                bn1.bn_stats(self, training)
-                ops.bn_act_apply(x, bn1.scale, bn1.shift, a, bn1.rows, bn1.cout, relu=True)
+                bn1.bn_apply(self, training, a)
                 if cs is not None:          # the shortcut conv overlaps conv1 on the side stream
                     self.run_side(lambda: cs.fprop(self, stats=False))
                 c1.fprop(self)
-                c1.bn_stats(self, training)
-                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a2, c1.rows, c1.cout, relu=True)
+                c1.bn_apply(self, training, a2)
                 if cs is not None:
                     self.join_side()
                 c2.fprop(self, stats=not last, add_src=(cs.y if cs is not None else x))
@@ -951,8 +1014,7 @@ class Engine:
 
         def fwd_stem(training):
             stem.fprop(self, True)
-            stem.bn_stats(self, training)
-            ops.bn_act_apply(stem.y, stem.scale, stem.shift, a0, stem.rows, 64, relu=True)
+            stem.bn_apply(self, training, a0)
         F.append(fwd_stem)
         x, H, W = a0, 32, 32
         for b in spec["blocks"]:
@@ -972,22 +1034,17 @@ class Engine:
 
             def fwd(training, c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, x=x, bits=bits):
                 if cs is not None:          # shortcut branch on the side stream (own statistics scratch)
-                    self.run_side(lambda: (cs.fprop(self), cs.bn_stats(self, training)))
+                    self.run_side(lambda: (cs.fprop(self), None if (FUSED_FINALIZE and training) else cs.bn_stats(self, training)))
                 c1.fprop(self)
-                c1.bn_stats(self, training)
-                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
+                c1.bn_apply(self, training, a1)
                 c2.fprop(self)
-                c2.bn_stats(self, training)
-                ops.bn_act_apply(c2.y, c2.scale, c2.shift, a2, c2.rows, c2.cout, relu=True)
+                c2.bn_apply(self, training, a2)
                 c3.fprop(self)
-                c3.bn_stats(self, training)
                 if cs is not None:
                     self.join_side()
-                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=cs.y,
-                                     res_scale=cs.scale, res_shift=cs.shift, relu_bits=bits)
+                    c3.bn_apply(self, training, out, res_unit=cs, relu_bits=bits)
                 else:
-                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=True, res=x,
-                                     relu_bits=bits)
+                    c3.bn_apply(self, training, out, res=x, relu_bits=bits)
             F.append(fwd)
             x, H, W = out, Ho, Wo
         fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
@@ -1050,8 +1107,7 @@ class Engine:
 
         def fwd_stem(training):
             stem.fprop(self, True)
-            stem.bn_stats(self, training)
-            ops.bn_act_apply(stem.y, stem.scale, stem.shift, a0, stem.rows, stem.cout, relu=True)
+            stem.bn_apply(self, training, a0)
         F.append(fwd_stem)
         x, H, W = a0, 32, 32
         for b in spec["blocks"]:
@@ -1071,22 +1127,17 @@ class Engine:
 
             def fwd(training, c1=c1, a1=a1, dw=dw, a2=a2, c3=c3, cs=cs, identity=identity, out=out, x=x):
                 if cs is not None:          # shortcut branch on the side stream (own statistics scratch)
-                    self.run_side(lambda: (cs.fprop(self), cs.bn_stats(self, training)))
+                    self.run_side(lambda: (cs.fprop(self), None if (FUSED_FINALIZE and training) else cs.bn_stats(self, training)))
                 c1.fprop(self)
-                c1.bn_stats(self, training)
-                ops.bn_act_apply(c1.y, c1.scale, c1.shift, a1, c1.rows, c1.cout, relu=True)
+                c1.bn_apply(self, training, a1)
                 dw.fprop(self)
-                dw.bn_stats(self, training)
-                ops.bn_act_apply(dw.y, dw.scale, dw.shift, a2, dw.rows, dw.cout, relu=True)
+                dw.bn_apply(self, training, a2)
                 c3.fprop(self)
-                c3.bn_stats(self, training)
                 if cs is not None:
                     self.join_side()
-                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=False, res=cs.y,
-                                     res_scale=cs.scale, res_shift=cs.shift)
+                    c3.bn_apply(self, training, out, relu=False, res_unit=cs)
                 else:
-                    ops.bn_act_apply(c3.y, c3.scale, c3.shift, out, c3.rows, c3.cout, relu=False,
-                                     res=(x if identity else None))
+                    c3.bn_apply(self, training, out, relu=False, res=(x if identity else None))
             F.append(fwd)
             x, H, W = out, Ho, Wo
         ch = ConvUnit(self, "conv2", "bn2", x, 320, 1280, 1, 1, H, W)
@@ -1095,8 +1146,7 @@ class Engine:
 
         def fwd_last(training):
             ch.fprop(self)
-            ch.bn_stats(self, training)
-            ops.bn_act_apply(ch.y, ch.scale, ch.shift, ah, ch.rows, ch.cout, relu=True)
+            ch.bn_apply(self, training, ah)
         F.append(fwd_last)
         fwd_head, bwd_head, dout = self._build_head(ah, H, W, "linear.weight", "linear.bias")
         F.append(fwd_head)
@@ -1152,6 +1202,8 @@ class Engine:
 
     # ------------------------------------------------------------------ execution
     def forward(self, training=True):
+        if FUSED_FINALIZE:
+            self._stat_f.zero_()
         for op in self.fwd_ops:
             op(training)
         return self.logits
@@ -1224,11 +1276,9 @@ class Engine:
 
     def zero_grad(self):
         self.G.zero_()
+        if FUSED_FINALIZE:
+            self._stat_b.zero_()
 
     def activation_bytes(self):
         return sum(t.numel() * t.element_size() for t in self._acts)
 
-
-DwUnit.bn_stats = ConvUnit.bn_stats
-DwUnit.bn_backward = ConvUnit.bn_backward
-DwUnit.bn_backward_from_partial = ConvUnit.bn_backward_from_partial

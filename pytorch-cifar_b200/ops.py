@@ -8,7 +8,7 @@ import os
 import torch
 
 from . import _lib
-from ._lib import ConvDesc, RepackEntry, check
+from ._lib import BnStats, ConvDesc, RepackEntry, check
 
 CIFAR_MEAN = (0.4914, 0.4822, 0.4465)   # reference main.py:34
 CIFAR_STD = (0.2023, 0.1994, 0.2010)    # reference main.py:34
@@ -111,6 +111,16 @@ def dwconv_fprop(x, weight, y, c_valid, stride, part_sum=None, part_sq=None):
     return rows.value
 
 
+def dwconv_fprop_acc(x, weight, y, c_valid, stride, stat_sum, stat_sq):
+    """Depthwise 3x3 whose BatchNorm sums are accumulated into one zero-filled row (for bn_act_apply_stats)."""
+    lib = _lib.load()
+    n, h, w, c = x.shape
+    _need(x, torch.bfloat16, "x"); _need(y, torch.bfloat16, "y"); _need(weight, torch.float32, "weight")
+    _need(stat_sum, torch.float32, "sum"); _need(stat_sq, torch.float32, "sumsq")
+    check(lib.b2c_dwconv_fprop_acc(_p(x), _p(weight), _p(y), n, h, w, c, c_valid, stride, _p(stat_sum), _p(stat_sq),
+                                   _stream()), "b2c_dwconv_fprop_acc")
+
+
 def dwconv_dgrad(dy, weight, dx, c_valid, stride):
     lib = _lib.load()
     n, h, w, c = dx.shape
@@ -151,6 +161,40 @@ def bn_act_apply(y, scale, shift, out, rows, channels, relu=True, res=None, res_
     _need(relu_bits, torch.uint8, "relu_bits")
     check(lib.b2c_bn_act_apply(_p(y), _p(scale), _p(shift), _p(res), _p(res_scale), _p(res_shift), _p(out),
                                rows, channels, 1 if relu else 0, _p(relu_bits), _stream()), "b2c_bn_act_apply")
+
+
+def bn_stats(stat_sum, stat_sq, gamma, beta, count, eps, momentum, running_mean, running_var, scale, shift, save_mean,
+             save_rstd, conv_bias=None):
+    """B2cBnStats record for bn_act_apply_stats (keep the tensors alive for as long as the record is used)."""
+    def a(t):
+        return None if t is None else t.data_ptr()
+    return BnStats(a(stat_sum), a(stat_sq), a(gamma), a(beta), a(conv_bias), a(running_mean), a(running_var), a(scale),
+                   a(shift), a(save_mean), a(save_rstd), float(count), float(eps), float(momentum))
+
+
+def bn_act_apply_stats(y, bn, out, rows, channels, relu=True, res=None, res_bn=None, relu_bits=None):
+    """bn_finalize + bn_act_apply in one launch from accumulated statistics (bn / res_bn: ops.bn_stats records)."""
+    lib = _lib.load()
+    _need(relu_bits, torch.uint8, "relu_bits")
+    check(lib.b2c_bn_act_apply_stats(_p(y), ctypes.byref(bn), _p(res), None if res_bn is None else ctypes.byref(res_bn),
+                                     _p(out), rows, channels, 1 if relu else 0, _p(relu_bits), _stream()),
+          "b2c_bn_act_apply_stats")
+
+
+def bn_bwd_reduce_acc(dout, act, y, dz_out, rows, channels, sums, relu_scale=None, relu_shift=None, relu_bits=None):
+    lib = _lib.load()
+    _need(relu_bits, torch.uint8, "relu_bits"); _need(sums, torch.float32, "sums")
+    check(lib.b2c_bn_bwd_reduce_acc(_p(dout), _p(act), _p(y), _p(dz_out), rows, channels, _p(sums), _p(relu_scale),
+                                    _p(relu_shift), _p(relu_bits), _stream()), "b2c_bn_bwd_reduce_acc")
+
+
+def bn_bwd_apply_stats(dz, y, sums, count, gamma, save_mean, save_rstd, dgamma, dbeta, dy, rows, channels, add=None,
+                       relu_scale=None, relu_shift=None):
+    """bn_bwd_finalize + bn_bwd_apply in one launch from one accumulated row sums[2][channels]."""
+    lib = _lib.load()
+    check(lib.b2c_bn_bwd_apply_stats(_p(dz), _p(y), _p(sums), float(count), _p(gamma), _p(save_mean), _p(save_rstd),
+                                     _p(dgamma), _p(dbeta), _p(add), _p(dy), rows, channels, _p(relu_scale),
+                                     _p(relu_shift), _stream()), "b2c_bn_bwd_apply_stats")
 
 
 def bn_bwd_partial_rows(rows, channels):

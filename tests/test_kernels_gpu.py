@@ -770,3 +770,140 @@ def test_conv_cta_pair_kernel(ops, shape):
                 dxs.append(dx)
             assert torch.isfinite(dxs[1].float()).all(), pair
             assert rel_err(dxs[1].float(), dxs[0].float()) < 1e-5, pair
+
+
+# ------------------------------------------------------------------------------------------------
+# Statistics accumulated into one row + finalize folded into the apply passes (B2cConvDesc.flags bit 9,
+# b2c_bn_act_apply_stats, b2c_bn_bwd_reduce_acc, b2c_bn_bwd_apply_stats) against the two / three-call forms.
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape", [(4, 32, 32, 64, 64, 3, 1), (64, 32, 32, 64, 64, 3, 1), (8, 16, 16, 128, 128, 3, 1),
+                                   (16, 8, 8, 256, 256, 3, 1), (32, 4, 4, 512, 512, 3, 1), (8, 32, 32, 64, 128, 3, 2),
+                                   (8, 32, 32, 64, 128, 1, 2), (5, 4, 4, 512, 512, 3, 1)])
+@pytest.mark.parametrize("pair", [0, 128])
+def test_conv_statistics_accumulated(ops, shape, pair):
+    n, h, w, cin, cout, k, stride = shape
+    x = nhwc_bf16(n, h, w, cin, 81)
+    wf = ops.pack_weight_fprop(weight(cout, cin, k, 82))
+    ho, wo = h // stride, w // stride
+    y0 = torch.empty(n, ho, wo, cout, device="cuda", dtype=torch.bfloat16)
+    ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    rows = ops.conv_fprop(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=pair), x, wf, y0, ps, pq)
+    y1 = torch.empty_like(y0)
+    acc = torch.zeros(2, cout, device="cuda")
+    for rep in (1, 2):                                    # accumulates: a second call doubles the sums
+        r1 = ops.conv_fprop(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=pair | 512), x, wf, y1, acc[0], acc[1])
+        torch.cuda.synchronize()
+        assert r1 == 1 and torch.equal(y0, y1)
+        assert (acc[0] - rep * ps[:rows].sum(0)).abs().max() <= 1e-4 * ps[:rows].abs().sum(0).max() + 1e-3
+        assert rel_err(acc[1], rep * pq[:rows].sum(0)) < 1e-5
+    # the fused dgrad + BatchNorm-backward reduction, same flag
+    dy = nhwc_bf16(n, ho, wo, cout, 83)
+    wd = ops.pack_weight_dgrad(weight(cout, cin, k, 82))
+    if not (k == 1 and stride == 2):
+        y_bn = nhwc_bf16(n, h, w, cin, 84)
+        g = torch.Generator(device="cuda").manual_seed(85)
+        scale = torch.rand(cin, device="cuda", generator=g) + 0.5
+        shift = torch.randn(cin, device="cuda", generator=g) * 0.3
+        dz0, dz1 = torch.empty(n, h, w, cin, device="cuda", dtype=torch.bfloat16), None
+        part = torch.zeros(148, 2, cin, device="cuda")
+        prow = ops.conv_dgrad_bn(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=pair), dy, wd, dz0, y_bn, scale,
+                                 shift, part)
+        dz1 = torch.empty_like(dz0)
+        sums = torch.zeros(2, cin, device="cuda")
+        p1 = ops.conv_dgrad_bn(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=pair | 512), dy, wd, dz1, y_bn,
+                               scale, shift, sums)
+        torch.cuda.synchronize()
+        assert p1 == 1 and torch.equal(dz0, dz1)
+        ref = part[:prow].sum(0)
+        assert (sums - ref).abs().max() <= 1e-4 * part[:prow].abs().sum(0).max() + 1e-3
+
+
+@pytest.mark.parametrize("C,rows", [(64, 4096), (192, 1000), (512, 80), (1280, 333), (64, 131072)])
+def test_bn_apply_with_fused_finalize(ops, C, rows):
+    """b2c_bn_act_apply_stats == b2c_bn_finalize + b2c_bn_act_apply: same scale / shift / mean / rstd / running
+    statistics and the same output bits, with identity and BatchNorm'ed residuals and the ReLU bit mask."""
+    g = torch.Generator(device="cuda").manual_seed(90)
+    y = (torch.randn(rows, C, device="cuda", generator=g) * 2 + 0.5).to(torch.bfloat16)
+    r = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+
+    def bn_inputs(t, seed):
+        gg = torch.Generator(device="cuda").manual_seed(seed)
+        tf = t.float()
+        d = dict(sum=tf.sum(0).contiguous(), sq=(tf * tf).sum(0).contiguous(),
+                 gamma=torch.rand(C, device="cuda", generator=gg) + 0.5, beta=torch.randn(C, device="cuda", generator=gg),
+                 rm=torch.randn(C, device="cuda", generator=gg), rv=torch.rand(C, device="cuda", generator=gg) + 0.5)
+        return d
+
+    def two_call(d):
+        o = {k: torch.empty(C, device="cuda") for k in ("scale", "shift", "mean", "rstd")}
+        rm, rv = d["rm"].clone(), d["rv"].clone()
+        ops.bn_finalize(d["sum"].view(1, C), d["sq"].view(1, C), 1, C, rows, d["gamma"], d["beta"], 1e-5, 0.1, rm, rv,
+                        o["scale"], o["shift"], o["mean"], o["rstd"])
+        return o, rm, rv
+
+    def record(d):
+        o = {k: torch.empty(C, device="cuda") for k in ("scale", "shift", "mean", "rstd")}
+        rm, rv = d["rm"].clone(), d["rv"].clone()
+        rec = ops.bn_stats(d["sum"], d["sq"], d["gamma"], d["beta"], rows, 1e-5, 0.1, rm, rv, o["scale"], o["shift"],
+                           o["mean"], o["rstd"])
+        return rec, o, rm, rv
+    dm, dr = bn_inputs(y, 91), bn_inputs(r, 92)
+    (om, rm0, rv0), (orr, _, _) = two_call(dm), two_call(dr)
+    for variant in ("plain", "identity", "affine"):
+        out0, out1 = torch.empty_like(y), torch.empty_like(y)
+        bits0 = torch.zeros(rows * C // 8, dtype=torch.uint8, device="cuda")
+        bits1 = torch.zeros_like(bits0)
+        rec, o1, rm1, rv1 = record(dm)
+        if variant == "plain":
+            ops.bn_act_apply(y, om["scale"], om["shift"], out0, rows, C, relu=True)
+            ops.bn_act_apply_stats(y, rec, out1, rows, C, relu=True)
+        elif variant == "identity":
+            ops.bn_act_apply(y, om["scale"], om["shift"], out0, rows, C, relu=True, res=r, relu_bits=bits0)
+            ops.bn_act_apply_stats(y, rec, out1, rows, C, relu=True, res=r, relu_bits=bits1)
+        else:
+            recr, o2, _, _ = record(dr)
+            ops.bn_act_apply(y, om["scale"], om["shift"], out0, rows, C, relu=False, res=r, res_scale=orr["scale"],
+                             res_shift=orr["shift"])
+            ops.bn_act_apply_stats(y, rec, out1, rows, C, relu=False, res=r, res_bn=recr)
+            torch.cuda.synchronize()
+            assert torch.equal(o2["scale"], orr["scale"]) and torch.equal(o2["shift"], orr["shift"])
+        torch.cuda.synchronize()
+        for kname in om:
+            assert torch.equal(o1[kname], om[kname]), (variant, kname)
+        assert torch.equal(rm1, rm0) and torch.equal(rv1, rv0)
+        assert torch.equal(out0, out1) and torch.equal(bits0, bits1), variant
+
+
+@pytest.mark.parametrize("C,rows", [(64, 4096), (192, 1000), (512, 80), (1280, 333)])
+def test_bn_backward_with_fused_finalize(ops, C, rows):
+    """b2c_bn_bwd_reduce_acc + b2c_bn_bwd_apply_stats == b2c_bn_bwd_reduce + b2c_bn_bwd_finalize + b2c_bn_bwd_apply."""
+    g = torch.Generator(device="cuda").manual_seed(95)
+    y = (torch.randn(rows, C, device="cuda", generator=g) * 1.5 + 0.3).to(torch.bfloat16)
+    dout = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+    add = torch.randn(rows, C, device="cuda", generator=g).to(torch.bfloat16)
+    gamma = torch.rand(C, device="cuda", generator=g) + 0.5
+    beta = torch.randn(C, device="cuda", generator=g) * 0.3
+    mean = y.float().mean(0)
+    rstd = (y.float().var(0, unbiased=False) + 1e-5).rsqrt()
+    scale = (gamma * rstd).contiguous()
+    shift = (beta - mean * scale).contiguous()
+    prow = ops.bn_bwd_partial_rows(rows, C)
+    partial = torch.empty(prow, 2, C, device="cuda")
+    ref = [torch.empty(C, device="cuda") for _ in range(5)]
+    dy0, dy1 = torch.empty_like(dout), torch.empty_like(dout)
+    for masked in (False, True):
+        sc, sh = (scale, shift) if masked else (None, None)
+        ops.bn_bwd_reduce(dout, None, y, None, rows, C, partial, sc, sh)
+        ops.bn_bwd_finalize(partial, prow, C, rows, gamma, mean, rstd, *ref)
+        ops.bn_bwd_apply(dout, y, ref[2], ref[3], ref[4], dy0, rows, C, add=add, relu_scale=sc, relu_shift=sh)
+        sums = torch.zeros(2, C, device="cuda")
+        dg, db = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+        ops.bn_bwd_reduce_acc(dout, None, y, None, rows, C, sums, sc, sh)
+        ops.bn_bwd_apply_stats(dout, y, sums, rows, gamma, mean, rstd, dg, db, dy1, rows, C, add=add, relu_scale=sc,
+                               relu_shift=sh)
+        torch.cuda.synchronize()
+        want = partial.double().sum(0)
+        assert (sums.double() - want).abs().max() <= 1e-5 * partial.abs().sum(0).max() + 1e-4
+        assert rel_err(dg, ref[0]) < 1e-4 and rel_err(db, ref[1]) < 1e-4
+        assert rel_err(dy1.float(), dy0.float()) < 2e-3           # coefficients from sums that differ by round-off

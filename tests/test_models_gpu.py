@@ -114,6 +114,14 @@ def test_depthwise_conv(ops, shape):
     assert rel(pq[:rows].sum(0)[:c], (yr.detach() ** 2).sum((0, 2, 3))) < 1e-3
     assert rel(dx[..., :c].float().permute(0, 3, 1, 2), xr.grad) < 1e-2
     assert rel(dw, wr.grad) < 1e-3
+    # statistics accumulated into one row (b2c_dwconv_fprop_acc): same output, same sums
+    y2 = torch.full_like(y, float("nan"))
+    acc = torch.zeros(2, cpad, device="cuda")
+    ops.dwconv_fprop_acc(x, wt, y2, c, stride, acc[0], acc[1])
+    torch.cuda.synchronize()
+    assert torch.equal(y, y2)
+    assert (acc[0] - ps[:rows].sum(0)).abs().max() <= 1e-4 * ps[:rows].abs().sum(0).max() + 1e-3
+    assert rel(acc[1], pq[:rows].sum(0)) < 1e-5
 
 
 def test_pointwise_conv_with_padded_channels(ops):
