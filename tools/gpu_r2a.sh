@@ -7,6 +7,13 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gp
 timeout 1500 python -m pytest tests -m gpu -q -p no:cacheprovider > gpurun_out/r2a_tests.log 2>&1
 echo "tests rc=$?" | tee -a gpurun_out/r2a_tests.log
 tail -40 gpurun_out/r2a_tests.log
+B2C_FUSED_FINALIZE=1 timeout 1500 python -m pytest tests -m gpu -q -p no:cacheprovider -x --deselect tests/test_reference_scripts_gpu.py > gpurun_out/r2a_tests_fused.log 2>&1
+echo "tests(fused finalize) rc=$?" | tee -a gpurun_out/r2a_tests_fused.log
+tail -15 gpurun_out/r2a_tests_fused.log
+for f in 0 1; do for b in 1024 128; do
+  B2C_FUSED_FINALIZE=$f timeout 600 python bench.py --steps 100 --warmup 10 --no-cpu --batch $b > gpurun_out/r2a_ab_f${f}_b${b}.json 2> gpurun_out/r2a_ab_f${f}_b${b}.err
+  echo "A/B fused=$f batch=$b rc=$?"; python -c "import json,sys; d=json.load(open('gpurun_out/r2a_ab_f${f}_b${b}.json')); print(d['value'], d['ms_per_step'], d['launches_per_step'], d['clocks'], d['final_loss'])"
+done; done
 timeout 600 python bench.py --steps 200 --warmup 20 > gpurun_out/r2a_bench.json 2> gpurun_out/r2a_bench.err
 echo "bench rc=$?"; cat gpurun_out/r2a_bench.json; tail -5 gpurun_out/r2a_bench.err
 timeout 300 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/r2a_ref.json 2> gpurun_out/r2a_ref.err
