@@ -79,6 +79,16 @@ typedef struct B2cConvDesc {
 B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, void* y, const void* add_src,
                    float* part_sum, float* part_sq, int* stat_rows, void* stream);
 
+/* y = conv1x1(cat([x0, x1], channels), w): the `Root` of the reference's DLA trees, `torch.cat(xs, 1)` followed by a
+ * 1x1 nn.Conv2d(2*cin, cout), models/dla_simple.py:44-56 — without materialising the concatenation: the two sources
+ * are read through their own tensor maps as the two halves of the GEMM's K axis. d describes ONE source (cin channels
+ * each, ksize 1, stride 1); `w_fprop2` is bf16 [2][cout][cin] (slab t multiplies x_t), which is what
+ * b2c_repack_weights writes for a [tap=2][cin][cout] master. Statistics as in b2c_conv_fprop. The gradients need no
+ * entry point of their own: dx_t = b2c_conv_dgrad with slab t of the [2][cin][cout] operand, dW slab t =
+ * b2c_conv_wgrad(x_t, dy). */
+B2C_API int b2c_conv1x1_cat_fprop(const B2cConvDesc* d, const void* x0, const void* x1, const void* w_fprop2, void* y,
+                          float* part_sum, float* part_sq, int* stat_rows, void* stream);
+
 /* dx[n,h,w,cin] = conv_transpose(dy, w) (+ add_src). Replaces cudnn_convolution_backward_input reached
  * from loss.backward(), main.py:104. `w_dgrad` is bf16 [tap][cin][cout]. add_src (optional, bf16, dx's
  * shape) is added in the epilogue; for ksize==1 && stride==2 it must be NULL (dx is zero-filled first)

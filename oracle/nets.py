@@ -104,6 +104,97 @@ def train_step_grads(x, target, params, buffers, forward=resnet_forward, taps=No
 
 
 # ------------------------------------------------------------------------------------------------
+# SimpleDLA (models/dla_simple.py) — the network main.py:71 constructs (first row)
+# ------------------------------------------------------------------------------------------------
+def _dla_tree(name, cin, cout, level, stride):
+    if level == 1:
+        left = ("block", name + ".left_tree", cin, cout, stride)
+        right = ("block", name + ".right_tree", cout, cout, 1)
+    else:
+        left = _dla_tree(name + ".left_tree", cin, cout, level - 1, stride)
+        right = _dla_tree(name + ".right_tree", cout, cout, level - 1, 1)
+    return ("tree", name, cout, left, right)
+
+
+DLA_TREES = [_dla_tree("layer3", 32, 64, 1, 1), _dla_tree("layer4", 64, 128, 2, 2),
+             _dla_tree("layer5", 128, 256, 2, 2), _dla_tree("layer6", 256, 512, 1, 2)]      # dla_simple.py:98-101
+
+
+def build_simpledla_params(seed):
+    """Construction order of SimpleDLA.__init__ (dla_simple.py:80-102): base, layer1, layer2, then per Tree the Root
+    first, then left_tree, right_tree (Tree.__init__ :61-70), each BasicBlock as in :19-36; Linear last."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    def node(n):
+        if n[0] == "block":
+            _, name, cin, cout, s = n
+            conv(name + ".conv1", cin, cout, 3, s); bn(name + ".bn1", cout)
+            conv(name + ".conv2", cout, cout, 3, 1); bn(name + ".bn2", cout)
+            if s != 1 or cin != cout:
+                conv(name + ".shortcut.0", cin, cout, 1, s); bn(name + ".shortcut.1", cout)
+        else:
+            _, name, cout, left, right = n
+            conv(name + ".root.conv", 2 * cout, cout, 1, 1); bn(name + ".root.bn", cout)
+            node(left); node(right)
+    for name, cin, cout in (("base", 3, 16), ("layer1", 16, 16), ("layer2", 16, 32)):
+        conv(name + ".0", cin, cout, 3, 1); bn(name + ".1", cout)
+    for t in DLA_TREES:
+        node(t)
+    lin = nn.Linear(512, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def simpledla_forward(x, params, buffers, training=True, taps=None):
+    def block(n, xin):
+        _, name, cin, cout, s = n
+        o = F.relu(_bn(F.conv2d(xin, params[name + ".conv1.weight"], stride=s, padding=1), name + ".bn1", params,
+                       buffers, training))                                                 # dla_simple.py:37
+        o = _bn(F.conv2d(o, params[name + ".conv2.weight"], padding=1), name + ".bn2", params, buffers, training)
+        if (name + ".shortcut.0.weight") in params:
+            sc = _bn(F.conv2d(xin, params[name + ".shortcut.0.weight"], stride=s), name + ".shortcut.1", params, buffers,
+                     training)
+        else:
+            sc = xin
+        return F.relu(o + sc)                                                              # :39-40
+
+    def node(n, xin):
+        if n[0] == "block":
+            return block(n, xin)
+        _, name, cout, left, right = n
+        out1 = node(left, xin)                                                             # :73
+        out2 = node(right, out1)                                                           # :74
+        y = F.conv2d(torch.cat([out1, out2], 1), params[name + ".root.conv.weight"])       # :52-53
+        if taps is not None:
+            taps[name + ".root.conv"] = y
+        return F.relu(_bn(y, name + ".root.bn", params, buffers, training))                # :54
+    out = x
+    for name in ("base", "layer1", "layer2"):                                              # :108-110
+        out = F.conv2d(out, params[name + ".0.weight"], padding=1)
+        if taps is not None:
+            taps[name + ".0"] = out
+        out = F.relu(_bn(out, name + ".1", params, buffers, training))
+    for t in DLA_TREES:                                                                    # :111-114
+        out = node(t, out)
+    out = F.avg_pool2d(out, 4).view(out.size(0), -1)                                       # :115-116
+    return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
 # VGG (models/vgg.py) — BASELINE config 3
 # ------------------------------------------------------------------------------------------------
 VGG_CFG = {

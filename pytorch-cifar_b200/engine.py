@@ -175,6 +175,55 @@ def mobilenetv2_spec(num_classes=10):
                 feat=1280, depthwise=depthwise, head_prefixes=("linear", "conv2", "bn2"))
 
 
+def simple_dla_spec(num_classes=10):
+    """SimpleDLA as models/dla_simple.py:59-116 composes it — the network main.py:71 constructs: three plain
+    conv3x3 + BN + ReLU layers (3->16->16->32), then four aggregation trees of BasicBlocks (64 level 1; 128 and 256
+    level 2, stride 2; 512 level 1, stride 2) and Linear(512, 10). A Tree registers its Root first, then the left
+    and right sub-trees (dla_simple.py:61-70), which fixes the parameter order."""
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    def block(name, cin, cout, stride):
+        params[name + ".conv1.weight"] = (cout, cin, 3, 3)
+        bn(name + ".bn1", cout)
+        params[name + ".conv2.weight"] = (cout, cout, 3, 3)
+        bn(name + ".bn2", cout)
+        sc = stride != 1 or cin != cout
+        if sc:
+            params[name + ".shortcut.0.weight"] = (cout, cin, 1, 1)
+            bn(name + ".shortcut.1", cout)
+        return dict(kind="block", name=name, cin=cin, cout=cout, stride=stride, shortcut=sc)
+
+    def tree(name, cin, cout, level, stride):
+        params[name + ".root.conv.weight"] = (cout, 2 * cout, 1, 1)
+        bn(name + ".root.bn", cout)
+        if level == 1:
+            left = block(name + ".left_tree", cin, cout, stride)
+            right = block(name + ".right_tree", cout, cout, 1)
+        else:
+            left = tree(name + ".left_tree", cin, cout, level - 1, stride)
+            right = tree(name + ".right_tree", cout, cout, level - 1, 1)
+        return dict(kind="tree", name=name, cin=cin, cout=cout, stride=stride, left=left, right=right)
+
+    plain = []
+    for name, cin, cout in (("base", 3, 16), ("layer1", 16, 16), ("layer2", 16, 32)):
+        params[name + ".0.weight"] = (cout, cin, 3, 3)
+        bn(name + ".1", cout)
+        plain.append((name, cin, cout))
+    trees = [tree("layer3", 32, 64, 1, 1), tree("layer4", 64, 128, 2, 2), tree("layer5", 128, 256, 2, 2),
+             tree("layer6", 256, 512, 1, 2)]
+    params["linear.weight"] = (num_classes, 512)
+    params["linear.bias"] = (num_classes,)
+    cat2 = {n for n in params if n.endswith(".root.conv.weight")}
+    return dict(family="dla", params=params, buffers=buffers, plain=plain, trees=trees, num_classes=num_classes,
+                feat=512, cat2=cat2)
+
+
 def _pad64(c):
     return _align(c, 64)
 
@@ -199,6 +248,9 @@ def backward_groups(spec):
     first_conv = next(n for n, sh in spec["params"].items() if len(sh) == 4)[:-len(".weight")]
 
     def key(name):
+        if spec["family"] == "dla":          # one backward op per top-level layer (a whole aggregation tree)
+            top = name.split(".")[0]
+            return "head" if top == "linear" else ("stem" if top == "base" else top)
         if name.startswith("layer"):
             return ".".join(name.split(".")[:2])
         if name.startswith("features."):
@@ -486,6 +538,40 @@ class ConvUnit(_BNOps):
             self.dgrad(dy, dx, add_src=dx)
 
 
+class RootUnit(_BNOps):
+    """`Root` of a DLA tree (models/dla_simple.py:44-56): relu(bn(conv1x1(cat([x0, x1], 1)))). The concatenation is
+    never materialised: the forward GEMM reads both sources as the two halves of its K axis; each source's data
+    gradient is a 1x1 dgrad with its own weight slab, each weight-gradient slab a 1x1 wgrad of its own source."""
+
+    def __init__(self, eng, name, x0, x1, C, cout, H, W):
+        N = eng.N
+        self.name, self.x0, self.x1, self.cin, self.cout, self.H, self.W = name + ".conv", x0, x1, C, cout, H, W
+        self.rows = N * H * W
+        self.y = eng.new_act(N, H, W, cout)
+        acc = 512 if FUSED_FINALIZE else 0
+        self.desc = ops.conv_desc(N, H, W, C, cout, 1, 1, flags=acc)
+        self.desc_d = ops.conv_desc(N, H, W, C, cout, 1, 1, flags=128 if CTA_PAIR == "all" else 0)
+        self.desc_w = ops.conv_desc(N, H, W, C, cout, 1, 1, flags=32)
+        self.ps, self.pq = eng.part_sum, eng.part_sq
+        self.fsum = eng.new_stat(2 * cout, forward=True)
+        self.wf, self.wd = eng.wf_view(self.name), eng.wd_view(self.name)        # [2][cout][C], [2][C][cout]
+        dw = eng.grad_flat(self.name + ".weight")                                  # stored [2][C][cout]
+        self.dw = [dw[:C * cout], dw[C * cout:]]
+        self.eng = eng
+        _bn_views(self, eng, name + ".bn", cout)
+
+    def fprop(self, eng):
+        ps, pq = (self.fsum[:self.cout], self.fsum[self.cout:]) if FUSED_FINALIZE else (self.ps, self.pq)
+        self.stat_rows = ops.conv1x1_cat_fprop(self.desc, self.x0, self.x1, self.wf, self.y, ps, pq)
+
+    def wgrad(self, dy):
+        self.eng.run_side(lambda: (ops.conv_wgrad(self.desc_w, self.x0, dy, self.dw[0]),
+                                   ops.conv_wgrad(self.desc_w, self.x1, dy, self.dw[1])))
+
+    def dgrad(self, dy, t, dx, add_src=None):
+        ops.conv_dgrad(self.desc_d, dy, self.wd[t], dx, add_src)
+
+
 class DwUnit(_BNOps):
     """Depthwise 3x3 conv + BatchNorm (models/mobilenetv2.py:20-21)."""
 
@@ -556,6 +642,8 @@ class Engine:
             self._build_mobilenetv2()
         elif spec["family"] == "bottleneck":
             self._build_bottleneck()
+        elif spec["family"] == "dla":
+            self._build_dla()
         else:
             raise NotImplementedError(spec["family"])
 
@@ -607,7 +695,19 @@ class Engine:
             cout, cin, k, _ = shape
             cout_p, cin_p = _pad64(cout), _pad64(cin)
             poff = self.p_off[name][0]
-            if cin == 3:      # stem: [cout_pad][64], k = tap*3 + c
+            if name in spec.get("cat2", ()):
+                # Root conv over cat([x0, x1]) (models/dla_simple.py:52-54): the [1][2C][cout] master IS [2][C][cout],
+                # so the operands are those of a two-tap conv with C input channels (b2c_conv1x1_cat_fprop)
+                assert name in self.tco and k == 1 and cin % 128 == 0, name
+                k, cin = 2, cin // 2
+                cin_p = _pad64(cin)
+                self.wf_off[cname] = (wf_n, (2, cout_p, cin_p))
+                self.wd_off[cname] = (wd_n, (2, cin_p, cout_p))
+                entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=wd_n, cout=cout, cin=cin, taps=2,
+                                    cin_pad=cin_p, cout_pad=cout_p, kflat=2))
+                wf_n += 2 * cout_p * cin_p
+                wd_n += 2 * cout_p * cin_p
+            elif cin == 3:      # stem: [cout_pad][64], k = tap*3 + c
                 self.wf_off[cname] = (wf_n, (1, cout_p, 64))
                 entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=-1, cout=cout, cin=cin, taps=k * k,
                                     cin_pad=64, kflat=1))
@@ -836,6 +936,132 @@ class Engine:
             stem.bn_backward(self, dout, a0, dout, dy0, relu_from_y=True)
             stem.wgrad(dy0)
         Bk.append(bwd_stem)
+        self.bwd_ops = Bk
+
+    # ------------------------------------------------------------------ SimpleDLA plan (models/dla_simple.py)
+    def _build_dla(self):
+        """models/dla_simple.py:108-116: base -> layer1 -> layer2 (conv3x3 + BN + ReLU each) -> four Trees ->
+        avg_pool2d(4) -> Linear. Tree.forward (:72-76): out1 = left(x); out2 = right(out1); root([out1, out2]).
+        Backward of a tree: root (BN/ReLU backward, both weight-gradient slabs, out2's data gradient), the right
+        sub-tree, then out1's gradient = root slab 0 + what the right sub-tree returned, then the left sub-tree."""
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        self.units = []
+        F = self.fwd_ops
+        eng = self
+
+        class Block:                     # BasicBlock, models/dla_simple.py:16-41 (= models/resnet.py:16-51)
+            def __init__(b, d, x, H, W):
+                name, cin, cout, s = d["name"], d["cin"], d["cout"], d["stride"]
+                b.x, b.H, b.W = x, H // s, W // s
+                b.c1 = ConvUnit(eng, name + ".conv1", name + ".bn1", x, cin, cout, 3, s, H, W)
+                b.a1 = eng.new_act(N, b.H, b.W, _pad64(cout))
+                b.c2 = ConvUnit(eng, name + ".conv2", name + ".bn2", b.a1, cout, cout, 3, 1, b.H, b.W)
+                b.cs = ConvUnit(eng, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W,
+                                private_stats=True) if d["shortcut"] else None
+                b.out = eng.new_act(N, b.H, b.W, _pad64(cout))
+                b.bits = torch.zeros(b.out.numel() // 8, dtype=torch.uint8, device=eng.device)
+                eng.units += [b.c1, b.c2] + ([b.cs] if b.cs else [])
+
+            def fwd(b, training):
+                c1, c2, cs = b.c1, b.c2, b.cs
+                if cs is not None:
+                    eng.run_side(lambda: (cs.fprop(eng), None if (FUSED_FINALIZE and training) else cs.bn_stats(eng, training)))
+                c1.fprop(eng)
+                c1.bn_apply(eng, training, b.a1)
+                c2.fprop(eng)
+                if cs is not None:
+                    eng.join_side()
+                    c2.bn_apply(eng, training, b.out, res_unit=cs, relu_bits=b.bits)
+                else:
+                    c2.bn_apply(eng, training, b.out, res=b.x, relu_bits=b.bits)
+
+            def plan_bwd(b, dout, ops_list):
+                """Appends this block's backward to ops_list; dout = gradient buffer of b.out. Returns d(b.x)."""
+                c1, c2, cs = b.c1, b.c2, b.cs
+                dy2, da1, dy1 = (eng.new_act(*t.shape) for t in (c2.y, b.a1, c1.y))
+                dys = eng.new_act(*cs.y.shape) if cs is not None else None
+                dx = eng.new_act(*b.x.shape)
+
+                def run():
+                    c2.bn_backward(eng, dout, b.out, dout, dy2, relu_bits=b.bits)
+                    if cs is not None:
+                        cs.bn_backward(eng, dout, None, None, dys)
+                    c2.wgrad(dy2)
+                    c1.bn_backward_from_partial(eng, da1, dy1, c2.dgrad_bn(eng, dy2, da1, c1))
+                    c1.wgrad(dy1)
+                    if cs is not None:
+                        cs.wgrad(dys)
+                        c1.dgrad_with_shortcut(dy1, dys, cs, dx)
+                    else:
+                        c1.dgrad(dy1, dx, add_src=dout)
+                ops_list.append(run)
+                return dx
+
+        class Tree:
+            def __init__(t, d, x, H, W):
+                sub = Tree if d["left"]["kind"] == "tree" else Block
+                t.left = sub(d["left"], x, H, W)
+                t.right = sub(d["right"], t.left.out, t.left.H, t.left.W)
+                t.H, t.W = t.left.H, t.left.W
+                t.root = RootUnit(eng, d["name"] + ".root", t.left.out, t.right.out, d["cout"], d["cout"], t.H, t.W)
+                t.out = eng.new_act(N, t.H, t.W, d["cout"])
+                eng.units.append(t.root)
+
+            def fwd(t, training):
+                t.left.fwd(training)
+                t.right.fwd(training)
+                t.root.fprop(eng)
+                t.root.bn_apply(eng, training, t.out)
+
+            def plan_bwd(t, dout, ops_list):
+                root = t.root
+                dyr = eng.new_act(*root.y.shape)
+                g2 = eng.new_act(*t.right.out.shape)
+
+                def run_root():
+                    root.bn_backward(eng, dout, t.out, dout, dyr, relu_from_y=True)
+                    root.wgrad(dyr)
+                    root.dgrad(dyr, 1, g2)
+                ops_list.append(run_root)
+                g1 = t.right.plan_bwd(g2, ops_list)                  # gradient of out1 through the right sub-tree
+                ops_list.append(lambda: root.dgrad(dyr, 0, g1, add_src=g1))      # + through the root's first slab
+                return t.left.plan_bwd(g1, ops_list)
+
+        x, H, W = self.x0, 32, 32
+        plain = []
+        for i, (name, cin, cout) in enumerate(spec["plain"]):
+            u = ConvUnit(self, name + ".0", name + ".1", x, cin, cout, 3, 1, 32, 32, stem=(i == 0))
+            act = self.new_act(N, 32, 32, u.cout)
+            self.units.append(u)
+            plain.append((u, act))
+            F.append(lambda training, u=u, act=act: (u.fprop(self), u.bn_apply(self, training, act)))
+            x = act
+        trees = []
+        for d in spec["trees"]:
+            t = Tree(d, x, H, W)
+            trees.append(t)
+            F.append(t.fwd)
+            x, H, W = t.out, t.H, t.W
+        fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        for t in reversed(trees):
+            sub = []
+            dout = t.plan_bwd(dout, sub)
+            Bk.append(lambda sub=sub: [f() for f in sub])
+        for i in range(len(plain) - 1, -1, -1):
+            u, act = plain[i]
+            dy = self.new_act(*u.y.shape)
+            dx = self.new_act(*u.x.shape) if i > 0 else None
+
+            def bwd_plain(u=u, act=act, dout=dout, dy=dy, dx=dx):
+                u.bn_backward(self, dout, act, dout, dy, relu_from_y=True)
+                u.wgrad(dy)
+                if dx is not None:
+                    u.dgrad(dy, dx)
+            Bk.append(bwd_plain)
+            dout = dx
         self.bwd_ops = Bk
 
     # ------------------------------------------------------------------ shared head (pool + linear)

@@ -60,6 +60,17 @@ def conv_fprop(d, x, w_fprop, y, part_sum=None, part_sq=None, add_src=None):
     return rows.value
 
 
+def conv1x1_cat_fprop(d, x0, x1, w_fprop2, y, part_sum=None, part_sq=None):
+    """y = conv1x1(cat([x0, x1], C)): d describes one source; w_fprop2 is [2][cout][cin]. Returns the stat rows."""
+    lib = _lib.load()
+    _need(x0, torch.bfloat16, "x0"); _need(x1, torch.bfloat16, "x1"); _need(w_fprop2, torch.bfloat16, "w")
+    _need(y, torch.bfloat16, "y"); _need(part_sum, torch.float32, "part_sum"); _need(part_sq, torch.float32, "part_sq")
+    rows = ctypes.c_int(0)
+    check(lib.b2c_conv1x1_cat_fprop(ctypes.byref(d), _p(x0), _p(x1), _p(w_fprop2), _p(y), _p(part_sum), _p(part_sq),
+                                    ctypes.byref(rows), _stream()), "b2c_conv1x1_cat_fprop")
+    return rows.value
+
+
 def conv_dgrad(d, dy, w_dgrad, dx, add_src=None):
     lib = _lib.load()
     _need(dy, torch.bfloat16, "dy"); _need(w_dgrad, torch.bfloat16, "w"); _need(dx, torch.bfloat16, "dx")

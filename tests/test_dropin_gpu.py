@@ -189,3 +189,57 @@ def test_checkpoint_file_with_module_prefix(tmp_path):
     with torch.no_grad():
         assert torch.equal(net(xe), other(xe))
         assert rel(net(xe), plain(xe)) < 6e-2
+
+
+REFERENCE_CTORS = {"resnet18": ("resnet", "ResNet18", ()), "vgg16": ("vgg", "VGG", ("VGG16",)),
+                   "preact18": ("preact_resnet", "PreActResNet18", ()), "mobilenetv2": ("mobilenetv2", "MobileNetV2", ()),
+                   "simpledla": ("dla_simple", "SimpleDLA", ())}
+
+
+@pytest.mark.parametrize("family", list(REFERENCE_CTORS))
+def test_the_references_own_classes(family):
+    """accelerate() on modules built by the reference's OWN model files (models/resnet.py, vgg.py, preact_resnet.py,
+    mobilenetv2.py, dla_simple.py — the copies staged under oracle/_ref/reference by oracle/stage_reference.py; the
+    GPU box has no /root/reference): the loop body of main.py:99-107 against the same module left on torch / cuDNN
+    in fp32."""
+    import importlib
+    import sys
+    import b200cifar
+    from b200cifar.accelerate import accelerate
+    from oracle.stage_reference import reference_dir
+    ref_dir = reference_dir()
+    if ref_dir is None:
+        pytest.fail("reference files are not staged: run `python oracle/stage_reference.py` where /root/reference exists")
+    if ref_dir not in sys.path:
+        sys.path.insert(0, ref_dir)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    mod, ctor, args = REFERENCE_CTORS[family]
+    cls = getattr(importlib.import_module("models." + mod), ctor)
+    assert cls.__module__ == "models." + mod                 # the defining file, not a star-import alias (SURVEY F11)
+    torch.manual_seed(0)
+    ref = cls(*args).cuda()
+    net = copy.deepcopy(ref)
+    keys = list(net.state_dict().keys())
+    assert accelerate(net) is net and list(net.state_dict().keys()) == keys
+    x, t = batch(128, 31)
+    crit = nn.CrossEntropyLoss()
+    opt = torch.optim.SGD(net.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)
+    opt_ref = torch.optim.SGD(ref.parameters(), lr=0.02, momentum=0.9, weight_decay=5e-4)
+    losses, losses_ref = [], []
+    for _ in range(3):
+        for n_, o_, ls in ((net, opt, losses), (ref, opt_ref, losses_ref)):
+            o_.zero_grad()
+            loss = crit(n_(x), t)
+            loss.backward()
+            o_.step()
+            ls.append(loss.item())
+    assert abs(losses[0] - losses_ref[0]) < 3e-2, (losses, losses_ref)
+    assert max(abs(a - b) for a, b in zip(losses, losses_ref)) < 0.2, (losses, losses_ref)
+    net.eval(); ref.eval()
+    plain = cls(*args).cuda()
+    plain.load_state_dict(net.state_dict())                  # our arenas into a fresh reference module
+    plain.eval()
+    xe, _ = batch(100, 32)
+    with torch.no_grad():
+        assert rel(net(xe), plain(xe)) < (0.25 if family == "mobilenetv2" else 8e-2)

@@ -907,3 +907,41 @@ def test_bn_backward_with_fused_finalize(ops, C, rows):
         assert (sums.double() - want).abs().max() <= 1e-5 * partial.abs().sum(0).max() + 1e-4
         assert rel_err(dg, ref[0]) < 1e-4 and rel_err(db, ref[1]) < 1e-4
         assert rel_err(dy1.float(), dy0.float()) < 2e-3           # coefficients from sums that differ by round-off
+
+
+@pytest.mark.parametrize("shape", [(8, 32, 32, 64, 64), (16, 16, 16, 128, 128), (32, 8, 8, 256, 256), (64, 4, 4, 512, 512),
+                                   (5, 4, 4, 512, 512)])
+def test_conv1x1_over_concat(ops, shape):
+    """b2c_conv1x1_cat_fprop: the Root of a DLA tree, conv1x1(cat([x0, x1], 1)) (models/dla_simple.py:52-53) read
+    through two tensor maps, against F.conv2d on the materialised concatenation; its gradients are the ordinary 1x1
+    dgrad / wgrad with one weight slab each."""
+    n, h, w, c, cout = shape
+    x0, x1 = nhwc_bf16(n, h, w, c, 101), nhwc_bf16(n, h, w, c, 102)
+    wt = weight(cout, 2 * c, 1, 103)
+    ref = F.conv2d(torch.cat([to_nchw(x0), to_nchw(x1)], 1), wt)
+    w2 = torch.stack([wt[:, :c, 0, 0], wt[:, c:, 0, 0]]).contiguous().to(torch.bfloat16)        # [2][cout][c]
+    y = torch.full((n, h, w, cout), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    rows = ops.conv1x1_cat_fprop(ops.conv_desc(n, h, w, c, cout, 1, 1), x0, x1, w2, y, ps, pq)
+    torch.cuda.synchronize()
+    assert torch.isfinite(to_nchw(y)).all() and rel_err(to_nchw(y), ref) < BF16_TOL
+    assert rel_err(pq[:rows].sum(0), (ref * ref).sum((0, 2, 3))) < F32_TOL
+    acc = torch.zeros(2, cout, device="cuda")
+    y2 = torch.empty_like(y)
+    assert ops.conv1x1_cat_fprop(ops.conv_desc(n, h, w, c, cout, 1, 1, flags=512), x0, x1, w2, y2, acc[0], acc[1]) == 1
+    torch.cuda.synchronize()
+    assert torch.equal(y, y2) and rel_err(acc[1], pq[:rows].sum(0)) < 1e-5
+    # gradients slab by slab
+    dy = nhwc_bf16(n, h, w, cout, 104)
+    gx = torch.nn.grad.conv2d_input((n, 2 * c, h, w), wt, to_nchw(dy))
+    gw = torch.nn.grad.conv2d_weight(torch.cat([to_nchw(x0), to_nchw(x1)], 1), (cout, 2 * c, 1, 1), to_nchw(dy))
+    for t, xt in enumerate((x0, x1)):
+        wd = wt[:, t * c:(t + 1) * c, 0, 0].t().contiguous().to(torch.bfloat16).view(1, c, cout)
+        dx = torch.empty(n, h, w, c, device="cuda", dtype=torch.bfloat16)
+        ops.conv_dgrad(ops.conv_desc(n, h, w, c, cout, 1, 1), dy, wd, dx)
+        dw = torch.zeros(1, c, cout, device="cuda")
+        ops.conv_wgrad(ops.conv_desc(n, h, w, c, cout, 1, 1, flags=32), xt, dy, dw)
+        torch.cuda.synchronize()
+        assert rel_err(to_nchw(dx), gx[:, t * c:(t + 1) * c]) < BF16_TOL
+        assert rel_err(dw[0].t(), gw[:, t * c:(t + 1) * c, 0, 0]) < 2e-3

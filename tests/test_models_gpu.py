@@ -164,7 +164,8 @@ def test_pointwise_conv_with_padded_channels(ops):
 BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop=0.7, lr=0.02),
           "preact18": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop=0.7, lr=0.02),
           "mobilenetv2": dict(logits=0.25, near=0.15, near_cos=0.99, min_cos=None, drop=0.92, lr=0.02),
-          "resnet50": dict(logits=0.3, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002)}
+          "resnet50": dict(logits=0.3, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
+          "simpledla": dict(logits=8e-2, near=8e-2, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02)}
 
 MODELS = {
     "vgg16": ("vgg_spec", "build_vgg_params", "vgg_forward", "features.0", ["classifier.weight", "features.41.weight",
@@ -175,6 +176,9 @@ MODELS = {
                     ["linear.weight", "bn2.weight", "bn2.bias"]),
     "resnet50": ("resnet50_spec", "build_bottleneck_params", "bottleneck_forward", "conv1",
                  ["linear.weight", "layer4.2.bn3.weight", "layer4.2.bn3.bias"]),
+    # SimpleDLA, what main.py:71 constructs (models/dla_simple.py): aggregation trees, Root = 1x1 conv over a concat
+    "simpledla": ("simple_dla_spec", "build_simpledla_params", "simpledla_forward", "base.0",
+                  ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
 }
 
 

@@ -46,20 +46,24 @@ def compare(acc, ref, steps):
     for a, b in zip(acc["test_losses"], ref["test_losses"]):
         assert abs(a - b) < 0.15, (acc["test_losses"], ref["test_losses"])
     ck = acc["ckpt"]
-    assert ck["top_level_keys"] == ["acc", "epoch", "net"] and ck["module_prefix"] and ck["n_entries"] == 122
+    assert ck["top_level_keys"] == ["acc", "epoch", "net"] and ck["module_prefix"]
+    assert ck["n_entries"] == ref["ckpt"]["n_entries"] >= 122
     assert "All keys matched" in ck["load_result"] and ck["epoch"] == 0
     mean_test = sum(acc["test_losses"]) / len(acc["test_losses"])
     assert abs(ck["plain_eval_loss"] - mean_test) < 0.1          # the saved weights in a plain fp32 model
 
 
-def test_main_py_unmodified(tmp_path):
-    """main.py: 428 samples = 3 batches of 128 + a ragged 44, then test() on 2 x 100 and the checkpoint."""
+@pytest.mark.parametrize("model", ["dla_simple.SimpleDLA", "resnet.ResNet18"])
+def test_main_py_unmodified(tmp_path, model):
+    """main.py: 428 samples = 3 batches of 128 + a ragged 44, then test() on 2 x 100 and the checkpoint.
+    SimpleDLA is the network main.py:71 itself constructs; ResNet-18 is the benchmarked one (main.py:58)."""
     args = ["--lr", "0.02"]
-    acc = run(tmp_path, "main_acc", "main.py", False, args)
-    ref = run(tmp_path, "main_ref", "main.py", True, args)
+    acc = run(tmp_path, "main_acc", "main.py", False, args, model=model)
+    ref = run(tmp_path, "main_ref", "main.py", True, args, model=model)
     compare(acc, ref, 4)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    json.dump(dict(accelerated=acc, plain=ref), open(os.path.join(ROOT, "gpurun_out", "reference_main_py.json"), "w"), indent=1)
+    json.dump(dict(accelerated=acc, plain=ref),
+              open(os.path.join(ROOT, "gpurun_out", f"reference_main_py_{model.split('.')[-1]}.json"), "w"), indent=1)
 
 
 def test_main_dist_py_unmodified_under_ddp(tmp_path):
