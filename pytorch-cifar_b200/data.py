@@ -105,3 +105,17 @@ def learnable_cifar(n=10000, seed=0, noise=48.0):
     labels = rs.randint(0, 10, size=(n,)).astype(np.int64)
     images = protos[labels] + rs.standard_normal((n, 32, 32, 3)).astype(np.float32) * noise
     return np.clip(images, 0, 255).astype(np.uint8), labels
+
+
+def hard_cifar(n=10000, seed=0, amplitude=6.0, noise=64.0):
+    """A synthetic task that does NOT saturate: 10 classes whose prototypes are weak, spatially smooth colour fields
+    (a 4x4x3 grid of N(0, amplitude^2) values around mid-grey, each cell 8x8 pixels, so random crops keep most of the
+    pattern) buried in per-pixel Gaussian noise. The accuracy a network reaches depends on how well it averages the
+    noise out, which makes the top-1 curve sensitive to the numerics of training (tests/test_accuracy_curve_gpu.py).
+    The prototypes depend on `seed // 1000` only, so train / test splits drawn with seeds 1000*k + i share them."""
+    protos = np.random.RandomState(7919 + seed // 1000).standard_normal((10, 4, 4, 3)).astype(np.float32) * amplitude
+    protos = np.repeat(np.repeat(protos, 8, axis=1), 8, axis=2) + 128.0
+    rs = np.random.RandomState(seed)
+    labels = rs.randint(0, 10, size=(n,)).astype(np.int64)
+    images = protos[labels] + rs.standard_normal((n, 32, 32, 3)).astype(np.float32) * noise
+    return np.clip(np.rint(images), 0, 255).astype(np.uint8), labels
