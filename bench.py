@@ -36,7 +36,7 @@ MODELS = {
                         metric="mobilenetv2_cifar10_train_images_per_sec",
                         workload="mobilenetv2_cifar10_train_batch512"),
 }
-NCU_TRAFFIC_FILE = os.path.join("profiles", "r2_ncu_conv_kernels.json")     # written by tools/ncu_summary.py
+NCU_TRAFFIC_FILE = os.path.join("profiles", "r2_ncu_conv_kernels.json")     # tools/ncu_summary.py on the GPU box
 
 
 def load_peaks():
@@ -444,11 +444,12 @@ def run_product(args):
     if M["bound"] == "tensor" and halo_calls:
         halo_launches = count_launches(halo_calls)
         achieved = halo_fl / (halo_ms * 1e-3) / 1e12
-        traffic, traffic_src = None, None
+        traffic, traffic_src, tensor_pipe_pct = None, None, None
         try:        # DRAM bytes per launch of the same kernel from the committed ncu --set full capture
             with open(os.path.join(ROOT, NCU_TRAFFIC_FILE)) as f:
                 cap = json.load(f)["conv_halo2_kernel"]
             traffic = cap["avg_dram_bytes_per_launch"]
+            tensor_pipe_pct = cap.get("tensor_pipe_pct")
             traffic_src = f"{NCU_TRAFFIC_FILE} (dram__bytes_read.sum + dram__bytes_write.sum, average over the " \
                           f"{cap['launches']} conv_halo2_kernel launches of one batch-{cap.get('batch', 1024)} step)"
         except Exception:
@@ -462,6 +463,7 @@ def run_product(args):
                                    "condition; against the burst figure the fraction is frac_of_burst",
                     "peak_burst": tf_b, "frac_of_burst": achieved / tf_b,
                     "traffic": traffic, "traffic_source": traffic_src,
+                    "ncu_tensor_pipe_pct": tensor_pipe_pct,     # sm__pipe_tensor_cycles_active % of elapsed, same capture
                     "launches_per_step": halo_launches, "avg_launch_us": halo_ms * 1e3 / halo_launches,
                     "flop_per_launch_avg": halo_fl / halo_launches, "ms_per_step": halo_ms,
                     "tap_gemm": fam(tap_fl, tap_ms, count_launches(tap_calls)),
