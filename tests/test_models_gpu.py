@@ -166,7 +166,7 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           "mobilenetv2": dict(logits=0.25, near=0.15, near_cos=0.99, min_cos=None, drop=0.92, lr=0.02),
           "resnet50": dict(logits=0.3, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
           # SimpleDLA: 33 convs deep; measured 8.2 % on the logits (profiles/r2_parity/parity_simpledla.json)
-          "simpledla": dict(logits=0.12, near=8e-2, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02)}
+          "simpledla": dict(logits=0.12, near=0.12, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02)}
 
 MODELS = {
     "vgg16": ("vgg_spec", "build_vgg_params", "vgg_forward", "features.0", ["classifier.weight", "features.41.weight",

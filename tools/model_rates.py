@@ -6,22 +6,19 @@ import numpy as np
 import torch
 import b200cifar
 from b200cifar import data, engine, trainer
-from oracle import nets
 
-MODELS = [("resnet18", "resnet_spec", "build_resnet_params", 1024), ("vgg16", "vgg_spec", "build_vgg_params", 1024),
-          ("preact_resnet18", "preact_resnet_spec", "build_preact_params", 1024),
-          ("mobilenetv2", "mobilenetv2_spec", "build_mobilenetv2_params", 512),
-          ("resnet50", "resnet50_spec", "build_bottleneck_params", 256)]
+MODELS = [("resnet18", "resnet_spec", 1024), ("vgg16", "vgg_spec", 1024), ("preact_resnet18", "preact_resnet_spec", 1024),
+          ("mobilenetv2", "mobilenetv2_spec", 512), ("resnet50", "resnet50_spec", 256), ("simpledla", "simple_dla_spec", 1024)]
 steps, warm = 30, 5
 images, labels = data.synthetic_cifar(8192, seed=0)
 out = []
-for name, spec_fn, build_fn, N in MODELS:
+for name, spec_fn, N in MODELS:
     if len(sys.argv) > 1 and name not in sys.argv[1:]:
         continue
     spec = getattr(engine, spec_fn)()
-    params, buffers = getattr(nets, build_fn)(0)
+    params, buffers = engine.init_params(spec, 0)
     tr = trainer.Trainer(spec, N, lr=0.01)
-    tr.load_params(params, {k: v for k, v in buffers.items() if not k.endswith("num_batches_tracked")})
+    tr.load_params(params, buffers)
     tr.set_dataset(images, labels)
     rng = data.TorchCpuMT19937(3)
     idx = [data.randperm(rng, 8192)[:N] for _ in range(4)]
