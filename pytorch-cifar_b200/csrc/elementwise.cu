@@ -909,11 +909,11 @@ sgd_kernel(float4* __restrict__ p, const float4* __restrict__ g, float4* __restr
 // kflat != 0 (stem): fprop B is [cout][64] with k = tap*cin + c (matches the im2col operand), no dgrad copy.
 // ------------------------------------------------------------------------------------------------
 // Work of one table entry in tiles, the unit one block processes per iteration: kflat 1 (stem) = 256 elements,
-// kflat 2 = one 32 (cin) x 32 (cout) tile of one tap, kflat 0 = one 32 x 32 tile with all its taps.
+// kflat 2 = one 32 (cin) x 64 (cout) tile of one tap, kflat 0 = one 32 x 32 tile with all its taps.
 __device__ __forceinline__ int repack_entry_tiles(const RepackEntry& e) {
     if (e.kflat == 1) return (e.cout * e.cin * e.taps + 255) >> 8;
-    const int t = ((e.cin + 31) >> 5) * ((e.cout + 31) >> 5);
-    return e.kflat == 2 ? e.taps * t : t;
+    if (e.kflat == 2) return e.taps * ((e.cin + 31) >> 5) * ((e.cout + 63) >> 6);
+    return ((e.cin + 31) >> 5) * ((e.cout + 31) >> 5);
 }
 
 // The tiles of ALL entries form one list that the grid strides over, so a block's share of the work does not depend
@@ -925,18 +925,24 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
     pdl_trigger_ew();
     pdl_wait();
     __shared__ float tile[32][32 * 9 + 1];
-    int ei = 0, first = 0;                       // entry of the current tile and the global index of its first tile
-    RepackEntry e = table[0];
-    int ntiles = repack_entry_tiles(e);
-    for (int g = blockIdx.x;; g += gridDim.x) {
-        while (ei < entries && g >= first + ntiles) {
-            first += ntiles;
-            if (++ei < entries) {
-                e = table[ei];
-                ntiles = repack_entry_tiles(e);
-            }
+    // first tile of every entry, once per block (a dependent chain of global loads per entry otherwise)
+    constexpr int kMaxEntries = 256;
+    __shared__ int s_first[kMaxEntries + 1];
+    if (threadIdx.x == 0) {
+        int acc = 0;
+        for (int i = 0; i < entries; ++i) {
+            s_first[i] = acc;
+            acc += repack_entry_tiles(table[i]);
         }
-        if (ei >= entries) return;
+        s_first[entries] = acc;
+    }
+    __syncthreads();
+    const int total = s_first[entries];
+    int ei = 0;
+    for (int g = blockIdx.x; g < total; g += gridDim.x) {
+        while (g >= s_first[ei + 1]) ++ei;
+        const RepackEntry e = table[ei];
+        const int first = s_first[ei];
         const int tidx = g - first;
         const int taps = e.taps;
         if (e.kflat == 1) {
@@ -955,28 +961,60 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
             // master is [tap][cin][cout] fp32 (the engine's internal layout of conv weights, which the wgrad kernels
             // write with coalesced vector reductions): the dgrad operand is a straight bf16 conversion, the fprop
             // operand a 32x32 transpose per tap. Channel counts are even; pairs go out as bf16x2.
-            float (*t2)[33] = reinterpret_cast<float (*)[33]>(&tile[0][0]);
-            const int ct = (e.cin + 31) >> 5, ot = (e.cout + 31) >> 5;
+            // Tile = 32 (cin) x 64 (cout): 16-byte loads of whole 256-byte rows, 8-byte stores of both operands.
+            float (*t2)[65] = reinterpret_cast<float (*)[65]>(&tile[0][0]);
+            const int ct = (e.cin + 31) >> 5, ot = (e.cout + 63) >> 6;
             const int t = tidx / (ct * ot);
             const int rem = tidx - t * ct * ot;
-            const int c0 = (rem / ot) << 5, o0 = (rem % ot) << 5;
-            const int nc = min(32, e.cin - c0), no = min(32, e.cout - o0);
+            const int c0 = (rem / ot) << 5, o0 = (rem % ot) << 6;
+            const int nc = min(32, e.cin - c0), no = min(64, e.cout - o0);
+            const bool vec = !(e.cout & 3) && !(e.cin & 3) && !(cout_pad & 3) && !(e.cin_pad & 3) && !(e.src_off & 3) &&
+                             !(e.wf_off & 3) && !((e.wd_off < 0 ? 0 : e.wd_off) & 3);
             __syncthreads();
-            for (int i = threadIdx.x; i < 32 * 32; i += 256) {
-                const int a = i >> 5, b = i & 31;
-                t2[a][b] = (a < nc && b < no)
-                               ? master[e.src_off + (static_cast<long long>(t) * e.cin + c0 + a) * e.cout + o0 + b]
-                               : 0.f;
+            for (int i = threadIdx.x; i < 32 * 16; i += 256) {       // 32 rows x 16 float4
+                const int a = i >> 4, b = (i & 15) << 2;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                const float* src = master + e.src_off + (static_cast<long long>(t) * e.cin + c0 + a) * e.cout + o0 + b;
+                if (a < nc) {
+                    if (vec && b + 3 < no) v = *reinterpret_cast<const float4*>(src);
+                    else {
+                        if (b < no) v.x = src[0];
+                        if (b + 1 < no) v.y = src[1];
+                        if (b + 2 < no) v.z = src[2];
+                        if (b + 3 < no) v.w = src[3];
+                    }
+                    // dgrad operand [tap][cin_pad][cout_pad]: the same row, converted
+                    if (e.wd_off >= 0) {
+                        __nv_bfloat16* dst = wd + e.wd_off + (static_cast<long long>(t) * e.cin_pad + c0 + a) * cout_pad + o0 + b;
+                        if (vec && b + 3 < no) {
+                            uint2 u;
+                            u.x = pack_bf16x2(v.x, v.y);
+                            u.y = pack_bf16x2(v.z, v.w);
+                            *reinterpret_cast<uint2*>(dst) = u;
+                        } else {
+                            if (b < no) dst[0] = __float2bfloat16(v.x);
+                            if (b + 1 < no) dst[1] = __float2bfloat16(v.y);
+                            if (b + 2 < no) dst[2] = __float2bfloat16(v.z);
+                            if (b + 3 < no) dst[3] = __float2bfloat16(v.w);
+                        }
+                    }
+                }
+                t2[a][b] = v.x; t2[a][b + 1] = v.y; t2[a][b + 2] = v.z; t2[a][b + 3] = v.w;
             }
             __syncthreads();
-            for (int i = threadIdx.x; i < 32 * 16; i += 256) {
-                const int a = i >> 4, b = (i & 15) * 2;
-                if (e.wd_off >= 0 && a < nc && b < no)
-                    *reinterpret_cast<__nv_bfloat162*>(wd + e.wd_off + (static_cast<long long>(t) * e.cin_pad + c0 + a) * cout_pad + o0 + b) =
-                        __floats2bfloat162_rn(t2[a][b], t2[a][b + 1]);
-                if (a < no && b < nc)
-                    *reinterpret_cast<__nv_bfloat162*>(wf + e.wf_off + (static_cast<long long>(t) * cout_pad + o0 + a) * e.cin_pad + c0 + b) =
-                        __floats2bfloat162_rn(t2[b][a], t2[b + 1][a]);
+            // fprop operand [tap][cout_pad][cin_pad]: row o holds the tile's 32 cin values, 4 per thread
+            for (int i = threadIdx.x; i < 64 * 8; i += 256) {
+                const int a = i >> 3, b = (i & 7) << 2;            // a: cout within the tile, b: cin within the tile
+                if (a >= no || b >= nc) continue;
+                __nv_bfloat16* dst = wf + e.wf_off + (static_cast<long long>(t) * cout_pad + o0 + a) * e.cin_pad + c0 + b;
+                if (vec && b + 3 < nc) {
+                    uint2 u;
+                    u.x = pack_bf16x2(t2[b][a], t2[b + 1][a]);
+                    u.y = pack_bf16x2(t2[b + 2][a], t2[b + 3][a]);
+                    *reinterpret_cast<uint2*>(dst) = u;
+                } else {
+                    for (int k = 0; k < 4 && b + k < nc; ++k) dst[k] = __float2bfloat16(t2[b + k][a]);
+                }
             }
             continue;
         }
@@ -1250,6 +1288,7 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
     if (entries == 0) return cudaSuccess;
     // the table lives on the device, so the tile total is not known here: a fixed grid of 8 blocks per SM strides over
     // the global tile list (ResNet-18: 10.9 k tiles)
+    if (entries > 256) return cudaErrorInvalidValue;      // kMaxEntries of the kernel's shared table index
     B2C_LAUNCH(repack_kernel, 148 * 8, 256, 0, s, master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd),
                                        table_dev, entries);
     return cudaGetLastError();
