@@ -59,7 +59,8 @@ typedef struct B2cConvDesc {
                                epilogue reduce 4 rows x 128 contiguous bytes per instruction;
                         bit 6: wgrad: keep the per-tap kernel where the row kernel (conv_wgrad_row.cu) would be
                                chosen (measurement aid);
-                        bit 7: fprop / stride-1 dgrad: CTA-pair kernels (tcgen05.mma.cta_group::2): conv_halo2.cu where
+                        bit 7: fprop / dgrad (stride 2 and the fused shortcut form included): CTA-pair kernels
+                               (tcgen05.mma.cta_group::2): conv_halo2.cu where
                                the halo kernel would run, conv_gemm2.cu otherwise (or with bit 0); wgrad: the pair
                                row kernel (conv_wgrad_row2.cu) where cin is a multiple of 256;
                         bit 8: wgrad: the pair row kernel for any cin the row kernel takes (test aid);

@@ -272,7 +272,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     rc = encode_2d(&mb, w_fprop, static_cast<long long>(taps) * d->cout, d->cin, pair ? bn / 2 : bn);
     if (rc) return rc;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
-    rc = pair ? cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, as_stream(stream)))
+    rc = pair ? cuda_rc(b2c::launch_tap_gemm2(bn, ma, ma, mb, p, max_ctas, stat_rows, as_stream(stream)))
               : cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, as_stream(stream)));
     if (acc && stat_rows != nullptr) *stat_rows = 1;
     return rc;
@@ -377,7 +377,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     }
 
     CUtensorMap ma, mb;
-    const bool pair = (d->flags & 128) != 0 && d->stride == 1 && dy_shortcut == nullptr;   // conv_gemm2.cu
+    const bool pair = (d->flags & 128) != 0;   // conv_gemm2.cu (CTA pair), all phase / shortcut forms included
     rc = encode_2d(&mb, w_dgrad, static_cast<long long>(taps + (dy_shortcut != nullptr ? 1 : 0)) * d->cin, d->cout,
                    pair ? bn / 2 : bn);
     if (rc) return rc;
@@ -402,7 +402,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         }
         p.sy = p.sx = 1;
         single_phase(p);
-        rc = pair ? cuda_rc(b2c::launch_tap_gemm2(bn, ma, mb, p, max_ctas, stat_rows, st))
+        rc = pair ? cuda_rc(b2c::launch_tap_gemm2(bn, ma, ma, mb, p, max_ctas, stat_rows, st))
                   : cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, stat_rows, st));
         if ((d->flags & 512) && stat_rows != nullptr) *stat_rows = 1;
         return rc;
@@ -433,6 +433,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         p.tap_a[0] = 0;
         p.tap_brow[0] = 0;
         single_phase(p);
+        if (pair) return cuda_rc(b2c::launch_tap_gemm2(bn, ma, ma, mb, p, max_ctas, nullptr, st));
         return cuda_rc(b2c::launch_tap_gemm(bn, ma, ma, mb, p, max_ctas, nullptr, st));
     }
     // 3x3: all four parity phases in ONE launch (tiles = phase x pixel tile): dy is read from HBM once and the
@@ -472,7 +473,8 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     p.phase_begin[4] = static_cast<uint8_t>(nt);
     p.num_taps = nt;
     p.num_phases = 4;
-    rc = cuda_rc(b2c::launch_tap_gemm(bn, ma, ma1, mb, p, max_ctas, stat_rows, st));
+    rc = pair ? cuda_rc(b2c::launch_tap_gemm2(bn, ma, ma1, mb, p, max_ctas, stat_rows, st))
+              : cuda_rc(b2c::launch_tap_gemm(bn, ma, ma1, mb, p, max_ctas, stat_rows, st));
     if ((d->flags & 512) && stat_rows != nullptr) *stat_rows = 1;
     return rc;
 }

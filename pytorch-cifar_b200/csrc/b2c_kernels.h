@@ -103,8 +103,8 @@ cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1
 cudaError_t launch_conv_halo2(int bn, const CUtensorMap& a, const CUtensorMap& b, const HaloParams& p, int max_ctas,
                               int* stat_rows, cudaStream_t stream);   // CTA-pair version (conv_halo2.cu), b box = bn/2 rows
 // CTA-pair (tcgen05.mma.cta_group::2) version of launch_tap_gemm; b has a box of bn/2 rows (conv_gemm2.cu)
-cudaError_t launch_tap_gemm2(int bn, const CUtensorMap& a0, const CUtensorMap& b, const TapGemmParams& p, int max_ctas,
-                             int* stat_rows, cudaStream_t stream);
+cudaError_t launch_tap_gemm2(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                             const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream);
 // 3x3 stride-1 wgrad with halo reuse (conv_wgrad_halo.cu)
 struct WgradHaloParams {
     int cin_slabs, cout_slabs;   // 64-channel slabs

@@ -12,7 +12,9 @@
 //   empty[s]    both CTAs, arrived by the leader's tcgen05.commit multicast: stage s has been consumed
 //   tfull[a]    both CTAs, commit multicast: accumulator a is complete (each CTA reads its own 128 rows from TMEM)
 //   tempty[a]   leader: its own epilogue warps drained accumulator a;  ptempty[a]: the peer's (remote arrive)
-// Not supported here (stay on conv_gemm.cu): output phases (stride-2 dgrad), the second activation map.
+// Output phases (the four parity phases of a stride-2 dgrad, written through a strided output) and the second
+// activation map (the fused 1x1 shortcut dgrad) work as in conv_gemm.cu: the two CTAs of a pair always run the SAME
+// phase and weight tile on adjacent pixel tiles, so they share every B tile and tap sequence.
 #include "b2c_kernels.h"
 #include "b2c_launch.h"
 #include "b2c_ptx.cuh"
@@ -103,8 +105,8 @@ __device__ __forceinline__ void umma2_commit_both(uint64_t* bar) {
 
 template <int BN, bool kStats>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(320, 1)
-tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapB,
-                 const __grid_constant__ TapGemmParams p) {
+tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+                 const __grid_constant__ CUtensorMap mapB, const __grid_constant__ TapGemmParams p) {
     using Cfg = Tap2Cfg<BN>;
     pdl_trigger_big();
     extern __shared__ uint8_t smem_raw[];
@@ -128,6 +130,7 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapA0);
+        tma_prefetch_desc(&mapA1);
         tma_prefetch_desc(&mapB);
     }
     if (warp == 1) {
@@ -157,29 +160,39 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
     const uint32_t tmem_base = *tmem_ptr;
     pdl_wait();
 
-    // pair tiles: (m_pair, n_tile), n_tile fastest; this CTA's pixel tile is 2*m_pair + rank
+    // pair tiles: (m_pair, phase, n_tile), n_tile fastest; this CTA's pixel tile is 2*m_pair + rank. The phase is
+    // rotated by m_pair so that a pair whose tile stride is a multiple of num_phases still sees every phase (they
+    // differ in tap count).
     const int m_pairs = (p.num_m_tiles + 1) >> 1;
-    const int total_tiles = m_pairs * p.num_n_tiles;
+    const int total_tiles = m_pairs * p.num_n_tiles * p.num_phases;
     const int img = p.gH * p.gW;
-    const int ph = 0;
-    auto decode = [&](int tile, int& m_tile, int& n_tile) {
-        const int mp = tile / p.num_n_tiles;
-        n_tile = tile - mp * p.num_n_tiles;
+    auto decode = [&](int tile, int& m_tile, int& n_tile, int& ph) {
+        const int rest = tile / p.num_n_tiles;
+        n_tile = tile - rest * p.num_n_tiles;
+        int mp;
+        if (p.num_phases == 1) {
+            mp = rest;
+            ph = 0;
+        } else {
+            mp = rest / p.num_phases;
+            ph = (rest - mp * p.num_phases + mp) % p.num_phases;
+        }
         m_tile = 2 * mp + static_cast<int>(rank);
     };
-    const int k_iters = p.num_taps * p.k_chunks;
 
     if (warp == 0) {
         // ------------------------------ TMA producer (both CTAs) ------------------------------
         int stage = 0;
         uint32_t phase = 0;
         for (int tile = pair; tile < total_tiles; tile += num_pairs) {
-            int m_tile, n_tile;
-            decode(tile, m_tile, n_tile);
+            int m_tile, n_tile, ph;
+            decode(tile, m_tile, n_tile, ph);
             const int p0 = m_tile * kBM;             // past the last tile for an odd tile count: TMA zero-fills
             const int n0 = p0 / img;
             const int h0 = (p0 - n0 * img) / p.gW;
-            for (int t = 0; t < p.num_taps; ++t) {
+            const int t_end = p.phase_begin[ph + 1];
+            for (int t = p.phase_begin[ph]; t < t_end; ++t) {
+                const CUtensorMap* ma = p.tap_a[t] ? &mapA1 : &mapA0;
                 const int cw = p.tap_dw[t];
                 const int ch = h0 * p.in_stride + p.tap_dh[t];
                 const int brow = p.tap_brow[t] + n_tile * BN + static_cast<int>(rank) * (BN / 2);
@@ -191,9 +204,9 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
                         uint8_t* sa = smem + stage * Cfg::kStageBytes;
                         const uint32_t bar = cluster_addr(&full[stage], 0);
                         if (p.a_split_w)
-                            tma2_load_5d(cluster_addr(sa, rank), &mapA0, bar, kc * 64, cw & 1, cw >> 1, ch, n0);
+                            tma2_load_5d(cluster_addr(sa, rank), ma, bar, kc * 64, cw & 1, cw >> 1, ch, n0);
                         else
-                            tma2_load_4d(cluster_addr(sa, rank), &mapA0, bar, kc * 64, cw, ch, n0);
+                            tma2_load_4d(cluster_addr(sa, rank), ma, bar, kc * 64, cw, ch, n0);
                         tma2_load_2d(cluster_addr(sa + kABytes, rank), &mapB, bar, kc * 64, brow);
                     }
                     __syncwarp();
@@ -214,6 +227,9 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+            int m_tile, n_tile, ph;
+            decode(tile, m_tile, n_tile, ph);
+            const int k_iters = (p.phase_begin[ph + 1] - p.phase_begin[ph]) * p.k_chunks;
             mbar_wait(&tempty[acc], acc_phase ^ 1u, 53);
             mbar_wait(&ptempty[acc], acc_phase ^ 1u, 54);
             tc_fence_after();
@@ -275,8 +291,8 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
         int acc = 0;
         uint32_t acc_phase = 0;
         for (int tile = pair; tile < total_tiles; tile += num_pairs) {
-            int m_tile, n_tile;
-            decode(tile, m_tile, n_tile);
+            int m_tile, n_tile, ph;
+            decode(tile, m_tile, n_tile, ph);
             mbar_wait(&tfull[acc], acc_phase, 4);
             tc_fence_after();
             const int pix = m_tile * kBM + row;
@@ -420,8 +436,8 @@ tap_gemm2_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constan
 }
 
 template <int BN, bool kStats>
-cudaError_t launch_one2(const CUtensorMap& a0, const CUtensorMap& b, const TapGemmParams& p, int max_ctas,
-                        int* stat_rows, cudaStream_t stream) {
+cudaError_t launch_one2(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b, const TapGemmParams& p,
+                        int max_ctas, int* stat_rows, cudaStream_t stream) {
     using Cfg = Tap2Cfg<BN>;
     auto kern = tap_gemm2_kernel<BN, kStats>;
     static bool attr_done = false;  // per instantiation
@@ -430,32 +446,31 @@ cudaError_t launch_one2(const CUtensorMap& a0, const CUtensorMap& b, const TapGe
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles;
+    const int total = ((p.num_m_tiles + 1) / 2) * p.num_n_tiles * p.num_phases;
     int pairs = total < max_ctas / 2 ? total : max_ctas / 2;
     pairs -= pairs % p.num_n_tiles;   // keeps n_tile constant per pair (per-CTA BatchNorm partial rows)
     if (pairs < p.num_n_tiles) pairs = p.num_n_tiles;
     if (stat_rows != nullptr) *stat_rows = 2 * (pairs / p.num_n_tiles);
-    B2C_LAUNCH(kern, 2 * pairs, 320, Cfg::kSmemBytes, stream, a0, b, p);
+    B2C_LAUNCH(kern, 2 * pairs, 320, Cfg::kSmemBytes, stream, a0, a1, b, p);
     return cudaGetLastError();
 }
 
 }  // namespace
 
 // b: 2-D map of the weight matrix with a box of BN/2 rows (each CTA of a pair loads half a tile)
-cudaError_t launch_tap_gemm2(int bn, const CUtensorMap& a0, const CUtensorMap& b, const TapGemmParams& p, int max_ctas,
-                             int* stat_rows, cudaStream_t stream) {
-    if (p.num_phases != 1) return cudaErrorInvalidValue;
+cudaError_t launch_tap_gemm2(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                             const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream) {
     const bool stats = p.part_sum != nullptr;
     switch (bn) {
         case 64:
-            return stats ? launch_one2<64, true>(a0, b, p, max_ctas, stat_rows, stream)
-                         : launch_one2<64, false>(a0, b, p, max_ctas, stat_rows, stream);
+            return stats ? launch_one2<64, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
+                         : launch_one2<64, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
         case 128:
-            return stats ? launch_one2<128, true>(a0, b, p, max_ctas, stat_rows, stream)
-                         : launch_one2<128, false>(a0, b, p, max_ctas, stat_rows, stream);
+            return stats ? launch_one2<128, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
+                         : launch_one2<128, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
         case 256:
-            return stats ? launch_one2<256, true>(a0, b, p, max_ctas, stat_rows, stream)
-                         : launch_one2<256, false>(a0, b, p, max_ctas, stat_rows, stream);
+            return stats ? launch_one2<256, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
+                         : launch_one2<256, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
         default:
             return cudaErrorInvalidValue;
     }

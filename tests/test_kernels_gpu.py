@@ -216,7 +216,8 @@ def test_conv_dgrad(ops, shape, with_add):
 
 @pytest.mark.parametrize("n,h,cin,cout", [(8, 32, 64, 128), (16, 16, 128, 256), (64, 8, 256, 512), (3, 16, 64, 64)])
 @pytest.mark.parametrize("with_add", [False, True])
-def test_conv_dgrad_with_shortcut(ops, n, h, cin, cout, with_add):
+@pytest.mark.parametrize("pair", [0, 128])
+def test_conv_dgrad_with_shortcut(ops, n, h, cin, cout, with_add, pair):
     """3x3 stride-2 dgrad + 1x1 stride-2 shortcut dgrad as one launch (four output phases as tiles) against the sum
     of the two torch input gradients; and the same 3x3 dgrad alone must agree with the traversal-free path."""
     ho = h // 2
@@ -231,7 +232,7 @@ def test_conv_dgrad_with_shortcut(ops, n, h, cin, cout, with_add):
     w10 = torch.cat([ops.pack_weight_dgrad(w3), ops.pack_weight_dgrad(w1)], 0).contiguous()
     assert w10.shape == (10, cin, cout)
     dx = torch.full((n, h, h, cin), float("nan"), device="cuda", dtype=torch.bfloat16)
-    d = ops.conv_desc(n, h, h, cin, cout, 3, 2)
+    d = ops.conv_desc(n, h, h, cin, cout, 3, 2, flags=pair)      # flags bit 7: the CTA-pair kernel
     ops.conv_dgrad_with_shortcut(d, dy, dys, w10, dx, add)
     torch.cuda.synchronize()
     got = to_nchw(dx)
@@ -945,3 +946,22 @@ def test_conv1x1_over_concat(ops, shape):
         torch.cuda.synchronize()
         assert rel_err(to_nchw(dx), gx[:, t * c:(t + 1) * c]) < BF16_TOL
         assert rel_err(dw[0].t(), gw[:, t * c:(t + 1) * c, 0, 0]) < 2e-3
+
+
+@pytest.mark.parametrize("shape", [(8, 32, 32, 64, 128, 3, 2), (16, 16, 16, 128, 256, 3, 2), (64, 8, 8, 256, 512, 3, 2),
+                                   (8, 32, 32, 64, 128, 1, 2), (5, 8, 8, 128, 128, 3, 2), (1024, 32, 32, 64, 128, 3, 2)])
+def test_stride2_dgrad_on_cta_pairs(ops, shape):
+    """flags bit 7 for the stride-2 data gradients: four output parity phases (3x3) / one strided phase (1x1) on the
+    CTA-pair kernel; same result as the single-CTA kernel (same operands, same accumulation order)."""
+    n, h, w, cin, cout, k, stride = shape
+    dy = nhwc_bf16(n, h // 2, w // 2, cout, 111)
+    wd = ops.pack_weight_dgrad(weight(cout, cin, k, 112))
+    outs = []
+    for flags in (0, 128):
+        dx = torch.full((n, h, w, cin), float("nan"), device="cuda", dtype=torch.bfloat16)
+        ops.conv_dgrad(ops.conv_desc(n, h, w, cin, cout, k, stride, flags=flags), dy, wd, dx)
+        outs.append(dx)
+    torch.cuda.synchronize()
+    assert torch.isfinite(outs[1].float()).all() and rel_err(outs[1].float(), outs[0].float()) < 1e-3
+    ref = torch.nn.grad.conv2d_input((n, cin, h, w), weight(cout, cin, k, 112), to_nchw(dy), stride=2, padding=k // 2)
+    assert rel_err(to_nchw(outs[1]), ref) < BF16_TOL
