@@ -1070,6 +1070,18 @@ inline int grid_for(long long work_items, int block, int max_blocks) {
 }  // namespace
 
 // ---------------------------------------- launchers ---------------------------------------------
+// Grid whose stride (grid * 256 threads) is a multiple of C/8 vectors, so a thread meets the same 8 channels in every
+// iteration: round the preferred grid down to a multiple of cvec / gcd(cvec, 256).
+static int uniform_grid(long long nvec, int cvec) {
+    int g = grid_for(nvec, 256, 148 * 8);
+    int a = cvec, b = 256;
+    while (b != 0) { const int t = a % b; a = b; b = t; }
+    const int unit = cvec / a;
+    if (g >= unit) g -= g % unit;
+    else g = unit;
+    return g;
+}
+
 cudaError_t launch_bn_finalize(const float* part_sum, const float* part_sq, int rows, int C, float count,
                                const float* gamma, const float* beta, const float* conv_bias, float eps,
                                float momentum, float* running_mean, float* running_var, float* scale, float* shift,
@@ -1090,7 +1102,9 @@ cudaError_t launch_bn_act_apply(const void* y, const float* scale, const float* 
                                 const float* res_scale, const float* res_shift, void* out, long long rows, int C,
                                 int relu, uint8_t* relu_bits, cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
-    const int grid = grid_for(nvec, 256, 148 * 8);
+    // a grid whose stride is a multiple of C/8: every channel count takes the register-resident (kUniform) variant
+    // (MobileNetV2's 96 / 144 / 192 / 576 / 960-channel layers fell to the per-iteration parameter loads otherwise)
+    const int grid = uniform_grid(nvec, C >> 3);
     const bool uniform = (static_cast<long long>(grid) * 256) % (C >> 3) == 0;
     const bool affine = res != nullptr && res_scale != nullptr;
     auto go = [&](auto kern) {
@@ -1152,7 +1166,7 @@ cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coef
                                 const float* coefC, const void* add, void* dy, long long rows, int C,
                                 const float* relu_scale, const float* relu_shift, cudaStream_t s) {
     const long long nvec = rows * (C >> 3);
-    const int grid = grid_for(nvec, 256, 148 * 8);
+    const int grid = uniform_grid(nvec, C >> 3);
     const bool uniform = (static_cast<long long>(grid) * 256) % (C >> 3) == 0;
     const bool masky = relu_scale != nullptr;
     auto go = [&](auto kern) {
@@ -1165,18 +1179,6 @@ cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coef
     else if (masky) go(bn_bwd_apply_kernel<false, true>);
     else go(bn_bwd_apply_kernel<false, false>);
     return cudaGetLastError();
-}
-
-// Grid whose stride (grid * 256 threads) is a multiple of C/8 vectors, so a thread meets the same 8 channels in every
-// iteration: round the preferred grid down to a multiple of cvec / gcd(cvec, 256).
-static int uniform_grid(long long nvec, int cvec) {
-    int g = grid_for(nvec, 256, 148 * 8);
-    int a = cvec, b = 256;
-    while (b != 0) { const int t = a % b; a = b; b = t; }
-    const int unit = cvec / a;
-    if (g >= unit) g -= g % unit;
-    else g = unit;
-    return g;
 }
 
 cudaError_t launch_bn_act_apply_stats(const void* y, const BnStatArgs& st, const void* res, const BnStatArgs* rst,
