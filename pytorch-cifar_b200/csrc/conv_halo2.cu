@@ -324,7 +324,8 @@ conv_halo2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
         }
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        // Row offsets of this lane's output rows in tile `tile` (rows past the end: ~0) and the tile's first column.
+        auto tile_rows = [&](int tile, unsigned long long (&ro)[4], int& col0) {
             const int m_pair = tile / p.num_n_tiles;
             const int n_tile = tile - m_pair * p.num_n_tiles;
             const int m_tile = 2 * m_pair + static_cast<int>(rank);
@@ -342,10 +343,49 @@ conv_halo2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
             }
             const bool valid = n < p.N;
             const size_t off = (static_cast<size_t>(n * p.H + h) * p.W + w) * p.out_ld;
-            const int col0 = n_tile * BN;
-            unsigned long long rowoff[4];
-            chunk_rowoffs(off, valid, lane, rowoff);
-            uint8_t* stg_w = store_stage + (warp - 2) * 2048;
+            col0 = n_tile * BN;
+            chunk_rowoffs(off, valid, lane, ro);
+        };
+        uint8_t* stg_w = store_stage + (warp - 2) * 2048;
+        // 64-wide tiles: a warp reads ONE 32x32 chunk of the epilogue operand (the residual / add_src, or y of the fused
+        // BatchNorm backward) per tile, and the tile's MMAs take ~0.8 us — less than a global load's latency, so a load
+        // issued after the accumulator wait makes the epilogue, not the tensor pipe, set the pace (layer-1 dgrad: 102 -
+        // 115 us against 68 us for the same GEMM as fprop). The operand of the NEXT tile is therefore requested one
+        // tile ahead: its raw 16-byte pieces travel in registers across the accumulator wait and are parked in the
+        // warp's shared-memory stage (the transpose the synchronous path does anyway) at the top of their own tile.
+        constexpr bool kPre = BN == 64;
+        const __nv_bfloat16* pre_src = nullptr;
+        // (one operand at a time: with both a residual and a fused BatchNorm backward the synchronous loads stay)
+        if (kPre) pre_src = bwd_fused ? (p.add_src != nullptr ? nullptr : p.bwd_y) : p.add_src;
+        uint4 raw[4];
+        unsigned long long rowoff[4];
+        int col0 = 0;
+        auto request = [&](const unsigned long long (&ro)[4], int col) {
+#pragma unroll
+            for (int it = 0; it < 4; ++it) {
+                raw[it] = make_uint4(0u, 0u, 0u, 0u);
+                if (ro[it] != ~0ull)
+                    raw[it] = __ldg(reinterpret_cast<const uint4*>(pre_src + ro[it] + col + (lane & 3) * 8));
+            }
+        };
+        if (pre_src != nullptr && pair < total_tiles) {
+            tile_rows(pair, rowoff, col0);
+            request(rowoff, col0 + half * 32);
+        }
+        for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+            if (pre_src != nullptr) {
+                __syncwarp();                               // earlier reads of the stage are done
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int r = it * 8 + (lane >> 2);
+                    *reinterpret_cast<uint4*>(stg_w + r * 64 + (((lane & 3) ^ ((r >> 1) & 3)) << 4)) = raw[it];
+                }
+                if (tile + num_pairs < total_tiles) {       // the next tile's operand: only `raw` outlives the wait
+                    tile_rows(tile + num_pairs, rowoff, col0);
+                    request(rowoff, col0 + half * 32);
+                }
+            }
+            tile_rows(tile, rowoff, col0);
             mbar_wait(&tfull[acc], acc_phase, 26);
             tc_fence_after();
 #pragma unroll 1
@@ -354,9 +394,20 @@ conv_halo2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                 tmem_ld_32x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                                   static_cast<uint32_t>(acc * BN + c * 32),
                               v);
+                auto unpark = [&](uint4 (&u)[4]) {          // the operand parked at the top of this tile
+                    __syncwarp();
+                    const uint4* prow = reinterpret_cast<const uint4*>(stg_w + lane * 64);
+                    const int sw = (lane >> 1) & 3;
+#pragma unroll
+                    for (int g4 = 0; g4 < 4; ++g4) u[g4] = prow[g4 ^ sw];
+                };
                 if (p.add_src != nullptr) {
                     uint4 au[4];
-                    load_chunk_staged(stg_w, p.add_src, rowoff, col0 + c * 32, au, lane);
+                    if (pre_src == p.add_src) {
+                        unpark(au);
+                    } else {
+                        load_chunk_staged(stg_w, p.add_src, rowoff, col0 + c * 32, au, lane);
+                    }
 #pragma unroll
                     for (int g4 = 0; g4 < 4; ++g4) {
                         v[g4 * 8 + 0] += bf16lo(au[g4].x);
@@ -375,7 +426,11 @@ conv_halo2_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constan
                         const float* scs = bwd_sc + c * 32;
                         const float* shs = bwd_sc + BN + c * 32;
                         uint4 yall[4];
-                        load_chunk_staged(stg_w, p.bwd_y, rowoff, col0 + c * 32, yall, lane);
+                        if (pre_src == p.bwd_y) {
+                            unpark(yall);
+                        } else {
+                            load_chunk_staged(stg_w, p.bwd_y, rowoff, col0 + c * 32, yall, lane);
+                        }
 #pragma unroll
                         for (int g4 = 0; g4 < 4; ++g4) {
                             const uint4 yu = yall[g4];
