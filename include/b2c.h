@@ -138,6 +138,19 @@ B2C_API int b2c_dwconv_fprop(const void* x, const float* weight, void* y, int n,
  * sumsq[channels], for b2c_bn_act_apply_stats. */
 B2C_API int b2c_dwconv_fprop_acc(const void* x, const float* weight, void* y, int n, int h, int w, int channels, int c_valid,
                          int stride, float* sum, float* sumsq, void* stream);
+/* The depthwise conv fed straight from the conv before it: `out = F.relu(self.bn1(self.conv1(x)))` followed by
+ * `self.conv2` (groups = planes), models/mobilenetv2.py:32-33. y_prev is conv1's RAW output; the kernel applies that
+ * BatchNorm + ReLU while loading, x = relu(y_prev * in_scale[c] + in_shift[c]) (scale / shift from b2c_bn_finalize), and
+ * pads with zeros AFTER the transform, so the activation between the two convs is never written or re-read — the BN
+ * apply lives in its consumer. Stride 1 only, shapes for which b2c_dwconv_input_transform_ok returns 1 (else
+ * B2C_ERR_UNSUPPORTED: use b2c_bn_act_apply + b2c_dwconv_fprop). accumulate != 0: statistics as in b2c_dwconv_fprop_acc.
+ * The matching weight gradient reads the same y_prev the same way; the data gradient needs no variant. */
+B2C_API int b2c_dwconv_input_transform_ok(int h, int w, int channels, int stride);
+B2C_API int b2c_dwconv_fprop_bnrelu(const void* y_prev, const float* in_scale, const float* in_shift, const float* weight,
+                            void* y, int n, int h, int w, int channels, int c_valid, float* part_sum, float* part_sq,
+                            int* stat_rows, int accumulate, void* stream);
+B2C_API int b2c_dwconv_wgrad_bnrelu(const void* y_prev, const float* in_scale, const float* in_shift, const void* dy,
+                            float* dweight, int n, int h, int w, int channels, int c_valid, void* stream);
 B2C_API int b2c_dwconv_dgrad(const void* dy, const float* weight, void* dx, int n, int h, int w, int channels, int c_valid,
                      int stride, void* stream);
 B2C_API int b2c_dwconv_wgrad(const void* x, const void* dy, float* dweight, int n, int h, int w, int channels, int c_valid,

@@ -73,6 +73,9 @@ SIGNATURES = {
     "b2c_conv_wgrad": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _LL, _P],
     "b2c_dwconv_stat_rows": [_LL, _I],
     "b2c_dwconv_fprop": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, ctypes.POINTER(_I), _P],
+    "b2c_dwconv_input_transform_ok": [_I, _I, _I, _I],
+    "b2c_dwconv_fprop_bnrelu": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P, _P, ctypes.POINTER(_I), _I, _P],
+    "b2c_dwconv_wgrad_bnrelu": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P],
     "b2c_dwconv_dgrad": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
     "b2c_dwconv_wgrad": [_P, _P, _P, _I, _I, _I, _I, _I, _I, _P],
     "b2c_bn_finalize": [_P, _P, _I, _I, _F, _P, _P, _P, _F, _F, _P, _P, _P, _P, _P, _P, _P],
@@ -113,7 +116,8 @@ class _LibProxy:
 
     def __getattr__(self, name):
         fn = getattr(self._cdll, name)
-        if name in ("b2c_error_string", "b2c_version", "b2c_bn_bwd_partial_rows", "b2c_dwconv_stat_rows"):
+        if name in ("b2c_error_string", "b2c_version", "b2c_bn_bwd_partial_rows", "b2c_dwconv_stat_rows",
+                    "b2c_dwconv_input_transform_ok"):
             return fn
 
         def call(*args):

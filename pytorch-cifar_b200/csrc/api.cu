@@ -670,6 +670,33 @@ int b2c_dwconv_fprop_acc(const void* x, const float* weight, void* y, int n, int
                                         as_stream(stream), 1));
 }
 
+int b2c_dwconv_input_transform_ok(int h, int w, int channels, int stride) {
+    if (channels < 8 || (channels & 7) || (channels >> 3) > 256) return 0;
+    return b2c::dw_input_transform_ok(h, w, channels, stride) ? 1 : 0;
+}
+
+int b2c_dwconv_fprop_bnrelu(const void* y_prev, const float* in_scale, const float* in_shift, const float* weight,
+                            void* y, int n, int h, int w, int channels, int c_valid, float* part_sum, float* part_sq,
+                            int* stat_rows, int accumulate, void* stream) {
+    int rc = check_dw(y_prev, weight, y, n, h, w, channels, c_valid, 1);
+    if (rc) return rc;
+    if (!in_scale || !in_shift || !aligned16(y_prev) || !aligned16(y) || (part_sum == nullptr) != (part_sq == nullptr))
+        return B2C_ERR_ARG;
+    if (!b2c::dw_input_transform_ok(h, w, channels, 1)) return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_dw_fprop_xf(y_prev, in_scale, in_shift, weight, y, n, h, w, channels, c_valid, part_sum,
+                                           part_sq, stat_rows, as_stream(stream), accumulate ? 1 : 0));
+}
+
+int b2c_dwconv_wgrad_bnrelu(const void* y_prev, const float* in_scale, const float* in_shift, const void* dy,
+                            float* dweight, int n, int h, int w, int channels, int c_valid, void* stream) {
+    int rc = check_dw(y_prev, dy, dweight, n, h, w, channels, c_valid, 1);
+    if (rc) return rc;
+    if (!in_scale || !in_shift || !aligned16(y_prev) || !aligned16(dy)) return B2C_ERR_ARG;
+    if (!b2c::dw_input_transform_ok(h, w, channels, 1)) return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_dw_wgrad_xf(y_prev, in_scale, in_shift, dy, dweight, n, h, w, channels, c_valid,
+                                           as_stream(stream)));
+}
+
 int b2c_dwconv_dgrad(const void* dy, const float* weight, void* dx, int n, int h, int w, int channels, int c_valid,
                      int stride, void* stream) {
     int rc = check_dw(dy, weight, dx, n, h, w, channels, c_valid, stride);

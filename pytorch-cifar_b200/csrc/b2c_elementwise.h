@@ -80,6 +80,13 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
 int dw_fprop_partial_rows(long long out_pixels, int C);
 cudaError_t launch_dw_fprop(const void* x, const float* w, void* y, int N, int H, int W, int C, int c_valid, int stride,
                             float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s, int stat_acc = 0);
+// Depthwise fprop / wgrad whose input is the preceding conv's raw output, BatchNorm + ReLU applied on load.
+bool dw_input_transform_ok(int H, int W, int C, int stride);
+cudaError_t launch_dw_fprop_xf(const void* y_prev, const float* in_scale, const float* in_shift, const float* w, void* y,
+                               int N, int H, int W, int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows,
+                               cudaStream_t s, int stat_acc);
+cudaError_t launch_dw_wgrad_xf(const void* y_prev, const float* in_scale, const float* in_shift, const void* dy,
+                               float* dw, int N, int H, int W, int C, int c_valid, cudaStream_t s);
 cudaError_t launch_dw_dgrad(const void* dy, const float* w, void* dx, int N, int H, int W, int C, int c_valid,
                             int stride, cudaStream_t s);
 cudaError_t launch_dw_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int c_valid,

@@ -217,11 +217,16 @@ __device__ __forceinline__ void unpack4(const uint2& u, float (&f)[4]) {
     f[0] = bf16lo(u.x); f[1] = bf16hi(u.x); f[2] = bf16lo(u.y); f[3] = bf16hi(u.y);
 }
 
-template <int MODE, int T>
+// XF (MODE 0 / 2): `in` is the raw output y of the preceding conv and the kernel applies that conv's BatchNorm + ReLU
+// while loading, x = relu(fma(y, in_scale[c], in_shift[c])) — `out = F.relu(self.bn1(self.conv1(x)))` feeding
+// `self.conv2` (depthwise), models/mobilenetv2.py:32-33 — so the activation between the two is never written or
+// re-read. Zero padding is applied AFTER the transform (a padded pixel is 0, not relu(shift)).
+template <int MODE, int T, bool XF = false>
 __global__ void __launch_bounds__(256)
 dw_strip_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, const float* __restrict__ wt,
                 uint2* __restrict__ out, float* __restrict__ dw, int N, int H, int W, int C, int c_valid,
-                float* __restrict__ part_sum, float* __restrict__ part_sq, int stat_acc) {
+                float* __restrict__ part_sum, float* __restrict__ part_sq, int stat_acc,
+                const float* __restrict__ in_scale = nullptr, const float* __restrict__ in_shift = nullptr) {
     pdl_trigger_ew();
     pdl_wait();
     extern __shared__ float red[];   // MODE 0: [rpi][2][C]; MODE 2: [rpi][9][C]
@@ -242,6 +247,14 @@ dw_strip_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, con
         }
     float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
     const uint2 zero = make_uint2(0u, 0u);
+    float xsc[4] = {1.f, 1.f, 1.f, 1.f}, xsh[4] = {0.f, 0.f, 0.f, 0.f};
+    if (XF) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            xsc[e] = __ldg(in_scale + cq * 4 + e);
+            xsh[e] = __ldg(in_shift + cq * 4 + e);
+        }
+    }
 
     for (long long it = static_cast<long long>(blockIdx.x) * rpi + rl; active && it < items;
          it += static_cast<long long>(gridDim.x) * rpi) {
@@ -253,27 +266,38 @@ dw_strip_kernel(const uint2* __restrict__ in, const uint2* __restrict__ in2, con
         // row pointer arithmetic in units of uint2 (4 channels)
         const uint2* base = in + ((n * H) * W + wo) * cq_n + cq;
         const long long row_pitch = static_cast<long long>(W) * cq_n;
+        bool rok = false;        // the row held in `raw` lies inside the image
         auto load_row = [&](int h, uint2 (&r)[3]) {
-            if (h < 0 || h >= H) { r[0] = zero; r[1] = zero; r[2] = zero; return; }
+            rok = h >= 0 && h < H;
+            if (!rok) { r[0] = zero; r[1] = zero; r[2] = zero; return; }
             const uint2* p = base + h * row_pitch;
             r[0] = left ? __ldg(p - cq_n) : zero;
             r[1] = __ldg(p);
             r[2] = right ? __ldg(p + cq_n) : zero;
         };
+        // raw row -> fp32 window slot; with XF the preceding BatchNorm + ReLU is applied to pixels inside the image
+        auto unpack_row = [&](const uint2 (&r)[3], float (&dst)[3][4]) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                unpack4(r[c], dst[c]);
+                if (XF) {
+                    const bool ok = rok && (c == 1 || (c == 0 ? left : right));
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) dst[c][e] = ok ? fmaxf(fmaf(dst[c][e], xsc[e], xsh[e]), 0.f) : 0.f;
+                }
+            }
+        };
         float win[3][3][4];      // [row slot][col][channel]; slot = input row modulo 3 (static after unrolling)
         uint2 raw[3];
         load_row(h0 - 1, raw);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) unpack4(raw[c], win[0][c]);
+        unpack_row(raw, win[0]);
         load_row(h0, raw);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) unpack4(raw[c], win[1][c]);
+        unpack_row(raw, win[1]);
         load_row(h0 + 1, raw);               // prefetched one row ahead of its use
 #pragma unroll
         for (int i = 0; i < T; ++i) {
             // rows h0+i-1, h0+i, h0+i+1 live in slots i%3, (i+1)%3, (i+2)%3
-#pragma unroll
-            for (int c = 0; c < 3; ++c) unpack4(raw[c], win[(i + 2) % 3][c]);
+            unpack_row(raw, win[(i + 2) % 3]);
             if (i + 1 < T) load_row(h0 + i + 2, raw);
             const long long opix = ((n * H + h0 + i) * W + wo) * cq_n + cq;
             if (MODE == 2) {
@@ -598,7 +622,8 @@ cudaError_t launch_dw_strip2(const void* in, const void* in2, const float* w, vo
 
 template <int MODE>
 cudaError_t launch_dw_strip(const void* in, const void* in2, const float* w, void* out, float* dw, int N, int H, int W,
-                            int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s, int stat_acc = 0) {
+                            int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t s, int stat_acc = 0,
+                            const float* in_scale = nullptr, const float* in_shift = nullptr) {
     const int cq_n = C >> 2;
     const int rpi = 256 / cq_n;
     const int T = (H % 8) == 0 ? 8 : 4;
@@ -613,27 +638,47 @@ cudaError_t launch_dw_strip(const void* in, const void* in2, const float* w, voi
     if (MODE == 2) smem = static_cast<size_t>(rpi) * 9 * C * sizeof(float);
     auto k8 = dw_strip_kernel<MODE, 8>;
     auto k4 = dw_strip_kernel<MODE, 4>;
+    constexpr bool kCanXf = MODE != 1;
+    auto x8 = dw_strip_kernel<MODE, 8, kCanXf>;       // input transformed on load (fprop / wgrad only)
+    auto x4 = dw_strip_kernel<MODE, 4, kCanXf>;
+    const bool xf = in_scale != nullptr;
+    if (xf && (!kCanXf || in_shift == nullptr)) return cudaErrorInvalidValue;
     if (MODE == 2) {
         static bool attr_done = false;
         if (!attr_done) {
             cudaError_t e = cudaFuncSetAttribute(k8, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
             if (e == cudaSuccess) e = cudaFuncSetAttribute(k4, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(x8, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(x4, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
             if (e != cudaSuccess) return e;
             attr_done = true;
         }
     }
-    if (T == 8)
-        B2C_LAUNCH(k8, static_cast<int>(blocks), 256, smem, s, static_cast<const uint2*>(in),
-                   static_cast<const uint2*>(in2), w, static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum,
-                   part_sq, stat_acc);
-    else
-        B2C_LAUNCH(k4, static_cast<int>(blocks), 256, smem, s, static_cast<const uint2*>(in),
-                   static_cast<const uint2*>(in2), w, static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum,
-                   part_sq, stat_acc);
+    auto kern = T == 8 ? (xf ? x8 : k8) : (xf ? x4 : k4);
+    B2C_LAUNCH(kern, static_cast<int>(blocks), 256, smem, s, static_cast<const uint2*>(in),
+               static_cast<const uint2*>(in2), w, static_cast<uint2*>(out), dw, N, H, W, C, c_valid, part_sum,
+               part_sq, stat_acc, in_scale, in_shift);
     return cudaGetLastError();
 }
 
 }  // namespace
+
+bool dw_input_transform_ok(int H, int W, int C, int stride) { return dw_strip_ok(H, W, C, stride); }
+
+cudaError_t launch_dw_fprop_xf(const void* y_prev, const float* in_scale, const float* in_shift, const float* w, void* y,
+                               int N, int H, int W, int C, int c_valid, float* part_sum, float* part_sq, int* stat_rows,
+                               cudaStream_t s, int stat_acc) {
+    if (!dw_strip_ok(H, W, C, 1)) return cudaErrorInvalidValue;
+    return launch_dw_strip<0>(y_prev, nullptr, w, y, nullptr, N, H, W, C, c_valid, part_sum, part_sq, stat_rows, s,
+                              stat_acc, in_scale, in_shift);
+}
+
+cudaError_t launch_dw_wgrad_xf(const void* y_prev, const float* in_scale, const float* in_shift, const void* dy,
+                               float* dw, int N, int H, int W, int C, int c_valid, cudaStream_t s) {
+    if (!dw_strip_ok(H, W, C, 1)) return cudaErrorInvalidValue;
+    return launch_dw_strip<2>(y_prev, dy, nullptr, nullptr, dw, N, H, W, C, c_valid, nullptr, nullptr, nullptr, s, 0,
+                              in_scale, in_shift);
+}
 
 int dw_fprop_partial_rows(long long out_pixels, int C) {
     const int rpi = 256 / (C >> 3);

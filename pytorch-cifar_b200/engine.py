@@ -381,6 +381,10 @@ TCO_LAYOUT = os.environ.get("B2C_TCO_LAYOUT", "1") != "0"
 # 1 = weight-gradient kernels run on a side stream, concurrently with the data-gradient chain that does not
 # depend on them (fork after the BN backward that produced dy, join before the optimizer / the bucket's all-reduce)
 ASYNC_WGRAD = os.environ.get("B2C_ASYNC_WGRAD", "1") != "0"
+# 1 = a stride-1 depthwise conv reads the RAW output of the 1x1 conv before it and applies that conv's BatchNorm + ReLU
+# while loading (b2c_dwconv_fprop_bnrelu / b2c_dwconv_wgrad_bnrelu): the expanded activation of a MobileNetV2 block —
+# its widest tensor — is never written or re-read; 0 = separate b2c_bn_act_apply pass
+DW_FUSED_INPUT = os.environ.get("B2C_DW_FUSED_INPUT", "1") != "0"
 # CTA-pair (tcgen05.mma.cta_group::2) fprop / dgrad kernels: "halo" = where the halo kernel runs (3x3 stride 1 on
 # 32/16/8-pixel images), "all" = the per-tap kernel's shapes too, "0" = single-CTA kernels everywhere
 CTA_PAIR = os.environ.get("B2C_CTA_PAIR", "all")
@@ -409,6 +413,17 @@ class _BNOps:
         else:
             ops.bn_eval_scale_shift(self.cout, self.gamma, self.beta, self.rm, self.rv, BN_EPS, self.scale,
                                     self.shift, conv_bias=getattr(self, "conv_bias", None))
+
+    def bn_scale_shift(self, eng, training):
+        """Only the BatchNorm's scale / shift / saved statistics / running statistics: for a unit whose apply pass is
+        folded into its consumer (DwUnit with src_unit)."""
+        if FUSED_FINALIZE and training:      # statistics were accumulated into one row by the producer
+            C = self.cout
+            ops.bn_finalize(self.fsum[:C], self.fsum[C:], 1, C, self.rows, self.gamma, self.beta, BN_EPS, BN_MOMENTUM,
+                            self.rm, self.rv, self.scale, self.shift, self.mean, self.rstd,
+                            conv_bias=getattr(self, "conv_bias", None))
+        else:
+            self.bn_stats(eng, training)
 
     def bn_apply(self, eng, training, out, relu=True, res=None, res_unit=None, relu_bits=None):
         """out = act(bn(y) + residual), residual = `res` (identity shortcut) or res_unit's own BatchNorm of
@@ -575,8 +590,11 @@ class RootUnit(_BNOps):
 class DwUnit(_BNOps):
     """Depthwise 3x3 conv + BatchNorm (models/mobilenetv2.py:20-21)."""
 
-    def __init__(self, eng, name, bn_name, x, C, stride, H, W):
+    def __init__(self, eng, name, bn_name, x, C, stride, H, W, src_unit=None):
+        """src_unit: the conv + BatchNorm unit whose relu(bn(y)) is this conv's input, when that activation is not
+        materialised (x is None): the kernels read src_unit.y and apply src_unit.scale / shift + ReLU on load."""
         N = eng.N
+        self.src = src_unit
         self.name, self.c_true, self.stride, self.H, self.W = name, C, stride, H, W
         self.cout = _pad64(C)
         self.Ho, self.Wo = H // stride, W // stride
@@ -591,7 +609,15 @@ class DwUnit(_BNOps):
         _bn_views(self, eng, bn_name, self.cout)
 
     def fprop(self, eng):
-        if FUSED_FINALIZE:
+        if self.src is not None:
+            u = self.src
+            if FUSED_FINALIZE:
+                self.stat_rows = ops.dwconv_fprop_bnrelu(u.y, u.scale, u.shift, self.w, self.y, self.c_true,
+                                                         self.fsum[:self.cout], self.fsum[self.cout:], accumulate=True)
+            else:
+                self.stat_rows = ops.dwconv_fprop_bnrelu(u.y, u.scale, u.shift, self.w, self.y, self.c_true,
+                                                         eng.part_sum, eng.part_sq)
+        elif FUSED_FINALIZE:
             ops.dwconv_fprop_acc(self.x, self.w, self.y, self.c_true, self.stride, self.fsum[:self.cout],
                                  self.fsum[self.cout:])
             self.stat_rows = 1
@@ -600,7 +626,11 @@ class DwUnit(_BNOps):
                                               eng.part_sq)
 
     def wgrad(self, dy):
-        self.eng.run_side(lambda: ops.dwconv_wgrad(self.x, dy, self.dw, self.c_true, self.stride))
+        if self.src is not None:
+            u = self.src
+            self.eng.run_side(lambda: ops.dwconv_wgrad_bnrelu(u.y, u.scale, u.shift, dy, self.dw, self.c_true))
+        else:
+            self.eng.run_side(lambda: ops.dwconv_wgrad(self.x, dy, self.dw, self.c_true, self.stride))
 
     def dgrad(self, dy, dx):
         ops.dwconv_dgrad(dy, self.w, dx, self.c_true, self.stride)
@@ -1339,8 +1369,9 @@ class Engine:
         for b in spec["blocks"]:
             name, cin, cout, planes, s = b["name"], b["cin"], b["cout"], b["planes"], b["stride"]
             c1 = ConvUnit(self, name + ".conv1", name + ".bn1", x, cin, planes, 1, 1, H, W)
-            a1 = self.new_act(N, H, W, c1.cout)
-            dw = DwUnit(self, name + ".conv2", name + ".bn2", a1, planes, s, H, W)
+            fused_in = DW_FUSED_INPUT and ops.dwconv_input_transform_ok(H, W, c1.cout, s)
+            a1 = None if fused_in else self.new_act(N, H, W, c1.cout)
+            dw = DwUnit(self, name + ".conv2", name + ".bn2", a1, planes, s, H, W, src_unit=c1 if fused_in else None)
             Ho, Wo = H // s, W // s
             a2 = self.new_act(N, Ho, Wo, dw.cout)
             c3 = ConvUnit(self, name + ".conv3", name + ".bn3", a2, planes, cout, 1, 1, Ho, Wo)
@@ -1355,7 +1386,10 @@ class Engine:
                 if cs is not None:          # shortcut branch on the side stream (own statistics scratch)
                     self.run_side(lambda: (cs.fprop(self), None if (FUSED_FINALIZE and training) else cs.bn_stats(self, training)))
                 c1.fprop(self)
-                c1.bn_apply(self, training, a1)
+                if a1 is None:          # relu(bn1(.)) is applied by the depthwise kernels while they load c1.y
+                    c1.bn_scale_shift(self, training)
+                else:
+                    c1.bn_apply(self, training, a1)
                 dw.fprop(self)
                 dw.bn_apply(self, training, a2)
                 c3.fprop(self)
@@ -1391,7 +1425,7 @@ class Engine:
             dys = self.new_act(*cs.y.shape) if cs is not None else None
             da2 = self.new_act(*a2.shape)
             dy2 = self.new_act(*dw.y.shape)
-            da1 = self.new_act(*a1.shape)
+            da1 = self.new_act(*c1.y.shape)
             dy1 = self.new_act(*c1.y.shape)
             dx = self.new_act(*xin.shape)
 

@@ -132,6 +132,31 @@ def dwconv_fprop_acc(x, weight, y, c_valid, stride, stat_sum, stat_sq):
                                    _stream()), "b2c_dwconv_fprop_acc")
 
 
+def dwconv_input_transform_ok(h, w, channels, stride):
+    return _lib.load().b2c_dwconv_input_transform_ok(h, w, channels, stride) == 1
+
+
+def dwconv_fprop_bnrelu(y_prev, in_scale, in_shift, weight, y, c_valid, part_sum=None, part_sq=None, accumulate=False):
+    """Depthwise 3x3 stride 1 over relu(bn(y_prev)), the BatchNorm + ReLU applied while loading; returns stat rows."""
+    lib = _lib.load()
+    n, h, w, c = y_prev.shape
+    _need(y_prev, torch.bfloat16, "y_prev"); _need(y, torch.bfloat16, "y"); _need(weight, torch.float32, "weight")
+    _need(in_scale, torch.float32, "in_scale"); _need(in_shift, torch.float32, "in_shift")
+    rows = ctypes.c_int(0)
+    check(lib.b2c_dwconv_fprop_bnrelu(_p(y_prev), _p(in_scale), _p(in_shift), _p(weight), _p(y), n, h, w, c, c_valid,
+                                      _p(part_sum), _p(part_sq), ctypes.byref(rows), 1 if accumulate else 0, _stream()),
+          "b2c_dwconv_fprop_bnrelu")
+    return rows.value
+
+
+def dwconv_wgrad_bnrelu(y_prev, in_scale, in_shift, dy, dweight, c_valid):
+    lib = _lib.load()
+    n, h, w, c = y_prev.shape
+    _need(dweight, torch.float32, "dweight")
+    check(lib.b2c_dwconv_wgrad_bnrelu(_p(y_prev), _p(in_scale), _p(in_shift), _p(dy), _p(dweight), n, h, w, c, c_valid,
+                                      _stream()), "b2c_dwconv_wgrad_bnrelu")
+
+
 def dwconv_dgrad(dy, weight, dx, c_valid, stride):
     lib = _lib.load()
     n, h, w, c = dx.shape

@@ -322,3 +322,50 @@ def test_prefetched_host_batches_match_resident_dataset(ops):
     for k in range(steps):     # later steps differ only by the summation order of the fp32 wgrad atomics
         assert abs(out["host"][k] - out["resident"][k]) < 2e-2 * out["resident"][0]
         assert abs(out["prefetch"][k] - out["resident"][k]) < 2e-2 * out["resident"][0]
+
+
+@pytest.mark.parametrize("shape", [(4, 32, 32, 128, 96), (8, 16, 16, 192, 192), (16, 8, 8, 384, 384), (32, 4, 4, 960, 960),
+                                   (3, 8, 8, 64, 64)])
+def test_depthwise_conv_fed_by_the_previous_batchnorm(ops, shape):
+    """b2c_dwconv_fprop_bnrelu / b2c_dwconv_wgrad_bnrelu: the depthwise conv reads the previous conv's raw output and
+    applies relu(y * scale + shift) while loading (models/mobilenetv2.py:32-33), zero padding after the transform.
+    Against fp32 torch on the materialised activation, and against the two-pass path (b2c_bn_act_apply, then
+    b2c_dwconv_fprop / wgrad), which differs only by the bf16 rounding of the intermediate it stores."""
+    n, h, w, cpad, c = shape
+    g = torch.Generator(device="cuda").manual_seed(70)
+    yprev = torch.zeros(n, h, w, cpad, device="cuda", dtype=torch.bfloat16)
+    yprev[..., :c] = (torch.randn(n, h, w, c, device="cuda", generator=g) * 1.5).to(torch.bfloat16)
+    scale = torch.zeros(cpad, device="cuda"); shift = torch.zeros(cpad, device="cuda")
+    scale[:c] = torch.rand(c, device="cuda", generator=g) + 0.5
+    shift[:c] = torch.randn(c, device="cuda", generator=g) * 0.5          # relu(shift) != 0: padding must not see it
+    wt = torch.randn(c, 1, 3, 3, device="cuda", generator=g) * 0.3
+    assert ops.dwconv_input_transform_ok(h, w, cpad, 1) and not ops.dwconv_input_transform_ok(h, w, cpad, 2)
+    a_ref = F.relu(yprev[..., :c].float() * scale[:c] + shift[:c]).permute(0, 3, 1, 2)
+    y_ref = F.conv2d(a_ref, wt, padding=1, groups=c)
+    dy = torch.zeros(n, h, w, cpad, device="cuda", dtype=torch.bfloat16)
+    dy[..., :c] = torch.randn(n, h, w, c, device="cuda", generator=g).to(torch.bfloat16)
+    dw_ref = torch.nn.grad.conv2d_weight(a_ref, (c, 1, 3, 3), dy[..., :c].float().permute(0, 3, 1, 2), padding=1, groups=c)
+    # fused
+    y = torch.full((n, h, w, cpad), float("nan"), device="cuda", dtype=torch.bfloat16)
+    ps = torch.zeros(ops.MAX_DW_STAT_ROWS, cpad, device="cuda"); pq = torch.zeros_like(ps)
+    rows = ops.dwconv_fprop_bnrelu(yprev, scale, shift, wt, y, c, ps, pq)
+    dw = torch.zeros(c, 1, 3, 3, device="cuda")
+    ops.dwconv_wgrad_bnrelu(yprev, scale, shift, dy, dw, c)
+    # two passes
+    a = torch.empty_like(yprev)
+    ops.bn_act_apply(yprev, scale, shift, a, n * h * w, cpad, relu=True)
+    y2 = torch.empty_like(y)
+    ops.dwconv_fprop(a, wt, y2, c, 1)
+    dw2 = torch.zeros(c, 1, 3, 3, device="cuda")
+    ops.dwconv_wgrad(a, dy, dw2, c, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(y.float()).all() and (y[..., c:] == 0).all()
+    assert rel(y[..., :c].float().permute(0, 3, 1, 2), y_ref) < 1e-2
+    assert rel(y.float(), y2.float()) < 1e-2
+    assert rel(ps[:rows].sum(0)[:c], y_ref.sum((0, 2, 3))) < 5e-3 or (ps[:rows].sum(0)[:c] - y_ref.sum((0, 2, 3))).abs().max() < 0.5
+    assert rel(pq[:rows].sum(0)[:c], (y_ref ** 2).sum((0, 2, 3))) < 2e-3
+    assert rel(dw, dw_ref) < 2e-3 and rel(dw, dw2) < 1e-2
+    acc = torch.zeros(2, cpad, device="cuda")
+    assert ops.dwconv_fprop_bnrelu(yprev, scale, shift, wt, y2, c, acc[0], acc[1], accumulate=True) == 1
+    torch.cuda.synchronize()
+    assert torch.equal(y, y2) and rel(acc[1], pq[:rows].sum(0)) < 1e-5
