@@ -383,8 +383,11 @@ TCO_LAYOUT = os.environ.get("B2C_TCO_LAYOUT", "1") != "0"
 ASYNC_WGRAD = os.environ.get("B2C_ASYNC_WGRAD", "1") != "0"
 # 1 = a stride-1 depthwise conv reads the RAW output of the 1x1 conv before it and applies that conv's BatchNorm + ReLU
 # while loading (b2c_dwconv_fprop_bnrelu / b2c_dwconv_wgrad_bnrelu): the expanded activation of a MobileNetV2 block —
-# its widest tensor — is never written or re-read; 0 = separate b2c_bn_act_apply pass
-DW_FUSED_INPUT = os.environ.get("B2C_DW_FUSED_INPUT", "1") != "0"
+# its widest tensor — is never written or re-read; 0 = separate b2c_bn_act_apply pass. Measured (batch 512,
+# profiles/r2o_dw_fused_input_ab.txt): 8.25 ms per step unfused, 10.10 ms fused — the strip kernels are bound by their
+# instruction issue, not by HBM, and the transform (fma + max + border select per loaded value, three loads per
+# output) doubles their instruction count, which costs more than the saved 4 B per element. Off by default.
+DW_FUSED_INPUT = os.environ.get("B2C_DW_FUSED_INPUT", "0") != "0"
 # CTA-pair (tcgen05.mma.cta_group::2) fprop / dgrad kernels: "halo" = where the halo kernel runs (3x3 stride 1 on
 # 32/16/8-pixel images), "all" = the per-tap kernel's shapes too, "0" = single-CTA kernels everywhere
 CTA_PAIR = os.environ.get("B2C_CTA_PAIR", "all")
