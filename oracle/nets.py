@@ -104,6 +104,63 @@ def train_step_grads(x, target, params, buffers, forward=resnet_forward, taps=No
 
 
 # ------------------------------------------------------------------------------------------------
+# MobileNet v1 (models/mobilenet.py) — same primitives as MobileNetV2
+# ------------------------------------------------------------------------------------------------
+MOBILENET_CFG = [64, (128, 2), 128, (256, 2), 256, (512, 2), 512, 512, 512, 512, 512, (1024, 2), 1024]    # mobilenet.py:27
+
+
+def _mobilenet_blocks():
+    cin, out = 32, []
+    for i, x in enumerate(MOBILENET_CFG):
+        cout, s = (x, 1) if isinstance(x, int) else x
+        out.append((f"layers.{i}", cin, cout, s))
+        cin = cout
+    return out
+
+
+def build_mobilenet_params(seed):
+    """Construction order of MobileNet.__init__ / Block.__init__ (mobilenet.py:13-18,31-34)."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride, groups=1):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, groups=groups, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+    conv("conv1", 3, 32, 3, 1); bn("bn1", 32)
+    for name, cin, cout, s in _mobilenet_blocks():
+        conv(name + ".conv1", cin, cin, 3, s, groups=cin); bn(name + ".bn1", cin)
+        conv(name + ".conv2", cin, cout, 1, 1); bn(name + ".bn2", cout)
+    lin = nn.Linear(1024, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def mobilenet_forward(x, params, buffers, training=True, taps=None):
+    out = F.conv2d(x, params["conv1.weight"], padding=1)
+    if taps is not None:
+        taps["conv1"] = out
+    out = F.relu(_bn(out, "bn1", params, buffers, training))                                           # mobilenet.py:48
+    for name, cin, cout, s in _mobilenet_blocks():
+        out = F.conv2d(out, params[name + ".conv1.weight"], stride=s, padding=1, groups=cin)
+        out = F.relu(_bn(out, name + ".bn1", params, buffers, training))                               # :21
+        out = F.conv2d(out, params[name + ".conv2.weight"])
+        if taps is not None:
+            taps[name + ".conv2"] = out
+        out = F.relu(_bn(out, name + ".bn2", params, buffers, training))                               # :22
+    out = F.avg_pool2d(out, 2).view(out.size(0), -1)                                                   # :50-51
+    return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
 # SimpleDLA (models/dla_simple.py) — the network main.py:71 constructs (SURVEY §8f N4, first row)
 # ------------------------------------------------------------------------------------------------
 def _dla_tree(name, cin, cout, level, stride):

@@ -10,7 +10,7 @@ plan of engine.py; every nn.Parameter / BN buffer becomes a view into the engine
 names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad` tensors handed to autograd
 are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
 Supported compositions: ResNet with BasicBlock or Bottleneck (models/resnet.py), VGG (models/vgg.py), PreActResNet with
-PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), SimpleDLA (models/dla_simple.py); anything else raises — there is no fallback path.
+PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), MobileNet (models/mobilenet.py), SimpleDLA (models/dla_simple.py); anything else raises — there is no fallback path.
 
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
 shadows class names across files and the reference tree may sit anywhere on sys.path.
@@ -21,7 +21,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .engine import (Engine, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, resnet_spec, simple_dla_spec,
+from .engine import (Engine, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, resnet_spec, simple_dla_spec,
                      vgg_spec, VGG_CFG)
 
 
@@ -56,6 +56,8 @@ def spec_from_module(net):
                 return vgg_spec(name, num_classes=net.classifier.out_features)
     if _is(net, "SimpleDLA") and hasattr(net, "layer6") and hasattr(net, "base") and _is(net.layer3, "Tree"):
         return simple_dla_spec(num_classes=net.linear.out_features)       # what main.py:71 constructs
+    if _is(net, "MobileNet") and hasattr(net, "layers") and len(net.layers) == 13 and hasattr(net, "bn1"):
+        return mobilenet_spec(num_classes=net.linear.out_features)
     if _is(net, "MobileNetV2") and hasattr(net, "layers") and hasattr(net, "conv2") and len(net.layers) == 17:
         return mobilenetv2_spec(num_classes=net.linear.out_features)
     raise NotImplementedError(f"accelerate: unsupported module {type(net).__module__}.{type(net).__name__}")

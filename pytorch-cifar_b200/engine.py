@@ -224,6 +224,39 @@ def simple_dla_spec(num_classes=10):
                 feat=512, cat2=cat2)
 
 
+MOBILENET_CFG = [64, (128, 2), 128, (256, 2), 256, (512, 2), 512, 512, 512, 512, 512, (1024, 2), 1024]   # models/mobilenet.py:27
+
+
+def mobilenet_spec(num_classes=10):
+    """MobileNet (v1) as models/mobilenet.py:11-52 composes it: conv3x3(3->32) + BN + ReLU, 13 blocks of depthwise 3x3
+    (stride 1 or 2) + BN + ReLU -> pointwise 1x1 + BN + ReLU, avg_pool2d(2), Linear(1024, 10)."""
+    params, buffers, blocks, depthwise = OrderedDict(), OrderedDict(), [], set()
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    params["conv1.weight"] = (32, 3, 3, 3)
+    bn("bn1", 32)
+    cin = 32
+    for i, x in enumerate(MOBILENET_CFG):
+        cout, s = (x, 1) if isinstance(x, int) else x
+        name = f"layers.{i}"
+        params[name + ".conv1.weight"] = (cin, 1, 3, 3)
+        depthwise.add(name + ".conv1.weight")
+        bn(name + ".bn1", cin)
+        params[name + ".conv2.weight"] = (cout, cin, 1, 1)
+        bn(name + ".bn2", cout)
+        blocks.append(dict(name=name, cin=cin, cout=cout, stride=s))
+        cin = cout
+    params["linear.weight"] = (num_classes, cin)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="mobilenet", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin,
+                depthwise=depthwise)
+
+
 def _pad64(c):
     return _align(c, 64)
 
@@ -650,7 +683,7 @@ class Engine:
         self._acts = []
         self._side, self._side_dirty = None, False
         f32 = dict(device=self.device, dtype=torch.float32)
-        stat_rows = ops.MAX_DW_STAT_ROWS if spec["family"] == "mobilenetv2" else ops.MAX_STAT_ROWS
+        stat_rows = ops.MAX_DW_STAT_ROWS if spec["family"] in ("mobilenetv2", "mobilenet") else ops.MAX_STAT_ROWS
         self.part_sum = torch.zeros(stat_rows, 2048, **f32)
         self.part_sq = torch.zeros(stat_rows, 2048, **f32)
         self.bwd_partial = torch.zeros(148 * 4 * 2 * 2048, **f32)
@@ -677,6 +710,8 @@ class Engine:
             self._build_bottleneck()
         elif spec["family"] == "dla":
             self._build_dla()
+        elif spec["family"] == "mobilenet":
+            self._build_mobilenet()
         else:
             raise NotImplementedError(spec["family"])
 
@@ -1453,6 +1488,64 @@ class Engine:
                     c1.dgrad(dy1, dx, add_src=dx)
                 else:
                     c1.dgrad(dy1, dx, add_src=(dout if identity else None))
+            Bk.append(bwd)
+            dout = dx
+        dy0 = self.new_act(*stem.y.shape)
+
+        def bwd_stem(dout=dout):
+            stem.bn_backward(self, dout, a0, dout, dy0, relu_from_y=True)
+            stem.wgrad(dy0)
+        Bk.append(bwd_stem)
+        self.bwd_ops = Bk
+
+    # ------------------------------------------------------------------ MobileNet (v1) plan
+    def _build_mobilenet(self):
+        """models/mobilenet.py:20-23,47-52: per block relu(bn1(depthwise 3x3, stride)) -> relu(bn2(pointwise 1x1));
+        stem conv3x3 + BN + ReLU; avg_pool2d(2) over the final 2x2 map; Linear(1024, 10)."""
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        stem = ConvUnit(self, "conv1", "bn1", self.x0, 3, 32, 3, 1, 32, 32, stem=True)
+        a0 = self.new_act(N, 32, 32, stem.cout)
+        self.units = [stem]
+        F, blocks = self.fwd_ops, []
+        F.append(lambda training: (stem.fprop(self, True), stem.bn_apply(self, training, a0)))
+        x, H, W = a0, 32, 32
+        for b in spec["blocks"]:
+            name, cin, cout, s = b["name"], b["cin"], b["cout"], b["stride"]
+            dw = DwUnit(self, name + ".conv1", name + ".bn1", x, cin, s, H, W)
+            Ho, Wo = H // s, W // s
+            a1 = self.new_act(N, Ho, Wo, dw.cout)
+            c2 = ConvUnit(self, name + ".conv2", name + ".bn2", a1, cin, cout, 1, 1, Ho, Wo)
+            a2 = self.new_act(N, Ho, Wo, c2.cout)
+            self.units += [dw, c2]
+            blocks.append((dw, a1, c2, a2, x))
+
+            def fwd(training, dw=dw, a1=a1, c2=c2, a2=a2):
+                dw.fprop(self)
+                dw.bn_apply(self, training, a1)
+                c2.fprop(self)
+                c2.bn_apply(self, training, a2)
+            F.append(fwd)
+            x, H, W = a2, Ho, Wo
+        fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        for (dw, a1, c2, a2, xin) in reversed(blocks):
+            dy2 = self.new_act(*c2.y.shape)
+            da1 = self.new_act(*a1.shape)
+            dy1 = self.new_act(*dw.y.shape)
+            dx = self.new_act(*xin.shape)
+
+            def bwd(dw=dw, a1=a1, c2=c2, a2=a2, dout=dout, dy2=dy2, da1=da1, dy1=dy1, dx=dx):
+                c2.bn_backward(self, dout, a2, dout, dy2, relu_from_y=True)
+                c2.wgrad(dy2)
+                if FUSE_DGRAD_BN:       # a1 = relu(bn1(depthwise out)): mask + sums from the pointwise dgrad's epilogue
+                    dw.bn_backward_from_partial(self, da1, dy1, c2.dgrad_bn(self, dy2, da1, dw))
+                else:
+                    c2.dgrad(dy2, da1)
+                    dw.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
+                dw.wgrad(dy1)
+                dw.dgrad(dy1, dx)
             Bk.append(bwd)
             dout = dx
         dy0 = self.new_act(*stem.y.shape)

@@ -65,9 +65,10 @@ def golden_other_nets():
     out = dict(x=x.numpy(), target=target.numpy())
     import models.mobilenetv2 as ref_mb
     import models.dla_simple as ref_dla
+    import models.mobilenet as ref_mb1
     for tag, ctor in (("vgg16", lambda: ref_vgg.VGG("VGG16")), ("preact18", ref_pre.PreActResNet18),
                       ("mobilenetv2", ref_mb.MobileNetV2), ("resnet50", __import__("models.resnet", fromlist=["x"]).ResNet50),
-                      ("simpledla", ref_dla.SimpleDLA)):
+                      ("simpledla", ref_dla.SimpleDLA), ("mobilenet", ref_mb1.MobileNet)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

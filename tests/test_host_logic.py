@@ -170,3 +170,34 @@ def test_bench_algorithmic_bytes():
     per_img = bench.algorithmic_bytes_per_image(engine.mobilenetv2_spec(), engine)
     assert abs(per_img * 128 / 3 / 1e6 - 880) < 5
     assert abs(bench.algorithmic_bytes_per_image(engine.resnet_spec(), engine) * 128 / 3 / 1e6 - 327.9) < 1
+
+
+def test_spec_from_the_references_own_modules():
+    """accelerate.spec_from_module on modules built by the reference's OWN model files (the tree itself, or the copy
+    staged under oracle/_ref): the derived spec lists exactly the module's parameters, names, order and shapes, for
+    every supported constructor; an unsupported one raises instead of falling back."""
+    import importlib
+    import sys
+    import pytest
+    from b200cifar.accelerate import spec_from_module
+    from oracle.stage_reference import reference_dir
+    ref = reference_dir()
+    if ref is None:
+        pytest.skip("reference files neither present nor staged")
+    if ref not in sys.path:
+        sys.path.insert(0, ref)
+    cases = [("resnet", n, ()) for n in ("ResNet18", "ResNet34", "ResNet50", "ResNet101", "ResNet152")] + \
+            [("vgg", "VGG", (v,)) for v in ("VGG11", "VGG13", "VGG16", "VGG19")] + \
+            [("preact_resnet", "PreActResNet18", ()), ("preact_resnet", "PreActResNet34", ()),
+             ("mobilenetv2", "MobileNetV2", ()), ("mobilenet", "MobileNet", ()), ("dla_simple", "SimpleDLA", ())]
+    for mod, ctor, args in cases:
+        net = getattr(importlib.import_module("models." + mod), ctor)(*args)
+        spec = spec_from_module(net)
+        want = [(n, tuple(p.shape)) for n, p in net.named_parameters()]
+        got = [(n, tuple(s)) for n, s in spec["params"].items()]
+        assert got == want, (mod, ctor)
+        bufs = {n for n, _ in net.named_buffers() if not n.endswith("num_batches_tracked")}
+        assert set(spec["buffers"]) == bufs, (mod, ctor)
+    for mod, ctor in (("googlenet", "GoogLeNet"), ("densenet", "DenseNet121"), ("lenet", "LeNet")):
+        with pytest.raises(NotImplementedError):
+            spec_from_module(getattr(importlib.import_module("models." + mod), ctor)())

@@ -166,6 +166,7 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           "mobilenetv2": dict(logits=0.25, near=0.15, near_cos=0.99, min_cos=None, drop=0.92, lr=0.02),
           "resnet50": dict(logits=0.3, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
           # SimpleDLA: 33 convs deep; measured 8.2 % on the logits (profiles/r2_parity/parity_simpledla.json)
+          "mobilenet": dict(logits=0.25, near=0.15, near_cos=0.99, min_cos=None, drop=0.95, lr=0.02),
           "simpledla": dict(logits=0.12, near=0.12, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02)}
 
 MODELS = {
@@ -177,6 +178,8 @@ MODELS = {
                     ["linear.weight", "bn2.weight", "bn2.bias"]),
     "resnet50": ("resnet50_spec", "build_bottleneck_params", "bottleneck_forward", "conv1",
                  ["linear.weight", "layer4.2.bn3.weight", "layer4.2.bn3.bias"]),
+    "mobilenet": ("mobilenet_spec", "build_mobilenet_params", "mobilenet_forward", "conv1",
+                  ["linear.weight", "layers.12.bn2.weight", "layers.12.bn2.bias"]),
     # SimpleDLA, what main.py:71 constructs (models/dla_simple.py): aggregation trees, Root = 1x1 conv over a concat
     "simpledla": ("simple_dla_spec", "build_simpledla_params", "simpledla_forward", "base.0",
                   ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
