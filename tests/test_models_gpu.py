@@ -166,7 +166,10 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           "mobilenetv2": dict(logits=0.25, near=0.15, near_cos=0.99, min_cos=None, drop=0.92, lr=0.02),
           "resnet50": dict(logits=0.3, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
           # SimpleDLA: 33 convs deep; measured 8.2 % on the logits (profiles/r2_parity/parity_simpledla.json)
-          "mobilenet": dict(logits=0.25, near=0.15, near_cos=0.99, min_cos=None, drop=0.95, lr=0.02),
+          # MobileNet v1: 27 layers without a residual path; at random init the per-layer bf16 noise grows ~1.35x per block
+          # (0.3 % after the stem -> 28 % on the logits, profiles/r2_parity/parity_mobilenet.json); stock bf16 autocast
+          # shows the same median gradient error (1.04 vs our 1.02)
+          "mobilenet": dict(logits=0.45, near=0.3, near_cos=0.95, min_cos=None, drop=0.95, lr=0.02),
           "simpledla": dict(logits=0.12, near=0.12, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02)}
 
 MODELS = {
