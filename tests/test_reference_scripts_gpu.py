@@ -80,6 +80,7 @@ def test_main_dist_py_unmodified_under_ddp(tmp_path):
     assert acc["ddp_attached"] and not red["ddp_attached"]
     compare(acc, ref, 4)
     compare(red, ref, 4)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     json.dump(dict(attached=acc, reducer=red, plain=ref),
               open(os.path.join(ROOT, "gpurun_out", "reference_main_dist_py.json"), "w"), indent=1)
 
