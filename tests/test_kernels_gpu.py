@@ -965,3 +965,91 @@ def test_stride2_dgrad_on_cta_pairs(ops, shape):
     assert torch.isfinite(outs[1].float()).all() and rel_err(outs[1].float(), outs[0].float()) < 1e-3
     ref = torch.nn.grad.conv2d_input((n, cin, h, w), weight(cout, cin, k, 112), to_nchw(dy), stride=2, padding=k // 2)
     assert rel_err(to_nchw(outs[1]), ref) < BF16_TOL
+
+
+def _guarded(shape, dtype, fill):
+    """A tensor of `shape` carved out of the middle of a larger sentinel-filled allocation (256-byte aligned), so that a
+    kernel writing outside its output is caught without a memory checker."""
+    n = 1
+    for s in shape:
+        n *= s
+    esz = torch.tensor([], dtype=dtype).element_size()
+    pad = 4096 // esz
+    whole = torch.full((n + 2 * pad,), fill, device="cuda", dtype=dtype)
+    return whole, whole[pad:pad + n].view(shape), pad
+
+
+def _guards_intact(whole, pad, fill):
+    return bool((whole[:pad] == fill).all() and (whole[-pad:] == fill).all())
+
+
+def test_round2_kernels_write_only_their_outputs(ops):
+    """Guard bands around the outputs of the kernels added or changed in round 2 (ragged sizes on purpose): the
+    CTA-pair stride-2 data gradients, the prefetching epilogue of the 64-wide halo kernel, the two-map 1x1 conv, the
+    weight re-layout and the BatchNorm apply with fused finalize."""
+    S = 777.0
+    # stride-2 dgrad phases + fused shortcut on CTA pairs, odd tile count
+    n, h, cin, cout = 5, 16, 64, 128
+    dy, dys = nhwc_bf16(n, h // 2, h // 2, cout, 121), nhwc_bf16(n, h // 2, h // 2, cout, 122)
+    w3, w1 = weight(cout, cin, 3, 123), weight(cout, cin, 1, 124)
+    w10 = torch.cat([ops.pack_weight_dgrad(w3), ops.pack_weight_dgrad(w1)], 0).contiguous()
+    whole, dx, pad = _guarded((n, h, h, cin), torch.bfloat16, S)
+    ops.conv_dgrad_with_shortcut(ops.conv_desc(n, h, h, cin, cout, 3, 2, flags=128), dy, dys, w10, dx)
+    torch.cuda.synchronize()
+    assert _guards_intact(whole, pad, S) and torch.isfinite(dx.float()).all() and (dx != S).float().mean() > 0.99
+    # 64-wide halo kernel, dgrad with a residual (epilogue operand requested a tile ahead), odd tile count
+    n, h = 3, 32
+    dy64 = nhwc_bf16(n, h, h, 64, 125)
+    add = nhwc_bf16(n, h, h, 64, 126)
+    wd = ops.pack_weight_dgrad(weight(64, 64, 3, 127))
+    whole, dx, pad = _guarded((n, h, h, 64), torch.bfloat16, S)
+    ops.conv_dgrad(ops.conv_desc(n, h, h, 64, 64, 3, 1, flags=128), dy64, wd, dx, add)
+    torch.cuda.synchronize()
+    ref = torch.nn.grad.conv2d_input((n, 64, h, h), weight(64, 64, 3, 127), to_nchw(dy64), padding=1) + to_nchw(add)
+    assert _guards_intact(whole, pad, S) and rel_err(to_nchw(dx), ref) < BF16_TOL
+    # two-map 1x1 conv
+    n, h, c, co = 5, 4, 128, 128
+    x0, x1 = nhwc_bf16(n, h, h, c, 128), nhwc_bf16(n, h, h, c, 129)
+    w2 = (torch.randn(2, co, c, device="cuda") * 0.05).to(torch.bfloat16)
+    whole, y, pad = _guarded((n, h, h, co), torch.bfloat16, S)
+    ops.conv1x1_cat_fprop(ops.conv_desc(n, h, h, c, co, 1, 1), x0, x1, w2, y)
+    torch.cuda.synchronize()
+    assert _guards_intact(whole, pad, S) and torch.isfinite(y.float()).all()
+    # weight re-layout: both operand arenas
+    g = torch.Generator(device="cuda").manual_seed(130)
+    shapes = [(96, 24, 1), (64, 64, 3), (40, 36, 3)]
+    entries, masters, offs, wf_n, wd_n = [], [], 0, 0, 0
+    for co_, ci_, k in shapes:
+        w = torch.randn(co_, ci_, k, k, device="cuda", generator=g)
+        masters.append(w)
+        cip, cop = (ci_ + 63) // 64 * 64, (co_ + 63) // 64 * 64
+        entries.append(dict(src_off=offs, wf_off=wf_n, wd_off=wd_n, cout=co_, cin=ci_, taps=k * k, cin_pad=cip, cout_pad=cop,
+                            kflat=2))
+        offs += w.numel(); wf_n += cop * cip * k * k; wd_n += cop * cip * k * k
+    master = torch.cat([w.permute(2, 3, 1, 0).reshape(-1) for w in masters]).contiguous()
+    whole_f, wf, pad_f = _guarded((wf_n,), torch.bfloat16, S)
+    whole_d, wdd, pad_d = _guarded((wd_n,), torch.bfloat16, S)
+    wf.zero_(); wdd.zero_()
+    ops.repack_weights(master, wf, wdd, ops.make_repack_table(entries, "cuda"), len(entries))
+    torch.cuda.synchronize()
+    assert _guards_intact(whole_f, pad_f, S) and _guards_intact(whole_d, pad_d, S)
+    for e, w in zip(entries, masters):
+        kk, cop, cip = e["taps"], e["cout_pad"], e["cin_pad"]
+        f = wf[e["wf_off"]:e["wf_off"] + kk * cop * cip].view(kk, cop, cip)
+        d = wdd[e["wd_off"]:e["wd_off"] + kk * cop * cip].view(kk, cip, cop)
+        assert torch.equal(f[:, :e["cout"], :e["cin"]], ops.pack_weight_fprop(w))
+        assert torch.equal(d[:, :e["cin"], :e["cout"]], ops.pack_weight_dgrad(w))
+    # BatchNorm apply with fused finalize, channel count that needs a rounded grid, rows not a multiple of anything
+    C, rows = 192, 1001
+    yv = (torch.randn(rows, C, device="cuda", generator=g) * 2).to(torch.bfloat16)
+    o = {k: torch.empty(C, device="cuda") for k in ("scale", "shift", "mean", "rstd")}
+    rec = ops.bn_stats(yv.float().sum(0).contiguous(), (yv.float() ** 2).sum(0).contiguous(),
+                       torch.ones(C, device="cuda"), torch.zeros(C, device="cuda"), rows, 1e-5, 0.1, None, None,
+                       o["scale"], o["shift"], o["mean"], o["rstd"])
+    whole, out, pad = _guarded((rows, C), torch.bfloat16, S)
+    ops.bn_act_apply_stats(yv, rec, out, rows, C, relu=True)
+    whole2, out2, pad2 = _guarded((rows, C), torch.bfloat16, S)
+    ops.bn_act_apply(yv, o["scale"], o["shift"], out2, rows, C, relu=True)
+    torch.cuda.synchronize()
+    assert _guards_intact(whole, pad, S) and _guards_intact(whole2, pad2, S) and torch.equal(out, out2)
+    assert rel_err(out.float(), F.relu(F.batch_norm(yv.float(), None, None, training=True))) < BF16_TOL
