@@ -243,3 +243,34 @@ def test_the_references_own_classes(family):
     xe, _ = batch(100, 32)
     with torch.no_grad():
         assert rel(net(xe), plain(xe)) < (0.25 if family.startswith("mobilenet") else 8e-2)
+
+
+def test_graph_replayed_drop_in_matches_eager():
+    """accelerate(net, graphs=True): forward and backward replayed as CUDA graphs from the third step on; same losses
+    and parameters as the eager launch sequence, across train / eval switches and a second batch size."""
+    import b200cifar
+    from b200cifar.accelerate import accelerate
+    a = accelerate(make("resnet18"))
+    b = accelerate(make("resnet18"), graphs=True)
+    crit = nn.CrossEntropyLoss()
+    oa = torch.optim.SGD(a.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
+    ob = torch.optim.SGD(b.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
+    (x, t), (x2, t2), (xe, _) = batch(128, 41), batch(64, 42), batch(100, 43)
+    for step in range(6):
+        xs, ts = (x2, t2) if step in (2, 5) else (x, t)             # a second batch size in between
+        la, lb = [], []
+        for net, opt, ls in ((a, oa, la), (b, ob, lb)):
+            net.train()
+            opt.zero_grad()
+            loss = crit(net(xs), ts)
+            loss.backward()
+            opt.step()
+            ls.append(loss.item())
+        assert abs(la[0] - lb[0]) < 2e-2, (step, la, lb)
+        if step in (1, 4):
+            a.eval(); b.eval()
+            with torch.no_grad():
+                assert rel(b(xe), a(xe)) < 5e-2
+    assert len(b._b2c_state._graphs) >= 4                      # fwd/bwd at two batch sizes (+ the eval forward)
+    for (n1, p1), (_, p2) in zip(a.named_parameters(), b.named_parameters()):
+        assert rel(p2, p1) < 2e-2, n1

@@ -60,6 +60,11 @@ for N in (128, 1024):
     n4 = accelerate(copy.deepcopy(base))
     row["accelerate_fused_sgd"] = rate(n4, FusedSGD(n4, lr=0.01, momentum=0.9, weight_decay=5e-4), N)
     row["accelerate_fused_sgd_no_item"] = rate(n4, FusedSGD(n4, lr=0.01, momentum=0.9, weight_decay=5e-4), N, item=False)
+    n5 = accelerate(copy.deepcopy(base), graphs=True)
+    row["accelerate_graphs_torch_sgd"] = rate(n5, torch.optim.SGD(n5.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4), N)
+    n6 = accelerate(copy.deepcopy(base), graphs=True)
+    row["accelerate_graphs_fused_sgd"] = rate(n6, FusedSGD(n6, lr=0.01, momentum=0.9, weight_decay=5e-4), N)
+    del n5, n6
     print(json.dumps(row), flush=True)
     out["rows"].append(row)
     del n1, n2, n3, n4
