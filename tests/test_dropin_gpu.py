@@ -272,5 +272,7 @@ def test_graph_replayed_drop_in_matches_eager():
             with torch.no_grad():
                 assert rel(b(xe), a(xe)) < 5e-2
     assert len(b._b2c_state._graphs) >= 4                      # fwd/bwd at two batch sizes (+ the eval forward)
-    for (n1, p1), (_, p2) in zip(a.named_parameters(), b.named_parameters()):
-        assert rel(p2, p1) < 2e-2, n1
+    # (two runs drift apart by the weight-gradient atomics' round-off; BatchNorm biases start at zero, so they are
+    # compared as part of the whole parameter vector, not tensor by tensor)
+    flat = lambda net: torch.cat([p.detach().reshape(-1) for p in net.parameters()])
+    assert rel(flat(b), flat(a)) < 1e-2
