@@ -8,7 +8,7 @@ follow the seed) the same run — the reference's optimiser settings, cosine sch
 (torch ops, oracle/nets.py, TF32 off) and once through the B200 path (Trainer, CUDA graph, ragged last batch kept).
 Compared: the mean top-1 over the last half of the epochs, averaged over the seeds. A single run of EITHER
 implementation moves by more than 0.5 pt from seed to seed, so the bound is 0.5 pt plus two standard errors of the
-difference of the two three-seed means; the per-seed spreads are reported next to it
+difference of the two three-seed means (floored at 0.25 pt each); the per-seed spreads are reported next to it
 (gpurun_out/top1_curve_hard_task.json)."""
 import json
 import os
@@ -119,7 +119,8 @@ def test_top1_curve_matches_fp32_oracle_on_a_task_that_does_not_saturate():
     json.dump(report, open("gpurun_out/top1_curve_hard_task.json", "w"), indent=1)
     final = float(ref[:, -1].mean())
     assert 0.55 < final < 0.97, ("the task must neither be unlearnable nor saturate", ref.tolist())
-    assert abs(diff) <= 0.005 + 2 * se, report
+    # (se is itself estimated from three seeds; it is floored at 0.25 pt, what the 4000-sample evaluations alone give)
+    assert abs(diff) <= 0.005 + 2 * max(se, 0.0025), report
     # the training loss, a smoother witness than eval accuracy: per-epoch means of the seed-averaged runs stay close
     ol, rl = np.mean(ours_loss, 0), np.mean(ref_loss, 0)
     assert np.all(np.abs(ol - rl) <= 0.05 * rl + 0.02), (ol.tolist(), rl.tolist())

@@ -253,8 +253,8 @@ def test_graph_replayed_drop_in_matches_eager():
     a = accelerate(make("resnet18"))
     b = accelerate(make("resnet18"), graphs=True)
     crit = nn.CrossEntropyLoss()
-    oa = torch.optim.SGD(a.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
-    ob = torch.optim.SGD(b.parameters(), lr=0.01, momentum=0.9, weight_decay=5e-4)
+    oa = torch.optim.SGD(a.parameters(), lr=0.005, momentum=0.9, weight_decay=5e-4)
+    ob = torch.optim.SGD(b.parameters(), lr=0.005, momentum=0.9, weight_decay=5e-4)
     (x, t), (x2, t2), (xe, _) = batch(128, 41), batch(64, 42), batch(100, 43)
     for step in range(6):
         xs, ts = (x2, t2) if step in (2, 5) else (x, t)             # a second batch size in between
