@@ -300,6 +300,22 @@ B2C_API int b2c_augment_im2col(const uint8_t* data, const long long* idx, const 
 /* fp32 NCHW network input (what the reference DataLoader yields, main.py:99) -> stem GEMM operand. */
 B2C_API int b2c_stem_im2col(const float* x_nchw_f32, void* out_im2col_bf16, int n, void* stream);
 
+/* The same two producers for a 1x1 stem conv (nn.Conv2d(3, 64, kernel_size=1), models/resnext.py:47): the operand is
+ * the image itself, [n,32,32,64] bf16 with channel c < 3 = the pixel and zeros above. */
+B2C_API int b2c_augment_nhwc64(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out_nhwc64_bf16, int n,
+                       const float* mean_host, const float* std_host, void* stream);
+B2C_API int b2c_stem_nhwc64(const float* x_nchw_f32, void* out_nhwc64_bf16, int n, void* stream);
+
+/* Weight gradient of a grouped conv — nn.Conv2d(C, C, 3, groups=g), models/resnext.py:19 — out of the dense one.
+ * A grouped conv runs here as a dense conv over block-diagonal bf16 operands (b2c_repack_weights with one table entry
+ * per group: the entry's operand offsets select the group's diagonal block, its cin_pad / cout_pad are the dense
+ * pitches; everything off the diagonal stays zero), so b2c_conv_wgrad (flags bit 5) yields a dense
+ * dense_tco[tap][cin][cout] fp32 matrix. This adds its diagonal blocks to the parameter's gradient in the reference's
+ * layout: dw_oihw[o][ci][tap] += dense_tco[tap][(o / (cout/g)) * (cin/g) + ci][o]  (autograd of
+ * aten::convolution with groups, main.py:104). The caller zero-fills dense_tco before the wgrad launch. */
+B2C_API int b2c_grouped_wgrad_extract(const float* dense_tco, float* dw_oihw, int cout, int cin, int taps, int groups,
+                              void* stream);
+
 /* optim.SGD(...).step(), main.py:87-88,105, over one flat fp32 arena (n % 4 == 0, 16-byte aligned).
  * hyper is a DEVICE array {lr, momentum, weight_decay, grad_scale, first_step(0/1)}. */
 B2C_API int b2c_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, const float* hyper,

@@ -524,3 +524,92 @@ def bottleneck_forward(x, params, buffers, training=True, num_blocks=RESNET50_BL
         out = F.relu(o + sc)                                                                          # :90-91
     out = F.avg_pool2d(out, 4).view(out.size(0), -1)
     return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
+# ResNeXt-29 (models/resnext.py:10-86): grouped 3x3 convs, 1x1 stem, three stages, avg_pool2d(8)
+# ------------------------------------------------------------------------------------------------
+RESNEXT29_BLOCKS = (3, 3, 3)
+
+
+def _resnext_blocks(num_blocks, cardinality, bottleneck_width):
+    cin, bw = 64, bottleneck_width
+    for li, nb in enumerate(num_blocks):                      # resnext.py:57-66: the width doubles after each stage
+        for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+            gw = cardinality * bw
+            yield f"layer{li + 1}.{bi}", cin, gw, 2 * gw, s
+            cin = 2 * gw
+        bw *= 2
+
+
+def build_resnext_params(seed, cardinality=2, bottleneck_width=64, num_blocks=RESNEXT29_BLOCKS):
+    """Seeded parameters equal to `torch.manual_seed(seed); models.resnext.ResNeXt(num_blocks, cardinality,
+    bottleneck_width)` (resnext.py:14-28,42-54): layers are constructed in the reference's order."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride, groups=1):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, groups=groups, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 64, 1, 1)                                # resnext.py:47: kernel_size=1
+    bn("bn1", 64)
+    cin_final = 64
+    for name, cin, gw, cout, s in _resnext_blocks(num_blocks, cardinality, bottleneck_width):
+        conv(name + ".conv1", cin, gw, 1, 1)                  # :17
+        bn(name + ".bn1", gw)
+        conv(name + ".conv2", gw, gw, 3, s, groups=cardinality)   # :19
+        bn(name + ".bn2", gw)
+        conv(name + ".conv3", gw, cout, 1, 1)                 # :21
+        bn(name + ".bn3", cout)
+        if s != 1 or cin != cout:                             # :24-29
+            conv(name + ".shortcut.0", cin, cout, 1, s)
+            bn(name + ".shortcut.1", cout)
+        cin_final = cout
+    lin = nn.Linear(cin_final, 10)                            # :54: cardinality * bottleneck_width * 8
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def resnext_forward(x, params, buffers, training=True, cardinality=2, bottleneck_width=64,
+                    num_blocks=RESNEXT29_BLOCKS, taps=None):
+    out = F.conv2d(x, params["conv1.weight"])                 # resnext.py:69
+    if taps is not None:
+        taps["conv1"] = out
+    out = F.relu(_bn(out, "bn1", params, buffers, training))
+    for name, cin, gw, cout, s in _resnext_blocks(num_blocks, cardinality, bottleneck_width):
+        xin = out
+        o = F.conv2d(xin, params[name + ".conv1.weight"])
+        if taps is not None:
+            taps[name + ".conv1"] = o
+        o = F.relu(_bn(o, name + ".bn1", params, buffers, training))                                      # :32
+        o = F.conv2d(o, params[name + ".conv2.weight"], stride=s, padding=1, groups=cardinality)
+        if taps is not None:
+            taps[name + ".conv2"] = o
+        o = F.relu(_bn(o, name + ".bn2", params, buffers, training))                                      # :33
+        o = _bn(F.conv2d(o, params[name + ".conv3.weight"]), name + ".bn3", params, buffers, training)   # :34
+        if (name + ".shortcut.0.weight") in params:
+            sc = _bn(F.conv2d(xin, params[name + ".shortcut.0.weight"], stride=s), name + ".shortcut.1", params, buffers,
+                     training)
+        else:
+            sc = xin
+        out = F.relu(o + sc)                                                                              # :35-36
+    out = F.avg_pool2d(out, 8).view(out.size(0), -1)          # :74-75
+    return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+def resnext_32x4d_forward(x, params, buffers, training=True, taps=None):
+    return resnext_forward(x, params, buffers, training, cardinality=32, bottleneck_width=4, taps=taps)
+
+
+def build_resnext_32x4d_params(seed):
+    return build_resnext_params(seed, cardinality=32, bottleneck_width=4)

@@ -98,6 +98,9 @@ SIGNATURES = {
     "b2c_augment_nchw": [_P, _P, _P, _P, _I, ctypes.POINTER(_F), ctypes.POINTER(_F), _P],
     "b2c_augment_im2col": [_P, _P, _P, _P, _I, ctypes.POINTER(_F), ctypes.POINTER(_F), _P],
     "b2c_stem_im2col": [_P, _P, _I, _P],
+    "b2c_augment_nhwc64": [_P, _P, _P, _P, _I, ctypes.POINTER(_F), ctypes.POINTER(_F), _P],
+    "b2c_stem_nhwc64": [_P, _P, _I, _P],
+    "b2c_grouped_wgrad_extract": [_P, _P, _I, _I, _I, _I, _P],
     "b2c_sgd_step": [_P, _P, _P, _LL, _P, _P],
     "b2c_repack_weights": [_P, _P, _P, _P, _I, _P],
 }

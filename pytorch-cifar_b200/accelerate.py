@@ -10,7 +10,8 @@ plan of engine.py; every nn.Parameter / BN buffer becomes a view into the engine
 names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad` tensors handed to autograd
 are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
 Supported compositions: ResNet with BasicBlock or Bottleneck (models/resnet.py), VGG (models/vgg.py), PreActResNet with
-PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), MobileNet (models/mobilenet.py), SimpleDLA (models/dla_simple.py); anything else raises — there is no fallback path.
+PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), MobileNet (models/mobilenet.py), SimpleDLA (models/dla_simple.py), ResNeXt
+(models/resnext.py, grouped convs); anything else raises — there is no fallback path.
 
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
 shadows class names across files and the reference tree may sit anywhere on sys.path.
@@ -21,8 +22,8 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .engine import (Engine, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, resnet_spec, simple_dla_spec,
-                     vgg_spec, VGG_CFG)
+from .engine import (Engine, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, resnet_spec, resnext_spec,
+                     simple_dla_spec, vgg_spec, VGG_CFG)
 
 
 def _is(m, name):
@@ -39,6 +40,11 @@ def spec_from_module(net):
         if kinds == {"Bottleneck"}:                       # ResNet-50/101/152: what main_dist.py:136 hard-codes
             return resnet_spec(tuple(blocks), num_classes=net.linear.out_features, bottleneck=True)
         raise NotImplementedError(f"accelerate: unsupported ResNet block types {sorted(kinds)}")
+    if _is(net, "ResNeXt") and hasattr(net, "layer3") and not hasattr(net, "layer4") and hasattr(net, "cardinality"):
+        blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 4)]       # models/resnext.py:48-52: three stages
+        conv2 = net.layer1[0].conv2
+        return resnext_spec(tuple(blocks), cardinality=conv2.groups, bottleneck_width=conv2.out_channels // conv2.groups,
+                            num_classes=net.linear.out_features)
     if _is(net, "PreActResNet") and hasattr(net, "layer4"):
         blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
         if not all(_is(b, "PreActBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):
@@ -75,7 +81,7 @@ class _PlanFn(torch.autograd.Function):
 
         def launch(xin):
             eng.repack()                                 # parameters may have changed (optimizer, load_state_dict)
-            ops.stem_im2col(xin, eng.x0)
+            ops.stem_im2col(xin, eng.x0, taps=eng.stem_taps)
             eng.forward(training=training)
         if state.use_graphs:
             xin = state.static_input(eng)

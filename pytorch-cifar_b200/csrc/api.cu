@@ -912,6 +912,29 @@ int b2c_stem_im2col(const float* x_nchw_f32, void* out_im2col_bf16, int n, void*
     return cuda_rc(b2c::launch_stem_im2col(x_nchw_f32, out_im2col_bf16, n, as_stream(stream)));
 }
 
+int b2c_augment_nhwc64(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out_nhwc64_bf16, int n,
+                       const float* mean_host, const float* std_host, void* stream) {
+    if (n == 0) return 0;
+    if (!data || !idx || !ijf || !out_nhwc64_bf16 || !mean_host || !std_host || n < 0 || !aligned16(data) ||
+        !aligned16(out_nhwc64_bf16))
+        return B2C_ERR_ARG;
+    return cuda_rc(
+        b2c::launch_augment_im2col(data, idx, ijf, out_nhwc64_bf16, n, mean_host, std_host, as_stream(stream), 1));
+}
+
+int b2c_stem_nhwc64(const float* x_nchw_f32, void* out_nhwc64_bf16, int n, void* stream) {
+    if (n == 0) return 0;
+    if (!x_nchw_f32 || !out_nhwc64_bf16 || n < 0 || !aligned16(out_nhwc64_bf16)) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_stem_im2col(x_nchw_f32, out_nhwc64_bf16, n, as_stream(stream), 1));
+}
+
+int b2c_grouped_wgrad_extract(const float* dense_tco, float* dw_oihw, int cout, int cin, int taps, int groups,
+                              void* stream) {
+    if (!dense_tco || !dw_oihw || cout <= 0 || cin <= 0 || taps <= 0 || groups <= 0) return B2C_ERR_ARG;
+    if (cout % groups || cin % groups) return B2C_ERR_ARG;
+    return cuda_rc(b2c::launch_grouped_wgrad_extract(dense_tco, dw_oihw, cout, cin, taps, groups, as_stream(stream)));
+}
+
 int b2c_sgd_step(float* param, const float* grad, float* momentum_buf, long long n, const float* hyper,
                  void* stream) {
     if (!param || !grad || !momentum_buf || !hyper || n < 0 || (n & 3) || !aligned16(param) || !aligned16(grad) ||

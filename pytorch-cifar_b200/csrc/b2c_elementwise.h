@@ -71,9 +71,12 @@ cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const flo
                             void* dact, float* dW, float* db, cudaStream_t s);
 cudaError_t launch_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out, int N,
                                 const float* mean, const float* stdv, cudaStream_t s);
+// taps: 9 = im2col operand of a 3x3 stem (k = tap*3 + c), 1 = operand of a 1x1 stem (k = c)
 cudaError_t launch_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out, int N,
-                                  const float* mean, const float* stdv, cudaStream_t s);
-cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s);
+                                  const float* mean, const float* stdv, cudaStream_t s, int taps = 9);
+cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s, int taps = 9);
+cudaError_t launch_grouped_wgrad_extract(const float* dense, float* dw, int cout, int cin, int taps, int groups,
+                                         cudaStream_t s);
 cudaError_t launch_sgd(float* p, const float* g, float* buf, long long n, const float* hyper, cudaStream_t s);
 cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackEntry* table_dev, int entries,
                           cudaStream_t s);

@@ -793,6 +793,17 @@ augment_nchw_kernel(const uint8_t* __restrict__ data, const long long* __restric
 
 // Fused fast path: augmented image written directly as the stem conv's im2col operand,
 // [N,32,32,64] bf16 with k = (r*3+s)*3 + c for k < 27 and zeros above (conv zero padding applied).
+// kTaps = 1: the operand of a 1x1 stem conv (models/resnext.py:47), k = c for k < 3.
+template <int kTaps>
+__device__ __forceinline__ __nv_bfloat16 stem_operand_value(const __nv_bfloat16* saug, int y, int x, int kk) {
+    if (kTaps == 1) return kk < 3 ? saug[((y + 1) * 34 + (x + 1)) * 3 + kk] : __float2bfloat16(0.f);
+    if (kk >= 27) return __float2bfloat16(0.f);
+    const int tap = kk / 3, c = kk - tap * 3;
+    const int r = tap / 3, s = tap - r * 3;
+    return saug[((y + r) * 34 + (x + s)) * 3 + c];
+}
+
+template <int kTaps>
 __global__ void __launch_bounds__(256)
 augment_im2col_kernel(const uint8_t* __restrict__ data, const long long* __restrict__ idx,
                       const int8_t* __restrict__ ijf, uint4* __restrict__ out, AugConst k) {
@@ -819,21 +830,13 @@ augment_im2col_kernel(const uint8_t* __restrict__ data, const long long* __restr
         const int y = pix >> 5, x = pix & 31;
         __nv_bfloat16 h[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int kk = vec * 8 + q;
-            __nv_bfloat16 v = __float2bfloat16(0.f);
-            if (kk < 27) {
-                const int tap = kk / 3, c = kk - tap * 3;
-                const int r = tap / 3, s = tap - r * 3;
-                v = saug[((y + r) * 34 + (x + s)) * 3 + c];
-            }
-            h[q] = v;
-        }
+        for (int q = 0; q < 8; ++q) h[q] = stem_operand_value<kTaps>(saug, y, x, vec * 8 + q);
         o[e] = *reinterpret_cast<uint4*>(h);
     }
 }
 
 // Drop-in path: fp32 NCHW network input (what the reference's DataLoader yields) -> stem im2col operand.
+template <int kTaps>
 __global__ void __launch_bounds__(256)
 stem_im2col_kernel(const float* __restrict__ x, uint4* __restrict__ out) {
     pdl_trigger_ew();
@@ -854,17 +857,34 @@ stem_im2col_kernel(const float* __restrict__ x, uint4* __restrict__ out) {
         const int y = pix >> 5, xx = pix & 31;
         __nv_bfloat16 h[8];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int kk = vec * 8 + q;
-            __nv_bfloat16 v = __float2bfloat16(0.f);
-            if (kk < 27) {
-                const int tap = kk / 3, c = kk - tap * 3;
-                const int r = tap / 3, s = tap - r * 3;
-                v = saug[((y + r) * 34 + (xx + s)) * 3 + c];
-            }
-            h[q] = v;
-        }
+        for (int q = 0; q < 8; ++q) h[q] = stem_operand_value<kTaps>(saug, y, xx, vec * 8 + q);
         o[e] = *reinterpret_cast<uint4*>(h);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Grouped conv (nn.Conv2d(..., groups=g), models/resnext.py:19). The conv runs as a dense conv whose bf16 operands are
+// block-diagonal (one repack entry per group fills its diagonal block, the rest stays zero), so the weight-gradient
+// kernels produce a dense [tap][cin][cout] fp32 matrix; only its diagonal blocks are gradients of real parameters:
+//   dw[o][ci][tap] += dense[tap][(o / cout_g) * cin_g + ci][o]        (dw in the reference's [cout][cin/g][kh][kw])
+// One thread per diagonal element, in the dense matrix's order (coalesced reads, scattered 4-byte writes: the whole
+// gradient is at most a few MB).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+grouped_wgrad_extract_kernel(const float* __restrict__ dense, float* __restrict__ dw, int cout, int cin, int taps,
+                             int groups) {
+    pdl_trigger_ew();
+    pdl_wait();
+    const int cout_g = cout / groups, cin_g = cin / groups;
+    const long long n = static_cast<long long>(taps) * cin * cout_g;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+         i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int ol = static_cast<int>(i % cout_g);
+        const long long r = i / cout_g;
+        const int c = static_cast<int>(r % cin), t = static_cast<int>(r / cin);
+        const int g = c / cin_g, o = g * cout_g + ol;
+        dw[(static_cast<long long>(o) * cin_g + (c - g * cin_g)) * taps + t] +=
+            dense[(static_cast<long long>(t) * cin + c) * cout + o];
     }
 }
 
@@ -926,7 +946,7 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
     pdl_wait();
     __shared__ float tile[32][32 * 9 + 1];
     // first tile of every entry, once per block (a dependent chain of global loads per entry otherwise)
-    constexpr int kMaxEntries = 256;
+    constexpr int kMaxEntries = 512;
     __shared__ int s_first[kMaxEntries + 1];
     if (threadIdx.x == 0) {
         int acc = 0;
@@ -1264,15 +1284,31 @@ cudaError_t launch_augment_nchw(const uint8_t* data, const long long* idx, const
 }
 
 cudaError_t launch_augment_im2col(const uint8_t* data, const long long* idx, const int8_t* ijf, void* out, int N,
-                                  const float* mean, const float* stdv, cudaStream_t s) {
+                                  const float* mean, const float* stdv, cudaStream_t s, int taps) {
     if (N == 0) return cudaSuccess;
-    B2C_LAUNCH(augment_im2col_kernel, N, 256, 0, s, data, idx, ijf, static_cast<uint4*>(out), make_aug(mean, stdv));
+    if (taps == 1) {
+        B2C_LAUNCH(augment_im2col_kernel<1>, N, 256, 0, s, data, idx, ijf, static_cast<uint4*>(out), make_aug(mean, stdv));
+    } else {
+        B2C_LAUNCH(augment_im2col_kernel<9>, N, 256, 0, s, data, idx, ijf, static_cast<uint4*>(out), make_aug(mean, stdv));
+    }
     return cudaGetLastError();
 }
 
-cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s) {
+cudaError_t launch_stem_im2col(const float* x, void* out, int N, cudaStream_t s, int taps) {
     if (N == 0) return cudaSuccess;
-    B2C_LAUNCH(stem_im2col_kernel, N, 256, 0, s, x, static_cast<uint4*>(out));
+    if (taps == 1) {
+        B2C_LAUNCH(stem_im2col_kernel<1>, N, 256, 0, s, x, static_cast<uint4*>(out));
+    } else {
+        B2C_LAUNCH(stem_im2col_kernel<9>, N, 256, 0, s, x, static_cast<uint4*>(out));
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_grouped_wgrad_extract(const float* dense, float* dw, int cout, int cin, int taps, int groups,
+                                         cudaStream_t s) {
+    const long long n = static_cast<long long>(taps) * cin * (cout / groups);
+    if (n == 0) return cudaSuccess;
+    B2C_LAUNCH(grouped_wgrad_extract_kernel, grid_for(n, 256, 148 * 8), 256, 0, s, dense, dw, cout, cin, taps, groups);
     return cudaGetLastError();
 }
 
@@ -1290,7 +1326,7 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
     if (entries == 0) return cudaSuccess;
     // the table lives on the device, so the tile total is not known here: a fixed grid of 8 blocks per SM strides over
     // the global tile list (ResNet-18: 10.9 k tiles)
-    if (entries > 256) return cudaErrorInvalidValue;      // kMaxEntries of the kernel's shared table index
+    if (entries > 512) return cudaErrorInvalidValue;      // kMaxEntries of the kernel's shared table index
     B2C_LAUNCH(repack_kernel, 148 * 8, 256, 0, s, master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd),
                                        table_dev, entries);
     return cudaGetLastError();

@@ -405,6 +405,50 @@ def _bottleneck_spec(num_blocks, planes, num_classes):
     return dict(family="bottleneck", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin)
 
 
+def resnext_spec(num_blocks=(3, 3, 3), cardinality=2, bottleneck_width=64, num_classes=10):
+    """ResNeXt-29 as models/resnext.py:10-71 composes it: a 1x1 stem conv (3 -> 64) + BN + ReLU, three stages of
+    `Block`s — conv1x1 -> BN -> ReLU -> grouped conv3x3 (groups = cardinality, stride) -> BN -> ReLU -> conv1x1 (x2)
+    -> BN -> += shortcut (1x1 conv + BN where the shape changes) -> ReLU — with the group width doubling per stage,
+    avg_pool2d(8), Linear(cardinality * bottleneck_width * 8, 10). `groups` maps the grouped convs' weights to g."""
+    params, buffers, blocks, groups = OrderedDict(), OrderedDict(), [], {}
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    params["conv1.weight"] = (64, 3, 1, 1)
+    bn("bn1", 64)
+    cin, bw = 64, bottleneck_width
+    for li, nb in enumerate(num_blocks):
+        for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+            name, gw = f"layer{li + 1}.{bi}", cardinality * bw
+            cout = 2 * gw
+            params[name + ".conv1.weight"] = (gw, cin, 1, 1)
+            bn(name + ".bn1", gw)
+            params[name + ".conv2.weight"] = (gw, gw // cardinality, 3, 3)
+            groups[name + ".conv2.weight"] = cardinality
+            bn(name + ".bn2", gw)
+            params[name + ".conv3.weight"] = (cout, gw, 1, 1)
+            bn(name + ".bn3", cout)
+            shortcut = s != 1 or cin != cout
+            if shortcut:
+                params[name + ".shortcut.0.weight"] = (cout, cin, 1, 1)
+                bn(name + ".shortcut.1", cout)
+            blocks.append(dict(name=name, cin=cin, planes=gw, cout=cout, stride=s, shortcut=shortcut))
+            cin = cout
+        bw *= 2
+    params["linear.weight"] = (num_classes, cin)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="bottleneck", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin,
+                groups=groups, stem_ksize=1)
+
+
+def resnext29_32x4d_spec(num_classes=10):
+    return resnext_spec(cardinality=32, bottleneck_width=4, num_classes=num_classes)
+
+
 # measurement switch (A/B runs on one box): 0 = separate dgrad and bn_bwd_reduce launches
 FUSE_DGRAD_BN = os.environ.get("B2C_FUSE_DGRAD_BN", "1") != "0"
 # 0 = residual units take their ReLU mask from the activation instead of the forward pass's bit mask
@@ -517,8 +561,12 @@ class ConvUnit(_BNOps):
     (self.cin / self.cout are those layout widths, *_true the reference's)."""
 
     def __init__(self, eng, name, bn_name, x, cin, cout, k, stride, H, W, stem=False, private_stats=False):
+        """stem: x is the stem operand built by the input kernels (im2col of the 3-channel image for k = 3, the image
+        itself padded to 64 channels for k = 1). A grouped conv (spec["groups"]) runs as a dense cin -> cout conv over
+        block-diagonal operands; its weight gradient goes through a dense scratch matrix (see wgrad)."""
         N = eng.N
         self.name, self.bn_name = name, bn_name
+        self.groups = eng.spec.get("groups", {}).get(name + ".weight", 1)
         self.cin_true, self.cout_true = cin, cout
         cin_p, cout_p = (64 if stem else _pad64(cin)), _pad64(cout)
         self.cin, self.cout, self.k, self.stride, self.H, self.W = cin_p, cout_p, k, stride, H, W
@@ -530,16 +578,22 @@ class ConvUnit(_BNOps):
         if stem:
             # the 3-channel stem runs as a 1x1 GEMM over an im2col operand (k = 27 padded to 64)
             self.desc = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, flags=512 if FUSED_FINALIZE else 0)
-            self.desc_w = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, cin_valid=27, kflat_cin=3, cout_valid=cout)
+            if k == 3:
+                self.desc_w = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, cin_valid=27, kflat_cin=3, cout_valid=cout)
+            else:
+                self.desc_w = ops.conv_desc(N, H, W, 64, cout_p, 1, 1, cin_valid=3, cout_valid=cout)
         else:
             halo_shape = k == 3 and stride == 1 and H == W and W in (32, 16, 8)
             pair = CTA_PAIR == "all" or (CTA_PAIR == "halo" and halo_shape)
             self.desc = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride,
                                       flags=(128 if pair else 0) | (512 if FUSED_FINALIZE else 0))
+            tco_out = (name + ".weight") in eng.tco or self.groups > 1       # gradient written [tap][cin][cout]
             self.desc_w = ops.conv_desc(N, H, W, cin_p, cout_p, k, stride, cin_valid=cin, cout_valid=cout,
-                                        flags=(32 | (128 if CTA_PAIR != "0" else 0)) if (name + ".weight") in eng.tco else 0)
+                                        flags=(32 | (128 if CTA_PAIR != "0" else 0)) if tco_out else 0)
         self.eng_scratch = eng.wgrad_scratch
         self.eng = eng
+        if self.groups > 1:
+            eng.grouped_dense(k * k * cin_p * cout_p)
         # BatchNorm partial-sum scratch: shared by the units of the main chain (used strictly one after the other);
         # a shortcut conv that runs concurrently on the side stream gets its own
         if private_stats:
@@ -567,6 +621,16 @@ class ConvUnit(_BNOps):
 
     # ---- backward pieces
     def wgrad(self, dy):
+        if self.groups > 1:
+            # dense [tap][cin][cout] gradient of the block-diagonal operand, then its diagonal blocks -> dw
+            dense = self.eng.grouped_dense(self.k * self.k * self.cin * self.cout)
+
+            def run():
+                dense.zero_()
+                ops.conv_wgrad(self.desc_w, self.x, dy, dense, scratch=self.eng_scratch)
+                ops.grouped_wgrad_extract(dense, self.dw, self.cout, self.cin, self.k * self.k, self.groups)
+            self.eng.run_side(run)
+            return
         self.eng.run_side(lambda: ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch))
 
     def dgrad(self, dy, dx, add_src=None):
@@ -698,6 +762,7 @@ class Engine:
         self._stat_b = torch.zeros(nstat + 64, **f32)
         self._stat_used = [0, 0]
         self.fwd_ops, self.bwd_ops = [], []
+        self.stem_taps = 9
         if spec["family"] == "resnet":
             self._build_resnet()
         elif spec["family"] == "vgg":
@@ -735,9 +800,10 @@ class Engine:
         self.wf_off, self.wd_off, entries = {}, {}, []
         # conv weights stored [tap][cin][cout] in the P / G / M arenas (see _arena_view): every dense conv except the
         # 3-channel stem (its wgrad addresses the im2col'ed k axis) with channel counts the vector path can take
+        grouped = spec.get("groups", {})
         self.tco = set() if not TCO_LAYOUT else {
             name for name, shape in spec["params"].items()
-            if len(shape) == 4 and name not in spec.get("depthwise", ()) and shape[1] != 3
+            if len(shape) == 4 and name not in spec.get("depthwise", ()) and name not in grouped and shape[1] != 3
             and shape[0] % 4 == 0 and shape[1] % 2 == 0}
         self.wd_pair = {}      # 3x3 stride-2 conv1 -> its block's 1x1 shortcut conv, stored right behind it in WD
         wf_n = wd_n = 0
@@ -775,6 +841,22 @@ class Engine:
                                     cin_pad=cin_p, cout_pad=cout_p, kflat=2))
                 wf_n += 2 * cout_p * cin_p
                 wd_n += 2 * cout_p * cin_p
+            elif name in grouped:
+                # nn.Conv2d(groups=g): master [cout][cin/g][kh][kw]; the operands are those of the dense cin -> cout
+                # conv, filled block-diagonally by one entry per group (off-diagonal blocks stay zero)
+                g = grouped[name]
+                cin_g, cout_g, cin = cin, cout // g, cin * g
+                cin_p = _pad64(cin)
+                assert cin == cin_p and cout == cout_p, name
+                self.wf_off[cname] = (wf_n, (k * k, cout_p, cin_p))
+                self.wd_off[cname] = (wd_n, (k * k, cin_p, cout_p))
+                for j in range(g):
+                    entries.append(dict(src_off=poff + j * cout_g * cin_g * k * k,
+                                        wf_off=wf_n + j * cout_g * cin_p + j * cin_g,
+                                        wd_off=wd_n + j * cin_g * cout_p + j * cout_g,
+                                        cout=cout_g, cin=cin_g, taps=k * k, cin_pad=cin_p, cout_pad=cout_p, kflat=0))
+                wf_n += cout_p * cin_p * k * k
+                wd_n += cout_p * cin_p * k * k
             elif cin == 3:      # stem: [cout_pad][64], k = tap*3 + c
                 self.wf_off[cname] = (wf_n, (1, cout_p, 64))
                 entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=-1, cout=cout, cin=cin, taps=k * k,
@@ -862,6 +944,13 @@ class Engine:
 
     def new_f32(self, *shape):
         return torch.zeros(*shape, device=self.device, dtype=torch.float32)
+
+    def grouped_dense(self, n):
+        """Dense weight-gradient matrix of a grouped conv (ConvUnit.wgrad): one buffer, sized for the largest, shared
+        by all grouped convs of the plan — they use it one after the other on the side stream."""
+        if getattr(self, "_grouped_dense", None) is None or self._grouped_dense.numel() < n:   # (plan construction)
+            self._grouped_dense = torch.zeros(n, device=self.device, dtype=torch.float32)
+        return self._grouped_dense[:n]
 
     def new_stat(self, n, forward):
         """n floats of the forward / backward statistic accumulator arena (16-byte aligned)."""
@@ -1301,7 +1390,8 @@ class Engine:
         -> += shortcut(x) (identity, or 1x1 conv(stride) + BN) -> relu. ResNet-50/101/152 (main_dist.py:136)."""
         spec, N = self.spec, self.N
         self.x0 = self.new_act(N, 32, 32, 64)
-        stem = ConvUnit(self, "conv1", "bn1", self.x0, 3, 64, 3, 1, 32, 32, stem=True)
+        self.stem_taps = spec.get("stem_ksize", 3) ** 2       # which operand the input kernels build (trainer, accelerate)
+        stem = ConvUnit(self, "conv1", "bn1", self.x0, 3, 64, spec.get("stem_ksize", 3), 1, 32, 32, stem=True)
         a0 = self.new_act(N, 32, 32, 64)
         self.units = [stem]
         F, blocks = self.fwd_ops, []

@@ -318,18 +318,33 @@ def augment_nchw(data_u8, idx, ijf, out, mean=CIFAR_MEAN, std=CIFAR_STD):
                                _stream()), "b2c_augment_nchw")
 
 
-def augment_im2col(data_u8, idx, ijf, out, mean=CIFAR_MEAN, std=CIFAR_STD):
+def augment_im2col(data_u8, idx, ijf, out, mean=CIFAR_MEAN, std=CIFAR_STD, taps=9):
+    """taps = 9: im2col operand of a 3x3 stem; taps = 1: the image padded to 64 channels (1x1 stem)."""
     lib = _lib.load()
     _need(data_u8, torch.uint8, "data"); _need(idx, torch.int64, "idx"); _need(ijf, torch.int8, "ijf")
     _need(out, torch.bfloat16, "out")
-    check(lib.b2c_augment_im2col(_p(data_u8), _p(idx), _p(ijf), _p(out), idx.numel(), _F3(*mean), _F3(*std),
-                                 _stream()), "b2c_augment_im2col")
+    fn, name = (lib.b2c_augment_im2col, "b2c_augment_im2col") if taps == 9 else \
+        (lib.b2c_augment_nhwc64, "b2c_augment_nhwc64")
+    check(fn(_p(data_u8), _p(idx), _p(ijf), _p(out), idx.numel(), _F3(*mean), _F3(*std), _stream()), name)
 
 
-def stem_im2col(x_nchw, out):
+def stem_im2col(x_nchw, out, taps=9):
     lib = _lib.load()
     _need(x_nchw, torch.float32, "x"); _need(out, torch.bfloat16, "out")
-    check(lib.b2c_stem_im2col(_p(x_nchw), _p(out), x_nchw.shape[0], _stream()), "b2c_stem_im2col")
+    if taps == 9:
+        check(lib.b2c_stem_im2col(_p(x_nchw), _p(out), x_nchw.shape[0], _stream()), "b2c_stem_im2col")
+    else:
+        check(lib.b2c_stem_nhwc64(_p(x_nchw), _p(out), x_nchw.shape[0], _stream()), "b2c_stem_nhwc64")
+
+
+def grouped_wgrad_extract(dense_tco, dw_oihw, cout, cin, taps, groups):
+    """dw_oihw[o][ci][tap] += dense_tco[tap][(o // (cout/g)) * (cin/g) + ci][o] (b2c_grouped_wgrad_extract)."""
+    lib = _lib.load()
+    _need(dense_tco, torch.float32, "dense"); _need(dw_oihw, torch.float32, "dw")
+    if dense_tco.numel() < taps * cin * cout or dw_oihw.numel() != cout * (cin // groups) * taps:
+        raise ValueError("grouped_wgrad_extract: buffer sizes do not match the conv")
+    check(lib.b2c_grouped_wgrad_extract(_p(dense_tco), _p(dw_oihw), cout, cin, taps, groups, _stream()),
+          "b2c_grouped_wgrad_extract")
 
 
 def sgd_step(param, grad, buf, hyper):

@@ -93,7 +93,7 @@ class Trainer:
     def _forward_loss(self, pl=None):
         pl = pl or self._main
         eng = pl["eng"]
-        ops.augment_im2col(self.data, pl["idx"], pl["ijf"], eng.x0)
+        ops.augment_im2col(self.data, pl["idx"], pl["ijf"], eng.x0, taps=eng.stem_taps)
         eng.zero_grad()
         eng.forward(True)
         ops.ce_loss(eng.logits, pl["tgt"], eng.N, self.K, eng.dlogits, self.loss, self.correct)
@@ -269,7 +269,7 @@ class Trainer:
             eng = ev["eng"]
             ev["data"].copy_(torch.from_numpy(images_u8[s:s + b]))
             ev["tgt"].copy_(torch.from_numpy(labels[s:s + b]))
-            ops.augment_im2col(ev["data"], ev["idx"], ev["ijf"], eng.x0)
+            ops.augment_im2col(ev["data"], ev["idx"], ev["ijf"], eng.x0, taps=eng.stem_taps)
             eng.forward(False)
             ops.ce_loss(eng.logits, ev["tgt"], b, self.K, eng.dlogits, ev["loss"], ev["correct"])
             correct += int(ev["correct"].item())

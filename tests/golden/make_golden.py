@@ -85,6 +85,31 @@ def golden_other_nets():
     np.savez_compressed(os.path.join(HERE, "other_nets_seed0_n4.npz"), **out)
 
 
+def golden_resnext():
+    """ResNeXt29_2x64d and ResNeXt29_32x4d (models/resnext.py:78-88; grouped convs): the same quantities as
+    golden_other_nets, in a file of their own."""
+    import models.resnext as ref_rx
+    rs = np.random.RandomState(2)
+    x = torch.from_numpy(rs.standard_normal((4, 3, 32, 32)).astype(np.float32))
+    target = torch.from_numpy(rs.randint(0, 10, size=(4,)).astype(np.int64))
+    out = dict(x=x.numpy(), target=target.numpy())
+    for tag, ctor in (("resnext29_2x64d", ref_rx.ResNeXt29_2x64d), ("resnext29_32x4d", ref_rx.ResNeXt29_32x4d)):
+        torch.manual_seed(0)
+        net = ctor()
+        net.train()
+        logits = net(x)
+        loss = torch.nn.CrossEntropyLoss()(logits, target)
+        loss.backward()
+        names = [n for n, _ in net.named_parameters()]
+        out[tag + "_names"] = np.array(names)
+        out[tag + "_wsum"] = np.array([p.detach().double().sum().item() for _, p in net.named_parameters()])
+        out[tag + "_gnorm"] = np.array([p.grad.norm().item() for _, p in net.named_parameters()])
+        out[tag + "_logits"] = logits.detach().numpy()
+        out[tag + "_loss"] = np.float32(loss.item())
+        print(tag, "loss", loss.item(), "params", len(names))
+    np.savez_compressed(os.path.join(HERE, "resnext_seed0_n4.npz"), **out)
+
+
 def golden_augment():
     import torchvision.transforms as transforms
     from PIL import Image
@@ -143,8 +168,12 @@ def golden_sampler():
 
 
 if __name__ == "__main__":
+    if sys.argv[1:] == ["resnext"]:          # only the fixture added last; the others stay byte-identical
+        golden_resnext()
+        sys.exit(0)
     golden_resnet18()
     golden_other_nets()
+    golden_resnext()
     golden_augment()
     golden_sgd()
     golden_sampler()

@@ -140,7 +140,9 @@ def test_package_initialiser_matches_reference_order():
     cases = [(engine.resnet_spec(), nets.build_resnet_params), (engine.vgg_spec("VGG16"), nets.build_vgg_params),
              (engine.preact_resnet_spec(), nets.build_preact_params),
              (engine.mobilenetv2_spec(), nets.build_mobilenetv2_params),
-             (engine.resnet50_spec(), nets.build_bottleneck_params)]
+             (engine.resnet50_spec(), nets.build_bottleneck_params),
+             (engine.resnext_spec(), nets.build_resnext_params),
+             (engine.resnext_spec(cardinality=32, bottleneck_width=4), nets.build_resnext_32x4d_params)]
     for spec, build in cases:
         for seed in (0, 3):
             p, b = engine.init_params(spec, seed)
@@ -189,7 +191,8 @@ def test_spec_from_the_references_own_modules():
     cases = [("resnet", n, ()) for n in ("ResNet18", "ResNet34", "ResNet50", "ResNet101", "ResNet152")] + \
             [("vgg", "VGG", (v,)) for v in ("VGG11", "VGG13", "VGG16", "VGG19")] + \
             [("preact_resnet", "PreActResNet18", ()), ("preact_resnet", "PreActResNet34", ()),
-             ("mobilenetv2", "MobileNetV2", ()), ("mobilenet", "MobileNet", ()), ("dla_simple", "SimpleDLA", ())]
+             ("mobilenetv2", "MobileNetV2", ()), ("mobilenet", "MobileNet", ()), ("dla_simple", "SimpleDLA", ())] + \
+            [("resnext", n, ()) for n in ("ResNeXt29_2x64d", "ResNeXt29_4x64d", "ResNeXt29_8x64d", "ResNeXt29_32x4d")]
     for mod, ctor, args in cases:
         net = getattr(importlib.import_module("models." + mod), ctor)(*args)
         spec = spec_from_module(net)
