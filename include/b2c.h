@@ -279,6 +279,14 @@ B2C_API int b2c_maxpool2x2_bwd(const void* x, const void* y, const void* dy, voi
 B2C_API int b2c_head_fwd(const void* act, int n, int hw, int channels, const float* weight, const float* bias,
                  int classes, float* pooled, float* logits, void* stream);
 
+/* The same head over an activation whose channel pitch act_ld exceeds the channel count (layouts padded to 64
+ * channels): F.adaptive_avg_pool2d(out, (1, 1)) -> view -> nn.Linear(368, 10) of models/regnet.py:104-106. Any
+ * channels <= 4096; pooled / weight / dweight keep the true width, channels >= `channels` of dact are left untouched. */
+B2C_API int b2c_head_fwd_ld(const void* act, int n, int hw, int channels, int act_ld, const float* weight, const float* bias,
+                    int classes, float* pooled, float* logits, void* stream);
+B2C_API int b2c_head_bwd_ld(const float* dlogits, const float* pooled, const float* weight, int n, int hw, int channels,
+                    int act_ld, int classes, void* dact, float* dweight, float* dbias, void* stream);
+
 /* nn.CrossEntropyLoss() (mean), main.py:86,103: loss[0], dlogits = (softmax - onehot)/n, and the number of
  * top-1 hits (main.py:108-110; may be NULL). target is int64. n <= 65536. */
 B2C_API int b2c_ce_loss(const float* logits, const long long* target, int n, int classes, float* dlogits, float* loss,
@@ -333,7 +341,7 @@ typedef struct B2cRepackEntry {
 } B2cRepackEntry;
 
 /* fp32 OIHW master weights (the reference's state_dict layout) -> bf16 GEMM operands, all convs in
- * one launch. `table` is a DEVICE array of `entries` records. */
+ * one launch. `table` is a DEVICE array of `entries` records (at most 1024). */
 B2C_API int b2c_repack_weights(const float* master, void* w_fprop_arena, void* w_dgrad_arena, const B2cRepackEntry* table,
                        int entries, void* stream);
 

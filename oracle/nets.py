@@ -613,3 +613,93 @@ def resnext_32x4d_forward(x, params, buffers, training=True, taps=None):
 
 def build_resnext_32x4d_params(seed):
     return build_resnext_params(seed, cardinality=32, bottleneck_width=4)
+
+
+# ------------------------------------------------------------------------------------------------
+# RegNetX (models/regnet.py:29-134, se_ratio 0): the same block with widths off the 64-channel grid
+# ------------------------------------------------------------------------------------------------
+REGNETX_CFG = {
+    "RegNetX_200MF": dict(depths=(1, 1, 4, 7), widths=(24, 56, 152, 368), strides=(1, 1, 2, 2), group_width=8),   # :113-122
+    "RegNetX_400MF": dict(depths=(1, 2, 7, 12), widths=(32, 64, 160, 384), strides=(1, 1, 2, 2), group_width=16),  # :125-134
+}
+
+
+def _regnet_blocks(cfg):
+    cin = 64
+    for li, (depth, width, stride) in enumerate(zip(cfg["depths"], cfg["widths"], cfg["strides"])):   # regnet.py:82-96
+        for bi in range(depth):
+            yield f"layer{li + 1}.{bi}", cin, width, (stride if bi == 0 else 1), width // cfg["group_width"]
+            cin = width
+
+
+def build_regnetx_params(seed, name="RegNetX_200MF"):
+    """Seeded parameters equal to `torch.manual_seed(seed); models.regnet.<name>()` (regnet.py:30-54,67-79)."""
+    cfg = REGNETX_CFG[name]
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(cname, cin, cout, k, stride, groups=1):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, groups=groups, bias=False)
+        params[cname + ".weight"] = m.weight.detach().clone()
+
+    def bn(bname, c):
+        m = nn.BatchNorm2d(c)
+        params[bname + ".weight"] = m.weight.detach().clone()
+        params[bname + ".bias"] = m.bias.detach().clone()
+        buffers[bname + ".running_mean"] = m.running_mean.clone()
+        buffers[bname + ".running_var"] = m.running_var.clone()
+        buffers[bname + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 64, 3, 1)
+    bn("bn1", 64)
+    cin_final = 64
+    for bname, cin, width, s, g in _regnet_blocks(cfg):
+        conv(bname + ".conv1", cin, width, 1, 1)               # :34 (w_b = w_out: bottleneck_ratio 1)
+        bn(bname + ".bn1", width)
+        conv(bname + ".conv2", width, width, 3, s, groups=g)   # :37-39
+        bn(bname + ".bn2", width)
+        conv(bname + ".conv3", width, width, 1, 1)             # :46
+        bn(bname + ".bn3", width)
+        if s != 1 or cin != width:                             # :49-55
+            conv(bname + ".shortcut.0", cin, width, 1, s)
+            bn(bname + ".shortcut.1", width)
+        cin_final = width
+    lin = nn.Linear(cin_final, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def regnetx_forward(x, params, buffers, training=True, name="RegNetX_200MF", taps=None):
+    cfg = REGNETX_CFG[name]
+    out = F.conv2d(x, params["conv1.weight"], padding=1)
+    if taps is not None:
+        taps["conv1"] = out
+    out = F.relu(_bn(out, "bn1", params, buffers, training))                                             # regnet.py:99
+    for bname, cin, width, s, g in _regnet_blocks(cfg):
+        xin = out
+        o = F.conv2d(xin, params[bname + ".conv1.weight"])
+        if taps is not None:
+            taps[bname + ".conv1"] = o
+        o = F.relu(_bn(o, bname + ".bn1", params, buffers, training))                                     # :58
+        o = F.conv2d(o, params[bname + ".conv2.weight"], stride=s, padding=1, groups=g)
+        if taps is not None:
+            taps[bname + ".conv2"] = o
+        o = F.relu(_bn(o, bname + ".bn2", params, buffers, training))                                     # :59
+        o = _bn(F.conv2d(o, params[bname + ".conv3.weight"]), bname + ".bn3", params, buffers, training)  # :62
+        if (bname + ".shortcut.0.weight") in params:
+            sc = _bn(F.conv2d(xin, params[bname + ".shortcut.0.weight"], stride=s), bname + ".shortcut.1", params,
+                     buffers, training)
+        else:
+            sc = xin
+        out = F.relu(o + sc)                                                                              # :63-64
+    out = F.adaptive_avg_pool2d(out, (1, 1)).view(out.size(0), -1)                                        # :104-105
+    return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+def build_regnetx_400mf_params(seed):
+    return build_regnetx_params(seed, "RegNetX_400MF")
+
+
+def regnetx_400mf_forward(x, params, buffers, training=True, taps=None):
+    return regnetx_forward(x, params, buffers, training, "RegNetX_400MF", taps)

@@ -11,7 +11,7 @@ names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad
 are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
 Supported compositions: ResNet with BasicBlock or Bottleneck (models/resnet.py), VGG (models/vgg.py), PreActResNet with
 PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), MobileNet (models/mobilenet.py), SimpleDLA (models/dla_simple.py), ResNeXt
-(models/resnext.py, grouped convs); anything else raises — there is no fallback path.
+(models/resnext.py, grouped convs), RegNetX (models/regnet.py without SE); anything else raises — there is no fallback path.
 
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
 shadows class names across files and the reference tree may sit anywhere on sys.path.
@@ -22,8 +22,8 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .engine import (Engine, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, resnet_spec, resnext_spec,
-                     simple_dla_spec, vgg_spec, VGG_CFG)
+from .engine import (Engine, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, regnetx_spec, resnet_spec,
+                     resnext_spec, simple_dla_spec, vgg_spec, REGNETX_CFG, VGG_CFG)
 
 
 def _is(m, name):
@@ -45,6 +45,14 @@ def spec_from_module(net):
         conv2 = net.layer1[0].conv2
         return resnext_spec(tuple(blocks), cardinality=conv2.groups, bottleneck_width=conv2.out_channels // conv2.groups,
                             num_classes=net.linear.out_features)
+    if _is(net, "RegNet") and hasattr(net, "cfg") and hasattr(net, "layer4"):
+        cfg = net.cfg                                                         # models/regnet.py:68-71
+        for name, ref in REGNETX_CFG.items():
+            if cfg.get("se_ratio", 0) == 0 and cfg.get("bottleneck_ratio") == 1 and \
+                    all(tuple(cfg[k]) == ref[k] for k in ("depths", "widths", "strides")) and \
+                    cfg["group_width"] == ref["group_width"]:
+                return regnetx_spec(name, num_classes=net.linear.out_features)
+        raise NotImplementedError("accelerate: only the RegNetX configurations (no squeeze-and-excitation) are supported")
     if _is(net, "PreActResNet") and hasattr(net, "layer4"):
         blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
         if not all(_is(b, "PreActBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):

@@ -873,6 +873,14 @@ int b2c_head_fwd(const void* act, int n, int hw, int channels, const float* weig
                                         as_stream(stream)));
 }
 
+int b2c_head_fwd_ld(const void* act, int n, int hw, int channels, int act_ld, const float* weight, const float* bias,
+                    int classes, float* pooled, float* logits, void* stream) {
+    if (!act || !weight || !bias || !pooled || !logits || n < 1 || hw < 1 || classes < 1 || channels < 1) return B2C_ERR_ARG;
+    if (channels > 4096 || act_ld < channels) return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_head_fwd(act, n, hw, channels, weight, bias, classes, pooled, logits,
+                                        as_stream(stream), act_ld));
+}
+
 int b2c_ce_loss(const float* logits, const long long* target, int n, int classes, float* dlogits, float* loss,
                 int* correct, void* stream) {
     if (!logits || !target || !dlogits || !loss || n < 1 || n > 65536 || classes < 1) return B2C_ERR_ARG;
@@ -886,6 +894,15 @@ int b2c_head_bwd(const float* dlogits, const float* pooled, const float* weight,
     if (channels > 4096 || (channels & 31)) return B2C_ERR_UNSUPPORTED;
     return cuda_rc(b2c::launch_head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, dbias,
                                         as_stream(stream)));
+}
+
+int b2c_head_bwd_ld(const float* dlogits, const float* pooled, const float* weight, int n, int hw, int channels,
+                    int act_ld, int classes, void* dact, float* dweight, float* dbias, void* stream) {
+    if (!dlogits || !pooled || !weight || !dact || !dweight || !dbias || n < 1 || hw < 1 || classes < 1 || channels < 1)
+        return B2C_ERR_ARG;
+    if (channels > 4096 || act_ld < channels) return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, dbias,
+                                        as_stream(stream), act_ld));
 }
 
 int b2c_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out_nchw_f32, int n,

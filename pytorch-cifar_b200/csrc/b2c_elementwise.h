@@ -63,12 +63,13 @@ cudaError_t launch_bn_bwd_apply(const void* dz, const void* y, const float* coef
 cudaError_t launch_maxpool_fwd(const void* x, void* y, int n, int h, int w, int C, cudaStream_t s);
 cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int C,
                                cudaStream_t s);
+// ld: channel pitch of act / dact (0 = C)
 cudaError_t launch_head_fwd(const void* act, int N, int hw, int C, const float* W, const float* bias, int K,
-                            float* pooled, float* logits, cudaStream_t s);
+                            float* pooled, float* logits, cudaStream_t s, int ld = 0);
 cudaError_t launch_ce_loss(const float* logits, const long long* target, int N, int K, float* dlogits, float* loss,
                            int* correct, cudaStream_t s);
 cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const float* W, int N, int hw, int C, int K,
-                            void* dact, float* dW, float* db, cudaStream_t s);
+                            void* dact, float* dW, float* db, cudaStream_t s, int ld = 0);
 cudaError_t launch_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out, int N,
                                 const float* mean, const float* stdv, cudaStream_t s);
 // taps: 9 = im2col operand of a 3x3 stem (k = tap*3 + c), 1 = operand of a 1x1 stem (k = c)

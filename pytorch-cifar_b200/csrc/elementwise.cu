@@ -605,7 +605,8 @@ maxpool_bwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ y, con
 // Head forward. Reference: F.avg_pool2d(out, 4) -> view -> nn.Linear(512, 10), models/resnet.py:137-139.
 // One block per image; thread c owns channel c (blockDim.x == C).
 // ------------------------------------------------------------------------------------------------
-__global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ act, int hw, int C, const float* __restrict__ W,
+// ld = channel pitch of act (>= C: layouts padded to 64 channels, e.g. RegNetX's 368-channel final map).
+__global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ act, int hw, int C, int ld, const float* __restrict__ W,
                                 const float* __restrict__ bias, int K, float* __restrict__ pooled,
                                 float* __restrict__ logits) {
     pdl_trigger_tiny();
@@ -614,8 +615,8 @@ __global__ void head_fwd_kernel(const __nv_bfloat16* __restrict__ act, int hw, i
     const int n = blockIdx.x;
     for (int c = threadIdx.x; c < C; c += blockDim.x) {
         float s = 0.f;
-        const __nv_bfloat16* a = act + static_cast<size_t>(n) * hw * C + c;
-        for (int i = 0; i < hw; ++i) s += __bfloat162float(a[static_cast<size_t>(i) * C]);
+        const __nv_bfloat16* a = act + static_cast<size_t>(n) * hw * ld + c;
+        for (int i = 0; i < hw; ++i) s += __bfloat162float(a[static_cast<size_t>(i) * ld]);
         s *= 1.f / static_cast<float>(hw);
         sp[c] = s;
         pooled[static_cast<size_t>(n) * C + c] = s;
@@ -687,7 +688,7 @@ __global__ void ce_loss_kernel(const float* __restrict__ logits, const long long
 
 // Head backward, part 1: gradient w.r.t. the last activation (avg-pool + linear backward), bf16 NHWC.
 __global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const float* __restrict__ W, int K, int hw,
-                                    int C, __nv_bfloat16* __restrict__ dact) {
+                                    int C, int ld, __nv_bfloat16* __restrict__ dact) {
     pdl_trigger_tiny();
     pdl_wait();
     const int n = blockIdx.x;
@@ -697,8 +698,8 @@ __global__ void head_bwd_act_kernel(const float* __restrict__ dlogits, const flo
             g = fmaf(dlogits[static_cast<size_t>(n) * K + k], __ldg(W + static_cast<size_t>(k) * C + c), g);
         g *= 1.f / static_cast<float>(hw);
         const __nv_bfloat16 b = __float2bfloat16(g);
-        __nv_bfloat16* d = dact + static_cast<size_t>(n) * hw * C + c;
-        for (int i = 0; i < hw; ++i) d[static_cast<size_t>(i) * C] = b;
+        __nv_bfloat16* d = dact + static_cast<size_t>(n) * hw * ld + c;
+        for (int i = 0; i < hw; ++i) d[static_cast<size_t>(i) * ld] = b;
     }
 }
 // Head backward, part 2: dW[k, c] = sum_n dlogits[n,k] * pooled[n,c]; db[k] = sum_n dlogits[n,k].
@@ -946,7 +947,7 @@ repack_kernel(const float* __restrict__ master, __nv_bfloat16* __restrict__ wf, 
     pdl_wait();
     __shared__ float tile[32][32 * 9 + 1];
     // first tile of every entry, once per block (a dependent chain of global loads per entry otherwise)
-    constexpr int kMaxEntries = 512;
+    constexpr int kMaxEntries = 1024;
     __shared__ int s_first[kMaxEntries + 1];
     if (threadIdx.x == 0) {
         int acc = 0;
@@ -1246,9 +1247,11 @@ cudaError_t launch_maxpool_bwd(const void* x, const void* y, const void* dy, voi
 }
 
 cudaError_t launch_head_fwd(const void* act, int N, int hw, int C, const float* W, const float* bias, int K,
-                            float* pooled, float* logits, cudaStream_t s) {
-    if (C > 4096 || (C & 31)) return cudaErrorInvalidValue;
-    B2C_LAUNCH(head_fwd_kernel, N, C < 512 ? C : 512, C * sizeof(float), s, static_cast<const __nv_bfloat16*>(act), hw, C, W, bias, K, pooled,
+                            float* pooled, float* logits, cudaStream_t s, int ld) {
+    if (ld == 0) ld = C;
+    if (C > 4096 || C < 1 || ld < C) return cudaErrorInvalidValue;
+    const int threads = C < 512 ? (C + 31) / 32 * 32 : 512;
+    B2C_LAUNCH(head_fwd_kernel, N, threads, C * sizeof(float), s, static_cast<const __nv_bfloat16*>(act), hw, C, ld, W, bias, K, pooled,
                                                     logits);
     return cudaGetLastError();
 }
@@ -1260,9 +1263,11 @@ cudaError_t launch_ce_loss(const float* logits, const long long* target, int N, 
 }
 
 cudaError_t launch_head_bwd(const float* dlogits, const float* pooled, const float* W, int N, int hw, int C, int K,
-                            void* dact, float* dW, float* db, cudaStream_t s) {
-    if (C > 4096) return cudaErrorInvalidValue;
-    B2C_LAUNCH(head_bwd_act_kernel, N, C < 512 ? C : 512, 0, s, dlogits, W, K, hw, C, static_cast<__nv_bfloat16*>(dact));
+                            void* dact, float* dW, float* db, cudaStream_t s, int ld) {
+    if (ld == 0) ld = C;
+    if (C > 4096 || C < 1 || ld < C) return cudaErrorInvalidValue;
+    const int threads = C < 512 ? (C + 31) / 32 * 32 : 512;
+    B2C_LAUNCH(head_bwd_act_kernel, N, threads, 0, s, dlogits, W, K, hw, C, ld, static_cast<__nv_bfloat16*>(dact));
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     dim3 grid((C + 31) / 32, K);
@@ -1326,7 +1331,7 @@ cudaError_t launch_repack(const float* master, void* wf, void* wd, const RepackE
     if (entries == 0) return cudaSuccess;
     // the table lives on the device, so the tile total is not known here: a fixed grid of 8 blocks per SM strides over
     // the global tile list (ResNet-18: 10.9 k tiles)
-    if (entries > 512) return cudaErrorInvalidValue;      // kMaxEntries of the kernel's shared table index
+    if (entries > 1024) return cudaErrorInvalidValue;      // kMaxEntries of the kernel's shared table index
     B2C_LAUNCH(repack_kernel, 148 * 8, 256, 0, s, master, static_cast<__nv_bfloat16*>(wf), static_cast<__nv_bfloat16*>(wd),
                                        table_dev, entries);
     return cudaGetLastError();

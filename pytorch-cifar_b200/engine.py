@@ -445,6 +445,56 @@ def resnext_spec(num_blocks=(3, 3, 3), cardinality=2, bottleneck_width=64, num_c
                 groups=groups, stem_ksize=1)
 
 
+REGNETX_CFG = {   # models/regnet.py:113-134 (the X variants: no squeeze-and-excitation)
+    "RegNetX_200MF": dict(depths=(1, 1, 4, 7), widths=(24, 56, 152, 368), strides=(1, 1, 2, 2), group_width=8),
+    "RegNetX_400MF": dict(depths=(1, 2, 7, 12), widths=(32, 64, 160, 384), strides=(1, 1, 2, 2), group_width=16),
+}
+
+
+def regnetx_spec(name="RegNetX_200MF", num_classes=10):
+    """RegNetX as models/regnet.py:29-110 composes it (bottleneck_ratio 1, se_ratio 0): conv3x3 stem (3 -> 64) + BN +
+    ReLU, four stages of `Block`s — conv1x1 -> BN -> ReLU -> grouped conv3x3 (groups = width / group_width, stride) ->
+    BN -> ReLU -> conv1x1 -> BN -> += shortcut (1x1 conv + BN where the shape changes) -> ReLU —,
+    adaptive_avg_pool2d(1) over the final 8x8 map, Linear(widths[-1], 10)."""
+    cfg = REGNETX_CFG[name]
+    params, buffers, blocks, groups = OrderedDict(), OrderedDict(), [], {}
+
+    def bn(bname, c):
+        params[bname + ".weight"] = (c,)
+        params[bname + ".bias"] = (c,)
+        buffers[bname + ".running_mean"] = (c,)
+        buffers[bname + ".running_var"] = (c,)
+
+    params["conv1.weight"] = (64, 3, 3, 3)
+    bn("bn1", 64)
+    cin = 64
+    for li, (depth, width, stride) in enumerate(zip(cfg["depths"], cfg["widths"], cfg["strides"])):
+        for bi in range(depth):
+            bname, s, g = f"layer{li + 1}.{bi}", (stride if bi == 0 else 1), width // cfg["group_width"]
+            params[bname + ".conv1.weight"] = (width, cin, 1, 1)
+            bn(bname + ".bn1", width)
+            params[bname + ".conv2.weight"] = (width, width // g, 3, 3)
+            if g > 1:
+                groups[bname + ".conv2.weight"] = g
+            bn(bname + ".bn2", width)
+            params[bname + ".conv3.weight"] = (width, width, 1, 1)
+            bn(bname + ".bn3", width)
+            shortcut = s != 1 or cin != width
+            if shortcut:
+                params[bname + ".shortcut.0.weight"] = (width, cin, 1, 1)
+                bn(bname + ".shortcut.1", width)
+            blocks.append(dict(name=bname, cin=cin, planes=width, cout=width, stride=s, shortcut=shortcut))
+            cin = width
+    params["linear.weight"] = (num_classes, cin)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="bottleneck", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin,
+                groups=groups)
+
+
+def regnetx_400mf_spec(num_classes=10):
+    return regnetx_spec("RegNetX_400MF", num_classes)
+
+
 def resnext29_32x4d_spec(num_classes=10):
     return resnext_spec(cardinality=32, bottleneck_width=4, num_classes=num_classes)
 
@@ -623,12 +673,13 @@ class ConvUnit(_BNOps):
     def wgrad(self, dy):
         if self.groups > 1:
             # dense [tap][cin][cout] gradient of the block-diagonal operand, then its diagonal blocks -> dw
-            dense = self.eng.grouped_dense(self.k * self.k * self.cin * self.cout)
+            cin, cout = self.cin_true, self.cout_true        # the dense matrix has the true channel counts (cin_valid)
+            dense = self.eng.grouped_dense(self.k * self.k * cin * cout)
 
             def run():
                 dense.zero_()
                 ops.conv_wgrad(self.desc_w, self.x, dy, dense, scratch=self.eng_scratch)
-                ops.grouped_wgrad_extract(dense, self.dw, self.cout, self.cin, self.k * self.k, self.groups)
+                ops.grouped_wgrad_extract(dense, self.dw, cout, cin, self.k * self.k, self.groups)
             self.eng.run_side(run)
             return
         self.eng.run_side(lambda: ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch))
@@ -846,8 +897,7 @@ class Engine:
                 # conv, filled block-diagonally by one entry per group (off-diagonal blocks stay zero)
                 g = grouped[name]
                 cin_g, cout_g, cin = cin, cout // g, cin * g
-                cin_p = _pad64(cin)
-                assert cin == cin_p and cout == cout_p, name
+                cin_p = _pad64(cin)          # (padded channels: rows / columns beyond the last group stay zero too)
                 self.wf_off[cname] = (wf_n, (k * k, cout_p, cin_p))
                 self.wd_off[cname] = (wd_n, (k * k, cin_p, cout_p))
                 for j in range(g):
@@ -1232,13 +1282,15 @@ class Engine:
         self.dlogits = self.new_f32(N, K)
         dout_last = self.new_act(*x.shape)
 
+        ld = x.shape[-1]                     # channel pitch of the last activation (padded to 64: RegNetX ends on 368)
+
         def fwd_head(training):
             ops.head_fwd(self.feat_act, N, self.feat_hw, self.feat_c, self.lin_w, self.lin_b, K, self.pooled,
-                         self.logits)
+                         self.logits, act_ld=ld)
 
         def bwd_head():
             ops.head_bwd(self.dlogits, self.pooled, self.lin_w, N, self.feat_hw, self.feat_c, K, dout_last,
-                         self.grad_view(wname), self.grad_view(bname))
+                         self.grad_view(wname), self.grad_view(bname), act_ld=ld)
         return fwd_head, bwd_head, dout_last
 
     # ------------------------------------------------------------------ VGG plan (models/vgg.py:20-38)
@@ -1404,14 +1456,14 @@ class Engine:
         for b in spec["blocks"]:
             name, cin, pl, cout, s = b["name"], b["cin"], b["planes"], b["cout"], b["stride"]
             c1 = ConvUnit(self, name + ".conv1", name + ".bn1", x, cin, pl, 1, 1, H, W)
-            a1 = self.new_act(N, H, W, pl)
+            a1 = self.new_act(N, H, W, _pad64(pl))          # (RegNetX widths are off the 64-channel layout grid)
             c2 = ConvUnit(self, name + ".conv2", name + ".bn2", a1, pl, pl, 3, s, H, W)
             Ho, Wo = H // s, W // s
-            a2 = self.new_act(N, Ho, Wo, pl)
+            a2 = self.new_act(N, Ho, Wo, _pad64(pl))
             c3 = ConvUnit(self, name + ".conv3", name + ".bn3", a2, pl, cout, 1, 1, Ho, Wo)
             cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W,
                           private_stats=True) if b["shortcut"] else None
-            out = self.new_act(N, Ho, Wo, cout)
+            out = self.new_act(N, Ho, Wo, _pad64(cout))
             bits = torch.zeros(out.numel() // 8, dtype=torch.uint8, device=self.device) if RELU_BITS else None
             self.units += [c1, c2, c3] + ([cs] if cs else [])
             blocks.append((c1, a1, c2, a2, c3, cs, out, x, bits))

@@ -288,8 +288,13 @@ def maxpool2x2_bwd(x, y, dy, dx):
     check(lib.b2c_maxpool2x2_bwd(_p(x), _p(y), _p(dy), _p(dx), n, h, w, c, _stream()), "b2c_maxpool2x2_bwd")
 
 
-def head_fwd(act, n, hw, channels, weight, bias, classes, pooled, logits):
+def head_fwd(act, n, hw, channels, weight, bias, classes, pooled, logits, act_ld=None):
+    """act_ld: channel pitch of act when it exceeds `channels` (padded layouts) -> b2c_head_fwd_ld."""
     lib = _lib.load()
+    if act_ld is not None and act_ld != channels:
+        check(lib.b2c_head_fwd_ld(_p(act), n, hw, channels, act_ld, _p(weight), _p(bias), classes, _p(pooled),
+                                  _p(logits), _stream()), "b2c_head_fwd_ld")
+        return
     check(lib.b2c_head_fwd(_p(act), n, hw, channels, _p(weight), _p(bias), classes, _p(pooled), _p(logits),
                            _stream()), "b2c_head_fwd")
 
@@ -301,8 +306,12 @@ def ce_loss(logits, target, n, classes, dlogits, loss, correct=None):
           "b2c_ce_loss")
 
 
-def head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, dbias):
+def head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, dbias, act_ld=None):
     lib = _lib.load()
+    if act_ld is not None and act_ld != channels:
+        check(lib.b2c_head_bwd_ld(_p(dlogits), _p(pooled), _p(weight), n, hw, channels, act_ld, classes, _p(dact),
+                                  _p(dweight), _p(dbias), _stream()), "b2c_head_bwd_ld")
+        return
     check(lib.b2c_head_bwd(_p(dlogits), _p(pooled), _p(weight), n, hw, channels, classes, _p(dact), _p(dweight),
                            _p(dbias), _stream()), "b2c_head_bwd")
 

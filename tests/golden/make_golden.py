@@ -86,14 +86,16 @@ def golden_other_nets():
 
 
 def golden_resnext():
-    """ResNeXt29_2x64d and ResNeXt29_32x4d (models/resnext.py:78-88; grouped convs): the same quantities as
-    golden_other_nets, in a file of their own."""
+    """ResNeXt29_2x64d / 32x4d (models/resnext.py:78-88) and RegNetX_200MF / 400MF (models/regnet.py:113-134), the
+    networks with grouped convs: the same quantities as golden_other_nets, in a file of their own."""
     import models.resnext as ref_rx
+    import models.regnet as ref_rg
     rs = np.random.RandomState(2)
     x = torch.from_numpy(rs.standard_normal((4, 3, 32, 32)).astype(np.float32))
     target = torch.from_numpy(rs.randint(0, 10, size=(4,)).astype(np.int64))
     out = dict(x=x.numpy(), target=target.numpy())
-    for tag, ctor in (("resnext29_2x64d", ref_rx.ResNeXt29_2x64d), ("resnext29_32x4d", ref_rx.ResNeXt29_32x4d)):
+    for tag, ctor in (("resnext29_2x64d", ref_rx.ResNeXt29_2x64d), ("resnext29_32x4d", ref_rx.ResNeXt29_32x4d),
+                      ("regnetx_200mf", ref_rg.RegNetX_200MF), ("regnetx_400mf", ref_rg.RegNetX_400MF)):
         torch.manual_seed(0)
         net = ctor()
         net.train()
@@ -107,7 +109,7 @@ def golden_resnext():
         out[tag + "_logits"] = logits.detach().numpy()
         out[tag + "_loss"] = np.float32(loss.item())
         print(tag, "loss", loss.item(), "params", len(names))
-    np.savez_compressed(os.path.join(HERE, "resnext_seed0_n4.npz"), **out)
+    np.savez_compressed(os.path.join(HERE, "grouped_nets_seed0_n4.npz"), **out)
 
 
 def golden_augment():

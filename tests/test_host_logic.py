@@ -142,7 +142,9 @@ def test_package_initialiser_matches_reference_order():
              (engine.mobilenetv2_spec(), nets.build_mobilenetv2_params),
              (engine.resnet50_spec(), nets.build_bottleneck_params),
              (engine.resnext_spec(), nets.build_resnext_params),
-             (engine.resnext_spec(cardinality=32, bottleneck_width=4), nets.build_resnext_32x4d_params)]
+             (engine.resnext_spec(cardinality=32, bottleneck_width=4), nets.build_resnext_32x4d_params),
+             (engine.regnetx_spec("RegNetX_200MF"), nets.build_regnetx_params),
+             (engine.regnetx_spec("RegNetX_400MF"), nets.build_regnetx_400mf_params)]
     for spec, build in cases:
         for seed in (0, 3):
             p, b = engine.init_params(spec, seed)
@@ -192,7 +194,8 @@ def test_spec_from_the_references_own_modules():
             [("vgg", "VGG", (v,)) for v in ("VGG11", "VGG13", "VGG16", "VGG19")] + \
             [("preact_resnet", "PreActResNet18", ()), ("preact_resnet", "PreActResNet34", ()),
              ("mobilenetv2", "MobileNetV2", ()), ("mobilenet", "MobileNet", ()), ("dla_simple", "SimpleDLA", ())] + \
-            [("resnext", n, ()) for n in ("ResNeXt29_2x64d", "ResNeXt29_4x64d", "ResNeXt29_8x64d", "ResNeXt29_32x4d")]
+            [("resnext", n, ()) for n in ("ResNeXt29_2x64d", "ResNeXt29_4x64d", "ResNeXt29_8x64d", "ResNeXt29_32x4d")] + \
+            [("regnet", "RegNetX_200MF", ()), ("regnet", "RegNetX_400MF", ())]
     for mod, ctor, args in cases:
         net = getattr(importlib.import_module("models." + mod), ctor)(*args)
         spec = spec_from_module(net)
@@ -201,6 +204,6 @@ def test_spec_from_the_references_own_modules():
         assert got == want, (mod, ctor)
         bufs = {n for n, _ in net.named_buffers() if not n.endswith("num_batches_tracked")}
         assert set(spec["buffers"]) == bufs, (mod, ctor)
-    for mod, ctor in (("googlenet", "GoogLeNet"), ("densenet", "DenseNet121"), ("lenet", "LeNet")):
+    for mod, ctor in (("googlenet", "GoogLeNet"), ("densenet", "DenseNet121"), ("lenet", "LeNet"), ("regnet", "RegNetY_400MF")):
         with pytest.raises(NotImplementedError):
             spec_from_module(getattr(importlib.import_module("models." + mod), ctor)())

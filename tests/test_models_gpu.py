@@ -174,7 +174,13 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           # ResNeXt-29 (29 convs, grouped 3x3, 8x8 final maps): measured 1.6 % / 1.9 % on the logits
           # (profiles/r2_parity/parity_resnext29_*.json); this batch's loss rises before it falls, for the oracle too
           "resnext29_2x64d": dict(logits=0.06, near=0.3, near_cos=0.95, min_cos=None, drop=0.9, lr=0.02),
-          "resnext29_32x4d": dict(logits=0.06, near=0.3, near_cos=0.95, min_cos=None, drop=0.9, lr=0.02)}
+          "resnext29_32x4d": dict(logits=0.06, near=0.3, near_cos=0.95, min_cos=None, drop=0.9, lr=0.02),
+          # RegNetX (41 / 68 convs; widths 24..384 padded to the 64-channel layout; 3..46 groups per conv)
+          # measured 5.1 % / 4.8 % on the logits (profiles/r2_parity/parity_regnetx_*.json). With lr 0.02 the fp32 oracle's
+          # loss on this batch climbs from 3.3 to 12 for the 400MF network (ours follows it step for step,
+          # profiles/r2_parity/train_curve_regnetx_400mf_lr0.02.json), so both train with lr 0.002 here, like ResNet-50
+          "regnetx_200mf": dict(logits=0.12, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
+          "regnetx_400mf": dict(logits=0.12, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002)}
 
 MODELS = {
     "vgg16": ("vgg_spec", "build_vgg_params", "vgg_forward", "features.0", ["classifier.weight", "features.41.weight",
@@ -192,6 +198,10 @@ MODELS = {
                         ["linear.weight", "layer3.2.bn3.weight", "layer3.2.bn3.bias"]),
     "resnext29_32x4d": ("resnext29_32x4d_spec", "build_resnext_32x4d_params", "resnext_32x4d_forward", "conv1",
                         ["linear.weight", "layer3.2.bn3.weight", "layer3.2.bn3.bias"]),
+    "regnetx_200mf": ("regnetx_spec", "build_regnetx_params", "regnetx_forward", "conv1",
+                      ["linear.weight", "layer4.6.bn3.weight", "layer4.6.bn3.bias"]),
+    "regnetx_400mf": ("regnetx_400mf_spec", "build_regnetx_400mf_params", "regnetx_400mf_forward", "conv1",
+                      ["linear.weight", "layer4.11.bn3.weight", "layer4.11.bn3.bias"]),
     # SimpleDLA, what main.py:71 constructs (models/dla_simple.py): aggregation trees, Root = 1x1 conv over a concat
     "simpledla": ("simple_dla_spec", "build_simpledla_params", "simpledla_forward", "base.0",
                   ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
@@ -454,3 +464,28 @@ def test_inputs_of_a_1x1_stem(ops):
     ops.augment_im2col(images, idx, ijf, out, taps=1)
     torch.cuda.synchronize()
     assert torch.equal(out[..., :3], ref.permute(0, 2, 3, 1).to(torch.bfloat16)) and (out[..., 3:] == 0).all()
+
+
+def test_head_over_a_padded_channel_layout(ops):
+    """b2c_head_fwd_ld / b2c_head_bwd_ld: adaptive_avg_pool2d(1) -> Linear(368, 10) (models/regnet.py:104-106) over
+    an activation stored with 384 channels per pixel; fp32 arithmetic, so tight against torch."""
+    n, hw, C, ld, K = 37, 64, 368, 384, 10
+    g = torch.Generator(device="cuda").manual_seed(95)
+    act = torch.zeros(n, hw, ld, device="cuda", dtype=torch.bfloat16)
+    act[..., :C] = torch.randn(n, hw, C, device="cuda", generator=g).to(torch.bfloat16)
+    W = torch.randn(K, C, device="cuda", generator=g) * 0.05
+    b = torch.randn(K, device="cuda", generator=g)
+    pooled, logits = torch.empty(n, C, device="cuda"), torch.empty(n, K, device="cuda")
+    ops.head_fwd(act, n, hw, C, W, b, K, pooled, logits, act_ld=ld)
+    a32 = act[..., :C].float().requires_grad_()
+    Wr, br = W.clone().requires_grad_(), b.clone().requires_grad_()
+    ref = F.linear(a32.mean(1), Wr, br)
+    dlog = torch.randn(n, K, device="cuda", generator=g)
+    ref.backward(dlog)
+    dact = torch.full((n, hw, ld), 7.0, device="cuda", dtype=torch.bfloat16)
+    dW, db = torch.empty(K, C, device="cuda"), torch.empty(K, device="cuda")
+    ops.head_bwd(dlog, pooled, W, n, hw, C, K, dact, dW, db, act_ld=ld)
+    torch.cuda.synchronize()
+    assert rel(logits, ref.detach()) < 1e-5 and rel(pooled, a32.detach().mean(1)) < 1e-6
+    assert rel(dW, Wr.grad) < 1e-5 and rel(db, br.grad) < 1e-5
+    assert rel(dact[..., :C].float(), a32.grad) < 5e-3 and (dact[..., C:] == 7.0).all()
