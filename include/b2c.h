@@ -90,6 +90,11 @@ B2C_API int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fp
 B2C_API int b2c_conv1x1_cat_fprop(const B2cConvDesc* d, const void* x0, const void* x1, const void* w_fprop2, void* y,
                           float* part_sum, float* part_sq, int* stat_rows, void* stream);
 
+/* The same over 2..4 sources (xs: HOST array of n_src device pointers): `Root((level + 2) * out_channels, ...)` of
+ * a level-2 tree, models/dla.py:61,72-84, concatenates four tensors. w_fprop_n is bf16 [n_src][cout][cin]. */
+B2C_API int b2c_conv1x1_catn_fprop(const B2cConvDesc* d, const void* const* xs, int n_src, const void* w_fprop_n, void* y,
+                           float* part_sum, float* part_sq, int* stat_rows, void* stream);
+
 /* dx[n,h,w,cin] = conv_transpose(dy, w) (+ add_src). Replaces cudnn_convolution_backward_input reached
  * from loss.backward(), main.py:104. `w_dgrad` is bf16 [tap][cin][cout]. add_src (optional, bf16, dx's
  * shape) is added in the epilogue; for ksize==1 && stride==2 it must be NULL (dx is zero-filled first)

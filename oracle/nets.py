@@ -703,3 +703,94 @@ def build_regnetx_400mf_params(seed):
 
 def regnetx_400mf_forward(x, params, buffers, training=True, taps=None):
     return regnetx_forward(x, params, buffers, training, "RegNetX_400MF", taps)
+
+
+# ------------------------------------------------------------------------------------------------
+# DLA (models/dla.py): level-2 trees aggregate FOUR tensors in their Root
+# ------------------------------------------------------------------------------------------------
+DLA_FULL_TREES = [("layer3", 32, 64, 1, 1), ("layer4", 64, 128, 2, 2), ("layer5", 128, 256, 2, 2),
+                  ("layer6", 256, 512, 1, 2)]          # (name, in, out, level, stride), dla.py:108-111
+
+
+def build_dla_params(seed):
+    """Construction order of DLA.__init__ (dla.py:88-112): base, layer1, layer2, then per Tree (:54-69) the Root
+    first; level 1: left_node, right_node; level 2: level_1 (a level-1 Tree), prev_root, left_node, right_node."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    def block(name, cin, cout, s):                            # dla.py:14-30
+        conv(name + ".conv1", cin, cout, 3, s); bn(name + ".bn1", cout)
+        conv(name + ".conv2", cout, cout, 3, 1); bn(name + ".bn2", cout)
+        if s != 1 or cin != cout:
+            conv(name + ".shortcut.0", cin, cout, 1, s); bn(name + ".shortcut.1", cout)
+
+    def tree(name, cin, cout, level, s):
+        if level == 1:
+            conv(name + ".root.conv", 2 * cout, cout, 1, 1); bn(name + ".root.bn", cout)          # :58
+            block(name + ".left_node", cin, cout, s)
+            block(name + ".right_node", cout, cout, 1)
+        else:
+            conv(name + ".root.conv", (level + 2) * cout, cout, 1, 1); bn(name + ".root.bn", cout)   # :62
+            for i in reversed(range(1, level)):                                                    # :63-66
+                tree(name + f".level_{i}", cin, cout, i, s)
+            block(name + ".prev_root", cin, cout, s)                                               # :67
+            block(name + ".left_node", cout, cout, 1)
+            block(name + ".right_node", cout, cout, 1)
+    for name, cin, cout in (("base", 3, 16), ("layer1", 16, 16), ("layer2", 16, 32)):
+        conv(name + ".0", cin, cout, 3, 1); bn(name + ".1", cout)
+    for name, cin, cout, level, s in DLA_FULL_TREES:
+        tree(name, cin, cout, level, s)
+    lin = nn.Linear(512, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def dla_forward(x, params, buffers, training=True, taps=None):
+    def block(name, xin, s):
+        o = F.relu(_bn(F.conv2d(xin, params[name + ".conv1.weight"], stride=s, padding=1), name + ".bn1", params,
+                       buffers, training))                                                 # dla.py:33
+        o = _bn(F.conv2d(o, params[name + ".conv2.weight"], padding=1), name + ".bn2", params, buffers, training)
+        if (name + ".shortcut.0.weight") in params:
+            sc = _bn(F.conv2d(xin, params[name + ".shortcut.0.weight"], stride=s), name + ".shortcut.1", params, buffers,
+                     training)
+        else:
+            sc = xin
+        return F.relu(o + sc)                                                              # :35-36
+
+    def tree(name, xin, level, s):
+        xs = [block(name + ".prev_root", xin, s)] if level > 1 else []                     # :72
+        h = xin
+        for i in reversed(range(1, level)):                                                # :73-76
+            h = tree(name + f".level_{i}", h, i, s)
+            xs.append(h)
+        h = block(name + ".left_node", h, s if level == 1 else 1)                          # :77-78
+        xs.append(h)
+        h = block(name + ".right_node", h, 1)                                              # :79-80
+        xs.append(h)
+        y = F.conv2d(torch.cat(xs, 1), params[name + ".root.conv.weight"])                 # :48-49
+        if taps is not None:
+            taps[name + ".root.conv"] = y
+        return F.relu(_bn(y, name + ".root.bn", params, buffers, training))                # :50
+    out = x
+    for name in ("base", "layer1", "layer2"):                                              # :115-117
+        out = F.conv2d(out, params[name + ".0.weight"], padding=1)
+        if taps is not None:
+            taps[name + ".0"] = out
+        out = F.relu(_bn(out, name + ".1", params, buffers, training))
+    for name, cin, cout, level, s in DLA_FULL_TREES:                                       # :118-121
+        out = tree(name, out, level, s)
+    out = F.avg_pool2d(out, 4).view(out.size(0), -1)                                       # :122-123
+    return F.linear(out, params["linear.weight"], params["linear.bias"])

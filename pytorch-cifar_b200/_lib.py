@@ -67,6 +67,8 @@ SIGNATURES = {
     "b2c_version": [],
     "b2c_conv_fprop": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, ctypes.POINTER(_I), _P],
     "b2c_conv1x1_cat_fprop": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, ctypes.POINTER(_I), _P],
+    "b2c_conv1x1_catn_fprop": [ctypes.POINTER(ConvDesc), ctypes.POINTER(ctypes.c_void_p), _I, _P, _P, _P, _P,
+                               ctypes.POINTER(_I), _P],
     "b2c_conv_dgrad": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P],
     "b2c_conv_dgrad_bn": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, _P, ctypes.POINTER(ctypes.c_int), _P],
     "b2c_conv_dgrad_with_shortcut": [ctypes.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P],

@@ -11,7 +11,7 @@ names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad
 are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
 Supported compositions: ResNet with BasicBlock or Bottleneck (models/resnet.py), VGG (models/vgg.py), PreActResNet with
 PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), MobileNet (models/mobilenet.py), SimpleDLA (models/dla_simple.py), ResNeXt
-(models/resnext.py, grouped convs), RegNetX (models/regnet.py without SE); anything else raises — there is no fallback path.
+(models/resnext.py, grouped convs), RegNetX (models/regnet.py without SE), DLA (models/dla.py); anything else raises — there is no fallback path.
 
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
 shadows class names across files and the reference tree may sit anywhere on sys.path.
@@ -22,7 +22,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .engine import (Engine, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, regnetx_spec, resnet_spec,
+from .engine import (Engine, dla_spec, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, regnetx_spec, resnet_spec,
                      resnext_spec, simple_dla_spec, vgg_spec, REGNETX_CFG, VGG_CFG)
 
 
@@ -70,6 +70,9 @@ def spec_from_module(net):
                 return vgg_spec(name, num_classes=net.classifier.out_features)
     if _is(net, "SimpleDLA") and hasattr(net, "layer6") and hasattr(net, "base") and _is(net.layer3, "Tree"):
         return simple_dla_spec(num_classes=net.linear.out_features)       # what main.py:71 constructs
+    if _is(net, "DLA") and hasattr(net, "layer6") and hasattr(net, "base") and hasattr(net.layer4, "level_1") \
+            and hasattr(net.layer4, "prev_root"):
+        return dla_spec(num_classes=net.linear.out_features)              # models/dla.py
     if _is(net, "MobileNet") and hasattr(net, "layers") and len(net.layers) == 13 and hasattr(net, "bn1"):
         return mobilenet_spec(num_classes=net.linear.out_features)
     if _is(net, "MobileNetV2") and hasattr(net, "layers") and hasattr(net, "conv2") and len(net.layers) == 17:

@@ -278,30 +278,32 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     return rc;
 }
 
-int b2c_conv1x1_cat_fprop(const B2cConvDesc* d, const void* x0, const void* x1, const void* w_fprop2, void* y,
-                          float* part_sum, float* part_sq, int* stat_rows, void* stream) {
+static int conv1x1_cat_impl(const B2cConvDesc* d, const void* const* xs, int n_src, const void* w_fprop, void* y,
+                            float* part_sum, float* part_sq, int* stat_rows, void* stream) {
     int rc = check_conv(d);
     if (rc) return rc;
     if (d->ksize != 1 || d->stride != 1) return B2C_ERR_UNSUPPORTED;
-    if (!x0 || !x1 || !w_fprop2 || !y || !aligned16(x0) || !aligned16(x1) || !aligned16(w_fprop2) || !aligned16(y))
-        return B2C_ERR_ARG;
+    if (n_src < 2 || n_src > 4) return B2C_ERR_UNSUPPORTED;
+    if (!xs || !w_fprop || !y || !aligned16(w_fprop) || !aligned16(y)) return B2C_ERR_ARG;
+    for (int t = 0; t < n_src; ++t)
+        if (!xs[t] || !aligned16(xs[t])) return B2C_ERR_ARG;
     if ((part_sum == nullptr) != (part_sq == nullptr)) return B2C_ERR_ARG;
     if (!grid_tiles(d->h, d->w, 128)) return B2C_ERR_UNSUPPORTED;
     const long long m_tiles = (static_cast<long long>(d->n) * d->h * d->w + 127) / 128;
     const int bn = pick_bn(d->block_n, d->cout, 256, m_tiles);
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
-    // the two sources are two "taps" of one GEMM: tap t reads activation map t and weight slab t ([t][cout][cin]),
-    // both at pixel offset (0, 0) — the K axis of the concatenated input, split across two tensors
+    // the sources are the "taps" of one GEMM: tap t reads activation map t and weight slab t ([t][cout][cin]),
+    // all at pixel offset (0, 0) — the K axis of the concatenated input, split across the tensors
     TapGemmParams p = {};
     p.m_total = d->n * d->h * d->w;
     p.num_m_tiles = (p.m_total + 127) / 128;
     p.num_n_tiles = d->cout / bn;
     p.k_chunks = d->cin / 64;
-    p.num_taps = 2;
+    p.num_taps = n_src;
     p.gH = d->h;
     p.gW = d->w;
     p.in_stride = 1;
-    for (int t = 0; t < 2; ++t) {
+    for (int t = 0; t < n_src; ++t) {
         p.tap_dh[t] = 0;
         p.tap_dw[t] = 0;
         p.tap_a[t] = static_cast<uint8_t>(t);
@@ -320,17 +322,28 @@ int b2c_conv1x1_cat_fprop(const B2cConvDesc* d, const void* x0, const void* x1, 
     p.stat_ld = acc ? 0 : d->cout;
     const int bh = (128 / d->w) < d->h ? (128 / d->w) : d->h;
     const int bnb = 128 / (d->w * bh);
-    CUtensorMap ma0, ma1, mb;
-    rc = encode_nhwc(&ma0, x0, d->n, d->h, d->w, d->cin, d->w, bh, bnb, 1);
-    if (rc) return rc;
-    rc = encode_nhwc(&ma1, x1, d->n, d->h, d->w, d->cin, d->w, bh, bnb, 1);
-    if (rc) return rc;
-    rc = encode_2d(&mb, w_fprop2, 2LL * d->cout, d->cin, bn);
+    CUtensorMap ma[4], mb;
+    for (int t = 0; t < 4; ++t) {
+        rc = encode_nhwc(&ma[t], xs[t < n_src ? t : n_src - 1], d->n, d->h, d->w, d->cin, d->w, bh, bnb, 1);
+        if (rc) return rc;
+    }
+    rc = encode_2d(&mb, w_fprop, static_cast<long long>(n_src) * d->cout, d->cin, bn);
     if (rc) return rc;
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
-    rc = cuda_rc(b2c::launch_tap_gemm(bn, ma0, ma1, mb, p, max_ctas, stat_rows, as_stream(stream)));
+    rc = cuda_rc(b2c::launch_tap_gemm4(bn, ma[0], ma[1], ma[2], ma[3], mb, p, max_ctas, stat_rows, as_stream(stream)));
     if (acc && stat_rows != nullptr) *stat_rows = 1;
     return rc;
+}
+
+int b2c_conv1x1_cat_fprop(const B2cConvDesc* d, const void* x0, const void* x1, const void* w_fprop2, void* y,
+                          float* part_sum, float* part_sq, int* stat_rows, void* stream) {
+    const void* xs[2] = {x0, x1};
+    return conv1x1_cat_impl(d, xs, 2, w_fprop2, y, part_sum, part_sq, stat_rows, stream);
+}
+
+int b2c_conv1x1_catn_fprop(const B2cConvDesc* d, const void* const* xs, int n_src, const void* w_fprop_n, void* y,
+                           float* part_sum, float* part_sq, int* stat_rows, void* stream) {
+    return conv1x1_cat_impl(d, xs, n_src, w_fprop_n, y, part_sum, part_sq, stat_rows, stream);
 }
 
 static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_shortcut, const void* w_dgrad,

@@ -22,7 +22,7 @@ struct TapGemmParams {
     int in_stride;    // A coordinate = grid coordinate * in_stride + tap offset
     int8_t tap_dh[kMaxTaps];
     int8_t tap_dw[kMaxTaps];
-    uint8_t tap_a[kMaxTaps];   // which A tensor map (0 or 1) the tap reads
+    uint8_t tap_a[kMaxTaps];   // which A tensor map the tap reads (0..3; the CTA-pair kernels take 0 or 1)
     int tap_brow[kMaxTaps];    // first row of the tap's weight slab in the B matrix
     // Output phases (stride-2 dgrad): a tile belongs to one phase = a sub-range of the tap list and an output
     // pixel offset. num_phases == 1 for everything else (phase_begin = {0, num_taps}).
@@ -100,6 +100,10 @@ cudaError_t launch_conv_halo(int bn, const CUtensorMap& a, const CUtensorMap& b,
                              int* stat_rows, cudaStream_t stream);
 cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
                             const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream);
+// up to four A tensor maps (tap_a[t] in 0..3): the 1x1 conv over a concatenation of up to four tensors
+cudaError_t launch_tap_gemm4(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& a2,
+                             const CUtensorMap& a3, const CUtensorMap& b, const TapGemmParams& p, int max_ctas,
+                             int* stat_rows, cudaStream_t stream);
 cudaError_t launch_conv_halo2(int bn, const CUtensorMap& a, const CUtensorMap& b, const HaloParams& p, int max_ctas,
                               int* stat_rows, cudaStream_t stream);   // CTA-pair version (conv_halo2.cu), b box = bn/2 rows
 // CTA-pair (tcgen05.mma.cta_group::2) version of launch_tap_gemm; b has a box of bn/2 rows (conv_gemm2.cu)

@@ -43,6 +43,7 @@ struct TapCfg {
 template <int BN, bool kStats>
 __global__ void __launch_bounds__(320, 1)
 tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant__ CUtensorMap mapA1,
+                const __grid_constant__ CUtensorMap mapA2, const __grid_constant__ CUtensorMap mapA3,
                 const __grid_constant__ CUtensorMap mapB, const __grid_constant__ TapGemmParams p) {
     using Cfg = TapCfg<BN>;
     pdl_trigger_big();
@@ -66,6 +67,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapA0);
         tma_prefetch_desc(&mapA1);
+        tma_prefetch_desc(&mapA2);
+        tma_prefetch_desc(&mapA3);
         tma_prefetch_desc(&mapB);
     }
     if (warp == 1) {
@@ -118,7 +121,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                 const int h0 = (p0 - n0 * img) / p.gW;
                 const int t_end = p.phase_begin[ph + 1];
                 for (int t = p.phase_begin[ph]; t < t_end; ++t) {
-                    const CUtensorMap* ma = p.tap_a[t] ? &mapA1 : &mapA0;
+                    const int am = p.tap_a[t];
+                    const CUtensorMap* ma = am == 0 ? &mapA0 : (am == 1 ? &mapA1 : (am == 2 ? &mapA2 : &mapA3));
                     const int cw = p.tap_dw[t];
                     const int ch = h0 * p.in_stride + p.tap_dh[t];
                     const int brow = p.tap_brow[t] + n_tile * BN;
@@ -357,8 +361,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
 }
 
 template <int BN, bool kStats>
-cudaError_t launch_one(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
-                       const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream) {
+cudaError_t launch_one(const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& a2, const CUtensorMap& a3,
+                       const CUtensorMap& b, const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream) {
     using Cfg = TapCfg<BN>;
     auto kern = tap_gemm_kernel<BN, kStats>;
     static bool attr_done = false;  // per instantiation
@@ -372,28 +376,34 @@ cudaError_t launch_one(const CUtensorMap& a0, const CUtensorMap& a1, const CUten
     grid -= grid % p.num_n_tiles;  // keeps n_tile constant per CTA (per-CTA BatchNorm partial rows)
     if (grid < p.num_n_tiles) grid = p.num_n_tiles;
     if (stat_rows != nullptr) *stat_rows = grid / p.num_n_tiles;
-    B2C_LAUNCH(kern, grid, 320, Cfg::kSmemBytes, stream, a0, a1, b, p);
+    B2C_LAUNCH(kern, grid, 320, Cfg::kSmemBytes, stream, a0, a1, a2, a3, b, p);
     return cudaGetLastError();
 }
 
 }  // namespace
 
-cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
-                            const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream) {
+cudaError_t launch_tap_gemm4(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& a2,
+                             const CUtensorMap& a3, const CUtensorMap& b, const TapGemmParams& p, int max_ctas,
+                             int* stat_rows, cudaStream_t stream) {
     const bool stats = p.part_sum != nullptr;
     switch (bn) {
         case 64:
-            return stats ? launch_one<64, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
-                         : launch_one<64, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
+            return stats ? launch_one<64, true>(a0, a1, a2, a3, b, p, max_ctas, stat_rows, stream)
+                         : launch_one<64, false>(a0, a1, a2, a3, b, p, max_ctas, stat_rows, stream);
         case 128:
-            return stats ? launch_one<128, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
-                         : launch_one<128, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
+            return stats ? launch_one<128, true>(a0, a1, a2, a3, b, p, max_ctas, stat_rows, stream)
+                         : launch_one<128, false>(a0, a1, a2, a3, b, p, max_ctas, stat_rows, stream);
         case 256:
-            return stats ? launch_one<256, true>(a0, a1, b, p, max_ctas, stat_rows, stream)
-                         : launch_one<256, false>(a0, a1, b, p, max_ctas, stat_rows, stream);
+            return stats ? launch_one<256, true>(a0, a1, a2, a3, b, p, max_ctas, stat_rows, stream)
+                         : launch_one<256, false>(a0, a1, a2, a3, b, p, max_ctas, stat_rows, stream);
         default:
             return cudaErrorInvalidValue;
     }
+}
+
+cudaError_t launch_tap_gemm(int bn, const CUtensorMap& a0, const CUtensorMap& a1, const CUtensorMap& b,
+                            const TapGemmParams& p, int max_ctas, int* stat_rows, cudaStream_t stream) {
+    return launch_tap_gemm4(bn, a0, a1, a1, a1, b, p, max_ctas, stat_rows, stream);
 }
 
 }  // namespace b2c

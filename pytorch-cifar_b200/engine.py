@@ -219,9 +219,66 @@ def simple_dla_spec(num_classes=10):
              tree("layer6", 256, 512, 1, 2)]
     params["linear.weight"] = (num_classes, 512)
     params["linear.bias"] = (num_classes,)
-    cat2 = {n for n in params if n.endswith(".root.conv.weight")}
+    catn = {n: 2 for n in params if n.endswith(".root.conv.weight")}
     return dict(family="dla", params=params, buffers=buffers, plain=plain, trees=trees, num_classes=num_classes,
-                feat=512, cat2=cat2)
+                feat=512, catn=catn)
+
+
+def dla_spec(num_classes=10):
+    """DLA as models/dla.py:53-125 composes it: the three plain conv layers of SimpleDLA, then trees whose level-2
+    form (layer4, layer5) is  xs = [prev_root(x)]; x = level_1(x); x = left_node(x); x = right_node(x);
+    root(xs + the three) — a Root over FOUR concatenated tensors — where level_1 is a level-1 tree (root over
+    [left_node, right_node]). Registration order (dla.py:57-69): root, level_1, prev_root, left_node, right_node."""
+    params, buffers, catn = OrderedDict(), OrderedDict(), {}
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    def block(name, cin, cout, stride):
+        params[name + ".conv1.weight"] = (cout, cin, 3, 3)
+        bn(name + ".bn1", cout)
+        params[name + ".conv2.weight"] = (cout, cout, 3, 3)
+        bn(name + ".bn2", cout)
+        sc = stride != 1 or cin != cout
+        if sc:
+            params[name + ".shortcut.0.weight"] = (cout, cin, 1, 1)
+            bn(name + ".shortcut.1", cout)
+        return dict(kind="block", name=name, cin=cin, cout=cout, stride=stride, shortcut=sc)
+
+    def root(name, n_src, cout):
+        params[name + ".root.conv.weight"] = (cout, n_src * cout, 1, 1)
+        catn[name + ".root.conv.weight"] = n_src
+        bn(name + ".root.bn", cout)
+
+    def tree(name, cin, cout, level, stride):
+        if level == 1:
+            root(name, 2, cout)
+            left = block(name + ".left_node", cin, cout, stride)
+            right = block(name + ".right_node", cout, cout, 1)
+            return dict(kind="tree", name=name, cin=cin, cout=cout, stride=stride, left=left, right=right)
+        assert level == 2
+        root(name, 4, cout)
+        level_1 = tree(name + ".level_1", cin, cout, 1, stride)
+        prev_root = block(name + ".prev_root", cin, cout, stride)
+        left = block(name + ".left_node", cout, cout, 1)
+        right = block(name + ".right_node", cout, cout, 1)
+        return dict(kind="tree2", name=name, cin=cin, cout=cout, stride=stride, level_1=level_1, prev_root=prev_root,
+                    left=left, right=right)
+
+    plain = []
+    for name, cin, cout in (("base", 3, 16), ("layer1", 16, 16), ("layer2", 16, 32)):
+        params[name + ".0.weight"] = (cout, cin, 3, 3)
+        bn(name + ".1", cout)
+        plain.append((name, cin, cout))
+    trees = [tree("layer3", 32, 64, 1, 1), tree("layer4", 64, 128, 2, 2), tree("layer5", 128, 256, 2, 2),
+             tree("layer6", 256, 512, 1, 2)]
+    params["linear.weight"] = (num_classes, 512)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="dla", params=params, buffers=buffers, plain=plain, trees=trees, num_classes=num_classes,
+                feat=512, catn=catn)
 
 
 MOBILENET_CFG = [64, (128, 2), 128, (256, 2), 256, (512, 2), 512, 512, 512, 512, 512, (1024, 2), 1024]   # models/mobilenet.py:27
@@ -709,9 +766,10 @@ class RootUnit(_BNOps):
     never materialised: the forward GEMM reads both sources as the two halves of its K axis; each source's data
     gradient is a 1x1 dgrad with its own weight slab, each weight-gradient slab a 1x1 wgrad of its own source."""
 
-    def __init__(self, eng, name, x0, x1, C, cout, H, W):
+    def __init__(self, eng, name, xs, C, cout, H, W):
+        """xs: the 2..4 concatenated tensors ([x0, x1] in dla_simple.py; up to level + 2 = 4 in dla.py:61)."""
         N = eng.N
-        self.name, self.x0, self.x1, self.cin, self.cout, self.H, self.W = name + ".conv", x0, x1, C, cout, H, W
+        self.name, self.xs, self.cin, self.cout, self.H, self.W = name + ".conv", list(xs), C, cout, H, W
         self.rows = N * H * W
         self.y = eng.new_act(N, H, W, cout)
         acc = 512 if FUSED_FINALIZE else 0
@@ -720,19 +778,21 @@ class RootUnit(_BNOps):
         self.desc_w = ops.conv_desc(N, H, W, C, cout, 1, 1, flags=32)
         self.ps, self.pq = eng.part_sum, eng.part_sq
         self.fsum = eng.new_stat(2 * cout, forward=True)
-        self.wf, self.wd = eng.wf_view(self.name), eng.wd_view(self.name)        # [2][cout][C], [2][C][cout]
-        dw = eng.grad_flat(self.name + ".weight")                                  # stored [2][C][cout]
-        self.dw = [dw[:C * cout], dw[C * cout:]]
+        self.wf, self.wd = eng.wf_view(self.name), eng.wd_view(self.name)        # [n][cout][C], [n][C][cout]
+        dw = eng.grad_flat(self.name + ".weight")                                  # stored [n][C][cout]
+        self.dw = [dw[t * C * cout:(t + 1) * C * cout] for t in range(len(self.xs))]
         self.eng = eng
         _bn_views(self, eng, name + ".bn", cout)
 
     def fprop(self, eng):
         ps, pq = (self.fsum[:self.cout], self.fsum[self.cout:]) if FUSED_FINALIZE else (self.ps, self.pq)
-        self.stat_rows = ops.conv1x1_cat_fprop(self.desc, self.x0, self.x1, self.wf, self.y, ps, pq)
+        if len(self.xs) == 2:
+            self.stat_rows = ops.conv1x1_cat_fprop(self.desc, self.xs[0], self.xs[1], self.wf, self.y, ps, pq)
+        else:
+            self.stat_rows = ops.conv1x1_catn_fprop(self.desc, self.xs, self.wf, self.y, ps, pq)
 
     def wgrad(self, dy):
-        self.eng.run_side(lambda: (ops.conv_wgrad(self.desc_w, self.x0, dy, self.dw[0]),
-                                   ops.conv_wgrad(self.desc_w, self.x1, dy, self.dw[1])))
+        self.eng.run_side(lambda: [ops.conv_wgrad(self.desc_w, x, dy, dw) for x, dw in zip(self.xs, self.dw)])
 
     def dgrad(self, dy, t, dx, add_src=None):
         ops.conv_dgrad(self.desc_d, dy, self.wd[t], dx, add_src)
@@ -880,18 +940,20 @@ class Engine:
             cout, cin, k, _ = shape
             cout_p, cin_p = _pad64(cout), _pad64(cin)
             poff = self.p_off[name][0]
-            if name in spec.get("cat2", ()):
-                # Root conv over cat([x0, x1]) (models/dla_simple.py:52-54): the [1][2C][cout] master IS [2][C][cout],
-                # so the operands are those of a two-tap conv with C input channels (b2c_conv1x1_cat_fprop)
-                assert name in self.tco and k == 1 and cin % 128 == 0, name
-                k, cin = 2, cin // 2
+            if name in spec.get("catn", ()):
+                # Root conv over cat(xs) (models/dla_simple.py:52-54, models/dla.py:47-50): the [1][n*C][cout] master IS
+                # [n][C][cout], so the operands are those of an n-tap conv with C input channels
+                # (b2c_conv1x1_cat_fprop / b2c_conv1x1_catn_fprop)
+                ns = spec["catn"][name]
+                assert name in self.tco and k == 1 and cin % (64 * ns) == 0, name
+                cin = cin // ns
                 cin_p = _pad64(cin)
-                self.wf_off[cname] = (wf_n, (2, cout_p, cin_p))
-                self.wd_off[cname] = (wd_n, (2, cin_p, cout_p))
-                entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=wd_n, cout=cout, cin=cin, taps=2,
+                self.wf_off[cname] = (wf_n, (ns, cout_p, cin_p))
+                self.wd_off[cname] = (wd_n, (ns, cin_p, cout_p))
+                entries.append(dict(src_off=poff, wf_off=wf_n, wd_off=wd_n, cout=cout, cin=cin, taps=ns,
                                     cin_pad=cin_p, cout_pad=cout_p, kflat=2))
-                wf_n += 2 * cout_p * cin_p
-                wd_n += 2 * cout_p * cin_p
+                wf_n += ns * cout_p * cin_p
+                wd_n += ns * cout_p * cin_p
             elif name in grouped:
                 # nn.Conv2d(groups=g): master [cout][cin/g][kh][kw]; the operands are those of the dense cin -> cout
                 # conv, filled block-diagonally by one entry per group (off-diagonal blocks stay zero)
@@ -1183,12 +1245,16 @@ class Engine:
                 else:
                     c2.bn_apply(eng, training, b.out, res=b.x, relu_bits=b.bits)
 
-            def plan_bwd(b, dout, ops_list):
-                """Appends this block's backward to ops_list; dout = gradient buffer of b.out. Returns d(b.x)."""
+            def plan_bwd(b, dout, ops_list, acc=None):
+                """Appends this block's backward to ops_list; dout = gradient buffer of b.out. Returns d(b.x).
+                acc: a buffer that already holds another consumer's gradient of b.x — this block's is added to it in
+                place (conv-shortcut blocks only: each of the two data-gradient kernels accumulates)."""
                 c1, c2, cs = b.c1, b.c2, b.cs
                 dy2, da1, dy1 = (eng.new_act(*t.shape) for t in (c2.y, b.a1, c1.y))
                 dys = eng.new_act(*cs.y.shape) if cs is not None else None
-                dx = eng.new_act(*b.x.shape)
+                if acc is not None and cs is None:
+                    raise NotImplementedError("accumulating input gradient of an identity-shortcut block")
+                dx = eng.new_act(*b.x.shape) if acc is None else acc
 
                 def run():
                     c2.bn_backward(eng, dout, b.out, dout, dy2, relu_bits=b.bits)
@@ -1199,7 +1265,11 @@ class Engine:
                     c1.wgrad(dy1)
                     if cs is not None:
                         cs.wgrad(dys)
-                        c1.dgrad_with_shortcut(dy1, dys, cs, dx)
+                        if acc is not None:
+                            cs.dgrad(dys, dx, add_src=dx)
+                            c1.dgrad(dy1, dx, add_src=dx)
+                        else:
+                            c1.dgrad_with_shortcut(dy1, dys, cs, dx)
                     else:
                         c1.dgrad(dy1, dx, add_src=dout)
                 ops_list.append(run)
@@ -1211,7 +1281,7 @@ class Engine:
                 t.left = sub(d["left"], x, H, W)
                 t.right = sub(d["right"], t.left.out, t.left.H, t.left.W)
                 t.H, t.W = t.left.H, t.left.W
-                t.root = RootUnit(eng, d["name"] + ".root", t.left.out, t.right.out, d["cout"], d["cout"], t.H, t.W)
+                t.root = RootUnit(eng, d["name"] + ".root", [t.left.out, t.right.out], d["cout"], d["cout"], t.H, t.W)
                 t.out = eng.new_act(N, t.H, t.W, d["cout"])
                 eng.units.append(t.root)
 
@@ -1221,7 +1291,7 @@ class Engine:
                 t.root.fprop(eng)
                 t.root.bn_apply(eng, training, t.out)
 
-            def plan_bwd(t, dout, ops_list):
+            def plan_bwd(t, dout, ops_list, acc=None):
                 root = t.root
                 dyr = eng.new_act(*root.y.shape)
                 g2 = eng.new_act(*t.right.out.shape)
@@ -1233,7 +1303,50 @@ class Engine:
                 ops_list.append(run_root)
                 g1 = t.right.plan_bwd(g2, ops_list)                  # gradient of out1 through the right sub-tree
                 ops_list.append(lambda: root.dgrad(dyr, 0, g1, add_src=g1))      # + through the root's first slab
-                return t.left.plan_bwd(g1, ops_list)
+                return t.left.plan_bwd(g1, ops_list, acc) if acc is not None else t.left.plan_bwd(g1, ops_list)
+
+        class Tree2:
+            """Level-2 tree of models/dla.py:57-84: prev_root(x) and level_1(x) both read the tree's input; left_node
+            reads level_1's output, right_node left_node's; the root concatenates all four. Backward: root, then
+            right_node, left_node, level_1 — each producer's gradient = its root slab + what its consumer returned —
+            then prev_root, whose input gradient is added to level_1's."""
+            def __init__(t, d, x, H, W):
+                t.prev = Block(d["prev_root"], x, H, W)
+                t.l1 = Tree(d["level_1"], x, H, W)
+                t.H, t.W = t.l1.H, t.l1.W
+                t.left = Block(d["left"], t.l1.out, t.H, t.W)
+                t.right = Block(d["right"], t.left.out, t.H, t.W)
+                t.root = RootUnit(eng, d["name"] + ".root", [t.prev.out, t.l1.out, t.left.out, t.right.out], d["cout"],
+                                  d["cout"], t.H, t.W)
+                t.out = eng.new_act(N, t.H, t.W, d["cout"])
+                eng.units.append(t.root)
+
+            def fwd(t, training):
+                t.prev.fwd(training)
+                t.l1.fwd(training)
+                t.left.fwd(training)
+                t.right.fwd(training)
+                t.root.fprop(eng)
+                t.root.bn_apply(eng, training, t.out)
+
+            def plan_bwd(t, dout, ops_list):
+                root = t.root
+                dyr = eng.new_act(*root.y.shape)
+                g_right = eng.new_act(*t.right.out.shape)
+                g_prev = eng.new_act(*t.prev.out.shape)
+
+                def run_root():
+                    root.bn_backward(eng, dout, t.out, dout, dyr, relu_from_y=True)
+                    root.wgrad(dyr)
+                    root.dgrad(dyr, 3, g_right)
+                    root.dgrad(dyr, 0, g_prev)
+                ops_list.append(run_root)
+                g_left = t.right.plan_bwd(g_right, ops_list)
+                ops_list.append(lambda: root.dgrad(dyr, 2, g_left, add_src=g_left))
+                g_l1 = t.left.plan_bwd(g_left, ops_list)
+                ops_list.append(lambda: root.dgrad(dyr, 1, g_l1, add_src=g_l1))
+                dx = t.prev.plan_bwd(g_prev, ops_list)               # d(x) through prev_root ...
+                return t.l1.plan_bwd(g_l1, ops_list, acc=dx)         # ... + through level_1, accumulated in place
 
         x, H, W = self.x0, 32, 32
         plain = []
@@ -1246,7 +1359,7 @@ class Engine:
             x = act
         trees = []
         for d in spec["trees"]:
-            t = Tree(d, x, H, W)
+            t = (Tree2 if d["kind"] == "tree2" else Tree)(d, x, H, W)
             trees.append(t)
             F.append(t.fwd)
             x, H, W = t.out, t.H, t.W

@@ -71,6 +71,20 @@ def conv1x1_cat_fprop(d, x0, x1, w_fprop2, y, part_sum=None, part_sq=None):
     return rows.value
 
 
+def conv1x1_catn_fprop(d, xs, w_fprop_n, y, part_sum=None, part_sq=None):
+    """y = conv1x1(cat(xs, C)) for 2..4 sources: d describes one source; w_fprop_n is [len(xs)][cout][cin]."""
+    lib = _lib.load()
+    for t in xs:
+        _need(t, torch.bfloat16, "x")
+    _need(w_fprop_n, torch.bfloat16, "w"); _need(y, torch.bfloat16, "y")
+    _need(part_sum, torch.float32, "part_sum"); _need(part_sq, torch.float32, "part_sq")
+    ptrs = (ctypes.c_void_p * len(xs))(*[t.data_ptr() for t in xs])
+    rows = ctypes.c_int(0)
+    check(lib.b2c_conv1x1_catn_fprop(ctypes.byref(d), ptrs, len(xs), _p(w_fprop_n), _p(y), _p(part_sum), _p(part_sq),
+                                     ctypes.byref(rows), _stream()), "b2c_conv1x1_catn_fprop")
+    return rows.value
+
+
 def conv_dgrad(d, dy, w_dgrad, dx, add_src=None):
     lib = _lib.load()
     _need(dy, torch.bfloat16, "dy"); _need(w_dgrad, torch.bfloat16, "w"); _need(dx, torch.bfloat16, "dx")

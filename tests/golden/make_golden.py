@@ -87,7 +87,8 @@ def golden_other_nets():
 
 def golden_resnext():
     """ResNeXt29_2x64d / 32x4d (models/resnext.py:78-88) and RegNetX_200MF / 400MF (models/regnet.py:113-134), the
-    networks with grouped convs: the same quantities as golden_other_nets, in a file of their own."""
+    networks with grouped convs, and DLA (models/dla.py): the same quantities as golden_other_nets, in a file of
+    their own."""
     import models.resnext as ref_rx
     import models.regnet as ref_rg
     rs = np.random.RandomState(2)
@@ -95,7 +96,8 @@ def golden_resnext():
     target = torch.from_numpy(rs.randint(0, 10, size=(4,)).astype(np.int64))
     out = dict(x=x.numpy(), target=target.numpy())
     for tag, ctor in (("resnext29_2x64d", ref_rx.ResNeXt29_2x64d), ("resnext29_32x4d", ref_rx.ResNeXt29_32x4d),
-                      ("regnetx_200mf", ref_rg.RegNetX_200MF), ("regnetx_400mf", ref_rg.RegNetX_400MF)):
+                      ("regnetx_200mf", ref_rg.RegNetX_200MF), ("regnetx_400mf", ref_rg.RegNetX_400MF),
+                      ("dla", __import__("models.dla", fromlist=["x"]).DLA)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

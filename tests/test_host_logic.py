@@ -144,7 +144,9 @@ def test_package_initialiser_matches_reference_order():
              (engine.resnext_spec(), nets.build_resnext_params),
              (engine.resnext_spec(cardinality=32, bottleneck_width=4), nets.build_resnext_32x4d_params),
              (engine.regnetx_spec("RegNetX_200MF"), nets.build_regnetx_params),
-             (engine.regnetx_spec("RegNetX_400MF"), nets.build_regnetx_400mf_params)]
+             (engine.regnetx_spec("RegNetX_400MF"), nets.build_regnetx_400mf_params),
+             (engine.dla_spec(), nets.build_dla_params), (engine.simple_dla_spec(), nets.build_simpledla_params),
+             (engine.mobilenet_spec(), nets.build_mobilenet_params)]
     for spec, build in cases:
         for seed in (0, 3):
             p, b = engine.init_params(spec, seed)
@@ -195,7 +197,7 @@ def test_spec_from_the_references_own_modules():
             [("preact_resnet", "PreActResNet18", ()), ("preact_resnet", "PreActResNet34", ()),
              ("mobilenetv2", "MobileNetV2", ()), ("mobilenet", "MobileNet", ()), ("dla_simple", "SimpleDLA", ())] + \
             [("resnext", n, ()) for n in ("ResNeXt29_2x64d", "ResNeXt29_4x64d", "ResNeXt29_8x64d", "ResNeXt29_32x4d")] + \
-            [("regnet", "RegNetX_200MF", ()), ("regnet", "RegNetX_400MF", ())]
+            [("regnet", "RegNetX_200MF", ()), ("regnet", "RegNetX_400MF", ()), ("dla", "DLA", ())]
     for mod, ctor, args in cases:
         net = getattr(importlib.import_module("models." + mod), ctor)(*args)
         spec = spec_from_module(net)

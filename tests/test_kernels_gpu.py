@@ -948,6 +948,34 @@ def test_conv1x1_over_concat(ops, shape):
         assert rel_err(dw[0].t(), gw[:, t * c:(t + 1) * c, 0, 0]) < 2e-3
 
 
+@pytest.mark.parametrize("shape", [(6, 16, 16, 128, 128, 4), (5, 8, 8, 256, 256, 4), (3, 16, 16, 128, 128, 3),
+                                   (130, 8, 8, 256, 256, 4)])
+def test_conv1x1_over_a_concat_of_up_to_four(ops, shape):
+    """b2c_conv1x1_catn_fprop: the Root of a level-2 tree of models/dla.py:61,72-84 — conv1x1(cat(xs, 1)) over FOUR
+    tensors, each read through its own tensor map — against F.conv2d on the materialised concatenation; statistics
+    like b2c_conv_fprop; with two sources it is b2c_conv1x1_cat_fprop bit for bit."""
+    n, h, w, c, cout, ns = shape
+    xs = [nhwc_bf16(n, h, w, c, 140 + t) for t in range(ns)]
+    wt = weight(cout, ns * c, 1, 150)
+    ref = F.conv2d(torch.cat([to_nchw(x) for x in xs], 1), wt)
+    wn = torch.stack([wt[:, t * c:(t + 1) * c, 0, 0] for t in range(ns)]).contiguous().to(torch.bfloat16)    # [ns][cout][c]
+    whole, y, pad = _guarded((n, h, w, cout), torch.bfloat16, 555.0)
+    ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    rows = ops.conv1x1_catn_fprop(ops.conv_desc(n, h, w, c, cout, 1, 1), xs, wn, y, ps, pq)
+    torch.cuda.synchronize()
+    assert _guards_intact(whole, pad, 555.0)
+    assert torch.isfinite(to_nchw(y)).all() and rel_err(to_nchw(y), ref) < BF16_TOL
+    assert rel_err(ps[:rows].sum(0), ref.sum((0, 2, 3))) < 5e-3 or (ps[:rows].sum(0) - ref.sum((0, 2, 3))).abs().max() < 0.5
+    assert rel_err(pq[:rows].sum(0), (ref * ref).sum((0, 2, 3))) < F32_TOL
+    y2 = torch.empty_like(y)
+    ops.conv1x1_catn_fprop(ops.conv_desc(n, h, w, c, cout, 1, 1), xs[:2], wn[:2].contiguous(), y2)
+    y3 = torch.empty_like(y)
+    ops.conv1x1_cat_fprop(ops.conv_desc(n, h, w, c, cout, 1, 1), xs[0], xs[1], wn[:2].contiguous(), y3)
+    torch.cuda.synchronize()
+    assert torch.equal(y2, y3)
+
+
 @pytest.mark.parametrize("shape", [(8, 32, 32, 64, 128, 3, 2), (16, 16, 16, 128, 256, 3, 2), (64, 8, 8, 256, 512, 3, 2),
                                    (8, 32, 32, 64, 128, 1, 2), (5, 8, 8, 128, 128, 3, 2), (1024, 32, 32, 64, 128, 3, 2)])
 def test_stride2_dgrad_on_cta_pairs(ops, shape):

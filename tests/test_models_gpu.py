@@ -171,6 +171,9 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           # shows the same median gradient error (1.04 vs our 1.02)
           "mobilenet": dict(logits=0.45, near=0.3, near_cos=0.95, min_cos=None, drop=0.95, lr=0.02),
           "simpledla": dict(logits=0.12, near=0.12, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02),
+          # DLA: 49 convs deep; measured 9.7 % on the logits, 12.7 % on the last BatchNorm's bias gradient — stock bf16
+          # autocast shows 12.9 % on the same tensor (profiles/r2_parity/parity_dla.json)
+          "dla": dict(logits=0.15, near=0.2, near_cos=0.98, min_cos=None, drop=0.9, lr=0.02),
           # ResNeXt-29 (29 convs, grouped 3x3, 8x8 final maps): measured 1.6 % / 1.9 % on the logits
           # (profiles/r2_parity/parity_resnext29_*.json); this batch's loss rises before it falls, for the oracle too
           "resnext29_2x64d": dict(logits=0.06, near=0.3, near_cos=0.95, min_cos=None, drop=0.9, lr=0.02),
@@ -202,6 +205,9 @@ MODELS = {
                       ["linear.weight", "layer4.6.bn3.weight", "layer4.6.bn3.bias"]),
     "regnetx_400mf": ("regnetx_400mf_spec", "build_regnetx_400mf_params", "regnetx_400mf_forward", "conv1",
                       ["linear.weight", "layer4.11.bn3.weight", "layer4.11.bn3.bias"]),
+    # DLA (models/dla.py): level-2 trees whose Root reads four tensors; two blocks read a tree's input
+    "dla": ("dla_spec", "build_dla_params", "dla_forward", "base.0",
+            ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
     # SimpleDLA, what main.py:71 constructs (models/dla_simple.py): aggregation trees, Root = 1x1 conv over a concat
     "simpledla": ("simple_dla_spec", "build_simpledla_params", "simpledla_forward", "base.0",
                   ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
