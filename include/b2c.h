@@ -292,6 +292,23 @@ B2C_API int b2c_head_fwd_ld(const void* act, int n, int hw, int channels, int ac
 B2C_API int b2c_head_bwd_ld(const float* dlogits, const float* pooled, const float* weight, int n, int hw, int channels,
                     int act_ld, int classes, void* dact, float* dweight, float* dbias, void* stream);
 
+/* Squeeze-and-excitation, models/senet.py:67-74 (and models/regnet.py:21-25):
+ *     w = F.avg_pool2d(out, out.size(2)); w = F.relu(fc1(w)); w = F.sigmoid(fc2(w)); out = out * w; out += shortcut
+ * y, add (optional: the shortcut) and out are bf16 [n, hw, ld] with `channels` <= ld real channels (ld % 8 == 0; the
+ * padded ones are zero and get scale 0); w1 [reduced][channels], b1 [reduced], w2 [channels][reduced], b2 [channels]
+ * are the fp32 parameters of the two 1x1 convs. Outputs kept for the backward pass: pooled [n][ld], hidden [n][reduced]
+ * (after the ReLU), scale [n][ld] (after the sigmoid), all fp32. Three launches: pool, per-image MLP, scale (+ add). */
+B2C_API int b2c_se_fwd(const void* y, int n, int hw, int channels, int ld, int reduced, const float* w1, const float* b1,
+               const float* w2, const float* b2, float* pooled, float* hidden, float* scale, const void* add, void* out,
+               void* stream);
+/* Its backward, given dout = d loss / d out: dy = dout * scale + (gradient through the pool) (bf16 [n, hw, ld]);
+ * dw1 / db1 / dw2 / db2 are ACCUMULATED (the caller zero-fills them with the other gradients). The gradient of the
+ * shortcut is dout itself. Scratch (caller-owned, fp32): ds [n][ld], dz1 [n][reduced], dp [n][ld]. */
+B2C_API int b2c_se_bwd(const void* dout, const void* y, int n, int hw, int channels, int ld, int reduced, const float* w1,
+               const float* w2, const float* pooled, const float* hidden, const float* scale, float* ds_scratch,
+               float* dz1_scratch, float* dp_scratch, float* dw1, float* db1, float* dw2, float* db2, void* dy,
+               void* stream);
+
 /* nn.CrossEntropyLoss() (mean), main.py:86,103: loss[0], dlogits = (softmax - onehot)/n, and the number of
  * top-1 hits (main.py:108-110; may be NULL). target is int64. n <= 65536. */
 B2C_API int b2c_ce_loss(const float* logits, const long long* target, int n, int classes, float* dlogits, float* loss,

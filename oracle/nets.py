@@ -794,3 +794,76 @@ def dla_forward(x, params, buffers, training=True, taps=None):
         out = tree(name, out, level, s)
     out = F.avg_pool2d(out, 4).view(out.size(0), -1)                                       # :122-123
     return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
+# SENet18 (models/senet.py): pre-activation blocks with squeeze-and-excitation
+# ------------------------------------------------------------------------------------------------
+def _senet_blocks(num_blocks=RESNET18_BLOCKS):
+    cin = 64
+    for li, (nb, pl) in enumerate(zip(num_blocks, RESNET_PLANES)):
+        for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+            yield f"layer{li + 1}.{bi}", cin, pl, s
+            cin = pl
+
+
+def build_senet_params(seed, num_blocks=RESNET18_BLOCKS):
+    """Seeded parameters equal to `torch.manual_seed(seed); models.senet.SENet18()`: SENet.__init__ (senet.py:82-94)
+    with PreActBlock.__init__ (:45-60) — bn1, conv1, bn2, conv2, shortcut conv, fc1, fc2 (1x1 convs with bias)."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride, bias=False):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, bias=bias)
+        params[name + ".weight"] = m.weight.detach().clone()
+        if bias:
+            params[name + ".bias"] = m.bias.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 64, 3, 1)
+    bn("bn1", 64)
+    for name, cin, pl, s in _senet_blocks(num_blocks):
+        bn(name + ".bn1", cin)
+        conv(name + ".conv1", cin, pl, 3, s)
+        bn(name + ".bn2", pl)
+        conv(name + ".conv2", pl, pl, 3, 1)
+        if s != 1 or cin != pl:
+            conv(name + ".shortcut.0", cin, pl, 1, s)
+        conv(name + ".fc1", pl, pl // 16, 1, 1, bias=True)
+        conv(name + ".fc2", pl // 16, pl, 1, 1, bias=True)
+    lin = nn.Linear(512, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def senet_forward(x, params, buffers, training=True, num_blocks=RESNET18_BLOCKS, taps=None):
+    out = F.conv2d(x, params["conv1.weight"], padding=1)
+    if taps is not None:
+        taps["conv1"] = out
+    out = F.relu(_bn(out, "bn1", params, buffers, training))                               # senet.py:104
+    for name, cin, pl, s in _senet_blocks(num_blocks):
+        xin = out
+        o = F.relu(_bn(xin, name + ".bn1", params, buffers, training))                     # :63
+        sc = F.conv2d(o, params[name + ".shortcut.0.weight"], stride=s) if (name + ".shortcut.0.weight") in params \
+            else xin                                                                       # :64
+        o = F.conv2d(o, params[name + ".conv1.weight"], stride=s, padding=1)               # :65
+        if taps is not None:
+            taps[name + ".conv1"] = o
+        o = F.conv2d(F.relu(_bn(o, name + ".bn2", params, buffers, training)), params[name + ".conv2.weight"],
+                     padding=1)                                                            # :66
+        if taps is not None:
+            taps[name + ".conv2"] = o
+        w = F.avg_pool2d(o, o.size(2))                                                     # :69
+        w = F.relu(F.conv2d(w, params[name + ".fc1.weight"], params[name + ".fc1.bias"]))  # :70
+        w = torch.sigmoid(F.conv2d(w, params[name + ".fc2.weight"], params[name + ".fc2.bias"]))   # :71
+        out = o * w + sc                                                                   # :73-75
+    out = F.avg_pool2d(out, 4).view(out.size(0), -1)                                       # :109-110
+    return F.linear(out, params["linear.weight"], params["linear.bias"])

@@ -96,6 +96,8 @@ SIGNATURES = {
     "b2c_bn_bwd_stats_noalloc": [_P, _P, _P, _P, _LL, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_head_fwd": [_P, _I, _I, _I, _P, _P, _I, _P, _P, _P],
     "b2c_ce_loss": [_P, _P, _I, _I, _P, _P, _P, _P],
+    "b2c_se_fwd": [_P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "b2c_se_bwd": [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_head_fwd_ld": [_P, _I, _I, _I, _I, _P, _P, _I, _P, _P, _P],
     "b2c_head_bwd_ld": [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P],
     "b2c_head_bwd": [_P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P],

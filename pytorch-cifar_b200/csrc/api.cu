@@ -918,6 +918,34 @@ int b2c_head_bwd_ld(const float* dlogits, const float* pooled, const float* weig
                                         as_stream(stream), act_ld));
 }
 
+int b2c_se_fwd(const void* y, int n, int hw, int channels, int ld, int reduced, const float* w1, const float* b1,
+               const float* w2, const float* b2, float* pooled, float* hidden, float* scale, const void* add, void* out,
+               void* stream) {
+    if (!y || !w1 || !b1 || !w2 || !b2 || !pooled || !hidden || !scale || !out || n < 1 || hw < 1 || channels < 1 ||
+        reduced < 1 || !aligned16(y) || !aligned16(out) || !aligned16(add) || !aligned16(scale))
+        return B2C_ERR_ARG;
+    if (ld < channels || (ld & 7) || channels > 4096 || reduced > 1024) return B2C_ERR_UNSUPPORTED;
+    cudaStream_t st = as_stream(stream);
+    int rc = cuda_rc(b2c::launch_se_pool(y, nullptr, n, hw, ld, 1.f / static_cast<float>(hw), pooled, st));
+    if (rc) return rc;
+    rc = cuda_rc(b2c::launch_se_fc(pooled, n, channels, reduced, ld, w1, b1, w2, b2, hidden, scale, st));
+    if (rc) return rc;
+    return cuda_rc(b2c::launch_se_scale(y, scale, add, out, n, hw, ld, st));
+}
+
+int b2c_se_bwd(const void* dout, const void* y, int n, int hw, int channels, int ld, int reduced, const float* w1,
+               const float* w2, const float* pooled, const float* hidden, const float* scale, float* ds_scratch,
+               float* dz1_scratch, float* dp_scratch, float* dw1, float* db1, float* dw2, float* db2, void* dy,
+               void* stream) {
+    if (!dout || !y || !w1 || !w2 || !pooled || !hidden || !scale || !ds_scratch || !dz1_scratch || !dp_scratch ||
+        !dw1 || !db1 || !dw2 || !db2 || !dy || n < 1 || hw < 1 || channels < 1 || reduced < 1 || !aligned16(dout) ||
+        !aligned16(y) || !aligned16(dy))
+        return B2C_ERR_ARG;
+    if (ld < channels || (ld & 7) || channels > 4096 || reduced > 1024) return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_se_bwd(dout, y, ds_scratch, scale, hidden, pooled, n, hw, channels, reduced, ld, w1, w2,
+                                      dz1_scratch, dp_scratch, dw1, db1, dw2, db2, dy, as_stream(stream)));
+}
+
 int b2c_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out_nchw_f32, int n,
                      const float* mean_host, const float* std_host, void* stream) {
     if (n == 0) return 0;   // empty batch: nothing to do (zero-size tensors have null pointers)

@@ -95,6 +95,15 @@ cudaError_t launch_dw_dgrad(const void* dy, const float* w, void* dx, int N, int
                             int stride, cudaStream_t s);
 cudaError_t launch_dw_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int c_valid,
                             int stride, cudaStream_t s);
+// Squeeze-and-excitation (se.cu). ld = channel pitch of the activations and of the [N][ld] fp32 per-image vectors.
+cudaError_t launch_se_pool(const void* a, const void* b, int N, int hw, int ld, float mult, float* out, cudaStream_t s);
+cudaError_t launch_se_fc(const float* p, int N, int C, int R, int ld, const float* W1, const float* b1,
+                         const float* W2, const float* b2, float* h, float* sc, cudaStream_t s);
+cudaError_t launch_se_scale(const void* y, const float* sc, const void* add, void* out, int N, int hw, int ld,
+                            cudaStream_t s);
+cudaError_t launch_se_bwd(const void* dout, const void* y, float* ds, const float* sc, const float* h, const float* p,
+                          int N, int hw, int C, int R, int ld, const float* W1, const float* W2, float* dz1, float* dp,
+                          float* dW1, float* db1, float* dW2, float* db2, void* dy, cudaStream_t s);
 int bn_bwd_noalloc_max_channels();
 cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, void* dz_out,
                                         long long rows, int C, float count, const float* gamma, const float* mean,

@@ -224,6 +224,45 @@ def simple_dla_spec(num_classes=10):
                 feat=512, catn=catn)
 
 
+def senet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=10):
+    """SENet18 as models/senet.py:44-117 composes it: conv3x3 stem + BN + ReLU, then PreActBlocks with
+    squeeze-and-excitation — out = relu(bn1(x)); sc = shortcut(out) | x; out = conv2(relu(bn2(conv1(out))));
+    w = sigmoid(fc2(relu(fc1(avg_pool(out))))); out = out * w + sc — avg_pool2d(4), Linear(512, 10).
+    fc1 / fc2 are 1x1 nn.Conv2d WITH bias (senet.py:59-60): `se_fc` lists their weights, which are not conv operands."""
+    params, buffers, blocks, se_fc = OrderedDict(), OrderedDict(), [], set()
+
+    def bn(name, c):
+        params[name + ".weight"] = (c,)
+        params[name + ".bias"] = (c,)
+        buffers[name + ".running_mean"] = (c,)
+        buffers[name + ".running_var"] = (c,)
+
+    params["conv1.weight"] = (64, 3, 3, 3)
+    bn("bn1", 64)
+    cin = 64
+    for li, (nb, pl) in enumerate(zip(num_blocks, planes)):
+        for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+            name = f"layer{li + 1}.{bi}"
+            bn(name + ".bn1", cin)
+            params[name + ".conv1.weight"] = (pl, cin, 3, 3)
+            bn(name + ".bn2", pl)
+            params[name + ".conv2.weight"] = (pl, pl, 3, 3)
+            shortcut = s != 1 or cin != pl
+            if shortcut:
+                params[name + ".shortcut.0.weight"] = (pl, cin, 1, 1)
+            params[name + ".fc1.weight"] = (pl // 16, pl, 1, 1)
+            params[name + ".fc1.bias"] = (pl // 16,)
+            params[name + ".fc2.weight"] = (pl, pl // 16, 1, 1)
+            params[name + ".fc2.bias"] = (pl,)
+            se_fc |= {name + ".fc1.weight", name + ".fc2.weight"}
+            blocks.append(dict(name=name, cin=cin, cout=pl, stride=s, shortcut=shortcut))
+            cin = pl
+    params["linear.weight"] = (num_classes, cin)
+    params["linear.bias"] = (num_classes,)
+    return dict(family="senet", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin,
+                se_fc=se_fc)
+
+
 def dla_spec(num_classes=10):
     """DLA as models/dla.py:53-125 composes it: the three plain conv layers of SimpleDLA, then trees whose level-2
     form (layer4, layer5) is  xs = [prev_root(x)]; x = level_1(x); x = left_node(x); x = right_node(x);
@@ -888,6 +927,8 @@ class Engine:
             self._build_dla()
         elif spec["family"] == "mobilenet":
             self._build_mobilenet()
+        elif spec["family"] == "senet":
+            self._build_senet()
         else:
             raise NotImplementedError(spec["family"])
 
@@ -912,14 +953,14 @@ class Engine:
         # conv weights stored [tap][cin][cout] in the P / G / M arenas (see _arena_view): every dense conv except the
         # 3-channel stem (its wgrad addresses the im2col'ed k axis) with channel counts the vector path can take
         grouped = spec.get("groups", {})
+        not_conv = set(spec.get("depthwise", ())) | set(spec.get("se_fc", ()))     # 4-D weights the GEMM kernels never see
         self.tco = set() if not TCO_LAYOUT else {
             name for name, shape in spec["params"].items()
-            if len(shape) == 4 and name not in spec.get("depthwise", ()) and name not in grouped and shape[1] != 3
+            if len(shape) == 4 and name not in not_conv and name not in grouped and shape[1] != 3
             and shape[0] % 4 == 0 and shape[1] % 2 == 0}
         self.wd_pair = {}      # 3x3 stride-2 conv1 -> its block's 1x1 shortcut conv, stored right behind it in WD
         wf_n = wd_n = 0
-        convs = [(name, shape) for name, shape in spec["params"].items()
-                 if len(shape) == 4 and name not in spec.get("depthwise", ())]
+        convs = [(name, shape) for name, shape in spec["params"].items() if len(shape) == 4 and name not in not_conv]
         # A down-sampling block's `conv1` (3x3) and `shortcut.0` (1x1) read the same input and have the same
         # channel counts: their dgrad operands sit back to back so ONE 10-slab matrix serves the fused dgrad
         # (b2c_conv_dgrad_with_shortcut).
@@ -1549,6 +1590,127 @@ class Engine:
         Bk.append(lambda dout=dout: stem.wgrad(dout))
         self.bwd_ops = Bk
 
+    # ------------------------------------------------------------------ SENet plan (models/senet.py)
+    def _build_senet(self):
+        """models/senet.py:62-78,97-107: the pre-activation block of _build_preact with squeeze-and-excitation between
+        conv2 and the residual add. Two things differ from PreActResNet: the stem has its own BN + ReLU, and a block's
+        output (conv2 out * w + shortcut) is written by the SE scale pass, not by a conv epilogue — so the statistics
+        the NEXT block's bn1 needs are taken from the materialised tensor (b2c_bn_bwd_reduce_acc with dz = y = the
+        tensor accumulates [sum | sum of squares] into one row; b2c_bn_finalize reads it as a single partial row)."""
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        stem = ConvUnit(self, "conv1", "bn1", self.x0, 3, 64, 3, 1, 32, 32, stem=True)
+        a0 = self.new_act(N, 32, 32, 64)
+        self.units = [stem]
+        F, blocks = self.fwd_ops, []
+        eng = self
+
+        class Source:
+            """A materialised tensor whose per-channel statistics feed a BatchNorm."""
+            def __init__(s, y, C):
+                s.y, s.C = y, C
+                s.fsum = eng.new_stat(2 * C, forward=True)
+
+            def take_stats(s):
+                rows = s.y.numel() // s.C
+                ops.bn_bwd_reduce_acc(s.y, None, s.y, None, rows, s.C, s.fsum)
+
+        class PreBN(_BNOps):
+            def __init__(s, bn_name, src, rows):
+                C = src.C
+                s.y, s.cout, s.rows = src.y, C, rows
+                s.fsum = src.fsum
+                s.ps, s.pq, s.stat_rows = src.fsum[:C], src.fsum[C:], 1
+                _bn_views(s, eng, bn_name, C)
+
+        def fwd_stem(training):
+            stem.fprop(self, True)
+            stem.bn_apply(self, training, a0)
+        F.append(fwd_stem)
+        src = Source(a0, 64)
+        F.append(lambda training, src=src: src.take_stats() if training else None)
+        x, H, W = a0, 32, 32
+        max_c = max(b["cout"] for b in spec["blocks"])
+        se_ds, se_dp = self.new_f32(N, max_c), self.new_f32(N, max_c)
+        se_dz1 = self.new_f32(N, max_c // 16)
+        nblk = len(spec["blocks"])
+        for bi, b in enumerate(spec["blocks"]):
+            name, cin, cout, s = b["name"], b["cin"], b["cout"], b["stride"]
+            bn1 = PreBN(name + ".bn1", src, N * H * W)
+            a = self.new_act(N, H, W, cin)
+            c1 = ConvUnit(self, name + ".conv1", name + ".bn2", a, cin, cout, 3, s, H, W)
+            Ho, Wo = H // s, W // s
+            a2 = self.new_act(N, Ho, Wo, cout)
+            c2 = ConvUnit(self, name + ".conv2", None, a2, cout, cout, 3, 1, Ho, Wo)
+            cs = ConvUnit(self, name + ".shortcut.0", None, a, cin, cout, 1, s, H, W) if b["shortcut"] else None
+            R = cout // 16
+            se = dict(R=R, hw=Ho * Wo, C=cout,
+                      w1=self.param_view(name + ".fc1.weight"), b1=self.param_view(name + ".fc1.bias"),
+                      w2=self.param_view(name + ".fc2.weight"), b2=self.param_view(name + ".fc2.bias"),
+                      dw1=self.grad_view(name + ".fc1.weight"), db1=self.grad_view(name + ".fc1.bias"),
+                      dw2=self.grad_view(name + ".fc2.weight"), db2=self.grad_view(name + ".fc2.bias"),
+                      pooled=self.new_f32(N, cout), hidden=self.new_f32(N, R), scale=self.new_f32(N, cout))
+            out = self.new_act(N, Ho, Wo, cout)
+            last = bi == nblk - 1
+            nsrc = None if last else Source(out, cout)
+            self.units += [c1, c2] + ([cs] if cs else [])
+            blocks.append((bn1, a, c1, a2, c2, cs, se, x))
+
+            def fwd(training, bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, cs=cs, se=se, out=out, x=x, nsrc=nsrc):
+                bn1.bn_apply(self, training, a)
+                if cs is not None:          # the shortcut conv overlaps conv1 on the side stream
+                    self.run_side(lambda: cs.fprop(self, stats=False))
+                c1.fprop(self)
+                c1.bn_apply(self, training, a2)
+                c2.fprop(self, stats=False)
+                if cs is not None:
+                    self.join_side()
+                ops.se_fwd(c2.y, N, se["hw"], se["C"], se["C"], se["R"], se["w1"], se["b1"], se["w2"], se["b2"],
+                           se["pooled"], se["hidden"], se["scale"], out, add=(cs.y if cs is not None else x))
+                if nsrc is not None and training:
+                    nsrc.take_stats()
+            F.append(fwd)
+            x, H, W, src = out, Ho, Wo, nsrc
+        fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        for (bn1, a, c1, a2, c2, cs, se, xin) in reversed(blocks):
+            dy2 = self.new_act(*c2.y.shape)
+            da2 = self.new_act(*a2.shape)
+            dy1 = self.new_act(*c1.y.shape)
+            da = self.new_act(*a.shape)
+            dx = self.new_act(*xin.shape)
+
+            def bwd(bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, cs=cs, se=se, dout=dout, dy2=dy2, da2=da2, dy1=dy1, da=da,
+                    dx=dx):
+                C, R = se["C"], se["R"]
+                ops.se_bwd(dout, c2.y, N, se["hw"], C, C, R, se["w1"], se["w2"], se["pooled"], se["hidden"],
+                           se["scale"], se_ds.view(-1)[:N * C], se_dz1.view(-1)[:N * R], se_dp.view(-1)[:N * C],
+                           se["dw1"], se["db1"], se["dw2"], se["db2"], dy2)
+                c2.wgrad(dy2)
+                if FUSE_DGRAD_BN:                           # a2 = relu(bn2(conv1 out))
+                    c1.bn_backward_from_partial(self, da2, dy1, c2.dgrad_bn(self, dy2, da2, c1))
+                else:
+                    c2.dgrad(dy2, da2)
+                    c1.bn_backward(self, da2, a2, da2, dy1, relu_from_y=True)
+                c1.wgrad(dy1)
+                if cs is not None:
+                    cs.wgrad(dout)
+                    c1.dgrad_with_shortcut(dy1, dout, cs, da)
+                    bn1.bn_backward(self, da, a, da, dx, relu_from_y=True)
+                else:
+                    c1.dgrad(dy1, da)
+                    bn1.bn_backward(self, da, a, da, dx, add=dout, relu_from_y=True)   # + the identity shortcut
+            Bk.append(bwd)
+            dout = dx
+        dy0 = self.new_act(*stem.y.shape)
+
+        def bwd_stem(dout=dout):
+            stem.bn_backward(self, dout, a0, dout, dy0, relu_from_y=True)
+            stem.wgrad(dy0)
+        Bk.append(bwd_stem)
+        self.bwd_ops = Bk
+
     # ------------------------------------------------------------------ Bottleneck ResNet plan
     def _build_bottleneck(self):
         """models/resnet.py:87-92: relu(bn1(conv1 1x1)) -> relu(bn2(conv2 3x3, stride)) -> bn3(conv3 1x1, x4)
@@ -1813,7 +1975,7 @@ class Engine:
 
     # ------------------------------------------------------------------ execution
     def forward(self, training=True):
-        if FUSED_FINALIZE:
+        if FUSED_FINALIZE or self.spec["family"] == "senet":      # (senet: statistics of materialised tensors, see there)
             self._stat_f.zero_()
         for op in self.fwd_ops:
             op(training)

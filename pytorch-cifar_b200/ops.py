@@ -330,6 +330,27 @@ def head_bwd(dlogits, pooled, weight, n, hw, channels, classes, dact, dweight, d
                            _p(dbias), _stream()), "b2c_head_bwd")
 
 
+def se_fwd(y, n, hw, channels, ld, reduced, w1, b1, w2, b2, pooled, hidden, scale, out, add=None):
+    """out = y * sigmoid(fc2(relu(fc1(avg_pool(y))))) (+ add) — b2c_se_fwd; w1 [reduced, channels(,1,1)] etc."""
+    lib = _lib.load()
+    _need(y, torch.bfloat16, "y"); _need(out, torch.bfloat16, "out"); _need(add, torch.bfloat16, "add")
+    for t, name in ((w1, "w1"), (b1, "b1"), (w2, "w2"), (b2, "b2"), (pooled, "pooled"), (hidden, "hidden"), (scale, "scale")):
+        _need(t, torch.float32, name)
+    check(lib.b2c_se_fwd(_p(y), n, hw, channels, ld, reduced, _p(w1), _p(b1), _p(w2), _p(b2), _p(pooled), _p(hidden),
+                         _p(scale), _p(add), _p(out), _stream()), "b2c_se_fwd")
+
+
+def se_bwd(dout, y, n, hw, channels, ld, reduced, w1, w2, pooled, hidden, scale, ds, dz1, dp, dw1, db1, dw2, db2, dy):
+    lib = _lib.load()
+    _need(dout, torch.bfloat16, "dout"); _need(y, torch.bfloat16, "y"); _need(dy, torch.bfloat16, "dy")
+    for t, name in ((w1, "w1"), (w2, "w2"), (pooled, "pooled"), (hidden, "hidden"), (scale, "scale"), (ds, "ds"),
+                    (dz1, "dz1"), (dp, "dp"), (dw1, "dw1"), (db1, "db1"), (dw2, "dw2"), (db2, "db2")):
+        _need(t, torch.float32, name)
+    check(lib.b2c_se_bwd(_p(dout), _p(y), n, hw, channels, ld, reduced, _p(w1), _p(w2), _p(pooled), _p(hidden),
+                         _p(scale), _p(ds), _p(dz1), _p(dp), _p(dw1), _p(db1), _p(dw2), _p(db2), _p(dy), _stream()),
+          "b2c_se_bwd")
+
+
 _F3 = ctypes.c_float * 3
 
 

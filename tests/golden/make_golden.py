@@ -87,7 +87,7 @@ def golden_other_nets():
 
 def golden_resnext():
     """ResNeXt29_2x64d / 32x4d (models/resnext.py:78-88) and RegNetX_200MF / 400MF (models/regnet.py:113-134), the
-    networks with grouped convs, and DLA (models/dla.py): the same quantities as golden_other_nets, in a file of
+    networks with grouped convs, DLA (models/dla.py) and SENet18 (models/senet.py): the same quantities as golden_other_nets, in a file of
     their own."""
     import models.resnext as ref_rx
     import models.regnet as ref_rg
@@ -97,7 +97,8 @@ def golden_resnext():
     out = dict(x=x.numpy(), target=target.numpy())
     for tag, ctor in (("resnext29_2x64d", ref_rx.ResNeXt29_2x64d), ("resnext29_32x4d", ref_rx.ResNeXt29_32x4d),
                       ("regnetx_200mf", ref_rg.RegNetX_200MF), ("regnetx_400mf", ref_rg.RegNetX_400MF),
-                      ("dla", __import__("models.dla", fromlist=["x"]).DLA)):
+                      ("dla", __import__("models.dla", fromlist=["x"]).DLA),
+                      ("senet18", __import__("models.senet", fromlist=["x"]).SENet18)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

@@ -171,6 +171,8 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           # shows the same median gradient error (1.04 vs our 1.02)
           "mobilenet": dict(logits=0.45, near=0.3, near_cos=0.95, min_cos=None, drop=0.95, lr=0.02),
           "simpledla": dict(logits=0.12, near=0.12, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02),
+          # SENet18: measured 0.65 % on the logits (profiles/r2_parity/parity_senet18.json)
+          "senet18": dict(logits=0.03, near=0.06, near_cos=0.99, min_cos=0.7, drop=0.9, lr=0.02),
           # DLA: 49 convs deep; measured 9.7 % on the logits, 12.7 % on the last BatchNorm's bias gradient — stock bf16
           # autocast shows 12.9 % on the same tensor (profiles/r2_parity/parity_dla.json)
           "dla": dict(logits=0.15, near=0.2, near_cos=0.98, min_cos=None, drop=0.9, lr=0.02),
@@ -208,6 +210,9 @@ MODELS = {
     # DLA (models/dla.py): level-2 trees whose Root reads four tensors; two blocks read a tree's input
     "dla": ("dla_spec", "build_dla_params", "dla_forward", "base.0",
             ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
+    # SENet18 (models/senet.py): pre-activation blocks with squeeze-and-excitation
+    "senet18": ("senet_spec", "build_senet_params", "senet_forward", "conv1",
+                ["linear.weight", "layer4.1.fc2.weight", "layer4.1.conv2.weight"]),
     # SimpleDLA, what main.py:71 constructs (models/dla_simple.py): aggregation trees, Root = 1x1 conv over a concat
     "simpledla": ("simple_dla_spec", "build_simpledla_params", "simpledla_forward", "base.0",
                   ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
@@ -246,7 +251,9 @@ def test_model_training_step(ops, model):
                for u in eng.units if u.name in taps}
     grads = eng.named_grads()
     # a conv bias followed by BatchNorm has a mathematically zero gradient (fp32 shows round-off noise, we write 0)
-    skip = {k for k in grads_ref if k.endswith(".bias") and cp[k[:-5] + ".weight"].dim() == 4}
+    # (not the squeeze-and-excitation 1x1 convs: their bias feeds a ReLU / sigmoid)
+    skip = {k for k in grads_ref if k.endswith(".bias") and cp[k[:-5] + ".weight"].dim() == 4
+            and (k[:-5] + ".weight") not in eng.spec.get("se_fc", ())}
     assert all(grads[k].abs().max().item() == 0 for k in skip)
     keep = {k: v for k, v in grads_ref.items() if k not in skip and v.norm().item() > 1e-6}
     g_rel = {k: rel(grads[k], v) for k, v in keep.items()}
@@ -495,3 +502,46 @@ def test_head_over_a_padded_channel_layout(ops):
     assert rel(logits, ref.detach()) < 1e-5 and rel(pooled, a32.detach().mean(1)) < 1e-6
     assert rel(dW, Wr.grad) < 1e-5 and rel(db, br.grad) < 1e-5
     assert rel(dact[..., :C].float(), a32.grad) < 5e-3 and (dact[..., C:] == 7.0).all()
+
+
+@pytest.mark.parametrize("shape", [(9, 8, 128, 128, 8), (5, 32, 64, 64, 4), (130, 4, 512, 512, 32), (7, 8, 96, 128, 6)])
+def test_squeeze_and_excitation(ops, shape):
+    """b2c_se_fwd / b2c_se_bwd: w = sigmoid(fc2(relu(fc1(avg_pool(y))))); out = y * w + shortcut (models/senet.py:67-75)
+    and its backward, against torch autograd in fp32 on the same bf16 inputs; the last case has 96 real channels in a
+    128-channel layout."""
+    n, hwside, C, ld, R = shape
+    hw = hwside * hwside
+    g = torch.Generator(device="cuda").manual_seed(97)
+    y = torch.zeros(n, hw, ld, device="cuda", dtype=torch.bfloat16)
+    y[..., :C] = torch.randn(n, hw, C, device="cuda", generator=g).to(torch.bfloat16)
+    add = torch.zeros_like(y)
+    add[..., :C] = torch.randn(n, hw, C, device="cuda", generator=g).to(torch.bfloat16)
+    w1 = torch.randn(R, C, 1, 1, device="cuda", generator=g) * 0.2
+    b1 = torch.randn(R, device="cuda", generator=g) * 0.1
+    w2 = torch.randn(C, R, 1, 1, device="cuda", generator=g) * 0.5
+    b2 = torch.randn(C, device="cuda", generator=g) * 0.1
+    pooled, hidden, scale = torch.empty(n, ld, device="cuda"), torch.empty(n, R, device="cuda"), torch.empty(n, ld, device="cuda")
+    out = torch.full_like(y, float("nan"))
+    ops.se_fwd(y, n, hw, C, ld, R, w1, b1, w2, b2, pooled, hidden, scale, out, add=add)
+    # torch
+    yr = y[..., :C].float().permute(0, 2, 1).reshape(n, C, hwside, hwside).requires_grad_()
+    leaves = [t.clone().requires_grad_() for t in (w1, b1, w2, b2)]
+    w = F.avg_pool2d(yr, hwside)
+    w = F.relu(F.conv2d(w, leaves[0], leaves[1]))
+    w = torch.sigmoid(F.conv2d(w, leaves[2], leaves[3]))
+    ref = yr * w + add[..., :C].float().permute(0, 2, 1).reshape(n, C, hwside, hwside)
+    dout = torch.zeros_like(y)
+    dout[..., :C] = torch.randn(n, hw, C, device="cuda", generator=g).to(torch.bfloat16)
+    ref.backward(dout[..., :C].float().permute(0, 2, 1).reshape(n, C, hwside, hwside))
+    ds, dz1, dp = torch.empty(n * ld, device="cuda"), torch.empty(n * R, device="cuda"), torch.empty(n * ld, device="cuda")
+    grads = [torch.full_like(t, 0.25) for t in (w1, b1, w2, b2)]              # the parameter gradients accumulate
+    dy = torch.full_like(y, float("nan"))
+    ops.se_bwd(dout, y, n, hw, C, ld, R, w1, w2, pooled, hidden, scale, ds, dz1, dp, grads[0], grads[1], grads[2],
+               grads[3], dy)
+    torch.cuda.synchronize()
+    to_nhwc = lambda t: t.reshape(n, C, hw).permute(0, 2, 1)
+    assert rel(out[..., :C].float(), to_nhwc(ref.detach())) < 5e-3 and (out[..., C:] == 0).all()
+    assert rel(scale[:, :C], w.detach().reshape(n, C)) < 1e-5 and (scale[:, C:] == 0).all()
+    assert rel(dy[..., :C].float(), to_nhwc(yr.grad)) < 5e-3 and (dy[..., C:] == 0).all()
+    for got, leaf in zip(grads, leaves):
+        assert rel(got - 0.25, leaf.grad) < 1e-4, leaf.shape
