@@ -621,6 +621,8 @@ def build_resnext_32x4d_params(seed):
 REGNETX_CFG = {
     "RegNetX_200MF": dict(depths=(1, 1, 4, 7), widths=(24, 56, 152, 368), strides=(1, 1, 2, 2), group_width=8),   # :113-122
     "RegNetX_400MF": dict(depths=(1, 2, 7, 12), widths=(32, 64, 160, 384), strides=(1, 1, 2, 2), group_width=16),  # :125-134
+    "RegNetY_400MF": dict(depths=(1, 2, 7, 12), widths=(32, 64, 160, 384), strides=(1, 1, 2, 2), group_width=16,
+                          se_ratio=0.25),                                                                           # :137-146
 }
 
 
@@ -638,9 +640,11 @@ def build_regnetx_params(seed, name="RegNetX_200MF"):
     torch.manual_seed(seed)
     params, buffers = OrderedDict(), OrderedDict()
 
-    def conv(cname, cin, cout, k, stride, groups=1):
-        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, groups=groups, bias=False)
+    def conv(cname, cin, cout, k, stride, groups=1, bias=False):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, groups=groups, bias=bias)
         params[cname + ".weight"] = m.weight.detach().clone()
+        if bias:
+            params[cname + ".bias"] = m.bias.detach().clone()
 
     def bn(bname, c):
         m = nn.BatchNorm2d(c)
@@ -658,6 +662,10 @@ def build_regnetx_params(seed, name="RegNetX_200MF"):
         bn(bname + ".bn1", width)
         conv(bname + ".conv2", width, width, 3, s, groups=g)   # :37-39
         bn(bname + ".bn2", width)
+        if cfg.get("se_ratio", 0) > 0:                          # :42-45, SE.__init__ :15-18
+            w_se = int(round(cin * cfg["se_ratio"]))
+            conv(bname + ".se.se1", width, w_se, 1, 1, bias=True)
+            conv(bname + ".se.se2", w_se, width, 1, 1, bias=True)
         conv(bname + ".conv3", width, width, 1, 1)             # :46
         bn(bname + ".bn3", width)
         if s != 1 or cin != width:                             # :49-55
@@ -686,6 +694,11 @@ def regnetx_forward(x, params, buffers, training=True, name="RegNetX_200MF", tap
         if taps is not None:
             taps[bname + ".conv2"] = o
         o = F.relu(_bn(o, bname + ".bn2", params, buffers, training))                                     # :59
+        if (bname + ".se.se1.weight") in params:                                                          # :60-61, :20-25
+            w = F.adaptive_avg_pool2d(o, (1, 1))
+            w = F.relu(F.conv2d(w, params[bname + ".se.se1.weight"], params[bname + ".se.se1.bias"]))
+            w = torch.sigmoid(F.conv2d(w, params[bname + ".se.se2.weight"], params[bname + ".se.se2.bias"]))
+            o = o * w
         o = _bn(F.conv2d(o, params[bname + ".conv3.weight"]), bname + ".bn3", params, buffers, training)  # :62
         if (bname + ".shortcut.0.weight") in params:
             sc = _bn(F.conv2d(xin, params[bname + ".shortcut.0.weight"], stride=s), bname + ".shortcut.1", params,
@@ -867,3 +880,11 @@ def senet_forward(x, params, buffers, training=True, num_blocks=RESNET18_BLOCKS,
         out = o * w + sc                                                                   # :73-75
     out = F.avg_pool2d(out, 4).view(out.size(0), -1)                                       # :109-110
     return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+def build_regnety_400mf_params(seed):
+    return build_regnetx_params(seed, "RegNetY_400MF")
+
+
+def regnety_400mf_forward(x, params, buffers, training=True, taps=None):
+    return regnetx_forward(x, params, buffers, training, "RegNetY_400MF", taps)

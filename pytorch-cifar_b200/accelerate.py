@@ -11,7 +11,7 @@ names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad
 are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
 Supported compositions: ResNet with BasicBlock or Bottleneck (models/resnet.py), VGG (models/vgg.py), PreActResNet with
 PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), MobileNet (models/mobilenet.py), SimpleDLA (models/dla_simple.py), ResNeXt
-(models/resnext.py, grouped convs), RegNetX (models/regnet.py without SE), DLA (models/dla.py), SENet18 (models/senet.py); anything else raises — there is no fallback path.
+(models/resnext.py, grouped convs), RegNetX / RegNetY (models/regnet.py), DLA (models/dla.py), SENet18 (models/senet.py); anything else raises — there is no fallback path.
 
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
 shadows class names across files and the reference tree may sit anywhere on sys.path.
@@ -23,7 +23,7 @@ import torch.nn as nn
 
 from . import ops
 from .engine import (Engine, dla_spec, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, regnetx_spec, resnet_spec,
-                     resnext_spec, senet_spec, simple_dla_spec, vgg_spec, REGNETX_CFG, VGG_CFG)
+                     resnext_spec, senet_spec, simple_dla_spec, vgg_spec, REGNET_CFG, VGG_CFG)
 
 
 def _is(m, name):
@@ -47,12 +47,12 @@ def spec_from_module(net):
                             num_classes=net.linear.out_features)
     if _is(net, "RegNet") and hasattr(net, "cfg") and hasattr(net, "layer4"):
         cfg = net.cfg                                                         # models/regnet.py:68-71
-        for name, ref in REGNETX_CFG.items():
-            if cfg.get("se_ratio", 0) == 0 and cfg.get("bottleneck_ratio") == 1 and \
+        for name, ref in REGNET_CFG.items():
+            if cfg.get("se_ratio", 0) == ref["se_ratio"] and cfg.get("bottleneck_ratio") == 1 and \
                     all(tuple(cfg[k]) == ref[k] for k in ("depths", "widths", "strides")) and \
                     cfg["group_width"] == ref["group_width"]:
                 return regnetx_spec(name, num_classes=net.linear.out_features)
-        raise NotImplementedError("accelerate: only the RegNetX configurations (no squeeze-and-excitation) are supported")
+        raise NotImplementedError("accelerate: only the RegNet configurations of models/regnet.py are supported")
     if _is(net, "SENet") and hasattr(net, "layer4") and hasattr(net, "bn1"):
         blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
         if not all(_is(b, "PreActBlock") and hasattr(b, "fc1") for i in range(1, 5) for b in getattr(net, f"layer{i}")):

@@ -92,14 +92,16 @@ se_fc_kernel(const float* __restrict__ p, int C, int R, int ld, const float* __r
         }
     }
     __syncthreads();
-    for (int c = threadIdx.x; c < ld; c += blockDim.x) {
-        float sv = 0.f;                    // padded channels: scale 0 (their activations are zero anyway)
-        if (c < C) {
-            float acc = b2[c];
-            for (int j = 0; j < R; ++j) acc = fmaf(__ldg(W2 + static_cast<size_t>(c) * R + j), sh[j], acc);
-            sv = 1.f / (1.f + expf(-acc));
-        }
-        s_out[static_cast<size_t>(n) * ld + c] = sv;
+    // one warp per channel, lanes over the hidden units: row c of W2 is read as one coalesced run (a thread per
+    // channel would touch 32 different lines per load: measured 52 us per launch for 512 images x 384 channels x 96)
+    for (int c = warp; c < ld; c += nw) {
+        float acc = 0.f;
+        if (c < C)
+            for (int j = lane; j < R; j += 32) acc = fmaf(__ldg(W2 + static_cast<size_t>(c) * R + j), sh[j], acc);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+        // padded channels: scale 0 (their activations are zero anyway)
+        if (lane == 0) s_out[static_cast<size_t>(n) * ld + c] = c < C ? 1.f / (1.f + expf(-(acc + b2[c]))) : 0.f;
     }
 }
 
@@ -172,13 +174,29 @@ se_fc_bwd_kernel(float* __restrict__ ds, const float* __restrict__ s, const floa
         ds[static_cast<size_t>(n) * ld + c] = v;
     }
     __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    for (int j = warp; j < R; j += nw) {
+    // dh[j] = sum_c W2[c][j] dz2[c]: threads run along j (coalesced rows of W2); when R is small, the channel range is
+    // split over 256 / Rp thread groups whose partial sums meet in shared memory
+    __shared__ float part[256];
+    const int Rp = (R + 31) & ~31;
+    if (Rp <= 256) {
+        const int G = 256 / Rp;
+        const int jj = threadIdx.x % Rp, g = threadIdx.x / Rp;
         float acc = 0.f;
-        for (int c = lane; c < C; c += 32) acc = fmaf(__ldg(W2 + static_cast<size_t>(c) * R + j), z2[c], acc);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-        if (lane == 0) {
+        if (g < G && jj < R)
+            for (int c = g; c < C; c += G) acc = fmaf(__ldg(W2 + static_cast<size_t>(c) * R + jj), z2[c], acc);
+        part[threadIdx.x] = acc;
+        __syncthreads();
+        if (threadIdx.x < R) {
+            float t = 0.f;
+            for (int q = 0; q < G; ++q) t += part[q * Rp + threadIdx.x];
+            const float v = h[static_cast<size_t>(n) * R + threadIdx.x] > 0.f ? t : 0.f;
+            z1[threadIdx.x] = v;
+            dz1_out[static_cast<size_t>(n) * R + threadIdx.x] = v;
+        }
+    } else {
+        for (int j = threadIdx.x; j < R; j += blockDim.x) {
+            float acc = 0.f;
+            for (int c = 0; c < C; ++c) acc = fmaf(__ldg(W2 + static_cast<size_t>(c) * R + j), z2[c], acc);
             const float v = h[static_cast<size_t>(n) * R + j] > 0.f ? acc : 0.f;
             z1[j] = v;
             dz1_out[static_cast<size_t>(n) * R + j] = v;

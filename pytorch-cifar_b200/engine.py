@@ -541,19 +541,22 @@ def resnext_spec(num_blocks=(3, 3, 3), cardinality=2, bottleneck_width=64, num_c
                 groups=groups, stem_ksize=1)
 
 
-REGNETX_CFG = {   # models/regnet.py:113-134 (the X variants: no squeeze-and-excitation)
-    "RegNetX_200MF": dict(depths=(1, 1, 4, 7), widths=(24, 56, 152, 368), strides=(1, 1, 2, 2), group_width=8),
-    "RegNetX_400MF": dict(depths=(1, 2, 7, 12), widths=(32, 64, 160, 384), strides=(1, 1, 2, 2), group_width=16),
+REGNET_CFG = {   # models/regnet.py:113-146
+    "RegNetX_200MF": dict(depths=(1, 1, 4, 7), widths=(24, 56, 152, 368), strides=(1, 1, 2, 2), group_width=8, se_ratio=0),
+    "RegNetX_400MF": dict(depths=(1, 2, 7, 12), widths=(32, 64, 160, 384), strides=(1, 1, 2, 2), group_width=16, se_ratio=0),
+    "RegNetY_400MF": dict(depths=(1, 2, 7, 12), widths=(32, 64, 160, 384), strides=(1, 1, 2, 2), group_width=16,
+                          se_ratio=0.25),
 }
 
 
 def regnetx_spec(name="RegNetX_200MF", num_classes=10):
-    """RegNetX as models/regnet.py:29-110 composes it (bottleneck_ratio 1, se_ratio 0): conv3x3 stem (3 -> 64) + BN +
+    """RegNetX / RegNetY as models/regnet.py:29-110 composes them (bottleneck_ratio 1): conv3x3 stem (3 -> 64) + BN +
     ReLU, four stages of `Block`s — conv1x1 -> BN -> ReLU -> grouped conv3x3 (groups = width / group_width, stride) ->
-    BN -> ReLU -> conv1x1 -> BN -> += shortcut (1x1 conv + BN where the shape changes) -> ReLU —,
-    adaptive_avg_pool2d(1) over the final 8x8 map, Linear(widths[-1], 10)."""
-    cfg = REGNETX_CFG[name]
-    params, buffers, blocks, groups = OrderedDict(), OrderedDict(), [], {}
+    BN -> ReLU -> [RegNetY: squeeze-and-excitation with round(w_in / 4) hidden units, regnet.py:42-45] -> conv1x1 -> BN
+    -> += shortcut (1x1 conv + BN where the shape changes) -> ReLU —, adaptive_avg_pool2d(1) over the final 8x8 map,
+    Linear(widths[-1], 10)."""
+    cfg = REGNET_CFG[name]
+    params, buffers, blocks, groups, se_fc = OrderedDict(), OrderedDict(), [], {}, set()
 
     def bn(bname, c):
         params[bname + ".weight"] = (c,)
@@ -573,22 +576,34 @@ def regnetx_spec(name="RegNetX_200MF", num_classes=10):
             if g > 1:
                 groups[bname + ".conv2.weight"] = g
             bn(bname + ".bn2", width)
+            se = 0
+            if cfg["se_ratio"] > 0:
+                se = int(round(cin * cfg["se_ratio"]))                   # regnet.py:44: w_in, not w_b
+                params[bname + ".se.se1.weight"] = (se, width, 1, 1)
+                params[bname + ".se.se1.bias"] = (se,)
+                params[bname + ".se.se2.weight"] = (width, se, 1, 1)
+                params[bname + ".se.se2.bias"] = (width,)
+                se_fc |= {bname + ".se.se1.weight", bname + ".se.se2.weight"}
             params[bname + ".conv3.weight"] = (width, width, 1, 1)
             bn(bname + ".bn3", width)
             shortcut = s != 1 or cin != width
             if shortcut:
                 params[bname + ".shortcut.0.weight"] = (width, cin, 1, 1)
                 bn(bname + ".shortcut.1", width)
-            blocks.append(dict(name=bname, cin=cin, planes=width, cout=width, stride=s, shortcut=shortcut))
+            blocks.append(dict(name=bname, cin=cin, planes=width, cout=width, stride=s, shortcut=shortcut, se=se))
             cin = width
     params["linear.weight"] = (num_classes, cin)
     params["linear.bias"] = (num_classes,)
     return dict(family="bottleneck", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes, feat=cin,
-                groups=groups)
+                groups=groups, se_fc=se_fc)
 
 
 def regnetx_400mf_spec(num_classes=10):
     return regnetx_spec("RegNetX_400MF", num_classes)
+
+
+def regnety_400mf_spec(num_classes=10):
+    return regnetx_spec("RegNetY_400MF", num_classes)
 
 
 def resnext29_32x4d_spec(num_classes=10):
@@ -1735,21 +1750,34 @@ class Engine:
             c2 = ConvUnit(self, name + ".conv2", name + ".bn2", a1, pl, pl, 3, s, H, W)
             Ho, Wo = H // s, W // s
             a2 = self.new_act(N, Ho, Wo, _pad64(pl))
-            c3 = ConvUnit(self, name + ".conv3", name + ".bn3", a2, pl, cout, 1, 1, Ho, Wo)
+            se = None
+            if b.get("se", 0):          # RegNetY: squeeze-and-excitation between relu(bn2(.)) and conv3 (regnet.py:60-61)
+                sn, ld, R = name + ".se", _pad64(pl), b["se"]
+                se = dict(R=R, hw=Ho * Wo, C=pl, ld=ld, out=self.new_act(N, Ho, Wo, ld),
+                          w1=self.param_view(sn + ".se1.weight"), b1=self.param_view(sn + ".se1.bias"),
+                          w2=self.param_view(sn + ".se2.weight"), b2=self.param_view(sn + ".se2.bias"),
+                          dw1=self.grad_view(sn + ".se1.weight"), db1=self.grad_view(sn + ".se1.bias"),
+                          dw2=self.grad_view(sn + ".se2.weight"), db2=self.grad_view(sn + ".se2.bias"),
+                          pooled=self.new_f32(N, ld), hidden=self.new_f32(N, R), scale=self.new_f32(N, ld),
+                          ds=self.new_f32(N * ld), dp=self.new_f32(N * ld), dz1=self.new_f32(N * R))
+            c3 = ConvUnit(self, name + ".conv3", name + ".bn3", se["out"] if se else a2, pl, cout, 1, 1, Ho, Wo)
             cs = ConvUnit(self, name + ".shortcut.0", name + ".shortcut.1", x, cin, cout, 1, s, H, W,
                           private_stats=True) if b["shortcut"] else None
             out = self.new_act(N, Ho, Wo, _pad64(cout))
             bits = torch.zeros(out.numel() // 8, dtype=torch.uint8, device=self.device) if RELU_BITS else None
             self.units += [c1, c2, c3] + ([cs] if cs else [])
-            blocks.append((c1, a1, c2, a2, c3, cs, out, x, bits))
+            blocks.append((c1, a1, c2, a2, c3, cs, out, x, bits, se))
 
-            def fwd(training, c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, x=x, bits=bits):
+            def fwd(training, c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, x=x, bits=bits, se=se):
                 if cs is not None:          # shortcut branch on the side stream (own statistics scratch)
                     self.run_side(lambda: (cs.fprop(self), None if (FUSED_FINALIZE and training) else cs.bn_stats(self, training)))
                 c1.fprop(self)
                 c1.bn_apply(self, training, a1)
                 c2.fprop(self)
                 c2.bn_apply(self, training, a2)
+                if se is not None:
+                    ops.se_fwd(a2, N, se["hw"], se["C"], se["ld"], se["R"], se["w1"], se["b1"], se["w2"], se["b2"],
+                               se["pooled"], se["hidden"], se["scale"], se["out"])
                 c3.fprop(self)
                 if cs is not None:
                     self.join_side()
@@ -1761,8 +1789,9 @@ class Engine:
         fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
         F.append(fwd_head)
         Bk = [bwd_head]
-        for (c1, a1, c2, a2, c3, cs, out, xin, bits) in reversed(blocks):
+        for (c1, a1, c2, a2, c3, cs, out, xin, bits, se) in reversed(blocks):
             dy3 = self.new_act(*c3.y.shape)
+            da2s = self.new_act(*a2.shape) if se is not None else None
             dys = self.new_act(*cs.y.shape) if cs is not None else None
             da2 = self.new_act(*a2.shape)
             dy2 = self.new_act(*c2.y.shape)
@@ -1771,12 +1800,18 @@ class Engine:
             dx = self.new_act(*xin.shape)
 
             def bwd(c1=c1, a1=a1, c2=c2, a2=a2, c3=c3, cs=cs, out=out, dout=dout, dy3=dy3, dys=dys, da2=da2,
-                    dy2=dy2, da1=da1, dy1=dy1, dx=dx, bits=bits):
+                    dy2=dy2, da1=da1, dy1=dy1, dx=dx, bits=bits, se=se, da2s=da2s):
                 c3.bn_backward(self, dout, out, dout, dy3, relu_bits=bits)      # mask in place -> dz
                 if cs is not None:
                     cs.bn_backward(self, dout, None, None, dys)
                 c3.wgrad(dy3)
-                if FUSE_DGRAD_BN:
+                if se is not None:          # conv3 read a2 * w: back through the excitation, then the plain BN backward
+                    c3.dgrad(dy3, da2s)
+                    ops.se_bwd(da2s, a2, N, se["hw"], se["C"], se["ld"], se["R"], se["w1"], se["w2"], se["pooled"],
+                               se["hidden"], se["scale"], se["ds"], se["dz1"], se["dp"], se["dw1"], se["db1"],
+                               se["dw2"], se["db2"], da2)
+                    c2.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
+                elif FUSE_DGRAD_BN:
                     c2.bn_backward_from_partial(self, da2, dy2, c3.dgrad_bn(self, dy3, da2, c2))
                 else:
                     c3.dgrad(dy3, da2)

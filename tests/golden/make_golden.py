@@ -98,7 +98,8 @@ def golden_resnext():
     for tag, ctor in (("resnext29_2x64d", ref_rx.ResNeXt29_2x64d), ("resnext29_32x4d", ref_rx.ResNeXt29_32x4d),
                       ("regnetx_200mf", ref_rg.RegNetX_200MF), ("regnetx_400mf", ref_rg.RegNetX_400MF),
                       ("dla", __import__("models.dla", fromlist=["x"]).DLA),
-                      ("senet18", __import__("models.senet", fromlist=["x"]).SENet18)):
+                      ("senet18", __import__("models.senet", fromlist=["x"]).SENet18),
+                      ("regnety_400mf", ref_rg.RegNetY_400MF)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

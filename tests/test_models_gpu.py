@@ -185,7 +185,8 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           # loss on this batch climbs from 3.3 to 12 for the 400MF network (ours follows it step for step,
           # profiles/r2_parity/train_curve_regnetx_400mf_lr0.02.json), so both train with lr 0.002 here, like ResNet-50
           "regnetx_200mf": dict(logits=0.12, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
-          "regnetx_400mf": dict(logits=0.12, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002)}
+          "regnetx_400mf": dict(logits=0.12, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
+          "regnety_400mf": dict(logits=0.12, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002)}
 
 MODELS = {
     "vgg16": ("vgg_spec", "build_vgg_params", "vgg_forward", "features.0", ["classifier.weight", "features.41.weight",
@@ -210,6 +211,8 @@ MODELS = {
     # DLA (models/dla.py): level-2 trees whose Root reads four tensors; two blocks read a tree's input
     "dla": ("dla_spec", "build_dla_params", "dla_forward", "base.0",
             ["linear.weight", "layer6.root.bn.weight", "layer6.root.bn.bias"]),
+    "regnety_400mf": ("regnety_400mf_spec", "build_regnety_400mf_params", "regnety_400mf_forward", "conv1",
+                      ["linear.weight", "layer4.11.bn3.weight", "layer4.11.bn3.bias"]),
     # SENet18 (models/senet.py): pre-activation blocks with squeeze-and-excitation
     "senet18": ("senet_spec", "build_senet_params", "senet_forward", "conv1",
                 ["linear.weight", "layer4.1.fc2.weight", "layer4.1.conv2.weight"]),

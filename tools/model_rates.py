@@ -11,7 +11,8 @@ MODELS = [("resnet18", "resnet_spec", 1024), ("vgg16", "vgg_spec", 1024), ("prea
           ("mobilenetv2", "mobilenetv2_spec", 512), ("resnet50", "resnet50_spec", 256), ("simpledla", "simple_dla_spec", 1024),
           ("mobilenet", "mobilenet_spec", 512), ("resnext29_2x64d", "resnext_spec", 512),
           ("regnetx_200mf", "regnetx_spec", 512), ("regnetx_400mf", "regnetx_400mf_spec", 512),
-          ("dla", "dla_spec", 1024), ("senet18", "senet_spec", 1024)]
+          ("dla", "dla_spec", 1024), ("senet18", "senet_spec", 1024),
+          ("regnety_400mf", "regnety_400mf_spec", 512)]
 steps, warm = 30, 5
 images, labels = data.synthetic_cifar(8192, seed=0)
 out = []
