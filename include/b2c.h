@@ -95,6 +95,14 @@ B2C_API int b2c_conv1x1_cat_fprop(const B2cConvDesc* d, const void* x0, const vo
 B2C_API int b2c_conv1x1_catn_fprop(const B2cConvDesc* d, const void* const* xs, int n_src, const void* w_fprop_n, void* y,
                            float* part_sum, float* part_sq, int* stat_rows, void* stream);
 
+/* The same over sources of DIFFERENT widths (cins: HOST array of n_src channel counts, each a multiple of 64 and at
+ * most d->cin): every 1x1 conv of an Inception module reads torch.cat([y1, y2, y3, y4], 1) of the previous one,
+ * models/googlenet.py:52-57. w_fprop_n is bf16 [n_src][cout][d->cin]: slab t holds source t's weights in its first
+ * cins[t] columns. */
+B2C_API int b2c_conv1x1_catr_fprop(const B2cConvDesc* d, const void* const* xs, const int* cins, int n_src,
+                           const void* w_fprop_n, void* y, float* part_sum, float* part_sq, int* stat_rows,
+                           void* stream);
+
 /* dx[n,h,w,cin] = conv_transpose(dy, w) (+ add_src). Replaces cudnn_convolution_backward_input reached
  * from loss.backward(), main.py:104. `w_dgrad` is bf16 [tap][cin][cout]. add_src (optional, bf16, dx's
  * shape) is added in the epilogue; for ksize==1 && stride==2 it must be NULL (dx is zero-filled first)
@@ -278,6 +286,21 @@ B2C_API int b2c_maxpool2x2_fwd(const void* x, void* y, int n, int h, int w, int 
 /* Its backward: dx[n,h,w,c] = dy of the window if x is the window's first maximum (torch's tie rule), else 0. */
 B2C_API int b2c_maxpool2x2_bwd(const void* x, const void* y, const void* dy, void* dx, int n, int h, int w, int channels,
                        void* stream);
+
+/* nn.MaxPool2d(3, stride, padding=1), models/googlenet.py:40 (stride 1, inside an Inception module) and :67 (stride 2,
+ * between stages), on NHWC bf16 [n,h,w,c] -> [n,h/stride,w/stride,c]; argmax (uint8, y's shape) receives the window
+ * position r*3+s of the first maximum in scan order (torch's tie rule) for the backward pass. */
+B2C_API int b2c_maxpool3x3_fwd(const void* x, void* y, void* argmax, int n, int h, int w, int channels, int stride,
+                       void* stream);
+/* dx[n,h,w,c] = (add, optional: another consumer's gradient of x) + the sum of dy over the windows whose maximum is
+ * this pixel. h, w are x's. */
+B2C_API int b2c_maxpool3x3_bwd(const void* dy, const void* argmax, const void* add, void* dx, int n, int h, int w, int channels,
+                       int stride, void* stream);
+/* dst[row][dst_off + c] = src[row][src_off + c] for c < channels (bf16; pitches, offsets and channels multiples of
+ * 8): torch.cat / its backward where a concatenation has to exist in memory — the input of GoogLeNet's
+ * avgpool + linear head, models/googlenet.py:96-98. */
+B2C_API int b2c_copy_channels(const void* src, int src_ld, int src_off, void* dst, int dst_ld, int dst_off, long long rows,
+                      int channels, void* stream);
 
 /* Head: F.avg_pool2d(out, 4) -> view -> nn.Linear, models/resnet.py:137-139. act is [n, hw, channels]
  * bf16; pooled [n, channels] and logits [n, classes] are fp32 outputs. */

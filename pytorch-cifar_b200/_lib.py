@@ -96,6 +96,11 @@ SIGNATURES = {
     "b2c_bn_bwd_stats_noalloc": [_P, _P, _P, _P, _LL, _I, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_head_fwd": [_P, _I, _I, _I, _P, _P, _I, _P, _P, _P],
     "b2c_ce_loss": [_P, _P, _I, _I, _P, _P, _P, _P],
+    "b2c_maxpool3x3_fwd": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
+    "b2c_maxpool3x3_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P],
+    "b2c_copy_channels": [_P, _I, _I, _P, _I, _I, _LL, _I, _P],
+    "b2c_conv1x1_catr_fprop": [ctypes.POINTER(ConvDesc), ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(_I), _I, _P, _P,
+                               _P, _P, ctypes.POINTER(_I), _P],
     "b2c_se_fwd": [_P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_se_bwd": [_P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b2c_head_fwd_ld": [_P, _I, _I, _I, _I, _P, _P, _I, _P, _P, _P],

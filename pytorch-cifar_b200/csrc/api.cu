@@ -279,7 +279,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
 }
 
 static int conv1x1_cat_impl(const B2cConvDesc* d, const void* const* xs, int n_src, const void* w_fprop, void* y,
-                            float* part_sum, float* part_sq, int* stat_rows, void* stream) {
+                            float* part_sum, float* part_sq, int* stat_rows, void* stream, const int* cins = nullptr) {
     int rc = check_conv(d);
     if (rc) return rc;
     if (d->ksize != 1 || d->stride != 1) return B2C_ERR_UNSUPPORTED;
@@ -289,6 +289,9 @@ static int conv1x1_cat_impl(const B2cConvDesc* d, const void* const* xs, int n_s
         if (!xs[t] || !aligned16(xs[t])) return B2C_ERR_ARG;
     if ((part_sum == nullptr) != (part_sq == nullptr)) return B2C_ERR_ARG;
     if (!grid_tiles(d->h, d->w, 128)) return B2C_ERR_UNSUPPORTED;
+    if (cins != nullptr)       // sources of different widths: each at most d->cin (the pitch of a weight slab)
+        for (int t = 0; t < n_src; ++t)
+            if (cins[t] < 64 || (cins[t] % 64) || cins[t] > d->cin || cins[t] / 64 > 255) return B2C_ERR_UNSUPPORTED;
     const long long m_tiles = (static_cast<long long>(d->n) * d->h * d->w + 127) / 128;
     const int bn = pick_bn(d->block_n, d->cout, 256, m_tiles);
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
@@ -308,6 +311,7 @@ static int conv1x1_cat_impl(const B2cConvDesc* d, const void* const* xs, int n_s
         p.tap_dw[t] = 0;
         p.tap_a[t] = static_cast<uint8_t>(t);
         p.tap_brow[t] = t * d->cout;
+        p.tap_kc[t] = cins != nullptr ? static_cast<uint8_t>(cins[t] / 64) : 0;
     }
     p.out = static_cast<__nv_bfloat16*>(y);
     p.out_H = d->h;
@@ -324,7 +328,8 @@ static int conv1x1_cat_impl(const B2cConvDesc* d, const void* const* xs, int n_s
     const int bnb = 128 / (d->w * bh);
     CUtensorMap ma[4], mb;
     for (int t = 0; t < 4; ++t) {
-        rc = encode_nhwc(&ma[t], xs[t < n_src ? t : n_src - 1], d->n, d->h, d->w, d->cin, d->w, bh, bnb, 1);
+        const int ts = t < n_src ? t : n_src - 1;
+        rc = encode_nhwc(&ma[t], xs[ts], d->n, d->h, d->w, cins != nullptr ? cins[ts] : d->cin, d->w, bh, bnb, 1);
         if (rc) return rc;
     }
     rc = encode_2d(&mb, w_fprop, static_cast<long long>(n_src) * d->cout, d->cin, bn);
@@ -344,6 +349,13 @@ int b2c_conv1x1_cat_fprop(const B2cConvDesc* d, const void* x0, const void* x1, 
 int b2c_conv1x1_catn_fprop(const B2cConvDesc* d, const void* const* xs, int n_src, const void* w_fprop_n, void* y,
                            float* part_sum, float* part_sq, int* stat_rows, void* stream) {
     return conv1x1_cat_impl(d, xs, n_src, w_fprop_n, y, part_sum, part_sq, stat_rows, stream);
+}
+
+int b2c_conv1x1_catr_fprop(const B2cConvDesc* d, const void* const* xs, const int* cins, int n_src,
+                           const void* w_fprop_n, void* y, float* part_sum, float* part_sq, int* stat_rows,
+                           void* stream) {
+    if (!cins) return B2C_ERR_ARG;
+    return conv1x1_cat_impl(d, xs, n_src, w_fprop_n, y, part_sum, part_sq, stat_rows, stream, cins);
 }
 
 static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_shortcut, const void* w_dgrad,
@@ -944,6 +956,35 @@ int b2c_se_bwd(const void* dout, const void* y, int n, int hw, int channels, int
     if (ld < channels || (ld & 7) || channels > 4096 || reduced > 1024) return B2C_ERR_UNSUPPORTED;
     return cuda_rc(b2c::launch_se_bwd(dout, y, ds_scratch, scale, hidden, pooled, n, hw, channels, reduced, ld, w1, w2,
                                       dz1_scratch, dp_scratch, dw1, db1, dw2, db2, dy, as_stream(stream)));
+}
+
+int b2c_maxpool3x3_fwd(const void* x, void* y, void* argmax, int n, int h, int w, int channels, int stride,
+                       void* stream) {
+    if (!x || !y || !argmax || n < 0 || h < 1 || w < 1 || !aligned16(x) || !aligned16(y) || !aligned16(argmax))
+        return B2C_ERR_ARG;
+    if ((channels & 7) || channels < 8 || (stride != 1 && stride != 2) || (h % stride) || (w % stride))
+        return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_maxpool3_fwd(x, y, argmax, n, h, w, channels, stride, as_stream(stream)));
+}
+
+int b2c_maxpool3x3_bwd(const void* dy, const void* argmax, const void* add, void* dx, int n, int h, int w, int channels,
+                       int stride, void* stream) {
+    if (!dy || !argmax || !dx || n < 0 || h < 1 || w < 1 || !aligned16(dy) || !aligned16(dx) || !aligned16(add) ||
+        !aligned16(argmax))
+        return B2C_ERR_ARG;
+    if ((channels & 7) || channels < 8 || (stride != 1 && stride != 2) || (h % stride) || (w % stride))
+        return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_maxpool3_bwd(dy, argmax, add, dx, n, h, w, channels, stride, as_stream(stream)));
+}
+
+int b2c_copy_channels(const void* src, int src_ld, int src_off, void* dst, int dst_ld, int dst_off, long long rows,
+                      int channels, void* stream) {
+    if (!src || !dst || rows < 0 || channels < 0 || !aligned16(src) || !aligned16(dst)) return B2C_ERR_ARG;
+    if (((src_ld | src_off | dst_ld | dst_off | channels) & 7) || src_off + channels > src_ld ||
+        dst_off + channels > dst_ld || src_off < 0 || dst_off < 0)
+        return B2C_ERR_UNSUPPORTED;
+    return cuda_rc(b2c::launch_copy_channels(src, src_ld, src_off, dst, dst_ld, dst_off, rows, channels,
+                                             as_stream(stream)));
 }
 
 int b2c_augment_nchw(const uint8_t* data, const long long* idx, const int8_t* ijf, float* out_nchw_f32, int n,

@@ -104,6 +104,13 @@ cudaError_t launch_se_scale(const void* y, const float* sc, const void* add, voi
 cudaError_t launch_se_bwd(const void* dout, const void* y, float* ds, const float* sc, const float* h, const float* p,
                           int N, int hw, int C, int R, int ld, const float* W1, const float* W2, float* dz1, float* dp,
                           float* dW1, float* db1, float* dW2, float* db2, void* dy, cudaStream_t s);
+// nn.MaxPool2d(3, stride, padding=1) and the channel-slice copy (pool3.cu)
+cudaError_t launch_maxpool3_fwd(const void* x, void* y, void* arg, int n, int h, int w, int C, int stride,
+                                cudaStream_t s);
+cudaError_t launch_maxpool3_bwd(const void* dy, const void* arg, const void* add, void* dx, int n, int h, int w, int C,
+                                int stride, cudaStream_t s);
+cudaError_t launch_copy_channels(const void* src, int src_ld, int src_off, void* dst, int dst_ld, int dst_off,
+                                 long long rows, int channels, cudaStream_t s);
 int bn_bwd_noalloc_max_channels();
 cudaError_t launch_bn_bwd_stats_noalloc(const void* dout, const void* act, const void* y, void* dz_out,
                                         long long rows, int C, float count, const float* gamma, const float* mean,

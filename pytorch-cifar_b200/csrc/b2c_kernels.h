@@ -24,6 +24,8 @@ struct TapGemmParams {
     int8_t tap_dw[kMaxTaps];
     uint8_t tap_a[kMaxTaps];   // which A tensor map the tap reads (0..3; the CTA-pair kernels take 0 or 1)
     int tap_brow[kMaxTaps];    // first row of the tap's weight slab in the B matrix
+    uint8_t tap_kc[kMaxTaps];  // 64-channel chunks of THIS tap's reduction; 0 = k_chunks (single-CTA kernel only: the
+                               // 1x1 conv over a concatenation of tensors of different widths)
     // Output phases (stride-2 dgrad): a tile belongs to one phase = a sub-range of the tap list and an output
     // pixel offset. num_phases == 1 for everything else (phase_begin = {0, num_taps}).
     int num_phases;

@@ -126,7 +126,8 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
                     const int cw = p.tap_dw[t];
                     const int ch = h0 * p.in_stride + p.tap_dh[t];
                     const int brow = p.tap_brow[t] + n_tile * BN;
-                    for (int kc = 0; kc < p.k_chunks; ++kc) {
+                    const int nk = p.tap_kc[t] != 0 ? p.tap_kc[t] : p.k_chunks;
+                    for (int kc = 0; kc < nk; ++kc) {
                         mbar_wait(&empty[stage], phase ^ 1u, 1);
                         if (elect_one_sync()) {
                             mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
@@ -157,7 +158,9 @@ tap_gemm_kernel(const __grid_constant__ CUtensorMap mapA0, const __grid_constant
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
                 int m_tile, n_tile, ph;
                 decode(tile, m_tile, n_tile, ph);
-                const int k_iters = (p.phase_begin[ph + 1] - p.phase_begin[ph]) * p.k_chunks;
+                int k_iters = 0;
+                for (int t = p.phase_begin[ph]; t < p.phase_begin[ph + 1]; ++t)
+                    k_iters += p.tap_kc[t] != 0 ? p.tap_kc[t] : p.k_chunks;
                 mbar_wait(&tempty[acc], acc_phase ^ 1u, 2);
                 tc_fence_after();
                 const uint32_t d = tmem_base + static_cast<uint32_t>(acc * BN);

@@ -85,6 +85,49 @@ def conv1x1_catn_fprop(d, xs, w_fprop_n, y, part_sum=None, part_sq=None):
     return rows.value
 
 
+def conv1x1_catr_fprop(d, xs, w_fprop_n, y, part_sum=None, part_sq=None):
+    """y = conv1x1(cat(xs, C)) for 2..4 sources of different (padded) widths xs[t].shape[-1] <= d.cin;
+    w_fprop_n is [len(xs)][cout][d.cin], slab t filled in its first xs[t].shape[-1] columns."""
+    lib = _lib.load()
+    for t in xs:
+        _need(t, torch.bfloat16, "x")
+    _need(w_fprop_n, torch.bfloat16, "w"); _need(y, torch.bfloat16, "y")
+    _need(part_sum, torch.float32, "part_sum"); _need(part_sq, torch.float32, "part_sq")
+    ptrs = (ctypes.c_void_p * len(xs))(*[t.data_ptr() for t in xs])
+    cins = (ctypes.c_int * len(xs))(*[t.shape[-1] for t in xs])
+    rows = ctypes.c_int(0)
+    check(lib.b2c_conv1x1_catr_fprop(ctypes.byref(d), ptrs, cins, len(xs), _p(w_fprop_n), _p(y), _p(part_sum),
+                                     _p(part_sq), ctypes.byref(rows), _stream()), "b2c_conv1x1_catr_fprop")
+    return rows.value
+
+
+def maxpool3x3_fwd(x, y, argmax, stride):
+    lib = _lib.load()
+    n, h, w, c = x.shape
+    _need(x, torch.bfloat16, "x"); _need(y, torch.bfloat16, "y"); _need(argmax, torch.uint8, "argmax")
+    check(lib.b2c_maxpool3x3_fwd(_p(x), _p(y), _p(argmax), n, h, w, c, stride, _stream()), "b2c_maxpool3x3_fwd")
+
+
+def maxpool3x3_bwd(dy, argmax, dx, stride, add=None):
+    lib = _lib.load()
+    n, h, w, c = dx.shape
+    _need(dy, torch.bfloat16, "dy"); _need(dx, torch.bfloat16, "dx"); _need(argmax, torch.uint8, "argmax")
+    _need(add, torch.bfloat16, "add")
+    check(lib.b2c_maxpool3x3_bwd(_p(dy), _p(argmax), _p(add), _p(dx), n, h, w, c, stride, _stream()),
+          "b2c_maxpool3x3_bwd")
+
+
+def copy_channels(src, src_off, dst, dst_off, channels):
+    """dst[..., dst_off:dst_off+channels] = src[..., src_off:src_off+channels] over all rows (b2c_copy_channels)."""
+    lib = _lib.load()
+    _need(src, torch.bfloat16, "src"); _need(dst, torch.bfloat16, "dst")
+    rows = src.numel() // src.shape[-1]
+    if rows != dst.numel() // dst.shape[-1]:
+        raise ValueError("copy_channels: row counts differ")
+    check(lib.b2c_copy_channels(_p(src), src.shape[-1], src_off, _p(dst), dst.shape[-1], dst_off, rows, channels,
+                                _stream()), "b2c_copy_channels")
+
+
 def conv_dgrad(d, dy, w_dgrad, dx, add_src=None):
     lib = _lib.load()
     _need(dy, torch.bfloat16, "dy"); _need(w_dgrad, torch.bfloat16, "w"); _need(dx, torch.bfloat16, "dx")

@@ -1081,3 +1081,68 @@ def test_round2_kernels_write_only_their_outputs(ops):
     torch.cuda.synchronize()
     assert _guards_intact(whole, pad, S) and _guards_intact(whole2, pad2, S) and torch.equal(out, out2)
     assert rel_err(out.float(), F.relu(F.batch_norm(yv.float(), None, None, training=True))) < BF16_TOL
+
+
+@pytest.mark.parametrize("shape", [(5, 32, 32, 64, 1), (3, 16, 16, 192, 1), (7, 8, 8, 128, 1), (4, 32, 32, 64, 2),
+                                   (6, 16, 16, 320, 2), (2, 4, 4, 8, 1)])
+def test_maxpool3x3(ops, shape):
+    """b2c_maxpool3x3_fwd / _bwd = nn.MaxPool2d(3, stride, padding=1) (models/googlenet.py:40,67): identical outputs and
+    input gradients on identical bf16 inputs, ties (many after a ReLU) resolved like torch; the optional `add`."""
+    n, h, w, c, stride = shape
+    g = torch.Generator(device="cuda").manual_seed(160)
+    x = torch.randn(n, h, w, c, device="cuda", generator=g).clamp_min(0).to(torch.bfloat16)       # many ties at 0
+    ho, wo = h // stride, w // stride
+    _, y, _ = _guarded((n, ho, wo, c), torch.bfloat16, 3.0)
+    arg = torch.empty(n, ho, wo, c, device="cuda", dtype=torch.uint8)
+    ops.maxpool3x3_fwd(x, y, arg, stride)
+    xr = to_nchw(x).requires_grad_()
+    yr = F.max_pool2d(xr, 3, stride, 1)
+    dy = nhwc_bf16(n, ho, wo, c, 161)
+    yr.backward(to_nchw(dy))
+    add = nhwc_bf16(n, h, w, c, 162)
+    whole, dx, pad = _guarded((n, h, w, c), torch.bfloat16, 3.0)
+    ops.maxpool3x3_bwd(dy, arg, dx, stride)
+    dx2 = torch.empty_like(dx)
+    ops.maxpool3x3_bwd(dy, arg, dx2, stride, add=add)
+    torch.cuda.synchronize()
+    assert torch.equal(to_nchw(y), yr.detach())
+    assert _guards_intact(whole, pad, 3.0)
+    # sums of up to 9 bf16 values are rounded once here and accumulated in fp32 by torch: compare at bf16 resolution
+    assert rel_err(to_nchw(dx), xr.grad) < 3e-3 and (to_nchw(dx) != 0).eq(xr.grad != 0).all()
+    assert rel_err(to_nchw(dx2), xr.grad + to_nchw(add)) < 3e-3
+
+
+def test_copy_channels(ops):
+    g = torch.Generator(device="cuda").manual_seed(163)
+    src = torch.randn(37, 8, 192, device="cuda", generator=g).to(torch.bfloat16)
+    whole, dst, pad = _guarded((37, 8, 320), torch.bfloat16, 9.0)
+    dst.fill_(1.0)
+    ops.copy_channels(src, 64, dst, 200, 104)
+    torch.cuda.synchronize()
+    assert _guards_intact(whole, pad, 9.0)
+    assert torch.equal(dst[..., 200:304], src[..., 64:168]) and (dst[..., :200] == 1).all() and (dst[..., 304:] == 1).all()
+
+
+@pytest.mark.parametrize("shape", [(6, 16, 16, (64, 128, 64, 64), 128), (5, 8, 8, (384, 192, 64, 128), 256),
+                                   (3, 32, 32, (64, 128), 64), (130, 8, 8, (256, 320, 128, 128), 384)])
+def test_conv1x1_over_a_concat_of_different_widths(ops, shape):
+    """b2c_conv1x1_catr_fprop: the 1x1 convs of an Inception module over torch.cat([y1, y2, y3, y4], 1) of the previous
+    one (models/googlenet.py:52-57), every source through its own tensor map with its own number of K chunks."""
+    n, h, w, cs, cout = shape
+    xs = [nhwc_bf16(n, h, w, c, 170 + t) for t, c in enumerate(cs)]
+    wt = weight(cout, sum(cs), 1, 175)
+    ref = F.conv2d(torch.cat([to_nchw(x) for x in xs], 1), wt)
+    cmax = max(cs)
+    wn = torch.zeros(len(cs), cout, cmax, device="cuda", dtype=torch.bfloat16)
+    off = 0
+    for t, c in enumerate(cs):
+        wn[t, :, :c] = wt[:, off:off + c, 0, 0].to(torch.bfloat16)
+        off += c
+    whole, y, pad = _guarded((n, h, w, cout), torch.bfloat16, 555.0)
+    ps = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    pq = torch.zeros(ops.MAX_STAT_ROWS, cout, device="cuda")
+    rows = ops.conv1x1_catr_fprop(ops.conv_desc(n, h, w, cmax, cout, 1, 1), xs, wn, y, ps, pq)
+    torch.cuda.synchronize()
+    assert _guards_intact(whole, pad, 555.0)
+    assert torch.isfinite(to_nchw(y)).all() and rel_err(to_nchw(y), ref) < BF16_TOL
+    assert rel_err(pq[:rows].sum(0), (ref * ref).sum((0, 2, 3))) < F32_TOL

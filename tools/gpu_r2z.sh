@@ -1,0 +1,7 @@
+#!/bin/bash
+mkdir -p gpurun_out
+cd "$(dirname "$0")/.."
+timeout 900 python -m pytest tests/test_kernels_gpu.py -x -q -m gpu -p no:cacheprovider \
+  -k "maxpool3x3 or copy_channels or concat" > gpurun_out/r2z_tests.log 2>&1
+echo "tests rc=$?"; tail -30 gpurun_out/r2z_tests.log | cut -c1-600
+echo ALLDONE
