@@ -888,3 +888,70 @@ def build_regnety_400mf_params(seed):
 
 def regnety_400mf_forward(x, params, buffers, training=True, taps=None):
     return regnetx_forward(x, params, buffers, training, "RegNetY_400MF", taps)
+
+
+# ------------------------------------------------------------------------------------------------
+# GoogLeNet (models/googlenet.py)
+# ------------------------------------------------------------------------------------------------
+GOOGLENET_CFG = [("a3", 192, 64, 96, 128, 16, 32, 32), ("b3", 256, 128, 128, 192, 32, 96, 64), "maxpool",
+                 ("a4", 480, 192, 96, 208, 16, 48, 64), ("b4", 512, 160, 112, 224, 24, 64, 64),
+                 ("c4", 512, 128, 128, 256, 24, 64, 64), ("d4", 512, 112, 144, 288, 32, 64, 64),
+                 ("e4", 528, 256, 160, 320, 32, 128, 128), "maxpool",
+                 ("a5", 832, 256, 160, 320, 32, 128, 128), ("b5", 832, 384, 192, 384, 48, 128, 128)]   # googlenet.py:64-78
+
+
+def build_googlenet_params(seed):
+    """Seeded parameters equal to `torch.manual_seed(seed); models.googlenet.GoogLeNet()`: pre_layers, then per
+    Inception (googlenet.py:8-47) the branches b1, b2, b3, b4 in order, every conv WITH bias; Linear last."""
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv_bn(cname, bname, cin, cout, k):
+        m = nn.Conv2d(cin, cout, kernel_size=k, padding=k // 2)
+        params[cname + ".weight"] = m.weight.detach().clone()
+        params[cname + ".bias"] = m.bias.detach().clone()
+        b = nn.BatchNorm2d(cout)
+        params[bname + ".weight"] = b.weight.detach().clone()
+        params[bname + ".bias"] = b.bias.detach().clone()
+        buffers[bname + ".running_mean"] = b.running_mean.clone()
+        buffers[bname + ".running_var"] = b.running_var.clone()
+        buffers[bname + ".num_batches_tracked"] = b.num_batches_tracked.clone()
+
+    conv_bn("pre_layers.0", "pre_layers.1", 3, 192, 3)
+    for m in GOOGLENET_CFG:
+        if m == "maxpool":
+            continue
+        name, cin, n1, n3r, n3, n5r, n5, npool = m
+        conv_bn(name + ".b1.0", name + ".b1.1", cin, n1, 1)
+        conv_bn(name + ".b2.0", name + ".b2.1", cin, n3r, 1)
+        conv_bn(name + ".b2.3", name + ".b2.4", n3r, n3, 3)
+        conv_bn(name + ".b3.0", name + ".b3.1", cin, n5r, 1)
+        conv_bn(name + ".b3.3", name + ".b3.4", n5r, n5, 3)
+        conv_bn(name + ".b3.6", name + ".b3.7", n5, n5, 3)
+        conv_bn(name + ".b4.1", name + ".b4.2", cin, npool, 1)
+    lin = nn.Linear(1024, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def googlenet_forward(x, params, buffers, training=True, taps=None):
+    def cbr(t, cname, bname, k):
+        y = F.conv2d(t, params[cname + ".weight"], params[cname + ".bias"], padding=k // 2)
+        if taps is not None:
+            taps[cname] = y
+        return F.relu(_bn(y, bname, params, buffers, training))
+    out = cbr(x, "pre_layers.0", "pre_layers.1", 3)                                   # googlenet.py:82
+    for m in GOOGLENET_CFG:
+        if m == "maxpool":
+            out = F.max_pool2d(out, 3, stride=2, padding=1)                           # :85, :91
+            continue
+        name = m[0]
+        y1 = cbr(out, name + ".b1.0", name + ".b1.1", 1)                              # :53
+        y2 = cbr(cbr(out, name + ".b2.0", name + ".b2.1", 1), name + ".b2.3", name + ".b2.4", 3)     # :54
+        y3 = cbr(cbr(cbr(out, name + ".b3.0", name + ".b3.1", 1), name + ".b3.3", name + ".b3.4", 3),
+                 name + ".b3.6", name + ".b3.7", 3)                                   # :55
+        y4 = cbr(F.max_pool2d(out, 3, stride=1, padding=1), name + ".b4.1", name + ".b4.2", 1)        # :56
+        out = torch.cat([y1, y2, y3, y4], 1)                                          # :57
+    out = F.avg_pool2d(out, 8, stride=1).view(out.size(0), -1)                        # :94-95
+    return F.linear(out, params["linear.weight"], params["linear.bias"])

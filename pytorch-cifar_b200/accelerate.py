@@ -11,7 +11,7 @@ names, shapes, dtypes, so checkpoints round-trip: main.py:77-84,138-148); `.grad
 are views of the gradient arena, so optim.SGD, DDP's reducer hooks and GradScaler-free scripts work unchanged.
 Supported compositions: ResNet with BasicBlock or Bottleneck (models/resnet.py), VGG (models/vgg.py), PreActResNet with
 PreActBlock (models/preact_resnet.py), MobileNetV2 (models/mobilenetv2.py), MobileNet (models/mobilenet.py), SimpleDLA (models/dla_simple.py), ResNeXt
-(models/resnext.py, grouped convs), RegNetX / RegNetY (models/regnet.py), DLA (models/dla.py), SENet18 (models/senet.py); anything else raises — there is no fallback path.
+(models/resnext.py, grouped convs), RegNetX / RegNetY (models/regnet.py), DLA (models/dla.py), SENet18 (models/senet.py), GoogLeNet (models/googlenet.py); anything else raises — there is no fallback path.
 
 Recognition is structural (attribute names and layer shapes), not by import path: `from models import *`
 shadows class names across files and the reference tree may sit anywhere on sys.path.
@@ -22,7 +22,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
-from .engine import (Engine, dla_spec, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, regnetx_spec, resnet_spec,
+from .engine import (Engine, dla_spec, googlenet_spec, mobilenet_spec, mobilenetv2_spec, plan_grad_buckets, preact_resnet_spec, regnetx_spec, resnet_spec,
                      resnext_spec, senet_spec, simple_dla_spec, vgg_spec, REGNET_CFG, VGG_CFG)
 
 
@@ -58,6 +58,8 @@ def spec_from_module(net):
         if not all(_is(b, "PreActBlock") and hasattr(b, "fc1") for i in range(1, 5) for b in getattr(net, f"layer{i}")):
             raise NotImplementedError("accelerate: only SENets of PreActBlocks (SENet18) are supported")
         return senet_spec(tuple(blocks), num_classes=net.linear.out_features)
+    if _is(net, "GoogLeNet") and hasattr(net, "pre_layers") and hasattr(net, "b5") and _is(net.a3, "Inception"):
+        return googlenet_spec(num_classes=net.linear.out_features)
     if _is(net, "PreActResNet") and hasattr(net, "layer4"):
         blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
         if not all(_is(b, "PreActBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):

@@ -263,6 +263,54 @@ def senet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=
                 se_fc=se_fc)
 
 
+GOOGLENET_CFG = [   # (name, in_planes, n1x1, n3x3red, n3x3, n5x5red, n5x5, pool_planes), models/googlenet.py:64-78
+    ("a3", 192, 64, 96, 128, 16, 32, 32), ("b3", 256, 128, 128, 192, 32, 96, 64), "maxpool",
+    ("a4", 480, 192, 96, 208, 16, 48, 64), ("b4", 512, 160, 112, 224, 24, 64, 64), ("c4", 512, 128, 128, 256, 24, 64, 64),
+    ("d4", 512, 112, 144, 288, 32, 64, 64), ("e4", 528, 256, 160, 320, 32, 128, 128), "maxpool",
+    ("a5", 832, 256, 160, 320, 32, 128, 128), ("b5", 832, 384, 192, 384, 48, 128, 128)]
+
+
+def googlenet_spec(num_classes=10):
+    """GoogLeNet as models/googlenet.py:7-99 composes it: conv3x3(3 -> 192, bias) + BN + ReLU, nine Inception modules —
+    four branches (1x1; 1x1 -> 3x3; 1x1 -> 3x3 -> 3x3; MaxPool(3, 1, 1) -> 1x1), every conv with a bias and followed by
+    BN + ReLU, outputs concatenated along the channels — with MaxPool(3, 2, 1) between the stages, AvgPool(8),
+    Linear(1024, 10). The concatenation is never written: `cat_src` lists, for each 1x1 conv that reads one, the widths
+    of the tensors it is made of (the four branch outputs of the module before)."""
+    params, buffers, modules, cat_src = OrderedDict(), OrderedDict(), [], {}
+
+    def conv_bn(cname, bname, cout, cin, k):
+        params[cname + ".weight"] = (cout, cin, k, k)
+        params[cname + ".bias"] = (cout,)
+        params[bname + ".weight"] = (cout,)
+        params[bname + ".bias"] = (cout,)
+        buffers[bname + ".running_mean"] = (cout,)
+        buffers[bname + ".running_var"] = (cout,)
+
+    conv_bn("pre_layers.0", "pre_layers.1", 192, 3, 3)
+    src = [192]
+    for m in GOOGLENET_CFG:
+        if m == "maxpool":
+            modules.append("maxpool")
+            continue
+        name, cin, n1, n3r, n3, n5r, n5, npool = m
+        assert cin == sum(src), name
+        conv_bn(name + ".b1.0", name + ".b1.1", n1, cin, 1)
+        conv_bn(name + ".b2.0", name + ".b2.1", n3r, cin, 1)
+        conv_bn(name + ".b2.3", name + ".b2.4", n3, n3r, 3)
+        conv_bn(name + ".b3.0", name + ".b3.1", n5r, cin, 1)
+        conv_bn(name + ".b3.3", name + ".b3.4", n5, n5r, 3)
+        conv_bn(name + ".b3.6", name + ".b3.7", n5, n5, 3)
+        conv_bn(name + ".b4.1", name + ".b4.2", npool, cin, 1)
+        for c in (".b1.0", ".b2.0", ".b3.0", ".b4.1"):
+            cat_src[name + c + ".weight"] = list(src)
+        modules.append(dict(name=name, n1=n1, n3r=n3r, n3=n3, n5r=n5r, n5=n5, npool=npool))
+        src = [n1, n3, n5, npool]
+    params["linear.weight"] = (num_classes, sum(src))
+    params["linear.bias"] = (num_classes,)
+    return dict(family="googlenet", params=params, buffers=buffers, modules=modules, num_classes=num_classes,
+                feat=sum(src), cat_src=cat_src)
+
+
 def dla_spec(num_classes=10):
     """DLA as models/dla.py:53-125 composes it: the three plain conv layers of SimpleDLA, then trees whose level-2
     form (layer4, layer5) is  xs = [prev_root(x)]; x = level_1(x); x = left_node(x); x = right_node(x);
@@ -377,9 +425,9 @@ def backward_groups(spec):
     first_conv = next(n for n, sh in spec["params"].items() if len(sh) == 4)[:-len(".weight")]
 
     def key(name):
-        if spec["family"] == "dla":          # one backward op per top-level layer (a whole aggregation tree)
+        if spec["family"] in ("dla", "googlenet"):   # one backward op per top-level layer (a tree / an Inception module)
             top = name.split(".")[0]
-            return "head" if top == "linear" else ("stem" if top == "base" else top)
+            return "head" if top == "linear" else ("stem" if top in ("base", "pre_layers") else top)
         if name.startswith("layer"):
             return ".".join(name.split(".")[:2])
         if name.startswith("features."):
@@ -852,6 +900,50 @@ class RootUnit(_BNOps):
         ops.conv_dgrad(self.desc_d, dy, self.wd[t], dx, add_src)
 
 
+class CatConvUnit(_BNOps):
+    """1x1 conv (+ bias, cancelled by the BatchNorm) + BN over torch.cat(xs, 1) of tensors of different widths — the
+    branch-entry convs of an Inception module (models/googlenet.py:11-15,18-21,28-31,42-44). Forward: one GEMM whose K
+    axis runs through the sources' own tensor maps; each source's data gradient is a 1x1 dgrad with its own weight
+    slab, each weight-gradient slab a 1x1 wgrad of its own source. With one source it is an ordinary 1x1 conv."""
+
+    def __init__(self, eng, name, bn_name, xs, cs, cout, H, W):
+        N = eng.N
+        self.name, self.xs, self.cs, self.H, self.W = name, list(xs), list(cs), H, W
+        self.cout_true, self.cout = cout, _pad64(cout)
+        self.rows = N * H * W
+        self.y = eng.new_act(N, H, W, self.cout)
+        cmax = max(x.shape[-1] for x in xs)
+        self.desc = ops.conv_desc(N, H, W, cmax, self.cout, 1, 1, flags=512 if FUSED_FINALIZE else 0)
+        self.desc_d = [ops.conv_desc(N, H, W, x.shape[-1], self.cout, 1, 1, flags=128 if CTA_PAIR == "all" else 0)
+                       for x in xs]
+        self.desc_w = [ops.conv_desc(N, H, W, x.shape[-1], self.cout, 1, 1, cin_valid=c, cout_valid=cout, flags=32)
+                       for x, c in zip(xs, cs)]
+        self.ps, self.pq = eng.part_sum, eng.part_sq
+        self.fsum = eng.new_stat(2 * self.cout, forward=True)
+        self.wf = eng.wf_view(name)                              # [n][cout_p][max padded c]
+        self.wd = eng.wd_slab_views(name)                        # n x [1][padded c_i][cout_p]
+        dw, self.dw, row = eng.grad_flat(name + ".weight"), [], 0            # stored [sum c_i][cout]
+        for c in cs:
+            self.dw.append(dw[row * cout:(row + c) * cout])
+            row += c
+        self.conv_bias = eng.param_view(name + ".bias") if (name + ".bias") in eng.p_off else None
+        self.eng = eng
+        _bn_views(self, eng, bn_name, self.cout)
+
+    def fprop(self, eng):
+        ps, pq = (self.fsum[:self.cout], self.fsum[self.cout:]) if FUSED_FINALIZE else (self.ps, self.pq)
+        if len(self.xs) == 1:
+            self.stat_rows = ops.conv_fprop(self.desc, self.xs[0], self.wf, self.y, ps, pq)
+        else:
+            self.stat_rows = ops.conv1x1_catr_fprop(self.desc, self.xs, self.wf, self.y, ps, pq)
+
+    def wgrad(self, dy):
+        self.eng.run_side(lambda: [ops.conv_wgrad(d, x, dy, dw) for d, x, dw in zip(self.desc_w, self.xs, self.dw)])
+
+    def dgrad(self, dy, t, dx, add_src=None):
+        ops.conv_dgrad(self.desc_d[t], dy, self.wd[t], dx, add_src)
+
+
 class DwUnit(_BNOps):
     """Depthwise 3x3 conv + BatchNorm (models/mobilenetv2.py:20-21)."""
 
@@ -944,6 +1036,8 @@ class Engine:
             self._build_mobilenet()
         elif spec["family"] == "senet":
             self._build_senet()
+        elif spec["family"] == "googlenet":
+            self._build_googlenet()
         else:
             raise NotImplementedError(spec["family"])
 
@@ -974,6 +1068,7 @@ class Engine:
             if len(shape) == 4 and name not in not_conv and name not in grouped and shape[1] != 3
             and shape[0] % 4 == 0 and shape[1] % 2 == 0}
         self.wd_pair = {}      # 3x3 stride-2 conv1 -> its block's 1x1 shortcut conv, stored right behind it in WD
+        self.wd_slabs = {}     # 1x1 conv over a ragged concatenation -> [(offset, shape)] of its per-source dgrad operands
         wf_n = wd_n = 0
         convs = [(name, shape) for name, shape in spec["params"].items() if len(shape) == 4 and name not in not_conv]
         # A down-sampling block's `conv1` (3x3) and `shortcut.0` (1x1) read the same input and have the same
@@ -996,7 +1091,24 @@ class Engine:
             cout, cin, k, _ = shape
             cout_p, cin_p = _pad64(cout), _pad64(cin)
             poff = self.p_off[name][0]
-            if name in spec.get("catn", ()):
+            if name in spec.get("cat_src", ()):
+                # 1x1 conv over a concatenation of tensors of different widths (models/googlenet.py:52-57): the master
+                # [1][sum c_i][cout] is one slab of c_i rows per source. fprop operand: [n][cout][max padded c_i], slab i
+                # filled in its first c_i columns (b2c_conv1x1_catr_fprop); dgrad operands: one [padded c_i][cout] each
+                cs = spec["cat_src"][name]
+                assert name in self.tco and k == 1 and sum(cs) == cin, name
+                cmax_p = max(_pad64(c) for c in cs)
+                self.wf_off[cname] = (wf_n, (len(cs), cout_p, cmax_p))
+                self.wd_slabs[cname] = []
+                row = 0
+                for i, c in enumerate(cs):
+                    self.wd_slabs[cname].append((wd_n, (1, _pad64(c), cout_p)))
+                    entries.append(dict(src_off=poff + row * cout, wf_off=wf_n + i * cout_p * cmax_p, wd_off=wd_n,
+                                        cout=cout, cin=c, taps=1, cin_pad=cmax_p, cout_pad=cout_p, kflat=2))
+                    wd_n += _pad64(c) * cout_p
+                    row += c
+                wf_n += len(cs) * cout_p * cmax_p
+            elif name in spec.get("catn", ()):
                 # Root conv over cat(xs) (models/dla_simple.py:52-54, models/dla.py:47-50): the [1][n*C][cout] master IS
                 # [n][C][cout], so the operands are those of an n-tap conv with C input channels
                 # (b2c_conv1x1_cat_fprop / b2c_conv1x1_catn_fprop)
@@ -1099,6 +1211,9 @@ class Engine:
         off, shape = self.wf_off[cname]
         n = shape[0] * shape[1] * shape[2]
         return self.WF[off:off + n].view(shape)
+
+    def wd_slab_views(self, cname):
+        return [self.WD[off:off + sh[0] * sh[1] * sh[2]].view(sh) for off, sh in self.wd_slabs[cname]]
 
     def wd_view(self, cname):
         off, shape = self.wd_off[cname]
@@ -1722,6 +1837,172 @@ class Engine:
 
         def bwd_stem(dout=dout):
             stem.bn_backward(self, dout, a0, dout, dy0, relu_from_y=True)
+            stem.wgrad(dy0)
+        Bk.append(bwd_stem)
+        self.bwd_ops = Bk
+
+    # ------------------------------------------------------------------ GoogLeNet plan (models/googlenet.py)
+    def _build_googlenet(self):
+        """A module's output is the LIST of its four branch outputs; the next module's 1x1 convs read the list through
+        one tensor map per tensor (CatConvUnit), its pool branch max-pools each tensor on its own, and each tensor's
+        gradient is the sum of what the four consumers send back (first writer plain, the others accumulate).
+        MaxPool(3, 2, 1) between stages pools every tensor of the list; only the head, which averages the whole 8x8 map
+        into Linear(1024, 10), sees a materialised concatenation (b2c_copy_channels)."""
+        spec, N = self.spec, self.N
+        self.x0 = self.new_act(N, 32, 32, 64)
+        stem = ConvUnit(self, "pre_layers.0", "pre_layers.1", self.x0, 3, 192, 3, 1, 32, 32, stem=True)
+        a0 = self.new_act(N, 32, 32, 192)
+        self.units = [stem]
+        F = self.fwd_ops
+        eng = self
+
+        def u8(t):
+            return torch.zeros(t.shape, dtype=torch.uint8, device=self.device)
+
+        class Inception:
+            def __init__(I, d, srcs, H, W):
+                name = d["name"]
+                I.H, I.W = H, W
+                I.xs, I.cs = [t for t, _ in srcs], [c for _, c in srcs]
+                act = lambda c: eng.new_act(N, H, W, _pad64(c))
+                I.b1 = CatConvUnit(eng, name + ".b1.0", name + ".b1.1", I.xs, I.cs, d["n1"], H, W)
+                I.y1 = act(d["n1"])
+                I.b2r = CatConvUnit(eng, name + ".b2.0", name + ".b2.1", I.xs, I.cs, d["n3r"], H, W)
+                I.a2r = act(d["n3r"])
+                I.b2 = ConvUnit(eng, name + ".b2.3", name + ".b2.4", I.a2r, d["n3r"], d["n3"], 3, 1, H, W)
+                I.y2 = act(d["n3"])
+                I.b3r = CatConvUnit(eng, name + ".b3.0", name + ".b3.1", I.xs, I.cs, d["n5r"], H, W)
+                I.a3r = act(d["n5r"])
+                I.b3a = ConvUnit(eng, name + ".b3.3", name + ".b3.4", I.a3r, d["n5r"], d["n5"], 3, 1, H, W)
+                I.a3a = act(d["n5"])
+                I.b3b = ConvUnit(eng, name + ".b3.6", name + ".b3.7", I.a3a, d["n5"], d["n5"], 3, 1, H, W)
+                I.y3 = act(d["n5"])
+                I.mp = [(eng.new_act(*x.shape), u8(x)) for x in I.xs]
+                I.b4 = CatConvUnit(eng, name + ".b4.1", name + ".b4.2", [m for m, _ in I.mp], I.cs, d["npool"], H, W)
+                I.y4 = act(d["npool"])
+                I.out = [(I.y1, d["n1"]), (I.y2, d["n3"]), (I.y3, d["n5"]), (I.y4, d["npool"])]
+                eng.units += [I.b1, I.b2r, I.b2, I.b3r, I.b3a, I.b3b, I.b4]
+
+            def fwd(I, training):
+                for unit, out in ((I.b1, I.y1), (I.b2r, I.a2r), (I.b2, I.y2), (I.b3r, I.a3r), (I.b3a, I.a3a),
+                                  (I.b3b, I.y3)):
+                    unit.fprop(eng)
+                    unit.bn_apply(eng, training, out)
+                for x, (m, arg) in zip(I.xs, I.mp):
+                    ops.maxpool3x3_fwd(x, m, arg, 1)
+                I.b4.fprop(eng)
+                I.b4.bn_apply(eng, training, I.y4)
+
+            def plan_bwd(I, gouts, ops_list, after=None):
+                """gouts: gradient buffers of y1..y4. Appends the module's backward; returns the gradient buffers of
+                its input tensors. after: extra work for the same backward op (the stage max-pool's backward)."""
+                g1, g2, g3, g4 = gouts
+                new = lambda t: eng.new_act(*t.shape)
+                dsrc = [new(x) for x in I.xs]
+                dmp = [new(x) for x in I.xs]
+                dy1, dy2r, dy2, dy3r, dy3a, dy3b, dy4 = (new(u.y) for u in (I.b1, I.b2r, I.b2, I.b3r, I.b3a, I.b3b, I.b4))
+                da2r, da3r, da3a = new(I.a2r), new(I.a3r), new(I.a3a)
+                n = len(I.xs)
+
+                def chain(conv, bn_unit, dy, da, dy_prev):
+                    """dy -> through `conv` -> relu(bn(bn_unit.y)) backward -> dy_prev."""
+                    if FUSE_DGRAD_BN:
+                        bn_unit.bn_backward_from_partial(eng, da, dy_prev, conv.dgrad_bn(eng, dy, da, bn_unit))
+                    else:
+                        conv.dgrad(dy, da)
+                        bn_unit.bn_backward(eng, da, None, da, dy_prev, relu_from_y=True)
+
+                def run():
+                    I.b1.bn_backward(eng, g1, I.y1, g1, dy1, relu_from_y=True)
+                    I.b1.wgrad(dy1)
+                    for t in range(n):
+                        I.b1.dgrad(dy1, t, dsrc[t])
+                    I.b2.bn_backward(eng, g2, I.y2, g2, dy2, relu_from_y=True)
+                    I.b2.wgrad(dy2)
+                    chain(I.b2, I.b2r, dy2, da2r, dy2r)
+                    I.b2r.wgrad(dy2r)
+                    for t in range(n):
+                        I.b2r.dgrad(dy2r, t, dsrc[t], add_src=dsrc[t])
+                    I.b3b.bn_backward(eng, g3, I.y3, g3, dy3b, relu_from_y=True)
+                    I.b3b.wgrad(dy3b)
+                    chain(I.b3b, I.b3a, dy3b, da3a, dy3a)
+                    I.b3a.wgrad(dy3a)
+                    chain(I.b3a, I.b3r, dy3a, da3r, dy3r)
+                    I.b3r.wgrad(dy3r)
+                    for t in range(n):
+                        I.b3r.dgrad(dy3r, t, dsrc[t], add_src=dsrc[t])
+                    I.b4.bn_backward(eng, g4, I.y4, g4, dy4, relu_from_y=True)
+                    I.b4.wgrad(dy4)
+                    for t in range(n):
+                        I.b4.dgrad(dy4, t, dmp[t])
+                        ops.maxpool3x3_bwd(dmp[t], I.mp[t][1], dsrc[t], 1, add=dsrc[t])
+                    if after is not None:
+                        after(dsrc)
+                ops_list.append(run)
+                return dsrc
+
+        def fwd_stem(training):
+            stem.fprop(self, True)
+            stem.bn_apply(self, training, a0)
+        F.append(fwd_stem)
+        srcs, H, W = [(a0, 192)], 32, 32
+        plan = []          # ("inc", Inception) | ("pool", [(x, pooled, arg)], H, W)
+        for d in spec["modules"]:
+            if d == "maxpool":
+                pooled = [(x, self.new_act(N, H // 2, W // 2, x.shape[-1]),
+                           torch.zeros(N, H // 2, W // 2, x.shape[-1], dtype=torch.uint8, device=self.device), c)
+                          for x, c in srcs]
+                plan.append(("pool", pooled))
+                F.append(lambda training, pooled=pooled: [ops.maxpool3x3_fwd(x, y, arg, 2) for x, y, arg, _ in pooled])
+                srcs, H, W = [(y, c) for _, y, _, c in pooled], H // 2, W // 2
+            else:
+                inc = Inception(d, srcs, H, W)
+                plan.append(("inc", inc))
+                F.append(inc.fwd)
+                srcs = inc.out
+        # head: the one place the concatenation exists
+        ctot = sum(c for _, c in srcs)
+        cat = self.new_act(N, H, W, ctot)
+        final = srcs
+
+        def fwd_cat(training):
+            off = 0
+            for t, c in final:
+                ops.copy_channels(t, 0, cat, off, c)
+                off += c
+        F.append(fwd_cat)
+        fwd_head, bwd_head, dcat = self._build_head(cat, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        gouts = [self.new_act(*t.shape) for t, _ in final]
+
+        def bwd_head_split(gouts=gouts):
+            bwd_head()
+            off = 0
+            for g, (t, c) in zip(gouts, final):
+                ops.copy_channels(dcat, off, g, 0, c)
+                off += c
+        Bk = [bwd_head_split]
+        for i in range(len(plan) - 1, -1, -1):
+            kind, item = plan[i]
+            if kind == "pool":
+                continue
+            after, gprev = None, None
+            if i > 0 and plan[i - 1][0] == "pool":      # this module reads max-pooled tensors: un-pool its input gradients
+                pooled = plan[i - 1][1]
+                gprev = [self.new_act(*x.shape) for x, _, _, _ in pooled]
+
+                def after(dsrc, pooled=pooled, gprev=gprev):
+                    for (x, y, arg, c), dpool, gx in zip(pooled, dsrc, gprev):
+                        ops.maxpool3x3_bwd(dpool, arg, gx, 2)
+            sub = []
+            dsrc = item.plan_bwd(gouts, sub, after)
+            Bk.append(lambda sub=sub: [f() for f in sub])
+            gouts = gprev if gprev is not None else dsrc
+        dy0 = self.new_act(*stem.y.shape)
+        d0 = gouts[0]
+
+        def bwd_stem():
+            stem.bn_backward(self, d0, a0, d0, dy0, relu_from_y=True)
             stem.wgrad(dy0)
         Bk.append(bwd_stem)
         self.bwd_ops = Bk

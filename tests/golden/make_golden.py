@@ -99,7 +99,8 @@ def golden_resnext():
                       ("regnetx_200mf", ref_rg.RegNetX_200MF), ("regnetx_400mf", ref_rg.RegNetX_400MF),
                       ("dla", __import__("models.dla", fromlist=["x"]).DLA),
                       ("senet18", __import__("models.senet", fromlist=["x"]).SENet18),
-                      ("regnety_400mf", ref_rg.RegNetY_400MF)):
+                      ("regnety_400mf", ref_rg.RegNetY_400MF),
+                      ("googlenet", __import__("models.googlenet", fromlist=["x"]).GoogLeNet)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

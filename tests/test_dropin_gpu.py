@@ -196,13 +196,13 @@ REFERENCE_CTORS = {"resnet18": ("resnet", "ResNet18", ()), "vgg16": ("vgg", "VGG
                    "simpledla": ("dla_simple", "SimpleDLA", ()), "mobilenet": ("mobilenet", "MobileNet", ()),
                    "resnext29_2x64d": ("resnext", "ResNeXt29_2x64d", ()), "resnext29_32x4d": ("resnext", "ResNeXt29_32x4d", ()),
                    "regnetx_200mf": ("regnet", "RegNetX_200MF", ()), "dla": ("dla", "DLA", ()),
-                   "senet18": ("senet", "SENet18", ())}
+                   "senet18": ("senet", "SENet18", ()), "googlenet": ("googlenet", "GoogLeNet", ())}
 
 
 @pytest.mark.parametrize("family", list(REFERENCE_CTORS))
 def test_the_references_own_classes(family):
     """accelerate() on modules built by the reference's OWN model files (models/resnet.py, vgg.py, preact_resnet.py,
-    mobilenetv2.py, mobilenet.py, dla_simple.py, dla.py, resnext.py, regnet.py, senet.py — the copies staged under oracle/_ref/reference by oracle/stage_reference.py; the
+    mobilenetv2.py, mobilenet.py, dla_simple.py, dla.py, resnext.py, regnet.py, senet.py, googlenet.py — the copies staged under oracle/_ref/reference by oracle/stage_reference.py; the
     GPU box has no /root/reference): the loop body of main.py:99-107 against the same module left on torch / cuDNN
     in fp32."""
     import importlib

@@ -147,6 +147,7 @@ def test_package_initialiser_matches_reference_order():
              (engine.regnetx_spec("RegNetX_400MF"), nets.build_regnetx_400mf_params),
              (engine.dla_spec(), nets.build_dla_params), (engine.simple_dla_spec(), nets.build_simpledla_params),
              (engine.senet_spec(), nets.build_senet_params), (engine.regnety_400mf_spec(), nets.build_regnety_400mf_params),
+             (engine.googlenet_spec(), nets.build_googlenet_params),
              (engine.mobilenet_spec(), nets.build_mobilenet_params)]
     for spec, build in cases:
         for seed in (0, 3):
@@ -199,7 +200,8 @@ def test_spec_from_the_references_own_modules():
              ("mobilenetv2", "MobileNetV2", ()), ("mobilenet", "MobileNet", ()), ("dla_simple", "SimpleDLA", ())] + \
             [("resnext", n, ()) for n in ("ResNeXt29_2x64d", "ResNeXt29_4x64d", "ResNeXt29_8x64d", "ResNeXt29_32x4d")] + \
             [("regnet", "RegNetX_200MF", ()), ("regnet", "RegNetX_400MF", ()), ("dla", "DLA", ()),
-             ("senet", "SENet18", ()), ("regnet", "RegNetY_400MF", ())]
+             ("senet", "SENet18", ()), ("regnet", "RegNetY_400MF", ()),
+             ("googlenet", "GoogLeNet", ())]
     for mod, ctor, args in cases:
         net = getattr(importlib.import_module("models." + mod), ctor)(*args)
         spec = spec_from_module(net)
@@ -208,6 +210,6 @@ def test_spec_from_the_references_own_modules():
         assert got == want, (mod, ctor)
         bufs = {n for n, _ in net.named_buffers() if not n.endswith("num_batches_tracked")}
         assert set(spec["buffers"]) == bufs, (mod, ctor)
-    for mod, ctor in (("googlenet", "GoogLeNet"), ("densenet", "DenseNet121"), ("lenet", "LeNet"), ("efficientnet", "EfficientNetB0")):
+    for mod, ctor in (("dpn", "DPN92"), ("densenet", "DenseNet121"), ("lenet", "LeNet"), ("efficientnet", "EfficientNetB0")):
         with pytest.raises(NotImplementedError):
             spec_from_module(getattr(importlib.import_module("models." + mod), ctor)())
