@@ -955,3 +955,68 @@ def googlenet_forward(x, params, buffers, training=True, taps=None):
         out = torch.cat([y1, y2, y3, y4], 1)                                          # :57
     out = F.avg_pool2d(out, 8, stride=1).view(out.size(0), -1)                        # :94-95
     return F.linear(out, params["linear.weight"], params["linear.bias"])
+
+
+# ------------------------------------------------------------------------------------------------
+# PreActResNet-50/101/152 (models/preact_resnet.py:36-61, PreActBottleneck)
+# ------------------------------------------------------------------------------------------------
+def _preact_bottleneck_blocks(num_blocks):
+    cin = 64
+    for li, (nb, planes) in enumerate(zip(num_blocks, RESNET_PLANES)):
+        for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+            yield f"layer{li + 1}.{bi}", cin, planes, 4 * planes, s
+            cin = 4 * planes
+
+
+def build_preact_bottleneck_params(seed, num_blocks=RESNET50_BLOCKS):
+    torch.manual_seed(seed)
+    params, buffers = OrderedDict(), OrderedDict()
+
+    def conv(name, cin, cout, k, stride):
+        m = nn.Conv2d(cin, cout, kernel_size=k, stride=stride, padding=k // 2, bias=False)
+        params[name + ".weight"] = m.weight.detach().clone()
+
+    def bn(name, c):
+        m = nn.BatchNorm2d(c)
+        params[name + ".weight"] = m.weight.detach().clone()
+        params[name + ".bias"] = m.bias.detach().clone()
+        buffers[name + ".running_mean"] = m.running_mean.clone()
+        buffers[name + ".running_var"] = m.running_var.clone()
+        buffers[name + ".num_batches_tracked"] = m.num_batches_tracked.clone()
+
+    conv("conv1", 3, 64, 3, 1)
+    cin_final = 64
+    for name, cin, planes, cout, s in _preact_bottleneck_blocks(num_blocks):
+        bn(name + ".bn1", cin)                                 # preact_resnet.py:42
+        conv(name + ".conv1", cin, planes, 1, 1)               # :43
+        bn(name + ".bn2", planes)
+        conv(name + ".conv2", planes, planes, 3, s)            # :45
+        bn(name + ".bn3", planes)
+        conv(name + ".conv3", planes, cout, 1, 1)              # :47
+        if s != 1 or cin != cout:                              # :49-52
+            conv(name + ".shortcut.0", cin, cout, 1, s)
+        cin_final = cout
+    lin = nn.Linear(cin_final, 10)
+    params["linear.weight"] = lin.weight.detach().clone()
+    params["linear.bias"] = lin.bias.detach().clone()
+    return params, buffers
+
+
+def preact_bottleneck_forward(x, params, buffers, training=True, num_blocks=RESNET50_BLOCKS, taps=None):
+    out = F.conv2d(x, params["conv1.weight"], padding=1)                                    # :85
+    if taps is not None:
+        taps["conv1"] = out
+    for name, cin, planes, cout, s in _preact_bottleneck_blocks(num_blocks):
+        xin = out
+        o = F.relu(_bn(xin, name + ".bn1", params, buffers, training))                      # :55
+        sc = F.conv2d(o, params[name + ".shortcut.0.weight"], stride=s) if (name + ".shortcut.0.weight") in params \
+            else xin                                                                        # :56
+        o = F.conv2d(o, params[name + ".conv1.weight"])                                     # :57
+        if taps is not None:
+            taps[name + ".conv1"] = o
+        o = F.conv2d(F.relu(_bn(o, name + ".bn2", params, buffers, training)), params[name + ".conv2.weight"], stride=s,
+                     padding=1)                                                             # :58
+        o = F.conv2d(F.relu(_bn(o, name + ".bn3", params, buffers, training)), params[name + ".conv3.weight"])   # :59
+        out = o + sc                                                                        # :60
+    out = F.avg_pool2d(out, 4).view(out.size(0), -1)
+    return F.linear(out, params["linear.weight"], params["linear.bias"])

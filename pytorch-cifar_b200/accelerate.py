@@ -62,9 +62,12 @@ def spec_from_module(net):
         return googlenet_spec(num_classes=net.linear.out_features)
     if _is(net, "PreActResNet") and hasattr(net, "layer4"):
         blocks = [len(getattr(net, f"layer{i}")) for i in range(1, 5)]
-        if not all(_is(b, "PreActBlock") for i in range(1, 5) for b in getattr(net, f"layer{i}")):
-            raise NotImplementedError("accelerate: only PreActBlock PreActResNets are supported")
-        return preact_resnet_spec(tuple(blocks), num_classes=net.linear.out_features)
+        kinds = {type(b).__name__ for i in range(1, 5) for b in getattr(net, f"layer{i}")}
+        if kinds == {"PreActBlock"}:
+            return preact_resnet_spec(tuple(blocks), num_classes=net.linear.out_features)
+        if kinds == {"PreActBottleneck"}:                 # PreActResNet-50/101/152
+            return preact_resnet_spec(tuple(blocks), num_classes=net.linear.out_features, bottleneck=True)
+        raise NotImplementedError(f"accelerate: unsupported PreActResNet block types {sorted(kinds)}")
     if _is(net, "VGG") and hasattr(net, "features") and hasattr(net, "classifier"):
         cfg = []
         for m in net.features:

@@ -102,11 +102,37 @@ def vgg_spec(name="VGG16", num_classes=10):
     return dict(family="vgg", params=params, buffers=buffers, layers=layers, num_classes=num_classes, feat=512)
 
 
-def preact_resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=10):
-    """PreActResNet-18/34 as models/preact_resnet.py:12-34,64-94 composes it."""
+def preact_resnet_spec(num_blocks=(2, 2, 2, 2), planes=(64, 128, 256, 512), num_classes=10, bottleneck=False):
+    """PreActResNet-18/34 as models/preact_resnet.py:12-34,64-94 composes it; bottleneck=True: PreActResNet-50/101/152
+    (PreActBottleneck, :36-61: bn1 -> relu -> conv1x1 -> bn2 -> relu -> conv3x3(stride) -> bn3 -> relu -> conv1x1 (x4),
+    += shortcut)."""
     params, buffers, blocks = OrderedDict(), OrderedDict(), []
     params["conv1.weight"] = (64, 3, 3, 3)
     in_planes = 64
+    if bottleneck:
+        def bn(name, c):
+            params[name + ".weight"] = (c,)
+            params[name + ".bias"] = (c,)
+            buffers[name + ".running_mean"] = (c,)
+            buffers[name + ".running_var"] = (c,)
+        for li, (nb, pl) in enumerate(zip(num_blocks, planes)):
+            for bi, s in enumerate([1 if li == 0 else 2] + [1] * (nb - 1)):
+                name, cout = f"layer{li + 1}.{bi}", 4 * pl
+                bn(name + ".bn1", in_planes)
+                params[name + ".conv1.weight"] = (pl, in_planes, 1, 1)
+                bn(name + ".bn2", pl)
+                params[name + ".conv2.weight"] = (pl, pl, 3, 3)
+                bn(name + ".bn3", pl)
+                params[name + ".conv3.weight"] = (cout, pl, 1, 1)
+                shortcut = s != 1 or in_planes != cout
+                if shortcut:
+                    params[name + ".shortcut.0.weight"] = (cout, in_planes, 1, 1)
+                blocks.append(dict(name=name, cin=in_planes, planes=pl, cout=cout, stride=s, shortcut=shortcut))
+                in_planes = cout
+        params["linear.weight"] = (num_classes, in_planes)
+        params["linear.bias"] = (num_classes,)
+        return dict(family="preact", params=params, buffers=buffers, blocks=blocks, num_classes=num_classes,
+                    feat=in_planes)
     for li, (nb, pl) in enumerate(zip(num_blocks, planes)):
         strides = [1 if li == 0 else 2] + [1] * (nb - 1)
         for bi, s in enumerate(strides):
@@ -652,6 +678,10 @@ def regnetx_400mf_spec(num_classes=10):
 
 def regnety_400mf_spec(num_classes=10):
     return regnetx_spec("RegNetY_400MF", num_classes)
+
+
+def preact_resnet50_spec(num_classes=10):
+    return preact_resnet_spec((3, 4, 6, 3), num_classes=num_classes, bottleneck=True)
 
 
 def resnext29_32x4d_spec(num_classes=10):
@@ -1666,6 +1696,8 @@ class Engine:
         F.append(lambda training: stem.fprop(self, True))
         x, H, W, producer = stem.y, 32, 32, stem
         nblk = len(spec["blocks"])
+        if spec["blocks"] and "planes" in spec["blocks"][0]:
+            return self._build_preact_bottleneck(stem, PreBN)
         for bi, b in enumerate(spec["blocks"]):
             name, cin, cout, s = b["name"], b["cin"], b["cout"], b["stride"]
             bn1 = PreBN(self, name + ".bn1", producer, cin, N * H * W)
@@ -1715,6 +1747,78 @@ class Engine:
                 else:
                     c1.dgrad(dy1, da)
                     bn1.bn_backward(self, da, a, da, dx, add=dout, relu_from_y=True)   # + gradient through the identity shortcut
+            Bk.append(bwd)
+            dout = dx
+        Bk.append(lambda dout=dout: stem.wgrad(dout))
+        self.bwd_ops = Bk
+
+    def _build_preact_bottleneck(self, stem, PreBN):
+        """models/preact_resnet.py:54-61 (PreActResNet-50/101/152): the pre-activation pattern of _build_preact with
+        three convs; conv3's epilogue adds the shortcut and emits the statistics of the next block's bn1."""
+        spec, N = self.spec, self.N
+        F, blocks = self.fwd_ops, []
+        x, H, W, producer = stem.y, 32, 32, stem
+        nblk = len(spec["blocks"])
+        for bi, b in enumerate(spec["blocks"]):
+            name, cin, pl, cout, s = b["name"], b["cin"], b["planes"], b["cout"], b["stride"]
+            bn1 = PreBN(self, name + ".bn1", producer, cin, N * H * W)
+            a = self.new_act(N, H, W, cin)
+            c1 = ConvUnit(self, name + ".conv1", name + ".bn2", a, cin, pl, 1, 1, H, W)
+            a2 = self.new_act(N, H, W, pl)
+            c2 = ConvUnit(self, name + ".conv2", name + ".bn3", a2, pl, pl, 3, s, H, W)
+            Ho, Wo = H // s, W // s
+            a3 = self.new_act(N, Ho, Wo, pl)
+            c3 = ConvUnit(self, name + ".conv3", None, a3, pl, cout, 1, 1, Ho, Wo)
+            cs = ConvUnit(self, name + ".shortcut.0", None, a, cin, cout, 1, s, H, W) if b["shortcut"] else None
+            last = bi == nblk - 1
+            self.units += [c1, c2, c3] + ([cs] if cs else [])
+            blocks.append((bn1, a, c1, a2, c2, a3, c3, cs, x))
+
+            def fwd(training, bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, a3=a3, c3=c3, cs=cs, x=x, producer=producer, last=last):
+                bn1.stat_rows = producer.stat_rows
+                bn1.bn_apply(self, training, a)
+                if cs is not None:
+                    self.run_side(lambda: cs.fprop(self, stats=False))
+                c1.fprop(self)
+                c1.bn_apply(self, training, a2)
+                c2.fprop(self)
+                c2.bn_apply(self, training, a3)
+                if cs is not None:
+                    self.join_side()
+                c3.fprop(self, stats=not last, add_src=(cs.y if cs is not None else x))
+            F.append(fwd)
+            x, H, W, producer = c3.y, Ho, Wo, c3
+        fwd_head, bwd_head, dout = self._build_head(x, H, W, "linear.weight", "linear.bias")
+        F.append(fwd_head)
+        Bk = [bwd_head]
+        for (bn1, a, c1, a2, c2, a3, c3, cs, xin) in reversed(blocks):
+            da3, dy2, da2, dy1 = (self.new_act(*t.shape) for t in (a3, c2.y, a2, c1.y))
+            da = self.new_act(*a.shape)
+            dx = self.new_act(*xin.shape)
+
+            def bwd(bn1=bn1, a=a, c1=c1, a2=a2, c2=c2, a3=a3, c3=c3, cs=cs, dout=dout, da3=da3, dy2=dy2, da2=da2,
+                    dy1=dy1, da=da, dx=dx):
+                c3.wgrad(dout)                              # d(conv3 out) = d(block out)
+                if FUSE_DGRAD_BN:
+                    c2.bn_backward_from_partial(self, da3, dy2, c3.dgrad_bn(self, dout, da3, c2))
+                else:
+                    c3.dgrad(dout, da3)
+                    c2.bn_backward(self, da3, a3, da3, dy2, relu_from_y=True)
+                c2.wgrad(dy2)
+                if FUSE_DGRAD_BN:
+                    c1.bn_backward_from_partial(self, da2, dy1, c2.dgrad_bn(self, dy2, da2, c1))
+                else:
+                    c2.dgrad(dy2, da2)
+                    c1.bn_backward(self, da2, a2, da2, dy1, relu_from_y=True)
+                c1.wgrad(dy1)
+                if cs is not None:
+                    cs.wgrad(dout)
+                    cs.dgrad(dout, da)
+                    c1.dgrad(dy1, da, add_src=da)
+                    bn1.bn_backward(self, da, a, da, dx, relu_from_y=True)
+                else:
+                    c1.dgrad(dy1, da)
+                    bn1.bn_backward(self, da, a, da, dx, add=dout, relu_from_y=True)   # + the identity shortcut
             Bk.append(bwd)
             dout = dx
         Bk.append(lambda dout=dout: stem.wgrad(dout))

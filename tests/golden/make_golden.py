@@ -100,7 +100,8 @@ def golden_resnext():
                       ("dla", __import__("models.dla", fromlist=["x"]).DLA),
                       ("senet18", __import__("models.senet", fromlist=["x"]).SENet18),
                       ("regnety_400mf", ref_rg.RegNetY_400MF),
-                      ("googlenet", __import__("models.googlenet", fromlist=["x"]).GoogLeNet)):
+                      ("googlenet", __import__("models.googlenet", fromlist=["x"]).GoogLeNet),
+                      ("preact50", __import__("models.preact_resnet", fromlist=["x"]).PreActResNet50)):
         torch.manual_seed(0)
         net = ctor()
         net.train()

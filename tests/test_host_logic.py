@@ -148,6 +148,7 @@ def test_package_initialiser_matches_reference_order():
              (engine.dla_spec(), nets.build_dla_params), (engine.simple_dla_spec(), nets.build_simpledla_params),
              (engine.senet_spec(), nets.build_senet_params), (engine.regnety_400mf_spec(), nets.build_regnety_400mf_params),
              (engine.googlenet_spec(), nets.build_googlenet_params),
+             (engine.preact_resnet50_spec(), nets.build_preact_bottleneck_params),
              (engine.mobilenet_spec(), nets.build_mobilenet_params)]
     for spec, build in cases:
         for seed in (0, 3):
@@ -197,6 +198,8 @@ def test_spec_from_the_references_own_modules():
     cases = [("resnet", n, ()) for n in ("ResNet18", "ResNet34", "ResNet50", "ResNet101", "ResNet152")] + \
             [("vgg", "VGG", (v,)) for v in ("VGG11", "VGG13", "VGG16", "VGG19")] + \
             [("preact_resnet", "PreActResNet18", ()), ("preact_resnet", "PreActResNet34", ()),
+             ("preact_resnet", "PreActResNet50", ()), ("preact_resnet", "PreActResNet101", ()),
+             ("preact_resnet", "PreActResNet152", ()),
              ("mobilenetv2", "MobileNetV2", ()), ("mobilenet", "MobileNet", ()), ("dla_simple", "SimpleDLA", ())] + \
             [("resnext", n, ()) for n in ("ResNeXt29_2x64d", "ResNeXt29_4x64d", "ResNeXt29_8x64d", "ResNeXt29_32x4d")] + \
             [("regnet", "RegNetX_200MF", ()), ("regnet", "RegNetX_400MF", ()), ("dla", "DLA", ()),

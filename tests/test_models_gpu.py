@@ -171,6 +171,7 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           # shows the same median gradient error (1.04 vs our 1.02)
           "mobilenet": dict(logits=0.45, near=0.3, near_cos=0.95, min_cos=None, drop=0.95, lr=0.02),
           "simpledla": dict(logits=0.12, near=0.12, near_cos=0.99, min_cos=None, drop=0.9, lr=0.02),
+          "preact50": dict(logits=0.3, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
           "googlenet": dict(logits=0.12, near=0.15, near_cos=0.98, min_cos=None, drop=0.9, lr=0.02),
           # SENet18: measured 0.65 % on the logits (profiles/r2_parity/parity_senet18.json)
           "senet18": dict(logits=0.03, near=0.06, near_cos=0.99, min_cos=0.7, drop=0.9, lr=0.02),
@@ -217,6 +218,8 @@ MODELS = {
     # GoogLeNet (models/googlenet.py): Inception modules, concatenations read through per-tensor maps, 3x3 max-pools
     "googlenet": ("googlenet_spec", "build_googlenet_params", "googlenet_forward", "pre_layers.0",
                   ["linear.weight", "b5.b1.1.weight", "b5.b4.2.bias"]),
+    "preact50": ("preact_resnet50_spec", "build_preact_bottleneck_params", "preact_bottleneck_forward", "conv1",
+                 ["linear.weight", "layer4.2.conv3.weight", "layer4.2.bn3.weight"]),
     # SENet18 (models/senet.py): pre-activation blocks with squeeze-and-excitation
     "senet18": ("senet_spec", "build_senet_params", "senet_forward", "conv1",
                 ["linear.weight", "layer4.1.fc2.weight", "layer4.1.conv2.weight"]),

@@ -12,7 +12,8 @@ MODELS = [("resnet18", "resnet_spec", 1024), ("vgg16", "vgg_spec", 1024), ("prea
           ("mobilenet", "mobilenet_spec", 512), ("resnext29_2x64d", "resnext_spec", 512),
           ("regnetx_200mf", "regnetx_spec", 512), ("regnetx_400mf", "regnetx_400mf_spec", 512),
           ("dla", "dla_spec", 1024), ("senet18", "senet_spec", 1024),
-          ("regnety_400mf", "regnety_400mf_spec", 512), ("googlenet", "googlenet_spec", 256)]
+          ("regnety_400mf", "regnety_400mf_spec", 512), ("googlenet", "googlenet_spec", 256),
+          ("preact_resnet50", "preact_resnet50_spec", 256)]
 steps, warm = 30, 5
 images, labels = data.synthetic_cifar(8192, seed=0)
 out = []
