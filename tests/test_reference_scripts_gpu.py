@@ -53,10 +53,12 @@ def compare(acc, ref, steps):
     assert abs(ck["plain_eval_loss"] - mean_test) < 0.1          # the saved weights in a plain fp32 model
 
 
-@pytest.mark.parametrize("model", ["dla_simple.SimpleDLA", "resnet.ResNet18"])
+@pytest.mark.parametrize("model", ["dla_simple.SimpleDLA", "resnet.ResNet18", "senet.SENet18", "googlenet.GoogLeNet",
+                                   "resnext.ResNeXt29_2x64d"])
 def test_main_py_unmodified(tmp_path, model):
     """main.py: 428 samples = 3 batches of 128 + a ragged 44, then test() on 2 x 100 and the checkpoint.
-    SimpleDLA is the network main.py:71 itself constructs; ResNet-18 is the benchmarked one (main.py:58)."""
+    SimpleDLA is the network main.py:71 itself constructs; ResNet-18 is the benchmarked one (main.py:58); SENet18,
+    GoogLeNet and ResNeXt29_2x64d are three more of the constructors main.py:57-70 offers."""
     args = ["--lr", "0.02"]
     acc = run(tmp_path, "main_acc", "main.py", False, args, model=model)
     ref = run(tmp_path, "main_ref", "main.py", True, args, model=model)
