@@ -69,6 +69,13 @@ typedef struct B2cConvDesc {
                                instead of one row per CTA; *stat_rows = 1. The consumers are b2c_bn_act_apply_stats /
                                b2c_bn_bwd_apply_stats, which finalize the statistics themselves (no finalize launch).
                                Sums of ~148 per-CTA partials in arrival order: run-to-run differences of a few ulp. */
+    int x_ld;        /* channel pitch (elements, multiple of 8) of the input-side tensors x / dx; 0 = cin */
+    int y_ld;        /* channel pitch of the output-side tensors y / dy / the fprop's add_src; 0 = cout. With a pitch
+                        wider than the channel count the pointers address a CHANNEL SLICE of a wider tensor: one group of
+                        nn.Conv2d(C, C, 3, groups=g) (models/resnext.py:19) is the conv {cin = cout = C/g, x_ld = y_ld = C}
+                        on x + j*C/g, y + j*C/g. Per-CTA statistic rows keep pitch cout (use flags bit 9 and offset
+                        part_sum / part_sq to accumulate a slice of a wider BatchNorm); not for b2c_conv_dgrad_bn,
+                        b2c_conv1x1_cat*_fprop or a 1x1 stride-2 dgrad without add_src. */
 } B2cConvDesc;
 
 /* y[n,ho,wo,cout] = conv(x, w). Replaces nn.Conv2d.forward -> aten::convolution (cuDNN)

@@ -29,7 +29,7 @@ class ConvDesc(ctypes.Structure):
     """Mirror of B2cConvDesc (include/b2c.h)."""
     _fields_ = [(n, ctypes.c_int) for n in
                 ("n", "h", "w", "cin", "cout", "ksize", "stride", "cin_valid", "cout_valid", "kflat_cin", "block_n", "max_ctas",
-                 "flags")]
+                 "flags", "x_ld", "y_ld")]
 
 
 class BnStats(ctypes.Structure):

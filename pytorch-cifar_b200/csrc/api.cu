@@ -40,13 +40,17 @@ EncodeTiledFn get_encode() {
 }
 
 // NHWC bf16 tensor [n, h, w, c] -> 4-D map, box {64 ch, bw, bh, bn} pixels, traversal stride `es` on w/h.
-int encode_nhwc(CUtensorMap* m, const void* base, int n, int h, int w, int c, int bw, int bh, int bn, int es) {
+// ld: channel pitch of the tensor in memory (0 = c): a channel slice of a wider tensor is the same map with the
+// slice's base pointer and the wide tensor's pitch.
+int encode_nhwc(CUtensorMap* m, const void* base, int n, int h, int w, int c, int bw, int bh, int bn, int es,
+                int ld = 0) {
     EncodeTiledFn enc = get_encode();
     if (enc == nullptr) return B2C_ERR_DRIVER;
+    if (ld == 0) ld = c;
     cuuint64_t dims[4] = {static_cast<cuuint64_t>(c), static_cast<cuuint64_t>(w), static_cast<cuuint64_t>(h),
                           static_cast<cuuint64_t>(n)};
-    cuuint64_t strides[3] = {static_cast<cuuint64_t>(c) * 2, static_cast<cuuint64_t>(w) * c * 2,
-                             static_cast<cuuint64_t>(h) * w * c * 2};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(ld) * 2, static_cast<cuuint64_t>(w) * ld * 2,
+                             static_cast<cuuint64_t>(h) * w * ld * 2};
     cuuint32_t box[4] = {64u, static_cast<cuuint32_t>(bw * es), static_cast<cuuint32_t>(bh * es),
                          static_cast<cuuint32_t>(bn)};
     cuuint32_t estr[4] = {1u, static_cast<cuuint32_t>(es), static_cast<cuuint32_t>(es), 1u};
@@ -61,13 +65,14 @@ int encode_nhwc(CUtensorMap* m, const void* base, int n, int h, int w, int c, in
 // TMA unit fetch the whole 2*bw bounding row from L2 and drop every other pixel (ncu: 604 MB of L2->SM reads
 // for 302 MB of operand on the 64->128 stride-2 layer). The H axis keeps the traversal stride (rows are
 // separate lines anyway). Dims {c, parity, w/2, h, n}; coordinates of pixel column w: (w & 1, w >> 1).
-int encode_nhwc_s2(CUtensorMap* m, const void* base, int n, int h, int w, int c, int bw, int bh, int bn) {
+int encode_nhwc_s2(CUtensorMap* m, const void* base, int n, int h, int w, int c, int bw, int bh, int bn, int ld = 0) {
     EncodeTiledFn enc = get_encode();
     if (enc == nullptr) return B2C_ERR_DRIVER;
+    if (ld == 0) ld = c;
     cuuint64_t dims[5] = {static_cast<cuuint64_t>(c), 2u, static_cast<cuuint64_t>(w / 2), static_cast<cuuint64_t>(h),
                           static_cast<cuuint64_t>(n)};
-    cuuint64_t strides[4] = {static_cast<cuuint64_t>(c) * 2, static_cast<cuuint64_t>(c) * 4,
-                             static_cast<cuuint64_t>(w) * c * 2, static_cast<cuuint64_t>(h) * w * c * 2};
+    cuuint64_t strides[4] = {static_cast<cuuint64_t>(ld) * 2, static_cast<cuuint64_t>(ld) * 4,
+                             static_cast<cuuint64_t>(w) * ld * 2, static_cast<cuuint64_t>(h) * w * ld * 2};
     cuuint32_t box[5] = {64u, 1u, static_cast<cuuint32_t>(bw), static_cast<cuuint32_t>(bh * 2),
                          static_cast<cuuint32_t>(bn)};
     cuuint32_t estr[5] = {1u, 1u, 1u, 2u, 1u};
@@ -123,9 +128,9 @@ bool use_halo(const B2cConvDesc* d) {
     return d->w == 32 || d->w == 16 || d->w == 8;
 }
 
-int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w, int gemm_n, int bn, bool flip,
-                void* out, const void* add_src, float* part_sum, float* part_sq, int* stat_rows, cudaStream_t st,
-                const BnFuse* bn_fuse = nullptr) {
+int launch_halo(const B2cConvDesc* d, const void* act, int act_c, int act_ld, const void* w, int gemm_n, int out_ld,
+                int bn, bool flip, void* out, const void* add_src, float* part_sum, float* part_sq, int* stat_rows,
+                cudaStream_t st, const BnFuse* bn_fuse = nullptr) {
     b2c::HaloParams p = {};
     p.N = d->n;
     p.H = d->h;
@@ -140,7 +145,7 @@ int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w,
     p.b_rows_per_tap = gemm_n;
     p.out = static_cast<__nv_bfloat16*>(out);
     p.add_src = static_cast<const __nv_bfloat16*>(add_src);
-    p.out_ld = gemm_n;
+    p.out_ld = out_ld;
     p.part_sum = part_sum;
     p.part_sq = part_sq;
     p.cout = gemm_n;
@@ -158,8 +163,8 @@ int launch_halo(const B2cConvDesc* d, const void* act, int act_c, const void* w,
     if (acc) p.stat_ld = 0;
     p.debug = d->flags & 0x3e;
     CUtensorMap ma, mb;
-    int rc = p.mode == 0 ? encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 18, 1, 1)
-                         : encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 8, 2, 1);
+    int rc = p.mode == 0 ? encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 18, 1, 1, act_ld)
+                         : encode_nhwc(&ma, act, d->n, d->h, d->w, act_c, 10, 8, 2, 1, act_ld);
     if (rc) return rc;
     const bool pair = (d->flags & 128) != 0;      // CTA-pair kernel (conv_halo2.cu): each CTA loads half a weight tile
     rc = encode_2d(&mb, w, 9LL * gemm_n, act_c, pair ? bn / 2 : bn);
@@ -193,8 +198,14 @@ int check_conv(const B2cConvDesc* d) {
     if (d->stride != 1 && d->stride != 2) return B2C_ERR_UNSUPPORTED;
     if (d->stride == 2 && ((d->h & 1) || (d->w & 1))) return B2C_ERR_UNSUPPORTED;
     if (d->block_n != 0 && d->block_n != 64 && d->block_n != 128 && d->block_n != 256) return B2C_ERR_ARG;
+    if (d->x_ld != 0 && (d->x_ld < d->cin || (d->x_ld & 7))) return B2C_ERR_ARG;
+    if (d->y_ld != 0 && (d->y_ld < d->cout || (d->y_ld & 7))) return B2C_ERR_ARG;
     return 0;
 }
+
+// channel pitch of the input-side tensor (x, dx) and of the output-side tensor (y, dy, add_src of the fprop)
+inline int x_pitch(const B2cConvDesc* d) { return d->x_ld != 0 ? d->x_ld : d->cin; }
+inline int y_pitch(const B2cConvDesc* d) { return d->y_ld != 0 ? d->y_ld : d->cout; }
 
 }  // namespace
 
@@ -229,7 +240,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     if (d->cout % bn) return B2C_ERR_UNSUPPORTED;
     const int taps = d->ksize * d->ksize;
     if (halo)
-        return launch_halo(d, x, d->cin, w_fprop, d->cout, bn, false, y, add_src, part_sum, part_sq, stat_rows,
+        return launch_halo(d, x, d->cin, x_pitch(d), w_fprop, d->cout, y_pitch(d), bn, false, y, add_src, part_sum, part_sq, stat_rows,
                            as_stream(stream));
 
     TapGemmParams p = {};
@@ -252,7 +263,7 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     p.add_src = static_cast<const __nv_bfloat16*>(add_src);
     p.out_H = ho;
     p.out_W = wo;
-    p.out_ld = d->cout;
+    p.out_ld = y_pitch(d);
     p.sy = p.sx = 1;
     single_phase(p);
     p.part_sum = part_sum;
@@ -265,8 +276,8 @@ int b2c_conv_fprop(const B2cConvDesc* d, const void* x, const void* w_fprop, voi
     const int bnb = 128 / (wo * bh);
     CUtensorMap ma, mb;
     p.a_split_w = d->stride == 2 && !(d->flags & 4);      // flags & 4: traversal-stride map (A/B measurements)
-    rc = p.a_split_w ? encode_nhwc_s2(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb)
-                     : encode_nhwc(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
+    rc = p.a_split_w ? encode_nhwc_s2(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, x_pitch(d))
+                     : encode_nhwc(&ma, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride, x_pitch(d));
     if (rc) return rc;
     const bool pair = (d->flags & 128) != 0;      // CTA-pair kernel (conv_gemm2.cu): each CTA loads half a weight tile
     rc = encode_2d(&mb, w_fprop, static_cast<long long>(taps) * d->cout, d->cin, pair ? bn / 2 : bn);
@@ -374,7 +385,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     const int max_ctas = d->max_ctas > 0 ? d->max_ctas : 148;
     cudaStream_t st = as_stream(stream);
     if (halo)
-        return launch_halo(d, dy, d->cout, w_dgrad, d->cin, bn, true, dx, add_src, nullptr, nullptr, nullptr, st,
+        return launch_halo(d, dy, d->cout, y_pitch(d), w_dgrad, d->cin, x_pitch(d), bn, true, dx, add_src, nullptr, nullptr, nullptr, st,
                            bn_fuse);
 
     TapGemmParams p = {};
@@ -385,7 +396,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     p.add_src = static_cast<const __nv_bfloat16*>(add_src);
     p.out_H = d->h;
     p.out_W = d->w;
-    p.out_ld = d->cin;
+    p.out_ld = x_pitch(d);
     p.part_sum = nullptr;
     p.part_sq = nullptr;
     p.cout = d->cin;
@@ -411,7 +422,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         if (!grid_tiles(d->h, d->w, 128)) return B2C_ERR_UNSUPPORTED;
         const int bh = (128 / d->w) < d->h ? (128 / d->w) : d->h;
         const int bnb = 128 / (d->w * bh);
-        rc = encode_nhwc(&ma, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+        rc = encode_nhwc(&ma, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1, y_pitch(d));
         if (rc) return rc;
         p.m_total = d->n * d->h * d->w;
         p.num_m_tiles = (p.m_total + 127) / 128;
@@ -438,7 +449,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
     if (!grid_tiles(ho, wo, 128)) return B2C_ERR_UNSUPPORTED;
     const int bh = (128 / wo) < ho ? (128 / wo) : ho;
     const int bnb = 128 / (wo * bh);
-    rc = encode_nhwc(&ma, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+    rc = encode_nhwc(&ma, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1, y_pitch(d));
     if (rc) return rc;
     p.m_total = d->n * ho * wo;
     p.num_m_tiles = (p.m_total + 127) / 128;
@@ -449,6 +460,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
         if (bn_fuse != nullptr) return B2C_ERR_UNSUPPORTED;
         if (add_src != nullptr && add_src != dx) return B2C_ERR_UNSUPPORTED;
         if (add_src == nullptr) {
+            if (x_pitch(d) != d->cin) return B2C_ERR_UNSUPPORTED;      // (the zero fill assumes a dense dx)
             cudaError_t e = cudaMemsetAsync(dx, 0, static_cast<size_t>(d->n) * d->h * d->w * d->cin * 2, st);
             if (e != cudaSuccess) return cuda_rc(e);
         }
@@ -484,7 +496,7 @@ static int conv_dgrad_impl(const B2cConvDesc* d, const void* dy, const void* dy_
             if (np == 0 && dy_shortcut != nullptr) {
                 // the 1x1 stride-2 shortcut conv reads x[2i, 2j]: its dgrad lands on phase (0, 0) only, as one more
                 // tap whose A operand is the shortcut's dy and whose weights are slab 9 of the B matrix
-                rc = encode_nhwc(&ma1, dy_shortcut, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+                rc = encode_nhwc(&ma1, dy_shortcut, d->n, ho, wo, d->cout, wo, bh, bnb, 1, y_pitch(d));
                 if (rc) return rc;
                 p.tap_dh[nt] = 0;
                 p.tap_dw[nt] = 0;
@@ -554,9 +566,9 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
             hp.splits = (hp.num_tiles + hp.tiles_per_split - 1) / hp.tiles_per_split;
             hp.partial = scratch;
             CUtensorMap mx, mdy;
-            rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, 10, 18, 1, 1);
+            rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, 10, 18, 1, 1, x_pitch(d));
             if (rc) return rc;
-            rc = encode_nhwc(&mdy, dy, d->n, d->h, d->w, d->cout, 8, 16, 1, 1);
+            rc = encode_nhwc(&mdy, dy, d->n, d->h, d->w, d->cout, 8, 16, 1, 1, y_pitch(d));
             if (rc) return rc;
             hp.tco = (d->flags & 32) ? 1 : 0;
             return cuda_rc(b2c::launch_wgrad_halo(mx, mdy, hp, dw, as_stream(stream)));
@@ -587,9 +599,9 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
         rp.steps_per_split = (rp.num_steps + splits - 1) / splits;
         rp.splits = (rp.num_steps + rp.steps_per_split - 1) / rp.steps_per_split;
         CUtensorMap mx, mdy;
-        rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, d->w + 2, w16 ? 4 : 8, 1, 1);
+        rc = encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, d->w + 2, w16 ? 4 : 8, 1, 1, x_pitch(d));
         if (rc) return rc;
-        rc = encode_nhwc(&mdy, dy, d->n, d->h, d->w, d->cout, d->w, w16 ? 4 : 8, 1, 1);
+        rc = encode_nhwc(&mdy, dy, d->n, d->h, d->w, d->cout, d->w, w16 ? 4 : 8, 1, 1, y_pitch(d));
         if (rc) return rc;
         if (pair) return cuda_rc(b2c::launch_wgrad_row2(mx, mdy, rp, w16 ? 1 : 0, as_stream(stream)));
         return cuda_rc(b2c::launch_wgrad_row(mx, mdy, rp, w16 ? 1 : 0, as_stream(stream)));
@@ -655,10 +667,10 @@ int b2c_conv_wgrad(const B2cConvDesc* d, const void* x, const void* dy, float* d
     CUtensorMap mx, mdy;
     p.debug = d->flags & 0x18;
     p.x_split_w = d->stride == 2 && !(d->flags & 4);
-    rc = p.x_split_w ? encode_nhwc_s2(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb)
-                     : encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride);
+    rc = p.x_split_w ? encode_nhwc_s2(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, x_pitch(d))
+                     : encode_nhwc(&mx, x, d->n, d->h, d->w, d->cin, wo, bh, bnb, d->stride, x_pitch(d));
     if (rc) return rc;
-    rc = encode_nhwc(&mdy, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1);
+    rc = encode_nhwc(&mdy, dy, d->n, ho, wo, d->cout, wo, bh, bnb, 1, y_pitch(d));
     if (rc) return rc;
     return cuda_rc(b2c::launch_wgrad(bn, mx, mdy, p, as_stream(stream)));
 }

@@ -33,8 +33,10 @@ def _need(t, dtype, name):
 
 
 def conv_desc(n, h, w, cin, cout, ksize, stride, cin_valid=0, kflat_cin=0, block_n=0, max_ctas=0, flags=0,
-              cout_valid=0):
-    return ConvDesc(n, h, w, cin, cout, ksize, stride, cin_valid, cout_valid, kflat_cin, block_n, max_ctas, flags)
+              cout_valid=0, x_ld=0, y_ld=0):
+    """x_ld / y_ld: channel pitch of the input- / output-side tensors when they are channel slices of wider ones."""
+    return ConvDesc(n, h, w, cin, cout, ksize, stride, cin_valid, cout_valid, kflat_cin, block_n, max_ctas, flags,
+                    x_ld, y_ld)
 
 
 def pack_weight_fprop(w_oihw):

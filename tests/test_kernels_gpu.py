@@ -1146,3 +1146,43 @@ def test_conv1x1_over_a_concat_of_different_widths(ops, shape):
     assert _guards_intact(whole, pad, 555.0)
     assert torch.isfinite(to_nchw(y)).all() and rel_err(to_nchw(y), ref) < BF16_TOL
     assert rel_err(pq[:rows].sum(0), (ref * ref).sum((0, 2, 3))) < F32_TOL
+
+
+@pytest.mark.parametrize("shape", [(6, 32, 128, 2, 1), (5, 16, 256, 4, 1), (9, 8, 512, 8, 1), (4, 16, 256, 2, 2),
+                                   (3, 32, 128, 2, 2), (7, 8, 256, 2, 1)])
+def test_grouped_conv_on_channel_slices(ops, shape):
+    """B2cConvDesc.x_ld / y_ld: one group of nn.Conv2d(C, C, 3, stride, padding=1, groups=g) (models/resnext.py:19) is
+    the dense C/g -> C/g conv on a channel slice of the C-wide tensors — forward with statistics accumulated into the
+    slice of one row, data gradient into a slice of dx (nothing outside the slice is written), weight gradient from
+    the two slices — against fp32 torch on the same bf16 inputs."""
+    n, hw, C, g, stride = shape
+    cg, ho = C // g, hw // stride
+    x, dy = nhwc_bf16(n, hw, hw, C, 180), nhwc_bf16(n, ho, ho, C, 181)
+    w = weight(C, cg, 3, 182)
+    y = torch.full((n, ho, ho, C), 7.0, device="cuda", dtype=torch.bfloat16)
+    dx = torch.full((n, hw, hw, C), 7.0, device="cuda", dtype=torch.bfloat16)
+    stats = torch.zeros(2, C, device="cuda")
+    dw = torch.zeros(C, cg, 3, 3, device="cuda")
+    scratch = torch.zeros(ops.WGRAD_SCRATCH_FLOATS, device="cuda")
+    d = ops.conv_desc(n, hw, hw, cg, cg, 3, stride, flags=128 | 512, x_ld=C, y_ld=C)
+    dwd = ops.conv_desc(n, hw, hw, cg, cg, 3, stride, x_ld=C, y_ld=C)
+    for j in (g - 1, 0):                           # all groups but one: the untouched slice must stay untouched
+        wj = w[j * cg:(j + 1) * cg]
+        xs, ys = x.view(-1)[j * cg:], y.view(-1)[j * cg:]
+        ops.conv_fprop(d, xs, ops.pack_weight_fprop(wj), ys, stats[0, j * cg:], stats[1, j * cg:])
+        ops.conv_dgrad(d, dy.view(-1)[j * cg:], ops.pack_weight_dgrad(wj), dx.view(-1)[j * cg:])
+        ops.conv_wgrad(dwd, xs, dy.view(-1)[j * cg:], dw[j * cg:(j + 1) * cg], scratch=scratch)
+    torch.cuda.synchronize()
+    xr, wr = to_nchw(x).requires_grad_(), w.clone().requires_grad_()
+    yr = F.conv2d(xr, wr, stride=stride, padding=1, groups=g)
+    yr.backward(to_nchw(dy))
+    for j in (g - 1, 0):
+        sl = slice(j * cg, (j + 1) * cg)
+        assert rel_err(to_nchw(y)[:, sl], yr.detach()[:, sl]) < BF16_TOL
+        assert rel_err(to_nchw(dx)[:, sl], xr.grad[:, sl]) < BF16_TOL
+        assert rel_err(dw[sl], wr.grad[sl]) < 2e-3
+        assert rel_err(stats[1, sl], (yr.detach()[:, sl] ** 2).sum((0, 2, 3))) < F32_TOL
+    if g > 2:
+        mid = slice(cg, (g - 1) * cg)
+        assert (y[..., mid] == 7.0).all() and (dx[..., mid] == 7.0).all() and (stats[:, mid] == 0).all()
+        assert (dw[mid] == 0).all()
