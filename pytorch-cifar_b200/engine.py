@@ -704,6 +704,9 @@ ASYNC_WGRAD = os.environ.get("B2C_ASYNC_WGRAD", "1") != "0"
 # instruction issue, not by HBM, and the transform (fma + max + border select per loaded value, three loads per
 # output) doubles their instruction count, which costs more than the saved 4 B per element. Off by default.
 DW_FUSED_INPUT = os.environ.get("B2C_DW_FUSED_INPUT", "0") != "0"
+# 1 = a grouped conv whose group width is a multiple of 64 (ResNeXt29_2x64d / 4x64d / 8x64d) runs one dense conv per
+# group on channel slices; 0 = always the dense conv over block-diagonal operands (g x the FLOPs)
+GROUP_SLICES = os.environ.get("B2C_GROUP_SLICES", "1") != "0"
 # CTA-pair (tcgen05.mma.cta_group::2) fprop / dgrad kernels: "halo" = where the halo kernel runs (3x3 stride 1 on
 # 32/16/8-pixel images), "all" = the per-tap kernel's shapes too, "0" = single-CTA kernels everywhere
 CTA_PAIR = os.environ.get("B2C_CTA_PAIR", "all")
@@ -831,7 +834,23 @@ class ConvUnit(_BNOps):
                                         flags=(32 | (128 if CTA_PAIR != "0" else 0)) if tco_out else 0)
         self.eng_scratch = eng.wgrad_scratch
         self.eng = eng
-        if self.groups > 1:
+        self.sliced = self.groups > 1 and name in eng.group_ops
+        if self.sliced:
+            # one dense conv per group on channel slices of x / y (see _layout_params); statistics are accumulated
+            # into this unit's own row (every group adds its slice), which forward() zero-fills
+            g, cg_in, cg_out = self.groups, cin_p // self.groups, cout_p // self.groups
+            eng.zero_stats_each_forward = True
+            self.g_desc = ops.conv_desc(N, H, W, cg_in, cg_out, k, stride, flags=(128 if pair else 0) | 512,
+                                        x_ld=cin_p, y_ld=cout_p)
+            self.g_desc_w = ops.conv_desc(N, H, W, cg_in, cg_out, k, stride, x_ld=cin_p, y_ld=cout_p)
+            self.g_wf = [eng.WF[a:a + sf[0] * sf[1] * sf[2]].view(sf) for a, _, sf, _ in eng.group_ops[name]]
+            self.g_wd = [eng.WD[b:b + sd[0] * sd[1] * sd[2]].view(sd) for _, b, _, sd in eng.group_ops[name]]
+            dwf = eng.grad_flat(name + ".weight")                      # [cout][cin/g][kh][kw]: group j = rows j*cout/g..
+            per = cg_out * cg_in * k * k
+            self.g_dw = [dwf[j * per:(j + 1) * per] for j in range(g)]
+            self.g_in = [j * cg_in for j in range(g)]
+            self.g_out = [j * cg_out for j in range(g)]
+        elif self.groups > 1:
             eng.grouped_dense(k * k * cin_p * cout_p)
         # BatchNorm partial-sum scratch: shared by the units of the main chain (used strictly one after the other);
         # a shortcut conv that runs concurrently on the side stream gets its own
@@ -841,9 +860,13 @@ class ConvUnit(_BNOps):
         else:
             self.ps, self.pq = eng.part_sum, eng.part_sq
         self.fsum = eng.new_stat(2 * cout_p, forward=True)     # statistics of y (also read by a PreAct block's bn1)
-        self.wf = eng.wf_view(name)
-        self.wd = None if stem else eng.wd_view(name)
-        self.wd10 = None if stem else eng.wd10_view(name)
+        if self.sliced:
+            self.ps, self.pq = self.fsum[:cout_p], self.fsum[cout_p:]
+            self.wf = self.wd = self.wd10 = None
+        else:
+            self.wf = eng.wf_view(name)
+            self.wd = None if stem else eng.wd_view(name)
+            self.wd10 = None if stem else eng.wd10_view(name)
         self.dw = eng.grad_flat(name + ".weight")      # storage order: OIHW, or [tap][cin][cout] (eng.tco)
         # a conv bias (VGG) is never added to y — the BatchNorm cancels it — but the running mean tracks it
         self.conv_bias = eng.param_view(name + ".bias") if (name + ".bias") in eng.p_off else None
@@ -852,6 +875,16 @@ class ConvUnit(_BNOps):
 
     # ---- forward pieces
     def fprop(self, eng, stats=True, add_src=None):
+        if self.sliced:
+            C = self.cout
+            xf, yf = self.x.view(-1), self.y.view(-1)
+            af = add_src.view(-1) if add_src is not None else None
+            for j, (ci, co) in enumerate(zip(self.g_in, self.g_out)):
+                ops.conv_fprop(self.g_desc, xf[ci:], self.g_wf[j], yf[co:],
+                               self.fsum[co:C] if stats else None, self.fsum[C + co:] if stats else None,
+                               add_src=af[co:] if af is not None else None)
+            self.stat_rows = 1
+            return
         if FUSED_FINALIZE:
             ps, pq = (self.fsum[:self.cout], self.fsum[self.cout:]) if stats else (None, None)
         else:
@@ -860,6 +893,11 @@ class ConvUnit(_BNOps):
 
     # ---- backward pieces
     def wgrad(self, dy):
+        if self.sliced:
+            xf, dyf = self.x.view(-1), dy.view(-1)
+            self.eng.run_side(lambda: [ops.conv_wgrad(self.g_desc_w, xf[ci:], dyf[co:], dw, scratch=self.eng_scratch)
+                                       for ci, co, dw in zip(self.g_in, self.g_out, self.g_dw)])
+            return
         if self.groups > 1:
             # dense [tap][cin][cout] gradient of the block-diagonal operand, then its diagonal blocks -> dw
             cin, cout = self.cin_true, self.cout_true        # the dense matrix has the true channel counts (cin_valid)
@@ -874,6 +912,12 @@ class ConvUnit(_BNOps):
         self.eng.run_side(lambda: ops.conv_wgrad(self.desc_w, self.x, dy, self.dw, scratch=self.eng_scratch))
 
     def dgrad(self, dy, dx, add_src=None):
+        if self.sliced:
+            dyf, dxf = dy.view(-1), dx.view(-1)
+            af = add_src.view(-1) if add_src is not None else None
+            for j, (ci, co) in enumerate(zip(self.g_in, self.g_out)):
+                ops.conv_dgrad(self.g_desc, dyf[co:], self.g_wd[j], dxf[ci:], af[ci:] if af is not None else None)
+            return
         ops.conv_dgrad(self.desc, dy, self.wd, dx, add_src)
 
     def dgrad_bn(self, eng, dy, dz, bn_unit, add_src=None):
@@ -1050,6 +1094,7 @@ class Engine:
         self._stat_used = [0, 0]
         self.fwd_ops, self.bwd_ops = [], []
         self.stem_taps = 9
+        self.zero_stats_each_forward = False
         if spec["family"] == "resnet":
             self._build_resnet()
         elif spec["family"] == "vgg":
@@ -1099,6 +1144,7 @@ class Engine:
             and shape[0] % 4 == 0 and shape[1] % 2 == 0}
         self.wd_pair = {}      # 3x3 stride-2 conv1 -> its block's 1x1 shortcut conv, stored right behind it in WD
         self.wd_slabs = {}     # 1x1 conv over a ragged concatenation -> [(offset, shape)] of its per-source dgrad operands
+        self.group_ops = {}    # grouped conv run group by group -> [(wf offset, wd offset, wf shape, wd shape)]
         wf_n = wd_n = 0
         convs = [(name, shape) for name, shape in spec["params"].items() if len(shape) == 4 and name not in not_conv]
         # A down-sampling block's `conv1` (3x3) and `shortcut.0` (1x1) read the same input and have the same
@@ -1152,6 +1198,19 @@ class Engine:
                                     cin_pad=cin_p, cout_pad=cout_p, kflat=2))
                 wf_n += ns * cout_p * cin_p
                 wd_n += ns * cout_p * cin_p
+            elif name in grouped and GROUP_SLICES and cin % 64 == 0 and (cout // grouped[name]) % 64 == 0:
+                # nn.Conv2d(groups=g) with group widths on the 64-channel grid: one dense cin/g -> cout/g conv per
+                # group on a channel slice of the activations (B2cConvDesc.x_ld / y_ld); its operands are the group's
+                # rows of the [cout][cin/g][kh][kw] master, which are a dense OIHW weight of their own
+                g = grouped[name]
+                cin_g, cout_g = cin, cout // g
+                self.group_ops[cname] = []
+                for j in range(g):
+                    self.group_ops[cname].append((wf_n, wd_n, (k * k, cout_g, cin_g), (k * k, cin_g, cout_g)))
+                    entries.append(dict(src_off=poff + j * cout_g * cin_g * k * k, wf_off=wf_n, wd_off=wd_n,
+                                        cout=cout_g, cin=cin_g, taps=k * k, cin_pad=cin_g, cout_pad=cout_g, kflat=0))
+                    wf_n += cout_g * cin_g * k * k
+                    wd_n += cout_g * cin_g * k * k
             elif name in grouped:
                 # nn.Conv2d(groups=g): master [cout][cin/g][kh][kw]; the operands are those of the dense cin -> cout
                 # conv, filled block-diagonally by one entry per group (off-diagonal blocks stay zero)
@@ -2202,9 +2261,9 @@ class Engine:
                     c3.dgrad(dy3, da2)
                     c2.bn_backward(self, da2, a2, da2, dy2, relu_from_y=True)
                 c2.wgrad(dy2)
-                if FUSE_DGRAD_BN:
+                if FUSE_DGRAD_BN and not c2.sliced:
                     c1.bn_backward_from_partial(self, da1, dy1, c2.dgrad_bn(self, dy2, da1, c1))
-                else:
+                else:       # (a conv run group by group has no fused dgrad + BatchNorm-backward epilogue)
                     c2.dgrad(dy2, da1)
                     c1.bn_backward(self, da1, a1, da1, dy1, relu_from_y=True)
                 c1.wgrad(dy1)
@@ -2395,8 +2454,8 @@ class Engine:
 
     # ------------------------------------------------------------------ execution
     def forward(self, training=True):
-        if FUSED_FINALIZE or self.spec["family"] == "senet":      # (senet: statistics of materialised tensors, see there)
-            self._stat_f.zero_()
+        if FUSED_FINALIZE or self.spec["family"] == "senet" or self.zero_stats_each_forward:
+            self._stat_f.zero_()      # (senet: statistics of materialised tensors; grouped convs run group by group)
         for op in self.fwd_ops:
             op(training)
         return self.logits
