@@ -68,7 +68,7 @@ def test_c_abi_exports_every_declared_symbol():
     l = _lib.load()
     assert l.b2c_version() >= 100
     assert b"not supported" in l.b2c_error_string(_lib.B2C_ERR_UNSUPPORTED)
-    assert ctypes.sizeof(_lib.ConvDesc) == 52 and ctypes.sizeof(_lib.RepackEntry) == 48
+    assert ctypes.sizeof(_lib.ConvDesc) == 60 and ctypes.sizeof(_lib.RepackEntry) == 48
 
 
 def test_spec_parameter_counts_match_the_reference():
