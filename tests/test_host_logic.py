@@ -97,7 +97,7 @@ def test_c_abi_rejects_bad_arguments_without_touching_the_gpu():
 
     def desc(**kw):
         base = dict(n=4, h=32, w=32, cin=64, cout=64, ksize=3, stride=1, cin_valid=0, cout_valid=0, kflat_cin=0,
-                    block_n=0, max_ctas=0, flags=0)
+                    block_n=0, max_ctas=0, flags=0, x_ld=0, y_ld=0)
         base.update(kw)
         return _lib.ConvDesc(*[base[f] for f, _ in _lib.ConvDesc._fields_])
 
@@ -105,6 +105,8 @@ def test_c_abi_rejects_bad_arguments_without_touching_the_gpu():
     fprop, dgrad, wgrad = raw("b2c_conv_fprop"), raw("b2c_conv_dgrad"), raw("b2c_conv_wgrad")
     U, A = _lib.B2C_ERR_UNSUPPORTED, _lib.B2C_ERR_ARG
     assert fprop(None, fake, fake, fake, None, None, None, ctypes.byref(rows), None) == A
+    for bad in (dict(x_ld=32), dict(y_ld=68)):          # a pitch below the channel count / off the 16-byte grid
+        assert fprop(ctypes.byref(desc(**bad)), fake, fake, fake, None, None, None, ctypes.byref(rows), None) == A, bad
     for bad in (dict(cin=48), dict(cout=96 + 8), dict(ksize=5), dict(stride=3), dict(stride=2, h=31)):
         assert fprop(ctypes.byref(desc(**bad)), fake, fake, fake, None, None, None, ctypes.byref(rows), None) == U, bad
     assert fprop(ctypes.byref(desc(block_n=96)), fake, fake, fake, None, None, None, ctypes.byref(rows), None) == A
