@@ -611,6 +611,14 @@ def resnext_32x4d_forward(x, params, buffers, training=True, taps=None):
     return resnext_forward(x, params, buffers, training, cardinality=32, bottleneck_width=4, taps=taps)
 
 
+def resnext_4x64d_forward(x, params, buffers, training=True, taps=None):
+    return resnext_forward(x, params, buffers, training, cardinality=4, bottleneck_width=64, taps=taps)
+
+
+def build_resnext_4x64d_params(seed):
+    return build_resnext_params(seed, cardinality=4, bottleneck_width=64)
+
+
 def build_resnext_32x4d_params(seed):
     return build_resnext_params(seed, cardinality=32, bottleneck_width=4)
 

@@ -684,6 +684,10 @@ def preact_resnet50_spec(num_classes=10):
     return preact_resnet_spec((3, 4, 6, 3), num_classes=num_classes, bottleneck=True)
 
 
+def resnext29_4x64d_spec(num_classes=10):
+    return resnext_spec(cardinality=4, bottleneck_width=64, num_classes=num_classes)
+
+
 def resnext29_32x4d_spec(num_classes=10):
     return resnext_spec(cardinality=32, bottleneck_width=4, num_classes=num_classes)
 

@@ -145,6 +145,7 @@ def test_package_initialiser_matches_reference_order():
              (engine.resnet50_spec(), nets.build_bottleneck_params),
              (engine.resnext_spec(), nets.build_resnext_params),
              (engine.resnext_spec(cardinality=32, bottleneck_width=4), nets.build_resnext_32x4d_params),
+             (engine.resnext29_4x64d_spec(), nets.build_resnext_4x64d_params),
              (engine.regnetx_spec("RegNetX_200MF"), nets.build_regnetx_params),
              (engine.regnetx_spec("RegNetX_400MF"), nets.build_regnetx_400mf_params),
              (engine.dla_spec(), nets.build_dla_params), (engine.simple_dla_spec(), nets.build_simpledla_params),

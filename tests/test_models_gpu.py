@@ -181,6 +181,9 @@ BOUNDS = {"vgg16": dict(logits=5e-2, near=6e-2, near_cos=0.99, min_cos=0.7, drop
           # ResNeXt-29 (29 convs, grouped 3x3, 8x8 final maps): measured 1.6 % / 1.9 % on the logits
           # (profiles/r2_parity/parity_resnext29_*.json); this batch's loss rises before it falls, for the oracle too
           "resnext29_2x64d": dict(logits=0.06, near=0.3, near_cos=0.95, min_cos=None, drop=0.9, lr=0.02),
+          # (4 groups run group by group; at lr 0.02 the fp32 oracle's loss on this batch climbs 2.5 -> 22.7 and ours
+          # follows it to three digits, profiles/r2_parity/train_curve_resnext29_4x64d_lr0.02.json: lr 0.002 here)
+          "resnext29_4x64d": dict(logits=0.06, near=0.3, near_cos=0.95, min_cos=None, drop=0.995, lr=0.002),
           "resnext29_32x4d": dict(logits=0.06, near=0.3, near_cos=0.95, min_cos=None, drop=0.9, lr=0.02),
           # RegNetX (41 / 68 convs; widths 24..384 padded to the 64-channel layout; 3..46 groups per conv)
           # measured 5.1 % / 4.8 % on the logits (profiles/r2_parity/parity_regnetx_*.json). With lr 0.02 the fp32 oracle's
@@ -203,6 +206,8 @@ MODELS = {
                   ["linear.weight", "layers.12.bn2.weight", "layers.12.bn2.bias"]),
     # ResNeXt-29 (models/resnext.py): 1x1 stem, grouped 3x3 convs (2 groups of 64.. / 32 groups of 4..), avg_pool2d(8)
     "resnext29_2x64d": ("resnext_spec", "build_resnext_params", "resnext_forward", "conv1",
+                        ["linear.weight", "layer3.2.bn3.weight", "layer3.2.bn3.bias"]),
+    "resnext29_4x64d": ("resnext29_4x64d_spec", "build_resnext_4x64d_params", "resnext_4x64d_forward", "conv1",
                         ["linear.weight", "layer3.2.bn3.weight", "layer3.2.bn3.bias"]),
     "resnext29_32x4d": ("resnext29_32x4d_spec", "build_resnext_32x4d_params", "resnext_32x4d_forward", "conv1",
                         ["linear.weight", "layer3.2.bn3.weight", "layer3.2.bn3.bias"]),

@@ -9,7 +9,7 @@ from b200cifar import data, engine, trainer
 
 MODELS = [("resnet18", "resnet_spec", 1024), ("vgg16", "vgg_spec", 1024), ("preact_resnet18", "preact_resnet_spec", 1024),
           ("mobilenetv2", "mobilenetv2_spec", 512), ("resnet50", "resnet50_spec", 256), ("simpledla", "simple_dla_spec", 1024),
-          ("mobilenet", "mobilenet_spec", 512), ("resnext29_2x64d", "resnext_spec", 512),
+          ("mobilenet", "mobilenet_spec", 512), ("resnext29_2x64d", "resnext_spec", 512), ("resnext29_4x64d", "resnext29_4x64d_spec", 256),
           ("regnetx_200mf", "regnetx_spec", 512), ("regnetx_400mf", "regnetx_400mf_spec", 512),
           ("dla", "dla_spec", 1024), ("senet18", "senet_spec", 1024),
           ("regnety_400mf", "regnety_400mf_spec", 512), ("googlenet", "googlenet_spec", 256),
