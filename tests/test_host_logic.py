@@ -125,6 +125,26 @@ def test_c_abi_rejects_bad_arguments_without_touching_the_gpu():
     assert raw("b2c_bn_bwd_partial_rows")(1 << 20, 64) == 148 * 4
     assert raw("b2c_bn_bwd_partial_rows")(10, 64) == 1
     assert raw("b2c_bn_bwd_partial_rows")(10, 12) == U
+    # entry points added for the wider model zoo: shapes off the vector grid, pitches below the channel count, ...
+    assert raw("b2c_maxpool3x3_fwd")(fake, fake, fake, 4, 32, 32, 64, 3, None) == U               # stride 3
+    assert raw("b2c_maxpool3x3_fwd")(fake, fake, fake, 4, 32, 32, 60, 1, None) == U               # channels % 8
+    assert raw("b2c_maxpool3x3_bwd")(fake, None, None, fake, 4, 32, 32, 64, 1, None) == A         # no argmax
+    assert raw("b2c_copy_channels")(fake, 64, 32, fake, 64, 0, 10, 64, None) == U                 # slice past the pitch
+    assert raw("b2c_copy_channels")(fake, 64, 0, odd, 64, 0, 10, 64, None) == A
+    assert raw("b2c_grouped_wgrad_extract")(fake, fake, 128, 128, 9, 3, None) == A                # 128 % 3
+    assert raw("b2c_head_fwd_ld")(fake, 4, 64, 368, 360, fake, fake, 10, fake, fake, None) == U   # pitch < channels
+    assert raw("b2c_se_fwd")(fake, 4, 64, 128, 100, 8, fake, fake, fake, fake, fake, fake, fake, None, fake, None) == U
+    assert raw("b2c_se_bwd")(fake, None, 4, 64, 128, 128, 8, *([fake] * 12), fake, None) == A     # no y
+    d1 = desc(ksize=1, cin=128)
+    ptrs = (ctypes.c_void_p * 4)(0x10000, 0x10000, 0x10000, 0x10000)
+    cat_n, cat_r = raw("b2c_conv1x1_catn_fprop"), raw("b2c_conv1x1_catr_fprop")
+    assert cat_n(ctypes.byref(d1), ptrs, 5, fake, fake, None, None, ctypes.byref(rows), None) == U      # > 4 sources
+    assert cat_n(ctypes.byref(desc(cin=128)), ptrs, 4, fake, fake, None, None, ctypes.byref(rows), None) == U   # 3x3
+    cins = (ctypes.c_int * 4)(64, 192, 64, 64)
+    assert cat_r(ctypes.byref(d1), ptrs, cins, 4, fake, fake, None, None, ctypes.byref(rows), None) == U   # wider than d.cin
+    cins = (ctypes.c_int * 4)(64, 96, 64, 64)
+    assert cat_r(ctypes.byref(d1), ptrs, cins, 4, fake, fake, None, None, ctypes.byref(rows), None) == U   # 96 % 64
+    assert cat_r(ctypes.byref(d1), ptrs, None, 4, fake, fake, None, None, ctypes.byref(rows), None) == A
     noalloc = raw("b2c_bn_bwd_stats_noalloc")
     args = [fake, None, fake, None, 1024, 1024, 1024.0] + [fake] * 8 + [None]
     assert noalloc(*args) == _lib.B2C_ERR_TOO_LARGE
